@@ -1,0 +1,95 @@
+// C ABI for convolution and batched GEMM (see include/odvae_b200.h).
+#include "common.cuh"
+#include "engine_host.h"
+
+using namespace odvae;
+
+extern "C" {
+
+int odvae_conv2d_tc_supported(int B, int H, int W, int CinP, int CoutP, int geom) {
+  EngineDesc d;
+  if (describe_conv_fwd(d, nullptr, nullptr, nullptr, nullptr, nullptr, B, H, W, CinP, CoutP, CoutP, geom, 0) != ODVAE_OK) return 0;
+  if (!d.tc_ok) return 0;
+  EngineDesc ds[4];
+  int n = 0;
+  if (describe_conv_dgrad(ds, &n, nullptr, nullptr, 2, nullptr, nullptr, B, H, W, CinP, CoutP, geom) != ODVAE_OK) return 0;
+  for (int i = 0; i < n; ++i)
+    if (!ds[i].tc_ok) return 0;
+  if (describe_conv_wgrad(d, nullptr, nullptr, nullptr, B, H, W, CinP, CoutP, geom, ODVAE_IMPL_TC) != ODVAE_OK) return 0;
+  return d.tc_ok ? 1 : 0;
+}
+
+int odvae_conv2d_fwd(const void* x, const void* w_packed, const float* bias, const void* residual, void* y, int B,
+                     int H, int W, int CinP, int CoutP, int Cout, int geom, int act_dtype, int impl, int out_nchw_f32,
+                     void* stream) {
+  EngineDesc d;
+  int st = describe_conv_fwd(d, x, w_packed, bias, residual, y, B, H, W, CinP, CoutP, Cout, geom, out_nchw_f32);
+  if (st != ODVAE_OK) return st;
+  return run_engine(d, impl, act_dtype, static_cast<cudaStream_t>(stream));
+}
+
+int odvae_conv2d_dgrad(const void* dy, const void* w_packed_dgrad, const void* dx_add, void* dx, int B, int H, int W,
+                       int CinP, int CoutP, int geom, int act_dtype, int impl, void* stream) {
+  EngineDesc ds[4];
+  int n = 0;
+  int st = describe_conv_dgrad(ds, &n, dy, w_packed_dgrad, act_dtype == ODVAE_BF16 ? 2 : 4, dx_add, dx, B, H, W, CinP,
+                               CoutP, geom);
+  if (st != ODVAE_OK) return st;
+  for (int i = 0; i < n; ++i) {
+    st = run_engine(ds[i], impl, act_dtype, static_cast<cudaStream_t>(stream));
+    if (st != ODVAE_OK) return st;
+  }
+  return ODVAE_OK;
+}
+
+size_t odvae_conv2d_wgrad_workspace_bytes(int B, int H, int W, int CinP, int CoutP, int geom, int impl) {
+  EngineDesc d;
+  if (describe_conv_wgrad(d, nullptr, nullptr, nullptr, B, H, W, CinP, CoutP, geom, impl) != ODVAE_OK) return 0;
+  const size_t part = static_cast<size_t>(d.p.num_z) * CoutP * CinP * sizeof(float);
+  return part + colsum_workspace_bytes(CoutP) + 256;
+}
+
+int odvae_conv2d_wgrad(const void* x, const void* dy, float* dw_oihw, float* db, int B, int H, int W, int CinP,
+                       int CoutP, int Cin, int Cout, int geom, int act_dtype, int impl, int accumulate,
+                       void* workspace, size_t ws_bytes, void* stream) {
+  cudaStream_t s = static_cast<cudaStream_t>(stream);
+  EngineDesc d;
+  float* ws = reinterpret_cast<float*>(workspace);
+  int st = describe_conv_wgrad(d, x, dy, ws, B, H, W, CinP, CoutP, geom, impl);
+  if (st != ODVAE_OK) return st;
+  const size_t part = static_cast<size_t>(d.p.num_z) * CoutP * CinP * sizeof(float);
+  if (ws_bytes < part + colsum_workspace_bytes(CoutP)) return ODVAE_ERR_WORKSPACE;
+  st = run_engine(d, impl, act_dtype, s);
+  if (st != ODVAE_OK) return st;
+  st = launch_wgrad_reduce(ws, dw_oihw, Cout, Cin, d.p.ntaps, CoutP, CinP, d.p.split_k, accumulate, s);
+  if (st != ODVAE_OK) return st;
+  if (db != nullptr) {
+    const int Ho = geom == ODVAE_CONV_3x3_S2 ? H / 2 : H, Wo = geom == ODVAE_CONV_3x3_S2 ? W / 2 : W;
+    float* cpart = reinterpret_cast<float*>(reinterpret_cast<uint8_t*>(workspace) + ((part + 255) / 256) * 256);
+    st = launch_colsum(dy, static_cast<long long>(B) * Ho * Wo, Cout, CoutP, act_dtype, db, accumulate, cpart, s);
+  }
+  return st;
+}
+
+int odvae_gemm_bf16(const void* A, const void* B, void* D, int M, int N, int K, int batch, int64_t lda, int64_t ldb,
+                    int64_t ldd, int64_t strideA, int64_t strideB, int64_t strideD, int a_mn, int b_mn, int out_dtype,
+                    float alpha, const float* bias, const void* residual, void* stream) {
+  EngineDesc d;
+  int st = describe_gemm(d, A, B, D, M, N, K, batch, lda, ldb, ldd, strideA, strideB, strideD, a_mn, b_mn,
+                         out_dtype == ODVAE_F32 ? OUT_F32 : OUT_BF16, alpha, bias, residual);
+  if (st != ODVAE_OK) return st;
+  return run_engine(d, ODVAE_IMPL_TC, ODVAE_BF16, static_cast<cudaStream_t>(stream));
+}
+
+int odvae_gemm_simt(const void* A, const void* B, void* D, int M, int N, int K, int batch, int64_t lda, int64_t ldb,
+                    int64_t ldd, int64_t strideA, int64_t strideB, int64_t strideD, int a_mn, int b_mn, int in_dtype,
+                    int out_dtype, float alpha, const float* bias, const void* residual, void* stream) {
+  EngineDesc d;
+  // out_dtype: ODVAE_F32 -> fp32 output; otherwise the activation dtype (= in_dtype)
+  int st = describe_gemm(d, A, B, D, M, N, K, batch, lda, ldb, ldd, strideA, strideB, strideD, a_mn, b_mn,
+                         (out_dtype == ODVAE_F32 && in_dtype != ODVAE_F32) ? OUT_F32 : OUT_BF16, alpha, bias, residual);
+  if (st != ODVAE_OK) return st;
+  return run_engine(d, ODVAE_IMPL_SIMT, in_dtype, static_cast<cudaStream_t>(stream));
+}
+
+}  // extern "C"

@@ -1,0 +1,52 @@
+// Problem description shared by the tcgen05 engine and the SIMT validation engine.
+#pragma once
+#include <stdint.h>
+
+namespace odvae {
+
+enum { KIND_GEMM = 0, KIND_CONV = 1, KIND_WGRAD = 2 };
+enum { OUT_BF16 = 0, OUT_F32 = 1, OUT_NCHW_F32 = 2 };
+
+struct TcParams {
+  int kind, a_mn, b_mn, BN, stages;
+  int num_m_tiles, num_n_tiles, num_z;  // z: GEMM batch | CONV 1 | WGRAD ntaps*split_k
+  int num_k_iters;
+  // spatial operand (CONV: A, WGRAD: B): coords (c, x, [ph], y, b)
+  int sp_rank, cchunks, ntaps;
+  int tap_dx[9], tap_dy[9], tap_c[9], tap_ph[9];
+  // CONV m-tile geometry (box bw x bh = 128 output pixels)
+  int bw_log2, tiles_x, tiles_y;
+  // WGRAD k-chunk geometry (box kbw x kbh = 64 output pixels)
+  int kbw_log2, kch_x, kch_y, split_k, kch_per_split;
+  // epilogue
+  int out_mode, n_valid, m_valid, out_h, out_w;
+  long long ldd, strideD, oB, oY, oX, o0;
+  float alpha;
+  const float* bias;
+  const void* residual;
+  void* D;
+};
+
+
+// Strided view of an operand (elements, innermost dimension first, strides[0] == 1).
+//   spatial operands: rank 4 (C, W, H, B) or rank 5 (2C, W/2, 2, H/2, B) for the stride-2 phase view
+//   GEMM operands   : rank 3 (inner, outer, batch)
+struct OperandView {
+  const void* ptr;
+  int rank;
+  long long dims[5];
+  long long strides[5];
+};
+
+struct EngineDesc {
+  TcParams p;
+  OperandView A, B;
+  uint32_t boxA[5], boxB[5];  // TMA boxes (tcgen05 engine only)
+  int tc_ok;                  // shapes satisfy the tcgen05 engine's tiling constraints
+  // SIMT-only geometry (does not depend on TMA boxes)
+  int conv_out_h, conv_out_w, conv_batch;  // output pixel grid of the gather (CONV: rows, WGRAD: K)
+  int chan_per_tap;
+  long long gemm_lda, gemm_ldb, gemm_k, gemm_n, gemm_strideA, gemm_strideB;
+};
+
+}  // namespace odvae

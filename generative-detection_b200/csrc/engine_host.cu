@@ -1,0 +1,485 @@
+// Host side of the GEMM/conv engines: problem description, TMA tensor maps, tile/BN/split choice,
+// launches of the tcgen05 engine (bf16) and of the SIMT validation engine (f32 or bf16).
+#include <cuda.h>
+#include <cudaTypedefs.h>
+
+#include <mutex>
+
+#include "engine_host.h"
+#include "simt_engine.cuh"
+#include "tc_engine.cuh"
+
+namespace odvae {
+
+// ---------------------------------------------------------------------------------------------
+// cuTensorMapEncodeTiled via the runtime's driver entry point (no link-time libcuda dependency)
+// ---------------------------------------------------------------------------------------------
+typedef CUresult (*EncodeTiledFn)(CUtensorMap*, CUtensorMapDataType, cuuint32_t, void*, const cuuint64_t*,
+                                  const cuuint64_t*, const cuuint32_t*, const cuuint32_t*, CUtensorMapInterleave,
+                                  CUtensorMapSwizzle, CUtensorMapL2promotion, CUtensorMapFloatOOBfill);
+
+static EncodeTiledFn get_encode_fn() {
+  static EncodeTiledFn fn = nullptr;
+  static std::once_flag once;
+  std::call_once(once, [] {
+    void* ptr = nullptr;
+    cudaDriverEntryPointQueryResult qres;
+    cudaError_t e = cudaGetDriverEntryPoint("cuTensorMapEncodeTiled", &ptr, cudaEnableDefault, &qres);
+    if (e == cudaSuccess && qres == cudaDriverEntryPointSuccess) fn = reinterpret_cast<EncodeTiledFn>(ptr);
+  });
+  return fn;
+}
+
+static int make_tmap_bf16(CUtensorMap* tm, const OperandView& v, const uint32_t* box) {
+  EncodeTiledFn fn = get_encode_fn();
+  if (!fn) {
+    set_last_cuda_error(cudaErrorUnknown, "cuTensorMapEncodeTiled entry point unavailable");
+    return ODVAE_ERR_CUDA;
+  }
+  cuuint64_t gdim[5];
+  cuuint64_t gstr[4];
+  cuuint32_t bx[5];
+  cuuint32_t es[5];
+  for (int i = 0; i < v.rank; ++i) {
+    gdim[i] = static_cast<cuuint64_t>(v.dims[i]);
+    bx[i] = box[i];
+    es[i] = 1;
+  }
+  for (int i = 1; i < v.rank; ++i) {
+    gstr[i - 1] = static_cast<cuuint64_t>(v.strides[i]) * 2;
+    if (gstr[i - 1] % 16 != 0) return ODVAE_ERR_SHAPE;
+  }
+  if ((reinterpret_cast<uintptr_t>(v.ptr) & 15) != 0) return ODVAE_ERR_SHAPE;
+  CUresult r = fn(tm, CU_TENSOR_MAP_DATA_TYPE_BFLOAT16, static_cast<cuuint32_t>(v.rank), const_cast<void*>(v.ptr),
+                  gdim, gstr, bx, es, CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_128B,
+                  CU_TENSOR_MAP_L2_PROMOTION_L2_256B, CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
+  if (r != CUDA_SUCCESS) {
+    set_last_cuda_error(cudaErrorInvalidValue, "cuTensorMapEncodeTiled failed");
+    return ODVAE_ERR_CUDA;
+  }
+  return ODVAE_OK;
+}
+
+static int pick_bn(long long n) {
+  const int cands[] = {256, 128, 64, 32, 16};
+  for (int c : cands)
+    if (n % c == 0) return c;
+  return 0;
+}
+static bool is_pow2(int v) { return v > 0 && (v & (v - 1)) == 0; }
+static int ilog2(int v) {
+  int l = 0;
+  while ((1 << l) < v) ++l;
+  return l;
+}
+
+static size_t tc_smem_bytes(int stages, int BN) {
+  return static_cast<size_t>(stages) * (TC_A_BYTES + static_cast<size_t>(BN) * 128) + (2 * stages + 4) * 8 + 16 + 1024;
+}
+static int tc_pick_stages(int BN, int num_k_iters) {
+  const size_t budget = 200 * 1024;
+  int s = static_cast<int>((budget - 2048) / (TC_A_BYTES + static_cast<size_t>(BN) * 128));
+  if (s > 8) s = 8;
+  if (s > num_k_iters) s = num_k_iters;
+  if (s < 1) s = 1;
+  return s;
+}
+
+static int launch_tc(EngineDesc& d, cudaStream_t stream) {
+  if (!d.tc_ok) return ODVAE_ERR_SHAPE;
+  CUtensorMap tmA, tmB;
+  int st = make_tmap_bf16(&tmA, d.A, d.boxA);
+  if (st != ODVAE_OK) return st;
+  st = make_tmap_bf16(&tmB, d.B, d.boxB);
+  if (st != ODVAE_OK) return st;
+  TcParams& p = d.p;
+  p.stages = tc_pick_stages(p.BN, p.num_k_iters);
+  const size_t smem = tc_smem_bytes(p.stages, p.BN);
+  static std::once_flag once;
+  static cudaError_t attr_err = cudaSuccess;
+  std::call_once(once, [] {
+    attr_err = cudaFuncSetAttribute(tc_engine_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, 227 * 1024);
+  });
+  if (attr_err != cudaSuccess) {
+    set_last_cuda_error(attr_err, "cudaFuncSetAttribute(tc_engine_kernel)");
+    return ODVAE_ERR_CUDA;
+  }
+  const long long total = static_cast<long long>(p.num_m_tiles) * p.num_n_tiles * p.num_z;
+  if (total <= 0 || p.num_k_iters <= 0) return ODVAE_ERR_SHAPE;
+  int grid = num_sms();
+  if (total < grid) grid = static_cast<int>(total);
+  tc_engine_kernel<<<grid, TC_THREADS, smem, stream>>>(tmA, tmB, p);
+  return check_launch("tc_engine_kernel");
+}
+
+static int launch_simt(const EngineDesc& d, int act_dtype, cudaStream_t stream) {
+  SimtParams s = {};
+  s.p = d.p;
+  s.A = d.A;
+  s.B = d.B;
+  const TcParams& p = d.p;
+  s.out_h = d.conv_out_h;
+  s.out_w = d.conv_out_w;
+  s.lda = d.gemm_lda;
+  s.ldb = d.gemm_ldb;
+  if (p.kind == KIND_GEMM) {
+    s.M = p.m_valid;
+    s.N = p.n_valid;
+    s.K = d.gemm_k;
+    s.strideA = d.gemm_strideA;
+    s.strideB = d.gemm_strideB;
+  } else if (p.kind == KIND_CONV) {
+    s.M = static_cast<long long>(d.conv_batch) * d.conv_out_h * d.conv_out_w;
+    s.N = d.gemm_n;
+    s.chan_per_tap = d.chan_per_tap;
+    s.K = static_cast<long long>(p.ntaps) * d.chan_per_tap;
+  } else {
+    s.M = p.m_valid;
+    s.N = p.n_valid;
+    s.K = static_cast<long long>(d.conv_batch) * d.conv_out_h * d.conv_out_w;
+    s.k_per_split = (s.K + p.split_k - 1) / p.split_k;
+  }
+  dim3 grid(static_cast<unsigned>((s.N + 63) / 64), static_cast<unsigned>((s.M + 63) / 64), static_cast<unsigned>(p.num_z));
+  if (grid.y > 65535 || grid.z > 65535) return ODVAE_ERR_SHAPE;
+  if (act_dtype == ODVAE_BF16)
+    simt_engine_kernel<bf16><<<grid, 256, 0, stream>>>(s);
+  else
+    simt_engine_kernel<float><<<grid, 256, 0, stream>>>(s);
+  return check_launch("simt_engine_kernel");
+}
+
+int run_engine(EngineDesc& d, int impl, int act_dtype, cudaStream_t stream) {
+  if (impl == ODVAE_IMPL_TC) {
+    if (act_dtype != ODVAE_BF16) return ODVAE_ERR_SHAPE;
+    return launch_tc(d, stream);
+  }
+  return launch_simt(d, act_dtype, stream);
+}
+
+// ---------------------------------------------------------------------------------------------
+// Batched GEMM description
+// ---------------------------------------------------------------------------------------------
+int describe_gemm(EngineDesc& d, const void* A, const void* B, void* D, int M, int N, int K, int batch, long long lda,
+                  long long ldb, long long ldd, long long strideA, long long strideB, long long strideD, int a_mn,
+                  int b_mn, int out_mode, float alpha, const float* bias, const void* residual) {
+  if (M <= 0 || N <= 0 || K <= 0 || batch <= 0) return ODVAE_ERR_SHAPE;
+  d = EngineDesc{};
+  TcParams& p = d.p;
+  int BN = pick_bn(N);
+  if (BN == 0) BN = N < 64 ? ((N + 15) / 16) * 16 : 64;
+  if (b_mn && (BN % 64 != 0)) BN = 64;
+  d.tc_ok = 1;
+  if (lda % 8 || ldb % 8) d.tc_ok = 0;
+  if (batch > 1 && (strideA % 8 || strideB % 8)) d.tc_ok = 0;
+  if (out_mode == OUT_BF16 && (ldd % 8 != 0 || strideD % 8 != 0)) d.tc_ok = 0;
+  if (out_mode == OUT_F32 && (ldd % 4 != 0 || strideD % 4 != 0)) d.tc_ok = 0;
+  const long long bsA = batch > 1 ? strideA : lda * (a_mn ? K : M);
+  const long long bsB = batch > 1 ? strideB : ldb * (b_mn ? K : N);
+  d.A.ptr = A;
+  d.A.rank = 3;
+  d.A.strides[0] = 1;
+  d.A.strides[1] = lda;
+  d.A.strides[2] = bsA;
+  d.A.dims[2] = batch;
+  if (!a_mn) {
+    d.A.dims[0] = K;
+    d.A.dims[1] = M;
+    d.boxA[0] = 64; d.boxA[1] = 128; d.boxA[2] = 1;
+  } else {
+    d.A.dims[0] = M;
+    d.A.dims[1] = K;
+    d.boxA[0] = 64; d.boxA[1] = 64; d.boxA[2] = 1;
+  }
+  d.B.ptr = B;
+  d.B.rank = 3;
+  d.B.strides[0] = 1;
+  d.B.strides[1] = ldb;
+  d.B.strides[2] = bsB;
+  d.B.dims[2] = batch;
+  if (!b_mn) {
+    d.B.dims[0] = K;
+    d.B.dims[1] = N;
+    d.boxB[0] = 64; d.boxB[1] = static_cast<uint32_t>(BN); d.boxB[2] = 1;
+  } else {
+    d.B.dims[0] = N;
+    d.B.dims[1] = K;
+    d.boxB[0] = 64; d.boxB[1] = 64; d.boxB[2] = 1;
+  }
+  p.kind = KIND_GEMM;
+  p.a_mn = a_mn;
+  p.b_mn = b_mn;
+  p.BN = BN;
+  p.num_m_tiles = (M + 127) / 128;
+  p.num_n_tiles = (N + BN - 1) / BN;
+  p.num_z = batch;
+  p.num_k_iters = (K + 63) / 64;
+  p.out_mode = out_mode;
+  p.n_valid = N;
+  p.m_valid = M;
+  p.ldd = ldd;
+  p.strideD = strideD;
+  p.alpha = alpha;
+  p.bias = bias;
+  p.residual = residual;
+  p.D = D;
+  d.gemm_lda = lda;
+  d.gemm_ldb = ldb;
+  d.gemm_k = K;
+  d.gemm_strideA = strideA;
+  d.gemm_strideB = strideB;
+  return ODVAE_OK;
+}
+
+// ---------------------------------------------------------------------------------------------
+// Spatial views over NHWC activations
+// ---------------------------------------------------------------------------------------------
+static void view4(OperandView& v, const void* ptr, int B, int H, int W, int C) {
+  v.ptr = ptr;
+  v.rank = 4;
+  v.dims[0] = C; v.dims[1] = W; v.dims[2] = H; v.dims[3] = B;
+  v.strides[0] = 1; v.strides[1] = C; v.strides[2] = static_cast<long long>(W) * C;
+  v.strides[3] = static_cast<long long>(H) * W * C;
+}
+// stride-2 phase view of [B,H,W,C]: element (c', j, ph, i, b) = x[b, 2i+ph, j, c'] with c' in [0,2C) covering
+// pixels (2j, 2j+1)
+static void view5_s2(OperandView& v, const void* ptr, int B, int H, int W, int C) {
+  v.ptr = ptr;
+  v.rank = 5;
+  v.dims[0] = 2 * C; v.dims[1] = W / 2; v.dims[2] = 2; v.dims[3] = H / 2; v.dims[4] = B;
+  v.strides[0] = 1; v.strides[1] = 2 * C; v.strides[2] = static_cast<long long>(W) * C;
+  v.strides[3] = 2ll * W * C; v.strides[4] = static_cast<long long>(H) * W * C;
+}
+static void spatial_box(uint32_t* box, int rank, int bw, int bh) {
+  if (rank == 5) {
+    box[0] = 64; box[1] = bw; box[2] = 1; box[3] = bh; box[4] = 1;
+  } else {
+    box[0] = 64; box[1] = bw; box[2] = bh; box[3] = 1;
+  }
+}
+static bool tile_geometry(int Ho, int Wo, int pixels, int* bw, int* bh) {
+  if (!is_pow2(Wo)) return false;
+  int w = Wo < pixels ? Wo : pixels;
+  int h = pixels / w;
+  if (h > Ho || Ho % h != 0) return false;
+  *bw = w;
+  *bh = h;
+  return true;
+}
+
+static void fill_taps_fwd(TcParams& p, int geom, int CinP) {
+  if (geom == ODVAE_CONV_1x1) {
+    p.ntaps = 1;
+    p.tap_dx[0] = p.tap_dy[0] = p.tap_c[0] = p.tap_ph[0] = 0;
+    p.sp_rank = 4;
+  } else if (geom == ODVAE_CONV_3x3_S1) {
+    p.ntaps = 9;
+    for (int r = 0; r < 3; ++r)
+      for (int s = 0; s < 3; ++s) {
+        const int t = r * 3 + s;
+        p.tap_dx[t] = s - 1;
+        p.tap_dy[t] = r - 1;
+        p.tap_c[t] = 0;
+        p.tap_ph[t] = 0;
+      }
+    p.sp_rank = 4;
+  } else {  // 3x3 stride 2, zero pad bottom/right (model.py:72-76), gathered through the phase view
+    p.ntaps = 9;
+    for (int r = 0; r < 3; ++r)
+      for (int s = 0; s < 3; ++s) {
+        const int t = r * 3 + s;
+        p.tap_dx[t] = s >> 1;
+        p.tap_dy[t] = r >> 1;
+        p.tap_c[t] = (s & 1) * CinP;
+        p.tap_ph[t] = r & 1;
+      }
+    p.sp_rank = 5;
+  }
+}
+
+static void conv_common(EngineDesc& d, int Bn, int Ho, int Wo, int gatherC, int N, int out_mode) {
+  TcParams& p = d.p;
+  int bw = 0, bh = 0;
+  const bool geo = tile_geometry(Ho, Wo, 128, &bw, &bh);
+  const int BN = pick_bn(N);
+  d.tc_ok = geo && gatherC % 64 == 0 && BN != 0;
+  p.kind = KIND_CONV;
+  p.BN = BN ? BN : 16;
+  p.cchunks = gatherC / 64;
+  p.num_k_iters = p.ntaps * p.cchunks;
+  if (geo) {
+    p.bw_log2 = ilog2(bw);
+    p.tiles_x = Wo / bw;
+    p.tiles_y = Ho / bh;
+    p.num_m_tiles = Bn * p.tiles_x * p.tiles_y;
+    spatial_box(d.boxA, p.sp_rank, bw, bh);
+  }
+  p.num_n_tiles = BN ? N / BN : 1;
+  p.num_z = 1;
+  p.m_valid = p.num_m_tiles * 128;
+  p.out_mode = out_mode;
+  p.alpha = 1.0f;
+  d.conv_batch = Bn;
+  d.conv_out_h = Ho;
+  d.conv_out_w = Wo;
+  d.chan_per_tap = gatherC;
+  d.gemm_n = N;
+  d.gemm_ldb = static_cast<long long>(p.ntaps) * gatherC;
+  // weight matrix [N][ntaps*gatherC], K-major
+  d.B.rank = 2;
+  d.B.dims[0] = d.gemm_ldb;
+  d.B.dims[1] = N;
+  d.B.strides[0] = 1;
+  d.B.strides[1] = d.gemm_ldb;
+  d.boxB[0] = 64;
+  d.boxB[1] = static_cast<uint32_t>(p.BN);
+}
+
+int describe_conv_fwd(EngineDesc& d, const void* x, const void* w_packed, const float* bias, const void* residual,
+                      void* y, int B, int H, int W, int CinP, int CoutP, int Cout, int geom, int out_nchw_f32) {
+  if (geom == ODVAE_CONV_3x3_S2 && ((H | W) & 1)) return ODVAE_ERR_SHAPE;
+  if (out_nchw_f32 && residual) return ODVAE_ERR_SHAPE;
+  const int Ho = geom == ODVAE_CONV_3x3_S2 ? H / 2 : H, Wo = geom == ODVAE_CONV_3x3_S2 ? W / 2 : W;
+  d = EngineDesc{};
+  TcParams& p = d.p;
+  fill_taps_fwd(p, geom, CinP);
+  if (geom == ODVAE_CONV_3x3_S2)
+    view5_s2(d.A, x, B, H, W, CinP);
+  else
+    view4(d.A, x, B, H, W, CinP);
+  conv_common(d, B, Ho, Wo, CinP, CoutP, out_nchw_f32 ? OUT_NCHW_F32 : OUT_BF16);
+  d.B.ptr = w_packed;
+  p.n_valid = out_nchw_f32 ? Cout : CoutP;
+  p.out_h = Ho;
+  p.out_w = Wo;
+  p.ldd = CoutP;
+  p.oB = static_cast<long long>(Ho) * Wo * CoutP;
+  p.oY = static_cast<long long>(Wo) * CoutP;
+  p.oX = CoutP;
+  p.o0 = 0;
+  p.bias = bias;
+  p.residual = residual;
+  p.D = y;
+  return ODVAE_OK;
+}
+
+// dgrad: up to 4 engine launches (stride-2 runs one per input parity phase)
+int describe_conv_dgrad(EngineDesc* ds, int* count, const void* dy, const void* w_packed_dgrad, int w_elem_bytes,
+                        const void* dx_add, void* dx, int B, int H, int W, int CinP, int CoutP, int geom) {
+  if (geom != ODVAE_CONV_3x3_S2) {
+    EngineDesc& d = ds[0];
+    d = EngineDesc{};
+    TcParams& p = d.p;
+    fill_taps_fwd(p, geom, CoutP);  // the 180-degree rotation is baked into the packed weights
+    view4(d.A, dy, B, H, W, CoutP);
+    conv_common(d, B, H, W, CoutP, CinP, OUT_BF16);
+    d.B.ptr = w_packed_dgrad;
+    p.n_valid = CinP;
+    p.out_h = H;
+    p.out_w = W;
+    p.ldd = CinP;
+    p.oB = static_cast<long long>(H) * W * CinP;
+    p.oY = static_cast<long long>(W) * CinP;
+    p.oX = CinP;
+    p.residual = dx_add;
+    p.D = dx;
+    *count = 1;
+    return ODVAE_OK;
+  }
+  if ((H | W) & 1) return ODVAE_ERR_SHAPE;
+  const int Ho = H / 2, Wo = W / 2;
+  long long w_off = 0;
+  int n = 0;
+  for (int py = 0; py < 2; ++py)
+    for (int px = 0; px < 2; ++px) {
+      EngineDesc& d = ds[n++];
+      d = EngineDesc{};
+      TcParams& p = d.p;
+      p.sp_rank = 4;
+      int nt = 0;
+      for (int r = 0; r < 3; ++r)
+        for (int s = 0; s < 3; ++s)
+          if ((r & 1) == py && (s & 1) == px) {
+            p.tap_dx[nt] = -(s >> 1);
+            p.tap_dy[nt] = -(r >> 1);
+            p.tap_c[nt] = 0;
+            p.tap_ph[nt] = 0;
+            ++nt;
+          }
+      p.ntaps = nt;
+      view4(d.A, dy, B, Ho, Wo, CoutP);
+      conv_common(d, B, Ho, Wo, CoutP, CinP, OUT_BF16);
+      d.B.ptr = reinterpret_cast<const uint8_t*>(w_packed_dgrad) + w_off * w_elem_bytes;
+      w_off += static_cast<long long>(nt) * CoutP * CinP;
+      p.n_valid = CinP;
+      p.out_h = Ho;
+      p.out_w = Wo;
+      p.ldd = CinP;
+      p.oB = static_cast<long long>(H) * W * CinP;
+      p.oY = 2ll * W * CinP;
+      p.oX = 2ll * CinP;
+      p.o0 = (static_cast<long long>(py) * W + px) * CinP;
+      p.residual = dx_add;
+      p.D = dx;
+    }
+  *count = 4;
+  return ODVAE_OK;
+}
+
+// wgrad: ws[tap][split][CoutP][CinP] (fp32) = sum over the split's output pixels of dy^T x_shifted
+int describe_conv_wgrad(EngineDesc& d, const void* x, const void* dy, float* ws, int B, int H, int W, int CinP,
+                        int CoutP, int geom, int impl) {
+  if (geom == ODVAE_CONV_3x3_S2 && ((H | W) & 1)) return ODVAE_ERR_SHAPE;
+  const int Ho = geom == ODVAE_CONV_3x3_S2 ? H / 2 : H, Wo = geom == ODVAE_CONV_3x3_S2 ? W / 2 : W;
+  d = EngineDesc{};
+  TcParams& p = d.p;
+  p.kind = KIND_WGRAD;
+  p.a_mn = 1;
+  p.b_mn = 1;
+  fill_taps_fwd(p, geom, CinP);
+  view4(d.A, dy, B, Ho, Wo, CoutP);
+  if (geom == ODVAE_CONV_3x3_S2)
+    view5_s2(d.B, x, B, H, W, CinP);
+  else
+    view4(d.B, x, B, H, W, CinP);
+  int kbw = 0, kbh = 0;
+  const bool geo = tile_geometry(Ho, Wo, 64, &kbw, &kbh);
+  const int BN = CinP % 256 == 0 ? 256 : (CinP % 128 == 0 ? 128 : 64);
+  const long long kpix = static_cast<long long>(B) * Ho * Wo;
+  d.tc_ok = geo && CinP % 64 == 0 && CoutP % 8 == 0 && kpix % 64 == 0;
+  p.BN = BN;
+  const long long base_tiles = static_cast<long long>(p.ntaps) * ((CoutP + 127) / 128) * ((CinP + BN - 1) / BN);
+  int split = 1;
+  if (impl == ODVAE_IMPL_TC && d.tc_ok) {
+    const long long kch = kpix / 64;
+    const int target = 2 * num_sms();
+    while (base_tiles * split < target && kch % (2 * split) == 0 && kch / (2 * split) >= 16) split *= 2;
+    p.kbw_log2 = ilog2(kbw);
+    p.kch_x = Wo / kbw;
+    p.kch_y = Ho / kbh;
+    p.kch_per_split = static_cast<int>(kch / split);
+    p.num_k_iters = p.kch_per_split;
+    spatial_box(d.boxA, 4, kbw, kbh);
+    spatial_box(d.boxB, p.sp_rank, kbw, kbh);
+  } else {
+    // SIMT: 64x64 output tiles; split K so the grid fills the machine
+    const long long tiles = static_cast<long long>(p.ntaps) * ((CoutP + 63) / 64) * ((CinP + 63) / 64);
+    while (tiles * split < 4 * num_sms() && kpix / (2 * split) >= 256) split *= 2;
+  }
+  p.split_k = split;
+  p.num_m_tiles = (CoutP + 127) / 128;
+  p.num_n_tiles = (CinP + BN - 1) / BN;
+  p.num_z = p.ntaps * split;
+  p.out_mode = OUT_F32;
+  p.n_valid = CinP;
+  p.m_valid = CoutP;
+  p.ldd = CinP;
+  p.alpha = 1.0f;
+  p.D = ws;
+  d.conv_batch = B;
+  d.conv_out_h = Ho;
+  d.conv_out_w = Wo;
+  d.gemm_lda = CoutP;
+  return ODVAE_OK;
+}
+
+}  // namespace odvae

@@ -1,0 +1,24 @@
+// Internal (C++) interface of the GEMM/conv engines; the C ABI in api_conv.cu wraps these.
+#pragma once
+#include <cuda_runtime.h>
+
+#include "engine_desc.h"
+
+namespace odvae {
+int run_engine(EngineDesc& d, int impl, int act_dtype, cudaStream_t stream);
+int describe_gemm(EngineDesc& d, const void* A, const void* B, void* D, int M, int N, int K, int batch, long long lda,
+                  long long ldb, long long ldd, long long strideA, long long strideB, long long strideD, int a_mn,
+                  int b_mn, int out_mode, float alpha, const float* bias, const void* residual);
+int describe_conv_fwd(EngineDesc& d, const void* x, const void* w_packed, const float* bias, const void* residual,
+                      void* y, int B, int H, int W, int CinP, int CoutP, int Cout, int geom, int out_nchw_f32);
+int describe_conv_dgrad(EngineDesc* ds, int* count, const void* dy, const void* w_packed_dgrad, int w_elem_bytes,
+                        const void* dx_add, void* dx, int B, int H, int W, int CinP, int CoutP, int geom);
+int describe_conv_wgrad(EngineDesc& d, const void* x, const void* dy, float* ws, int B, int H, int W, int CinP,
+                        int CoutP, int geom, int impl);
+// layout.cu
+int launch_wgrad_reduce(const float* ws, float* dw, int Cout, int Cin, int taps, int CoutP, int CinP, int split_k,
+                        int accumulate, cudaStream_t st);
+size_t colsum_workspace_bytes(int cols);
+int launch_colsum(const void* m, long long rows, int cols, int ld, int act_dtype, float* out, int accumulate,
+                  float* part, cudaStream_t st);
+}  // namespace odvae

@@ -1,0 +1,429 @@
+// Layout / dtype conversion, weight packing, nearest-2x upsample and small reductions.
+// All memory-bound: 16-byte vector accesses, grids sized in multiples of the SM count.
+#include "common.cuh"
+
+namespace odvae {
+
+template <typename T> struct Vec16;  // 16-byte vector of T
+template <> struct Vec16<float> { static constexpr int N = 4; };
+template <> struct Vec16<bf16> { static constexpr int N = 8; };
+
+// ---------------------------------------------------------------------------------------------
+// NCHW fp32 <-> NHWC T
+// ---------------------------------------------------------------------------------------------
+template <typename T>
+__global__ void nchw_to_nhwc_kernel(const float* __restrict__ src, T* __restrict__ dst, int B, int C, int HW,
+                                    int Cpad, float scale, float shift) {
+  const long long total = static_cast<long long>(B) * HW;
+  for (long long i = blockIdx.x * static_cast<long long>(blockDim.x) + threadIdx.x; i < total;
+       i += static_cast<long long>(gridDim.x) * blockDim.x) {
+    const int b = static_cast<int>(i / HW);
+    const int p = static_cast<int>(i - static_cast<long long>(b) * HW);
+    const float* s = src + (static_cast<long long>(b) * C) * HW + p;
+    T* d = dst + i * Cpad;
+    constexpr int V = Vec16<T>::N;
+    for (int c0 = 0; c0 < Cpad; c0 += V) {
+      T tmp[V];
+#pragma unroll
+      for (int j = 0; j < V; ++j) {
+        const int c = c0 + j;
+        float v = (c < C) ? __ldg(s + static_cast<long long>(c) * HW) * scale + shift : 0.0f;
+        tmp[j] = from_f32<T>(v);
+      }
+      *reinterpret_cast<uint4*>(d + c0) = *reinterpret_cast<const uint4*>(tmp);
+    }
+  }
+}
+
+template <typename T>
+__global__ void nhwc_to_nchw_kernel(const T* __restrict__ src, float* __restrict__ dst, int B, int C, int HW,
+                                    int Cpad) {
+  const long long total = static_cast<long long>(B) * HW;
+  for (long long i = blockIdx.x * static_cast<long long>(blockDim.x) + threadIdx.x; i < total;
+       i += static_cast<long long>(gridDim.x) * blockDim.x) {
+    const int b = static_cast<int>(i / HW);
+    const int p = static_cast<int>(i - static_cast<long long>(b) * HW);
+    const T* s = src + i * Cpad;
+    float* d = dst + (static_cast<long long>(b) * C) * HW + p;
+    constexpr int V = Vec16<T>::N;
+    for (int c0 = 0; c0 < C; c0 += V) {
+      T tmp[V];
+      *reinterpret_cast<uint4*>(tmp) = *reinterpret_cast<const uint4*>(s + c0);
+#pragma unroll
+      for (int j = 0; j < V; ++j)
+        if (c0 + j < C) d[static_cast<long long>(c0 + j) * HW] = to_f32<T>(tmp[j]);
+    }
+  }
+}
+
+// ---------------------------------------------------------------------------------------------
+// min / max of an fp32 tensor (two-stage, deterministic)
+// ---------------------------------------------------------------------------------------------
+__global__ void minmax_stage1(const float* __restrict__ src, long long n, float* __restrict__ part) {
+  float mn = INFINITY, mx = -INFINITY;
+  for (long long i = blockIdx.x * static_cast<long long>(blockDim.x) + threadIdx.x; i < n;
+       i += static_cast<long long>(gridDim.x) * blockDim.x) {
+    float v = __ldg(src + i);
+    mn = fminf(mn, v);
+    mx = fmaxf(mx, v);
+  }
+  __shared__ float smn[32], smx[32];
+  mn = warp_min(mn);
+  mx = warp_max(mx);
+  if ((threadIdx.x & 31) == 0) {
+    smn[threadIdx.x >> 5] = mn;
+    smx[threadIdx.x >> 5] = mx;
+  }
+  __syncthreads();
+  if (threadIdx.x < 32) {
+    const int nw = blockDim.x >> 5;
+    mn = threadIdx.x < nw ? smn[threadIdx.x] : INFINITY;
+    mx = threadIdx.x < nw ? smx[threadIdx.x] : -INFINITY;
+    mn = warp_min(mn);
+    mx = warp_max(mx);
+    if (threadIdx.x == 0) {
+      part[2 * blockIdx.x] = mn;
+      part[2 * blockIdx.x + 1] = mx;
+    }
+  }
+}
+__global__ void minmax_stage2(const float* __restrict__ part, int nblk, float* __restrict__ out2) {
+  float mn = INFINITY, mx = -INFINITY;
+  for (int i = threadIdx.x; i < nblk; i += blockDim.x) {
+    mn = fminf(mn, part[2 * i]);
+    mx = fmaxf(mx, part[2 * i + 1]);
+  }
+  __shared__ float smn[32], smx[32];
+  mn = warp_min(mn);
+  mx = warp_max(mx);
+  if ((threadIdx.x & 31) == 0) {
+    smn[threadIdx.x >> 5] = mn;
+    smx[threadIdx.x >> 5] = mx;
+  }
+  __syncthreads();
+  if (threadIdx.x < 32) {
+    const int nw = blockDim.x >> 5;
+    mn = threadIdx.x < nw ? smn[threadIdx.x] : INFINITY;
+    mx = threadIdx.x < nw ? smx[threadIdx.x] : -INFINITY;
+    mn = warp_min(mn);
+    mx = warp_max(mx);
+    if (threadIdx.x == 0) {
+      out2[0] = mn;
+      out2[1] = mx;
+    }
+  }
+}
+
+// ---------------------------------------------------------------------------------------------
+// Conv weight packing from the fp32 OIHW master
+// ---------------------------------------------------------------------------------------------
+// which=0: P[co][tap][ci] = w[co][ci][r][s]
+// which=1 (s1 / 1x1): P[ci][tap'][co] = w[co][ci][kh-1-r'][kw-1-s']
+// which=1 (s2): 4 parity-phase matrices [CinP][nt*CoutP], phases (py,px) in order 00,01,10,11,
+//               taps of a phase in (r,s) ascending order: entry = w[co][ci][r][s]
+template <typename T>
+__global__ void pack_conv_weight_kernel(const float* __restrict__ w, T* __restrict__ P, int Cout, int Cin, int k,
+                                        int CoutP, int CinP, int which, int s2) {
+  const int taps = k * k;
+  const long long total = static_cast<long long>(CoutP) * CinP * taps;
+  for (long long e = blockIdx.x * static_cast<long long>(blockDim.x) + threadIdx.x; e < total;
+       e += static_cast<long long>(gridDim.x) * blockDim.x) {
+    int co, ci, r, s;
+    if (which == 0) {
+      ci = static_cast<int>(e % CinP);
+      long long q = e / CinP;
+      int tap = static_cast<int>(q % taps);
+      co = static_cast<int>(q / taps);
+      r = tap / k;
+      s = tap % k;
+    } else if (!s2) {
+      co = static_cast<int>(e % CoutP);
+      long long q = e / CoutP;
+      int tap = static_cast<int>(q % taps);
+      ci = static_cast<int>(q / taps);
+      r = k - 1 - tap / k;
+      s = k - 1 - tap % k;
+    } else {
+      // phase sizes: nt = 4,2,2,1
+      const long long unit = static_cast<long long>(CinP) * CoutP;
+      long long rem = e;
+      int py = 0, px = 0, nt = 4;
+      const int nts[4] = {4, 2, 2, 1};
+      int ph = 0;
+      for (; ph < 4; ++ph) {
+        if (rem < nts[ph] * unit) break;
+        rem -= nts[ph] * unit;
+      }
+      py = ph >> 1;
+      px = ph & 1;
+      nt = nts[ph];
+      co = static_cast<int>(rem % CoutP);
+      long long q = rem / CoutP;
+      int t = static_cast<int>(q % nt);
+      ci = static_cast<int>(q / nt);
+      // t-th tap with (r&1)==py, (s&1)==px in ascending (r,s)
+      const int ns = px == 0 ? 2 : 1;
+      const int ri = t / ns, si = t % ns;
+      r = py == 0 ? 2 * ri : 1;
+      s = px == 0 ? 2 * si : 1;
+    }
+    float v = 0.0f;
+    if (co < Cout && ci < Cin) v = __ldg(w + ((static_cast<long long>(co) * Cin + ci) * k + r) * k + s);
+    P[e] = from_f32<T>(v);
+  }
+}
+
+// dw[co][ci][tap] (+)= sum_split ws[(tap*split_k + split)][co][ci]   (ws rows: CoutP x CinP)
+__global__ void wgrad_reduce_kernel(const float* __restrict__ ws, float* __restrict__ dw, int Cout, int Cin,
+                                    int taps, int CoutP, int CinP, int split_k, int accumulate) {
+  const long long total = static_cast<long long>(Cout) * Cin * taps;
+  for (long long e = blockIdx.x * static_cast<long long>(blockDim.x) + threadIdx.x; e < total;
+       e += static_cast<long long>(gridDim.x) * blockDim.x) {
+    // iterate with ci fastest for coalesced workspace reads
+    const int ci = static_cast<int>(e % Cin);
+    long long q = e / Cin;
+    const int tap = static_cast<int>(q % taps);
+    const int co = static_cast<int>(q / taps);
+    float acc = 0.0f;
+    for (int s = 0; s < split_k; ++s)
+      acc += __ldg(ws + ((static_cast<long long>(tap) * split_k + s) * CoutP + co) * CinP + ci);
+    float* d = dw + (static_cast<long long>(co) * Cin + ci) * taps + tap;
+    *d = accumulate ? (*d + acc) : acc;
+  }
+}
+
+// column sums of a [rows][ld] matrix (bias gradients): stage 1 partials [nblk][cols], stage 2 final
+template <typename T>
+__global__ void colsum_stage1(const T* __restrict__ m, long long rows, int cols, int ld, float* __restrict__ part) {
+  // blockDim = (32, 8): x over columns (strided), y over rows
+  const long long rows_per_blk = (rows + gridDim.x - 1) / gridDim.x;
+  const long long r0 = blockIdx.x * rows_per_blk;
+  const long long r1 = r0 + rows_per_blk < rows ? r0 + rows_per_blk : rows;
+  __shared__ float sm[8][33];
+  for (int c0 = 0; c0 < cols; c0 += 32) {
+    const int c = c0 + threadIdx.x;
+    float acc = 0.0f;
+    if (c < cols)
+      for (long long r = r0 + threadIdx.y; r < r1; r += 8) acc += to_f32<T>(m[r * ld + c]);
+    sm[threadIdx.y][threadIdx.x] = acc;
+    __syncthreads();
+    if (threadIdx.y == 0 && c < cols) {
+      float t = 0.0f;
+#pragma unroll
+      for (int j = 0; j < 8; ++j) t += sm[j][threadIdx.x];
+      part[static_cast<long long>(blockIdx.x) * cols + c] = t;
+    }
+    __syncthreads();
+  }
+}
+__global__ void colsum_stage2(const float* __restrict__ part, int nblk, int cols, float* __restrict__ out,
+                              int accumulate) {
+  const int c = blockIdx.x * blockDim.x + threadIdx.x;
+  if (c >= cols) return;
+  float t = 0.0f;
+  for (int i = 0; i < nblk; ++i) t += part[static_cast<long long>(i) * cols + c];
+  out[c] = accumulate ? out[c] + t : t;
+}
+
+// ---------------------------------------------------------------------------------------------
+// nearest 2x upsample and adjoint, NHWC
+// ---------------------------------------------------------------------------------------------
+template <typename T>
+__global__ void upsample2x_kernel(const T* __restrict__ x, T* __restrict__ y, int B, int H, int W, int C) {
+  constexpr int V = Vec16<T>::N;
+  const int cv = C / V;
+  const long long total = static_cast<long long>(B) * (2 * H) * (2 * W) * cv;
+  for (long long i = blockIdx.x * static_cast<long long>(blockDim.x) + threadIdx.x; i < total;
+       i += static_cast<long long>(gridDim.x) * blockDim.x) {
+    const int c = static_cast<int>(i % cv);
+    long long q = i / cv;
+    const int xo = static_cast<int>(q % (2 * W));
+    q /= (2 * W);
+    const int yo = static_cast<int>(q % (2 * H));
+    const int b = static_cast<int>(q / (2 * H));
+    const uint4 v = __ldg(reinterpret_cast<const uint4*>(x + ((static_cast<long long>(b) * H + (yo >> 1)) * W + (xo >> 1)) * C) + c);
+    reinterpret_cast<uint4*>(y)[i] = v;
+  }
+}
+template <typename T>
+__global__ void upsample2x_bwd_kernel(const T* __restrict__ dy, T* __restrict__ dx, int B, int H, int W, int C) {
+  constexpr int V = Vec16<T>::N;
+  const int cv = C / V;
+  const long long total = static_cast<long long>(B) * H * W * cv;
+  for (long long i = blockIdx.x * static_cast<long long>(blockDim.x) + threadIdx.x; i < total;
+       i += static_cast<long long>(gridDim.x) * blockDim.x) {
+    const int c = static_cast<int>(i % cv);
+    long long q = i / cv;
+    const int xi = static_cast<int>(q % W);
+    q /= W;
+    const int yi = static_cast<int>(q % H);
+    const int b = static_cast<int>(q / H);
+    float acc[V];
+#pragma unroll
+    for (int j = 0; j < V; ++j) acc[j] = 0.0f;
+#pragma unroll
+    for (int dyy = 0; dyy < 2; ++dyy)
+#pragma unroll
+      for (int dxx = 0; dxx < 2; ++dxx) {
+        T tmp[V];
+        *reinterpret_cast<uint4*>(tmp) = __ldg(reinterpret_cast<const uint4*>(
+            dy + ((static_cast<long long>(b) * 2 * H + 2 * yi + dyy) * 2 * W + 2 * xi + dxx) * C) + c);
+#pragma unroll
+        for (int j = 0; j < V; ++j) acc[j] += to_f32<T>(tmp[j]);
+      }
+    T out[V];
+#pragma unroll
+    for (int j = 0; j < V; ++j) out[j] = from_f32<T>(acc[j]);
+    reinterpret_cast<uint4*>(dx)[i] = *reinterpret_cast<const uint4*>(out);
+  }
+}
+
+template <typename T>
+__global__ void add_kernel(const T* __restrict__ a, const T* __restrict__ b, T* __restrict__ o, long long nvec) {
+  constexpr int V = Vec16<T>::N;
+  for (long long i = blockIdx.x * static_cast<long long>(blockDim.x) + threadIdx.x; i < nvec;
+       i += static_cast<long long>(gridDim.x) * blockDim.x) {
+    T ta[V], tb[V], to[V];
+    *reinterpret_cast<uint4*>(ta) = __ldg(reinterpret_cast<const uint4*>(a) + i);
+    *reinterpret_cast<uint4*>(tb) = __ldg(reinterpret_cast<const uint4*>(b) + i);
+#pragma unroll
+    for (int j = 0; j < V; ++j) to[j] = from_f32<T>(to_f32<T>(ta[j]) + to_f32<T>(tb[j]));
+    reinterpret_cast<uint4*>(o)[i] = *reinterpret_cast<const uint4*>(to);
+  }
+}
+
+static int grid_for(long long work_items, int threads, int per_sm = 8) {
+  long long blocks = (work_items + threads - 1) / threads;
+  long long cap = static_cast<long long>(num_sms()) * per_sm;
+  if (blocks > cap) blocks = cap;
+  if (blocks < 1) blocks = 1;
+  return static_cast<int>(blocks);
+}
+
+// internal entry points used by api.cu ----------------------------------------------------------
+int launch_wgrad_reduce(const float* ws, float* dw, int Cout, int Cin, int taps, int CoutP, int CinP, int split_k,
+                        int accumulate, cudaStream_t st) {
+  const long long total = static_cast<long long>(Cout) * Cin * taps;
+  wgrad_reduce_kernel<<<grid_for(total, 256), 256, 0, st>>>(ws, dw, Cout, Cin, taps, CoutP, CinP, split_k, accumulate);
+  return check_launch("wgrad_reduce_kernel");
+}
+
+static constexpr int COLSUM_BLOCKS = 296;
+size_t colsum_workspace_bytes(int cols) { return static_cast<size_t>(COLSUM_BLOCKS) * cols * sizeof(float); }
+int launch_colsum(const void* m, long long rows, int cols, int ld, int act_dtype, float* out, int accumulate,
+                  float* part, cudaStream_t st) {
+  int nblk = COLSUM_BLOCKS;
+  if (rows < nblk * 8) nblk = static_cast<int>((rows + 7) / 8);
+  if (nblk < 1) nblk = 1;
+  dim3 blk(32, 8);
+  if (act_dtype == ODVAE_BF16)
+    colsum_stage1<bf16><<<nblk, blk, 0, st>>>(reinterpret_cast<const bf16*>(m), rows, cols, ld, part);
+  else
+    colsum_stage1<float><<<nblk, blk, 0, st>>>(reinterpret_cast<const float*>(m), rows, cols, ld, part);
+  int s = check_launch("colsum_stage1");
+  if (s != ODVAE_OK) return s;
+  colsum_stage2<<<(cols + 127) / 128, 128, 0, st>>>(part, nblk, cols, out, accumulate);
+  return check_launch("colsum_stage2");
+}
+
+}  // namespace odvae
+
+using namespace odvae;
+
+extern "C" {
+
+int odvae_nchw_to_nhwc(const float* src, void* dst, int B, int C, int H, int W, int Cpad, int act_dtype, float scale,
+                       float shift, void* stream) {
+  if (B <= 0 || C <= 0 || Cpad < C) return ODVAE_ERR_SHAPE;
+  cudaStream_t st = static_cast<cudaStream_t>(stream);
+  const long long total = static_cast<long long>(B) * H * W;
+  if (act_dtype == ODVAE_BF16) {
+    if (Cpad % 8) return ODVAE_ERR_SHAPE;
+    nchw_to_nhwc_kernel<bf16><<<grid_for(total, 256), 256, 0, st>>>(src, reinterpret_cast<bf16*>(dst), B, C, H * W, Cpad, scale, shift);
+  } else {
+    if (Cpad % 4) return ODVAE_ERR_SHAPE;
+    nchw_to_nhwc_kernel<float><<<grid_for(total, 256), 256, 0, st>>>(src, reinterpret_cast<float*>(dst), B, C, H * W, Cpad, scale, shift);
+  }
+  return check_launch("nchw_to_nhwc_kernel");
+}
+
+int odvae_nhwc_to_nchw(const void* src, float* dst, int B, int C, int H, int W, int Cpad, int act_dtype, void* stream) {
+  if (B <= 0 || C <= 0 || Cpad < C) return ODVAE_ERR_SHAPE;
+  cudaStream_t st = static_cast<cudaStream_t>(stream);
+  const long long total = static_cast<long long>(B) * H * W;
+  if (act_dtype == ODVAE_BF16) {
+    if (Cpad % 8) return ODVAE_ERR_SHAPE;
+    nhwc_to_nchw_kernel<bf16><<<grid_for(total, 256), 256, 0, st>>>(reinterpret_cast<const bf16*>(src), dst, B, C, H * W, Cpad);
+  } else {
+    if (Cpad % 4) return ODVAE_ERR_SHAPE;
+    nhwc_to_nchw_kernel<float><<<grid_for(total, 256), 256, 0, st>>>(reinterpret_cast<const float*>(src), dst, B, C, H * W, Cpad);
+  }
+  return check_launch("nhwc_to_nchw_kernel");
+}
+
+int odvae_minmax(const float* src, int64_t n, float* out2, void* workspace, size_t ws_bytes, void* stream) {
+  const int nblk = 2 * num_sms();
+  if (ws_bytes < static_cast<size_t>(nblk) * 2 * sizeof(float)) return ODVAE_ERR_WORKSPACE;
+  cudaStream_t st = static_cast<cudaStream_t>(stream);
+  minmax_stage1<<<nblk, 512, 0, st>>>(src, n, reinterpret_cast<float*>(workspace));
+  int s = check_launch("minmax_stage1");
+  if (s != ODVAE_OK) return s;
+  minmax_stage2<<<1, 256, 0, st>>>(reinterpret_cast<const float*>(workspace), nblk, out2);
+  return check_launch("minmax_stage2");
+}
+
+int odvae_pack_conv_weight(const float* w_oihw, void* packed, int Cout, int Cin, int geom, int CoutP, int CinP,
+                           int which, int act_dtype, void* stream) {
+  if (CoutP < Cout || CinP < Cin) return ODVAE_ERR_SHAPE;
+  const int k = geom == ODVAE_CONV_1x1 ? 1 : 3;
+  const int s2 = (geom == ODVAE_CONV_3x3_S2 && which == 1) ? 1 : 0;
+  cudaStream_t st = static_cast<cudaStream_t>(stream);
+  const long long total = static_cast<long long>(CoutP) * CinP * k * k;
+  if (act_dtype == ODVAE_BF16)
+    pack_conv_weight_kernel<bf16><<<grid_for(total, 256), 256, 0, st>>>(w_oihw, reinterpret_cast<bf16*>(packed), Cout, Cin, k, CoutP, CinP, which, s2);
+  else
+    pack_conv_weight_kernel<float><<<grid_for(total, 256), 256, 0, st>>>(w_oihw, reinterpret_cast<float*>(packed), Cout, Cin, k, CoutP, CinP, which, s2);
+  return check_launch("pack_conv_weight_kernel");
+}
+
+int odvae_upsample2x(const void* x, void* y, int B, int H, int W, int C, int act_dtype, void* stream) {
+  cudaStream_t st = static_cast<cudaStream_t>(stream);
+  if (act_dtype == ODVAE_BF16) {
+    if (C % 8) return ODVAE_ERR_SHAPE;
+    const long long total = static_cast<long long>(B) * 4 * H * W * (C / 8);
+    upsample2x_kernel<bf16><<<grid_for(total, 256), 256, 0, st>>>(reinterpret_cast<const bf16*>(x), reinterpret_cast<bf16*>(y), B, H, W, C);
+  } else {
+    if (C % 4) return ODVAE_ERR_SHAPE;
+    const long long total = static_cast<long long>(B) * 4 * H * W * (C / 4);
+    upsample2x_kernel<float><<<grid_for(total, 256), 256, 0, st>>>(reinterpret_cast<const float*>(x), reinterpret_cast<float*>(y), B, H, W, C);
+  }
+  return check_launch("upsample2x_kernel");
+}
+
+int odvae_upsample2x_bwd(const void* dy, void* dx, int B, int H, int W, int C, int act_dtype, void* stream) {
+  cudaStream_t st = static_cast<cudaStream_t>(stream);
+  if (act_dtype == ODVAE_BF16) {
+    if (C % 8) return ODVAE_ERR_SHAPE;
+    const long long total = static_cast<long long>(B) * H * W * (C / 8);
+    upsample2x_bwd_kernel<bf16><<<grid_for(total, 256), 256, 0, st>>>(reinterpret_cast<const bf16*>(dy), reinterpret_cast<bf16*>(dx), B, H, W, C);
+  } else {
+    if (C % 4) return ODVAE_ERR_SHAPE;
+    const long long total = static_cast<long long>(B) * H * W * (C / 4);
+    upsample2x_bwd_kernel<float><<<grid_for(total, 256), 256, 0, st>>>(reinterpret_cast<const float*>(dy), reinterpret_cast<float*>(dx), B, H, W, C);
+  }
+  return check_launch("upsample2x_bwd_kernel");
+}
+
+int odvae_add(const void* a, const void* b, void* out, int64_t n, int act_dtype, void* stream) {
+  cudaStream_t st = static_cast<cudaStream_t>(stream);
+  if (act_dtype == ODVAE_BF16) {
+    if (n % 8) return ODVAE_ERR_SHAPE;
+    add_kernel<bf16><<<grid_for(n / 8, 256), 256, 0, st>>>(reinterpret_cast<const bf16*>(a), reinterpret_cast<const bf16*>(b), reinterpret_cast<bf16*>(out), n / 8);
+  } else {
+    if (n % 4) return ODVAE_ERR_SHAPE;
+    add_kernel<float><<<grid_for(n / 4, 256), 256, 0, st>>>(reinterpret_cast<const float*>(a), reinterpret_cast<const float*>(b), reinterpret_cast<float*>(out), n / 4);
+  }
+  return check_launch("add_kernel");
+}
+
+}  // extern "C"

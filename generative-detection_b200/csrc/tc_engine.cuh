@@ -1,0 +1,327 @@
+// The tcgen05 GEMM engine: one persistent, warp-specialised kernel that serves
+//   KIND_GEMM  : batched GEMM with K-major or MN-major operands (attention QK^T / PV / gradients)
+//   KIND_CONV  : implicit-GEMM convolution forward / dgrad (A gathered by TMA from NHWC with OOB zero fill)
+//   KIND_WGRAD : convolution weight gradient (both operands MN-major, K = pixels, deterministic split-K)
+// Tile = 128 (M, TMEM lanes) x BN (<=256) with BLOCK_K = 64 bf16 (one 128-byte swizzle atom per row).
+#pragma once
+#include "common.cuh"
+#include "tc_primitives.cuh"
+#include "engine_desc.h"
+
+namespace odvae {
+
+static constexpr int TC_BLOCK_M = 128;
+static constexpr int TC_BLOCK_K = 64;
+static constexpr int TC_A_BYTES = TC_BLOCK_M * TC_BLOCK_K * 2;  // 16 KiB
+static constexpr int TC_THREADS = 256;
+static constexpr int TC_TMEM_COLS = 512;
+
+struct TileCoord {
+  int m_tile, n_tile, z;
+  int b, y0, x0;  // CONV
+  int tap, split; // WGRAD
+};
+
+__device__ __forceinline__ TileCoord decode_tile(const TcParams& p, int t) {
+  TileCoord c;
+  c.n_tile = t % p.num_n_tiles;
+  int r = t / p.num_n_tiles;
+  c.m_tile = r % p.num_m_tiles;
+  c.z = r / p.num_m_tiles;
+  c.b = c.y0 = c.x0 = c.tap = c.split = 0;
+  if (p.kind == KIND_CONV) {
+    int per_img = p.tiles_x * p.tiles_y;
+    c.b = c.m_tile / per_img;
+    int q = c.m_tile - c.b * per_img;
+    int ty = q / p.tiles_x, tx = q - ty * p.tiles_x;
+    int bw = 1 << p.bw_log2;
+    c.x0 = tx * bw;
+    c.y0 = ty * (TC_BLOCK_M >> p.bw_log2);
+  } else if (p.kind == KIND_WGRAD) {
+    c.tap = c.z / p.split_k;
+    c.split = c.z - c.tap * p.split_k;
+  }
+  return c;
+}
+
+__device__ __forceinline__ void spatial_load(void* dst, const CUtensorMap* tm, uint64_t* bar, int rank, int c,
+                                             int x, int ph, int y, int b) {
+  if (rank == 5)
+    tma_load_5d(dst, tm, bar, c, x, ph, y, b);
+  else
+    tma_load_4d(dst, tm, bar, c, x, y, b);
+}
+
+__global__ void __launch_bounds__(TC_THREADS, 1)
+tc_engine_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUtensorMap tmB,
+                 const __grid_constant__ TcParams p) {
+  extern __shared__ __align__(1024) uint8_t smem_raw[];
+  // manual 1024-byte alignment (SWIZZLE_128B atoms)
+  uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~uintptr_t(1023));
+  const int stages = p.stages;
+  const int BN = p.BN;
+  const uint32_t b_bytes = static_cast<uint32_t>(BN) * 128u;
+  uint8_t* sA = smem;
+  uint8_t* sB = smem + static_cast<size_t>(stages) * TC_A_BYTES;
+  uint64_t* bars = reinterpret_cast<uint64_t*>(sB + static_cast<size_t>(stages) * b_bytes);
+  uint64_t* full_bar = bars;
+  uint64_t* empty_bar = bars + stages;
+  uint64_t* tfull_bar = bars + 2 * stages;
+  uint64_t* tempty_bar = bars + 2 * stages + 2;
+  uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(bars + 2 * stages + 4);
+
+  const int warp = threadIdx.x >> 5;
+  const int lane = threadIdx.x & 31;
+  const int total_tiles = p.num_m_tiles * p.num_n_tiles * p.num_z;
+
+  if (warp == 0 && lane == 0) {
+    tma_prefetch_desc(&tmA);
+    tma_prefetch_desc(&tmB);
+  }
+  if (warp == 1 && lane == 0) {
+    for (int i = 0; i < stages; ++i) {
+      mbar_init(&full_bar[i], 1);
+      mbar_init(&empty_bar[i], 1);
+    }
+    for (int i = 0; i < 2; ++i) {
+      mbar_init(&tfull_bar[i], 1);
+      mbar_init(&tempty_bar[i], 128);
+    }
+    fence_barrier_init();
+  }
+  if (warp == 2) {
+    tmem_alloc(tmem_slot, TC_TMEM_COLS);
+    tmem_relinquish();
+  }
+  tc_fence_before();
+  __syncthreads();
+  tc_fence_after();
+  const uint32_t tmem_base = *tmem_slot;
+
+  if (warp == 0) {
+    // ============================ TMA producer ============================
+    if (lane == 0) {
+      int stage = 0;
+      uint32_t phase = 0;
+      for (int t = blockIdx.x; t < total_tiles; t += gridDim.x) {
+        const TileCoord tc = decode_tile(p, t);
+        const int m0 = tc.m_tile * TC_BLOCK_M;
+        const int n0 = tc.n_tile * BN;
+        for (int kit = 0; kit < p.num_k_iters; ++kit) {
+          mbar_wait(&empty_bar[stage], phase ^ 1u);
+          uint64_t* fb = &full_bar[stage];
+          mbar_arrive_expect_tx(fb, TC_A_BYTES + b_bytes);
+          uint8_t* a_dst = sA + static_cast<size_t>(stage) * TC_A_BYTES;
+          uint8_t* b_dst = sB + static_cast<size_t>(stage) * b_bytes;
+          if (p.kind == KIND_GEMM) {
+            const int k0 = kit * TC_BLOCK_K;
+            if (!p.a_mn) {
+              tma_load_3d(a_dst, &tmA, fb, k0, m0, tc.z);
+            } else {
+              tma_load_3d(a_dst, &tmA, fb, m0, k0, tc.z);
+              tma_load_3d(a_dst + 8192, &tmA, fb, m0 + 64, k0, tc.z);
+            }
+            if (!p.b_mn) {
+              tma_load_3d(b_dst, &tmB, fb, k0, n0, tc.z);
+            } else {
+              for (int j = 0; j < (BN >> 6); ++j) tma_load_3d(b_dst + j * 8192, &tmB, fb, n0 + 64 * j, k0, tc.z);
+            }
+          } else if (p.kind == KIND_CONV) {
+            const int tap = kit / p.cchunks;
+            const int cc = kit - tap * p.cchunks;
+            spatial_load(a_dst, &tmA, fb, p.sp_rank, cc * 64 + p.tap_c[tap], tc.x0 + p.tap_dx[tap], p.tap_ph[tap],
+                         tc.y0 + p.tap_dy[tap], tc.b);
+            tma_load_2d(b_dst, &tmB, fb, kit * TC_BLOCK_K, n0);
+          } else {  // KIND_WGRAD
+            const int q = tc.split * p.kch_per_split + kit;
+            const int per_img = p.kch_x * p.kch_y;
+            const int b = q / per_img;
+            const int r = q - b * per_img;
+            const int cy = r / p.kch_x, cx = r - cy * p.kch_x;
+            const int x0 = cx << p.kbw_log2;
+            const int y0 = cy * (TC_BLOCK_K >> p.kbw_log2);
+            tma_load_4d(a_dst, &tmA, fb, m0, x0, y0, b);
+            tma_load_4d(a_dst + 8192, &tmA, fb, m0 + 64, x0, y0, b);
+            for (int j = 0; j < (BN >> 6); ++j)
+              spatial_load(b_dst + j * 8192, &tmB, fb, p.sp_rank, n0 + 64 * j + p.tap_c[tc.tap],
+                           x0 + p.tap_dx[tc.tap], p.tap_ph[tc.tap], y0 + p.tap_dy[tc.tap], b);
+          }
+          if (++stage == stages) {
+            stage = 0;
+            phase ^= 1u;
+          }
+        }
+      }
+    }
+    __syncwarp();
+  } else if (warp == 1) {
+    // ============================ MMA issuer ============================
+    if (lane == 0) {
+      const uint32_t idesc = make_idesc_bf16(TC_BLOCK_M, static_cast<uint32_t>(BN), p.a_mn, p.b_mn);
+      int stage = 0;
+      uint32_t phase = 0;
+      int acc = 0;
+      uint32_t acc_phase = 0;
+      for (int t = blockIdx.x; t < total_tiles; t += gridDim.x) {
+        mbar_wait(&tempty_bar[acc], acc_phase ^ 1u);
+        tc_fence_after();
+        const uint32_t d_tmem = tmem_base + static_cast<uint32_t>(acc * BN);
+        for (int kit = 0; kit < p.num_k_iters; ++kit) {
+          mbar_wait(&full_bar[stage], phase);
+          tc_fence_after();
+          const uint32_t a_base = smem_u32(sA + static_cast<size_t>(stage) * TC_A_BYTES);
+          const uint32_t b_base = smem_u32(sB + static_cast<size_t>(stage) * b_bytes);
+#pragma unroll
+          for (int k = 0; k < TC_BLOCK_K / 16; ++k) {
+            const uint64_t adesc = p.a_mn ? make_smem_desc_sw128(a_base + k * 2048, 8192, 1024)
+                                          : make_smem_desc_sw128(a_base + k * 32, 0, 1024);
+            const uint64_t bdesc = p.b_mn ? make_smem_desc_sw128(b_base + k * 2048, 8192, 1024)
+                                          : make_smem_desc_sw128(b_base + k * 32, 0, 1024);
+            umma_bf16(d_tmem, adesc, bdesc, idesc, (kit | k) != 0 ? 1u : 0u);
+          }
+          umma_commit(&empty_bar[stage]);  // frees this smem stage once the MMAs above retire
+          if (++stage == stages) {
+            stage = 0;
+            phase ^= 1u;
+          }
+        }
+        umma_commit(&tfull_bar[acc]);  // accumulator complete -> epilogue
+        if (++acc == 2) {
+          acc = 0;
+          acc_phase ^= 1u;
+        }
+      }
+    }
+    __syncwarp();
+  } else if (warp >= 4) {
+    // ============================ epilogue (4 warps = 128 TMEM lanes) ============================
+    const int q = warp & 3;         // TMEM lane quadrant this warp may access
+    const int r = q * 32 + lane;    // row within the tile
+    int acc = 0;
+    uint32_t acc_phase = 0;
+    for (int t = blockIdx.x; t < total_tiles; t += gridDim.x) {
+      const TileCoord tc = decode_tile(p, t);
+      const int m0 = tc.m_tile * TC_BLOCK_M;
+      const int n0 = tc.n_tile * BN;
+      mbar_wait(&tfull_bar[acc], acc_phase);
+      tc_fence_after();
+
+      bool row_ok = true;
+      long long row_off = 0;  // element offset of (row, column n0) in D / residual
+      int yy = 0, xx = 0;
+      if (p.kind == KIND_GEMM) {
+        row_ok = (m0 + r) < p.m_valid;
+        row_off = static_cast<long long>(tc.z) * p.strideD + static_cast<long long>(m0 + r) * p.ldd + n0;
+      } else if (p.kind == KIND_CONV) {
+        yy = tc.y0 + (r >> p.bw_log2);
+        xx = tc.x0 + (r & ((1 << p.bw_log2) - 1));
+        row_off = static_cast<long long>(tc.b) * p.oB + static_cast<long long>(yy) * p.oY +
+                  static_cast<long long>(xx) * p.oX + p.o0 + n0;
+      } else {
+        row_ok = (m0 + r) < p.m_valid;
+        row_off = (static_cast<long long>(tc.z) * p.m_valid + (m0 + r)) * p.ldd + n0;
+      }
+      const uint32_t t_row = tmem_base + (static_cast<uint32_t>(q * 32) << 16) + static_cast<uint32_t>(acc * BN);
+
+      for (int c = 0; c < BN; c += 16) {
+        uint32_t v[16];
+        tmem_ld_x16(t_row + static_cast<uint32_t>(c), v);
+        tmem_ld_wait();
+        const int ncol = n0 + c;  // global column of v[0]
+        if (row_ok && ncol < p.n_valid) {
+          float f[16];
+#pragma unroll
+          for (int i = 0; i < 16; ++i) f[i] = __uint_as_float(v[i]) * p.alpha;
+          const bool full = (ncol + 16 <= p.n_valid);
+          if (p.bias != nullptr) {
+            if (full) {
+#pragma unroll
+              for (int i = 0; i < 16; i += 4) {
+                float4 bv = __ldg(reinterpret_cast<const float4*>(p.bias + ncol + i));
+                f[i] += bv.x; f[i + 1] += bv.y; f[i + 2] += bv.z; f[i + 3] += bv.w;
+              }
+            } else {
+              for (int i = 0; i < 16; ++i)
+                if (ncol + i < p.n_valid) f[i] += __ldg(p.bias + ncol + i);
+            }
+          }
+          if (p.out_mode == OUT_BF16) {
+            bf16* dst = reinterpret_cast<bf16*>(p.D) + row_off + c;
+            if (full) {
+              if (p.residual != nullptr) {
+                const uint4* rp = reinterpret_cast<const uint4*>(reinterpret_cast<const bf16*>(p.residual) + row_off + c);
+                uint4 r0 = __ldg(rp), r1 = __ldg(rp + 1);
+                uint32_t rw[8] = {r0.x, r0.y, r0.z, r0.w, r1.x, r1.y, r1.z, r1.w};
+#pragma unroll
+                for (int i = 0; i < 8; ++i) {
+                  float2 rv = unpack_bf16x2(rw[i]);
+                  f[2 * i] += rv.x;
+                  f[2 * i + 1] += rv.y;
+                }
+              }
+              uint4 o0, o1;
+              o0.x = pack_bf16x2(f[0], f[1]);   o0.y = pack_bf16x2(f[2], f[3]);
+              o0.z = pack_bf16x2(f[4], f[5]);   o0.w = pack_bf16x2(f[6], f[7]);
+              o1.x = pack_bf16x2(f[8], f[9]);   o1.y = pack_bf16x2(f[10], f[11]);
+              o1.z = pack_bf16x2(f[12], f[13]); o1.w = pack_bf16x2(f[14], f[15]);
+              reinterpret_cast<uint4*>(dst)[0] = o0;
+              reinterpret_cast<uint4*>(dst)[1] = o1;
+            } else {
+              for (int i = 0; i < 16; ++i)
+                if (ncol + i < p.n_valid) {
+                  float val = f[i];
+                  if (p.residual != nullptr)
+                    val += __bfloat162float(reinterpret_cast<const bf16*>(p.residual)[row_off + c + i]);
+                  dst[i] = __float2bfloat16_rn(val);
+                }
+            }
+          } else if (p.out_mode == OUT_F32) {
+            float* dst = reinterpret_cast<float*>(p.D) + row_off + c;
+            if (full) {
+              if (p.residual != nullptr) {
+                const float4* rp = reinterpret_cast<const float4*>(reinterpret_cast<const float*>(p.residual) + row_off + c);
+#pragma unroll
+                for (int i = 0; i < 4; ++i) {
+                  float4 rv = __ldg(rp + i);
+                  f[4 * i] += rv.x; f[4 * i + 1] += rv.y; f[4 * i + 2] += rv.z; f[4 * i + 3] += rv.w;
+                }
+              }
+#pragma unroll
+              for (int i = 0; i < 4; ++i)
+                reinterpret_cast<float4*>(dst)[i] = make_float4(f[4 * i], f[4 * i + 1], f[4 * i + 2], f[4 * i + 3]);
+            } else {
+              for (int i = 0; i < 16; ++i)
+                if (ncol + i < p.n_valid) {
+                  float val = f[i];
+                  if (p.residual != nullptr) val += reinterpret_cast<const float*>(p.residual)[row_off + c + i];
+                  dst[i] = val;
+                }
+            }
+          } else {  // OUT_NCHW_F32: D[b][n][yy][xx], consecutive lanes -> consecutive xx (coalesced)
+            float* base = reinterpret_cast<float*>(p.D);
+            for (int i = 0; i < 16; ++i)
+              if (ncol + i < p.n_valid) {
+                long long off = ((static_cast<long long>(tc.b) * p.n_valid + (ncol + i)) * p.out_h + yy) * p.out_w + xx;
+                base[off] = f[i];
+              }
+          }
+        }
+      }
+      tc_fence_before();
+      mbar_arrive(&tempty_bar[acc]);
+      if (++acc == 2) {
+        acc = 0;
+        acc_phase ^= 1u;
+      }
+    }
+  }
+
+  tc_fence_before();
+  __syncthreads();
+  if (warp == 2) {
+    tc_fence_after();
+    tmem_dealloc(tmem_base, TC_TMEM_COLS);
+  }
+}
+
+}  // namespace odvae

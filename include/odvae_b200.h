@@ -1,0 +1,191 @@
+/* odvae_b200 — C ABI of the B200-native OD-VAE AutoencoderKL hot path.
+ *
+ * Every entry point is `extern "C"`, takes plain device pointers + sizes + a CUDA stream handle
+ * (`void* stream` == cudaStream_t), enqueues work on that stream and returns immediately with a
+ * status code (0 = ok, negative = error).  Nothing here allocates, synchronises or throws.
+ * There is NO CPU fallback: on a device that is not sm_100 the calls return ODVAE_ERR_ARCH.
+ *
+ * Activation layout inside the library is NHWC ("channels-last"); `act_dtype` selects the element
+ * type of activation tensors: ODVAE_F32 (validation mode, SIMT kernels) or ODVAE_BF16 (the timed
+ * mode; convolutions / GEMMs run on tcgen05 tensor cores with fp32 accumulation in TMEM).
+ * Parameters and parameter gradients are fp32 in the reference's own layouts (OIHW conv weights,
+ * [out,in] linear weights) so reference checkpoints load unchanged.
+ *
+ * Each function cites the reference interface it replaces; paths are relative to the reference
+ * root, LD/ = submodules/latent-diffusion/.
+ */
+#ifndef ODVAE_B200_H
+#define ODVAE_B200_H
+
+#include <stddef.h>
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+#if defined(__GNUC__)
+#pragma GCC visibility push(default)
+#endif
+
+#define ODVAE_OK 0
+#define ODVAE_ERR_SHAPE (-1)     /* unsupported / inconsistent shape or argument */
+#define ODVAE_ERR_ARCH (-2)      /* device is not sm_100 */
+#define ODVAE_ERR_WORKSPACE (-3) /* workspace too small */
+#define ODVAE_ERR_CUDA (-4)      /* a CUDA runtime/driver call failed (see odvae_last_cuda_error) */
+
+#define ODVAE_F32 0
+#define ODVAE_BF16 1
+
+/* conv geometry selectors (LD/ldm/modules/diffusionmodules/model.py) */
+#define ODVAE_CONV_3x3_S1 0  /* Conv2d(k=3,s=1,p=1): model.py:92-106,383-387,487-491,529-533 */
+#define ODVAE_CONV_1x1 1     /* Conv2d(k=1): nin_shortcut model.py:115-119, q/k/v/proj :156-175 */
+#define ODVAE_CONV_3x3_S2 2  /* F.pad(0,1,0,1) + Conv2d(k=3,s=2,p=0): Downsample model.py:72-76 */
+
+/* conv implementation selectors */
+#define ODVAE_IMPL_SIMT 0 /* CUDA-core implicit GEMM, any dtype (validation / fp32 mode) */
+#define ODVAE_IMPL_TC 1   /* tcgen05 + TMA implicit GEMM, bf16 only */
+
+const char* odvae_status_string(int status);
+const char* odvae_last_cuda_error(void);
+/* 1 when the current device is compute capability 10.x */
+int odvae_device_supported(void);
+int odvae_version(void);
+
+/* ---------------------------------------------------------------------------------------------
+ * Layout / dtype conversion at the module boundary (AE.py:223, LD/ldm/models/autoencoder.py:344-349)
+ * ------------------------------------------------------------------------------------------- */
+/* src: NCHW fp32 [B,C,H,W] -> dst: NHWC act_dtype [B,H,W,Cpad], channels >= C zero-filled.
+ * Optional affine `dst = src*scale + shift` fuses the reference's _rescale (AE.py:434-436). */
+int odvae_nchw_to_nhwc(const float* src, void* dst, int B, int C, int H, int W, int Cpad, int act_dtype,
+                       float scale, float shift, void* stream);
+/* src: NHWC act_dtype [B,H,W,Cpad] -> dst NCHW fp32 [B,C,H,W] (first C channels) */
+int odvae_nhwc_to_nchw(const void* src, float* dst, int B, int C, int H, int W, int Cpad, int act_dtype,
+                       void* stream);
+/* global min and max of an fp32 tensor (AE.py:436 `_rescale`): out[0]=min, out[1]=max */
+int odvae_minmax(const float* src, int64_t n, float* out2, void* workspace, size_t ws_bytes, void* stream);
+
+/* ---------------------------------------------------------------------------------------------
+ * Convolution (torch.nn.Conv2d call sites).  x: NHWC [B,H,W,CinP]; y: NHWC
+ * [B,Ho,Wo,CoutP].  Weights are pre-packed by odvae_pack_conv_weight from the fp32 OIHW master.
+ * ------------------------------------------------------------------------------------------- */
+/* Packs fp32 OIHW [Cout,Cin,k,k] (k from geom) into the layouts the kernels consume.
+ *   which = 0: forward   [CoutP][taps][CinP]   (K-major rows per output channel)
+ *   which = 1: dgrad     [CinP][taps'][CoutP]  (taps rotated 180 degrees); for ODVAE_CONV_3x3_S2 four
+ *              input-parity-phase matrices [CinP][nt*CoutP] (nt = 4,2,2,1) are concatenated
+ * act_dtype selects bf16 (TC path) or f32 (SIMT path) packing. Padded rows/cols are zero. */
+int odvae_pack_conv_weight(const float* w_oihw, void* packed, int Cout, int Cin, int geom, int CoutP, int CinP,
+                           int which, int act_dtype, void* stream);
+/* 1 when fwd, dgrad and wgrad of this conv can all run on the tcgen05 engine (TMA tiling constraints:
+ * CinP % 64 == 0, CoutP % 64 == 0 for dgrad, power-of-two output width, >= 128 output pixels per image). */
+int odvae_conv2d_tc_supported(int B, int H, int W, int CinP, int CoutP, int geom);
+/* y = conv(x, w) + bias (+ residual).  `residual` (same layout as y) may be NULL.
+ * out_nchw_f32 != 0 writes y as NCHW fp32 [B,Cout,Ho,Wo] instead (decoder.conv_out -> dec_obj). */
+int odvae_conv2d_fwd(const void* x, const void* w_packed, const float* bias, const void* residual, void* y,
+                     int B, int H, int W, int CinP, int CoutP, int Cout, int geom, int act_dtype, int impl,
+                     int out_nchw_f32, void* stream);
+/* dx = conv_transpose(dy, w) (+ dx_add).  dy: NHWC [B,Ho,Wo,CoutP]; dx: NHWC [B,H,W,CinP].
+ * `w_packed` is the which=1 packing. */
+int odvae_conv2d_dgrad(const void* dy, const void* w_packed_dgrad, const void* dx_add, void* dx, int B, int H,
+                       int W, int CinP, int CoutP, int geom, int act_dtype, int impl, void* stream);
+/* dw (fp32 OIHW [Cout,Cin,kh,kw]) = sum over batch/pixels of dy (x) x ; db[Cout] = sum dy.
+ * Deterministic: split-K partials go to `workspace` and are reduced in a fixed order.
+ * accumulate != 0 adds into dw/db instead of overwriting. db may be NULL. */
+size_t odvae_conv2d_wgrad_workspace_bytes(int B, int H, int W, int CinP, int CoutP, int geom, int impl);
+int odvae_conv2d_wgrad(const void* x, const void* dy, float* dw_oihw, float* db, int B, int H, int W, int CinP,
+                       int CoutP, int Cin, int Cout, int geom, int act_dtype, int impl, int accumulate,
+                       void* workspace, size_t ws_bytes, void* stream);
+
+/* nearest-neighbour 2x upsample (F.interpolate, model.py:54) and its adjoint (2x2 sum-pool) */
+int odvae_upsample2x(const void* x, void* y, int B, int H, int W, int C, int act_dtype, void* stream);
+int odvae_upsample2x_bwd(const void* dy, void* dx, int B, int H, int W, int C, int act_dtype, void* stream);
+
+/* ---------------------------------------------------------------------------------------------
+ * Batched GEMM on tcgen05 (attention QK^T / PV and their gradients; torch.bmm at model.py:186-198).
+ * D[b] = alpha * op(A[b]) * op(B[b])^T (+bias[n]) (+residual), bf16 in, fp32 accumulate.
+ *   a_mn = 0: A stored [M][K] (K contiguous, ld = lda);  a_mn = 1: A stored [K][M] (M contiguous)
+ *   b_mn = 0: B stored [N][K] (K contiguous, ld = ldb);  b_mn = 1: B stored [K][N] (N contiguous)
+ * out_dtype: ODVAE_F32 or ODVAE_BF16.  strides are in elements.
+ * ------------------------------------------------------------------------------------------- */
+int odvae_gemm_bf16(const void* A, const void* B, void* D, int M, int N, int K, int batch, int64_t lda,
+                    int64_t ldb, int64_t ldd, int64_t strideA, int64_t strideB, int64_t strideD, int a_mn,
+                    int b_mn, int out_dtype, float alpha, const float* bias, const void* residual, void* stream);
+
+/* ---------------------------------------------------------------------------------------------
+ * GroupNorm(32, C, eps=1e-6, affine) [+ SiLU]  (Normalize model.py:38-39, nonlinearity :33-35)
+ * x, y: NHWC [B,HW,C]; stats: fp32 [B,G,2] = (mean, rstd).
+ * ------------------------------------------------------------------------------------------- */
+size_t odvae_groupnorm_workspace_bytes(int B, int HW, int C, int G);
+int odvae_groupnorm_stats(const void* x, float* stats, int B, int HW, int C, int G, float eps, int act_dtype,
+                          void* workspace, size_t ws_bytes, void* stream);
+int odvae_groupnorm_apply(const void* x, const float* stats, const float* gamma, const float* beta, void* y,
+                          int B, int HW, int C, int G, int silu, int act_dtype, void* stream);
+/* dx = d/dx [silu](GN(x)) . dy (+ dx_add);  dgamma/dbeta fp32 [C] (accumulate != 0 adds). */
+int odvae_groupnorm_bwd(const void* x, const float* stats, const float* gamma, const float* beta, const void* dy,
+                        const void* dx_add, void* dx, float* dgamma, float* dbeta, int B, int HW, int C, int G,
+                        int silu, int act_dtype, int accumulate, void* workspace, size_t ws_bytes, void* stream);
+
+/* ---------------------------------------------------------------------------------------------
+ * Attention core of AttnBlock (model.py:183-198): single head, scale = C^-0.5.
+ * qkv: NHWC-token layout [B,N,3C] (q | k | v per token).  P: bf16/f32 [B,N,N] probabilities (saved
+ * for backward).  o: [B,N,C].
+ * ------------------------------------------------------------------------------------------- */
+/* row softmax of fp32 scores S[rows][n] * scale -> P (act_dtype), in place allowed when f32 */
+int odvae_softmax_rows(const float* S, void* P, int64_t rows, int n, float scale, int act_dtype, void* stream);
+/* dS = P * (dP - rowsum(dP*P)) * scale ; dP fp32 [rows][n], P act_dtype, dS act_dtype */
+int odvae_softmax_rows_bwd(const float* dP, const void* P, void* dS, int64_t rows, int n, float scale,
+                           int act_dtype, void* stream);
+/* SIMT batched GEMM for the f32 validation mode (same operand conventions as odvae_gemm_bf16) */
+int odvae_gemm_simt(const void* A, const void* B, void* D, int M, int N, int K, int batch, int64_t lda,
+                    int64_t ldb, int64_t ldd, int64_t strideA, int64_t strideB, int64_t strideD, int a_mn,
+                    int b_mn, int in_dtype, int out_dtype, float alpha, const float* bias, const void* residual,
+                    void* stream);
+
+/* ---------------------------------------------------------------------------------------------
+ * Latent sampling + KL (DiagonalGaussianDistribution DIST.py:24-46, dropout/noise AE.py:226-241)
+ * moments: NHWC act_dtype [B,HW,2*Cz] (mean | logvar per pixel).
+ * outputs (all fp32, NCHW [B,Cz,h,w] = the module-boundary layout): mean, logvar (clamped).
+ * z: NHWC act_dtype [B,HW,CzPad] = (mean + std*eps)*keep*keep_scale + noise + enc_pose (zero padded).
+ * kl[B] = 0.5*sum(mean^2 + var - 1 - logvar).  eps/noise fp32 NCHW, keep uint8 NCHW, enc_pose fp32 [B,Cz*HW]
+ * (NCHW flattened; may be NULL).
+ * ------------------------------------------------------------------------------------------- */
+int odvae_sample_kl_fwd(const void* moments, const float* eps, const uint8_t* keep, const float* noise,
+                        const float* enc_pose, float keep_scale, float* mean, float* logvar, void* z,
+                        float* kl, int B, int HW, int Cz, int CzPad, int act_dtype, void* stream);
+/* dmoments = d(z)/d(moments)^T dz + dkl[b] * dKL/dmoments (+ direct grads on mean/logvar outputs).
+ * dz: NHWC act_dtype [B,HW,CzPad]; denc_pose fp32 [B,Cz*HW] (NCHW flattened) = dz. */
+int odvae_sample_kl_bwd(const void* dz, const float* dkl, const float* dmean_direct, const float* dlogvar_direct,
+                        const float* mean, const float* logvar, const float* eps, const uint8_t* keep,
+                        float keep_scale, void* dmoments, float* denc_pose, int B, int HW, int Cz, int CzPad,
+                        int act_dtype, void* stream);
+
+/* ---------------------------------------------------------------------------------------------
+ * Masked L1 reconstruction term (PoseLoss._get_rec_loss/_get_nll_loss LOSS.py:134-158, masks :250-257)
+ * x, xhat: NCHW fp32 [B,3,H,W]; mask2d: fp32 [B,1,H,W]; sums[b] = sum |x*m - xhat*m| (0 if !use_pixel).
+ * sgn (int8 NCHW) = sign(x*m - xhat*m)*m, saved for backward.
+ * ------------------------------------------------------------------------------------------- */
+int odvae_l1_masked_fwd(const float* x, const float* xhat, const float* mask2d, float* sums, int8_t* sgn, int B,
+                        int C, int HW, void* workspace, size_t ws_bytes, void* stream);
+size_t odvae_l1_masked_workspace_bytes(int B, int C, int HW);
+/* dxhat[b,c,p] = -sgn * coef[b]  (coef folds mask_bg, 1/(exp(logvar)+eps), 1/sum(mask_bg), upstream grad) */
+int odvae_l1_masked_bwd(const int8_t* sgn, const float* coef, float* dxhat, int B, int C, int HW, void* stream);
+
+/* ---------------------------------------------------------------------------------------------
+ * Fused Adam (AE.py:365-377: lr, betas=(0.5,0.9), eps=1e-8) + global-norm clip (CFG:140) on flat
+ * fp32 buffers.
+ * ------------------------------------------------------------------------------------------- */
+size_t odvae_sumsq_workspace_bytes(int64_t n);
+int odvae_sumsq(const float* g, int64_t n, float* out1, void* workspace, size_t ws_bytes, void* stream);
+int odvae_adam_step(float* p, const float* g, float* m, float* v, int64_t n, float lr, float beta1, float beta2,
+                    float eps, float bias_corr1, float bias_corr2, const float* gnorm_sq, float max_norm,
+                    void* stream);
+
+/* generic elementwise helpers on activations (residual adds that cannot be fused) */
+int odvae_add(const void* a, const void* b, void* out, int64_t n, int act_dtype, void* stream);
+
+#if defined(__GNUC__)
+#pragma GCC visibility pop
+#endif
+#ifdef __cplusplus
+}
+#endif
+#endif /* ODVAE_B200_H */

@@ -1,0 +1,146 @@
+"""GPU parity of the GEMM / convolution engines (tcgen05 and SIMT) through the C ABI.
+
+Reference here is torch fp32 math on the same (bf16-rounded) inputs: these are unit tests of single
+kernels; whole-path parity against the oracle/goldens lives in test_parity_gpu.py.
+Tolerances: bf16 tensor-core path <= 1e-2 relative (per-tensor max-abs / max-ref), fp32 SIMT <= 1e-4.
+"""
+import pytest
+import torch
+import torch.nn.functional as F
+
+pytestmark = pytest.mark.gpu
+
+from odvae_b200 import kernels as K  # noqa: E402
+from odvae_b200.lib import CONV_1x1, CONV_3x3_S1, CONV_3x3_S2, IMPL_SIMT, IMPL_TC  # noqa: E402
+
+DEV = "cuda"
+
+
+def rel_err(a, ref):
+    a, ref = a.float(), ref.float()
+    return float((a - ref).abs().max() / ref.abs().max().clamp_min(1e-20))
+
+
+def tol(dtype):
+    return 1e-2 if dtype == torch.bfloat16 else 1e-4
+
+
+def ref_conv(x_nhwc, w, b, geom):
+    x = x_nhwc.float().permute(0, 3, 1, 2)
+    if geom == CONV_3x3_S2:
+        return F.conv2d(F.pad(x, (0, 1, 0, 1)), w, b, stride=2)
+    if geom == CONV_1x1:
+        return F.conv2d(x, w, b)
+    return F.conv2d(x, w, b, padding=1)
+
+
+CONV_CASES = [
+    # B, H, W, Cin, Cout
+    (2, 32, 32, 64, 128),
+    (1, 16, 16, 128, 256),
+    (2, 16, 16, 64, 64),
+    (1, 128, 128, 64, 64),
+]
+
+
+IMPLS3 = [pytest.param(IMPL_TC, torch.bfloat16, id="tc-bf16"), pytest.param(IMPL_SIMT, torch.float32, id="simt-f32"),
+          pytest.param(IMPL_SIMT, torch.bfloat16, id="simt-bf16")]
+IMPLS2 = IMPLS3[:2]
+
+
+@pytest.mark.parametrize("impl,dtype", IMPLS3)
+@pytest.mark.parametrize("geom", [CONV_3x3_S1, CONV_1x1, CONV_3x3_S2])
+@pytest.mark.parametrize("case", CONV_CASES)
+def test_conv_fwd_dgrad_wgrad(impl, dtype, geom, case):
+    B, H, W, Cin, Cout = case
+    torch.manual_seed(0)
+    k = 1 if geom == CONV_1x1 else 3
+    x = torch.randn(B, H, W, Cin, device=DEV).to(dtype)
+    w = (torch.randn(Cout, Cin, k, k, device=DEV) / (Cin * k * k) ** 0.5)
+    b = torch.randn(Cout, device=DEV)
+    wq = w.to(dtype).float() if dtype == torch.bfloat16 else w
+    Ho, Wo = K.geom_out_hw(geom, H, W)
+    res = torch.randn(B, Ho, Wo, Cout, device=DEV).to(dtype)
+
+    xr = x.float().requires_grad_(True)
+    wr = wq.clone().requires_grad_(True)
+    y_ref = ref_conv(xr, wr, b, geom) + res.float().permute(0, 3, 1, 2)
+    dy = torch.randn(B, Ho, Wo, Cout, device=DEV).to(dtype)
+    y_ref.backward(dy.float().permute(0, 3, 1, 2))
+
+    wp = K.pack_conv_weight(w, geom, Cout, Cin, 0, dtype)
+    y = K.conv_fwd(x, wp, b, Cout, geom, impl, residual=res)
+    torch.cuda.synchronize()
+    assert rel_err(y.permute(0, 3, 1, 2), y_ref) < tol(dtype)
+
+    wd = K.pack_conv_weight(w, geom, Cout, Cin, 1, dtype)
+    add = torch.randn(B, H, W, Cin, device=DEV).to(dtype)
+    dx = K.conv_dgrad(dy, wd, Cin, geom, impl, (H, W), dx_add=add)
+    torch.cuda.synchronize()
+    assert rel_err(dx.float() - add.float(), xr.grad.permute(0, 2, 3, 1)) < 2 * tol(dtype)
+
+    dw, db = K.conv_wgrad(x, dy, Cin, Cout, geom, impl)
+    torch.cuda.synchronize()
+    assert rel_err(dw, wr.grad) < tol(dtype)
+    assert rel_err(db, dy.float().sum(dim=(0, 1, 2))) < tol(dtype)
+
+
+@pytest.mark.parametrize("impl,dtype", IMPLS2)
+def test_conv_out_nchw_thin(impl, dtype):
+    """decoder.conv_out: 128 -> 3 channels written as NCHW fp32 (weights padded to 16 rows)."""
+    B, H, W, Cin, Cout = 2, 32, 32, 128, 3
+    torch.manual_seed(1)
+    x = torch.randn(B, H, W, Cin, device=DEV).to(dtype)
+    w = torch.randn(Cout, Cin, 3, 3, device=DEV) / (Cin * 9) ** 0.5
+    b = torch.randn(Cout, device=DEV)
+    wq = w.to(dtype).float()
+    wp = K.pack_conv_weight(w, CONV_3x3_S1, 16, Cin, 0, dtype)
+    y = K.conv_fwd(x, wp, b, Cout, CONV_3x3_S1, impl, out_nchw_f32=True)
+    torch.cuda.synchronize()
+    assert y.shape == (B, Cout, H, W) and y.dtype == torch.float32
+    assert rel_err(y, ref_conv(x, wq, b, CONV_3x3_S1)) < tol(dtype)
+
+
+GEMM_CASES = [
+    # M, N, K, batch
+    (256, 256, 128, 2),
+    (128, 512, 64, 1),
+    (200, 192, 72, 3),
+    (1024, 1024, 256, 2),
+]
+
+
+@pytest.mark.parametrize("impl,dtype", IMPLS2)
+@pytest.mark.parametrize("a_mn,b_mn", [(False, False), (False, True), (True, False), (True, True)])
+@pytest.mark.parametrize("case", GEMM_CASES)
+@pytest.mark.parametrize("out_f32", [False, True])
+def test_gemm(impl, dtype, a_mn, b_mn, case, out_f32):
+    M, N, Kd, batch = case
+    torch.manual_seed(2)
+    A = torch.randn(batch, M, Kd, device=DEV).to(dtype)
+    Bm = torch.randn(batch, N, Kd, device=DEV).to(dtype)
+    ref = 0.5 * torch.bmm(A.float(), Bm.float().transpose(1, 2))
+    As = A.transpose(1, 2).contiguous() if a_mn else A
+    Bs = Bm.transpose(1, 2).contiguous() if b_mn else Bm
+    out_dtype = torch.float32 if out_f32 else dtype
+    D = K.gemm(As, Bs, M, N, Kd, batch=batch, strideA=M * Kd, strideB=N * Kd, a_mn=a_mn, b_mn=b_mn,
+               out_dtype=out_dtype, alpha=0.5, impl=impl)
+    torch.cuda.synchronize()
+    assert rel_err(D, ref) < tol(dtype)
+
+
+def test_gemm_tc_strided_views():
+    """q/k/v live interleaved in one [B,N,3C] tensor (row stride 3C); S = q k^T, O = P v."""
+    Bn, N, C = 2, 256, 128
+    torch.manual_seed(3)
+    qkv = torch.randn(Bn, N, 3 * C, device=DEV).bfloat16()
+    q, k, v = qkv[..., :C], qkv[..., C:2 * C], qkv[..., 2 * C:]
+    S = K.gemm(q, k, N, N, C, batch=Bn, lda=3 * C, ldb=3 * C, strideA=N * 3 * C, strideB=N * 3 * C,
+               out_dtype=torch.float32, alpha=C ** -0.5)
+    torch.cuda.synchronize()
+    S_ref = torch.bmm(q.float(), k.float().transpose(1, 2)) * C ** -0.5
+    assert rel_err(S, S_ref) < 1e-2
+    P = torch.softmax(S_ref, dim=-1).bfloat16()
+    O = K.gemm(P, v, N, C, N, batch=Bn, ldb=3 * C, strideA=N * N, strideB=N * 3 * C, b_mn=True)
+    torch.cuda.synchronize()
+    assert rel_err(O, torch.bmm(P.float(), v.float())) < 1e-2

@@ -1,0 +1,370 @@
+// GroupNorm(32 groups, eps, affine) [+ SiLU] forward / backward on NHWC activations.
+// Reference: Normalize (LD model.py:38-39) + nonlinearity x*sigmoid(x) (model.py:33-35).
+// Memory-bound: every pass reads whole pixels (all channels, 16-byte vectors, fully coalesced);
+// per-(image,channel) partial sums go through a small fp32 workspace and are combined in a fixed
+// order (deterministic, no atomics).
+#include "common.cuh"
+
+namespace odvae {
+
+template <typename T> struct VecN;
+template <> struct VecN<float> { static constexpr int V = 4; };
+template <> struct VecN<bf16> { static constexpr int V = 8; };
+
+static constexpr int GN_THREADS = 256;
+
+// MODE 0: per-(b,c) sums of (x, x^2)          -> forward statistics
+// MODE 1: per-(b,c) sums of (dy', dy' * xhat)  -> backward reductions, dy' = dy * silu'(u) when silu
+// part layout: [B][nsplit][C][2]
+template <typename T, int MODE>
+__global__ void __launch_bounds__(GN_THREADS)
+gn_reduce_kernel(const T* __restrict__ x, const T* __restrict__ dy, const float* __restrict__ stats,
+                 const float* __restrict__ gamma, const float* __restrict__ beta, float* __restrict__ part, int HW,
+                 int C, int G, int silu) {
+  constexpr int V = VecN<T>::V;
+  const int cv = C / V;
+  const int rows = GN_THREADS / cv;
+  const int col = threadIdx.x % cv, row = threadIdx.x / cv;
+  const int b = blockIdx.y, split = blockIdx.x, nsplit = gridDim.x;
+  const int per = (HW + nsplit - 1) / nsplit;
+  const int p0 = split * per;
+  const int p1 = p0 + per < HW ? p0 + per : HW;
+  const int c0 = col * V;
+
+  float s0[V], s1[V];
+#pragma unroll
+  for (int j = 0; j < V; ++j) s0[j] = s1[j] = 0.0f;
+  float mu[V], rs[V], sc[V], sh[V];
+  if (MODE == 1) {
+    const int cpg = C / G;
+#pragma unroll
+    for (int j = 0; j < V; ++j) {
+      const int c = c0 + j;
+      const int g = c / cpg;
+      mu[j] = __ldg(stats + (static_cast<long long>(b) * G + g) * 2);
+      rs[j] = __ldg(stats + (static_cast<long long>(b) * G + g) * 2 + 1);
+      const float gm = __ldg(gamma + c);
+      sc[j] = rs[j] * gm;
+      sh[j] = __ldg(beta + c) - mu[j] * sc[j];
+    }
+  }
+  if (row < rows) {
+    const T* xb = x + static_cast<long long>(b) * HW * C + c0;
+    const T* dyb = MODE == 1 ? dy + static_cast<long long>(b) * HW * C + c0 : nullptr;
+    for (int p = p0 + row; p < p1; p += rows) {
+      T xv[V];
+      *reinterpret_cast<uint4*>(xv) = __ldg(reinterpret_cast<const uint4*>(xb + static_cast<long long>(p) * C));
+      if (MODE == 0) {
+#pragma unroll
+        for (int j = 0; j < V; ++j) {
+          const float v = to_f32<T>(xv[j]);
+          s0[j] += v;
+          s1[j] = fmaf(v, v, s1[j]);
+        }
+      } else {
+        T dv[V];
+        *reinterpret_cast<uint4*>(dv) = __ldg(reinterpret_cast<const uint4*>(dyb + static_cast<long long>(p) * C));
+#pragma unroll
+        for (int j = 0; j < V; ++j) {
+          const float v = to_f32<T>(xv[j]);
+          float d = to_f32<T>(dv[j]);
+          if (silu) d *= silu_grad_f(fmaf(v, sc[j], sh[j]));
+          s0[j] += d;
+          s1[j] = fmaf(d, (v - mu[j]) * rs[j], s1[j]);
+        }
+      }
+    }
+  }
+  // block reduction over rows: red[2][rows][C]
+  extern __shared__ float red[];
+  float* r0 = red;
+  float* r1 = red + rows * C;
+  if (row < rows) {
+#pragma unroll
+    for (int j = 0; j < V; ++j) {
+      r0[row * C + c0 + j] = s0[j];
+      r1[row * C + c0 + j] = s1[j];
+    }
+  }
+  __syncthreads();
+  for (int c = threadIdx.x; c < C; c += GN_THREADS) {
+    float a = 0.0f, bb = 0.0f;
+    for (int r = 0; r < rows; ++r) {
+      a += r0[r * C + c];
+      bb += r1[r * C + c];
+    }
+    float* dst = part + ((static_cast<long long>(b) * nsplit + split) * C + c) * 2;
+    dst[0] = a;
+    dst[1] = bb;
+  }
+}
+
+// forward finalize: one CTA per image; stats[b][g] = (mean, rstd)
+__global__ void gn_stats_finalize_kernel(const float* __restrict__ part, float* __restrict__ stats, int nsplit, int HW,
+                                         int C, int G, float eps) {
+  const int b = blockIdx.x;
+  const int cpg = C / G;
+  for (int g = threadIdx.x; g < G; g += blockDim.x) {
+    float s = 0.0f, ss = 0.0f;
+    for (int sp = 0; sp < nsplit; ++sp) {
+      const float* src = part + ((static_cast<long long>(b) * nsplit + sp) * C + g * cpg) * 2;
+      for (int j = 0; j < cpg; ++j) {
+        s += src[2 * j];
+        ss += src[2 * j + 1];
+      }
+    }
+    const float n = static_cast<float>(cpg) * HW;
+    const float mean = s / n;
+    float var = ss / n - mean * mean;
+    var = var < 0.0f ? 0.0f : var;
+    stats[(static_cast<long long>(b) * G + g) * 2] = mean;
+    stats[(static_cast<long long>(b) * G + g) * 2 + 1] = rsqrtf(var + eps);
+  }
+}
+
+// y = [silu]((x - mean) * rstd * gamma + beta)
+template <typename T>
+__global__ void __launch_bounds__(GN_THREADS)
+gn_apply_kernel(const T* __restrict__ x, const float* __restrict__ stats, const float* __restrict__ gamma,
+                const float* __restrict__ beta, T* __restrict__ y, int HW, int C, int G, int silu) {
+  constexpr int V = VecN<T>::V;
+  extern __shared__ float sm[];
+  float* scale = sm;
+  float* shift = sm + C;
+  const int b = blockIdx.y;
+  const int cpg = C / G;
+  for (int c = threadIdx.x; c < C; c += GN_THREADS) {
+    const int g = c / cpg;
+    const float mean = __ldg(stats + (static_cast<long long>(b) * G + g) * 2);
+    const float rstd = __ldg(stats + (static_cast<long long>(b) * G + g) * 2 + 1);
+    const float sc = rstd * __ldg(gamma + c);
+    scale[c] = sc;
+    shift[c] = __ldg(beta + c) - mean * sc;
+  }
+  __syncthreads();
+  const int cv = C / V;
+  const long long nvec = static_cast<long long>(HW) * cv;
+  const uint4* xb = reinterpret_cast<const uint4*>(x + static_cast<long long>(b) * HW * C);
+  uint4* yb = reinterpret_cast<uint4*>(y + static_cast<long long>(b) * HW * C);
+  for (long long i = blockIdx.x * static_cast<long long>(GN_THREADS) + threadIdx.x; i < nvec;
+       i += static_cast<long long>(gridDim.x) * GN_THREADS) {
+    const int c0 = static_cast<int>(i % cv) * V;
+    T xv[V], yv[V];
+    *reinterpret_cast<uint4*>(xv) = __ldg(xb + i);
+#pragma unroll
+    for (int j = 0; j < V; ++j) {
+      float u = fmaf(to_f32<T>(xv[j]), scale[c0 + j], shift[c0 + j]);
+      if (silu) u = silu_f(u);
+      yv[j] = from_f32<T>(u);
+    }
+    yb[i] = *reinterpret_cast<const uint4*>(yv);
+  }
+}
+
+// backward finalize A: one CTA per image. AB[b][c] = (sum dy', sum dy' xhat); coef[b][g] = (c2, c3)
+//   dx = c1 * dy' + c2 * x + c3,  c1 = rstd*gamma_c, c2 = -rstd^2 s2/n, c3 = rstd (mean rstd s2 - s1)/n
+__global__ void gn_bwd_finalize_a_kernel(const float* __restrict__ part, const float* __restrict__ stats,
+                                         const float* __restrict__ gamma, float* __restrict__ AB,
+                                         float* __restrict__ coef, int nsplit, int HW, int C, int G) {
+  extern __shared__ float sm[];  // [C][2] gamma-weighted sums
+  const int b = blockIdx.x;
+  const int cpg = C / G;
+  for (int c = threadIdx.x; c < C; c += blockDim.x) {
+    float a = 0.0f, bb = 0.0f;
+    for (int sp = 0; sp < nsplit; ++sp) {
+      const float* src = part + ((static_cast<long long>(b) * nsplit + sp) * C + c) * 2;
+      a += src[0];
+      bb += src[1];
+    }
+    AB[(static_cast<long long>(b) * C + c) * 2] = a;
+    AB[(static_cast<long long>(b) * C + c) * 2 + 1] = bb;
+    const float gm = __ldg(gamma + c);
+    sm[2 * c] = gm * a;
+    sm[2 * c + 1] = gm * bb;
+  }
+  __syncthreads();
+  for (int g = threadIdx.x; g < G; g += blockDim.x) {
+    float s1 = 0.0f, s2 = 0.0f;
+    for (int j = 0; j < cpg; ++j) {
+      s1 += sm[2 * (g * cpg + j)];
+      s2 += sm[2 * (g * cpg + j) + 1];
+    }
+    const float mean = stats[(static_cast<long long>(b) * G + g) * 2];
+    const float rstd = stats[(static_cast<long long>(b) * G + g) * 2 + 1];
+    const float inv_n = 1.0f / (static_cast<float>(cpg) * HW);
+    coef[(static_cast<long long>(b) * G + g) * 2] = -rstd * rstd * s2 * inv_n;
+    coef[(static_cast<long long>(b) * G + g) * 2 + 1] = rstd * (mean * rstd * s2 - s1) * inv_n;
+  }
+}
+
+// backward finalize B: dgamma[c] = sum_b AB[b][c][1], dbeta[c] = sum_b AB[b][c][0]
+__global__ void gn_bwd_finalize_b_kernel(const float* __restrict__ AB, float* __restrict__ dgamma,
+                                         float* __restrict__ dbeta, int B, int C, int accumulate) {
+  const int c = blockIdx.x * blockDim.x + threadIdx.x;
+  if (c >= C) return;
+  float a = 0.0f, bb = 0.0f;
+  for (int b = 0; b < B; ++b) {
+    a += AB[(static_cast<long long>(b) * C + c) * 2];
+    bb += AB[(static_cast<long long>(b) * C + c) * 2 + 1];
+  }
+  dbeta[c] = accumulate ? dbeta[c] + a : a;
+  dgamma[c] = accumulate ? dgamma[c] + bb : bb;
+}
+
+template <typename T>
+__global__ void __launch_bounds__(GN_THREADS)
+gn_bwd_apply_kernel(const T* __restrict__ x, const T* __restrict__ dy, const T* __restrict__ dx_add,
+                    const float* __restrict__ stats, const float* __restrict__ gamma, const float* __restrict__ beta,
+                    const float* __restrict__ coef, T* __restrict__ dx, int HW, int C, int G, int silu) {
+  constexpr int V = VecN<T>::V;
+  extern __shared__ float sm[];
+  float* scale = sm;          // rstd*gamma  (= c1)
+  float* shift = sm + C;      // beta - mean*rstd*gamma
+  float* c2 = sm + 2 * C;
+  float* c3 = sm + 3 * C;
+  const int b = blockIdx.y;
+  const int cpg = C / G;
+  for (int c = threadIdx.x; c < C; c += GN_THREADS) {
+    const int g = c / cpg;
+    const float mean = __ldg(stats + (static_cast<long long>(b) * G + g) * 2);
+    const float rstd = __ldg(stats + (static_cast<long long>(b) * G + g) * 2 + 1);
+    const float sc = rstd * __ldg(gamma + c);
+    scale[c] = sc;
+    shift[c] = __ldg(beta + c) - mean * sc;
+    c2[c] = __ldg(coef + (static_cast<long long>(b) * G + g) * 2);
+    c3[c] = __ldg(coef + (static_cast<long long>(b) * G + g) * 2 + 1);
+  }
+  __syncthreads();
+  const int cv = C / V;
+  const long long nvec = static_cast<long long>(HW) * cv;
+  const long long base = static_cast<long long>(b) * HW * C;
+  const uint4* xb = reinterpret_cast<const uint4*>(x + base);
+  const uint4* dyb = reinterpret_cast<const uint4*>(dy + base);
+  const uint4* ab = dx_add ? reinterpret_cast<const uint4*>(dx_add + base) : nullptr;
+  uint4* dxb = reinterpret_cast<uint4*>(dx + base);
+  for (long long i = blockIdx.x * static_cast<long long>(GN_THREADS) + threadIdx.x; i < nvec;
+       i += static_cast<long long>(gridDim.x) * GN_THREADS) {
+    const int c0 = static_cast<int>(i % cv) * V;
+    T xv[V], dv[V], av[V], ov[V];
+    *reinterpret_cast<uint4*>(xv) = __ldg(xb + i);
+    *reinterpret_cast<uint4*>(dv) = __ldg(dyb + i);
+    if (ab) *reinterpret_cast<uint4*>(av) = __ldg(ab + i);
+#pragma unroll
+    for (int j = 0; j < V; ++j) {
+      const float xf = to_f32<T>(xv[j]);
+      float d = to_f32<T>(dv[j]);
+      if (silu) d *= silu_grad_f(fmaf(xf, scale[c0 + j], shift[c0 + j]));
+      float o = fmaf(scale[c0 + j], d, fmaf(c2[c0 + j], xf, c3[c0 + j]));
+      if (ab) o += to_f32<T>(av[j]);
+      ov[j] = from_f32<T>(o);
+    }
+    dxb[i] = *reinterpret_cast<const uint4*>(ov);
+  }
+}
+
+static int gn_nsplit(int B, int HW) {
+  int target = (2 * num_sms() + B - 1) / B;
+  int maxs = HW / 32;
+  if (maxs < 1) maxs = 1;
+  if (target > maxs) target = maxs;
+  if (target > 128) target = 128;
+  if (target < 1) target = 1;
+  return target;
+}
+static bool gn_shape_ok(int C, int G, int V) {
+  if (C % G != 0 || C % V != 0) return false;
+  const int cv = C / V;
+  return cv <= GN_THREADS && (GN_THREADS % cv) == 0 && C <= 2048;
+}
+static int gn_apply_blocks(int B, int HW, int C, int V) {
+  long long nvec = static_cast<long long>(HW) * (C / V);
+  long long blocks = (nvec + GN_THREADS * 4 - 1) / (GN_THREADS * 4);
+  long long cap = (8ll * num_sms() + B - 1) / B;
+  if (cap < 1) cap = 1;
+  if (blocks > cap) blocks = cap;
+  if (blocks < 1) blocks = 1;
+  return static_cast<int>(blocks);
+}
+
+}  // namespace odvae
+
+using namespace odvae;
+
+extern "C" {
+
+size_t odvae_groupnorm_workspace_bytes(int B, int HW, int C, int G) {
+  const int ns = gn_nsplit(B, HW);
+  return (static_cast<size_t>(B) * ns * C * 2 + static_cast<size_t>(B) * C * 2 + static_cast<size_t>(B) * G * 2) * sizeof(float) + 256;
+}
+
+int odvae_groupnorm_stats(const void* x, float* stats, int B, int HW, int C, int G, float eps, int act_dtype,
+                          void* workspace, size_t ws_bytes, void* stream) {
+  cudaStream_t st = static_cast<cudaStream_t>(stream);
+  const int V = act_dtype == ODVAE_BF16 ? 8 : 4;
+  if (!gn_shape_ok(C, G, V)) return ODVAE_ERR_SHAPE;
+  const int ns = gn_nsplit(B, HW);
+  if (ws_bytes < static_cast<size_t>(B) * ns * C * 2 * sizeof(float)) return ODVAE_ERR_WORKSPACE;
+  float* part = reinterpret_cast<float*>(workspace);
+  const int rows = GN_THREADS / (C / V);
+  const size_t smem = static_cast<size_t>(2) * rows * C * sizeof(float);
+  dim3 grid(ns, B);
+  if (act_dtype == ODVAE_BF16)
+    gn_reduce_kernel<bf16, 0><<<grid, GN_THREADS, smem, st>>>(reinterpret_cast<const bf16*>(x), nullptr, nullptr, nullptr, nullptr, part, HW, C, G, 0);
+  else
+    gn_reduce_kernel<float, 0><<<grid, GN_THREADS, smem, st>>>(reinterpret_cast<const float*>(x), nullptr, nullptr, nullptr, nullptr, part, HW, C, G, 0);
+  int s = check_launch("gn_reduce_kernel<0>");
+  if (s != ODVAE_OK) return s;
+  gn_stats_finalize_kernel<<<B, 32, 0, st>>>(part, stats, ns, HW, C, G, eps);
+  return check_launch("gn_stats_finalize_kernel");
+}
+
+int odvae_groupnorm_apply(const void* x, const float* stats, const float* gamma, const float* beta, void* y, int B,
+                          int HW, int C, int G, int silu, int act_dtype, void* stream) {
+  cudaStream_t st = static_cast<cudaStream_t>(stream);
+  const int V = act_dtype == ODVAE_BF16 ? 8 : 4;
+  if (!gn_shape_ok(C, G, V)) return ODVAE_ERR_SHAPE;
+  dim3 grid(gn_apply_blocks(B, HW, C, V), B);
+  const size_t smem = static_cast<size_t>(2) * C * sizeof(float);
+  if (act_dtype == ODVAE_BF16)
+    gn_apply_kernel<bf16><<<grid, GN_THREADS, smem, st>>>(reinterpret_cast<const bf16*>(x), stats, gamma, beta, reinterpret_cast<bf16*>(y), HW, C, G, silu);
+  else
+    gn_apply_kernel<float><<<grid, GN_THREADS, smem, st>>>(reinterpret_cast<const float*>(x), stats, gamma, beta, reinterpret_cast<float*>(y), HW, C, G, silu);
+  return check_launch("gn_apply_kernel");
+}
+
+int odvae_groupnorm_bwd(const void* x, const float* stats, const float* gamma, const float* beta, const void* dy,
+                        const void* dx_add, void* dx, float* dgamma, float* dbeta, int B, int HW, int C, int G,
+                        int silu, int act_dtype, int accumulate, void* workspace, size_t ws_bytes, void* stream) {
+  cudaStream_t st = static_cast<cudaStream_t>(stream);
+  const int V = act_dtype == ODVAE_BF16 ? 8 : 4;
+  if (!gn_shape_ok(C, G, V)) return ODVAE_ERR_SHAPE;
+  const int ns = gn_nsplit(B, HW);
+  if (ws_bytes < odvae_groupnorm_workspace_bytes(B, HW, C, G) - 256) return ODVAE_ERR_WORKSPACE;
+  float* part = reinterpret_cast<float*>(workspace);
+  float* AB = part + static_cast<size_t>(B) * ns * C * 2;
+  float* coef = AB + static_cast<size_t>(B) * C * 2;
+  const int rows = GN_THREADS / (C / V);
+  const size_t smem = static_cast<size_t>(2) * rows * C * sizeof(float);
+  dim3 grid(ns, B);
+  if (act_dtype == ODVAE_BF16)
+    gn_reduce_kernel<bf16, 1><<<grid, GN_THREADS, smem, st>>>(reinterpret_cast<const bf16*>(x), reinterpret_cast<const bf16*>(dy), stats, gamma, beta, part, HW, C, G, silu);
+  else
+    gn_reduce_kernel<float, 1><<<grid, GN_THREADS, smem, st>>>(reinterpret_cast<const float*>(x), reinterpret_cast<const float*>(dy), stats, gamma, beta, part, HW, C, G, silu);
+  int s = check_launch("gn_reduce_kernel<1>");
+  if (s != ODVAE_OK) return s;
+  gn_bwd_finalize_a_kernel<<<B, 256, static_cast<size_t>(2) * C * sizeof(float), st>>>(part, stats, gamma, AB, coef, ns, HW, C, G);
+  s = check_launch("gn_bwd_finalize_a_kernel");
+  if (s != ODVAE_OK) return s;
+  gn_bwd_finalize_b_kernel<<<(C + 127) / 128, 128, 0, st>>>(AB, dgamma, dbeta, B, C, accumulate);
+  s = check_launch("gn_bwd_finalize_b_kernel");
+  if (s != ODVAE_OK) return s;
+  dim3 grid2(gn_apply_blocks(B, HW, C, V), B);
+  const size_t smem2 = static_cast<size_t>(4) * C * sizeof(float);
+  if (act_dtype == ODVAE_BF16)
+    gn_bwd_apply_kernel<bf16><<<grid2, GN_THREADS, smem2, st>>>(reinterpret_cast<const bf16*>(x), reinterpret_cast<const bf16*>(dy), reinterpret_cast<const bf16*>(dx_add), stats, gamma, beta, coef, reinterpret_cast<bf16*>(dx), HW, C, G, silu);
+  else
+    gn_bwd_apply_kernel<float><<<grid2, GN_THREADS, smem2, st>>>(reinterpret_cast<const float*>(x), reinterpret_cast<const float*>(dy), reinterpret_cast<const float*>(dx_add), stats, gamma, beta, coef, reinterpret_cast<float*>(dx), HW, C, G, silu);
+  return check_launch("gn_bwd_apply_kernel");
+}
+
+}  // extern "C"

@@ -1,0 +1,452 @@
+// Memory-bound kernels around the GEMM engines: attention softmax fwd/bwd, reparameterised latent
+// sampling + KL, masked L1 reconstruction sums, small-MLP activations, column sums, rescale.
+// All reductions are fixed-order (no atomics) so results are bit-stable run to run.
+#include "common.cuh"
+#include "engine_host.h"
+
+namespace odvae {
+
+// ---------------------------------------------------------------------------------------------
+// group reductions: WIDTH = 32 (one warp per row) or 256 (one CTA per row)
+// ---------------------------------------------------------------------------------------------
+template <int WIDTH, bool IS_MAX>
+__device__ __forceinline__ float group_reduce(float v, float* sm) {
+  v = IS_MAX ? warp_max(v) : warp_sum(v);
+  if (WIDTH == 32) return v;
+  const int w = threadIdx.x >> 5, l = threadIdx.x & 31;
+  __syncthreads();  // protect sm from the previous use
+  if (l == 0) sm[w] = v;
+  __syncthreads();
+  float r = (l < WIDTH / 32) ? sm[l] : (IS_MAX ? -INFINITY : 0.0f);
+  r = IS_MAX ? warp_max(r) : warp_sum(r);
+  return r;
+}
+
+// P[row][:] = softmax(S[row][:] * scale).  Three passes over a row that stays in L1/L2.
+template <typename T, int WIDTH>
+__global__ void __launch_bounds__(256) softmax_rows_kernel(const float* __restrict__ S, T* __restrict__ P,
+                                                           long long rows, int n, float scale) {
+  __shared__ float sm[8];
+  const int rows_per_blk = 256 / WIDTH;
+  const int sub = threadIdx.x / WIDTH, t = threadIdx.x % WIDTH;
+  for (long long row = static_cast<long long>(blockIdx.x) * rows_per_blk + sub; row < rows;
+       row += static_cast<long long>(gridDim.x) * rows_per_blk) {
+    const float4* s4 = reinterpret_cast<const float4*>(S + row * n);
+    const int nv = n >> 2;
+    float mx = -INFINITY;
+    for (int i = t; i < nv; i += WIDTH) {
+      const float4 v = s4[i];
+      mx = fmaxf(fmaxf(mx, fmaxf(v.x, v.y)), fmaxf(v.z, v.w));
+    }
+    mx = group_reduce<WIDTH, true>(mx, sm) * scale;
+    float sum = 0.0f;
+    for (int i = t; i < nv; i += WIDTH) {
+      const float4 v = s4[i];
+      sum += expf(v.x * scale - mx) + expf(v.y * scale - mx) + expf(v.z * scale - mx) + expf(v.w * scale - mx);
+    }
+    sum = group_reduce<WIDTH, false>(sum, sm);
+    const float inv = 1.0f / sum;
+    T* prow = P + row * n;
+    for (int i = t; i < nv; i += WIDTH) {
+      const float4 v = s4[i];
+      const float e0 = expf(v.x * scale - mx) * inv, e1 = expf(v.y * scale - mx) * inv;
+      const float e2 = expf(v.z * scale - mx) * inv, e3 = expf(v.w * scale - mx) * inv;
+      if (sizeof(T) == 4) {
+        reinterpret_cast<float4*>(prow)[i] = make_float4(e0, e1, e2, e3);
+      } else {
+        uint2 o;
+        o.x = pack_bf16x2(e0, e1);
+        o.y = pack_bf16x2(e2, e3);
+        reinterpret_cast<uint2*>(prow)[i] = o;
+      }
+    }
+    if (WIDTH != 32) __syncthreads();
+  }
+}
+
+template <typename T> __device__ __forceinline__ void load4(const T* p, int i, float (&f)[4]);
+template <> __device__ __forceinline__ void load4<float>(const float* p, int i, float (&f)[4]) {
+  const float4 v = reinterpret_cast<const float4*>(p)[i];
+  f[0] = v.x; f[1] = v.y; f[2] = v.z; f[3] = v.w;
+}
+template <> __device__ __forceinline__ void load4<bf16>(const bf16* p, int i, float (&f)[4]) {
+  const uint2 v = reinterpret_cast<const uint2*>(p)[i];
+  const float2 a = unpack_bf16x2(v.x), b = unpack_bf16x2(v.y);
+  f[0] = a.x; f[1] = a.y; f[2] = b.x; f[3] = b.y;
+}
+template <typename T> __device__ __forceinline__ void store4(T* p, int i, const float (&f)[4]);
+template <> __device__ __forceinline__ void store4<float>(float* p, int i, const float (&f)[4]) {
+  reinterpret_cast<float4*>(p)[i] = make_float4(f[0], f[1], f[2], f[3]);
+}
+template <> __device__ __forceinline__ void store4<bf16>(bf16* p, int i, const float (&f)[4]) {
+  uint2 o;
+  o.x = pack_bf16x2(f[0], f[1]);
+  o.y = pack_bf16x2(f[2], f[3]);
+  reinterpret_cast<uint2*>(p)[i] = o;
+}
+
+// dS = P * (dP - sum_j dP_j P_j) * scale
+template <typename T, int WIDTH>
+__global__ void __launch_bounds__(256) softmax_rows_bwd_kernel(const float* __restrict__ dP, const T* __restrict__ P,
+                                                               T* __restrict__ dS, long long rows, int n,
+                                                               float scale) {
+  __shared__ float sm[8];
+  const int rows_per_blk = 256 / WIDTH;
+  const int sub = threadIdx.x / WIDTH, t = threadIdx.x % WIDTH;
+  for (long long row = static_cast<long long>(blockIdx.x) * rows_per_blk + sub; row < rows;
+       row += static_cast<long long>(gridDim.x) * rows_per_blk) {
+    const float* dprow = dP + row * n;
+    const T* prow = P + row * n;
+    const int nv = n >> 2;
+    float dot = 0.0f;
+    for (int i = t; i < nv; i += WIDTH) {
+      float d[4], p[4];
+      load4<float>(dprow, i, d);
+      load4<T>(prow, i, p);
+      dot += d[0] * p[0] + d[1] * p[1] + d[2] * p[2] + d[3] * p[3];
+    }
+    dot = group_reduce<WIDTH, false>(dot, sm);
+    T* orow = dS + row * n;
+    for (int i = t; i < nv; i += WIDTH) {
+      float d[4], p[4], o[4];
+      load4<float>(dprow, i, d);
+      load4<T>(prow, i, p);
+#pragma unroll
+      for (int j = 0; j < 4; ++j) o[j] = p[j] * (d[j] - dot) * scale;
+      store4<T>(orow, i, o);
+    }
+    if (WIDTH != 32) __syncthreads();
+  }
+}
+
+// ---------------------------------------------------------------------------------------------
+// Latent sampling + KL.  One CTA per sample; element order = NCHW (c*HW + p) to match the
+// module-boundary tensors (mean, logvar, eps, keep, noise, enc_pose).
+// ---------------------------------------------------------------------------------------------
+__device__ __forceinline__ float block_sum_256(float v, float* sm) {
+  v = warp_sum(v);
+  const int w = threadIdx.x >> 5, l = threadIdx.x & 31;
+  __syncthreads();
+  if (l == 0) sm[w] = v;
+  __syncthreads();
+  float r = l < 8 ? sm[l] : 0.0f;
+  return warp_sum(r);
+}
+
+template <typename T>
+__global__ void __launch_bounds__(256) sample_kl_fwd_kernel(
+    const T* __restrict__ moments, const float* __restrict__ eps, const uint8_t* __restrict__ keep,
+    const float* __restrict__ noise, const float* __restrict__ enc_pose, float keep_scale, float* __restrict__ mean_o,
+    float* __restrict__ logvar_o, T* __restrict__ z, float* __restrict__ kl, int HW, int Cz, int CzPad, int ldm) {
+  __shared__ float sm[8];
+  const int b = blockIdx.x;
+  const int n = Cz * HW;
+  float acc = 0.0f;
+  for (int i = threadIdx.x; i < n; i += 256) {
+    const int c = i / HW, p = i - c * HW;
+    const long long mrow = (static_cast<long long>(b) * HW + p) * ldm;
+    const float mu = to_f32<T>(moments[mrow + c]);
+    float lv = to_f32<T>(moments[mrow + Cz + c]);
+    lv = fminf(fmaxf(lv, -30.0f), 20.0f);
+    const float sd = expf(0.5f * lv), var = expf(lv);
+    const long long o = static_cast<long long>(b) * n + i;
+    mean_o[o] = mu;
+    logvar_o[o] = lv;
+    acc += mu * mu + var - 1.0f - lv;
+    if (z != nullptr) {
+      float zz = mu + sd * eps[o];
+      if (keep != nullptr) zz = keep[o] ? zz * keep_scale : 0.0f;
+      if (noise != nullptr) zz += noise[o];
+      if (enc_pose != nullptr) zz += enc_pose[o];
+      z[(static_cast<long long>(b) * HW + p) * CzPad + c] = from_f32<T>(zz);
+    }
+  }
+  if (z != nullptr && CzPad > Cz) {
+    const int padc = CzPad - Cz;
+    for (int i = threadIdx.x; i < padc * HW; i += 256) {
+      const int p = i / padc, c = Cz + (i - p * padc);
+      z[(static_cast<long long>(b) * HW + p) * CzPad + c] = from_f32<T>(0.0f);
+    }
+  }
+  acc = block_sum_256(acc, sm);
+  if (threadIdx.x == 0) kl[b] = 0.5f * acc;
+}
+
+template <typename T>
+__global__ void __launch_bounds__(256) sample_kl_bwd_kernel(
+    const T* __restrict__ dz, const float* __restrict__ dkl, const float* __restrict__ dmean_direct,
+    const float* __restrict__ dlogvar_direct, const float* __restrict__ mean, const float* __restrict__ logvar,
+    const float* __restrict__ eps, const uint8_t* __restrict__ keep, float keep_scale, T* __restrict__ dmoments,
+    float* __restrict__ denc_pose, int HW, int Cz, int CzPad, int ldm) {
+  const int b = blockIdx.x;
+  const int n = Cz * HW;
+  const float gk = dkl != nullptr ? dkl[b] : 0.0f;
+  for (int i = threadIdx.x; i < n; i += 256) {
+    const int c = i / HW, p = i - c * HW;
+    const long long o = static_cast<long long>(b) * n + i;
+    const float mu = mean[o], lv = logvar[o];
+    float g = 0.0f;
+    if (dz != nullptr) g = to_f32<T>(dz[(static_cast<long long>(b) * HW + p) * CzPad + c]);
+    if (denc_pose != nullptr) denc_pose[o] = g;
+    if (keep != nullptr) g = keep[o] ? g * keep_scale : 0.0f;
+    float dmu = g + gk * mu;
+    float dlv = gk * 0.5f * (expf(lv) - 1.0f);
+    if (dz != nullptr) dlv += g * eps[o] * 0.5f * expf(0.5f * lv);
+    if (dmean_direct != nullptr) dmu += dmean_direct[o];
+    if (dlogvar_direct != nullptr) dlv += dlogvar_direct[o];
+    if (!(lv > -30.0f && lv < 20.0f)) dlv = 0.0f;  // clamp(-30, 20) passes no gradient outside
+    const long long mrow = (static_cast<long long>(b) * HW + p) * ldm;
+    dmoments[mrow + c] = from_f32<T>(dmu);
+    dmoments[mrow + Cz + c] = from_f32<T>(dlv);
+  }
+  const int padc = ldm - 2 * Cz;
+  for (int i = threadIdx.x; i < padc * HW; i += 256) {
+    const int p = i / padc, c = 2 * Cz + (i - p * padc);
+    dmoments[(static_cast<long long>(b) * HW + p) * ldm + c] = from_f32<T>(0.0f);
+  }
+}
+
+// ---------------------------------------------------------------------------------------------
+// Masked L1: sums[b] = sum_{c,p} |x*m - xhat*m| ; sgn = sign(x*m - xhat*m) * m
+// grid (nsplit, B); partials -> fixed-order final sum
+// ---------------------------------------------------------------------------------------------
+static constexpr int L1_SPLIT = 32;
+
+__global__ void __launch_bounds__(256) l1_masked_fwd_kernel(const float* __restrict__ x, const float* __restrict__ xh,
+                                                            const float* __restrict__ m, float* __restrict__ part,
+                                                            int8_t* __restrict__ sgn, int C, int HW) {
+  __shared__ float sm[8];
+  const int b = blockIdx.y;
+  const int nv = HW >> 2;  // float4 per channel plane
+  const int total = C * nv;
+  float acc = 0.0f;
+  for (int i = blockIdx.x * 256 + threadIdx.x; i < total; i += gridDim.x * 256) {
+    const int c = i / nv, pv = i - c * nv;
+    const long long off = (static_cast<long long>(b) * C + c) * HW;
+    const float4 xv = __ldg(reinterpret_cast<const float4*>(x + off) + pv);
+    const float4 hv = __ldg(reinterpret_cast<const float4*>(xh + off) + pv);
+    const float4 mv = __ldg(reinterpret_cast<const float4*>(m + static_cast<long long>(b) * HW) + pv);
+    const float d0 = xv.x * mv.x - hv.x * mv.x, d1 = xv.y * mv.y - hv.y * mv.y;
+    const float d2 = xv.z * mv.z - hv.z * mv.z, d3 = xv.w * mv.w - hv.w * mv.w;
+    acc += fabsf(d0) + fabsf(d1) + fabsf(d2) + fabsf(d3);
+    if (sgn != nullptr) {
+      char4 s;
+      s.x = static_cast<signed char>(((d0 > 0.0f) - (d0 < 0.0f)) * mv.x);
+      s.y = static_cast<signed char>(((d1 > 0.0f) - (d1 < 0.0f)) * mv.y);
+      s.z = static_cast<signed char>(((d2 > 0.0f) - (d2 < 0.0f)) * mv.z);
+      s.w = static_cast<signed char>(((d3 > 0.0f) - (d3 < 0.0f)) * mv.w);
+      reinterpret_cast<char4*>(sgn + off)[pv] = s;
+    }
+  }
+  acc = block_sum_256(acc, sm);
+  if (threadIdx.x == 0) part[b * gridDim.x + blockIdx.x] = acc;
+}
+__global__ void l1_masked_final_kernel(const float* __restrict__ part, float* __restrict__ sums, int nsplit) {
+  const int b = blockIdx.x * blockDim.x + threadIdx.x;
+  if (b >= gridDim.x * blockDim.x) return;
+  float a = 0.0f;
+  for (int i = 0; i < nsplit; ++i) a += part[b * nsplit + i];
+  sums[b] = a;
+}
+// dxhat = -sgn * coef[b]
+__global__ void __launch_bounds__(256) l1_masked_bwd_kernel(const int8_t* __restrict__ sgn,
+                                                            const float* __restrict__ coef, float* __restrict__ dxh,
+                                                            int CHW4, long long total4) {
+  for (long long i = blockIdx.x * 256ll + threadIdx.x; i < total4; i += gridDim.x * 256ll) {
+    const int b = static_cast<int>(i / CHW4);
+    const float cf = -__ldg(coef + b);
+    const char4 s = reinterpret_cast<const char4*>(sgn)[i];
+    reinterpret_cast<float4*>(dxh)[i] = make_float4(s.x * cf, s.y * cf, s.z * cf, s.w * cf);
+  }
+}
+
+// ---------------------------------------------------------------------------------------------
+// small helpers
+// ---------------------------------------------------------------------------------------------
+// dst = 2*(x - min)/(max - min) - 1  (AE.py:434-436)
+__global__ void rescale_kernel(const float* __restrict__ src, float* __restrict__ dst, long long n,
+                               const float* __restrict__ mm) {
+  const float mn = mm[0], range = mm[1] - mm[0];
+  for (long long i = blockIdx.x * static_cast<long long>(blockDim.x) + threadIdx.x; i < n;
+       i += static_cast<long long>(gridDim.x) * blockDim.x)
+    dst[i] = 2.0f * (src[i] - mn) / range - 1.0f;
+}
+
+// act: 1 = tanh, 2 = silu   (y may alias x)
+__global__ void act_fwd_kernel(const float* __restrict__ x, float* __restrict__ y, long long n, int act) {
+  for (long long i = blockIdx.x * static_cast<long long>(blockDim.x) + threadIdx.x; i < n;
+       i += static_cast<long long>(gridDim.x) * blockDim.x) {
+    const float v = x[i];
+    y[i] = act == 1 ? tanhf(v) : v / (1.0f + expf(-v));
+  }
+}
+// dx = dy * act'(x)  (x = pre-activation)
+__global__ void act_bwd_kernel(const float* __restrict__ x, const float* __restrict__ dy, float* __restrict__ dx,
+                               long long n, int act) {
+  for (long long i = blockIdx.x * static_cast<long long>(blockDim.x) + threadIdx.x; i < n;
+       i += static_cast<long long>(gridDim.x) * blockDim.x) {
+    const float v = x[i];
+    float g;
+    if (act == 1) {
+      const float t = tanhf(v);
+      g = 1.0f - t * t;
+    } else {
+      const float s = 1.0f / (1.0f + expf(-v));
+      g = s * (1.0f + v * (1.0f - s));
+    }
+    dx[i] = dy[i] * g;
+  }
+}
+
+static int grid_1d(long long items, int threads, int per_sm = 8) {
+  long long blocks = (items + threads - 1) / threads;
+  const long long cap = static_cast<long long>(num_sms()) * per_sm;
+  if (blocks > cap) blocks = cap;
+  if (blocks < 1) blocks = 1;
+  return static_cast<int>(blocks);
+}
+
+}  // namespace odvae
+
+using namespace odvae;
+
+extern "C" {
+
+int odvae_softmax_rows(const float* S, void* P, int64_t rows, int n, float scale, int act_dtype, void* stream) {
+  if (n <= 0 || (n & 3) || rows <= 0) return ODVAE_ERR_SHAPE;
+  cudaStream_t st = static_cast<cudaStream_t>(stream);
+  const bool small = n <= 1024;
+  const int rpb = small ? 8 : 1;
+  const long long want = (rows + rpb - 1) / rpb;
+  const int grid = static_cast<int>(want < 16ll * num_sms() ? want : 16ll * num_sms());
+  if (act_dtype == ODVAE_BF16) {
+    if (small) softmax_rows_kernel<bf16, 32><<<grid, 256, 0, st>>>(S, reinterpret_cast<bf16*>(P), rows, n, scale);
+    else softmax_rows_kernel<bf16, 256><<<grid, 256, 0, st>>>(S, reinterpret_cast<bf16*>(P), rows, n, scale);
+  } else {
+    if (small) softmax_rows_kernel<float, 32><<<grid, 256, 0, st>>>(S, reinterpret_cast<float*>(P), rows, n, scale);
+    else softmax_rows_kernel<float, 256><<<grid, 256, 0, st>>>(S, reinterpret_cast<float*>(P), rows, n, scale);
+  }
+  return check_launch("softmax_rows_kernel");
+}
+
+int odvae_softmax_rows_bwd(const float* dP, const void* P, void* dS, int64_t rows, int n, float scale, int act_dtype,
+                           void* stream) {
+  if (n <= 0 || (n & 3) || rows <= 0) return ODVAE_ERR_SHAPE;
+  cudaStream_t st = static_cast<cudaStream_t>(stream);
+  const bool small = n <= 1024;
+  const int rpb = small ? 8 : 1;
+  const long long want = (rows + rpb - 1) / rpb;
+  const int grid = static_cast<int>(want < 16ll * num_sms() ? want : 16ll * num_sms());
+  if (act_dtype == ODVAE_BF16) {
+    const bf16* p = reinterpret_cast<const bf16*>(P);
+    bf16* d = reinterpret_cast<bf16*>(dS);
+    if (small) softmax_rows_bwd_kernel<bf16, 32><<<grid, 256, 0, st>>>(dP, p, d, rows, n, scale);
+    else softmax_rows_bwd_kernel<bf16, 256><<<grid, 256, 0, st>>>(dP, p, d, rows, n, scale);
+  } else {
+    const float* p = reinterpret_cast<const float*>(P);
+    float* d = reinterpret_cast<float*>(dS);
+    if (small) softmax_rows_bwd_kernel<float, 32><<<grid, 256, 0, st>>>(dP, p, d, rows, n, scale);
+    else softmax_rows_bwd_kernel<float, 256><<<grid, 256, 0, st>>>(dP, p, d, rows, n, scale);
+  }
+  return check_launch("softmax_rows_bwd_kernel");
+}
+
+int odvae_sample_kl_fwd(const void* moments, const float* eps, const uint8_t* keep, const float* noise,
+                        const float* enc_pose, float keep_scale, float* mean, float* logvar, void* z, float* kl, int B,
+                        int HW, int Cz, int CzPad, int ld_moments, int act_dtype, void* stream) {
+  if (B <= 0 || ld_moments < 2 * Cz || CzPad < Cz) return ODVAE_ERR_SHAPE;
+  if (z != nullptr && eps == nullptr) return ODVAE_ERR_SHAPE;
+  cudaStream_t st = static_cast<cudaStream_t>(stream);
+  if (act_dtype == ODVAE_BF16)
+    sample_kl_fwd_kernel<bf16><<<B, 256, 0, st>>>(reinterpret_cast<const bf16*>(moments), eps, keep, noise, enc_pose,
+                                                  keep_scale, mean, logvar, reinterpret_cast<bf16*>(z), kl, HW, Cz,
+                                                  CzPad, ld_moments);
+  else
+    sample_kl_fwd_kernel<float><<<B, 256, 0, st>>>(reinterpret_cast<const float*>(moments), eps, keep, noise, enc_pose,
+                                                   keep_scale, mean, logvar, reinterpret_cast<float*>(z), kl, HW, Cz,
+                                                   CzPad, ld_moments);
+  return check_launch("sample_kl_fwd_kernel");
+}
+
+int odvae_sample_kl_bwd(const void* dz, const float* dkl, const float* dmean_direct, const float* dlogvar_direct,
+                        const float* mean, const float* logvar, const float* eps, const uint8_t* keep, float keep_scale,
+                        void* dmoments, float* denc_pose, int B, int HW, int Cz, int CzPad, int ld_moments,
+                        int act_dtype, void* stream) {
+  if (B <= 0 || ld_moments < 2 * Cz || CzPad < Cz) return ODVAE_ERR_SHAPE;
+  if (dz != nullptr && eps == nullptr) return ODVAE_ERR_SHAPE;
+  cudaStream_t st = static_cast<cudaStream_t>(stream);
+  if (act_dtype == ODVAE_BF16)
+    sample_kl_bwd_kernel<bf16><<<B, 256, 0, st>>>(reinterpret_cast<const bf16*>(dz), dkl, dmean_direct, dlogvar_direct,
+                                                  mean, logvar, eps, keep, keep_scale,
+                                                  reinterpret_cast<bf16*>(dmoments), denc_pose, HW, Cz, CzPad,
+                                                  ld_moments);
+  else
+    sample_kl_bwd_kernel<float><<<B, 256, 0, st>>>(reinterpret_cast<const float*>(dz), dkl, dmean_direct,
+                                                   dlogvar_direct, mean, logvar, eps, keep, keep_scale,
+                                                   reinterpret_cast<float*>(dmoments), denc_pose, HW, Cz, CzPad,
+                                                   ld_moments);
+  return check_launch("sample_kl_bwd_kernel");
+}
+
+size_t odvae_l1_masked_workspace_bytes(int B, int C, int HW) {
+  (void)C;
+  (void)HW;
+  return static_cast<size_t>(B) * L1_SPLIT * sizeof(float) + 256;
+}
+
+int odvae_l1_masked_fwd(const float* x, const float* xhat, const float* mask2d, float* sums, int8_t* sgn, int B, int C,
+                        int HW, void* workspace, size_t ws_bytes, void* stream) {
+  if (B <= 0 || (HW & 3)) return ODVAE_ERR_SHAPE;
+  if (ws_bytes < static_cast<size_t>(B) * L1_SPLIT * sizeof(float)) return ODVAE_ERR_WORKSPACE;
+  cudaStream_t st = static_cast<cudaStream_t>(stream);
+  float* part = reinterpret_cast<float*>(workspace);
+  dim3 grid(L1_SPLIT, B);
+  l1_masked_fwd_kernel<<<grid, 256, 0, st>>>(x, xhat, mask2d, part, sgn, C, HW);
+  int s = check_launch("l1_masked_fwd_kernel");
+  if (s != ODVAE_OK) return s;
+  // one thread per sample; grid*block == B exactly
+  int threads = 1;
+  while (threads < 128 && B % (threads * 2) == 0) threads *= 2;
+  l1_masked_final_kernel<<<B / threads, threads, 0, st>>>(part, sums, L1_SPLIT);
+  return check_launch("l1_masked_final_kernel");
+}
+
+int odvae_l1_masked_bwd(const int8_t* sgn, const float* coef, float* dxhat, int B, int C, int HW, void* stream) {
+  if (B <= 0 || (HW & 3)) return ODVAE_ERR_SHAPE;
+  cudaStream_t st = static_cast<cudaStream_t>(stream);
+  const int chw4 = C * HW / 4;
+  const long long total4 = static_cast<long long>(B) * chw4;
+  l1_masked_bwd_kernel<<<grid_1d(total4, 256), 256, 0, st>>>(sgn, coef, dxhat, chw4, total4);
+  return check_launch("l1_masked_bwd_kernel");
+}
+
+int odvae_rescale(const float* src, float* dst, int64_t n, const float* minmax, void* stream) {
+  cudaStream_t st = static_cast<cudaStream_t>(stream);
+  rescale_kernel<<<grid_1d(n, 256), 256, 0, st>>>(src, dst, n, minmax);
+  return check_launch("rescale_kernel");
+}
+
+int odvae_act_fwd(const float* x, float* y, int64_t n, int act, void* stream) {
+  if (act != 1 && act != 2) return ODVAE_ERR_SHAPE;
+  cudaStream_t st = static_cast<cudaStream_t>(stream);
+  act_fwd_kernel<<<grid_1d(n, 256), 256, 0, st>>>(x, y, n, act);
+  return check_launch("act_fwd_kernel");
+}
+
+int odvae_act_bwd(const float* x, const float* dy, float* dx, int64_t n, int act, void* stream) {
+  if (act != 1 && act != 2) return ODVAE_ERR_SHAPE;
+  cudaStream_t st = static_cast<cudaStream_t>(stream);
+  act_bwd_kernel<<<grid_1d(n, 256), 256, 0, st>>>(x, dy, dx, n, act);
+  return check_launch("act_bwd_kernel");
+}
+
+size_t odvae_colsum_workspace_bytes(int cols) { return colsum_workspace_bytes(cols) + 256; }
+
+int odvae_colsum(const void* m, int64_t rows, int cols, int ld, int dtype, float* out, int accumulate, void* workspace,
+                 size_t ws_bytes, void* stream) {
+  if (ws_bytes < colsum_workspace_bytes(cols)) return ODVAE_ERR_WORKSPACE;
+  return launch_colsum(m, rows, cols, ld, dtype, out, accumulate, reinterpret_cast<float*>(workspace),
+                       static_cast<cudaStream_t>(stream));
+}
+
+}  // extern "C"

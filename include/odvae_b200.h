@@ -142,7 +142,8 @@ int odvae_gemm_simt(const void* A, const void* B, void* D, int M, int N, int K, 
 
 /* ---------------------------------------------------------------------------------------------
  * Latent sampling + KL (DiagonalGaussianDistribution DIST.py:24-46, dropout/noise AE.py:226-241)
- * moments: NHWC act_dtype [B,HW,2*Cz] (mean | logvar per pixel).
+ * moments: NHWC act_dtype [B,HW,ld_moments], channels [0,Cz) = mean, [Cz,2Cz) = logvar, rest padding.
+ * z / eps / keep / noise may be NULL (mode() / no dropout / no noise); dz / dkl may be NULL in bwd.
  * outputs (all fp32, NCHW [B,Cz,h,w] = the module-boundary layout): mean, logvar (clamped).
  * z: NHWC act_dtype [B,HW,CzPad] = (mean + std*eps)*keep*keep_scale + noise + enc_pose (zero padded).
  * kl[B] = 0.5*sum(mean^2 + var - 1 - logvar).  eps/noise fp32 NCHW, keep uint8 NCHW, enc_pose fp32 [B,Cz*HW]
@@ -150,13 +151,13 @@ int odvae_gemm_simt(const void* A, const void* B, void* D, int M, int N, int K, 
  * ------------------------------------------------------------------------------------------- */
 int odvae_sample_kl_fwd(const void* moments, const float* eps, const uint8_t* keep, const float* noise,
                         const float* enc_pose, float keep_scale, float* mean, float* logvar, void* z,
-                        float* kl, int B, int HW, int Cz, int CzPad, int act_dtype, void* stream);
+                        float* kl, int B, int HW, int Cz, int CzPad, int ld_moments, int act_dtype, void* stream);
 /* dmoments = d(z)/d(moments)^T dz + dkl[b] * dKL/dmoments (+ direct grads on mean/logvar outputs).
  * dz: NHWC act_dtype [B,HW,CzPad]; denc_pose fp32 [B,Cz*HW] (NCHW flattened) = dz. */
 int odvae_sample_kl_bwd(const void* dz, const float* dkl, const float* dmean_direct, const float* dlogvar_direct,
                         const float* mean, const float* logvar, const float* eps, const uint8_t* keep,
                         float keep_scale, void* dmoments, float* denc_pose, int B, int HW, int Cz, int CzPad,
-                        int act_dtype, void* stream);
+                        int ld_moments, int act_dtype, void* stream);
 
 /* ---------------------------------------------------------------------------------------------
  * Masked L1 reconstruction term (PoseLoss._get_rec_loss/_get_nll_loss LOSS.py:134-158, masks :250-257)
@@ -174,13 +175,30 @@ int odvae_l1_masked_bwd(const int8_t* sgn, const float* coef, float* dxhat, int 
  * fp32 buffers.
  * ------------------------------------------------------------------------------------------- */
 size_t odvae_sumsq_workspace_bytes(int64_t n);
-int odvae_sumsq(const float* g, int64_t n, float* out1, void* workspace, size_t ws_bytes, void* stream);
+/* out1[0] (+)= sum g^2, fixed-order two-stage reduction */
+int odvae_sumsq(const float* g, int64_t n, float* out1, int accumulate, void* workspace, size_t ws_bytes,
+                void* stream);
+/* p -= lr/bc1 * m / (sqrt(v)/sqrt(bc2) + eps) after m,v updates with g * min(1, max_norm/(sqrt(gnorm_sq)+1e-6));
+ * gnorm_sq may be NULL (no clipping). bias_corr{1,2} = 1 - beta^t computed by the caller. */
 int odvae_adam_step(float* p, const float* g, float* m, float* v, int64_t n, float lr, float beta1, float beta2,
                     float eps, float bias_corr1, float bias_corr2, const float* gnorm_sq, float max_norm,
                     void* stream);
 
 /* generic elementwise helpers on activations (residual adds that cannot be fused) */
 int odvae_add(const void* a, const void* b, void* out, int64_t n, int act_dtype, void* stream);
+
+/* dst = 2*(src - min)/(max - min) - 1 with minmax = {min, max} on the device (AE.py:434-436 `_rescale`) */
+int odvae_rescale(const float* src, float* dst, int64_t n, const float* minmax, void* stream);
+
+/* Pose MLP activations on fp32 [n] (pose_decoder.py:82-94 Tanh, pose_encoder.py:82-98 SiLU):
+ * act = 1 tanh, 2 silu.  bwd: dx = dy * act'(x) with x the pre-activation. */
+int odvae_act_fwd(const float* x, float* y, int64_t n, int act, void* stream);
+int odvae_act_bwd(const float* x, const float* dy, float* dx, int64_t n, int act, void* stream);
+
+/* out[c] (+)= sum_r m[r*ld + c]  (nn.Linear bias gradients); dtype = ODVAE_F32 / ODVAE_BF16 */
+size_t odvae_colsum_workspace_bytes(int cols);
+int odvae_colsum(const void* m, int64_t rows, int cols, int ld, int dtype, float* out, int accumulate,
+                 void* workspace, size_t ws_bytes, void* stream);
 
 #if defined(__GNUC__)
 #pragma GCC visibility pop

@@ -14,10 +14,14 @@ from odvae_b200 import kernels as K  # noqa: E402
 from odvae_b200.lib import CONV_1x1, CONV_3x3_S1, CONV_3x3_S2, IMPL_SIMT, IMPL_TC  # noqa: E402
 
 DEV = "cuda"
+# the torch reference must be true fp32 (cuDNN / cuBLAS default to TF32 on CUDA)
+torch.backends.cudnn.allow_tf32 = False
+torch.backends.cuda.matmul.allow_tf32 = False
 
 
 def rel_err(a, ref):
     a, ref = a.float(), ref.float()
+    a, ref = a.detach(), ref.detach()
     return float((a - ref).abs().max() / ref.abs().max().clamp_min(1e-20))
 
 
@@ -53,6 +57,8 @@ IMPLS2 = IMPLS3[:2]
 @pytest.mark.parametrize("case", CONV_CASES)
 def test_conv_fwd_dgrad_wgrad(impl, dtype, geom, case):
     B, H, W, Cin, Cout = case
+    if impl == IMPL_TC and not K.conv_tc_supported(B, H, W, Cin, Cout, geom):
+        pytest.skip("outside the tcgen05 engine's tiling domain (< 128 output pixels per image): SIMT engine serves it")
     torch.manual_seed(0)
     k = 1 if geom == CONV_1x1 else 3
     x = torch.randn(B, H, W, Cin, device=DEV).to(dtype)
@@ -77,7 +83,7 @@ def test_conv_fwd_dgrad_wgrad(impl, dtype, geom, case):
     add = torch.randn(B, H, W, Cin, device=DEV).to(dtype)
     dx = K.conv_dgrad(dy, wd, Cin, geom, impl, (H, W), dx_add=add)
     torch.cuda.synchronize()
-    assert rel_err(dx.float() - add.float(), xr.grad.permute(0, 2, 3, 1)) < 2 * tol(dtype)
+    assert rel_err(dx.float() - add.float(), xr.grad) < 2 * tol(dtype)
 
     dw, db = K.conv_wgrad(x, dy, Cin, Cout, geom, impl)
     torch.cuda.synchronize()

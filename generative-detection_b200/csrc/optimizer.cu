@@ -79,6 +79,93 @@ adam_kernel(float* __restrict__ p, const float* __restrict__ g, float* __restric
   }
 }
 
+
+// ---------------------------------------------------------------------------------------------
+// Multi-tensor variants: one launch over a device-resident chunk table (no flattening copies).
+// table row = {p, g, m, v (device addresses), count}; one CTA per row; rows are <= 64 Ki elements.
+// ---------------------------------------------------------------------------------------------
+struct MtRow {
+  unsigned long long p, g, m, v;
+  long long n;
+};
+
+__global__ void __launch_bounds__(256) mt_sumsq_stage1(const MtRow* __restrict__ rows, float* __restrict__ part) {
+  const MtRow r = rows[blockIdx.x];
+  const float* g = reinterpret_cast<const float*>(r.g);
+  float acc = 0.0f;
+  if ((r.g & 15ull) == 0) {
+    const long long nv = r.n >> 2;
+    const float4* g4 = reinterpret_cast<const float4*>(g);
+    for (long long i = threadIdx.x; i < nv; i += 256) {
+      const float4 v = __ldg(g4 + i);
+      acc += v.x * v.x + v.y * v.y + v.z * v.z + v.w * v.w;
+    }
+    for (long long i = (nv << 2) + threadIdx.x; i < r.n; i += 256) acc += g[i] * g[i];
+  } else {
+    for (long long i = threadIdx.x; i < r.n; i += 256) acc += g[i] * g[i];
+  }
+  __shared__ float sm[8];
+  acc = warp_sum(acc);
+  if ((threadIdx.x & 31) == 0) sm[threadIdx.x >> 5] = acc;
+  __syncthreads();
+  if (threadIdx.x < 32) {
+    float t = threadIdx.x < 8 ? sm[threadIdx.x] : 0.0f;
+    t = warp_sum(t);
+    if (threadIdx.x == 0) part[blockIdx.x] = t;
+  }
+}
+
+__global__ void __launch_bounds__(256)
+mt_adam_kernel(const MtRow* __restrict__ rows, float lr, float b1, float b2, float eps, float bc1, float bc2,
+               const float* __restrict__ gnorm_sq, float max_norm, float grad_scale) {
+  const MtRow r = rows[blockIdx.x];
+  float* p = reinterpret_cast<float*>(r.p);
+  const float* g = reinterpret_cast<const float*>(r.g);
+  float* m = reinterpret_cast<float*>(r.m);
+  float* v = reinterpret_cast<float*>(r.v);
+  float clip = grad_scale;
+  if (gnorm_sq != nullptr && max_norm > 0.0f) {
+    // the norm was taken over the unscaled gradients: ||s*g|| = s*||g||
+    const float c = max_norm / (sqrtf(gnorm_sq[0]) * grad_scale + 1e-6f);
+    clip = c < 1.0f ? c * grad_scale : grad_scale;
+  }
+  const float step = lr / bc1;
+  const float inv_sqrt_bc2 = rsqrtf(bc2);
+  long long done = 0;
+  if (((r.p | r.g | r.m | r.v) & 15ull) == 0) {
+    const long long nv = r.n >> 2;
+    for (long long i = threadIdx.x; i < nv; i += 256) {
+      float4 pv = reinterpret_cast<float4*>(p)[i];
+      const float4 gv = __ldg(reinterpret_cast<const float4*>(g) + i);
+      float4 mv = reinterpret_cast<float4*>(m)[i];
+      float4 vv = reinterpret_cast<float4*>(v)[i];
+      float* pp = reinterpret_cast<float*>(&pv);
+      const float* gg = reinterpret_cast<const float*>(&gv);
+      float* mm = reinterpret_cast<float*>(&mv);
+      float* vvp = reinterpret_cast<float*>(&vv);
+#pragma unroll
+      for (int j = 0; j < 4; ++j) {
+        const float gr = gg[j] * clip;
+        mm[j] = b1 * mm[j] + (1.0f - b1) * gr;
+        vvp[j] = b2 * vvp[j] + (1.0f - b2) * gr * gr;
+        pp[j] -= step * mm[j] / (sqrtf(vvp[j]) * inv_sqrt_bc2 + eps);
+      }
+      reinterpret_cast<float4*>(p)[i] = pv;
+      reinterpret_cast<float4*>(m)[i] = mv;
+      reinterpret_cast<float4*>(v)[i] = vv;
+    }
+    done = nv << 2;
+  }
+  for (long long i = done + threadIdx.x; i < r.n; i += 256) {
+    const float gr = g[i] * clip;
+    const float mi = b1 * m[i] + (1.0f - b1) * gr;
+    const float vi = b2 * v[i] + (1.0f - b2) * gr * gr;
+    m[i] = mi;
+    v[i] = vi;
+    p[i] -= step * mi / (sqrtf(vi) * inv_sqrt_bc2 + eps);
+  }
+}
+
 }  // namespace odvae
 
 using namespace odvae;
@@ -119,6 +206,27 @@ int odvae_adam_step(float* p, const float* g, float* m, float* v, int64_t n, flo
   adam_kernel<<<static_cast<int>(blocks), 256, 0, st>>>(p, g, m, v, n, lr, beta1, beta2, eps, bias_corr1, bias_corr2,
                                                        gnorm_sq, max_norm);
   return check_launch("adam_kernel");
+}
+
+int odvae_mt_sumsq(const void* table, int nrows, float* out1, void* workspace, size_t ws_bytes, void* stream) {
+  if (nrows <= 0) return ODVAE_ERR_SHAPE;
+  if (ws_bytes < static_cast<size_t>(nrows) * sizeof(float)) return ODVAE_ERR_WORKSPACE;
+  cudaStream_t st = static_cast<cudaStream_t>(stream);
+  float* part = reinterpret_cast<float*>(workspace);
+  mt_sumsq_stage1<<<nrows, 256, 0, st>>>(reinterpret_cast<const MtRow*>(table), part);
+  int s = check_launch("mt_sumsq_stage1");
+  if (s != ODVAE_OK) return s;
+  sumsq_stage2<<<1, 32, 0, st>>>(part, nrows, out1, 0);
+  return check_launch("sumsq_stage2");
+}
+
+int odvae_mt_adam_step(const void* table, int nrows, float lr, float beta1, float beta2, float eps, float bias_corr1,
+                       float bias_corr2, const float* gnorm_sq, float max_norm, float grad_scale, void* stream) {
+  if (nrows <= 0) return ODVAE_ERR_SHAPE;
+  cudaStream_t st = static_cast<cudaStream_t>(stream);
+  mt_adam_kernel<<<nrows, 256, 0, st>>>(reinterpret_cast<const MtRow*>(table), lr, beta1, beta2, eps, bias_corr1,
+                                        bias_corr2, gnorm_sq, max_norm, grad_scale);
+  return check_launch("mt_adam_kernel");
 }
 
 }  // extern "C"

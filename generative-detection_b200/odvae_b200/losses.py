@@ -1,0 +1,224 @@
+"""PoseLoss with the reference's constructor / forward signature and log keys.
+
+Reference: src/modules/losses/contperceptual.py:26-375 (PoseLoss) on top of
+LD/ldm/modules/losses/contperceptual.py:7-43 (LPIPSWithDiscriminator: `logvar` parameter, discriminator,
+adaptive weight). optimizer_idx 0 runs as two kernels each way: the fused masked-L1 reduction over the
+images (ops.L1Masked) and the one-CTA "loss heads" kernel for everything per-sample / scalar (LossHeads).
+
+Not implemented yet (arithmetic lives in the un-vendored taming-transformers): LPIPS and the
+PatchGAN discriminator. `perceptual_weight > 0` or `disc_factor > 0` raise at forward time; with
+`disc_factor == 0` the generator term is exactly 0 in the reference's total (LOSS.py:294-317), only the
+logged `g_loss` differs (reported as 0 here).
+"""
+import ctypes
+import math
+import pickle as pkl
+
+import torch
+import torch.nn as nn
+
+from . import ops
+from .distributions import DiagonalGaussianDistribution
+
+POSE_6D_DIM = 4
+LHW_DIM = 3
+FILL_FACTOR_DIM = 1
+BBOX_DIM = POSE_6D_DIM + LHW_DIM + FILL_FACTOR_DIM
+BACKGROUND_CLASS_IDX = 1  # LOSS.py:17 (sic)
+
+# out16 layout of odvae_loss_heads_fwd
+O_TOTAL, O_NLL, O_KL, O_REC, O_POSE, O_CLASS, O_BBOX, O_FILL, O_KLB, O_T1, O_T2, O_T3, O_V3, O_NFG = range(14)
+
+
+def adopt_weight(weight, global_step, threshold=0, value=0.0):
+    # LD/ldm/modules/losses/vqperceptual.py:20-23 (same semantics as taming's)
+    return value if global_step < threshold else weight
+
+
+class NLayerDiscriminator(nn.Module):
+    """Parameter container with taming's PatchGAN layout (state_dict keys `main.{0,2,3,5,6,8,9,11}.*`) so that
+    `configure_optimizers` and reference checkpoints keep working; its forward pass is SURVEY 8 f2 (next)."""
+
+    def __init__(self, input_nc=3, ndf=64, n_layers=3, use_actnorm=False):
+        super().__init__()
+        kw, padw = 4, 1
+        seq = [nn.Conv2d(input_nc, ndf, kw, 2, padw), nn.LeakyReLU(0.2, True)]
+        nf_mult = 1
+        for n in range(1, n_layers):
+            nf_prev, nf_mult = nf_mult, min(2 ** n, 8)
+            seq += [nn.Conv2d(ndf * nf_prev, ndf * nf_mult, kw, 2, padw, bias=False),
+                    nn.BatchNorm2d(ndf * nf_mult), nn.LeakyReLU(0.2, True)]
+        nf_prev, nf_mult = nf_mult, min(2 ** n_layers, 8)
+        seq += [nn.Conv2d(ndf * nf_prev, ndf * nf_mult, kw, 1, padw, bias=False),
+                nn.BatchNorm2d(ndf * nf_mult), nn.LeakyReLU(0.2, True)]
+        seq += [nn.Conv2d(ndf * nf_mult, 1, kw, 1, padw)]
+        self.main = nn.Sequential(*seq)
+        for m in self.modules():  # taming weights_init
+            if isinstance(m, nn.Conv2d):
+                nn.init.normal_(m.weight.data, 0.0, 0.02)
+            elif isinstance(m, nn.BatchNorm2d):
+                nn.init.normal_(m.weight.data, 1.0, 0.02)
+                nn.init.constant_(m.bias.data, 0)
+
+    def forward(self, x):
+        raise NotImplementedError("the PatchGAN discriminator forward is SURVEY 8 f2 (next); run with disc_factor=0")
+
+
+class LossHeads(torch.autograd.Function):
+    @staticmethod
+    def forward(ctx, dec_pose, bbox_mean, bbox_logvar, l1_sums, kl_obj, logvar, gts, cfg):
+        pose_gt, bbox_gt, fill_gt, class_gt, prior_row, prior = gts
+        B, ncls, npix, w7 = cfg
+        dev = dec_pose.device
+        dec_pose, bbox_mean, bbox_logvar = ops._c(dec_pose), ops._c(bbox_mean), ops._c(bbox_logvar)
+        out = torch.empty(16, dtype=torch.float32, device=dev)
+        warr = (ctypes.c_float * 7)(*w7)
+        ops.call("loss_heads_fwd", dec_pose, bbox_mean, bbox_logvar, l1_sums, kl_obj, logvar, pose_gt, bbox_gt,
+                 fill_gt, class_gt, prior_row, prior, B, ncls, BACKGROUND_CLASS_IDX, float(npix), warr, out)
+        ctx.cfg, ctx.gts = cfg, gts
+        ctx.has = (l1_sums is not None, kl_obj is not None)
+        ctx.save_for_backward(dec_pose, bbox_mean, bbox_logvar, l1_sums, kl_obj, logvar, out)
+        return out
+
+    @staticmethod
+    def backward(ctx, dout):
+        dec_pose, bbox_mean, bbox_logvar, l1_sums, kl_obj, logvar, out = ctx.saved_tensors
+        pose_gt, bbox_gt, fill_gt, class_gt, prior_row, prior = ctx.gts
+        B, ncls, npix, w7 = ctx.cfg
+        dev = dec_pose.device
+        dout = ops._c(dout.float())
+        d_dec = torch.empty_like(dec_pose)
+        d_mean = torch.empty_like(bbox_mean)
+        d_lv = torch.empty_like(bbox_logvar)
+        d_l1 = torch.empty(B, dtype=torch.float32, device=dev) if ctx.has[0] else None
+        d_kl = torch.empty(B, dtype=torch.float32, device=dev) if ctx.has[1] else None
+        d_logvar = torch.empty((), dtype=torch.float32, device=dev)
+        warr = (ctypes.c_float * 7)(*w7)
+        ops.call("loss_heads_bwd", dec_pose, bbox_mean, bbox_logvar, l1_sums, kl_obj, logvar, pose_gt, bbox_gt, fill_gt,
+                 class_gt, prior_row, prior, B, ncls, BACKGROUND_CLASS_IDX, float(npix), warr, out, dout, d_dec,
+                 d_mean, d_lv, d_l1, d_kl, d_logvar)
+        return d_dec, d_mean, d_lv, d_l1, d_kl, d_logvar, None, None
+
+
+class PoseLoss(nn.Module):
+    def __init__(self, train_on_yaw=True, kl_weight_obj=1.0, kl_weight_bbox=1e-6, pose_weight=1.0, mask_weight=0.0,
+                 class_weight=1.0, bbox_weight=1.0, fill_factor_weight=1.0, pose_loss_fn=None, mask_loss_fn=None,
+                 encoder_pretrain_steps=0, pose_conditioned_generation_steps=7000, use_mask_loss=True,
+                 use_class_loss=False, use_bbox_loss=False, num_classes=1,
+                 dataset_stats_path="dataset_stats/combined/all.pkl",
+                 # LPIPSWithDiscriminator (LD contperceptual.py:8-30)
+                 disc_start=0, logvar_init=0.0, kl_weight=1.0, pixelloss_weight=1.0, disc_num_layers=3,
+                 disc_in_channels=3, disc_factor=1.0, disc_weight=1.0, perceptual_weight=1.0, use_actnorm=False,
+                 disc_conditional=False, disc_loss="hinge"):
+        super().__init__()
+        assert disc_loss in ["hinge", "vanilla"]
+        assert pose_loss_fn is not None, "Please provide a pose loss function."
+        assert mask_loss_fn is not None, "Please provide a mask loss function."
+        assert pose_loss_fn in ["l1", "l2", "mse"], "Please provide a valid pose loss function in ['l1', 'l2', 'mse']."
+        if pose_loss_fn != "l1" or not train_on_yaw:
+            raise NotImplementedError("the fused loss implements the north-star config: pose_loss_fn='l1', train_on_yaw")
+        self.kl_weight, self.pixel_weight = kl_weight, pixelloss_weight
+        self.perceptual_weight = perceptual_weight
+        self.logvar = nn.Parameter(torch.ones(size=()) * logvar_init)
+        self.discriminator = NLayerDiscriminator(input_nc=disc_in_channels, n_layers=disc_num_layers,
+                                                 use_actnorm=use_actnorm)
+        self.discriminator_iter_start = disc_start
+        self.disc_factor, self.discriminator_weight, self.disc_conditional = disc_factor, disc_weight, disc_conditional
+        self.pose_conditioned_generation_steps = pose_conditioned_generation_steps
+        self.encoder_pretrain_steps = encoder_pretrain_steps
+        self.pose_weight, self.mask_weight, self.fill_factor_weight = pose_weight, mask_weight, fill_factor_weight
+        self.class_weight, self.bbox_weight = class_weight, bbox_weight
+        self.use_mask_loss, self.num_classes = use_mask_loss, num_classes
+        self.kl_weight_obj, self.kl_weight_bbox = kl_weight_obj, kl_weight_bbox
+        self.train_on_yaw = train_on_yaw
+        with open(dataset_stats_path, "rb") as handle:
+            dataset_stats = pkl.load(handle)
+        self.bbox_distribution_dict = self._create_distribution_from_dataset_stats(dataset_stats)
+        self._labels = list(self.bbox_distribution_dict.keys())
+        table = torch.stack([torch.cat((d.mean, d.logvar), dim=1) for d in self.bbox_distribution_dict.values()])
+        self._prior_table_cpu = table.float().contiguous()  # [L,8,2] (mean, clamped logvar)
+        self._prior_table = None
+
+    def _create_distribution_from_dataset_stats(self, dataset_stats):  # LOSS.py:82-109
+        dist_dict = {}
+        for label, stats in dataset_stats.items():
+            means, logvars = torch.zeros(BBOX_DIM), torch.zeros(BBOX_DIM)
+            rot = "yaw" if self.train_on_yaw else "v3"
+            for idx, key in enumerate(["t1", "t2", "t3", rot, "l", "h", "w", "fill_factor"]):
+                if key == "yaw":
+                    mean, logvar = 0.0, 2 * torch.log(torch.tensor(math.pi))
+                elif key in ("t1", "t2"):
+                    mean, logvar = 0.0, 2 * torch.log(torch.tensor(1.0))
+                elif key == "fill_factor":
+                    mean, logvar = 0.5, 2 * torch.log(torch.tensor(math.sqrt(2)))
+                else:
+                    mean, logvar = stats[key]
+                means[idx], logvars[idx] = mean, logvar
+            dist_dict[label] = DiagonalGaussianDistribution(torch.cat((means.unsqueeze(1), logvars.unsqueeze(1)), dim=1))
+        return dist_dict
+
+    def _prior_rows(self, labels, device):
+        idx = {l: i for i, l in enumerate(self._labels)}
+        rows = []
+        for l in labels:
+            if l == "background":
+                rows.append(-1)
+            else:
+                rows.append(idx[l])  # KeyError for an unknown label, like the reference's dict lookup
+        return torch.tensor(rows, dtype=torch.int32).to(device, non_blocking=True)
+
+    def forward(self, rgb_gt, mask_gt, pose_gt, dec_obj, dec_pose, class_gt, class_gt_label, bbox_gt, fill_factor_gt,
+                posterior_obj, bbox_posterior, optimizer_idx, global_step, mask_2d_bbox, last_layer=None, cond=None,
+                split="train", weights=None):
+        if mask_gt is not None or weights is not None or cond is not None:
+            raise NotImplementedError("image masks / per-pixel weights / conditioning are unused by the north-star config")
+        if self.perceptual_weight > 0:
+            raise NotImplementedError("LPIPS (taming, needs vgg.pth) is SURVEY 8 f2; set perceptual_weight=0")
+        if self.disc_factor > 0:
+            raise NotImplementedError("the GAN terms are SURVEY 8 f2; set disc_factor=0")
+        dev = rgb_gt.device
+        self.use_mask_loss = False  # LOSS.py:230-248 (mask_gt is None)
+        use_pixel = not (global_step < (self.encoder_pretrain_steps + self.pose_conditioned_generation_steps))
+        if optimizer_idx == 1:
+            zero = torch.zeros((), device=dev)
+            return zero, {"{}/disc_loss".format(split): zero, "{}/logits_real".format(split): zero,
+                          "{}/logits_fake".format(split): zero}
+
+        B = rgb_gt.shape[0]
+        ncls = dec_pose.shape[1] - BBOX_DIM
+        npix = rgb_gt.shape[1] * rgb_gt.shape[2] * rgb_gt.shape[3]
+        f32 = dict(device=dev, dtype=torch.float32)
+        mask2d = ops._c(mask_2d_bbox.to(**f32, non_blocking=True))
+        gts = (ops._c(pose_gt.to(**f32)), ops._c(bbox_gt.to(**f32)), ops._c(fill_factor_gt.to(**f32).reshape(-1)),
+               ops._c(class_gt.to(device=dev, dtype=torch.int64)), self._prior_rows(class_gt_label, dev),
+               self._prior(dev))
+        l1_sums = None
+        if use_pixel:
+            l1_sums = ops.L1Masked.apply(ops._c(rgb_gt.float()), dec_obj[:, :3].contiguous(), mask2d)
+        train_rec = global_step > self.encoder_pretrain_steps and self.encoder_pretrain_steps != -1
+        w7 = (1.0 if train_rec else 0.0, self.kl_weight_obj if train_rec else 0.0, self.pose_weight,
+              self.class_weight, self.bbox_weight, self.fill_factor_weight, self.kl_weight_bbox)
+        out = LossHeads.apply(dec_pose, bbox_posterior.mean, bbox_posterior.logvar, l1_sums, posterior_obj.kl(),
+                              self.logvar, gts, (B, ncls, npix, tuple(float(v) for v in w7)))
+        loss = out[O_TOTAL]
+        d = out.detach()
+        disc_factor = adopt_weight(self.disc_factor, global_step, threshold=self.discriminator_iter_start)
+        zero = torch.zeros((), device=dev)
+        k = lambda name: "{}/{}".format(split, name)
+        log = {k("total_loss"): d[O_TOTAL], k("logvar"): self.logvar.detach(), k("kl_loss_obj"): d[O_KL],
+               k("nll_loss"): d[O_NLL], k("weighted_nll_loss"): d[O_NLL], k("rec_loss"): d[O_REC],
+               k("d_weight"): zero, k("disc_factor"): torch.tensor(disc_factor), k("g_loss"): zero,
+               k("pose_loss"): d[O_POSE], k("weighted_pose_loss"): self.pose_weight * d[O_POSE],
+               k("mask_loss"): zero, k("weighted_mask_loss"): zero, k("class_loss"): d[O_CLASS],
+               k("weighted_class_loss"): self.class_weight * d[O_CLASS], k("bbox_loss"): d[O_BBOX],
+               k("weighted_bbox_loss"): self.bbox_weight * d[O_BBOX], k("t1_loss"): d[O_T1], k("t2_loss"): d[O_T2],
+               k("t3_loss"): d[O_T3], k("v3_loss"): d[O_V3], k("kl_loss_bbox"): d[O_KLB],
+               k("weighted_kl_loss_bbox"): self.kl_weight_bbox * d[O_KLB],
+               k("weighted_kl_loss_obj"): self.kl_weight_obj * d[O_KL], k("fill_factor_loss"): d[O_FILL],
+               k("weighted_fill_factor_loss"): self.fill_factor_weight * d[O_FILL]}
+        return loss, log
+
+    def _prior(self, dev):
+        if self._prior_table is None or self._prior_table.device != dev:
+            self._prior_table = self._prior_table_cpu.to(dev)
+        return self._prior_table

@@ -1,0 +1,616 @@
+"""Autograd layer over the C ABI (include/odvae_b200.h).
+
+Every Function below enqueues only kernels of libodvae_b200.so; torch supplies device memory
+(`torch.empty`), streams and the autograd tape. Activations travel as NHWC tensors
+[B,H,W,Cp] (Cp = channels padded to a multiple of 64) in the module's compute dtype:
+bfloat16 (tcgen05 engine, the timed mode) or float32 (SIMT engine, the <=1e-4 validation mode).
+
+Backward passes are hand-written per block (ResnetBlock, AttnBlock, ...) rather than per
+primitive so that gradient accumulation is fused into kernel epilogues (`dx_add`) and the tape
+stays short (~60 nodes for the whole autoencoder).
+
+Reference call sites are cited per Function; LD/ = submodules/latent-diffusion/.
+"""
+import torch
+
+from . import lib
+from .lib import BF16, CONV_1x1, CONV_3x3_S1, CONV_3x3_S2, F32, IMPL_SIMT, IMPL_TC, call
+
+GROUPS = 32      # Normalize(): GroupNorm(num_groups=32, eps=1e-6)  LD model.py:38-39
+GN_EPS = 1e-6
+
+# bumped whenever parameters change behind autograd's back (FusedAdam kernels, load_state_dict)
+_WEIGHT_EPOCH = [0]
+
+
+def bump_weight_epoch():
+    _WEIGHT_EPOCH[0] += 1
+
+
+def act_code(dtype):
+    if dtype == torch.bfloat16:
+        return BF16
+    if dtype == torch.float32:
+        return F32
+    raise TypeError("activations must be float32 or bfloat16, got %s" % dtype)
+
+
+def cpad(c):
+    """Channel padding of activation buffers (multiples of 64 feed TMA/tcgen05 tiles directly)."""
+    return (c + 63) // 64 * 64
+
+
+_WS = {}
+
+
+def workspace(nbytes, device, tag):
+    """Grow-only scratch per (device, stream, tag); never part of a state_dict."""
+    key = (device.index, torch.cuda.current_stream(device).cuda_stream, tag)
+    buf = _WS.get(key)
+    if buf is None or buf.numel() < nbytes:
+        buf = torch.empty(max(int(nbytes), 1 << 16), dtype=torch.uint8, device=device)
+        _WS[key] = buf
+    return buf
+
+
+_TC_OK = {}
+
+
+def conv_impl(dtype, B, H, W, CinP, CoutP, geom):
+    if dtype != torch.bfloat16:
+        return IMPL_SIMT
+    key = (B, H, W, CinP, CoutP, geom)
+    ok = _TC_OK.get(key)
+    if ok is None:
+        ok = bool(call("conv2d_tc_supported", B, H, W, CinP, CoutP, geom))
+        _TC_OK[key] = ok
+    return IMPL_TC if ok else IMPL_SIMT
+
+
+def out_hw(geom, H, W):
+    return (H // 2, W // 2) if geom == CONV_3x3_S2 else (H, W)
+
+
+def geom_k(geom):
+    return 1 if geom == CONV_1x1 else 3
+
+
+# ------------------------------------------------------------------------------------------------
+# parameter-side caches: packed weights / padded biases, refreshed when the parameter changes
+# ------------------------------------------------------------------------------------------------
+class ParamCache:
+    """Packed copies of one conv's parameters. Keyed by (param version, global weight epoch)."""
+
+    def __init__(self):
+        self.store = {}
+
+    def get(self, key, params, build):
+        stamp = tuple(p._version for p in params) + tuple(p.data_ptr() for p in params) + (_WEIGHT_EPOCH[0],)
+        hit = self.store.get(key)
+        if hit is not None and hit[0] == stamp:
+            return hit[1]
+        val = build(hit[1] if hit is not None else None)
+        self.store[key] = (stamp, val)
+        return val
+
+
+def pack_weight(w, geom, CoutP, CinP, which, dtype, out=None):
+    k = geom_k(geom)
+    if out is None:
+        out = torch.empty(CoutP * CinP * k * k, dtype=dtype, device=w.device)
+    call("pack_conv_weight", w, out, w.shape[0], w.shape[1], geom, CoutP, CinP, which, act_code(dtype))
+    return out
+
+
+def pad_vector(v, n, out=None):
+    """fp32 [C] -> zero-padded fp32 [n] (bias rows of padded output channels)."""
+    if v.numel() == n:
+        return v
+    if out is None:
+        out = torch.empty(n, dtype=torch.float32, device=v.device)
+    call("nchw_to_nhwc", v, out, 1, v.numel(), 1, 1, n, F32, 1.0, 0.0)
+    return out
+
+
+class ConvSpec:
+    """Geometry + caches of one Conv2d (torch.nn.Conv2d call sites)."""
+
+    def __init__(self, cin, cout, geom, cout_pad=None):
+        self.cin, self.cout, self.geom = cin, cout, geom
+        self.cinp = cpad(cin)
+        self.coutp = cout_pad if cout_pad is not None else cpad(cout)
+        self.cache = ParamCache()
+
+    def w_fwd(self, w, dtype, coutp=None):
+        coutp = coutp or self.coutp
+        return self.cache.get(("f", dtype, coutp), (w,),
+                              lambda old: pack_weight(w.detach(), self.geom, coutp, self.cinp, 0, dtype, old))
+
+    def w_dgrad(self, w, dtype, coutp=None):
+        coutp = coutp or self.coutp
+        return self.cache.get(("d", dtype, coutp), (w,),
+                              lambda old: pack_weight(w.detach(), self.geom, coutp, self.cinp, 1, dtype, old))
+
+    def bias(self, b, n=None):
+        n = n or self.coutp
+        if b is None:
+            return None
+        if b.numel() == n:
+            return b.detach()
+        return self.cache.get(("b", n), (b,), lambda old: pad_vector(b.detach(), n, old))
+
+
+def grad_dst(p):
+    """Destination view for a parameter gradient when the flat gradient arena is enabled."""
+    return getattr(p, "_odvae_grad_dst", None)
+
+
+def _new_grad(p):
+    dst = grad_dst(p)
+    if dst is not None:
+        return dst, True
+    return torch.empty(p.shape, dtype=torch.float32, device=p.device), False
+
+
+def _ret(g, direct):
+    return None if direct else g
+
+
+# ------------------------------------------------------------------------------------------------
+# raw (non-autograd) kernel wrappers
+# ------------------------------------------------------------------------------------------------
+def conv_fwd_raw(x, spec, w, b, residual=None, out_nchw=False):
+    B, H, W, CinP = x.shape
+    assert CinP == spec.cinp, (CinP, spec.cinp)
+    Ho, Wo = out_hw(spec.geom, H, W)
+    if out_nchw:
+        coutp = 16 if spec.cout <= 16 else spec.coutp
+        impl = conv_impl(x.dtype, B, H, W, CinP, 64, spec.geom) if coutp == 16 else \
+            conv_impl(x.dtype, B, H, W, CinP, coutp, spec.geom)
+        y = torch.empty(B, spec.cout, Ho, Wo, dtype=torch.float32, device=x.device)
+        call("conv2d_fwd", x, spec.w_fwd(w, x.dtype, coutp), None if b is None else b.detach(), None, y, B, H, W,
+             CinP, coutp, spec.cout, spec.geom, act_code(x.dtype), impl, 1)
+        return y
+    impl = conv_impl(x.dtype, B, H, W, CinP, spec.coutp, spec.geom)
+    y = torch.empty(B, Ho, Wo, spec.coutp, dtype=x.dtype, device=x.device)
+    call("conv2d_fwd", x, spec.w_fwd(w, x.dtype), spec.bias(b), residual, y, B, H, W, CinP, spec.coutp, spec.cout,
+         spec.geom, act_code(x.dtype), impl, 0)
+    return y
+
+
+def conv_dgrad_raw(dy, spec, w, in_hw, dx_add=None):
+    B, Ho, Wo, CoutP = dy.shape
+    H, W = in_hw
+    impl = conv_impl(dy.dtype, B, H, W, spec.cinp, CoutP, spec.geom)
+    dx = torch.empty(B, H, W, spec.cinp, dtype=dy.dtype, device=dy.device)
+    call("conv2d_dgrad", dy, spec.w_dgrad(w, dy.dtype, CoutP), dx_add, dx, B, H, W, spec.cinp, CoutP, spec.geom,
+         act_code(dy.dtype), impl)
+    return dx
+
+
+def conv_wgrad_raw(x, dy, spec, w, b):
+    """-> (dw, db) as autograd return values (None where written straight into the gradient arena)."""
+    B, H, W, CinP = x.shape
+    CoutP = dy.shape[-1]
+    impl = conv_impl(x.dtype, B, H, W, CinP, CoutP, spec.geom)
+    dw, dw_direct = _new_grad(w)
+    db, db_direct = (None, True) if b is None else _new_grad(b)
+    nbytes = call("conv2d_wgrad_workspace_bytes", B, H, W, CinP, CoutP, spec.geom, impl)
+    ws = workspace(nbytes, x.device, "wgrad")
+    call("conv2d_wgrad", x, dy, dw, db, B, H, W, CinP, CoutP, spec.cin, spec.cout, spec.geom, act_code(x.dtype),
+         impl, 0, ws, ws.numel())
+    return _ret(dw, dw_direct), _ret(db, db_direct)
+
+
+def gn_stats_raw(x, C):
+    B, H, W, Cp = x.shape
+    assert Cp == C, "GroupNorm runs on unpadded channel counts (C % 64 == 0)"
+    stats = torch.empty(B, GROUPS, 2, dtype=torch.float32, device=x.device)
+    nbytes = call("groupnorm_workspace_bytes", B, H * W, C, GROUPS)
+    ws = workspace(nbytes, x.device, "gn")
+    call("groupnorm_stats", x, stats, B, H * W, C, GROUPS, GN_EPS, act_code(x.dtype), ws, ws.numel())
+    return stats
+
+
+def gn_apply_raw(x, stats, gamma, beta, silu):
+    B, H, W, C = x.shape
+    y = torch.empty_like(x)
+    call("groupnorm_apply", x, stats, gamma.detach(), beta.detach(), y, B, H * W, C, GROUPS, 1 if silu else 0,
+         act_code(x.dtype))
+    return y
+
+
+def gn_bwd_raw(x, stats, gamma, beta, dy, silu, dx_add=None):
+    B, H, W, C = x.shape
+    dx = torch.empty_like(x)
+    dgamma, g_direct = _new_grad(gamma)
+    dbeta, b_direct = _new_grad(beta)
+    nbytes = call("groupnorm_workspace_bytes", B, H * W, C, GROUPS)
+    ws = workspace(nbytes, x.device, "gn")
+    call("groupnorm_bwd", x, stats, gamma.detach(), beta.detach(), dy, dx_add, dx, dgamma, dbeta, B, H * W, C,
+         GROUPS, 1 if silu else 0, act_code(x.dtype), 0, ws, ws.numel())
+    return dx, _ret(dgamma, g_direct), _ret(dbeta, b_direct)
+
+
+def gemm_raw(A, Bm, D, M, N, K, batch, lda, ldb, ldd, sA, sB, sD, a_mn, b_mn, alpha=1.0, bias=None, residual=None):
+    """D[b] = alpha * op(A[b]) op(B[b])^T (+bias)(+residual); engine chosen by the operand dtype."""
+    if A.dtype == torch.bfloat16:
+        call("gemm_bf16", A, Bm, D, M, N, K, batch, lda, ldb, ldd, sA, sB, sD, int(a_mn), int(b_mn),
+             act_code(D.dtype), float(alpha), bias, residual)
+    else:
+        call("gemm_simt", A, Bm, D, M, N, K, batch, lda, ldb, ldd, sA, sB, sD, int(a_mn), int(b_mn), F32, F32,
+             float(alpha), bias, residual)
+    return D
+
+
+def nchw_to_nhwc_raw(x, Cpad, dtype, scale=1.0, shift=0.0):
+    B, C, H, W = x.shape
+    out = torch.empty(B, H, W, Cpad, dtype=dtype, device=x.device)
+    call("nchw_to_nhwc", x, out, B, C, H, W, Cpad, act_code(dtype), float(scale), float(shift))
+    return out
+
+
+def nhwc_to_nchw_raw(x, C):
+    B, H, W, Cpad = x.shape
+    out = torch.empty(B, C, H, W, dtype=torch.float32, device=x.device)
+    call("nhwc_to_nchw", x, out, B, C, H, W, Cpad, act_code(x.dtype))
+    return out
+
+
+def _c(t):
+    return t if t.is_contiguous() else t.contiguous()
+
+
+# ------------------------------------------------------------------------------------------------
+# layout conversion at the module boundary (AE.py:223; LD/ldm/models/autoencoder.py:344-349)
+# ------------------------------------------------------------------------------------------------
+class ToNHWC(torch.autograd.Function):
+    @staticmethod
+    def forward(ctx, x, Cpad, dtype):
+        ctx.C = x.shape[1]
+        return nchw_to_nhwc_raw(_c(x.float()), Cpad, dtype)
+
+    @staticmethod
+    def backward(ctx, dy):
+        return nhwc_to_nchw_raw(_c(dy), ctx.C), None, None
+
+
+class ToNCHW(torch.autograd.Function):
+    @staticmethod
+    def forward(ctx, x, C):
+        ctx.Cpad, ctx.dtype = x.shape[-1], x.dtype
+        return nhwc_to_nchw_raw(x, C)
+
+    @staticmethod
+    def backward(ctx, dy):
+        return nchw_to_nhwc_raw(_c(dy.float()), ctx.Cpad, ctx.dtype), None
+
+
+# ------------------------------------------------------------------------------------------------
+# Conv2d  (LD model.py:92-106,383-387,428-432,487-491,529-533; Downsample :66-76; quant convs AE.py:88-90)
+# ------------------------------------------------------------------------------------------------
+class Conv(torch.autograd.Function):
+    @staticmethod
+    def forward(ctx, x, w, b, spec, out_nchw, need_dx):
+        ctx.spec, ctx.out_nchw, ctx.need_dx = spec, out_nchw, need_dx
+        ctx.save_for_backward(x, w, b)
+        return conv_fwd_raw(x, spec, w, b, out_nchw=out_nchw)
+
+    @staticmethod
+    def backward(ctx, dy):
+        x, w, b = ctx.saved_tensors
+        spec = ctx.spec
+        if ctx.out_nchw:  # dec_obj gradient arrives NCHW fp32 (masked-L1 backward): bring it to NHWC
+            dy = nchw_to_nhwc_raw(_c(dy.float()), cpad(spec.cout), x.dtype)
+        else:
+            dy = _c(dy)
+        dx = None
+        if ctx.need_dx and ctx.needs_input_grad[0]:
+            dx = conv_dgrad_raw(dy, spec, w, x.shape[1:3])
+        dw, db = conv_wgrad_raw(x, dy, spec, w, b)
+        return dx, dw, db, None, None, None
+
+
+# ------------------------------------------------------------------------------------------------
+# GroupNorm (+SiLU) as a standalone node (norm_out before conv_out: LD model.py:453-455,563-565)
+# ------------------------------------------------------------------------------------------------
+class GroupNormAct(torch.autograd.Function):
+    @staticmethod
+    def forward(ctx, x, gamma, beta, silu):
+        stats = gn_stats_raw(x, x.shape[-1])
+        ctx.silu = silu
+        ctx.save_for_backward(x, stats, gamma, beta)
+        return gn_apply_raw(x, stats, gamma, beta, silu)
+
+    @staticmethod
+    def backward(ctx, dy):
+        x, stats, gamma, beta = ctx.saved_tensors
+        dx, dg, db = gn_bwd_raw(x, stats, gamma, beta, _c(dy), ctx.silu)
+        return dx, dg, db, None
+
+
+# ------------------------------------------------------------------------------------------------
+# ResnetBlock  (LD model.py:121-141, temb=None, dropout 0):
+#   out = shortcut(x) + conv2(silu(GN2(conv1(silu(GN1(x))))))
+# ------------------------------------------------------------------------------------------------
+class ResBlock(torch.autograd.Function):
+    @staticmethod
+    def forward(ctx, x, g1, b1, w1, c1b, g2, b2, w2, c2b, wn, nb, blk):
+        s1 = gn_stats_raw(x, blk.cin)
+        a1 = gn_apply_raw(x, s1, g1, b1, True)
+        h1 = conv_fwd_raw(a1, blk.spec1, w1, c1b)
+        s2 = gn_stats_raw(h1, blk.cout)
+        a2 = gn_apply_raw(h1, s2, g2, b2, True)
+        sc = x if wn is None else conv_fwd_raw(x, blk.spec_nin, wn, nb)
+        out = conv_fwd_raw(a2, blk.spec2, w2, c2b, residual=sc)
+        ctx.blk = blk
+        ctx.has_nin = wn is not None
+        ctx.save_for_backward(x, s1, a1, h1, s2, a2, g1, b1, w1, c1b, g2, b2, w2, c2b, wn, nb)
+        return out
+
+    @staticmethod
+    def backward(ctx, dout):
+        x, s1, a1, h1, s2, a2, g1, b1, w1, c1b, g2, b2, w2, c2b, wn, nb = ctx.saved_tensors
+        blk = ctx.blk
+        dout = _c(dout)
+        hw = x.shape[1:3]
+        dwn = dnb = None
+        if ctx.has_nin:
+            dsc = conv_dgrad_raw(dout, blk.spec_nin, wn, hw)
+            dwn, dnb = conv_wgrad_raw(x, dout, blk.spec_nin, wn, nb)
+        else:
+            dsc = dout
+        da2 = conv_dgrad_raw(dout, blk.spec2, w2, hw)
+        dw2, dc2b = conv_wgrad_raw(a2, dout, blk.spec2, w2, c2b)
+        dh1, dg2, db2 = gn_bwd_raw(h1, s2, g2, b2, da2, True)
+        del da2
+        da1 = conv_dgrad_raw(dh1, blk.spec1, w1, hw)
+        dw1, dc1b = conv_wgrad_raw(a1, dh1, blk.spec1, w1, c1b)
+        del dh1
+        dx, dg1, db1 = gn_bwd_raw(x, s1, g1, b1, da1, True, dx_add=dsc)
+        return dx, dg1, db1, dw1, dc1b, dg2, db2, dw2, dc2b, dwn, dnb, None
+
+
+# ------------------------------------------------------------------------------------------------
+# AttnBlock  (LD model.py:178-202): out = x + proj(softmax(q^T k / sqrt(C)) v), single head
+# q, k, v projections run as ONE 1x1 conv with 3C output channels; the residual add is fused into
+# the proj_out epilogue. Unfused core: S (fp32) and P (act dtype) are materialised per block.
+# ------------------------------------------------------------------------------------------------
+class AttnBlock(torch.autograd.Function):
+    @staticmethod
+    def forward(ctx, x, gamma, beta, wq, bq, wk, bk, wv, bv, wp, bp, blk):
+        B, H, W, C = x.shape
+        N = H * W
+        dt = x.dtype
+        stats = gn_stats_raw(x, C)
+        hn = gn_apply_raw(x, stats, gamma, beta, False)
+        wqkv, bqkv = blk.fused_qkv(wq, bq, wk, bk, wv, bv, dt)
+        qkv = torch.empty(B, H, W, 3 * C, dtype=dt, device=x.device)
+        impl = conv_impl(dt, B, H, W, C, 3 * C, CONV_1x1)
+        call("conv2d_fwd", hn, wqkv, bqkv, None, qkv, B, H, W, C, 3 * C, 3 * C, CONV_1x1, act_code(dt), impl, 0)
+        q, k, v = qkv[..., :C], qkv[..., C:2 * C], qkv[..., 2 * C:]
+        S = torch.empty(B, N, N, dtype=torch.float32, device=x.device)
+        gemm_raw(q, k, S, N, N, C, B, 3 * C, 3 * C, N, N * 3 * C, N * 3 * C, N * N, False, False)
+        P = torch.empty(B, N, N, dtype=dt, device=x.device)
+        call("softmax_rows", S, P, B * N, N, float(int(C) ** (-0.5)), act_code(dt))
+        del S
+        O = torch.empty(B, H, W, C, dtype=dt, device=x.device)
+        gemm_raw(P, v, O, N, C, N, B, N, 3 * C, C, N * N, N * 3 * C, N * C, False, True)
+        out = conv_fwd_raw(O, blk.spec_proj, wp, bp, residual=x)
+        ctx.blk = blk
+        ctx.save_for_backward(x, stats, hn, qkv, P, O, gamma, beta, wq, bq, wk, bk, wv, bv, wp, bp)
+        return out
+
+    @staticmethod
+    def backward(ctx, dout):
+        x, stats, hn, qkv, P, O, gamma, beta, wq, bq, wk, bk, wv, bv, wp, bp = ctx.saved_tensors
+        blk = ctx.blk
+        B, H, W, C = x.shape
+        N = H * W
+        dt = x.dtype
+        dout = _c(dout)
+        scale = float(int(C) ** (-0.5))
+        q, k, v = qkv[..., :C], qkv[..., C:2 * C], qkv[..., 2 * C:]
+        dO = conv_dgrad_raw(dout, blk.spec_proj, wp, (H, W))
+        dwp, dbp = conv_wgrad_raw(O, dout, blk.spec_proj, wp, bp)
+        dqkv = torch.empty_like(qkv)
+        dq, dk, dv = dqkv[..., :C], dqkv[..., C:2 * C], dqkv[..., 2 * C:]
+        # dV[j,c] = sum_i P[i,j] dO[i,c]
+        gemm_raw(P, dO, dv, N, C, N, B, N, C, 3 * C, N * N, N * C, N * 3 * C, True, True)
+        # dP[i,j] = sum_c dO[i,c] v[j,c]
+        dP = torch.empty(B, N, N, dtype=torch.float32, device=x.device)
+        gemm_raw(dO, v, dP, N, N, C, B, C, 3 * C, N, N * C, N * 3 * C, N * N, False, False)
+        dS = torch.empty(B, N, N, dtype=dt, device=x.device)
+        call("softmax_rows_bwd", dP, P, dS, B * N, N, scale, act_code(dt))
+        del dP
+        # dQ[i,c] = sum_j dS[i,j] k[j,c] ; dK[j,c] = sum_i dS[i,j] q[i,c]
+        gemm_raw(dS, k, dq, N, C, N, B, N, 3 * C, 3 * C, N * N, N * 3 * C, N * 3 * C, False, True)
+        gemm_raw(dS, q, dk, N, C, N, B, N, 3 * C, 3 * C, N * N, N * 3 * C, N * 3 * C, True, True)
+        del dS
+        # fused qkv projection backward: dgrad as a GEMM against the forward packing ([3C][C], N-major view)
+        wqkv, _ = blk.fused_qkv(wq, bq, wk, bk, wv, bv, dt)
+        dhn = torch.empty_like(hn)
+        M = B * N
+        gemm_raw(dqkv, wqkv, dhn, M, C, 3 * C, 1, 3 * C, C, C, 0, 0, 0, False, True)
+        dwqkv, dbqkv, direct = blk.qkv_grad_buffers(wq, bq)
+        impl = conv_impl(dt, B, H, W, C, 3 * C, CONV_1x1)
+        nbytes = call("conv2d_wgrad_workspace_bytes", B, H, W, C, 3 * C, CONV_1x1, impl)
+        ws = workspace(nbytes, x.device, "wgrad")
+        call("conv2d_wgrad", hn, dqkv, dwqkv, dbqkv, B, H, W, C, 3 * C, C, 3 * C, CONV_1x1, act_code(dt), impl, 0, ws,
+             ws.numel())
+        dx, dg, db = gn_bwd_raw(x, stats, gamma, beta, dhn, False, dx_add=dout)
+        if direct:
+            gq = gk = gv = gbq = gbk = gbv = None
+        else:
+            gq, gk, gv = (dwqkv[i * C:(i + 1) * C].view(C, C, 1, 1) for i in range(3))
+            gbq, gbk, gbv = (dbqkv[i * C:(i + 1) * C] for i in range(3))
+        return dx, dg, db, gq, gbq, gk, gbk, gv, gbv, dwp, dbp, None
+
+
+# ------------------------------------------------------------------------------------------------
+# Upsample  (LD model.py:53-57): nearest 2x, then 3x3 conv.  Only the low-resolution input is kept.
+# ------------------------------------------------------------------------------------------------
+def upsample2x_raw(x):
+    B, H, W, C = x.shape
+    y = torch.empty(B, 2 * H, 2 * W, C, dtype=x.dtype, device=x.device)
+    call("upsample2x", x, y, B, H, W, C, act_code(x.dtype))
+    return y
+
+
+class UpsampleConv(torch.autograd.Function):
+    @staticmethod
+    def forward(ctx, x, w, b, spec):
+        u = upsample2x_raw(x)
+        ctx.spec = spec
+        ctx.save_for_backward(x, w, b)
+        return conv_fwd_raw(u, spec, w, b)
+
+    @staticmethod
+    def backward(ctx, dy):
+        x, w, b = ctx.saved_tensors
+        spec = ctx.spec
+        dy = _c(dy)
+        B, H, W, C = x.shape
+        u = upsample2x_raw(x)
+        dw, db = conv_wgrad_raw(u, dy, spec, w, b)
+        del u
+        du = conv_dgrad_raw(dy, spec, w, (2 * H, 2 * W))
+        dx = torch.empty_like(x)
+        call("upsample2x_bwd", du, dx, B, H, W, C, act_code(x.dtype))
+        return dx, dw, db, None
+
+
+# ------------------------------------------------------------------------------------------------
+# DiagonalGaussian sample + dropout + noise + pose-feature add + KL, one kernel each way
+# (LD distributions.py:24-46; AE.py:226-241,253)
+# ------------------------------------------------------------------------------------------------
+class SampleKL(torch.autograd.Function):
+    @staticmethod
+    def forward(ctx, moments, enc_pose, eps, keep, noise, keep_scale, Cz, CzPad, want_z):
+        B, H, W, ld = moments.shape
+        HW = H * W
+        dev = moments.device
+        mean = torch.empty(B, Cz, H, W, dtype=torch.float32, device=dev)
+        logvar = torch.empty(B, Cz, H, W, dtype=torch.float32, device=dev)
+        kl = torch.empty(B, dtype=torch.float32, device=dev)
+        z = torch.empty(B, H, W, CzPad, dtype=moments.dtype, device=dev) if want_z else None
+        call("sample_kl_fwd", moments, eps, keep, noise, enc_pose, float(keep_scale), mean, logvar, z, kl, B, HW, Cz,
+             CzPad, ld, act_code(moments.dtype))
+        ctx.cfg = (Cz, CzPad, ld, float(keep_scale), moments.dtype, enc_pose is not None)
+        ctx.save_for_backward(mean, logvar, eps, keep)
+        if z is None:
+            z = torch.empty(0, device=dev)
+        return mean, logvar, z, kl
+
+    @staticmethod
+    def backward(ctx, dmean, dlogvar, dz, dkl):
+        mean, logvar, eps, keep = ctx.saved_tensors
+        Cz, CzPad, ld, keep_scale, dtype, has_pose = ctx.cfg
+        B, _, H, W = mean.shape
+        dev = mean.device
+        if dz is not None and dz.numel() == 0:
+            dz = None
+        dz = None if dz is None else _c(dz)
+        dkl = None if dkl is None else _c(dkl.float())
+        dmean = None if dmean is None else _c(dmean.float())
+        dlogvar = None if dlogvar is None else _c(dlogvar.float())
+        dmom = torch.empty(B, H, W, ld, dtype=dtype, device=dev)
+        dpose = torch.empty(B, Cz * H * W, dtype=torch.float32, device=dev) if (has_pose and dz is not None) else None
+        call("sample_kl_bwd", dz, dkl, dmean, dlogvar, mean, logvar, eps, keep, keep_scale, dmom, dpose, B, H * W, Cz,
+             CzPad, ld, act_code(dtype))
+        if has_pose and dpose is None:
+            dpose = torch.zeros(B, Cz * H * W, dtype=torch.float32, device=dev)
+        return dmom, dpose, None, None, None, None, None, None, None
+
+
+# ------------------------------------------------------------------------------------------------
+# Masked L1 reconstruction sums (PoseLoss._get_rec_loss / mask multiplies, LOSS.py:134-145,250-257)
+# ------------------------------------------------------------------------------------------------
+class L1Masked(torch.autograd.Function):
+    """sums[b] = sum_{c,p} |x*m - xhat*m|.  Gradient flows to xhat only (x is the ground truth)."""
+
+    @staticmethod
+    def forward(ctx, x, xhat, mask2d):
+        B, C, H, W = xhat.shape
+        HW = H * W
+        sums = torch.empty(B, dtype=torch.float32, device=xhat.device)
+        sgn = torch.empty(B, C, H, W, dtype=torch.int8, device=xhat.device)
+        nbytes = call("l1_masked_workspace_bytes", B, C, HW)
+        ws = workspace(nbytes, xhat.device, "l1")
+        call("l1_masked_fwd", x, xhat, mask2d, sums, sgn, B, C, HW, ws, ws.numel())
+        ctx.save_for_backward(sgn)
+        return sums
+
+    @staticmethod
+    def backward(ctx, dsums):
+        (sgn,) = ctx.saved_tensors
+        B, C, H, W = sgn.shape
+        dxhat = torch.empty(B, C, H, W, dtype=torch.float32, device=sgn.device)
+        call("l1_masked_bwd", sgn, _c(dsums.float()), dxhat, B, C, H * W)
+        return None, dxhat, None
+
+
+# ------------------------------------------------------------------------------------------------
+# nn.Linear / activations of the pose MLPs (pose_decoder.py:82-97, pose_encoder.py:82-131), fp32 SIMT GEMM
+# ------------------------------------------------------------------------------------------------
+class Linear(torch.autograd.Function):
+    @staticmethod
+    def forward(ctx, x, w, b):
+        M, K = x.shape
+        N = w.shape[0]
+        y = torch.empty(M, N, dtype=torch.float32, device=x.device)
+        gemm_raw(x, w.detach(), y, M, N, K, 1, K, K, N, 0, 0, 0, False, False, bias=None if b is None else b.detach())
+        ctx.save_for_backward(x, w, b)
+        return y
+
+    @staticmethod
+    def backward(ctx, dy):
+        x, w, b = ctx.saved_tensors
+        dy = _c(dy.float())
+        M, K = x.shape
+        N = w.shape[0]
+        dx = None
+        if ctx.needs_input_grad[0]:
+            dx = torch.empty(M, K, dtype=torch.float32, device=x.device)
+            gemm_raw(dy, w.detach(), dx, M, K, N, 1, N, K, K, 0, 0, 0, False, True)
+        dw, dw_direct = _new_grad(w)
+        gemm_raw(dy, x, dw, N, K, M, 1, N, K, K, 0, 0, 0, True, True)
+        db = None
+        if b is not None:
+            db, db_direct = _new_grad(b)
+            nbytes = call("colsum_workspace_bytes", N)
+            ws = workspace(nbytes, x.device, "colsum")
+            call("colsum", dy, M, N, N, F32, db, 0, ws, ws.numel())
+            db = _ret(db, db_direct)
+        return dx, _ret(dw, dw_direct), db
+
+
+class Act(torch.autograd.Function):
+    """act = 1 tanh, 2 silu on fp32 tensors."""
+
+    @staticmethod
+    def forward(ctx, x, act):
+        x = _c(x)
+        y = torch.empty_like(x)
+        call("act_fwd", x, y, x.numel(), act)
+        ctx.act = act
+        ctx.save_for_backward(x)
+        return y
+
+    @staticmethod
+    def backward(ctx, dy):
+        (x,) = ctx.saved_tensors
+        dx = torch.empty_like(x)
+        call("act_bwd", x, _c(dy), dx, x.numel(), ctx.act)
+        return dx, None
+
+
+def rescale_minmax(x):
+    """AE.py:434-436 `_rescale`: 2*(x-min)/(max-min)-1 over the whole batch tensor; two kernels, no host sync."""
+    x = _c(x.float())
+    mm = torch.empty(2, dtype=torch.float32, device=x.device)
+    ws = workspace(1 << 16, x.device, "minmax")
+    call("minmax", x, x.numel(), mm, ws, ws.numel())
+    out = torch.empty_like(x)
+    call("rescale", x, out, x.numel(), mm)
+    return out

@@ -184,6 +184,53 @@ int odvae_adam_step(float* p, const float* g, float* m, float* v, int64_t n, flo
                     float eps, float bias_corr1, float bias_corr2, const float* gnorm_sq, float max_norm,
                     void* stream);
 
+/* Multi-tensor variants over a device-resident chunk table (no flattening copies): `table` is
+ * nrows x {uint64 p, uint64 g, uint64 m, uint64 v, int64 count} (40 bytes per row, count <= 65536);
+ * one CTA per row.  odvae_mt_sumsq: out1[0] = sum over all rows of g^2 (fixed order; workspace holds
+ * nrows floats; p/m/v entries ignored).  odvae_mt_adam_step: Adam on every row with the gradient scaled by
+ * grad_scale (1/world_size after a sum-allreduce) and clipped by max_norm against gnorm_sq (taken over
+ * the UNSCALED gradients; NULL = no clipping). */
+int odvae_mt_sumsq(const void* table, int nrows, float* out1, void* workspace, size_t ws_bytes, void* stream);
+int odvae_mt_adam_step(const void* table, int nrows, float lr, float beta1, float beta2, float eps,
+                       float bias_corr1, float bias_corr2, const float* gnorm_sq, float max_norm,
+                       float grad_scale, void* stream);
+
+/* ---------------------------------------------------------------------------------------------
+ * Small heads (csrc/heads.cu): pose-MLP glue and the whole PoseLoss reduction tail, one launch each way.
+ * ------------------------------------------------------------------------------------------- */
+/* PoseEncoderSpatialVAE tile+add (pose_encoder.py:121-125): h[b][p*F+f] = hx[p*F+f] + hz[b][f];
+ * bwd: dhx[P*F] = sum_b dh, dhz[B][F] = sum_p dh. */
+int odvae_tile_add_fwd(const float* hx, const float* hz, float* h, int B, int P, int F, void* stream);
+int odvae_tile_add_bwd(const float* dh, float* dhx, float* dhz, int B, int P, int F, void* stream);
+/* PoseAutoencoder._decode_pose (AE.py:126-160): zz [B][16+ncls] = (mu[8] | logvar[8] | logits[ncls]) ->
+ * mean/logvar [B][8] (logvar clamped to [-30,20]) and dec_pose [B][8+ncls] = (mu + exp(logvar/2)*eps | logits).
+ * eps == NULL gives mode().  bwd: any of d_dec_pose / d_mean / d_logvar may be NULL. */
+int odvae_pose_head_fwd(const float* zz, const float* eps, float* dec_pose, float* mean, float* logvar, int B,
+                        int ncls, void* stream);
+int odvae_pose_head_bwd(const float* zz, const float* eps, const float* d_dec_pose, const float* d_mean,
+                        const float* d_logvar, float* dzz, int B, int ncls, void* stream);
+/* PoseLoss.forward tail, optimizer_idx 0 (LOSS.py:221-228,260-278,307-321): mask_bg = class_gt != background_idx,
+ * focal class loss (mmdet FocalLoss() defaults), masked MSE bbox / fill-factor, masked L1 + SmoothL1(sin) pose,
+ * NLL from the per-sample masked-L1 sums (l1_sums[B], NULL = pixel loss off; npix = C*H*W per sample) with the
+ * learned scalar `logvar`, masked KL(obj) (kl_obj[B], may be NULL), per-class prior KL of the bbox posterior
+ * (prior [L][8][2] = (mean, clamped logvar); prior_row[b] = table row or -1 for the "background" label; the
+ * [8,8] cross term of src/util/distributions.py:29-41 is reproduced).  Terms divided by sum(mask_bg) are 0
+ * when it is 0.  weights7 (HOST pointer) = {nll, kl_obj, pose, class, bbox, fill, kl_bbox} weights of `total`.
+ * out16: 0 total 1 nll 2 kl_obj 3 rec_mean 4 pose 5 class 6 bbox 7 fill 8 kl_bbox 9-12 mean t1,t2,t3,v3
+ * 13 sum(mask_bg).  bwd takes dout16 (gradient of every out entry) and writes the input gradients
+ * (d_l1_sums / d_kl_obj may be NULL). */
+int odvae_loss_heads_fwd(const float* dec_pose, const float* bbox_mean, const float* bbox_logvar,
+                         const float* l1_sums, const float* kl_obj, const float* logvar, const float* pose_gt,
+                         const float* bbox_gt, const float* fill_gt, const int64_t* class_gt, const int* prior_row,
+                         const float* prior, int B, int ncls, int background_idx, float npix, const float* weights7,
+                         float* out16, void* stream);
+int odvae_loss_heads_bwd(const float* dec_pose, const float* bbox_mean, const float* bbox_logvar,
+                         const float* l1_sums, const float* kl_obj, const float* logvar, const float* pose_gt,
+                         const float* bbox_gt, const float* fill_gt, const int64_t* class_gt, const int* prior_row,
+                         const float* prior, int B, int ncls, int background_idx, float npix, const float* weights7,
+                         const float* out16, const float* dout16, float* d_dec_pose, float* d_bbox_mean,
+                         float* d_bbox_logvar, float* d_l1_sums, float* d_kl_obj, float* d_logvar, void* stream);
+
 /* generic elementwise helpers on activations (residual adds that cannot be fused) */
 int odvae_add(const void* a, const void* b, void* out, int64_t n, int act_dtype, void* stream);
 

@@ -5,10 +5,11 @@ import pytest
 
 ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
 PKG = os.path.join(ROOT, "generative-detection_b200")
-for p in (PKG, ROOT):
+for p in (PKG, ROOT, os.path.dirname(os.path.abspath(__file__))):
     if p not in sys.path:
         sys.path.insert(0, p)
 
 
 def pytest_configure(config):
     config.addinivalue_line("markers", "gpu: needs a B200 (sm_100a) device; run with -m gpu")
+    config.addinivalue_line("markers", "slow: long CPU case (still part of the default CPU run)")

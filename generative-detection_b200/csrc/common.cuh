@@ -11,6 +11,7 @@ namespace odvae {
 void set_last_cuda_error(cudaError_t e, const char* where);
 int check_launch(const char* where);  // returns ODVAE_OK or ODVAE_ERR_CUDA after a kernel launch
 int num_sms();
+unsigned long long launch_count();
 
 #define ODVAE_CUDA_TRY(expr)                       \
   do {                                             \
@@ -55,10 +56,10 @@ __device__ __forceinline__ float warp_min(float v) {
   return v;
 }
 
-__device__ __forceinline__ float silu_f(float u) { return u / (1.0f + __expf(-u)); }
+__device__ __forceinline__ float silu_f(float u) { return __fdividef(u, 1.0f + __expf(-u)); }
 // d/du [u * sigmoid(u)]
 __device__ __forceinline__ float silu_grad_f(float u) {
-  float s = 1.0f / (1.0f + __expf(-u));
+  float s = __fdividef(1.0f, 1.0f + __expf(-u));
   return s * (1.0f + u * (1.0f - s));
 }
 

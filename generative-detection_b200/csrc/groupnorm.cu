@@ -51,7 +51,36 @@ gn_reduce_kernel(const T* __restrict__ x, const T* __restrict__ dy, const float*
   if (row < rows) {
     const T* xb = x + static_cast<long long>(b) * HW * C + c0;
     const T* dyb = MODE == 1 ? dy + static_cast<long long>(b) * HW * C + c0 : nullptr;
-    for (int p = p0 + row; p < p1; p += rows) {
+    constexpr int U = 4;
+    int p = p0 + row;
+    for (; p + (U - 1) * rows < p1; p += U * rows) {
+      T xv[U][V], dv[U][V];
+#pragma unroll
+      for (int u = 0; u < U; ++u)
+        *reinterpret_cast<uint4*>(xv[u]) = __ldg(reinterpret_cast<const uint4*>(xb + static_cast<long long>(p + u * rows) * C));
+      if (MODE == 1) {
+#pragma unroll
+        for (int u = 0; u < U; ++u)
+          *reinterpret_cast<uint4*>(dv[u]) = __ldg(reinterpret_cast<const uint4*>(dyb + static_cast<long long>(p + u * rows) * C));
+      }
+#pragma unroll
+      for (int u = 0; u < U; ++u) {
+#pragma unroll
+        for (int j = 0; j < V; ++j) {
+          const float v = to_f32<T>(xv[u][j]);
+          if (MODE == 0) {
+            s0[j] += v;
+            s1[j] = fmaf(v, v, s1[j]);
+          } else {
+            float d = to_f32<T>(dv[u][j]);
+            if (silu) d *= silu_grad_f(fmaf(v, sc[j], sh[j]));
+            s0[j] += d;
+            s1[j] = fmaf(d, (v - mu[j]) * rs[j], s1[j]);
+          }
+        }
+      }
+    }
+    for (; p < p1; p += rows) {
       T xv[V];
       *reinterpret_cast<uint4*>(xv) = __ldg(reinterpret_cast<const uint4*>(xb + static_cast<long long>(p) * C));
       if (MODE == 0) {
@@ -146,16 +175,35 @@ gn_apply_kernel(const T* __restrict__ x, const float* __restrict__ stats, const 
   const long long nvec = static_cast<long long>(HW) * cv;
   const uint4* xb = reinterpret_cast<const uint4*>(x + static_cast<long long>(b) * HW * C);
   uint4* yb = reinterpret_cast<uint4*>(y + static_cast<long long>(b) * HW * C);
-  for (long long i = blockIdx.x * static_cast<long long>(GN_THREADS) + threadIdx.x; i < nvec;
-       i += static_cast<long long>(gridDim.x) * GN_THREADS) {
+  const long long stride = static_cast<long long>(gridDim.x) * GN_THREADS;
+  constexpr int U = 4;
+  long long i = blockIdx.x * static_cast<long long>(GN_THREADS) + threadIdx.x;
+  for (; i + (U - 1) * stride < nvec; i += U * stride) {
+    T xv[U][V];
+#pragma unroll
+    for (int u = 0; u < U; ++u) *reinterpret_cast<uint4*>(xv[u]) = __ldg(xb + i + u * stride);
+#pragma unroll
+    for (int u = 0; u < U; ++u) {
+      const int c0 = static_cast<int>((i + u * stride) % cv) * V;
+      T yv[V];
+#pragma unroll
+      for (int j = 0; j < V; ++j) {
+        float v = fmaf(to_f32<T>(xv[u][j]), scale[c0 + j], shift[c0 + j]);
+        if (silu) v = silu_f(v);
+        yv[j] = from_f32<T>(v);
+      }
+      yb[i + u * stride] = *reinterpret_cast<const uint4*>(yv);
+    }
+  }
+  for (; i < nvec; i += stride) {
     const int c0 = static_cast<int>(i % cv) * V;
     T xv[V], yv[V];
     *reinterpret_cast<uint4*>(xv) = __ldg(xb + i);
 #pragma unroll
     for (int j = 0; j < V; ++j) {
-      float u = fmaf(to_f32<T>(xv[j]), scale[c0 + j], shift[c0 + j]);
-      if (silu) u = silu_f(u);
-      yv[j] = from_f32<T>(u);
+      float v = fmaf(to_f32<T>(xv[j]), scale[c0 + j], shift[c0 + j]);
+      if (silu) v = silu_f(v);
+      yv[j] = from_f32<T>(v);
     }
     yb[i] = *reinterpret_cast<const uint4*>(yv);
   }
@@ -242,28 +290,43 @@ gn_bwd_apply_kernel(const T* __restrict__ x, const T* __restrict__ dy, const T* 
   const uint4* dyb = reinterpret_cast<const uint4*>(dy + base);
   const uint4* ab = dx_add ? reinterpret_cast<const uint4*>(dx_add + base) : nullptr;
   uint4* dxb = reinterpret_cast<uint4*>(dx + base);
-  for (long long i = blockIdx.x * static_cast<long long>(GN_THREADS) + threadIdx.x; i < nvec;
-       i += static_cast<long long>(gridDim.x) * GN_THREADS) {
-    const int c0 = static_cast<int>(i % cv) * V;
-    T xv[V], dv[V], av[V], ov[V];
-    *reinterpret_cast<uint4*>(xv) = __ldg(xb + i);
-    *reinterpret_cast<uint4*>(dv) = __ldg(dyb + i);
-    if (ab) *reinterpret_cast<uint4*>(av) = __ldg(ab + i);
+  const long long stride = static_cast<long long>(gridDim.x) * GN_THREADS;
+  constexpr int U = 2;
+  long long i = blockIdx.x * static_cast<long long>(GN_THREADS) + threadIdx.x;
+  for (; i < nvec; i += U * stride) {
+    T xv[U][V], dv[U][V], av[U][V];
 #pragma unroll
-    for (int j = 0; j < V; ++j) {
-      const float xf = to_f32<T>(xv[j]);
-      float d = to_f32<T>(dv[j]);
-      if (silu) d *= silu_grad_f(fmaf(xf, scale[c0 + j], shift[c0 + j]));
-      float o = fmaf(scale[c0 + j], d, fmaf(c2[c0 + j], xf, c3[c0 + j]));
-      if (ab) o += to_f32<T>(av[j]);
-      ov[j] = from_f32<T>(o);
+    for (int u = 0; u < U; ++u) {
+      const long long k = i + u * stride;
+      if (k < nvec) {
+        *reinterpret_cast<uint4*>(xv[u]) = __ldg(xb + k);
+        *reinterpret_cast<uint4*>(dv[u]) = __ldg(dyb + k);
+        if (ab) *reinterpret_cast<uint4*>(av[u]) = __ldg(ab + k);
+      }
     }
-    dxb[i] = *reinterpret_cast<const uint4*>(ov);
+#pragma unroll
+    for (int u = 0; u < U; ++u) {
+      const long long k = i + u * stride;
+      if (k < nvec) {
+        const int c0 = static_cast<int>(k % cv) * V;
+        T ov[V];
+#pragma unroll
+        for (int j = 0; j < V; ++j) {
+          const float xf = to_f32<T>(xv[u][j]);
+          float d = to_f32<T>(dv[u][j]);
+          if (silu) d *= silu_grad_f(fmaf(xf, scale[c0 + j], shift[c0 + j]));
+          float o = fmaf(scale[c0 + j], d, fmaf(c2[c0 + j], xf, c3[c0 + j]));
+          if (ab) o += to_f32<T>(av[u][j]);
+          ov[j] = from_f32<T>(o);
+        }
+        dxb[k] = *reinterpret_cast<const uint4*>(ov);
+      }
+    }
   }
 }
 
 static int gn_nsplit(int B, int HW) {
-  int target = (2 * num_sms() + B - 1) / B;
+  int target = (6 * num_sms() + B - 1) / B;
   int maxs = HW / 32;
   if (maxs < 1) maxs = 1;
   if (target > maxs) target = maxs;

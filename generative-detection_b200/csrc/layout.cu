@@ -216,6 +216,52 @@ __global__ void colsum_stage1(const T* __restrict__ m, long long rows, int cols,
     __syncthreads();
   }
 }
+// vectorised variant: every thread streams 16-byte vectors of whole rows (ld % V == 0, ld / V <= 256); the block's
+// row lanes are combined through shared memory in a fixed order. Columns >= cols (channel padding) are dropped.
+template <typename T, int V>
+__global__ void __launch_bounds__(256) colsum_stage1_vec(const T* __restrict__ m, long long rows, int cols, int ld,
+                                                          float* __restrict__ part) {
+  const int nvec = ld / V;
+  const int lanes = 256 / nvec;  // row lanes per block
+  const int cv = threadIdx.x % nvec, lane = threadIdx.x / nvec;
+  const long long rows_per_blk = (rows + gridDim.x - 1) / gridDim.x;
+  const long long r0 = blockIdx.x * rows_per_blk;
+  const long long r1 = r0 + rows_per_blk < rows ? r0 + rows_per_blk : rows;
+  float acc[V];
+#pragma unroll
+  for (int j = 0; j < V; ++j) acc[j] = 0.0f;
+  if (lane < lanes) {
+    const T* base = m + static_cast<long long>(cv) * V;
+    long long r = r0 + lane;
+    for (; r + 3ll * lanes < r1; r += 4ll * lanes) {
+      T v0[V], v1[V], v2[V], v3[V];
+      *reinterpret_cast<uint4*>(v0) = __ldg(reinterpret_cast<const uint4*>(base + r * ld));
+      *reinterpret_cast<uint4*>(v1) = __ldg(reinterpret_cast<const uint4*>(base + (r + lanes) * ld));
+      *reinterpret_cast<uint4*>(v2) = __ldg(reinterpret_cast<const uint4*>(base + (r + 2ll * lanes) * ld));
+      *reinterpret_cast<uint4*>(v3) = __ldg(reinterpret_cast<const uint4*>(base + (r + 3ll * lanes) * ld));
+#pragma unroll
+      for (int j = 0; j < V; ++j)
+        acc[j] += (to_f32<T>(v0[j]) + to_f32<T>(v1[j])) + (to_f32<T>(v2[j]) + to_f32<T>(v3[j]));
+    }
+    for (; r < r1; r += lanes) {
+      T v0[V];
+      *reinterpret_cast<uint4*>(v0) = __ldg(reinterpret_cast<const uint4*>(base + r * ld));
+#pragma unroll
+      for (int j = 0; j < V; ++j) acc[j] += to_f32<T>(v0[j]);
+    }
+  }
+  extern __shared__ float csm[];  // [lanes][ld]
+  if (lane < lanes) {
+#pragma unroll
+    for (int j = 0; j < V; ++j) csm[lane * ld + cv * V + j] = acc[j];
+  }
+  __syncthreads();
+  for (int c = threadIdx.x; c < cols; c += 256) {
+    float t = 0.0f;
+    for (int l = 0; l < lanes; ++l) t += csm[l * ld + c];
+    part[static_cast<long long>(blockIdx.x) * cols + c] = t;
+  }
+}
 __global__ void colsum_stage2(const float* __restrict__ part, int nblk, int cols, float* __restrict__ out,
                               int accumulate) {
   const int c = blockIdx.x * blockDim.x + threadIdx.x;
@@ -308,18 +354,29 @@ int launch_wgrad_reduce(const float* ws, float* dw, int Cout, int Cin, int taps,
   return check_launch("wgrad_reduce_kernel");
 }
 
-static constexpr int COLSUM_BLOCKS = 296;
+static constexpr int COLSUM_BLOCKS = 592;
 size_t colsum_workspace_bytes(int cols) { return static_cast<size_t>(COLSUM_BLOCKS) * cols * sizeof(float); }
 int launch_colsum(const void* m, long long rows, int cols, int ld, int act_dtype, float* out, int accumulate,
                   float* part, cudaStream_t st) {
   int nblk = COLSUM_BLOCKS;
   if (rows < nblk * 8) nblk = static_cast<int>((rows + 7) / 8);
   if (nblk < 1) nblk = 1;
-  dim3 blk(32, 8);
-  if (act_dtype == ODVAE_BF16)
-    colsum_stage1<bf16><<<nblk, blk, 0, st>>>(reinterpret_cast<const bf16*>(m), rows, cols, ld, part);
-  else
-    colsum_stage1<float><<<nblk, blk, 0, st>>>(reinterpret_cast<const float*>(m), rows, cols, ld, part);
+  const int V = act_dtype == ODVAE_BF16 ? 8 : 4;
+  const bool vec = ld % V == 0 && ld / V <= 256 && 256 % (ld / V) == 0 && (reinterpret_cast<uintptr_t>(m) & 15) == 0 &&
+                   static_cast<size_t>(256 / (ld / V)) * ld * sizeof(float) <= 48 * 1024;
+  if (vec) {
+    const size_t smem = static_cast<size_t>(256 / (ld / V)) * ld * sizeof(float);
+    if (act_dtype == ODVAE_BF16)
+      colsum_stage1_vec<bf16, 8><<<nblk, 256, smem, st>>>(reinterpret_cast<const bf16*>(m), rows, cols, ld, part);
+    else
+      colsum_stage1_vec<float, 4><<<nblk, 256, smem, st>>>(reinterpret_cast<const float*>(m), rows, cols, ld, part);
+  } else {
+    dim3 blk(32, 8);
+    if (act_dtype == ODVAE_BF16)
+      colsum_stage1<bf16><<<nblk, blk, 0, st>>>(reinterpret_cast<const bf16*>(m), rows, cols, ld, part);
+    else
+      colsum_stage1<float><<<nblk, blk, 0, st>>>(reinterpret_cast<const float*>(m), rows, cols, ld, part);
+  }
   int s = check_launch("colsum_stage1");
   if (s != ODVAE_OK) return s;
   colsum_stage2<<<(cols + 127) / 128, 128, 0, st>>>(part, nblk, cols, out, accumulate);

@@ -2,6 +2,7 @@
 #include <stdio.h>
 #include <string.h>
 
+#include <atomic>
 #include <mutex>
 
 #include "common.cuh"
@@ -14,7 +15,11 @@ void set_last_cuda_error(cudaError_t e, const char* where) {
   snprintf(g_last_error, sizeof(g_last_error), "%s: %s (%s)", where, cudaGetErrorName(e), cudaGetErrorString(e));
 }
 
+static std::atomic<unsigned long long> g_launches{0};
+unsigned long long launch_count() { return g_launches.load(std::memory_order_relaxed); }
+
 int check_launch(const char* where) {
+  g_launches.fetch_add(1, std::memory_order_relaxed);  // called exactly once after every kernel launch
   cudaError_t e = cudaGetLastError();
   if (e != cudaSuccess) {
     set_last_cuda_error(e, where);
@@ -62,5 +67,7 @@ int odvae_device_supported(void) {
 }
 
 int odvae_version(void) { return 100; }
+
+int64_t odvae_launch_count(void) { return static_cast<int64_t>(odvae::launch_count()); }
 
 }  // extern "C"

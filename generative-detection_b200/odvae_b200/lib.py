@@ -29,7 +29,7 @@ def parse_header(path=HEADER):
     text = re.sub(r"/\*.*?\*/", "", text, flags=re.S)
     text = re.sub(r"//[^\n]*", "", text)
     protos = {}
-    for m in re.finditer(r"(const char\*|int|size_t)\s+(odvae_\w+)\s*\(([^)]*)\)\s*;", text):
+    for m in re.finditer(r"(const char\*|int64_t|int|size_t)\s+(odvae_\w+)\s*\(([^)]*)\)\s*;", text):
         ret, name, args = m.group(1), m.group(2), m.group(3).strip()
         arglist = []
         if args and args != "void":
@@ -63,7 +63,7 @@ class _Lib:
             dll = ctypes.CDLL(LIB_PATH)
             for name, (ret, args) in self.protos.items():
                 fn = getattr(dll, name)  # raises AttributeError if the symbol is not exported
-                fn.restype = {"int": ctypes.c_int, "size_t": ctypes.c_size_t, "const char*": ctypes.c_char_p}[ret]
+                fn.restype = {"int": ctypes.c_int, "int64_t": ctypes.c_int64, "size_t": ctypes.c_size_t, "const char*": ctypes.c_char_p}[ret]
                 fn.argtypes = [_ctype_of(t) for t, _ in args]
             self._dll = dll
         return self._dll

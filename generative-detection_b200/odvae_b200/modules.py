@@ -24,6 +24,20 @@ def _check_cuda(x):
     require_device()
 
 
+_ARENA = [None]  # set by odvae_b200.ddp users (TrainStep): bucket-boundary hooks are attached while it is set
+
+
+def _run(mod, h, *args, **kw):
+    """Call `mod(h)`; when a gradient arena is active, hook the input activation so that the bucket(s) holding
+    the module's parameter gradients are all-reduced as soon as its backward has been enqueued."""
+    arena = _ARENA[0]
+    if arena is not None and h.requires_grad:
+        first = next(mod.parameters(), None)
+        if first is not None and id(first) in arena._index:
+            h.register_hook(arena.boundary_hook(first))
+    return mod(h, *args, **kw)
+
+
 class Conv2d(nn.Module):
     """Parameter container + geometry of one torch.nn.Conv2d of the reference (same init as torch)."""
 
@@ -149,7 +163,7 @@ class _Mid(nn.Module):
         self.block_2 = ResnetBlock(channels)
 
     def forward(self, h):
-        return self.block_2(self.attn_1(self.block_1(h)))
+        return _run(self.block_2, _run(self.attn_1, _run(self.block_1, h)))
 
 
 class Encoder(nn.Module):
@@ -194,14 +208,14 @@ class Encoder(nn.Module):
         for i_level in range(self.num_resolutions):
             lvl = self.down[i_level]
             for i_block in range(self.num_res_blocks):
-                h = lvl.block[i_block](h)
+                h = _run(lvl.block[i_block], h)
                 if len(lvl.attn) > 0:
-                    h = lvl.attn[i_block](h)
+                    h = _run(lvl.attn[i_block], h)
             if i_level != self.num_resolutions - 1:
-                h = lvl.downsample(h)
+                h = _run(lvl.downsample, h)
         h = self.mid(h)
-        h = self.norm_out(h, silu=True)
-        return self.conv_out(h)
+        h = _run(self.norm_out, h, silu=True)
+        return _run(self.conv_out, h)
 
     def forward(self, x):
         return ops.ToNCHW.apply(self.forward_nhwc(x), self.out_channels)
@@ -241,18 +255,18 @@ class Decoder(nn.Module):
 
     def forward_nhwc(self, z):
         """z: NHWC [B,h,w,pad64(z_channels)] -> dec NCHW fp32 [B,out_ch,H,W]."""
-        h = self.conv_in(z)
+        h = _run(self.conv_in, z)
         h = self.mid(h)
         for i_level in reversed(range(self.num_resolutions)):
             lvl = self.up[i_level]
             for i_block in range(self.num_res_blocks + 1):
-                h = lvl.block[i_block](h)
+                h = _run(lvl.block[i_block], h)
                 if len(lvl.attn) > 0:
-                    h = lvl.attn[i_block](h)
+                    h = _run(lvl.attn[i_block], h)
             if i_level != 0:
-                h = lvl.upsample(h)
-        h = self.norm_out(h, silu=True)
-        return self.conv_out(h, out_nchw=True)
+                h = _run(lvl.upsample, h)
+        h = _run(self.norm_out, h, silu=True)
+        return _run(self.conv_out, h, out_nchw=True)
 
     def forward(self, z):
         _check_cuda(z)

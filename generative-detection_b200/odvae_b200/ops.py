@@ -439,7 +439,10 @@ class AttnBlock(torch.autograd.Function):
         call("conv2d_wgrad", hn, dqkv, dwqkv, dbqkv, B, H, W, C, 3 * C, C, 3 * C, CONV_1x1, act_code(dt), impl, 0, ws,
              ws.numel())
         dx, dg, db = gn_bwd_raw(x, stats, gamma, beta, dhn, False, dx_add=dout)
-        if direct:
+        if grad_dst(wq) is not None:  # arena mode: device-to-device copies of the three row blocks
+            for i, (w_, b_) in enumerate(((wq, bq), (wk, bk), (wv, bv))):
+                grad_dst(w_).copy_(dwqkv[i * C:(i + 1) * C].view(C, C, 1, 1))
+                grad_dst(b_).copy_(dbqkv[i * C:(i + 1) * C])
             gq = gk = gv = gbq = gbk = gbv = None
         else:
             gq, gk, gv = (dwqkv[i * C:(i + 1) * C].view(C, C, 1, 1) for i in range(3))

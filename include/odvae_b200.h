@@ -50,6 +50,8 @@ const char* odvae_last_cuda_error(void);
 /* 1 when the current device is compute capability 10.x */
 int odvae_device_supported(void);
 int odvae_version(void);
+/* number of kernels this library has launched in this process (all streams, all threads) */
+int64_t odvae_launch_count(void);
 
 /* ---------------------------------------------------------------------------------------------
  * Layout / dtype conversion at the module boundary (AE.py:223, LD/ldm/models/autoencoder.py:344-349)

@@ -1,0 +1,114 @@
+"""GPU unit tests of the memory-bound kernels through the C ABI against plain torch fp32 math on the same
+(bf16-rounded) inputs. Tolerances: f32 kernels 1e-4 (2e-4 where a long fp32 reduction is involved), bf16 storage 1e-2."""
+import pytest
+import torch
+import torch.nn.functional as F
+
+pytestmark = pytest.mark.gpu
+
+from odvae_b200 import ops  # noqa: E402
+
+DEV = "cuda"
+
+
+def rel(a, ref):
+    a, ref = a.detach().float(), ref.detach().float()
+    return float((a - ref).abs().max() / ref.abs().max().clamp_min(1e-20))
+
+
+@pytest.mark.parametrize("dtype", [torch.float32, torch.bfloat16])
+@pytest.mark.parametrize("shape", [(2, 16, 16, 128), (3, 32, 32, 64), (1, 64, 64, 256), (2, 8, 8, 512), (65, 16, 16, 128)])
+@pytest.mark.parametrize("silu", [False, True])
+def test_groupnorm_fwd_bwd(dtype, shape, silu):
+    torch.manual_seed(0)
+    B, H, W, C = shape
+    x = (torch.randn(shape, device=DEV) * 1.5 + 0.3).to(dtype)
+    gamma = 1 + 0.1 * torch.randn(C, device=DEV)
+    beta = 0.1 * torch.randn(C, device=DEV)
+    dy = torch.randn(shape, device=DEV).to(dtype)
+    add = torch.randn(shape, device=DEV).to(dtype)
+    xr = x.float().permute(0, 3, 1, 2).requires_grad_(True)
+    gr, br = gamma.clone().requires_grad_(True), beta.clone().requires_grad_(True)
+    y_ref = F.group_norm(xr, 32, gr, br, eps=1e-6)
+    if silu:
+        y_ref = F.silu(y_ref)
+    y_ref.backward(dy.float().permute(0, 3, 1, 2))
+    stats = ops.gn_stats_raw(x, C)
+    y = ops.gn_apply_raw(x, stats, gamma, beta, silu)
+    dx, dg, db = ops.gn_bwd_raw(x, stats, gamma, beta, dy, silu, dx_add=add)
+    torch.cuda.synchronize()
+    tol = 1e-2 if dtype == torch.bfloat16 else 2e-4
+    assert rel(y.permute(0, 3, 1, 2), y_ref) < tol
+    assert rel(dx.float() - add.float(), xr.grad.permute(0, 2, 3, 1)) < 2 * tol
+    assert rel(dg, gr.grad) < tol and rel(db, br.grad) < tol
+
+
+@pytest.mark.parametrize("dtype", [torch.float32, torch.bfloat16])
+@pytest.mark.parametrize("rows,cols,ld", [(4096, 128, 128), (1000, 3, 64), (77, 500, 500), (300000, 64, 64), (513, 512, 512)])
+def test_colsum(dtype, rows, cols, ld):
+    torch.manual_seed(1)
+    m = torch.randn(rows, ld, device=DEV).to(dtype)
+    out = torch.empty(cols, device=DEV)
+    ws = ops.workspace(ops.call("colsum_workspace_bytes", cols), m.device, "colsum")
+    ops.call("colsum", m, rows, cols, ld, ops.act_code(dtype), out, 0, ws, ws.numel())
+    torch.cuda.synchronize()
+    ref = m.float()[:, :cols].double().sum(0).float()
+    assert float((out - ref).abs().max()) < 2e-4 * float(m.float().abs().double().sum(0).max())
+
+
+@pytest.mark.parametrize("dtype", [torch.float32, torch.bfloat16])
+@pytest.mark.parametrize("n", [256, 4096])
+def test_softmax_rows_fwd_bwd(dtype, n):
+    torch.manual_seed(2)
+    rows, scale = 300, 0.0625
+    S = torch.randn(rows, n, device=DEV) * 8
+    P = torch.empty(rows, n, dtype=dtype, device=DEV)
+    ops.call("softmax_rows", S, P, rows, n, scale, ops.act_code(dtype))
+    Sr = S.clone().requires_grad_(True)
+    Pr = torch.softmax(Sr * scale, dim=-1)
+    dP = torch.randn(rows, n, device=DEV)
+    Pr.backward(dP)
+    dS = torch.empty(rows, n, dtype=dtype, device=DEV)
+    ops.call("softmax_rows_bwd", dP, P, dS, rows, n, scale, ops.act_code(dtype))
+    torch.cuda.synchronize()
+    tol = 1e-2 if dtype == torch.bfloat16 else 1e-4
+    assert rel(P, Pr) < tol
+    assert rel(dS, Sr.grad) < 2 * tol
+
+
+def test_sample_kl_and_l1_against_torch():
+    torch.manual_seed(3)
+    B, HW, Cz = 3, 256, 16
+    mom = torch.randn(B, 16, 16, 64, device=DEV) * 2
+    mom[..., 16:32] *= 12  # exercise the clamp
+    eps, noise = torch.randn(B, Cz, 16, 16, device=DEV), torch.randn(B, Cz, 16, 16, device=DEV)
+    keep = (torch.rand(B, Cz, 16, 16, device=DEV) > 0.6).to(torch.uint8)
+    pose = torch.randn(B, Cz * HW, device=DEV)
+    momr = mom.clone().requires_grad_(True)
+    poser = pose.clone().requires_grad_(True)
+    mean, logvar, z, kl = ops.SampleKL.apply(momr, poser, eps, keep, noise, 2.5, Cz, 64, True)
+    m = mom.permute(0, 3, 1, 2).clone().requires_grad_(True)
+    mu, lv = m[:, :16], torch.clamp(m[:, 16:32], -30, 20)
+    z_ref = (mu + torch.exp(0.5 * lv) * eps) * keep * 2.5 + noise + pose.view(B, Cz, 16, 16)
+    kl_ref = 0.5 * (mu ** 2 + torch.exp(lv) - 1 - lv).sum(dim=[1, 2, 3])
+    wz, wk = torch.randn_like(z_ref), torch.randn(B, device=DEV)
+    ((z_ref * wz).sum() + (kl_ref * wk).sum()).backward()
+    wz_nhwc = torch.zeros(B, 16, 16, 64, device=DEV)
+    wz_nhwc[..., :16] = wz.permute(0, 2, 3, 1)
+    ((z * wz_nhwc).sum() + (kl * wk).sum()).backward()
+    torch.cuda.synchronize()
+    assert rel(z[..., :16].permute(0, 3, 1, 2), z_ref) < 1e-5 and float(z[..., 16:].abs().max()) == 0
+    assert rel(kl, kl_ref) < 1e-5 and rel(mean, mu) < 1e-6 and rel(logvar, lv) < 1e-6
+    assert rel(momr.grad[..., :32].permute(0, 3, 1, 2), m.grad[:, :32]) < 1e-4
+    assert rel(poser.grad.view(B, Cz, 16, 16), wz) < 1e-6
+    # masked L1
+    x, xh = torch.rand(B, 3, 32, 32, device=DEV), torch.randn(B, 3, 32, 32, device=DEV, requires_grad=True)
+    mk = (torch.rand(B, 1, 32, 32, device=DEV) > 0.4).float()
+    sums = ops.L1Masked.apply(x, xh, mk)
+    w = torch.randn(B, device=DEV)
+    (sums * w).sum().backward()
+    xr = xh.detach().clone().requires_grad_(True)
+    ref = (x * mk - xr * mk).abs().sum(dim=[1, 2, 3])
+    (ref * w).sum().backward()
+    torch.cuda.synchronize()
+    assert rel(sums, ref) < 1e-5 and rel(xh.grad, xr.grad) < 1e-6

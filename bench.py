@@ -42,6 +42,10 @@ def parse():
     ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
     ap.add_argument("--cpu-baseline", type=int, default=1, help="time the CPU oracle on rank 0 at N=1 (0 = skip)")
     ap.add_argument("--no-roofline", action="store_true")
+    ap.add_argument("--ncu-step", action="store_true",
+                    help="profiling aid: after warm-up run ONE step between cudaProfilerStart/Stop and exit "
+                         "(use with `ncu --profile-from-start off`); prints no bench line")
+    ap.add_argument("--shapes", default="", help="write the per-shape engine timing table (JSON) to this path")
     return ap.parse_args()
 
 
@@ -204,6 +208,16 @@ class EngineProfiler:
         return 2.0 * B * Ho * Wo * cout * cin * taps
 
     @staticmethod
+    def shape_key(name, a):
+        if name == "gemm_bf16":
+            return "gemm M%d N%d K%d b%d a_mn%d b_mn%d" % (a[3], a[4], a[5], a[6], a[13], a[14])
+        if name == "conv2d_fwd":
+            return "fwd B%d %dx%d %d->%d g%d" % (a[5], a[6], a[7], a[8], a[9], a[11])
+        if name == "conv2d_dgrad":
+            return "dgrad B%d %dx%d %d<-%d g%d" % (a[4], a[5], a[6], a[7], a[8], a[9])
+        return "wgrad B%d %dx%d %dx%d g%d" % (a[4], a[5], a[6], a[7], a[8], a[11])
+
+    @staticmethod
     def _real(cp):
         return cp  # activations are padded only at the 3/16/32-channel edges; counted via Cin/Cout where known
 
@@ -217,7 +231,7 @@ class EngineProfiler:
                 e0.record()
                 out = self.orig(name, *a)
                 e1.record()
-                self.records.append((name, e0, e1, self.flops(name, a)))
+                self.records.append((name, e0, e1, self.flops(name, a), self.shape_key(name, a)))
                 return out
             return self.orig(name, *a)
 
@@ -228,13 +242,23 @@ class EngineProfiler:
 
     def summary(self):
         torch.cuda.synchronize()
-        tot_ms = sum(e0.elapsed_time(e1) for _, e0, e1, _ in self.records)
-        tot_fl = sum(f for *_, f in self.records)
+        tot_ms = sum(e0.elapsed_time(e1) for _, e0, e1, _, _ in self.records)
+        tot_fl = sum(r[3] for r in self.records)
         by = {}
-        for n, e0, e1, f in self.records:
+        for n, e0, e1, f, _ in self.records:
             t, ff, c = by.get(n, (0.0, 0.0, 0))
             by[n] = (t + e0.elapsed_time(e1), ff + f, c + 1)
         return tot_ms, tot_fl, len(self.records), by
+
+    def shapes(self):
+        tab = {}
+        for n, e0, e1, f, key in self.records:
+            t, ff, c = tab.get(key, (0.0, 0.0, 0))
+            tab[key] = (t + e0.elapsed_time(e1), ff + f, c + 1)
+        rows = [{"shape": k, "calls": c, "ms": t, "tflops": ff / (t * 1e-3) / 1e12 if t > 0 else None}
+                for k, (t, ff, c) in tab.items()]
+        rows.sort(key=lambda r: -r["ms"])
+        return rows
 
 
 # --------------------------------------------------------------------------------------------------
@@ -305,6 +329,13 @@ def run_ours(args):
 
     for i in range(max(args.warmup, 3)):
         step_fn(clone(resident), i)
+    if args.ncu_step:
+        torch.cuda.synchronize()
+        torch.cuda.profiler.start()
+        step_fn(clone(resident), 0)
+        torch.cuda.synchronize()
+        torch.cuda.profiler.stop()
+        return
     launches0 = lib.call("launch_count")
     sampler = ClockSampler(local)
     if rank == 0:
@@ -321,6 +352,9 @@ def run_ours(args):
         step_fn(clone(resident), 0)
         prof.remove()
         eng_ms, counted, ncalls, by = prof.summary()
+        if args.shapes:
+            with open(args.shapes, "w") as f:
+                json.dump(prof.shapes(), f, indent=1)
         pk, how = peaks()
         peak = pk["bf16_tflops_sustained"]
         achieved = FLOPS_TRAIN_PER_IMG * B / (eng_ms * 1e-3) / 1e12

@@ -45,7 +45,7 @@ int odvae_conv2d_dgrad(const void* dy, const void* w_packed_dgrad, const void* d
 size_t odvae_conv2d_wgrad_workspace_bytes(int B, int H, int W, int CinP, int CoutP, int geom, int impl) {
   EngineDesc d;
   if (describe_conv_wgrad(d, nullptr, nullptr, nullptr, B, H, W, CinP, CoutP, geom, impl) != ODVAE_OK) return 0;
-  const size_t part = static_cast<size_t>(d.p.num_z) * CoutP * CinP * sizeof(float);
+  const size_t part = static_cast<size_t>(d.p.ntaps) * d.p.split_k * CoutP * CinP * sizeof(float);
   return part + colsum_workspace_bytes(CoutP) + 256;
 }
 
@@ -57,7 +57,7 @@ int odvae_conv2d_wgrad(const void* x, const void* dy, float* dw_oihw, float* db,
   float* ws = reinterpret_cast<float*>(workspace);
   int st = describe_conv_wgrad(d, x, dy, ws, B, H, W, CinP, CoutP, geom, impl);
   if (st != ODVAE_OK) return st;
-  const size_t part = static_cast<size_t>(d.p.num_z) * CoutP * CinP * sizeof(float);
+  const size_t part = static_cast<size_t>(d.p.ntaps) * d.p.split_k * CoutP * CinP * sizeof(float);
   if (ws_bytes < part + colsum_workspace_bytes(CoutP)) return ODVAE_ERR_WORKSPACE;
   st = run_engine(d, impl, act_dtype, s);
   if (st != ODVAE_OK) return st;
@@ -78,6 +78,22 @@ int odvae_gemm_bf16(const void* A, const void* B, void* D, int M, int N, int K, 
   int st = describe_gemm(d, A, B, D, M, N, K, batch, lda, ldb, ldd, strideA, strideB, strideD, a_mn, b_mn,
                          out_dtype == ODVAE_F32 ? OUT_F32 : OUT_BF16, alpha, bias, residual);
   if (st != ODVAE_OK) return st;
+  return run_engine(d, ODVAE_IMPL_TC, ODVAE_BF16, static_cast<cudaStream_t>(stream));
+}
+
+static int fmt_of(int dtype) { return dtype == ODVAE_F16 ? FMT_F16 : FMT_BF16; }
+
+int odvae_gemm_16(const void* A, const void* B, void* D, int M, int N, int K, int batch, int64_t lda, int64_t ldb,
+                  int64_t ldd, int64_t strideA, int64_t strideB, int64_t strideD, int a_mn, int b_mn, int a_dtype,
+                  int b_dtype, int out_dtype, float alpha, const float* bias, const void* residual, void* stream) {
+  if ((a_dtype != ODVAE_BF16 && a_dtype != ODVAE_F16) || a_dtype != b_dtype) return ODVAE_ERR_SHAPE;
+  EngineDesc d;
+  const int om = out_dtype == ODVAE_F32 ? OUT_F32 : (out_dtype == ODVAE_F16 ? OUT_F16 : OUT_BF16);
+  int st = describe_gemm(d, A, B, D, M, N, K, batch, lda, ldb, ldd, strideA, strideB, strideD, a_mn, b_mn, om, alpha,
+                         bias, residual);
+  if (st != ODVAE_OK) return st;
+  d.p.a_fmt = fmt_of(a_dtype);
+  d.p.b_fmt = fmt_of(b_dtype);
   return run_engine(d, ODVAE_IMPL_TC, ODVAE_BF16, static_cast<cudaStream_t>(stream));
 }
 

@@ -1,6 +1,7 @@
 // Shared helpers for the odvae_b200 CUDA library.
 #pragma once
 #include <cuda_bf16.h>
+#include <cuda_fp16.h>
 #include <cuda_runtime.h>
 #include <stdint.h>
 
@@ -23,11 +24,16 @@ unsigned long long launch_count();
   } while (0)
 
 typedef __nv_bfloat16 bf16;
+typedef __half f16;
 
 template <typename T> __device__ __forceinline__ float to_f32(T v);
 template <> __device__ __forceinline__ float to_f32<float>(float v) { return v; }
 template <> __device__ __forceinline__ float to_f32<bf16>(bf16 v) { return __bfloat162float(v); }
+template <> __device__ __forceinline__ float to_f32<f16>(f16 v) { return __half2float(v); }
 template <typename T> __device__ __forceinline__ T from_f32(float v);
+// fp16 stores saturate (|v| > 65504 -> +-65504) instead of producing inf
+__device__ __forceinline__ float sat_f16(float v) { return fminf(fmaxf(v, -65504.0f), 65504.0f); }
+template <> __device__ __forceinline__ f16 from_f32<f16>(float v) { return __float2half_rn(sat_f16(v)); }
 template <> __device__ __forceinline__ float from_f32<float>(float v) { return v; }
 template <> __device__ __forceinline__ bf16 from_f32<bf16>(float v) { return __float2bfloat16_rn(v); }
 
@@ -38,6 +44,21 @@ __device__ __forceinline__ uint32_t pack_bf16x2(float lo, float hi) {
 __device__ __forceinline__ float2 unpack_bf16x2(uint32_t v) {
   __nv_bfloat162 h = *reinterpret_cast<__nv_bfloat162*>(&v);
   return __bfloat1622float2(h);
+}
+__device__ __forceinline__ uint32_t pack_f16x2(float lo, float hi) {
+  __half2 h = __floats2half2_rn(sat_f16(lo), sat_f16(hi));
+  return *reinterpret_cast<uint32_t*>(&h);
+}
+__device__ __forceinline__ float2 unpack_f16x2(uint32_t v) {
+  __half2 h = *reinterpret_cast<__half2*>(&v);
+  return __half22float2(h);
+}
+// runtime-selected 16-bit packing (engine epilogues): half = true -> IEEE fp16, else bf16
+__device__ __forceinline__ uint32_t pack_16x2(float lo, float hi, bool half) {
+  return half ? pack_f16x2(lo, hi) : pack_bf16x2(lo, hi);
+}
+__device__ __forceinline__ float2 unpack_16x2(uint32_t v, bool half) {
+  return half ? unpack_f16x2(v) : unpack_bf16x2(v);
 }
 
 __device__ __forceinline__ float warp_sum(float v) {

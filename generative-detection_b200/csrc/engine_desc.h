@@ -5,10 +5,12 @@
 namespace odvae {
 
 enum { KIND_GEMM = 0, KIND_CONV = 1, KIND_WGRAD = 2 };
-enum { OUT_BF16 = 0, OUT_F32 = 1, OUT_NCHW_F32 = 2 };
+enum { OUT_BF16 = 0, OUT_F32 = 1, OUT_NCHW_F32 = 2, OUT_F16 = 3 };
+enum { FMT_F16 = 0, FMT_BF16 = 1 };  // tcgen05 kind::f16 operand format codes
 
 struct TcParams {
   int kind, a_mn, b_mn, BN, stages;
+  int a_fmt, b_fmt;  // FMT_* of the A / B operands
   int num_m_tiles, num_n_tiles, num_z;  // z: GEMM batch | CONV 1 | WGRAD ntaps*split_k
   int num_k_iters;
   // spatial operand (CONV: A, WGRAD: B): coords (c, x, [ph], y, b)
@@ -18,6 +20,7 @@ struct TcParams {
   int bw_log2, tiles_x, tiles_y;
   // WGRAD k-chunk geometry (box kbw x kbh = 64 output pixels)
   int kbw_log2, kch_x, kch_y, split_k, kch_per_split;
+  int wg_T, kch_total;  // taps accumulated per tile (1 or 3 = one filter row); pixel chunks over all splits
   // epilogue
   int out_mode, n_valid, m_valid, out_h, out_w;
   long long ldd, strideD, oB, oY, oX, o0;

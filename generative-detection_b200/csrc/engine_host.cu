@@ -73,11 +73,12 @@ static int ilog2(int v) {
   return l;
 }
 
+// BN here = B-operand rows per stage (WGRAD tap groups: wg_T * BN)
 static size_t tc_smem_bytes(int stages, int BN) {
   return static_cast<size_t>(stages) * (TC_A_BYTES + static_cast<size_t>(BN) * 128) + (2 * stages + 4) * 8 + 16 + 1024;
 }
 static int tc_pick_stages(int BN, int num_k_iters) {
-  const size_t budget = 200 * 1024;
+  const size_t budget = 224 * 1024;
   int s = static_cast<int>((budget - 2048) / (TC_A_BYTES + static_cast<size_t>(BN) * 128));
   if (s > 8) s = 8;
   if (s > num_k_iters) s = num_k_iters;
@@ -93,8 +94,9 @@ static int launch_tc(EngineDesc& d, cudaStream_t stream) {
   st = make_tmap_bf16(&tmB, d.B, d.boxB);
   if (st != ODVAE_OK) return st;
   TcParams& p = d.p;
-  p.stages = tc_pick_stages(p.BN, p.num_k_iters);
-  const size_t smem = tc_smem_bytes(p.stages, p.BN);
+  const int b_rows = p.kind == KIND_WGRAD ? p.BN * p.wg_T : p.BN;
+  p.stages = tc_pick_stages(b_rows, p.num_k_iters);
+  const size_t smem = tc_smem_bytes(p.stages, b_rows);
   static std::once_flag once;
   static cudaError_t attr_err = cudaSuccess;
   std::call_once(once, [] {
@@ -171,7 +173,7 @@ int describe_gemm(EngineDesc& d, const void* A, const void* B, void* D, int M, i
   d.tc_ok = 1;
   if (lda % 8 || ldb % 8) d.tc_ok = 0;
   if (batch > 1 && (strideA % 8 || strideB % 8)) d.tc_ok = 0;
-  if (out_mode == OUT_BF16 && (ldd % 8 != 0 || strideD % 8 != 0)) d.tc_ok = 0;
+  if ((out_mode == OUT_BF16 || out_mode == OUT_F16) && (ldd % 8 != 0 || strideD % 8 != 0)) d.tc_ok = 0;
   if (out_mode == OUT_F32 && (ldd % 4 != 0 || strideD % 4 != 0)) d.tc_ok = 0;
   const long long bsA = batch > 1 ? strideA : lda * (a_mn ? K : M);
   const long long bsB = batch > 1 ? strideB : ldb * (b_mn ? K : N);
@@ -206,6 +208,7 @@ int describe_gemm(EngineDesc& d, const void* A, const void* B, void* D, int M, i
     d.boxB[0] = 64; d.boxB[1] = 64; d.boxB[2] = 1;
   }
   p.kind = KIND_GEMM;
+  p.a_fmt = p.b_fmt = FMT_BF16;
   p.a_mn = a_mn;
   p.b_mn = b_mn;
   p.BN = BN;
@@ -303,6 +306,7 @@ static void conv_common(EngineDesc& d, int Bn, int Ho, int Wo, int gatherC, int 
   const int BN = pick_bn(N);
   d.tc_ok = geo && gatherC % 64 == 0 && BN != 0;
   p.kind = KIND_CONV;
+  p.a_fmt = p.b_fmt = FMT_BF16;
   p.BN = BN ? BN : 16;
   p.cchunks = gatherC / 64;
   p.num_k_iters = p.ntaps * p.cchunks;
@@ -433,6 +437,7 @@ int describe_conv_wgrad(EngineDesc& d, const void* x, const void* dy, float* ws,
   d = EngineDesc{};
   TcParams& p = d.p;
   p.kind = KIND_WGRAD;
+  p.a_fmt = p.b_fmt = FMT_BF16;
   p.a_mn = 1;
   p.b_mn = 1;
   fill_taps_fwd(p, geom, CinP);
@@ -443,20 +448,31 @@ int describe_conv_wgrad(EngineDesc& d, const void* x, const void* dy, float* ws,
     view4(d.B, x, B, H, W, CinP);
   int kbw = 0, kbh = 0;
   const bool geo = tile_geometry(Ho, Wo, 64, &kbw, &kbh);
-  const int BN = CinP % 256 == 0 ? 256 : (CinP % 128 == 0 ? 128 : 64);
   const long long kpix = static_cast<long long>(B) * Ho * Wo;
   d.tc_ok = geo && CinP % 64 == 0 && CoutP % 8 == 0 && kpix % 64 == 0;
+  const bool tc = impl == ODVAE_IMPL_TC && d.tc_ok;
+  // tcgen05: a tile accumulates one whole filter row (3 taps) so that the dy tile is fetched once per 3 taps and
+  // the MMAs run N = 256 + 128 wide; 1x1 convs keep one tap with the widest BN that divides CinP.
+  const int T = (tc && p.ntaps == 9) ? 3 : 1;
+  int BN = CinP % 256 == 0 ? 256 : (CinP % 128 == 0 ? 128 : 64);
+  if (T == 3 && BN > 128) BN = 128;
   p.BN = BN;
-  const long long base_tiles = static_cast<long long>(p.ntaps) * ((CoutP + 127) / 128) * ((CinP + BN - 1) / BN);
+  p.wg_T = T;
+  const long long base_tiles = static_cast<long long>(p.ntaps / T) * ((CoutP + 127) / 128) * ((CinP + BN - 1) / BN);
   int split = 1;
-  if (impl == ODVAE_IMPL_TC && d.tc_ok) {
+  if (tc) {
     const long long kch = kpix / 64;
-    const int target = 2 * num_sms();
-    while (base_tiles * split < target && kch % (2 * split) == 0 && kch / (2 * split) >= 16) split *= 2;
+    // one wave of tiles over the SMs; at least 8 pixel chunks per tile; uneven split (last split = remainder)
+    long long want = num_sms() / base_tiles;
+    if (want > kch / 8) want = kch / 8;
+    if (want < 1) want = 1;
+    const long long kps = (kch + want - 1) / want;
+    split = static_cast<int>((kch + kps - 1) / kps);
     p.kbw_log2 = ilog2(kbw);
     p.kch_x = Wo / kbw;
     p.kch_y = Ho / kbh;
-    p.kch_per_split = static_cast<int>(kch / split);
+    p.kch_per_split = static_cast<int>(kps);
+    p.kch_total = static_cast<int>(kch);
     p.num_k_iters = p.kch_per_split;
     spatial_box(d.boxA, 4, kbw, kbh);
     spatial_box(d.boxB, p.sp_rank, kbw, kbh);
@@ -468,7 +484,7 @@ int describe_conv_wgrad(EngineDesc& d, const void* x, const void* dy, float* ws,
   p.split_k = split;
   p.num_m_tiles = (CoutP + 127) / 128;
   p.num_n_tiles = (CinP + BN - 1) / BN;
-  p.num_z = p.ntaps * split;
+  p.num_z = (p.ntaps / T) * split;
   p.out_mode = OUT_F32;
   p.n_valid = CinP;
   p.m_valid = CoutP;

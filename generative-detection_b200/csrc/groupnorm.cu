@@ -152,43 +152,43 @@ __global__ void gn_stats_finalize_kernel(const float* __restrict__ part, float* 
 }
 
 // y = [silu]((x - mean) * rstd * gamma + beta)
+// The grid-stride (gridDim.x * GN_THREADS vectors) is a multiple of C/V, so every thread keeps ONE channel vector for
+// the whole loop: scale/shift live in registers and the loop body is load -> fma (+SiLU) -> store.
 template <typename T>
 __global__ void __launch_bounds__(GN_THREADS)
 gn_apply_kernel(const T* __restrict__ x, const float* __restrict__ stats, const float* __restrict__ gamma,
                 const float* __restrict__ beta, T* __restrict__ y, int HW, int C, int G, int silu) {
   constexpr int V = VecN<T>::V;
-  extern __shared__ float sm[];
-  float* scale = sm;
-  float* shift = sm + C;
   const int b = blockIdx.y;
   const int cpg = C / G;
-  for (int c = threadIdx.x; c < C; c += GN_THREADS) {
+  const int cv = C / V;
+  long long i = blockIdx.x * static_cast<long long>(GN_THREADS) + threadIdx.x;
+  const int c0 = static_cast<int>(i % cv) * V;
+  float scale[V], shift[V];
+#pragma unroll
+  for (int j = 0; j < V; ++j) {
+    const int c = c0 + j;
     const int g = c / cpg;
     const float mean = __ldg(stats + (static_cast<long long>(b) * G + g) * 2);
     const float rstd = __ldg(stats + (static_cast<long long>(b) * G + g) * 2 + 1);
-    const float sc = rstd * __ldg(gamma + c);
-    scale[c] = sc;
-    shift[c] = __ldg(beta + c) - mean * sc;
+    scale[j] = rstd * __ldg(gamma + c);
+    shift[j] = __ldg(beta + c) - mean * scale[j];
   }
-  __syncthreads();
-  const int cv = C / V;
   const long long nvec = static_cast<long long>(HW) * cv;
   const uint4* xb = reinterpret_cast<const uint4*>(x + static_cast<long long>(b) * HW * C);
   uint4* yb = reinterpret_cast<uint4*>(y + static_cast<long long>(b) * HW * C);
   const long long stride = static_cast<long long>(gridDim.x) * GN_THREADS;
   constexpr int U = 4;
-  long long i = blockIdx.x * static_cast<long long>(GN_THREADS) + threadIdx.x;
   for (; i + (U - 1) * stride < nvec; i += U * stride) {
     T xv[U][V];
 #pragma unroll
     for (int u = 0; u < U; ++u) *reinterpret_cast<uint4*>(xv[u]) = __ldg(xb + i + u * stride);
 #pragma unroll
     for (int u = 0; u < U; ++u) {
-      const int c0 = static_cast<int>((i + u * stride) % cv) * V;
       T yv[V];
 #pragma unroll
       for (int j = 0; j < V; ++j) {
-        float v = fmaf(to_f32<T>(xv[u][j]), scale[c0 + j], shift[c0 + j]);
+        float v = fmaf(to_f32<T>(xv[u][j]), scale[j], shift[j]);
         if (silu) v = silu_f(v);
         yv[j] = from_f32<T>(v);
       }
@@ -196,12 +196,11 @@ gn_apply_kernel(const T* __restrict__ x, const float* __restrict__ stats, const 
     }
   }
   for (; i < nvec; i += stride) {
-    const int c0 = static_cast<int>(i % cv) * V;
     T xv[V], yv[V];
     *reinterpret_cast<uint4*>(xv) = __ldg(xb + i);
 #pragma unroll
     for (int j = 0; j < V; ++j) {
-      float v = fmaf(to_f32<T>(xv[j]), scale[c0 + j], shift[c0 + j]);
+      float v = fmaf(to_f32<T>(xv[j]), scale[j], shift[j]);
       if (silu) v = silu_f(v);
       yv[j] = from_f32<T>(v);
     }
@@ -259,31 +258,30 @@ __global__ void gn_bwd_finalize_b_kernel(const float* __restrict__ AB, float* __
   dgamma[c] = accumulate ? dgamma[c] + bb : bb;
 }
 
+// dx = c1 * dy' + c2 * x + c3 (+ dx_add); one channel vector per thread for the whole loop (see gn_apply_kernel)
 template <typename T>
 __global__ void __launch_bounds__(GN_THREADS)
 gn_bwd_apply_kernel(const T* __restrict__ x, const T* __restrict__ dy, const T* __restrict__ dx_add,
                     const float* __restrict__ stats, const float* __restrict__ gamma, const float* __restrict__ beta,
                     const float* __restrict__ coef, T* __restrict__ dx, int HW, int C, int G, int silu) {
   constexpr int V = VecN<T>::V;
-  extern __shared__ float sm[];
-  float* scale = sm;          // rstd*gamma  (= c1)
-  float* shift = sm + C;      // beta - mean*rstd*gamma
-  float* c2 = sm + 2 * C;
-  float* c3 = sm + 3 * C;
   const int b = blockIdx.y;
   const int cpg = C / G;
-  for (int c = threadIdx.x; c < C; c += GN_THREADS) {
+  const int cv = C / V;
+  long long i = blockIdx.x * static_cast<long long>(GN_THREADS) + threadIdx.x;
+  const int c0 = static_cast<int>(i % cv) * V;
+  float scale[V], shift[V], c2[V], c3[V];
+#pragma unroll
+  for (int j = 0; j < V; ++j) {
+    const int c = c0 + j;
     const int g = c / cpg;
     const float mean = __ldg(stats + (static_cast<long long>(b) * G + g) * 2);
     const float rstd = __ldg(stats + (static_cast<long long>(b) * G + g) * 2 + 1);
-    const float sc = rstd * __ldg(gamma + c);
-    scale[c] = sc;
-    shift[c] = __ldg(beta + c) - mean * sc;
-    c2[c] = __ldg(coef + (static_cast<long long>(b) * G + g) * 2);
-    c3[c] = __ldg(coef + (static_cast<long long>(b) * G + g) * 2 + 1);
+    scale[j] = rstd * __ldg(gamma + c);
+    shift[j] = __ldg(beta + c) - mean * scale[j];
+    c2[j] = __ldg(coef + (static_cast<long long>(b) * G + g) * 2);
+    c3[j] = __ldg(coef + (static_cast<long long>(b) * G + g) * 2 + 1);
   }
-  __syncthreads();
-  const int cv = C / V;
   const long long nvec = static_cast<long long>(HW) * cv;
   const long long base = static_cast<long long>(b) * HW * C;
   const uint4* xb = reinterpret_cast<const uint4*>(x + base);
@@ -292,7 +290,6 @@ gn_bwd_apply_kernel(const T* __restrict__ x, const T* __restrict__ dy, const T* 
   uint4* dxb = reinterpret_cast<uint4*>(dx + base);
   const long long stride = static_cast<long long>(gridDim.x) * GN_THREADS;
   constexpr int U = 2;
-  long long i = blockIdx.x * static_cast<long long>(GN_THREADS) + threadIdx.x;
   for (; i < nvec; i += U * stride) {
     T xv[U][V], dv[U][V], av[U][V];
 #pragma unroll
@@ -308,14 +305,13 @@ gn_bwd_apply_kernel(const T* __restrict__ x, const T* __restrict__ dy, const T* 
     for (int u = 0; u < U; ++u) {
       const long long k = i + u * stride;
       if (k < nvec) {
-        const int c0 = static_cast<int>(k % cv) * V;
         T ov[V];
 #pragma unroll
         for (int j = 0; j < V; ++j) {
           const float xf = to_f32<T>(xv[u][j]);
           float d = to_f32<T>(dv[u][j]);
-          if (silu) d *= silu_grad_f(fmaf(xf, scale[c0 + j], shift[c0 + j]));
-          float o = fmaf(scale[c0 + j], d, fmaf(c2[c0 + j], xf, c3[c0 + j]));
+          if (silu) d *= silu_grad_f(fmaf(xf, scale[j], shift[j]));
+          float o = fmaf(scale[j], d, fmaf(c2[j], xf, c3[j]));
           if (ab) o += to_f32<T>(av[u][j]);
           ov[j] = from_f32<T>(o);
         }
@@ -387,7 +383,7 @@ int odvae_groupnorm_apply(const void* x, const float* stats, const float* gamma,
   const int V = act_dtype == ODVAE_BF16 ? 8 : 4;
   if (!gn_shape_ok(C, G, V)) return ODVAE_ERR_SHAPE;
   dim3 grid(gn_apply_blocks(B, HW, C, V), B);
-  const size_t smem = static_cast<size_t>(2) * C * sizeof(float);
+  const size_t smem = 0;
   if (act_dtype == ODVAE_BF16)
     gn_apply_kernel<bf16><<<grid, GN_THREADS, smem, st>>>(reinterpret_cast<const bf16*>(x), stats, gamma, beta, reinterpret_cast<bf16*>(y), HW, C, G, silu);
   else
@@ -422,7 +418,7 @@ int odvae_groupnorm_bwd(const void* x, const float* stats, const float* gamma, c
   s = check_launch("gn_bwd_finalize_b_kernel");
   if (s != ODVAE_OK) return s;
   dim3 grid2(gn_apply_blocks(B, HW, C, V), B);
-  const size_t smem2 = static_cast<size_t>(4) * C * sizeof(float);
+  const size_t smem2 = 0;
   if (act_dtype == ODVAE_BF16)
     gn_bwd_apply_kernel<bf16><<<grid2, GN_THREADS, smem2, st>>>(reinterpret_cast<const bf16*>(x), reinterpret_cast<const bf16*>(dy), reinterpret_cast<const bf16*>(dx_add), stats, gamma, beta, coef, reinterpret_cast<bf16*>(dx), HW, C, G, silu);
   else

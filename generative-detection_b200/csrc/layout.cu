@@ -185,8 +185,15 @@ __global__ void wgrad_reduce_kernel(const float* __restrict__ ws, float* __restr
     const int tap = static_cast<int>(q % taps);
     const int co = static_cast<int>(q / taps);
     float acc = 0.0f;
-    for (int s = 0; s < split_k; ++s)
-      acc += __ldg(ws + ((static_cast<long long>(tap) * split_k + s) * CoutP + co) * CinP + ci);
+    const float* src = ws + (static_cast<long long>(tap) * split_k * CoutP + co) * CinP + ci;
+    const long long sstride = static_cast<long long>(CoutP) * CinP;
+    int s = 0;
+    for (; s + 3 < split_k; s += 4) {  // four independent loads in flight, added in split order
+      const float a0 = __ldg(src + s * sstride), a1 = __ldg(src + (s + 1) * sstride);
+      const float a2 = __ldg(src + (s + 2) * sstride), a3 = __ldg(src + (s + 3) * sstride);
+      acc += a0; acc += a1; acc += a2; acc += a3;
+    }
+    for (; s < split_k; ++s) acc += __ldg(src + s * sstride);
     float* d = dw + (static_cast<long long>(co) * Cin + ci) * taps + tap;
     *d = accumulate ? (*d + acc) : acc;
   }
@@ -262,13 +269,31 @@ __global__ void __launch_bounds__(256) colsum_stage1_vec(const T* __restrict__ m
     part[static_cast<long long>(blockIdx.x) * cols + c] = t;
   }
 }
+// blockDim = (32, 8): x over columns, y over 8 row lanes of the partial list; lanes are combined in a fixed order
 __global__ void colsum_stage2(const float* __restrict__ part, int nblk, int cols, float* __restrict__ out,
                               int accumulate) {
-  const int c = blockIdx.x * blockDim.x + threadIdx.x;
-  if (c >= cols) return;
+  const int c = blockIdx.x * 32 + threadIdx.x;
+  __shared__ float sm[8][33];
   float t = 0.0f;
-  for (int i = 0; i < nblk; ++i) t += part[static_cast<long long>(i) * cols + c];
-  out[c] = accumulate ? out[c] + t : t;
+  if (c < cols) {
+    int i = threadIdx.y;
+    for (; i + 24 < nblk; i += 32) {  // four independent loads in flight, added in index order
+      const float a0 = __ldg(part + static_cast<long long>(i) * cols + c);
+      const float a1 = __ldg(part + static_cast<long long>(i + 8) * cols + c);
+      const float a2 = __ldg(part + static_cast<long long>(i + 16) * cols + c);
+      const float a3 = __ldg(part + static_cast<long long>(i + 24) * cols + c);
+      t += a0; t += a1; t += a2; t += a3;
+    }
+    for (; i < nblk; i += 8) t += __ldg(part + static_cast<long long>(i) * cols + c);
+  }
+  sm[threadIdx.y][threadIdx.x] = t;
+  __syncthreads();
+  if (threadIdx.y == 0 && c < cols) {
+    float r = 0.0f;
+#pragma unroll
+    for (int j = 0; j < 8; ++j) r += sm[j][threadIdx.x];
+    out[c] = accumulate ? out[c] + r : r;
+  }
 }
 
 // ---------------------------------------------------------------------------------------------
@@ -379,7 +404,7 @@ int launch_colsum(const void* m, long long rows, int cols, int ld, int act_dtype
   }
   int s = check_launch("colsum_stage1");
   if (s != ODVAE_OK) return s;
-  colsum_stage2<<<(cols + 127) / 128, 128, 0, st>>>(part, nblk, cols, out, accumulate);
+  colsum_stage2<<<(cols + 31) / 32, dim3(32, 8), 0, st>>>(part, nblk, cols, out, accumulate);
   return check_launch("colsum_stage2");
 }
 

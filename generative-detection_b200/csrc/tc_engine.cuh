@@ -38,10 +38,18 @@ __device__ __forceinline__ TileCoord decode_tile(const TcParams& p, int t) {
     c.x0 = tx * bw;
     c.y0 = ty * (TC_BLOCK_M >> p.bw_log2);
   } else if (p.kind == KIND_WGRAD) {
-    c.tap = c.z / p.split_k;
-    c.split = c.z - c.tap * p.split_k;
+    const int grp = c.z / p.split_k;
+    c.split = c.z - grp * p.split_k;
+    c.tap = grp * p.wg_T;  // first tap of this tile's tap group
   }
   return c;
+}
+
+// k-iterations of one tile: WGRAD splits its pixel chunks unevenly (the last split takes the remainder)
+__device__ __forceinline__ int tile_k_iters(const TcParams& p, const TileCoord& c) {
+  if (p.kind != KIND_WGRAD) return p.num_k_iters;
+  const int rem = p.kch_total - c.split * p.kch_per_split;
+  return rem < p.kch_per_split ? rem : p.kch_per_split;
 }
 
 __device__ __forceinline__ void spatial_load(void* dst, const CUtensorMap* tm, uint64_t* bar, int rank, int c,
@@ -60,7 +68,10 @@ tc_engine_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant_
   uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~uintptr_t(1023));
   const int stages = p.stages;
   const int BN = p.BN;
-  const uint32_t b_bytes = static_cast<uint32_t>(BN) * 128u;
+  const int wgT = p.kind == KIND_WGRAD ? p.wg_T : 1;
+  const uint32_t b_bytes = static_cast<uint32_t>(BN) * 128u * static_cast<uint32_t>(wgT);  // per stage
+  const int acc_cols = BN * wgT;                      // TMEM columns of one accumulator
+  const int num_acc = 2 * acc_cols <= TC_TMEM_COLS ? 2 : 1;
   uint8_t* sA = smem;
   uint8_t* sB = smem + static_cast<size_t>(stages) * TC_A_BYTES;
   uint64_t* bars = reinterpret_cast<uint64_t*>(sB + static_cast<size_t>(stages) * b_bytes);
@@ -107,7 +118,8 @@ tc_engine_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant_
         const TileCoord tc = decode_tile(p, t);
         const int m0 = tc.m_tile * TC_BLOCK_M;
         const int n0 = tc.n_tile * BN;
-        for (int kit = 0; kit < p.num_k_iters; ++kit) {
+        const int nk = tile_k_iters(p, tc);
+        for (int kit = 0; kit < nk; ++kit) {
           mbar_wait(&empty_bar[stage], phase ^ 1u);
           uint64_t* fb = &full_bar[stage];
           mbar_arrive_expect_tx(fb, TC_A_BYTES + b_bytes);
@@ -142,9 +154,13 @@ tc_engine_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant_
             const int y0 = cy * (TC_BLOCK_K >> p.kbw_log2);
             tma_load_4d(a_dst, &tmA, fb, m0, x0, y0, b);
             tma_load_4d(a_dst + 8192, &tmA, fb, m0 + 64, x0, y0, b);
-            for (int j = 0; j < (BN >> 6); ++j)
-              spatial_load(b_dst + j * 8192, &tmB, fb, p.sp_rank, n0 + 64 * j + p.tap_c[tc.tap],
-                           x0 + p.tap_dx[tc.tap], p.tap_ph[tc.tap], y0 + p.tap_dy[tc.tap], b);
+            // wg_T tap tiles back to back: [tap][BN/64 chunks of 64 channels x 64 pixels]
+            for (int tt = 0; tt < wgT; ++tt) {
+              const int tap = tc.tap + tt;
+              for (int j = 0; j < (BN >> 6); ++j)
+                spatial_load(b_dst + (tt * (BN >> 6) + j) * 8192, &tmB, fb, p.sp_rank, n0 + 64 * j + p.tap_c[tap],
+                             x0 + p.tap_dx[tap], p.tap_ph[tap], y0 + p.tap_dy[tap], b);
+            }
           }
           if (++stage == stages) {
             stage = 0;
@@ -157,7 +173,11 @@ tc_engine_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant_
   } else if (warp == 1) {
     // ============================ MMA issuer ============================
     if (lane == 0) {
-      const uint32_t idesc = make_idesc_bf16(TC_BLOCK_M, static_cast<uint32_t>(BN), p.a_mn, p.b_mn);
+      // one accumulator = acc_cols columns, written by MMAs of N <= 256 over consecutive 64-wide B chunks
+      const int n_first = acc_cols > 256 ? 256 : acc_cols;
+      const int n_rest = acc_cols - n_first;
+      const uint32_t idesc = make_idesc_16(TC_BLOCK_M, static_cast<uint32_t>(n_first), p.a_mn, p.b_mn, p.a_fmt, p.b_fmt);
+      const uint32_t idesc2 = make_idesc_16(TC_BLOCK_M, static_cast<uint32_t>(n_rest > 0 ? n_rest : 16), p.a_mn, p.b_mn, p.a_fmt, p.b_fmt);
       int stage = 0;
       uint32_t phase = 0;
       int acc = 0;
@@ -165,8 +185,10 @@ tc_engine_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant_
       for (int t = blockIdx.x; t < total_tiles; t += gridDim.x) {
         mbar_wait(&tempty_bar[acc], acc_phase ^ 1u);
         tc_fence_after();
-        const uint32_t d_tmem = tmem_base + static_cast<uint32_t>(acc * BN);
-        for (int kit = 0; kit < p.num_k_iters; ++kit) {
+        const uint32_t d_tmem = tmem_base + static_cast<uint32_t>(acc * acc_cols);
+        const TileCoord tcm = decode_tile(p, t);
+        const int nk = tile_k_iters(p, tcm);
+        for (int kit = 0; kit < nk; ++kit) {
           mbar_wait(&full_bar[stage], phase);
           tc_fence_after();
           const uint32_t a_base = smem_u32(sA + static_cast<size_t>(stage) * TC_A_BYTES);
@@ -178,6 +200,10 @@ tc_engine_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant_
             const uint64_t bdesc = p.b_mn ? make_smem_desc_sw128(b_base + k * 2048, 8192, 1024)
                                           : make_smem_desc_sw128(b_base + k * 32, 0, 1024);
             umma_bf16(d_tmem, adesc, bdesc, idesc, (kit | k) != 0 ? 1u : 0u);
+            if (n_rest > 0) {  // WGRAD tap groups only (MN-major B): chunks 4.. of the stage
+              const uint64_t bdesc2 = make_smem_desc_sw128(b_base + 4 * 8192 + k * 2048, 8192, 1024);
+              umma_bf16(d_tmem + 256u, adesc, bdesc2, idesc2, (kit | k) != 0 ? 1u : 0u);
+            }
           }
           umma_commit(&empty_bar[stage]);  // frees this smem stage once the MMAs above retire
           if (++stage == stages) {
@@ -186,7 +212,7 @@ tc_engine_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant_
           }
         }
         umma_commit(&tfull_bar[acc]);  // accumulator complete -> epilogue
-        if (++acc == 2) {
+        if (++acc == num_acc) {
           acc = 0;
           acc_phase ^= 1u;
         }
@@ -219,14 +245,22 @@ tc_engine_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant_
                   static_cast<long long>(xx) * p.oX + p.o0 + n0;
       } else {
         row_ok = (m0 + r) < p.m_valid;
-        row_off = (static_cast<long long>(tc.z) * p.m_valid + (m0 + r)) * p.ldd + n0;
+        row_off = ((static_cast<long long>(tc.tap) * p.split_k + tc.split) * p.m_valid + (m0 + r)) * p.ldd + n0;
       }
-      const uint32_t t_row = tmem_base + (static_cast<uint32_t>(q * 32) << 16) + static_cast<uint32_t>(acc * BN);
+      const uint32_t t_row = tmem_base + (static_cast<uint32_t>(q * 32) << 16) + static_cast<uint32_t>(acc * acc_cols);
+      const long long row_off0 = row_off;
+      const long long tap_stride = static_cast<long long>(p.split_k) * p.m_valid * p.ldd;  // WGRAD: next tap's slab
 
-      for (int c = 0; c < BN; c += 16) {
+      for (int cc = 0; cc < acc_cols; cc += 16) {
         uint32_t v[16];
-        tmem_ld_x16(t_row + static_cast<uint32_t>(c), v);
+        tmem_ld_x16(t_row + static_cast<uint32_t>(cc), v);
         tmem_ld_wait();
+        int c = cc;  // column within this tap's BN-wide block
+        if (wgT > 1) {
+          const int tt = cc / BN;
+          c = cc - tt * BN;
+          row_off = row_off0 + tt * tap_stride;
+        }
         const int ncol = n0 + c;  // global column of v[0]
         if (row_ok && ncol < p.n_valid) {
           float f[16];
@@ -245,25 +279,26 @@ tc_engine_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant_
                 if (ncol + i < p.n_valid) f[i] += __ldg(p.bias + ncol + i);
             }
           }
-          if (p.out_mode == OUT_BF16) {
-            bf16* dst = reinterpret_cast<bf16*>(p.D) + row_off + c;
+          if (p.out_mode == OUT_BF16 || p.out_mode == OUT_F16) {
+            const bool half = p.out_mode == OUT_F16;  // 16-bit output (and residual) format
+            uint16_t* dst = reinterpret_cast<uint16_t*>(p.D) + row_off + c;
             if (full) {
               if (p.residual != nullptr) {
-                const uint4* rp = reinterpret_cast<const uint4*>(reinterpret_cast<const bf16*>(p.residual) + row_off + c);
+                const uint4* rp = reinterpret_cast<const uint4*>(reinterpret_cast<const uint16_t*>(p.residual) + row_off + c);
                 uint4 r0 = __ldg(rp), r1 = __ldg(rp + 1);
                 uint32_t rw[8] = {r0.x, r0.y, r0.z, r0.w, r1.x, r1.y, r1.z, r1.w};
 #pragma unroll
                 for (int i = 0; i < 8; ++i) {
-                  float2 rv = unpack_bf16x2(rw[i]);
+                  float2 rv = unpack_16x2(rw[i], half);
                   f[2 * i] += rv.x;
                   f[2 * i + 1] += rv.y;
                 }
               }
               uint4 o0, o1;
-              o0.x = pack_bf16x2(f[0], f[1]);   o0.y = pack_bf16x2(f[2], f[3]);
-              o0.z = pack_bf16x2(f[4], f[5]);   o0.w = pack_bf16x2(f[6], f[7]);
-              o1.x = pack_bf16x2(f[8], f[9]);   o1.y = pack_bf16x2(f[10], f[11]);
-              o1.z = pack_bf16x2(f[12], f[13]); o1.w = pack_bf16x2(f[14], f[15]);
+              o0.x = pack_16x2(f[0], f[1], half);   o0.y = pack_16x2(f[2], f[3], half);
+              o0.z = pack_16x2(f[4], f[5], half);   o0.w = pack_16x2(f[6], f[7], half);
+              o1.x = pack_16x2(f[8], f[9], half);   o1.y = pack_16x2(f[10], f[11], half);
+              o1.z = pack_16x2(f[12], f[13], half); o1.w = pack_16x2(f[14], f[15], half);
               reinterpret_cast<uint4*>(dst)[0] = o0;
               reinterpret_cast<uint4*>(dst)[1] = o1;
             } else {
@@ -271,8 +306,8 @@ tc_engine_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant_
                 if (ncol + i < p.n_valid) {
                   float val = f[i];
                   if (p.residual != nullptr)
-                    val += __bfloat162float(reinterpret_cast<const bf16*>(p.residual)[row_off + c + i]);
-                  dst[i] = __float2bfloat16_rn(val);
+                    val += unpack_16x2(reinterpret_cast<const uint16_t*>(p.residual)[row_off + c + i], half).x;
+                  dst[i] = static_cast<uint16_t>(pack_16x2(val, 0.0f, half) & 0xffffu);
                 }
             }
           } else if (p.out_mode == OUT_F32) {
@@ -309,7 +344,7 @@ tc_engine_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant_
       }
       tc_fence_before();
       mbar_arrive(&tempty_bar[acc]);
-      if (++acc == 2) {
+      if (++acc == num_acc) {
         acc = 0;
         acc_phase ^= 1u;
       }

@@ -14,7 +14,7 @@ REPO_ROOT = os.path.dirname(os.path.dirname(_HERE))
 HEADER = os.path.join(REPO_ROOT, "include", "odvae_b200.h")
 LIB_PATH = os.path.join(_HERE, "libodvae_b200.so")
 
-F32, BF16 = 0, 1
+F32, BF16, F16 = 0, 1, 2
 CONV_3x3_S1, CONV_1x1, CONV_3x3_S2 = 0, 1, 2
 IMPL_SIMT, IMPL_TC = 0, 1
 

@@ -35,6 +35,7 @@ extern "C" {
 
 #define ODVAE_F32 0
 #define ODVAE_BF16 1
+#define ODVAE_F16 2 /* IEEE half: forward activations / packed forward weights of the mixed 16-bit mode */
 
 /* conv geometry selectors (LD/ldm/modules/diffusionmodules/model.py) */
 #define ODVAE_CONV_3x3_S1 0  /* Conv2d(k=3,s=1,p=1): model.py:92-106,383-387,487-491,529-533 */
@@ -111,6 +112,14 @@ int odvae_upsample2x_bwd(const void* dy, void* dx, int B, int H, int W, int C, i
 int odvae_gemm_bf16(const void* A, const void* B, void* D, int M, int N, int K, int batch, int64_t lda,
                     int64_t ldb, int64_t ldd, int64_t strideA, int64_t strideB, int64_t strideD, int a_mn,
                     int b_mn, int out_dtype, float alpha, const float* bias, const void* residual, void* stream);
+
+/* Same contraction with the operand format chosen by the caller: a_dtype == b_dtype in {ODVAE_BF16, ODVAE_F16}
+ * (measured on B200: tcgen05.mma kind::f16 with DIFFERENT A and B formats raises an illegal-instruction trap, so a
+ * mixed pair returns ODVAE_ERR_SHAPE); out_dtype in {ODVAE_F32, ODVAE_BF16, ODVAE_F16} is independent of the
+ * operand format; residual (if any) has the output dtype. */
+int odvae_gemm_16(const void* A, const void* B, void* D, int M, int N, int K, int batch, int64_t lda, int64_t ldb,
+                  int64_t ldd, int64_t strideA, int64_t strideB, int64_t strideD, int a_mn, int b_mn, int a_dtype,
+                  int b_dtype, int out_dtype, float alpha, const float* bias, const void* residual, void* stream);
 
 /* ---------------------------------------------------------------------------------------------
  * GroupNorm(32, C, eps=1e-6, affine) [+ SiLU]  (Normalize model.py:38-39, nonlinearity :33-35)

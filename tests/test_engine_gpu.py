@@ -150,3 +150,43 @@ def test_gemm_tc_strided_views():
     O = K.gemm(P, v, N, C, N, batch=Bn, ldb=3 * C, strideA=N * N, strideB=N * 3 * C, b_mn=True)
     torch.cuda.synchronize()
     assert rel_err(O, torch.bmm(P.float(), v.float())) < 1e-2
+
+
+# ------------------------------------------------------------------------------------------------
+# fp16 / bf16 operand formats with independent output formats through odvae_gemm_16. A and B must share one format:
+# on B200 a tcgen05.mma kind::f16 with different A/B formats traps (illegal instruction, measured in round 1), so the
+# C ABI rejects that pair up front.
+# ------------------------------------------------------------------------------------------------
+from odvae_b200.lib import BF16, F16, F32, call  # noqa: E402
+
+_CODE = {torch.bfloat16: BF16, torch.float16: F16, torch.float32: F32}
+
+
+@pytest.mark.parametrize("a_dt,b_dt,o_dt", [
+    (torch.float16, torch.float16, torch.float16),
+    (torch.float16, torch.float16, torch.bfloat16),
+    (torch.float16, torch.float16, torch.float32),
+    (torch.bfloat16, torch.bfloat16, torch.float16),
+])
+@pytest.mark.parametrize("a_mn,b_mn", [(0, 0), (1, 1), (0, 1)])
+def test_gemm_mixed_16bit_formats(a_dt, b_dt, o_dt, a_mn, b_mn):
+    torch.manual_seed(5)
+    M, N, K, batch = 256, 192, 320, 2
+    A = torch.randn(batch, K, M, device=DEV) if a_mn else torch.randn(batch, M, K, device=DEV)
+    Bm = torch.randn(batch, K, N, device=DEV) if b_mn else torch.randn(batch, N, K, device=DEV)
+    A, Bm = A.to(a_dt), Bm.to(b_dt)
+    D = torch.empty(batch, M, N, dtype=o_dt, device=DEV)
+    call("gemm_16", A, Bm, D, M, N, K, batch, M if a_mn else K, N if b_mn else K, N, M * K, N * K, M * N, a_mn, b_mn,
+         _CODE[a_dt], _CODE[b_dt], _CODE[o_dt], 0.5, None, None)
+    Af = A.float().transpose(1, 2) if a_mn else A.float()
+    Bf = Bm.float() if b_mn else Bm.float().transpose(1, 2)
+    ref = 0.5 * torch.bmm(Af, Bf)
+    assert rel_err(D, ref) < (1e-2 if o_dt == torch.bfloat16 else (2e-3 if o_dt == torch.float16 else 1e-5))
+
+
+def test_gemm_rejects_mixed_operand_formats():
+    A = torch.zeros(128, 64, dtype=torch.float16, device=DEV)
+    Bm = torch.zeros(128, 64, dtype=torch.bfloat16, device=DEV)
+    D = torch.empty(128, 128, dtype=torch.float32, device=DEV)
+    with pytest.raises(RuntimeError):
+        call("gemm_16", A, Bm, D, 128, 128, 64, 1, 64, 64, 128, 0, 0, 0, 0, 0, F16, BF16, F32, 1.0, None, None)

@@ -32,7 +32,7 @@ orig = dict(conv=O.conv, group_norm=O.group_norm, resnet_block=O.resnet_block, a
 def rnd(t, dt):
     return t if dt is None else t.to(dt).float()
 
-def run(act=None, wt=None, out=None, resid=None, gn=None, attn=None):
+def run(act=None, wt=None, out=None, resid=None, gn=None, attn=None, attn_all=None):
     """act: dtype conv inputs are rounded to; wt: weights; out: conv outputs; resid: block outputs; gn: GN+SiLU output"""
     def conv(sd_, pre, x_, stride=1, padding=0):
         w = rnd(sd_[pre + ".weight"], wt)
@@ -46,6 +46,19 @@ def run(act=None, wt=None, out=None, resid=None, gn=None, attn=None):
             x_ = F.conv2d(rnd(x_, act), rnd(sd_[pre + ".nin_shortcut.weight"], wt), sd_[pre + ".nin_shortcut.bias"])
         return rnd(x_ + h, resid)
     def attn_block(sd_, pre, x_):
+        if attn_all is not None:  # the whole block in one format (operands, weights, P, O); residual add in `resid`
+            a = attn_all
+            h = rnd(O.group_norm(sd_, pre + ".norm", x_), a)
+            cv = lambda n, t: rnd(F.conv2d(rnd(t, a), rnd(sd_[pre + n + ".weight"], a), sd_[pre + n + ".bias"]), a)
+            q, k, v = cv(".q", h), cv(".k", h), cv(".v", h)
+            b, c, hh, ww = q.shape
+            q = q.reshape(b, c, hh * ww).permute(0, 2, 1)
+            k = k.reshape(b, c, hh * ww)
+            w = rnd(torch.softmax(torch.bmm(q, k) * (int(c) ** (-0.5)), dim=2), a)
+            v = v.reshape(b, c, hh * ww)
+            h = rnd(torch.bmm(v, w.permute(0, 2, 1)).reshape(b, c, hh, ww), a)
+            y = F.conv2d(h, rnd(sd_[pre + ".proj_out.weight"], a), sd_[pre + ".proj_out.bias"])
+            return rnd(x_ + y, resid)
         h = rnd(O.group_norm(sd_, pre + ".norm", x_), gn)
         q, k, v = conv(sd_, pre + ".q", h), conv(sd_, pre + ".k", h), conv(sd_, pre + ".v", h)
         b, c, hh, ww = q.shape
@@ -78,6 +91,8 @@ cases = {
     "only residual bf16": dict(resid=bf),
     "only gn-out/act bf16": dict(act=bf, gn=bf),
     "only conv-out bf16": dict(out=bf),
+    "all fp16, attention blocks bf16": dict(act=hf, wt=hf, out=hf, resid=hf, gn=hf, attn=hf, attn_all=bf),
+    "all fp16, only P bf16": dict(act=hf, wt=hf, out=hf, resid=hf, gn=hf, attn=bf),
     "fp16 acts, bf16 weights": dict(act=hf, wt=bf, out=hf, resid=hf, gn=hf, attn=hf),
     "fp16 weights, bf16 acts": dict(act=bf, wt=hf, out=bf, resid=bf, gn=bf, attn=bf),
 }

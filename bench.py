@@ -185,7 +185,7 @@ def run_reference(args):
 class EngineProfiler:
     """Wraps ops.call for ONE extra (untimed) step: brackets each conv/GEMM C-ABI call with CUDA events on the
     launching stream and adds up the algorithmic FLOPs (2*M*N*K of the real, unpadded problem)."""
-    NAMES = {"conv2d_fwd", "conv2d_dgrad", "conv2d_wgrad", "gemm_bf16"}
+    NAMES = {"conv2d_fwd", "conv2d_dgrad", "conv2d_wgrad", "gemm_bf16", "attn_scores_softmax", "attn_dsoftmax"}
 
     def __init__(self):
         self.records = []
@@ -194,6 +194,10 @@ class EngineProfiler:
         if name == "gemm_bf16":
             M, N, K, batch = a[3], a[4], a[5], a[6]
             return 2.0 * M * N * K * batch
+        if name == "attn_scores_softmax":  # algorithmic: ONE q k^T (the second pass is a recompute, not counted)
+            return 2.0 * a[3] * a[4] * a[4] * a[5]
+        if name == "attn_dsoftmax":
+            return 2.0 * a[5] * a[6] * a[6] * a[7]
         if name == "conv2d_fwd":
             B, H, W, CinP, CoutP, Cout, geom = a[5], a[6], a[7], a[8], a[9], a[10], a[11]
             cin, cout = self._real(CinP), Cout
@@ -211,6 +215,10 @@ class EngineProfiler:
     def shape_key(name, a):
         if name == "gemm_bf16":
             return "gemm M%d N%d K%d b%d a_mn%d b_mn%d" % (a[3], a[4], a[5], a[6], a[13], a[14])
+        if name == "attn_scores_softmax":
+            return "attn qk^T+softmax (2 passes) B%d N%d C%d" % (a[3], a[4], a[5])
+        if name == "attn_dsoftmax":
+            return "attn dP+dsoftmax B%d N%d C%d" % (a[5], a[6], a[7])
         if name == "conv2d_fwd":
             return "fwd B%d %dx%d %d->%d g%d" % (a[5], a[6], a[7], a[8], a[9], a[11])
         if name == "conv2d_dgrad":

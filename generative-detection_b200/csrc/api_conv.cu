@@ -97,6 +97,57 @@ int odvae_gemm_16(const void* A, const void* B, void* D, int M, int N, int K, in
   return run_engine(d, ODVAE_IMPL_TC, ODVAE_BF16, static_cast<cudaStream_t>(stream));
 }
 
+// ---- fused attention core (tcgen05 only): scores + softmax in two GEMM passes, softmax backward in the dP GEMM ----
+static int attn_nt(int N) {
+  EngineDesc d;
+  if (describe_gemm(d, nullptr, nullptr, nullptr, N, N, 64, 1, 64, 64, N, 0, 0, 0, 0, 0, OUT_BF16, 1.0f, nullptr,
+                    nullptr) != ODVAE_OK)
+    return 0;
+  return d.p.num_n_tiles;
+}
+
+size_t odvae_attn_softmax_workspace_bytes(int B, int N) {
+  return static_cast<size_t>(B) * attn_nt(N) * N * 2 * sizeof(float) + 256;
+}
+
+int odvae_attn_scores_softmax(const void* q, const void* k, void* P, int B, int N, int C, int64_t ldq, int64_t ldk,
+                              int64_t strideq, int64_t stridek, float scale, int dtype, void* workspace,
+                              size_t ws_bytes, void* stream) {
+  if (dtype != ODVAE_BF16 && dtype != ODVAE_F16) return ODVAE_ERR_SHAPE;
+  if (ws_bytes < odvae_attn_softmax_workspace_bytes(B, N) - 256) return ODVAE_ERR_WORKSPACE;
+  cudaStream_t s = static_cast<cudaStream_t>(stream);
+  const int om = dtype == ODVAE_F16 ? OUT_F16 : OUT_BF16;
+  for (int pass = 0; pass < 2; ++pass) {
+    EngineDesc d;
+    int st = describe_gemm(d, q, k, P, N, N, C, B, ldq, ldk, N, strideq, stridek, static_cast<int64_t>(N) * N, 0, 0, om,
+                           scale, nullptr, nullptr);
+    if (st != ODVAE_OK) return st;
+    d.p.a_fmt = d.p.b_fmt = fmt_of(dtype);
+    d.p.epi = pass == 0 ? EPI_ROWSTATS : EPI_SOFTMAX;
+    d.p.aux_out = reinterpret_cast<float*>(workspace);
+    d.p.aux_f32 = reinterpret_cast<const float*>(workspace);
+    st = run_engine(d, ODVAE_IMPL_TC, ODVAE_BF16, s);
+    if (st != ODVAE_OK) return st;
+  }
+  return ODVAE_OK;
+}
+
+int odvae_attn_dsoftmax(const void* dO, const void* v, const void* P, const float* delta, void* dS, int B, int N,
+                        int C, int64_t ldo, int64_t ldv, int64_t strideo, int64_t stridev, float scale, int dtype,
+                        void* stream) {
+  if (dtype != ODVAE_BF16 && dtype != ODVAE_F16) return ODVAE_ERR_SHAPE;
+  EngineDesc d;
+  const int om = dtype == ODVAE_F16 ? OUT_F16 : OUT_BF16;
+  int st = describe_gemm(d, dO, v, dS, N, N, C, B, ldo, ldv, N, strideo, stridev, static_cast<int64_t>(N) * N, 0, 0, om,
+                         scale, nullptr, nullptr);
+  if (st != ODVAE_OK) return st;
+  d.p.a_fmt = d.p.b_fmt = fmt_of(dtype);
+  d.p.epi = EPI_DSOFTMAX;
+  d.p.aux_f32 = delta;
+  d.p.aux16 = P;
+  return run_engine(d, ODVAE_IMPL_TC, ODVAE_BF16, static_cast<cudaStream_t>(stream));
+}
+
 int odvae_gemm_simt(const void* A, const void* B, void* D, int M, int N, int K, int batch, int64_t lda, int64_t ldb,
                     int64_t ldd, int64_t strideA, int64_t strideB, int64_t strideD, int a_mn, int b_mn, int in_dtype,
                     int out_dtype, float alpha, const float* bias, const void* residual, void* stream) {

@@ -6,7 +6,9 @@ namespace odvae {
 
 enum { KIND_GEMM = 0, KIND_CONV = 1, KIND_WGRAD = 2 };
 enum { OUT_BF16 = 0, OUT_F32 = 1, OUT_NCHW_F32 = 2, OUT_F16 = 3 };
-enum { FMT_F16 = 0, FMT_BF16 = 1 };  // tcgen05 kind::f16 operand format codes
+enum { FMT_F16 = 0, FMT_BF16 = 1 };
+// fused attention epilogues of KIND_GEMM (see tc_engine.cuh): row statistics / softmax / softmax backward
+enum { EPI_NONE = 0, EPI_ROWSTATS = 1, EPI_SOFTMAX = 2, EPI_DSOFTMAX = 3 };  // tcgen05 kind::f16 operand format codes
 
 struct TcParams {
   int kind, a_mn, b_mn, BN, stages;
@@ -25,6 +27,10 @@ struct TcParams {
   int out_mode, n_valid, m_valid, out_h, out_w;
   long long ldd, strideD, oB, oY, oX, o0;
   float alpha;
+  int epi;               // EPI_*
+  const float* aux_f32;  // SOFTMAX: row partials [z][n_tile][M][2] (max, sum) in the log2 domain; DSOFTMAX: delta [z][M]
+  float* aux_out;        // ROWSTATS: row partials (same layout)
+  const void* aux16;     // DSOFTMAX: P, same layout / format as D
   const float* bias;
   const void* residual;
   void* D;

@@ -310,6 +310,35 @@ static int grid_1d(long long items, int threads, int per_sm = 8) {
 
 using namespace odvae;
 
+namespace odvae {
+// out[r] = sum_c a[r][c] * b[r][c]: one warp per row, 16-byte vectors, shuffle tree (fixed order)
+template <bool HALF>
+__global__ void __launch_bounds__(256) rowdot16_kernel(const uint16_t* __restrict__ a, const uint16_t* __restrict__ b,
+                                                       float* __restrict__ out, long long rows, int C, long long lda,
+                                                       long long ldb) {
+  const int lane = threadIdx.x & 31;
+  const long long warp = (blockIdx.x * static_cast<long long>(blockDim.x) + threadIdx.x) >> 5;
+  const long long nwarps = (static_cast<long long>(gridDim.x) * blockDim.x) >> 5;
+  for (long long r = warp; r < rows; r += nwarps) {
+    float acc = 0.0f;
+    for (int c = lane * 8; c < C; c += 256) {
+      const uint4 av = __ldg(reinterpret_cast<const uint4*>(a + r * lda + c));
+      const uint4 bv = __ldg(reinterpret_cast<const uint4*>(b + r * ldb + c));
+      const uint32_t aw[4] = {av.x, av.y, av.z, av.w}, bw[4] = {bv.x, bv.y, bv.z, bv.w};
+#pragma unroll
+      for (int i = 0; i < 4; ++i) {
+        const float2 x = unpack_16x2(aw[i], HALF), y = unpack_16x2(bw[i], HALF);
+        acc = fmaf(x.x, y.x, acc);
+        acc = fmaf(x.y, y.y, acc);
+      }
+    }
+    acc = warp_sum(acc);
+    if (lane == 0) out[r] = acc;
+  }
+}
+}  // namespace odvae
+
+
 extern "C" {
 
 int odvae_softmax_rows(const float* S, void* P, int64_t rows, int n, float scale, int act_dtype, void* stream) {
@@ -327,6 +356,23 @@ int odvae_softmax_rows(const float* S, void* P, int64_t rows, int n, float scale
     else softmax_rows_kernel<float, 256><<<grid, 256, 0, st>>>(S, reinterpret_cast<float*>(P), rows, n, scale);
   }
   return check_launch("softmax_rows_kernel");
+}
+
+int odvae_rowdot(const void* a, const void* b, float* out, int64_t rows, int C, int64_t lda, int64_t ldb, int dtype,
+                 void* stream) {
+  if ((dtype != ODVAE_BF16 && dtype != ODVAE_F16) || C % 8 || lda % 8 || ldb % 8) return ODVAE_ERR_SHAPE;
+  if (rows <= 0) return ODVAE_OK;
+  cudaStream_t st = static_cast<cudaStream_t>(stream);
+  long long blocks = (rows + 7) / 8;
+  const long long cap = 16ll * num_sms();
+  if (blocks > cap) blocks = cap;
+  const uint16_t* pa = reinterpret_cast<const uint16_t*>(a);
+  const uint16_t* pb = reinterpret_cast<const uint16_t*>(b);
+  if (dtype == ODVAE_F16)
+    rowdot16_kernel<true><<<static_cast<int>(blocks), 256, 0, st>>>(pa, pb, out, rows, C, lda, ldb);
+  else
+    rowdot16_kernel<false><<<static_cast<int>(blocks), 256, 0, st>>>(pa, pb, out, rows, C, lda, ldb);
+  return check_launch("rowdot16_kernel");
 }
 
 int odvae_softmax_rows_bwd(const float* dP, const void* P, void* dS, int64_t rows, int n, float scale, int act_dtype,

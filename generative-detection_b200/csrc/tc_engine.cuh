@@ -251,6 +251,98 @@ tc_engine_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant_
       const long long row_off0 = row_off;
       const long long tap_stride = static_cast<long long>(p.split_k) * p.m_valid * p.ldd;  // WGRAD: next tap's slab
 
+      if (p.epi != EPI_NONE) {
+        // ---- fused attention epilogues (KIND_GEMM, one accumulator row per thread) ----
+        const long long stat_row = static_cast<long long>(tc.z) * p.m_valid + (m0 + r);
+        const float s2 = p.alpha * 1.4426950408889634f;  // scores are handled in the log2 domain: exp(a*s) = 2^(s2*s)
+        if (p.epi == EPI_ROWSTATS) {
+          // online (max, sum 2^(v - max)) over this tile's BN columns -> partial [z][n_tile][row]
+          float mx = -INFINITY, l = 0.0f;
+          for (int cc = 0; cc < BN; cc += 16) {
+            uint32_t v[16];
+            tmem_ld_x16(t_row + static_cast<uint32_t>(cc), v);
+            tmem_ld_wait();
+            float f[16];
+            float cm = -INFINITY;
+#pragma unroll
+            for (int i = 0; i < 16; ++i) {
+              f[i] = (n0 + cc + i < p.n_valid) ? __uint_as_float(v[i]) * s2 : -INFINITY;
+              cm = fmaxf(cm, f[i]);
+            }
+            const float mn = fmaxf(mx, cm);
+            float acc_l = 0.0f;
+#pragma unroll
+            for (int i = 0; i < 16; ++i) acc_l += exp2f(f[i] - mn);
+            l = l * exp2f(mx - mn) + acc_l;
+            mx = mn;
+          }
+          if (row_ok) {
+            float2* dst = reinterpret_cast<float2*>(p.aux_out) +
+                          (static_cast<long long>(tc.z) * p.num_n_tiles + tc.n_tile) * p.m_valid + (m0 + r);
+            *dst = make_float2(mx, l);
+          }
+        } else if (p.epi == EPI_SOFTMAX) {
+          // combine the row's partials (fixed order), then P = 2^(s2*s - max) / sum
+          float mx = -INFINITY, l = 0.0f;
+          if (row_ok) {
+            const float2* src = reinterpret_cast<const float2*>(p.aux_f32) +
+                                static_cast<long long>(tc.z) * p.num_n_tiles * p.m_valid + (m0 + r);
+            for (int t2 = 0; t2 < p.num_n_tiles; ++t2) mx = fmaxf(mx, __ldg(src + static_cast<long long>(t2) * p.m_valid).x);
+            for (int t2 = 0; t2 < p.num_n_tiles; ++t2) {
+              const float2 pr = __ldg(src + static_cast<long long>(t2) * p.m_valid);
+              l += pr.y * exp2f(pr.x - mx);
+            }
+          }
+          const float inv_l = row_ok ? __fdividef(1.0f, l) : 0.0f;
+          const bool half = p.out_mode == OUT_F16;
+          for (int cc = 0; cc < BN; cc += 16) {
+            uint32_t v[16];
+            tmem_ld_x16(t_row + static_cast<uint32_t>(cc), v);
+            tmem_ld_wait();
+            if (row_ok && n0 + cc < p.n_valid) {
+              float f[16];
+#pragma unroll
+              for (int i = 0; i < 16; ++i) f[i] = exp2f(fmaf(__uint_as_float(v[i]), s2, -mx)) * inv_l;
+              uint16_t* dst = reinterpret_cast<uint16_t*>(p.D) + row_off + cc;
+              uint4 o0, o1;
+              o0.x = pack_16x2(f[0], f[1], half);   o0.y = pack_16x2(f[2], f[3], half);
+              o0.z = pack_16x2(f[4], f[5], half);   o0.w = pack_16x2(f[6], f[7], half);
+              o1.x = pack_16x2(f[8], f[9], half);   o1.y = pack_16x2(f[10], f[11], half);
+              o1.z = pack_16x2(f[12], f[13], half); o1.w = pack_16x2(f[14], f[15], half);
+              reinterpret_cast<uint4*>(dst)[0] = o0;
+              reinterpret_cast<uint4*>(dst)[1] = o1;
+            }
+          }
+        } else {  // EPI_DSOFTMAX: dS = P * (dP - delta) * alpha, P read row-wise in D's layout
+          const float delta = row_ok ? __ldg(p.aux_f32 + stat_row) : 0.0f;
+          const bool half = p.out_mode == OUT_F16;
+          for (int cc = 0; cc < BN; cc += 16) {
+            uint32_t v[16];
+            tmem_ld_x16(t_row + static_cast<uint32_t>(cc), v);
+            tmem_ld_wait();
+            if (row_ok && n0 + cc < p.n_valid) {
+              const uint4* pp = reinterpret_cast<const uint4*>(reinterpret_cast<const uint16_t*>(p.aux16) + row_off + cc);
+              const uint4 p0 = __ldg(pp), p1 = __ldg(pp + 1);
+              const uint32_t pw[8] = {p0.x, p0.y, p0.z, p0.w, p1.x, p1.y, p1.z, p1.w};
+              float f[16];
+#pragma unroll
+              for (int i = 0; i < 8; ++i) {
+                const float2 pv = unpack_16x2(pw[i], half);
+                f[2 * i] = pv.x * (__uint_as_float(v[2 * i]) - delta) * p.alpha;
+                f[2 * i + 1] = pv.y * (__uint_as_float(v[2 * i + 1]) - delta) * p.alpha;
+              }
+              uint16_t* dst = reinterpret_cast<uint16_t*>(p.D) + row_off + cc;
+              uint4 o0, o1;
+              o0.x = pack_16x2(f[0], f[1], half);   o0.y = pack_16x2(f[2], f[3], half);
+              o0.z = pack_16x2(f[4], f[5], half);   o0.w = pack_16x2(f[6], f[7], half);
+              o1.x = pack_16x2(f[8], f[9], half);   o1.y = pack_16x2(f[10], f[11], half);
+              o1.z = pack_16x2(f[12], f[13], half); o1.w = pack_16x2(f[14], f[15], half);
+              reinterpret_cast<uint4*>(dst)[0] = o0;
+              reinterpret_cast<uint4*>(dst)[1] = o1;
+            }
+          }
+        }
+      } else
       for (int cc = 0; cc < acc_cols; cc += 16) {
         uint32_t v[16];
         tmem_ld_x16(t_row + static_cast<uint32_t>(cc), v);

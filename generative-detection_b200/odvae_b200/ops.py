@@ -67,6 +67,11 @@ def conv_impl(dtype, B, H, W, CinP, CoutP, geom):
     return IMPL_TC if ok else IMPL_SIMT
 
 
+def attn_fused(dtype, N, C):
+    """The fused tcgen05 attention core needs 16-bit operands and TMA-tileable shapes."""
+    return dtype == torch.bfloat16 and N % 128 == 0 and C % 64 == 0
+
+
 def out_hw(geom, H, W):
     return (H // 2, W // 2) if geom == CONV_3x3_S2 else (H, W)
 
@@ -389,11 +394,19 @@ class AttnBlock(torch.autograd.Function):
         impl = conv_impl(dt, B, H, W, C, 3 * C, CONV_1x1)
         call("conv2d_fwd", hn, wqkv, bqkv, None, qkv, B, H, W, C, 3 * C, 3 * C, CONV_1x1, act_code(dt), impl, 0)
         q, k, v = qkv[..., :C], qkv[..., C:2 * C], qkv[..., 2 * C:]
-        S = torch.empty(B, N, N, dtype=torch.float32, device=x.device)
-        gemm_raw(q, k, S, N, N, C, B, 3 * C, 3 * C, N, N * 3 * C, N * 3 * C, N * N, False, False)
         P = torch.empty(B, N, N, dtype=dt, device=x.device)
-        call("softmax_rows", S, P, B * N, N, float(int(C) ** (-0.5)), act_code(dt))
-        del S
+        scale = float(int(C) ** (-0.5))
+        if attn_fused(dt, N, C):
+            # q k^T and the softmax in two tcgen05 GEMM passes; the fp32 scores never reach HBM
+            nbytes = call("attn_softmax_workspace_bytes", B, N)
+            ws = workspace(nbytes, x.device, "attn")
+            call("attn_scores_softmax", q, k, P, B, N, C, 3 * C, 3 * C, N * 3 * C, N * 3 * C, scale, act_code(dt), ws,
+                 ws.numel())
+        else:
+            S = torch.empty(B, N, N, dtype=torch.float32, device=x.device)
+            gemm_raw(q, k, S, N, N, C, B, 3 * C, 3 * C, N, N * 3 * C, N * 3 * C, N * N, False, False)
+            call("softmax_rows", S, P, B * N, N, scale, act_code(dt))
+            del S
         O = torch.empty(B, H, W, C, dtype=dt, device=x.device)
         gemm_raw(P, v, O, N, C, N, B, N, 3 * C, C, N * N, N * 3 * C, N * C, False, True)
         out = conv_fwd_raw(O, blk.spec_proj, wp, bp, residual=x)
@@ -418,11 +431,17 @@ class AttnBlock(torch.autograd.Function):
         # dV[j,c] = sum_i P[i,j] dO[i,c]
         gemm_raw(P, dO, dv, N, C, N, B, N, C, 3 * C, N * N, N * C, N * 3 * C, True, True)
         # dP[i,j] = sum_c dO[i,c] v[j,c]
-        dP = torch.empty(B, N, N, dtype=torch.float32, device=x.device)
-        gemm_raw(dO, v, dP, N, N, C, B, C, 3 * C, N, N * C, N * 3 * C, N * N, False, False)
         dS = torch.empty(B, N, N, dtype=dt, device=x.device)
-        call("softmax_rows_bwd", dP, P, dS, B * N, N, scale, act_code(dt))
-        del dP
+        if attn_fused(dt, N, C):
+            # delta_i = sum_j P_ij dP_ij = sum_c dO_ic O_ic; dS = P * (dO v^T - delta) * scale in the GEMM epilogue
+            delta = torch.empty(B * N, dtype=torch.float32, device=x.device)
+            call("rowdot", dO, O, delta, B * N, C, C, C, act_code(dt))
+            call("attn_dsoftmax", dO, v, P, delta, dS, B, N, C, C, 3 * C, N * C, N * 3 * C, scale, act_code(dt))
+        else:
+            dP = torch.empty(B, N, N, dtype=torch.float32, device=x.device)
+            gemm_raw(dO, v, dP, N, N, C, B, C, 3 * C, N, N * C, N * 3 * C, N * N, False, False)
+            call("softmax_rows_bwd", dP, P, dS, B * N, N, scale, act_code(dt))
+            del dP
         # dQ[i,c] = sum_j dS[i,j] k[j,c] ; dK[j,c] = sum_i dS[i,j] q[i,c]
         gemm_raw(dS, k, dq, N, C, N, B, N, 3 * C, 3 * C, N * N, N * 3 * C, N * 3 * C, False, True)
         gemm_raw(dS, q, dk, N, C, N, B, N, 3 * C, 3 * C, N * N, N * 3 * C, N * 3 * C, True, True)

@@ -122,6 +122,26 @@ int odvae_gemm_16(const void* A, const void* B, void* D, int M, int N, int K, in
                   int b_dtype, int out_dtype, float alpha, const float* bias, const void* residual, void* stream);
 
 /* ---------------------------------------------------------------------------------------------
+ * Fused attention core of AttnBlock (model.py:187-197: w_ = softmax(q^T k * C^-0.5), single head), tcgen05 only.
+ * odvae_attn_scores_softmax: P[b] = softmax_rows(scale * q[b] k[b]^T) written ONCE in `dtype` (bf16 / fp16); the
+ *   fp32 score matrix never reaches HBM. Two passes of the q k^T GEMM: pass 1's epilogue leaves per-row
+ *   (max, sum exp) partials per column tile in the workspace, pass 2's epilogue combines them in a fixed order and
+ *   writes the normalised probabilities. q, k: [B][N][C] views with row strides ldq / ldk and batch strides.
+ * odvae_attn_dsoftmax: dS[b] = P[b] * (dO[b] v[b]^T - delta[b][:,None]) * scale, the softmax backward fused into the
+ *   dP GEMM's epilogue; delta[b][i] = sum_c dO[b][i][c] O[b][i][c] (= sum_j P_ij dP_ij), from odvae_rowdot.
+ * ------------------------------------------------------------------------------------------- */
+size_t odvae_attn_softmax_workspace_bytes(int B, int N);
+int odvae_attn_scores_softmax(const void* q, const void* k, void* P, int B, int N, int C, int64_t ldq, int64_t ldk,
+                              int64_t strideq, int64_t stridek, float scale, int dtype, void* workspace,
+                              size_t ws_bytes, void* stream);
+int odvae_attn_dsoftmax(const void* dO, const void* v, const void* P, const float* delta, void* dS, int B, int N,
+                        int C, int64_t ldo, int64_t ldv, int64_t strideo, int64_t stridev, float scale, int dtype,
+                        void* stream);
+/* out[r] = sum_c a[r*lda + c] * b[r*ldb + c], c < C (C % 8 == 0), 16-bit inputs of `dtype`, fp32 accumulate */
+int odvae_rowdot(const void* a, const void* b, float* out, int64_t rows, int C, int64_t lda, int64_t ldb, int dtype,
+                 void* stream);
+
+/* ---------------------------------------------------------------------------------------------
  * GroupNorm(32, C, eps=1e-6, affine) [+ SiLU]  (Normalize model.py:38-39, nonlinearity :33-35)
  * x, y: NHWC [B,HW,C]; stats: fp32 [B,G,2] = (mean, rstd).
  * ------------------------------------------------------------------------------------------- */

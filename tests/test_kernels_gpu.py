@@ -112,3 +112,34 @@ def test_sample_kl_and_l1_against_torch():
     (ref * w).sum().backward()
     torch.cuda.synchronize()
     assert rel(sums, ref) < 1e-5 and rel(xh.grad, xr.grad) < 1e-6
+
+
+@pytest.mark.parametrize("B,N,C", [(2, 256, 512), (1, 1024, 256), (2, 4096, 256)])
+def test_fused_attention_core_against_torch(B, N, C):
+    """odvae_attn_scores_softmax / odvae_rowdot / odvae_attn_dsoftmax vs torch fp32 on the same bf16 inputs
+    (AttnBlock core, LD model.py:187-197). Tolerance 1e-2 relative (bf16 outputs)."""
+    torch.manual_seed(11)
+    dt = torch.bfloat16
+    qkv = torch.randn(B, N, 3 * C, device="cuda").to(dt)
+    q, k, v = qkv[..., :C], qkv[..., C:2 * C], qkv[..., 2 * C:]
+    scale = float(C) ** -0.5
+    P = torch.empty(B, N, N, dtype=dt, device="cuda")
+    nbytes = ops.call("attn_softmax_workspace_bytes", B, N)
+    ws = torch.empty(nbytes, dtype=torch.uint8, device="cuda")
+    ops.call("attn_scores_softmax", q, k, P, B, N, C, 3 * C, 3 * C, N * 3 * C, N * 3 * C, scale, ops.act_code(dt), ws,
+             ws.numel())
+    Pr = torch.softmax(torch.bmm(q.float(), k.float().transpose(1, 2)) * scale, dim=-1)
+    assert float((P.float().sum(-1) - 1).abs().max()) < 2e-2
+    assert float((P.float() - Pr).abs().max() / Pr.abs().max()) < 1e-2
+    # backward: dS = P * (dP - rowsum(P*dP)) * scale with dP = dO v^T
+    dO = torch.randn(B, N, C, device="cuda").to(dt)
+    O = torch.bmm(P.float(), v.float()).to(dt)
+    delta = torch.empty(B * N, dtype=torch.float32, device="cuda")
+    ops.call("rowdot", dO, O, delta, B * N, C, C, C, ops.act_code(dt))
+    dref = (dO.float() * O.float()).sum(-1).reshape(-1)
+    assert float((delta - dref).abs().max() / dref.abs().max()) < 1e-5
+    dS = torch.empty(B, N, N, dtype=dt, device="cuda")
+    ops.call("attn_dsoftmax", dO, v, P, delta, dS, B, N, C, C, 3 * C, N * C, N * 3 * C, scale, ops.act_code(dt))
+    dP = torch.bmm(dO.float(), v.float().transpose(1, 2))
+    dSr = P.float() * (dP - delta.view(B, N, 1)) * scale
+    assert float((dS.float() - dSr).abs().max() / dSr.abs().max()) < 1e-2

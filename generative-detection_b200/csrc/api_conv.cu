@@ -20,11 +20,17 @@ int odvae_conv2d_tc_supported(int B, int H, int W, int CinP, int CoutP, int geom
 }
 
 int odvae_conv2d_fwd(const void* x, const void* w_packed, const float* bias, const void* residual, void* y, int B,
-                     int H, int W, int CinP, int CoutP, int Cout, int geom, int act_dtype, int impl, int out_nchw_f32,
-                     void* stream) {
+                     int H, int W, int CinP, int CoutP, int Cout, int geom, int act_dtype, int out_dtype, int impl,
+                     int out_nchw_f32, void* stream) {
   EngineDesc d;
   int st = describe_conv_fwd(d, x, w_packed, bias, residual, y, B, H, W, CinP, CoutP, Cout, geom, out_nchw_f32);
   if (st != ODVAE_OK) return st;
+  if (!out_nchw_f32) {
+    // NHWC output (and residual) format: fp32 mode keeps fp32; 16-bit modes choose bf16 / fp16 independently of the
+    // operand format (mixed mode: bf16 attention projections add into the fp16 residual stream)
+    if ((act_dtype == ODVAE_F32) != (out_dtype == ODVAE_F32)) return ODVAE_ERR_SHAPE;
+    if (out_dtype == ODVAE_F16) d.p.out_mode = OUT_F16;
+  }
   return run_engine(d, impl, act_dtype, static_cast<cudaStream_t>(stream));
 }
 
@@ -32,7 +38,7 @@ int odvae_conv2d_dgrad(const void* dy, const void* w_packed_dgrad, const void* d
                        int CinP, int CoutP, int geom, int act_dtype, int impl, void* stream) {
   EngineDesc ds[4];
   int n = 0;
-  int st = describe_conv_dgrad(ds, &n, dy, w_packed_dgrad, act_dtype == ODVAE_BF16 ? 2 : 4, dx_add, dx, B, H, W, CinP,
+  int st = describe_conv_dgrad(ds, &n, dy, w_packed_dgrad, act_dtype == ODVAE_F32 ? 4 : 2, dx_add, dx, B, H, W, CinP,
                                CoutP, geom);
   if (st != ODVAE_OK) return st;
   for (int i = 0; i < n; ++i) {
@@ -81,8 +87,6 @@ int odvae_gemm_bf16(const void* A, const void* B, void* D, int M, int N, int K, 
   return run_engine(d, ODVAE_IMPL_TC, ODVAE_BF16, static_cast<cudaStream_t>(stream));
 }
 
-static int fmt_of(int dtype) { return dtype == ODVAE_F16 ? FMT_F16 : FMT_BF16; }
-
 int odvae_gemm_16(const void* A, const void* B, void* D, int M, int N, int K, int batch, int64_t lda, int64_t ldb,
                   int64_t ldd, int64_t strideA, int64_t strideB, int64_t strideD, int a_mn, int b_mn, int a_dtype,
                   int b_dtype, int out_dtype, float alpha, const float* bias, const void* residual, void* stream) {
@@ -92,9 +96,7 @@ int odvae_gemm_16(const void* A, const void* B, void* D, int M, int N, int K, in
   int st = describe_gemm(d, A, B, D, M, N, K, batch, lda, ldb, ldd, strideA, strideB, strideD, a_mn, b_mn, om, alpha,
                          bias, residual);
   if (st != ODVAE_OK) return st;
-  d.p.a_fmt = fmt_of(a_dtype);
-  d.p.b_fmt = fmt_of(b_dtype);
-  return run_engine(d, ODVAE_IMPL_TC, ODVAE_BF16, static_cast<cudaStream_t>(stream));
+  return run_engine(d, ODVAE_IMPL_TC, a_dtype, static_cast<cudaStream_t>(stream));
 }
 
 // ---- fused attention core (tcgen05 only): scores + softmax in two GEMM passes, softmax backward in the dP GEMM ----
@@ -122,11 +124,10 @@ int odvae_attn_scores_softmax(const void* q, const void* k, void* P, int B, int 
     int st = describe_gemm(d, q, k, P, N, N, C, B, ldq, ldk, N, strideq, stridek, static_cast<int64_t>(N) * N, 0, 0, om,
                            scale, nullptr, nullptr);
     if (st != ODVAE_OK) return st;
-    d.p.a_fmt = d.p.b_fmt = fmt_of(dtype);
     d.p.epi = pass == 0 ? EPI_ROWSTATS : EPI_SOFTMAX;
     d.p.aux_out = reinterpret_cast<float*>(workspace);
     d.p.aux_f32 = reinterpret_cast<const float*>(workspace);
-    st = run_engine(d, ODVAE_IMPL_TC, ODVAE_BF16, s);
+    st = run_engine(d, ODVAE_IMPL_TC, dtype, s);
     if (st != ODVAE_OK) return st;
   }
   return ODVAE_OK;
@@ -141,11 +142,10 @@ int odvae_attn_dsoftmax(const void* dO, const void* v, const void* P, const floa
   int st = describe_gemm(d, dO, v, dS, N, N, C, B, ldo, ldv, N, strideo, stridev, static_cast<int64_t>(N) * N, 0, 0, om,
                          scale, nullptr, nullptr);
   if (st != ODVAE_OK) return st;
-  d.p.a_fmt = d.p.b_fmt = fmt_of(dtype);
   d.p.epi = EPI_DSOFTMAX;
   d.p.aux_f32 = delta;
   d.p.aux16 = P;
-  return run_engine(d, ODVAE_IMPL_TC, ODVAE_BF16, static_cast<cudaStream_t>(stream));
+  return run_engine(d, ODVAE_IMPL_TC, dtype, static_cast<cudaStream_t>(stream));
 }
 
 int odvae_gemm_simt(const void* A, const void* B, void* D, int M, int N, int K, int batch, int64_t lda, int64_t ldb,

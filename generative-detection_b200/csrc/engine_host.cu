@@ -143,16 +143,23 @@ static int launch_simt(const EngineDesc& d, int act_dtype, cudaStream_t stream) 
   }
   dim3 grid(static_cast<unsigned>((s.N + 63) / 64), static_cast<unsigned>((s.M + 63) / 64), static_cast<unsigned>(p.num_z));
   if (grid.y > 65535 || grid.z > 65535) return ODVAE_ERR_SHAPE;
-  if (act_dtype == ODVAE_BF16)
-    simt_engine_kernel<bf16><<<grid, 256, 0, stream>>>(s);
-  else
-    simt_engine_kernel<float><<<grid, 256, 0, stream>>>(s);
+  const bool out_half = p.out_mode == OUT_F16;
+  if (act_dtype == ODVAE_BF16) {
+    if (out_half) simt_engine_kernel<bf16, f16><<<grid, 256, 0, stream>>>(s);
+    else simt_engine_kernel<bf16, bf16><<<grid, 256, 0, stream>>>(s);
+  } else if (act_dtype == ODVAE_F16) {
+    if (out_half) simt_engine_kernel<f16, f16><<<grid, 256, 0, stream>>>(s);
+    else simt_engine_kernel<f16, bf16><<<grid, 256, 0, stream>>>(s);
+  } else {
+    simt_engine_kernel<float, float><<<grid, 256, 0, stream>>>(s);
+  }
   return check_launch("simt_engine_kernel");
 }
 
 int run_engine(EngineDesc& d, int impl, int act_dtype, cudaStream_t stream) {
   if (impl == ODVAE_IMPL_TC) {
-    if (act_dtype != ODVAE_BF16) return ODVAE_ERR_SHAPE;
+    if (act_dtype != ODVAE_BF16 && act_dtype != ODVAE_F16) return ODVAE_ERR_SHAPE;
+    d.p.a_fmt = d.p.b_fmt = (act_dtype == ODVAE_F16 ? FMT_F16 : FMT_BF16);  // one operand format per MMA (B200 traps on mixes)
     return launch_tc(d, stream);
   }
   return launch_simt(d, act_dtype, stream);

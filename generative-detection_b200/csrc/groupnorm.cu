@@ -10,15 +10,16 @@ namespace odvae {
 template <typename T> struct VecN;
 template <> struct VecN<float> { static constexpr int V = 4; };
 template <> struct VecN<bf16> { static constexpr int V = 8; };
+template <> struct VecN<f16> { static constexpr int V = 8; };
 
 static constexpr int GN_THREADS = 256;
 
 // MODE 0: per-(b,c) sums of (x, x^2)          -> forward statistics
 // MODE 1: per-(b,c) sums of (dy', dy' * xhat)  -> backward reductions, dy' = dy * silu'(u) when silu
 // part layout: [B][nsplit][C][2]
-template <typename T, int MODE>
+template <typename T, typename TG, int MODE>
 __global__ void __launch_bounds__(GN_THREADS)
-gn_reduce_kernel(const T* __restrict__ x, const T* __restrict__ dy, const float* __restrict__ stats,
+gn_reduce_kernel(const T* __restrict__ x, const TG* __restrict__ dy, const float* __restrict__ stats,
                  const float* __restrict__ gamma, const float* __restrict__ beta, float* __restrict__ part, int HW,
                  int C, int G, int silu) {
   constexpr int V = VecN<T>::V;
@@ -50,11 +51,12 @@ gn_reduce_kernel(const T* __restrict__ x, const T* __restrict__ dy, const float*
   }
   if (row < rows) {
     const T* xb = x + static_cast<long long>(b) * HW * C + c0;
-    const T* dyb = MODE == 1 ? dy + static_cast<long long>(b) * HW * C + c0 : nullptr;
+    const TG* dyb = MODE == 1 ? dy + static_cast<long long>(b) * HW * C + c0 : nullptr;
     constexpr int U = 4;
     int p = p0 + row;
     for (; p + (U - 1) * rows < p1; p += U * rows) {
-      T xv[U][V], dv[U][V];
+      T xv[U][V];
+      TG dv[U][V];
 #pragma unroll
       for (int u = 0; u < U; ++u)
         *reinterpret_cast<uint4*>(xv[u]) = __ldg(reinterpret_cast<const uint4*>(xb + static_cast<long long>(p + u * rows) * C));
@@ -72,7 +74,7 @@ gn_reduce_kernel(const T* __restrict__ x, const T* __restrict__ dy, const float*
             s0[j] += v;
             s1[j] = fmaf(v, v, s1[j]);
           } else {
-            float d = to_f32<T>(dv[u][j]);
+            float d = to_f32<TG>(dv[u][j]);
             if (silu) d *= silu_grad_f(fmaf(v, sc[j], sh[j]));
             s0[j] += d;
             s1[j] = fmaf(d, (v - mu[j]) * rs[j], s1[j]);
@@ -91,12 +93,12 @@ gn_reduce_kernel(const T* __restrict__ x, const T* __restrict__ dy, const float*
           s1[j] = fmaf(v, v, s1[j]);
         }
       } else {
-        T dv[V];
+        TG dv[V];
         *reinterpret_cast<uint4*>(dv) = __ldg(reinterpret_cast<const uint4*>(dyb + static_cast<long long>(p) * C));
 #pragma unroll
         for (int j = 0; j < V; ++j) {
           const float v = to_f32<T>(xv[j]);
-          float d = to_f32<T>(dv[j]);
+          float d = to_f32<TG>(dv[j]);
           if (silu) d *= silu_grad_f(fmaf(v, sc[j], sh[j]));
           s0[j] += d;
           s1[j] = fmaf(d, (v - mu[j]) * rs[j], s1[j]);
@@ -154,10 +156,13 @@ __global__ void gn_stats_finalize_kernel(const float* __restrict__ part, float* 
 // y = [silu]((x - mean) * rstd * gamma + beta)
 // The grid-stride (gridDim.x * GN_THREADS vectors) is a multiple of C/V, so every thread keeps ONE channel vector for
 // the whole loop: scale/shift live in registers and the loop body is load -> fma (+SiLU) -> store.
-template <typename T>
+// TO / TO2: formats of y and of the optional second copy y2 (mixed mode: fp16 for the forward conv, bf16 for wgrad);
+// sizeof(T) == sizeof(TO) == sizeof(TO2) so all three share one vector index.
+template <typename T, typename TO, typename TO2>
 __global__ void __launch_bounds__(GN_THREADS)
 gn_apply_kernel(const T* __restrict__ x, const float* __restrict__ stats, const float* __restrict__ gamma,
-                const float* __restrict__ beta, T* __restrict__ y, int HW, int C, int G, int silu) {
+                const float* __restrict__ beta, TO* __restrict__ y, TO2* __restrict__ y2, int HW, int C, int G,
+                int silu) {
   constexpr int V = VecN<T>::V;
   const int b = blockIdx.y;
   const int cpg = C / G;
@@ -177,6 +182,7 @@ gn_apply_kernel(const T* __restrict__ x, const float* __restrict__ stats, const 
   const long long nvec = static_cast<long long>(HW) * cv;
   const uint4* xb = reinterpret_cast<const uint4*>(x + static_cast<long long>(b) * HW * C);
   uint4* yb = reinterpret_cast<uint4*>(y + static_cast<long long>(b) * HW * C);
+  uint4* y2b = y2 ? reinterpret_cast<uint4*>(y2 + static_cast<long long>(b) * HW * C) : nullptr;
   const long long stride = static_cast<long long>(gridDim.x) * GN_THREADS;
   constexpr int U = 4;
   for (; i + (U - 1) * stride < nvec; i += U * stride) {
@@ -185,26 +191,33 @@ gn_apply_kernel(const T* __restrict__ x, const float* __restrict__ stats, const 
     for (int u = 0; u < U; ++u) *reinterpret_cast<uint4*>(xv[u]) = __ldg(xb + i + u * stride);
 #pragma unroll
     for (int u = 0; u < U; ++u) {
-      T yv[V];
+      TO yv[V];
+      TO2 y2v[V];
 #pragma unroll
       for (int j = 0; j < V; ++j) {
         float v = fmaf(to_f32<T>(xv[u][j]), scale[j], shift[j]);
         if (silu) v = silu_f(v);
-        yv[j] = from_f32<T>(v);
+        yv[j] = from_f32<TO>(v);
+        y2v[j] = from_f32<TO2>(v);
       }
       yb[i + u * stride] = *reinterpret_cast<const uint4*>(yv);
+      if (y2b) y2b[i + u * stride] = *reinterpret_cast<const uint4*>(y2v);
     }
   }
   for (; i < nvec; i += stride) {
-    T xv[V], yv[V];
+    T xv[V];
+    TO yv[V];
+    TO2 y2v[V];
     *reinterpret_cast<uint4*>(xv) = __ldg(xb + i);
 #pragma unroll
     for (int j = 0; j < V; ++j) {
       float v = fmaf(to_f32<T>(xv[j]), scale[j], shift[j]);
       if (silu) v = silu_f(v);
-      yv[j] = from_f32<T>(v);
+      yv[j] = from_f32<TO>(v);
+      y2v[j] = from_f32<TO2>(v);
     }
     yb[i] = *reinterpret_cast<const uint4*>(yv);
+    if (y2b) y2b[i] = *reinterpret_cast<const uint4*>(y2v);
   }
 }
 
@@ -259,11 +272,11 @@ __global__ void gn_bwd_finalize_b_kernel(const float* __restrict__ AB, float* __
 }
 
 // dx = c1 * dy' + c2 * x + c3 (+ dx_add); one channel vector per thread for the whole loop (see gn_apply_kernel)
-template <typename T>
+template <typename T, typename TG>
 __global__ void __launch_bounds__(GN_THREADS)
-gn_bwd_apply_kernel(const T* __restrict__ x, const T* __restrict__ dy, const T* __restrict__ dx_add,
+gn_bwd_apply_kernel(const T* __restrict__ x, const TG* __restrict__ dy, const TG* __restrict__ dx_add,
                     const float* __restrict__ stats, const float* __restrict__ gamma, const float* __restrict__ beta,
-                    const float* __restrict__ coef, T* __restrict__ dx, int HW, int C, int G, int silu) {
+                    const float* __restrict__ coef, TG* __restrict__ dx, int HW, int C, int G, int silu) {
   constexpr int V = VecN<T>::V;
   const int b = blockIdx.y;
   const int cpg = C / G;
@@ -291,7 +304,8 @@ gn_bwd_apply_kernel(const T* __restrict__ x, const T* __restrict__ dy, const T* 
   const long long stride = static_cast<long long>(gridDim.x) * GN_THREADS;
   constexpr int U = 2;
   for (; i < nvec; i += U * stride) {
-    T xv[U][V], dv[U][V], av[U][V];
+    T xv[U][V];
+    TG dv[U][V], av[U][V];
 #pragma unroll
     for (int u = 0; u < U; ++u) {
       const long long k = i + u * stride;
@@ -305,15 +319,15 @@ gn_bwd_apply_kernel(const T* __restrict__ x, const T* __restrict__ dy, const T* 
     for (int u = 0; u < U; ++u) {
       const long long k = i + u * stride;
       if (k < nvec) {
-        T ov[V];
+        TG ov[V];
 #pragma unroll
         for (int j = 0; j < V; ++j) {
           const float xf = to_f32<T>(xv[u][j]);
-          float d = to_f32<T>(dv[u][j]);
+          float d = to_f32<TG>(dv[u][j]);
           if (silu) d *= silu_grad_f(fmaf(xf, scale[j], shift[j]));
           float o = fmaf(scale[j], d, fmaf(c2[j], xf, c3[j]));
-          if (ab) o += to_f32<T>(av[u][j]);
-          ov[j] = from_f32<T>(o);
+          if (ab) o += to_f32<TG>(av[u][j]);
+          ov[j] = from_f32<TG>(o);
         }
         dxb[k] = *reinterpret_cast<const uint4*>(ov);
       }
@@ -359,7 +373,7 @@ size_t odvae_groupnorm_workspace_bytes(int B, int HW, int C, int G) {
 int odvae_groupnorm_stats(const void* x, float* stats, int B, int HW, int C, int G, float eps, int act_dtype,
                           void* workspace, size_t ws_bytes, void* stream) {
   cudaStream_t st = static_cast<cudaStream_t>(stream);
-  const int V = act_dtype == ODVAE_BF16 ? 8 : 4;
+  const int V = act_dtype == ODVAE_F32 ? 4 : 8;
   if (!gn_shape_ok(C, G, V)) return ODVAE_ERR_SHAPE;
   const int ns = gn_nsplit(B, HW);
   if (ws_bytes < static_cast<size_t>(B) * ns * C * 2 * sizeof(float)) return ODVAE_ERR_WORKSPACE;
@@ -368,35 +382,53 @@ int odvae_groupnorm_stats(const void* x, float* stats, int B, int HW, int C, int
   const size_t smem = static_cast<size_t>(2) * rows * C * sizeof(float);
   dim3 grid(ns, B);
   if (act_dtype == ODVAE_BF16)
-    gn_reduce_kernel<bf16, 0><<<grid, GN_THREADS, smem, st>>>(reinterpret_cast<const bf16*>(x), nullptr, nullptr, nullptr, nullptr, part, HW, C, G, 0);
+    gn_reduce_kernel<bf16, bf16, 0><<<grid, GN_THREADS, smem, st>>>(reinterpret_cast<const bf16*>(x), nullptr, nullptr, nullptr, nullptr, part, HW, C, G, 0);
+  else if (act_dtype == ODVAE_F16)
+    gn_reduce_kernel<f16, bf16, 0><<<grid, GN_THREADS, smem, st>>>(reinterpret_cast<const f16*>(x), nullptr, nullptr, nullptr, nullptr, part, HW, C, G, 0);
   else
-    gn_reduce_kernel<float, 0><<<grid, GN_THREADS, smem, st>>>(reinterpret_cast<const float*>(x), nullptr, nullptr, nullptr, nullptr, part, HW, C, G, 0);
+    gn_reduce_kernel<float, float, 0><<<grid, GN_THREADS, smem, st>>>(reinterpret_cast<const float*>(x), nullptr, nullptr, nullptr, nullptr, part, HW, C, G, 0);
   int s = check_launch("gn_reduce_kernel<0>");
   if (s != ODVAE_OK) return s;
   gn_stats_finalize_kernel<<<B, 32, 0, st>>>(part, stats, ns, HW, C, G, eps);
   return check_launch("gn_stats_finalize_kernel");
 }
 
-int odvae_groupnorm_apply(const void* x, const float* stats, const float* gamma, const float* beta, void* y, int B,
-                          int HW, int C, int G, int silu, int act_dtype, void* stream) {
+// (in, out, out2) format combinations the modes use: f32 -> f32; bf16 -> bf16; fp16 -> fp16 (+ bf16 copy for the
+// weight-gradient GEMM); fp16 -> bf16 (attention blocks run in bf16 inside the mixed mode)
+int odvae_groupnorm_apply(const void* x, const float* stats, const float* gamma, const float* beta, void* y, void* y2,
+                          int B, int HW, int C, int G, int silu, int in_dtype, int out_dtype, int out2_dtype,
+                          void* stream) {
   cudaStream_t st = static_cast<cudaStream_t>(stream);
-  const int V = act_dtype == ODVAE_BF16 ? 8 : 4;
+  const int V = in_dtype == ODVAE_F32 ? 4 : 8;
   if (!gn_shape_ok(C, G, V)) return ODVAE_ERR_SHAPE;
   dim3 grid(gn_apply_blocks(B, HW, C, V), B);
-  const size_t smem = 0;
-  if (act_dtype == ODVAE_BF16)
-    gn_apply_kernel<bf16><<<grid, GN_THREADS, smem, st>>>(reinterpret_cast<const bf16*>(x), stats, gamma, beta, reinterpret_cast<bf16*>(y), HW, C, G, silu);
+  if (in_dtype == ODVAE_F32 && out_dtype == ODVAE_F32 && y2 == nullptr)
+    gn_apply_kernel<float, float, float><<<grid, GN_THREADS, 0, st>>>(reinterpret_cast<const float*>(x), stats, gamma, beta, reinterpret_cast<float*>(y), nullptr, HW, C, G, silu);
+  else if (in_dtype == ODVAE_BF16 && out_dtype == ODVAE_BF16 && (y2 == nullptr || out2_dtype == ODVAE_BF16))
+    gn_apply_kernel<bf16, bf16, bf16><<<grid, GN_THREADS, 0, st>>>(reinterpret_cast<const bf16*>(x), stats, gamma, beta, reinterpret_cast<bf16*>(y), reinterpret_cast<bf16*>(y2), HW, C, G, silu);
+  else if (in_dtype == ODVAE_F16 && out_dtype == ODVAE_F16 && (y2 == nullptr || out2_dtype == ODVAE_BF16))
+    gn_apply_kernel<f16, f16, bf16><<<grid, GN_THREADS, 0, st>>>(reinterpret_cast<const f16*>(x), stats, gamma, beta, reinterpret_cast<f16*>(y), reinterpret_cast<bf16*>(y2), HW, C, G, silu);
+  else if (in_dtype == ODVAE_F16 && out_dtype == ODVAE_BF16 && y2 == nullptr)
+    gn_apply_kernel<f16, bf16, bf16><<<grid, GN_THREADS, 0, st>>>(reinterpret_cast<const f16*>(x), stats, gamma, beta, reinterpret_cast<bf16*>(y), nullptr, HW, C, G, silu);
   else
-    gn_apply_kernel<float><<<grid, GN_THREADS, smem, st>>>(reinterpret_cast<const float*>(x), stats, gamma, beta, reinterpret_cast<float*>(y), HW, C, G, silu);
+    return ODVAE_ERR_SHAPE;
   return check_launch("gn_apply_kernel");
 }
 
+// act_dtype: format of x (the saved forward input); grad_dtype: format of dy / dx_add / dx.
+// Supported pairs: (f32, f32), (bf16, bf16), (fp16, bf16).
 int odvae_groupnorm_bwd(const void* x, const float* stats, const float* gamma, const float* beta, const void* dy,
                         const void* dx_add, void* dx, float* dgamma, float* dbeta, int B, int HW, int C, int G,
-                        int silu, int act_dtype, int accumulate, void* workspace, size_t ws_bytes, void* stream) {
+                        int silu, int act_dtype, int grad_dtype, int accumulate, void* workspace, size_t ws_bytes,
+                        void* stream) {
   cudaStream_t st = static_cast<cudaStream_t>(stream);
-  const int V = act_dtype == ODVAE_BF16 ? 8 : 4;
+  const int V = act_dtype == ODVAE_F32 ? 4 : 8;
   if (!gn_shape_ok(C, G, V)) return ODVAE_ERR_SHAPE;
+  const int combo = (act_dtype == ODVAE_F32 && grad_dtype == ODVAE_F32)     ? 0
+                    : (act_dtype == ODVAE_BF16 && grad_dtype == ODVAE_BF16) ? 1
+                    : (act_dtype == ODVAE_F16 && grad_dtype == ODVAE_BF16)  ? 2
+                                                                            : -1;
+  if (combo < 0) return ODVAE_ERR_SHAPE;
   const int ns = gn_nsplit(B, HW);
   if (ws_bytes < odvae_groupnorm_workspace_bytes(B, HW, C, G) - 256) return ODVAE_ERR_WORKSPACE;
   float* part = reinterpret_cast<float*>(workspace);
@@ -405,10 +437,12 @@ int odvae_groupnorm_bwd(const void* x, const float* stats, const float* gamma, c
   const int rows = GN_THREADS / (C / V);
   const size_t smem = static_cast<size_t>(2) * rows * C * sizeof(float);
   dim3 grid(ns, B);
-  if (act_dtype == ODVAE_BF16)
-    gn_reduce_kernel<bf16, 1><<<grid, GN_THREADS, smem, st>>>(reinterpret_cast<const bf16*>(x), reinterpret_cast<const bf16*>(dy), stats, gamma, beta, part, HW, C, G, silu);
+  if (combo == 1)
+    gn_reduce_kernel<bf16, bf16, 1><<<grid, GN_THREADS, smem, st>>>(reinterpret_cast<const bf16*>(x), reinterpret_cast<const bf16*>(dy), stats, gamma, beta, part, HW, C, G, silu);
+  else if (combo == 2)
+    gn_reduce_kernel<f16, bf16, 1><<<grid, GN_THREADS, smem, st>>>(reinterpret_cast<const f16*>(x), reinterpret_cast<const bf16*>(dy), stats, gamma, beta, part, HW, C, G, silu);
   else
-    gn_reduce_kernel<float, 1><<<grid, GN_THREADS, smem, st>>>(reinterpret_cast<const float*>(x), reinterpret_cast<const float*>(dy), stats, gamma, beta, part, HW, C, G, silu);
+    gn_reduce_kernel<float, float, 1><<<grid, GN_THREADS, smem, st>>>(reinterpret_cast<const float*>(x), reinterpret_cast<const float*>(dy), stats, gamma, beta, part, HW, C, G, silu);
   int s = check_launch("gn_reduce_kernel<1>");
   if (s != ODVAE_OK) return s;
   gn_bwd_finalize_a_kernel<<<B, 256, static_cast<size_t>(2) * C * sizeof(float), st>>>(part, stats, gamma, AB, coef, ns, HW, C, G);
@@ -418,11 +452,12 @@ int odvae_groupnorm_bwd(const void* x, const float* stats, const float* gamma, c
   s = check_launch("gn_bwd_finalize_b_kernel");
   if (s != ODVAE_OK) return s;
   dim3 grid2(gn_apply_blocks(B, HW, C, V), B);
-  const size_t smem2 = 0;
-  if (act_dtype == ODVAE_BF16)
-    gn_bwd_apply_kernel<bf16><<<grid2, GN_THREADS, smem2, st>>>(reinterpret_cast<const bf16*>(x), reinterpret_cast<const bf16*>(dy), reinterpret_cast<const bf16*>(dx_add), stats, gamma, beta, coef, reinterpret_cast<bf16*>(dx), HW, C, G, silu);
+  if (combo == 1)
+    gn_bwd_apply_kernel<bf16, bf16><<<grid2, GN_THREADS, 0, st>>>(reinterpret_cast<const bf16*>(x), reinterpret_cast<const bf16*>(dy), reinterpret_cast<const bf16*>(dx_add), stats, gamma, beta, coef, reinterpret_cast<bf16*>(dx), HW, C, G, silu);
+  else if (combo == 2)
+    gn_bwd_apply_kernel<f16, bf16><<<grid2, GN_THREADS, 0, st>>>(reinterpret_cast<const f16*>(x), reinterpret_cast<const bf16*>(dy), reinterpret_cast<const bf16*>(dx_add), stats, gamma, beta, coef, reinterpret_cast<bf16*>(dx), HW, C, G, silu);
   else
-    gn_bwd_apply_kernel<float><<<grid2, GN_THREADS, smem2, st>>>(reinterpret_cast<const float*>(x), reinterpret_cast<const float*>(dy), reinterpret_cast<const float*>(dx_add), stats, gamma, beta, coef, reinterpret_cast<float*>(dx), HW, C, G, silu);
+    gn_bwd_apply_kernel<float, float><<<grid2, GN_THREADS, 0, st>>>(reinterpret_cast<const float*>(x), reinterpret_cast<const float*>(dy), reinterpret_cast<const float*>(dx_add), stats, gamma, beta, coef, reinterpret_cast<float*>(dx), HW, C, G, silu);
   return check_launch("gn_bwd_apply_kernel");
 }
 

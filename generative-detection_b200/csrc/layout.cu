@@ -7,6 +7,7 @@ namespace odvae {
 template <typename T> struct Vec16;  // 16-byte vector of T
 template <> struct Vec16<float> { static constexpr int N = 4; };
 template <> struct Vec16<bf16> { static constexpr int N = 8; };
+template <> struct Vec16<f16> { static constexpr int N = 8; };
 
 // ---------------------------------------------------------------------------------------------
 // NCHW fp32 <-> NHWC T
@@ -363,6 +364,23 @@ __global__ void add_kernel(const T* __restrict__ a, const T* __restrict__ b, T* 
   }
 }
 
+// fp16 <-> bf16 over 16-byte vectors (SRC_HALF: fp16 -> bf16, else bf16 -> fp16 with saturation)
+template <bool SRC_HALF>
+__global__ void __launch_bounds__(256) cast16_kernel(const uint4* __restrict__ src, uint4* __restrict__ dst, long long nvec) {
+  for (long long i = blockIdx.x * static_cast<long long>(blockDim.x) + threadIdx.x; i < nvec;
+       i += static_cast<long long>(gridDim.x) * blockDim.x) {
+    const uint4 v = __ldg(src + i);
+    const uint32_t w[4] = {v.x, v.y, v.z, v.w};
+    uint32_t o[4];
+#pragma unroll
+    for (int j = 0; j < 4; ++j) {
+      const float2 f = unpack_16x2(w[j], SRC_HALF);
+      o[j] = pack_16x2(f.x, f.y, !SRC_HALF);
+    }
+    dst[i] = make_uint4(o[0], o[1], o[2], o[3]);
+  }
+}
+
 static int grid_for(long long work_items, int threads, int per_sm = 8) {
   long long blocks = (work_items + threads - 1) / threads;
   long long cap = static_cast<long long>(num_sms()) * per_sm;
@@ -422,6 +440,9 @@ int odvae_nchw_to_nhwc(const float* src, void* dst, int B, int C, int H, int W, 
   if (act_dtype == ODVAE_BF16) {
     if (Cpad % 8) return ODVAE_ERR_SHAPE;
     nchw_to_nhwc_kernel<bf16><<<grid_for(total, 256), 256, 0, st>>>(src, reinterpret_cast<bf16*>(dst), B, C, H * W, Cpad, scale, shift);
+  } else if (act_dtype == ODVAE_F16) {
+    if (Cpad % 8) return ODVAE_ERR_SHAPE;
+    nchw_to_nhwc_kernel<f16><<<grid_for(total, 256), 256, 0, st>>>(src, reinterpret_cast<f16*>(dst), B, C, H * W, Cpad, scale, shift);
   } else {
     if (Cpad % 4) return ODVAE_ERR_SHAPE;
     nchw_to_nhwc_kernel<float><<<grid_for(total, 256), 256, 0, st>>>(src, reinterpret_cast<float*>(dst), B, C, H * W, Cpad, scale, shift);
@@ -436,6 +457,9 @@ int odvae_nhwc_to_nchw(const void* src, float* dst, int B, int C, int H, int W, 
   if (act_dtype == ODVAE_BF16) {
     if (Cpad % 8) return ODVAE_ERR_SHAPE;
     nhwc_to_nchw_kernel<bf16><<<grid_for(total, 256), 256, 0, st>>>(reinterpret_cast<const bf16*>(src), dst, B, C, H * W, Cpad);
+  } else if (act_dtype == ODVAE_F16) {
+    if (Cpad % 8) return ODVAE_ERR_SHAPE;
+    nhwc_to_nchw_kernel<f16><<<grid_for(total, 256), 256, 0, st>>>(reinterpret_cast<const f16*>(src), dst, B, C, H * W, Cpad);
   } else {
     if (Cpad % 4) return ODVAE_ERR_SHAPE;
     nhwc_to_nchw_kernel<float><<<grid_for(total, 256), 256, 0, st>>>(reinterpret_cast<const float*>(src), dst, B, C, H * W, Cpad);
@@ -463,6 +487,8 @@ int odvae_pack_conv_weight(const float* w_oihw, void* packed, int Cout, int Cin,
   const long long total = static_cast<long long>(CoutP) * CinP * k * k;
   if (act_dtype == ODVAE_BF16)
     pack_conv_weight_kernel<bf16><<<grid_for(total, 256), 256, 0, st>>>(w_oihw, reinterpret_cast<bf16*>(packed), Cout, Cin, k, CoutP, CinP, which, s2);
+  else if (act_dtype == ODVAE_F16)
+    pack_conv_weight_kernel<f16><<<grid_for(total, 256), 256, 0, st>>>(w_oihw, reinterpret_cast<f16*>(packed), Cout, Cin, k, CoutP, CinP, which, s2);
   else
     pack_conv_weight_kernel<float><<<grid_for(total, 256), 256, 0, st>>>(w_oihw, reinterpret_cast<float*>(packed), Cout, Cin, k, CoutP, CinP, which, s2);
   return check_launch("pack_conv_weight_kernel");
@@ -470,7 +496,7 @@ int odvae_pack_conv_weight(const float* w_oihw, void* packed, int Cout, int Cin,
 
 int odvae_upsample2x(const void* x, void* y, int B, int H, int W, int C, int act_dtype, void* stream) {
   cudaStream_t st = static_cast<cudaStream_t>(stream);
-  if (act_dtype == ODVAE_BF16) {
+  if (act_dtype == ODVAE_BF16 || act_dtype == ODVAE_F16) {  // a copy: any 16-bit format
     if (C % 8) return ODVAE_ERR_SHAPE;
     const long long total = static_cast<long long>(B) * 4 * H * W * (C / 8);
     upsample2x_kernel<bf16><<<grid_for(total, 256), 256, 0, st>>>(reinterpret_cast<const bf16*>(x), reinterpret_cast<bf16*>(y), B, H, W, C);
@@ -494,6 +520,18 @@ int odvae_upsample2x_bwd(const void* dy, void* dx, int B, int H, int W, int C, i
     upsample2x_bwd_kernel<float><<<grid_for(total, 256), 256, 0, st>>>(reinterpret_cast<const float*>(dy), reinterpret_cast<float*>(dx), B, H, W, C);
   }
   return check_launch("upsample2x_bwd_kernel");
+}
+
+int odvae_cast16(const void* src, void* dst, int64_t n, int src_dtype, int dst_dtype, void* stream) {
+  if (n % 8) return ODVAE_ERR_SHAPE;
+  cudaStream_t st = static_cast<cudaStream_t>(stream);
+  if (src_dtype == ODVAE_F16 && dst_dtype == ODVAE_BF16)
+    cast16_kernel<true><<<grid_for(n / 8, 256), 256, 0, st>>>(reinterpret_cast<const uint4*>(src), reinterpret_cast<uint4*>(dst), n / 8);
+  else if (src_dtype == ODVAE_BF16 && dst_dtype == ODVAE_F16)
+    cast16_kernel<false><<<grid_for(n / 8, 256), 256, 0, st>>>(reinterpret_cast<const uint4*>(src), reinterpret_cast<uint4*>(dst), n / 8);
+  else
+    return ODVAE_ERR_SHAPE;
+  return check_launch("cast16_kernel");
 }
 
 int odvae_add(const void* a, const void* b, void* out, int64_t n, int act_dtype, void* stream) {

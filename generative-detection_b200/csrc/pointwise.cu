@@ -407,6 +407,10 @@ int odvae_sample_kl_fwd(const void* moments, const float* eps, const uint8_t* ke
     sample_kl_fwd_kernel<bf16><<<B, 256, 0, st>>>(reinterpret_cast<const bf16*>(moments), eps, keep, noise, enc_pose,
                                                   keep_scale, mean, logvar, reinterpret_cast<bf16*>(z), kl, HW, Cz,
                                                   CzPad, ld_moments);
+  else if (act_dtype == ODVAE_F16)
+    sample_kl_fwd_kernel<f16><<<B, 256, 0, st>>>(reinterpret_cast<const f16*>(moments), eps, keep, noise, enc_pose,
+                                                 keep_scale, mean, logvar, reinterpret_cast<f16*>(z), kl, HW, Cz,
+                                                 CzPad, ld_moments);
   else
     sample_kl_fwd_kernel<float><<<B, 256, 0, st>>>(reinterpret_cast<const float*>(moments), eps, keep, noise, enc_pose,
                                                    keep_scale, mean, logvar, reinterpret_cast<float*>(z), kl, HW, Cz,

@@ -70,7 +70,8 @@ __device__ __forceinline__ float simt_load_b(const SimtParams& s, long long n, l
   }
 }
 
-template <typename T>
+// T: operand format; TO: format of a 16-bit / "activation dtype" output and of its residual
+template <typename T, typename TO>
 __global__ void __launch_bounds__(256) simt_engine_kernel(const __grid_constant__ SimtParams s) {
   const TcParams& p = s.p;
   __shared__ float As[16][64 + 4];
@@ -142,9 +143,9 @@ __global__ void __launch_bounds__(256) simt_engine_kernel(const __grid_constant_
       if (n >= p.n_valid) continue;
       float v = acc[i][j] * p.alpha;
       if (p.bias != nullptr) v += __ldg(p.bias + n);
-      if (p.out_mode == OUT_BF16) {  // "activation dtype" output
-        if (p.residual != nullptr) v += to_f32<T>(reinterpret_cast<const T*>(p.residual)[row_off + n]);
-        reinterpret_cast<T*>(p.D)[row_off + n] = from_f32<T>(v);
+      if (p.out_mode == OUT_BF16 || p.out_mode == OUT_F16) {  // "activation dtype" output
+        if (p.residual != nullptr) v += to_f32<TO>(reinterpret_cast<const TO*>(p.residual)[row_off + n]);
+        reinterpret_cast<TO*>(p.D)[row_off + n] = from_f32<TO>(v);
       } else if (p.out_mode == OUT_F32) {
         if (p.residual != nullptr) v += reinterpret_cast<const float*>(p.residual)[row_off + n];
         reinterpret_cast<float*>(p.D)[row_off + n] = v;

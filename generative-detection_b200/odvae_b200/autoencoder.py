@@ -123,7 +123,8 @@ class PoseAutoencoder(_Base):
         super().__init__()
         if isinstance(compute_dtype, str):
             compute_dtype = {"bf16": torch.bfloat16, "bfloat16": torch.bfloat16, "fp32": torch.float32,
-                             "float32": torch.float32}[compute_dtype]
+                             "float32": torch.float32, "fp16": torch.float16, "float16": torch.float16,
+                             "mixed": torch.float16}[compute_dtype]
         self.compute_dtype = compute_dtype
         self.fused_optimizer = fused_optimizer
         self.encoder_pretrain_steps = lossconfig["params"]["encoder_pretrain_steps"]
@@ -162,6 +163,7 @@ class PoseAutoencoder(_Base):
         self.feat_dims = feat_dims
         self.inject_noise = None  # (eps_obj, keep{0,1}, z_noise, eps_bbox) CPU/GPU tensors: parity tests only
         self.register_load_state_dict_post_hook(lambda *a: ops.bump_weight_epoch())
+        self.fmt = ops.assign_format(self, compute_dtype)  # quant convs included (encoder/decoder did their own)
 
     # ------------------------------------------------------------------ checkpoint / misc API
     def init_from_ckpt(self, path, ignore_keys=list()):
@@ -256,15 +258,15 @@ class PoseAutoencoder(_Base):
         if want_z and eps is None:
             eps = torch.zeros(moments.shape[0], zc, moments.shape[1], moments.shape[2], device=moments.device)
         mean, logvar, z, kl = ops.SampleKL.apply(moments, enc_pose, eps, keep, noise, keep_scale, zc, ops.cpad(zc),
-                                                 want_z)
-        post = FusedPosterior(mean, logvar, kl, lambda: ops.ToNCHW.apply(moments, 2 * zc))
+                                                 want_z, self.fmt)
+        post = FusedPosterior(mean, logvar, kl, lambda: ops.ToNCHW.apply(moments, 2 * zc, self.compute_dtype))
         return post, (z if want_z else None)
 
     def encode(self, x):
         x = x.to(self.device)
         moments, pose_feat = self._encode_nhwc(x.contiguous().float())
         post, _ = self._posterior(moments)
-        return post, ops.ToNCHW.apply(pose_feat, self.embed_dim)
+        return post, ops.ToNCHW.apply(pose_feat, self.embed_dim, self.compute_dtype)
 
     def decode(self, z):
         h = ops.ToNHWC.apply(z.to(self.device), ops.cpad(self.embed_dim), self.compute_dtype)
@@ -294,7 +296,7 @@ class PoseAutoencoder(_Base):
         self.dropout_prob = p = self._get_dropout_prob()
         eps, keep, noise, eps_bbox = self._draw_noise(B, self.feature_dims, p, sample_posterior, input_im.device)
         moments, pose_feat = self._encode_nhwc(input_im)
-        dec_pose, bbox_posterior = self._decode_pose(ops.ToNCHW.apply(pose_feat, self.embed_dim), sample_posterior,
+        dec_pose, bbox_posterior = self._decode_pose(ops.ToNCHW.apply(pose_feat, self.embed_dim, self.compute_dtype), sample_posterior,
                                                      eps_bbox)
         keep_scale = 1.0 / (1.0 - p) if 0 < p < 1.0 else 1.0
         if self.global_step < self.encoder_pretrain_steps:  # AE.py:246-247: decoder skipped

@@ -69,7 +69,8 @@ def conv_fwd(x, w_packed, bias, Cout, geom, impl, residual=None, out_nchw_f32=Fa
         y = torch.empty(B, Cout, Ho, Wo, dtype=torch.float32, device=x.device)
     else:
         y = torch.empty(B, Ho, Wo, CoutP, dtype=x.dtype, device=x.device)
-    call("conv2d_fwd", x, w_packed, bias, residual, y, B, H, W, CinP, CoutP, Cout, geom, act_code(x.dtype), impl,
+    call("conv2d_fwd", x, w_packed, bias, residual, y, B, H, W, CinP, CoutP, Cout, geom, act_code(x.dtype),
+         act_code(x.dtype), impl,
          1 if out_nchw_f32 else 0)
     return y
 

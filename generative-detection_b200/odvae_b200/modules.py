@@ -62,8 +62,10 @@ class GroupNorm(nn.Module):
         self.weight = nn.Parameter(torch.ones(channels))
         self.bias = nn.Parameter(torch.zeros(channels))
 
+    fmt = None  # set by ops.assign_format()
+
     def forward(self, x, silu=False):
-        return ops.GroupNormAct.apply(x, self.weight, self.bias, silu)
+        return ops.GroupNormAct.apply(x, self.weight, self.bias, silu, self.fmt)
 
 
 class ResnetBlock(nn.Module):
@@ -99,20 +101,22 @@ class AttnBlock(nn.Module):
         self.spec_proj = self.proj_out.spec
         self._cache = ops.ParamCache()
 
-    def fused_qkv(self, wq, bq, wk, bk, wv, bv, dtype):
-        """-> (packed [3C][C] weight in `dtype`, fp32 [3C] bias) for the single q|k|v projection."""
+    def fused_qkv(self, wq, bq, wk, bk, wv, bv, code):
+        """-> (packed [3C][C] weight in the format `code`, fp32 [3C] bias) for the single q|k|v projection."""
         C = self.channels
+        if isinstance(code, torch.dtype):
+            code = ops.act_code(code)
 
         def build(old):
             wbuf, bbuf = old if old is not None else (
-                torch.empty(3 * C * C, dtype=dtype, device=wq.device),
+                torch.empty(3 * C * C, dtype=ops.buf_dtype(code), device=wq.device),
                 torch.empty(3 * C, dtype=torch.float32, device=wq.device))
             for i, (w, b) in enumerate(((wq, bq), (wk, bk), (wv, bv))):
-                ops.pack_weight(w.detach(), CONV_1x1, C, C, 0, dtype, out=wbuf[i * C * C:(i + 1) * C * C])
+                ops.pack_weight(w.detach(), CONV_1x1, C, C, 0, code, out=wbuf[i * C * C:(i + 1) * C * C])
                 bbuf[i * C:(i + 1) * C].copy_(b.detach())
             return wbuf, bbuf
 
-        return self._cache.get(("qkv", dtype), (wq, bq, wk, bk, wv, bv), build)
+        return self._cache.get(("qkv", code), (wq, bq, wk, bk, wv, bv), build)
 
     def qkv_grad_buffers(self, wq, bq):
         C = self.channels
@@ -199,6 +203,7 @@ class Encoder(nn.Module):
         self.norm_out = GroupNorm(block_in)
         self.out_channels = 2 * z_channels if double_z else z_channels
         self.conv_out = Conv2d(block_in, self.out_channels, 3, CONV_3x3_S1)
+        ops.assign_format(self, compute_dtype)
 
     def forward_nhwc(self, x):
         """x: NCHW fp32 image -> NHWC activations [B,h,w,pad64(out_channels)]."""
@@ -218,7 +223,7 @@ class Encoder(nn.Module):
         return _run(self.conv_out, h)
 
     def forward(self, x):
-        return ops.ToNCHW.apply(self.forward_nhwc(x), self.out_channels)
+        return ops.ToNCHW.apply(self.forward_nhwc(x), self.out_channels, self.compute_dtype)
 
 
 class Decoder(nn.Module):
@@ -252,6 +257,7 @@ class Decoder(nn.Module):
             self.up.insert(0, lvl)
         self.norm_out = GroupNorm(block_in)
         self.conv_out = Conv2d(block_in, out_ch, 3, CONV_3x3_S1)
+        ops.assign_format(self, compute_dtype)
 
     def forward_nhwc(self, z):
         """z: NHWC [B,h,w,pad64(z_channels)] -> dec NCHW fp32 [B,out_ch,H,W]."""

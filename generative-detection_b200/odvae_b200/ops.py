@@ -14,7 +14,7 @@ Reference call sites are cited per Function; LD/ = submodules/latent-diffusion/.
 import torch
 
 from . import lib
-from .lib import BF16, CONV_1x1, CONV_3x3_S1, CONV_3x3_S2, F32, IMPL_SIMT, IMPL_TC, call
+from .lib import BF16, CONV_1x1, CONV_3x3_S1, CONV_3x3_S2, F16, F32, IMPL_SIMT, IMPL_TC, call
 
 GROUPS = 32      # Normalize(): GroupNorm(num_groups=32, eps=1e-6)  LD model.py:38-39
 GN_EPS = 1e-6
@@ -33,6 +33,78 @@ def act_code(dtype):
     if dtype == torch.float32:
         return F32
     raise TypeError("activations must be float32 or bfloat16, got %s" % dtype)
+
+
+class Format:
+    """Numeric formats of one compute mode (C-ABI dtype codes).
+
+    fwd  : forward activations and packed forward weights of convs / GroupNorm outside attention blocks
+    attn : everything inside an AttnBlock (normalised input, q|k|v, P, O and their packed weights)
+    grad : every activation gradient, dgrad-packed weights and both operands of the weight-gradient GEMMs
+
+    compute_dtype float32  -> fwd = attn = grad = f32  (SIMT engine; the <=1e-4 validation mode)
+    compute_dtype bfloat16 -> fwd = attn = grad = bf16
+    compute_dtype float16  -> the MIXED mode: fwd = IEEE fp16 (11-bit significand: measured 8x lower forward error
+        than bf16, which does not meet the 1e-2 tolerance through ~60 stacked layers), attn = grad = bf16 (range).
+        tcgen05 needs both MMA operands in one format (a mix traps on B200), so the weight-gradient GEMMs read a bf16
+        copy of the forward operand (written by the GroupNorm apply kernel, or by `cast16` at the few other sites).
+
+    Torch labelling: autograd casts a gradient to the dtype of the forward tensor it belongs to, so in the mixed mode
+    forward NHWC buffers are labelled torch.bfloat16 while holding fp16 bit patterns (only this library's kernels
+    ever read them; decode with `.view(torch.float16)`), and gradients are genuine bfloat16 tensors.
+    """
+
+    def __init__(self, fwd, attn, grad):
+        self.fwd, self.attn, self.grad = fwd, attn, grad
+        self.mixed = fwd != grad
+        self.buf = torch.float32 if fwd == F32 else torch.bfloat16
+
+    def __repr__(self):
+        return "Format(fwd=%d, attn=%d, grad=%d)" % (self.fwd, self.attn, self.grad)
+
+
+FORMAT_F32 = Format(F32, F32, F32)
+FORMAT_BF16 = Format(BF16, BF16, BF16)
+FORMAT_MIXED = Format(F16, BF16, BF16)
+
+
+def format_for(compute_dtype):
+    if isinstance(compute_dtype, Format):
+        return compute_dtype
+    return {torch.float32: FORMAT_F32, torch.bfloat16: FORMAT_BF16, torch.float16: FORMAT_MIXED}[compute_dtype]
+
+
+def format_of(x, holder=None):
+    """Format carried by a module/spec (`holder.fmt`), else the one the tensor's torch dtype implies."""
+    fmt = getattr(holder, "fmt", None) if holder is not None else None
+    if fmt is not None:
+        return fmt
+    return FORMAT_F32 if x.dtype == torch.float32 else FORMAT_BF16
+
+
+def assign_format(root, compute_dtype):
+    """Stamp every sub-module and ConvSpec under `root` with the Format of `compute_dtype`."""
+    fmt = format_for(compute_dtype)
+    for m in root.modules():
+        m.fmt = fmt
+        spec = getattr(m, "spec", None)
+        if isinstance(spec, ConvSpec):
+            spec.fmt = fmt
+    return fmt
+
+
+def buf_dtype(code):
+    return torch.float32 if code == F32 else torch.bfloat16
+
+
+def cast16_raw(x, src, dst):
+    """16-bit format conversion of a whole tensor (fp16 <-> bf16); identity when the codes agree."""
+    if src == dst:
+        return x
+    x = _c(x)
+    y = torch.empty_like(x)
+    call("cast16", x, y, x.numel(), src, dst)
+    return y
 
 
 def cpad(c):
@@ -56,8 +128,11 @@ def workspace(nbytes, device, tag):
 _TC_OK = {}
 
 
-def conv_impl(dtype, B, H, W, CinP, CoutP, geom):
-    if dtype != torch.bfloat16:
+def conv_impl(code, B, H, W, CinP, CoutP, geom):
+    """code: operand dtype code (or a torch dtype, for callers that predate Format)."""
+    if isinstance(code, torch.dtype):
+        code = act_code(code)
+    if code == F32:
         return IMPL_SIMT
     key = (B, H, W, CinP, CoutP, geom)
     ok = _TC_OK.get(key)
@@ -67,9 +142,9 @@ def conv_impl(dtype, B, H, W, CinP, CoutP, geom):
     return IMPL_TC if ok else IMPL_SIMT
 
 
-def attn_fused(dtype, N, C):
+def attn_fused(code, N, C):
     """The fused tcgen05 attention core needs 16-bit operands and TMA-tileable shapes."""
-    return dtype == torch.bfloat16 and N % 128 == 0 and C % 64 == 0
+    return code != F32 and N % 128 == 0 and C % 64 == 0
 
 
 def out_hw(geom, H, W):
@@ -99,11 +174,14 @@ class ParamCache:
         return val
 
 
-def pack_weight(w, geom, CoutP, CinP, which, dtype, out=None):
+def pack_weight(w, geom, CoutP, CinP, which, code, out=None):
+    """code: dtype code of the packed copy (a torch dtype is accepted too)."""
+    if isinstance(code, torch.dtype):
+        code = act_code(code)
     k = geom_k(geom)
     if out is None:
-        out = torch.empty(CoutP * CinP * k * k, dtype=dtype, device=w.device)
-    call("pack_conv_weight", w, out, w.shape[0], w.shape[1], geom, CoutP, CinP, which, act_code(dtype))
+        out = torch.empty(CoutP * CinP * k * k, dtype=buf_dtype(code), device=w.device)
+    call("pack_conv_weight", w, out, w.shape[0], w.shape[1], geom, CoutP, CinP, which, code)
     return out
 
 
@@ -120,21 +198,23 @@ def pad_vector(v, n, out=None):
 class ConvSpec:
     """Geometry + caches of one Conv2d (torch.nn.Conv2d call sites)."""
 
+    fmt = None  # set by assign_format(); None = derive from the activation's torch dtype
+
     def __init__(self, cin, cout, geom, cout_pad=None):
         self.cin, self.cout, self.geom = cin, cout, geom
         self.cinp = cpad(cin)
         self.coutp = cout_pad if cout_pad is not None else cpad(cout)
         self.cache = ParamCache()
 
-    def w_fwd(self, w, dtype, coutp=None):
+    def w_fwd(self, w, code, coutp=None):
         coutp = coutp or self.coutp
-        return self.cache.get(("f", dtype, coutp), (w,),
-                              lambda old: pack_weight(w.detach(), self.geom, coutp, self.cinp, 0, dtype, old))
+        return self.cache.get(("f", code, coutp), (w,),
+                              lambda old: pack_weight(w.detach(), self.geom, coutp, self.cinp, 0, code, old))
 
-    def w_dgrad(self, w, dtype, coutp=None):
+    def w_dgrad(self, w, code, coutp=None):
         coutp = coutp or self.coutp
-        return self.cache.get(("d", dtype, coutp), (w,),
-                              lambda old: pack_weight(w.detach(), self.geom, coutp, self.cinp, 1, dtype, old))
+        return self.cache.get(("d", code, coutp), (w,),
+                              lambda old: pack_weight(w.detach(), self.geom, coutp, self.cinp, 1, code, old))
 
     def bias(self, b, n=None):
         n = n or self.coutp
@@ -164,81 +244,110 @@ def _ret(g, direct):
 # ------------------------------------------------------------------------------------------------
 # raw (non-autograd) kernel wrappers
 # ------------------------------------------------------------------------------------------------
-def conv_fwd_raw(x, spec, w, b, residual=None, out_nchw=False):
+def conv_fwd_raw(x, spec, w, b, residual=None, out_nchw=False, op=None, out=None):
+    """op: format code of x and the packed weights; out: format code of the NHWC y / residual.
+    Defaults: the spec's Format (fwd code for both), else what x's torch dtype implies."""
+    fmt = format_of(x, spec)
+    op = fmt.fwd if op is None else op
+    out = fmt.fwd if out is None else out
     B, H, W, CinP = x.shape
     assert CinP == spec.cinp, (CinP, spec.cinp)
     Ho, Wo = out_hw(spec.geom, H, W)
     if out_nchw:
         coutp = 16 if spec.cout <= 16 else spec.coutp
-        impl = conv_impl(x.dtype, B, H, W, CinP, 64, spec.geom) if coutp == 16 else \
-            conv_impl(x.dtype, B, H, W, CinP, coutp, spec.geom)
+        impl = conv_impl(op, B, H, W, CinP, 64, spec.geom) if coutp == 16 else \
+            conv_impl(op, B, H, W, CinP, coutp, spec.geom)
         y = torch.empty(B, spec.cout, Ho, Wo, dtype=torch.float32, device=x.device)
-        call("conv2d_fwd", x, spec.w_fwd(w, x.dtype, coutp), None if b is None else b.detach(), None, y, B, H, W,
-             CinP, coutp, spec.cout, spec.geom, act_code(x.dtype), impl, 1)
+        call("conv2d_fwd", x, spec.w_fwd(w, op, coutp), None if b is None else b.detach(), None, y, B, H, W,
+             CinP, coutp, spec.cout, spec.geom, op, out, impl, 1)
         return y
-    impl = conv_impl(x.dtype, B, H, W, CinP, spec.coutp, spec.geom)
-    y = torch.empty(B, Ho, Wo, spec.coutp, dtype=x.dtype, device=x.device)
-    call("conv2d_fwd", x, spec.w_fwd(w, x.dtype), spec.bias(b), residual, y, B, H, W, CinP, spec.coutp, spec.cout,
-         spec.geom, act_code(x.dtype), impl, 0)
+    impl = conv_impl(op, B, H, W, CinP, spec.coutp, spec.geom)
+    y = torch.empty(B, Ho, Wo, spec.coutp, dtype=buf_dtype(out), device=x.device)
+    call("conv2d_fwd", x, spec.w_fwd(w, op), spec.bias(b), residual, y, B, H, W, CinP, spec.coutp, spec.cout,
+         spec.geom, op, out, impl, 0)
     return y
 
 
 def conv_dgrad_raw(dy, spec, w, in_hw, dx_add=None):
+    """All operands in the gradient format."""
+    g = format_of(dy, spec).grad
     B, Ho, Wo, CoutP = dy.shape
     H, W = in_hw
-    impl = conv_impl(dy.dtype, B, H, W, spec.cinp, CoutP, spec.geom)
+    impl = conv_impl(g, B, H, W, spec.cinp, CoutP, spec.geom)
     dx = torch.empty(B, H, W, spec.cinp, dtype=dy.dtype, device=dy.device)
-    call("conv2d_dgrad", dy, spec.w_dgrad(w, dy.dtype, CoutP), dx_add, dx, B, H, W, spec.cinp, CoutP, spec.geom,
-         act_code(dy.dtype), impl)
+    call("conv2d_dgrad", dy, spec.w_dgrad(w, g, CoutP), dx_add, dx, B, H, W, spec.cinp, CoutP, spec.geom, g, impl)
     return dx
 
 
 def conv_wgrad_raw(x, dy, spec, w, b):
-    """-> (dw, db) as autograd return values (None where written straight into the gradient arena)."""
+    """x must already be in the GRADIENT format (mixed mode: the bf16 copy of the fp16 forward operand).
+    -> (dw, db) as autograd return values (None where written straight into the gradient arena)."""
+    g = format_of(dy, spec).grad
     B, H, W, CinP = x.shape
     CoutP = dy.shape[-1]
-    impl = conv_impl(x.dtype, B, H, W, CinP, CoutP, spec.geom)
+    impl = conv_impl(g, B, H, W, CinP, CoutP, spec.geom)
     dw, dw_direct = _new_grad(w)
     db, db_direct = (None, True) if b is None else _new_grad(b)
     nbytes = call("conv2d_wgrad_workspace_bytes", B, H, W, CinP, CoutP, spec.geom, impl)
     ws = workspace(nbytes, x.device, "wgrad")
-    call("conv2d_wgrad", x, dy, dw, db, B, H, W, CinP, CoutP, spec.cin, spec.cout, spec.geom, act_code(x.dtype),
-         impl, 0, ws, ws.numel())
+    call("conv2d_wgrad", x, dy, dw, db, B, H, W, CinP, CoutP, spec.cin, spec.cout, spec.geom, g, impl, 0, ws,
+         ws.numel())
     return _ret(dw, dw_direct), _ret(db, db_direct)
 
 
-def gn_stats_raw(x, C):
+def grad_operand(x, fmt):
+    """The copy of a forward activation that a weight-gradient GEMM may contract with dy."""
+    return cast16_raw(x, fmt.fwd, fmt.grad) if fmt.mixed else x
+
+
+def gn_stats_raw(x, C, code=None):
     B, H, W, Cp = x.shape
     assert Cp == C, "GroupNorm runs on unpadded channel counts (C % 64 == 0)"
+    code = act_code(x.dtype) if code is None else code
     stats = torch.empty(B, GROUPS, 2, dtype=torch.float32, device=x.device)
     nbytes = call("groupnorm_workspace_bytes", B, H * W, C, GROUPS)
     ws = workspace(nbytes, x.device, "gn")
-    call("groupnorm_stats", x, stats, B, H * W, C, GROUPS, GN_EPS, act_code(x.dtype), ws, ws.numel())
+    call("groupnorm_stats", x, stats, B, H * W, C, GROUPS, GN_EPS, code, ws, ws.numel())
     return stats
 
 
-def gn_apply_raw(x, stats, gamma, beta, silu):
+def gn_apply_raw(x, stats, gamma, beta, silu, in_code=None, out_code=None, copy_code=None):
+    """-> y, or (y, y2) when copy_code is given (second copy of the output in that format, same kernel)."""
     B, H, W, C = x.shape
-    y = torch.empty_like(x)
-    call("groupnorm_apply", x, stats, gamma.detach(), beta.detach(), y, B, H * W, C, GROUPS, 1 if silu else 0,
-         act_code(x.dtype))
-    return y
+    in_code = act_code(x.dtype) if in_code is None else in_code
+    out_code = in_code if out_code is None else out_code
+    y = torch.empty(B, H, W, C, dtype=buf_dtype(out_code), device=x.device)
+    y2 = None if copy_code is None else torch.empty(B, H, W, C, dtype=buf_dtype(copy_code), device=x.device)
+    call("groupnorm_apply", x, stats, gamma.detach(), beta.detach(), y, y2, B, H * W, C, GROUPS, 1 if silu else 0,
+         in_code, out_code, copy_code if copy_code is not None else out_code)
+    return y if copy_code is None else (y, y2)
 
 
-def gn_bwd_raw(x, stats, gamma, beta, dy, silu, dx_add=None):
+def gn_apply_pair(x, stats, gamma, beta, silu, fmt):
+    """(forward operand, weight-gradient operand) of the conv that consumes this GroupNorm output."""
+    if fmt.mixed:
+        return gn_apply_raw(x, stats, gamma, beta, silu, fmt.fwd, fmt.fwd, fmt.grad)
+    y = gn_apply_raw(x, stats, gamma, beta, silu, fmt.fwd, fmt.fwd)
+    return y, y
+
+
+def gn_bwd_raw(x, stats, gamma, beta, dy, silu, dx_add=None, x_code=None, g_code=None):
     B, H, W, C = x.shape
-    dx = torch.empty_like(x)
+    x_code = act_code(x.dtype) if x_code is None else x_code
+    g_code = act_code(dy.dtype) if g_code is None else g_code
+    dx = torch.empty_like(dy)
     dgamma, g_direct = _new_grad(gamma)
     dbeta, b_direct = _new_grad(beta)
     nbytes = call("groupnorm_workspace_bytes", B, H * W, C, GROUPS)
     ws = workspace(nbytes, x.device, "gn")
     call("groupnorm_bwd", x, stats, gamma.detach(), beta.detach(), dy, dx_add, dx, dgamma, dbeta, B, H * W, C,
-         GROUPS, 1 if silu else 0, act_code(x.dtype), 0, ws, ws.numel())
+         GROUPS, 1 if silu else 0, x_code, g_code, 0, ws, ws.numel())
     return dx, _ret(dgamma, g_direct), _ret(dbeta, b_direct)
 
 
 def gemm_raw(A, Bm, D, M, N, K, batch, lda, ldb, ldd, sA, sB, sD, a_mn, b_mn, alpha=1.0, bias=None, residual=None):
-    """D[b] = alpha * op(A[b]) op(B[b])^T (+bias)(+residual); engine chosen by the operand dtype."""
+    """D[b] = alpha * op(A[b]) op(B[b])^T (+bias)(+residual); engine chosen by the operand dtype
+    (bf16 operands -> tcgen05; attention blocks run in bf16 in both 16-bit modes)."""
     if A.dtype == torch.bfloat16:
         call("gemm_bf16", A, Bm, D, M, N, K, batch, lda, ldb, ldd, sA, sB, sD, int(a_mn), int(b_mn),
              act_code(D.dtype), float(alpha), bias, residual)
@@ -248,17 +357,20 @@ def gemm_raw(A, Bm, D, M, N, K, batch, lda, ldb, ldd, sA, sB, sD, a_mn, b_mn, al
     return D
 
 
-def nchw_to_nhwc_raw(x, Cpad, dtype, scale=1.0, shift=0.0):
+def nchw_to_nhwc_raw(x, Cpad, code, scale=1.0, shift=0.0):
+    """code: dtype code of the NHWC result (a torch dtype is accepted too)."""
+    if isinstance(code, torch.dtype):
+        code = act_code(code)
     B, C, H, W = x.shape
-    out = torch.empty(B, H, W, Cpad, dtype=dtype, device=x.device)
-    call("nchw_to_nhwc", x, out, B, C, H, W, Cpad, act_code(dtype), float(scale), float(shift))
+    out = torch.empty(B, H, W, Cpad, dtype=buf_dtype(code), device=x.device)
+    call("nchw_to_nhwc", x, out, B, C, H, W, Cpad, code, float(scale), float(shift))
     return out
 
 
-def nhwc_to_nchw_raw(x, C):
+def nhwc_to_nchw_raw(x, C, code=None):
     B, H, W, Cpad = x.shape
     out = torch.empty(B, C, H, W, dtype=torch.float32, device=x.device)
-    call("nhwc_to_nchw", x, out, B, C, H, W, Cpad, act_code(x.dtype))
+    call("nhwc_to_nchw", x, out, B, C, H, W, Cpad, act_code(x.dtype) if code is None else code)
     return out
 
 
@@ -271,24 +383,26 @@ def _c(t):
 # ------------------------------------------------------------------------------------------------
 class ToNHWC(torch.autograd.Function):
     @staticmethod
-    def forward(ctx, x, Cpad, dtype):
-        ctx.C = x.shape[1]
-        return nchw_to_nhwc_raw(_c(x.float()), Cpad, dtype)
+    def forward(ctx, x, Cpad, compute_dtype):
+        fmt = format_for(compute_dtype)
+        ctx.C, ctx.fmt = x.shape[1], fmt
+        return nchw_to_nhwc_raw(_c(x.float()), Cpad, fmt.fwd)
 
     @staticmethod
     def backward(ctx, dy):
-        return nhwc_to_nchw_raw(_c(dy), ctx.C), None, None
+        return nhwc_to_nchw_raw(_c(dy), ctx.C, ctx.fmt.grad), None, None
 
 
 class ToNCHW(torch.autograd.Function):
     @staticmethod
-    def forward(ctx, x, C):
-        ctx.Cpad, ctx.dtype = x.shape[-1], x.dtype
-        return nhwc_to_nchw_raw(x, C)
+    def forward(ctx, x, C, compute_dtype=None):
+        fmt = format_for(compute_dtype) if compute_dtype is not None else format_of(x)
+        ctx.Cpad, ctx.fmt = x.shape[-1], fmt
+        return nhwc_to_nchw_raw(x, C, fmt.fwd)
 
     @staticmethod
     def backward(ctx, dy):
-        return nchw_to_nhwc_raw(_c(dy.float()), ctx.Cpad, ctx.dtype), None
+        return nchw_to_nhwc_raw(_c(dy.float()), ctx.Cpad, ctx.fmt.grad), None, None
 
 
 # ------------------------------------------------------------------------------------------------
@@ -298,21 +412,22 @@ class Conv(torch.autograd.Function):
     @staticmethod
     def forward(ctx, x, w, b, spec, out_nchw, need_dx):
         ctx.spec, ctx.out_nchw, ctx.need_dx = spec, out_nchw, need_dx
+        ctx.fmt = format_of(x, spec)
         ctx.save_for_backward(x, w, b)
         return conv_fwd_raw(x, spec, w, b, out_nchw=out_nchw)
 
     @staticmethod
     def backward(ctx, dy):
         x, w, b = ctx.saved_tensors
-        spec = ctx.spec
+        spec, fmt = ctx.spec, ctx.fmt
         if ctx.out_nchw:  # dec_obj gradient arrives NCHW fp32 (masked-L1 backward): bring it to NHWC
-            dy = nchw_to_nhwc_raw(_c(dy.float()), cpad(spec.cout), x.dtype)
+            dy = nchw_to_nhwc_raw(_c(dy.float()), cpad(spec.cout), fmt.grad)
         else:
             dy = _c(dy)
         dx = None
         if ctx.need_dx and ctx.needs_input_grad[0]:
             dx = conv_dgrad_raw(dy, spec, w, x.shape[1:3])
-        dw, db = conv_wgrad_raw(x, dy, spec, w, b)
+        dw, db = conv_wgrad_raw(grad_operand(x, fmt), dy, spec, w, b)
         return dx, dw, db, None, None, None
 
 
@@ -321,58 +436,63 @@ class Conv(torch.autograd.Function):
 # ------------------------------------------------------------------------------------------------
 class GroupNormAct(torch.autograd.Function):
     @staticmethod
-    def forward(ctx, x, gamma, beta, silu):
-        stats = gn_stats_raw(x, x.shape[-1])
-        ctx.silu = silu
+    def forward(ctx, x, gamma, beta, silu, fmt=None):
+        fmt = fmt if fmt is not None else format_of(x)
+        stats = gn_stats_raw(x, x.shape[-1], fmt.fwd)
+        ctx.silu, ctx.fmt = silu, fmt
         ctx.save_for_backward(x, stats, gamma, beta)
-        return gn_apply_raw(x, stats, gamma, beta, silu)
+        return gn_apply_raw(x, stats, gamma, beta, silu, fmt.fwd, fmt.fwd)
 
     @staticmethod
     def backward(ctx, dy):
         x, stats, gamma, beta = ctx.saved_tensors
-        dx, dg, db = gn_bwd_raw(x, stats, gamma, beta, _c(dy), ctx.silu)
-        return dx, dg, db, None
+        dx, dg, db = gn_bwd_raw(x, stats, gamma, beta, _c(dy), ctx.silu, x_code=ctx.fmt.fwd, g_code=ctx.fmt.grad)
+        return dx, dg, db, None, None
 
 
 # ------------------------------------------------------------------------------------------------
 # ResnetBlock  (LD model.py:121-141, temb=None, dropout 0):
 #   out = shortcut(x) + conv2(silu(GN2(conv1(silu(GN1(x))))))
+# Saved for backward: x, h1 (GroupNorm inputs, forward format) and a1, a2 in the GRADIENT format (they are only
+# needed again as weight-gradient operands; the mixed mode's GN apply kernel writes that copy alongside the fp16 one).
 # ------------------------------------------------------------------------------------------------
 class ResBlock(torch.autograd.Function):
     @staticmethod
     def forward(ctx, x, g1, b1, w1, c1b, g2, b2, w2, c2b, wn, nb, blk):
-        s1 = gn_stats_raw(x, blk.cin)
-        a1 = gn_apply_raw(x, s1, g1, b1, True)
-        h1 = conv_fwd_raw(a1, blk.spec1, w1, c1b)
-        s2 = gn_stats_raw(h1, blk.cout)
-        a2 = gn_apply_raw(h1, s2, g2, b2, True)
-        sc = x if wn is None else conv_fwd_raw(x, blk.spec_nin, wn, nb)
-        out = conv_fwd_raw(a2, blk.spec2, w2, c2b, residual=sc)
-        ctx.blk = blk
+        fmt = format_of(x, blk)
+        s1 = gn_stats_raw(x, blk.cin, fmt.fwd)
+        a1, a1g = gn_apply_pair(x, s1, g1, b1, True, fmt)
+        h1 = conv_fwd_raw(a1, blk.spec1, w1, c1b, op=fmt.fwd, out=fmt.fwd)
+        del a1
+        s2 = gn_stats_raw(h1, blk.cout, fmt.fwd)
+        a2, a2g = gn_apply_pair(h1, s2, g2, b2, True, fmt)
+        sc = x if wn is None else conv_fwd_raw(x, blk.spec_nin, wn, nb, op=fmt.fwd, out=fmt.fwd)
+        out = conv_fwd_raw(a2, blk.spec2, w2, c2b, residual=sc, op=fmt.fwd, out=fmt.fwd)
+        ctx.blk, ctx.fmt = blk, fmt
         ctx.has_nin = wn is not None
-        ctx.save_for_backward(x, s1, a1, h1, s2, a2, g1, b1, w1, c1b, g2, b2, w2, c2b, wn, nb)
+        ctx.save_for_backward(x, s1, a1g, h1, s2, a2g, g1, b1, w1, c1b, g2, b2, w2, c2b, wn, nb)
         return out
 
     @staticmethod
     def backward(ctx, dout):
         x, s1, a1, h1, s2, a2, g1, b1, w1, c1b, g2, b2, w2, c2b, wn, nb = ctx.saved_tensors
-        blk = ctx.blk
+        blk, fmt = ctx.blk, ctx.fmt
         dout = _c(dout)
         hw = x.shape[1:3]
         dwn = dnb = None
         if ctx.has_nin:
             dsc = conv_dgrad_raw(dout, blk.spec_nin, wn, hw)
-            dwn, dnb = conv_wgrad_raw(x, dout, blk.spec_nin, wn, nb)
+            dwn, dnb = conv_wgrad_raw(grad_operand(x, fmt), dout, blk.spec_nin, wn, nb)
         else:
             dsc = dout
         da2 = conv_dgrad_raw(dout, blk.spec2, w2, hw)
         dw2, dc2b = conv_wgrad_raw(a2, dout, blk.spec2, w2, c2b)
-        dh1, dg2, db2 = gn_bwd_raw(h1, s2, g2, b2, da2, True)
+        dh1, dg2, db2 = gn_bwd_raw(h1, s2, g2, b2, da2, True, x_code=fmt.fwd, g_code=fmt.grad)
         del da2
         da1 = conv_dgrad_raw(dh1, blk.spec1, w1, hw)
         dw1, dc1b = conv_wgrad_raw(a1, dh1, blk.spec1, w1, c1b)
         del dh1
-        dx, dg1, db1 = gn_bwd_raw(x, s1, g1, b1, da1, True, dx_add=dsc)
+        dx, dg1, db1 = gn_bwd_raw(x, s1, g1, b1, da1, True, dx_add=dsc, x_code=fmt.fwd, g_code=fmt.grad)
         return dx, dg1, db1, dw1, dc1b, dg2, db2, dw2, dc2b, dwn, dnb, None
 
 
@@ -386,31 +506,33 @@ class AttnBlock(torch.autograd.Function):
     def forward(ctx, x, gamma, beta, wq, bq, wk, bk, wv, bv, wp, bp, blk):
         B, H, W, C = x.shape
         N = H * W
-        dt = x.dtype
-        stats = gn_stats_raw(x, C)
-        hn = gn_apply_raw(x, stats, gamma, beta, False)
-        wqkv, bqkv = blk.fused_qkv(wq, bq, wk, bk, wv, bv, dt)
+        fmt = format_of(x, blk)
+        ac = fmt.attn            # format code inside the block (bf16 in both 16-bit modes)
+        dt = buf_dtype(ac)
+        stats = gn_stats_raw(x, C, fmt.fwd)
+        hn = gn_apply_raw(x, stats, gamma, beta, False, fmt.fwd, ac)
+        wqkv, bqkv = blk.fused_qkv(wq, bq, wk, bk, wv, bv, ac)
         qkv = torch.empty(B, H, W, 3 * C, dtype=dt, device=x.device)
-        impl = conv_impl(dt, B, H, W, C, 3 * C, CONV_1x1)
-        call("conv2d_fwd", hn, wqkv, bqkv, None, qkv, B, H, W, C, 3 * C, 3 * C, CONV_1x1, act_code(dt), impl, 0)
+        impl = conv_impl(ac, B, H, W, C, 3 * C, CONV_1x1)
+        call("conv2d_fwd", hn, wqkv, bqkv, None, qkv, B, H, W, C, 3 * C, 3 * C, CONV_1x1, ac, ac, impl, 0)
         q, k, v = qkv[..., :C], qkv[..., C:2 * C], qkv[..., 2 * C:]
         P = torch.empty(B, N, N, dtype=dt, device=x.device)
         scale = float(int(C) ** (-0.5))
-        if attn_fused(dt, N, C):
+        if attn_fused(ac, N, C):
             # q k^T and the softmax in two tcgen05 GEMM passes; the fp32 scores never reach HBM
             nbytes = call("attn_softmax_workspace_bytes", B, N)
             ws = workspace(nbytes, x.device, "attn")
-            call("attn_scores_softmax", q, k, P, B, N, C, 3 * C, 3 * C, N * 3 * C, N * 3 * C, scale, act_code(dt), ws,
+            call("attn_scores_softmax", q, k, P, B, N, C, 3 * C, 3 * C, N * 3 * C, N * 3 * C, scale, ac, ws,
                  ws.numel())
         else:
             S = torch.empty(B, N, N, dtype=torch.float32, device=x.device)
             gemm_raw(q, k, S, N, N, C, B, 3 * C, 3 * C, N, N * 3 * C, N * 3 * C, N * N, False, False)
-            call("softmax_rows", S, P, B * N, N, scale, act_code(dt))
+            call("softmax_rows", S, P, B * N, N, scale, ac)
             del S
         O = torch.empty(B, H, W, C, dtype=dt, device=x.device)
         gemm_raw(P, v, O, N, C, N, B, N, 3 * C, C, N * N, N * 3 * C, N * C, False, True)
-        out = conv_fwd_raw(O, blk.spec_proj, wp, bp, residual=x)
-        ctx.blk = blk
+        out = conv_fwd_raw(O, blk.spec_proj, wp, bp, residual=x, op=ac, out=fmt.fwd)  # adds into the residual stream
+        ctx.blk, ctx.fmt = blk, fmt
         ctx.save_for_backward(x, stats, hn, qkv, P, O, gamma, beta, wq, bq, wk, bk, wv, bv, wp, bp)
         return out
 
@@ -420,7 +542,9 @@ class AttnBlock(torch.autograd.Function):
         blk = ctx.blk
         B, H, W, C = x.shape
         N = H * W
-        dt = x.dtype
+        fmt = ctx.fmt
+        ac = fmt.attn
+        dt = buf_dtype(ac)
         dout = _c(dout)
         scale = float(int(C) ** (-0.5))
         q, k, v = qkv[..., :C], qkv[..., C:2 * C], qkv[..., 2 * C:]
@@ -432,32 +556,32 @@ class AttnBlock(torch.autograd.Function):
         gemm_raw(P, dO, dv, N, C, N, B, N, C, 3 * C, N * N, N * C, N * 3 * C, True, True)
         # dP[i,j] = sum_c dO[i,c] v[j,c]
         dS = torch.empty(B, N, N, dtype=dt, device=x.device)
-        if attn_fused(dt, N, C):
+        if attn_fused(ac, N, C):
             # delta_i = sum_j P_ij dP_ij = sum_c dO_ic O_ic; dS = P * (dO v^T - delta) * scale in the GEMM epilogue
             delta = torch.empty(B * N, dtype=torch.float32, device=x.device)
-            call("rowdot", dO, O, delta, B * N, C, C, C, act_code(dt))
-            call("attn_dsoftmax", dO, v, P, delta, dS, B, N, C, C, 3 * C, N * C, N * 3 * C, scale, act_code(dt))
+            call("rowdot", dO, O, delta, B * N, C, C, C, ac)
+            call("attn_dsoftmax", dO, v, P, delta, dS, B, N, C, C, 3 * C, N * C, N * 3 * C, scale, ac)
         else:
             dP = torch.empty(B, N, N, dtype=torch.float32, device=x.device)
             gemm_raw(dO, v, dP, N, N, C, B, C, 3 * C, N, N * C, N * 3 * C, N * N, False, False)
-            call("softmax_rows_bwd", dP, P, dS, B * N, N, scale, act_code(dt))
+            call("softmax_rows_bwd", dP, P, dS, B * N, N, scale, ac)
             del dP
         # dQ[i,c] = sum_j dS[i,j] k[j,c] ; dK[j,c] = sum_i dS[i,j] q[i,c]
         gemm_raw(dS, k, dq, N, C, N, B, N, 3 * C, 3 * C, N * N, N * 3 * C, N * 3 * C, False, True)
         gemm_raw(dS, q, dk, N, C, N, B, N, 3 * C, 3 * C, N * N, N * 3 * C, N * 3 * C, True, True)
         del dS
         # fused qkv projection backward: dgrad as a GEMM against the forward packing ([3C][C], N-major view)
-        wqkv, _ = blk.fused_qkv(wq, bq, wk, bk, wv, bv, dt)
+        wqkv, _ = blk.fused_qkv(wq, bq, wk, bk, wv, bv, ac)
         dhn = torch.empty_like(hn)
         M = B * N
         gemm_raw(dqkv, wqkv, dhn, M, C, 3 * C, 1, 3 * C, C, C, 0, 0, 0, False, True)
         dwqkv, dbqkv, direct = blk.qkv_grad_buffers(wq, bq)
-        impl = conv_impl(dt, B, H, W, C, 3 * C, CONV_1x1)
+        impl = conv_impl(ac, B, H, W, C, 3 * C, CONV_1x1)
         nbytes = call("conv2d_wgrad_workspace_bytes", B, H, W, C, 3 * C, CONV_1x1, impl)
         ws = workspace(nbytes, x.device, "wgrad")
-        call("conv2d_wgrad", hn, dqkv, dwqkv, dbqkv, B, H, W, C, 3 * C, C, 3 * C, CONV_1x1, act_code(dt), impl, 0, ws,
+        call("conv2d_wgrad", hn, dqkv, dwqkv, dbqkv, B, H, W, C, 3 * C, C, 3 * C, CONV_1x1, ac, impl, 0, ws,
              ws.numel())
-        dx, dg, db = gn_bwd_raw(x, stats, gamma, beta, dhn, False, dx_add=dout)
+        dx, dg, db = gn_bwd_raw(x, stats, gamma, beta, dhn, False, dx_add=dout, x_code=fmt.fwd, g_code=fmt.grad)
         if grad_dst(wq) is not None:  # arena mode: device-to-device copies of the three row blocks
             for i, (w_, b_) in enumerate(((wq, bq), (wk, bk), (wv, bv))):
                 grad_dst(w_).copy_(dwqkv[i * C:(i + 1) * C].view(C, C, 1, 1))
@@ -473,6 +597,7 @@ class AttnBlock(torch.autograd.Function):
 # Upsample  (LD model.py:53-57): nearest 2x, then 3x3 conv.  Only the low-resolution input is kept.
 # ------------------------------------------------------------------------------------------------
 def upsample2x_raw(x):
+    """Nearest 2x: a pure copy, so any 16-bit format goes through the 16-bit kernel."""
     B, H, W, C = x.shape
     y = torch.empty(B, 2 * H, 2 * W, C, dtype=x.dtype, device=x.device)
     call("upsample2x", x, y, B, H, W, C, act_code(x.dtype))
@@ -483,22 +608,22 @@ class UpsampleConv(torch.autograd.Function):
     @staticmethod
     def forward(ctx, x, w, b, spec):
         u = upsample2x_raw(x)
-        ctx.spec = spec
+        ctx.spec, ctx.fmt = spec, format_of(x, spec)
         ctx.save_for_backward(x, w, b)
         return conv_fwd_raw(u, spec, w, b)
 
     @staticmethod
     def backward(ctx, dy):
         x, w, b = ctx.saved_tensors
-        spec = ctx.spec
+        spec, fmt = ctx.spec, ctx.fmt
         dy = _c(dy)
         B, H, W, C = x.shape
-        u = upsample2x_raw(x)
+        u = upsample2x_raw(grad_operand(x, fmt))  # re-materialised in the gradient format for the wgrad GEMM
         dw, db = conv_wgrad_raw(u, dy, spec, w, b)
         del u
         du = conv_dgrad_raw(dy, spec, w, (2 * H, 2 * W))
-        dx = torch.empty_like(x)
-        call("upsample2x_bwd", du, dx, B, H, W, C, act_code(x.dtype))
+        dx = torch.empty(B, H, W, C, dtype=dy.dtype, device=dy.device)
+        call("upsample2x_bwd", du, dx, B, H, W, C, fmt.grad)
         return dx, dw, db, None
 
 
@@ -508,7 +633,9 @@ class UpsampleConv(torch.autograd.Function):
 # ------------------------------------------------------------------------------------------------
 class SampleKL(torch.autograd.Function):
     @staticmethod
-    def forward(ctx, moments, enc_pose, eps, keep, noise, keep_scale, Cz, CzPad, want_z):
+    def forward(ctx, moments, enc_pose, eps, keep, noise, keep_scale, Cz, CzPad, want_z, fmt=None):
+        fmt = fmt if fmt is not None else format_of(moments)
+        ctx.fmt = fmt
         B, H, W, ld = moments.shape
         HW = H * W
         dev = moments.device
@@ -517,7 +644,7 @@ class SampleKL(torch.autograd.Function):
         kl = torch.empty(B, dtype=torch.float32, device=dev)
         z = torch.empty(B, H, W, CzPad, dtype=moments.dtype, device=dev) if want_z else None
         call("sample_kl_fwd", moments, eps, keep, noise, enc_pose, float(keep_scale), mean, logvar, z, kl, B, HW, Cz,
-             CzPad, ld, act_code(moments.dtype))
+             CzPad, ld, fmt.fwd)
         ctx.cfg = (Cz, CzPad, ld, float(keep_scale), moments.dtype, enc_pose is not None)
         ctx.save_for_backward(mean, logvar, eps, keep)
         if z is None:
@@ -539,10 +666,10 @@ class SampleKL(torch.autograd.Function):
         dmom = torch.empty(B, H, W, ld, dtype=dtype, device=dev)
         dpose = torch.empty(B, Cz * H * W, dtype=torch.float32, device=dev) if (has_pose and dz is not None) else None
         call("sample_kl_bwd", dz, dkl, dmean, dlogvar, mean, logvar, eps, keep, keep_scale, dmom, dpose, B, H * W, Cz,
-             CzPad, ld, act_code(dtype))
+             CzPad, ld, ctx.fmt.grad)
         if has_pose and dpose is None:
             dpose = torch.zeros(B, Cz * H * W, dtype=torch.float32, device=dev)
-        return dmom, dpose, None, None, None, None, None, None, None
+        return dmom, dpose, None, None, None, None, None, None, None, None
 
 
 # ------------------------------------------------------------------------------------------------

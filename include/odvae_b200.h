@@ -75,17 +75,19 @@ int odvae_minmax(const float* src, int64_t n, float* out2, void* workspace, size
  *   which = 0: forward   [CoutP][taps][CinP]   (K-major rows per output channel)
  *   which = 1: dgrad     [CinP][taps'][CoutP]  (taps rotated 180 degrees); for ODVAE_CONV_3x3_S2 four
  *              input-parity-phase matrices [CinP][nt*CoutP] (nt = 4,2,2,1) are concatenated
- * act_dtype selects bf16 (TC path) or f32 (SIMT path) packing. Padded rows/cols are zero. */
+ * act_dtype selects bf16 / fp16 (TC path) or f32 (SIMT path) packing. Padded rows/cols are zero. */
 int odvae_pack_conv_weight(const float* w_oihw, void* packed, int Cout, int Cin, int geom, int CoutP, int CinP,
                            int which, int act_dtype, void* stream);
 /* 1 when fwd, dgrad and wgrad of this conv can all run on the tcgen05 engine (TMA tiling constraints:
  * CinP % 64 == 0, CoutP % 64 == 0 for dgrad, power-of-two output width, >= 128 output pixels per image). */
 int odvae_conv2d_tc_supported(int B, int H, int W, int CinP, int CoutP, int geom);
-/* y = conv(x, w) + bias (+ residual).  `residual` (same layout as y) may be NULL.
+/* y = conv(x, w) + bias (+ residual).  `residual` (same layout and format as y) may be NULL.
+ * act_dtype: format of x and w_packed (f32 | bf16 | fp16); out_dtype: format of the NHWC y / residual (f32 iff
+ * act_dtype is f32; bf16 or fp16 otherwise, independent of the operand format).
  * out_nchw_f32 != 0 writes y as NCHW fp32 [B,Cout,Ho,Wo] instead (decoder.conv_out -> dec_obj). */
 int odvae_conv2d_fwd(const void* x, const void* w_packed, const float* bias, const void* residual, void* y,
-                     int B, int H, int W, int CinP, int CoutP, int Cout, int geom, int act_dtype, int impl,
-                     int out_nchw_f32, void* stream);
+                     int B, int H, int W, int CinP, int CoutP, int Cout, int geom, int act_dtype, int out_dtype,
+                     int impl, int out_nchw_f32, void* stream);
 /* dx = conv_transpose(dy, w) (+ dx_add).  dy: NHWC [B,Ho,Wo,CoutP]; dx: NHWC [B,H,W,CinP].
  * `w_packed` is the which=1 packing. */
 int odvae_conv2d_dgrad(const void* dy, const void* w_packed_dgrad, const void* dx_add, void* dx, int B, int H,
@@ -148,12 +150,18 @@ int odvae_rowdot(const void* a, const void* b, float* out, int64_t rows, int C, 
 size_t odvae_groupnorm_workspace_bytes(int B, int HW, int C, int G);
 int odvae_groupnorm_stats(const void* x, float* stats, int B, int HW, int C, int G, float eps, int act_dtype,
                           void* workspace, size_t ws_bytes, void* stream);
-int odvae_groupnorm_apply(const void* x, const float* stats, const float* gamma, const float* beta, void* y,
-                          int B, int HW, int C, int G, int silu, int act_dtype, void* stream);
-/* dx = d/dx [silu](GN(x)) . dy (+ dx_add);  dgamma/dbeta fp32 [C] (accumulate != 0 adds). */
+/* y (and, if y2 != NULL, a second copy y2 in out2_dtype) = [silu](GN(x)). Format triples (in, out, out2):
+ * f32->f32; bf16->bf16(+bf16); fp16->fp16(+bf16: the copy a weight-gradient GEMM contracts with bf16 dy);
+ * fp16->bf16 (attention blocks of the mixed mode). */
+int odvae_groupnorm_apply(const void* x, const float* stats, const float* gamma, const float* beta, void* y, void* y2,
+                          int B, int HW, int C, int G, int silu, int in_dtype, int out_dtype, int out2_dtype,
+                          void* stream);
+/* dx = d/dx [silu](GN(x)) . dy (+ dx_add);  dgamma/dbeta fp32 [C] (accumulate != 0 adds).
+ * act_dtype = format of x, grad_dtype = format of dy / dx_add / dx: (f32,f32), (bf16,bf16) or (fp16,bf16). */
 int odvae_groupnorm_bwd(const void* x, const float* stats, const float* gamma, const float* beta, const void* dy,
                         const void* dx_add, void* dx, float* dgamma, float* dbeta, int B, int HW, int C, int G,
-                        int silu, int act_dtype, int accumulate, void* workspace, size_t ws_bytes, void* stream);
+                        int silu, int act_dtype, int grad_dtype, int accumulate, void* workspace, size_t ws_bytes,
+                        void* stream);
 
 /* ---------------------------------------------------------------------------------------------
  * Attention core of AttnBlock (model.py:183-198): single head, scale = C^-0.5.
@@ -272,6 +280,10 @@ int odvae_rescale(const float* src, float* dst, int64_t n, const float* minmax, 
  * act = 1 tanh, 2 silu.  bwd: dx = dy * act'(x) with x the pre-activation. */
 int odvae_act_fwd(const float* x, float* y, int64_t n, int act, void* stream);
 int odvae_act_bwd(const float* x, const float* dy, float* dx, int64_t n, int act, void* stream);
+
+/* 16-bit format conversion, n % 8 == 0: (ODVAE_F16 -> ODVAE_BF16) or (ODVAE_BF16 -> ODVAE_F16, saturating).
+ * Mixed mode: the bf16 copy of an fp16 forward activation that a weight-gradient GEMM contracts with bf16 dy. */
+int odvae_cast16(const void* src, void* dst, int64_t n, int src_dtype, int dst_dtype, void* stream);
 
 /* out[c] (+)= sum_r m[r*ld + c]  (nn.Linear bias gradients); dtype = ODVAE_F32 / ODVAE_BF16 */
 size_t odvae_colsum_workspace_bytes(int cols);

@@ -109,26 +109,34 @@ static int attn_nt(int N) {
 }
 
 size_t odvae_attn_softmax_workspace_bytes(int B, int N) {
-  return static_cast<size_t>(B) * attn_nt(N) * N * 2 * sizeof(float) + 256;
+  // row partials (two column halves per tile) + the combined log-sum-exp per row
+  return static_cast<size_t>(B) * attn_nt(N) * 2 * N * 2 * sizeof(float) + static_cast<size_t>(B) * N * sizeof(float) + 256;
 }
 
 int odvae_attn_scores_softmax(const void* q, const void* k, void* P, int B, int N, int C, int64_t ldq, int64_t ldk,
                               int64_t strideq, int64_t stridek, float scale, int dtype, void* workspace,
                               size_t ws_bytes, void* stream) {
-  if (dtype != ODVAE_BF16 && dtype != ODVAE_F16) return ODVAE_ERR_SHAPE;
+  if ((dtype != ODVAE_BF16 && dtype != ODVAE_F16) || N % 256 != 0 || C % 64 != 0) return ODVAE_ERR_SHAPE;
   if (ws_bytes < odvae_attn_softmax_workspace_bytes(B, N) - 256) return ODVAE_ERR_WORKSPACE;
   cudaStream_t s = static_cast<cudaStream_t>(stream);
   const int om = dtype == ODVAE_F16 ? OUT_F16 : OUT_BF16;
+  const int slots = attn_nt(N) * 2;
+  float* part = reinterpret_cast<float*>(workspace);
+  float* lse2 = part + static_cast<size_t>(B) * slots * N * 2;
   for (int pass = 0; pass < 2; ++pass) {
     EngineDesc d;
     int st = describe_gemm(d, q, k, P, N, N, C, B, ldq, ldk, N, strideq, stridek, static_cast<int64_t>(N) * N, 0, 0, om,
                            scale, nullptr, nullptr);
     if (st != ODVAE_OK) return st;
     d.p.epi = pass == 0 ? EPI_ROWSTATS : EPI_SOFTMAX;
-    d.p.aux_out = reinterpret_cast<float*>(workspace);
-    d.p.aux_f32 = reinterpret_cast<const float*>(workspace);
+    d.p.aux_out = part;
+    d.p.aux_f32 = lse2;
     st = run_engine(d, ODVAE_IMPL_TC, dtype, s);
     if (st != ODVAE_OK) return st;
+    if (pass == 0) {
+      st = launch_attn_stats_combine(part, lse2, B, slots, N, s);
+      if (st != ODVAE_OK) return st;
+    }
   }
   return ODVAE_OK;
 }
@@ -136,7 +144,7 @@ int odvae_attn_scores_softmax(const void* q, const void* k, void* P, int B, int 
 int odvae_attn_dsoftmax(const void* dO, const void* v, const void* P, const float* delta, void* dS, int B, int N,
                         int C, int64_t ldo, int64_t ldv, int64_t strideo, int64_t stridev, float scale, int dtype,
                         void* stream) {
-  if (dtype != ODVAE_BF16 && dtype != ODVAE_F16) return ODVAE_ERR_SHAPE;
+  if ((dtype != ODVAE_BF16 && dtype != ODVAE_F16) || N % 256 != 0 || C % 64 != 0) return ODVAE_ERR_SHAPE;
   EngineDesc d;
   const int om = dtype == ODVAE_F16 ? OUT_F16 : OUT_BF16;
   int st = describe_gemm(d, dO, v, dS, N, N, C, B, ldo, ldv, N, strideo, stridev, static_cast<int64_t>(N) * N, 0, 0, om,

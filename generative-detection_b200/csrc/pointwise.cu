@@ -339,6 +339,31 @@ __global__ void __launch_bounds__(256) rowdot16_kernel(const uint16_t* __restric
 }  // namespace odvae
 
 
+namespace odvae {
+// lse2[z][row] = max_t m_t + log2(sum_t l_t 2^(m_t - max)) over the row's column-tile partials (fixed order)
+__global__ void attn_stats_combine_kernel(const float2* __restrict__ part, float* __restrict__ lse2, int slots,
+                                          long long rows_per_z, long long total_rows) {
+  const long long i = blockIdx.x * static_cast<long long>(blockDim.x) + threadIdx.x;
+  if (i >= total_rows) return;
+  const long long z = i / rows_per_z, row = i - z * rows_per_z;
+  const float2* src = part + z * slots * rows_per_z + row;
+  float mx = -INFINITY;
+  for (int t = 0; t < slots; ++t) mx = fmaxf(mx, __ldg(src + t * rows_per_z).x);
+  float l = 0.0f;
+  for (int t = 0; t < slots; ++t) {
+    const float2 pr = __ldg(src + t * rows_per_z);
+    l += pr.y * exp2f(pr.x - mx);
+  }
+  lse2[i] = mx + log2f(l);
+}
+int launch_attn_stats_combine(const float* part, float* lse2, int B, int slots, int N, cudaStream_t st) {
+  const long long total = static_cast<long long>(B) * N;
+  attn_stats_combine_kernel<<<static_cast<int>((total + 255) / 256), 256, 0, st>>>(
+      reinterpret_cast<const float2*>(part), lse2, slots, N, total);
+  return check_launch("attn_stats_combine_kernel");
+}
+}  // namespace odvae
+
 extern "C" {
 
 int odvae_softmax_rows(const float* S, void* P, int64_t rows, int n, float scale, int act_dtype, void* stream) {

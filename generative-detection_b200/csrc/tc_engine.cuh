@@ -4,6 +4,8 @@
 //   KIND_WGRAD : convolution weight gradient (both operands MN-major, K = pixels, deterministic split-K)
 // Tile = 128 (M, TMEM lanes) x BN (<=256) with BLOCK_K = 64 bf16 (one 128-byte swizzle atom per row).
 #pragma once
+#include <type_traits>
+
 #include "common.cuh"
 #include "tc_primitives.cuh"
 #include "engine_desc.h"
@@ -13,7 +15,7 @@ namespace odvae {
 static constexpr int TC_BLOCK_M = 128;
 static constexpr int TC_BLOCK_K = 64;
 static constexpr int TC_A_BYTES = TC_BLOCK_M * TC_BLOCK_K * 2;  // 16 KiB
-static constexpr int TC_THREADS = 256;
+static constexpr int TC_THREADS = 320;  // warp 0: TMEM alloc + TMA producer; warp 1: MMA issuer; warps 2-9: epilogue
 static constexpr int TC_TMEM_COLS = 512;
 
 struct TileCoord {
@@ -96,11 +98,12 @@ tc_engine_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant_
     }
     for (int i = 0; i < 2; ++i) {
       mbar_init(&tfull_bar[i], 1);
-      mbar_init(&tempty_bar[i], 128);
+      mbar_init(&tempty_bar[i], 256);
     }
     fence_barrier_init();
   }
-  if (warp == 2) {
+  __syncwarp();
+  if (warp == 0) {
     tmem_alloc(tmem_slot, TC_TMEM_COLS);
     tmem_relinquish();
   }
@@ -219,18 +222,23 @@ tc_engine_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant_
       }
     }
     __syncwarp();
-  } else if (warp >= 4) {
-    // ============================ epilogue (4 warps = 128 TMEM lanes) ============================
+  } else if (warp >= 2) {
+    // ============================ epilogue (8 warps) ============================
+    // A warp may only touch the TMEM lane quadrant (warp id % 4); two warps share a quadrant and split the
+    // accumulator's columns in halves, so all four SM sub-partitions carry two epilogue warps each.
     const int q = warp & 3;         // TMEM lane quadrant this warp may access
     const int r = q * 32 + lane;    // row within the tile
+    const int half = (warp - 2) >> 2;
+    const bool split_cols = (acc_cols % 32) == 0;
+    const int nhalf = split_cols ? 2 : 1;
+    const int c_begin = split_cols ? half * (acc_cols >> 1) : 0;
+    const int c_end = split_cols ? c_begin + (acc_cols >> 1) : (half == 0 ? acc_cols : 0);
     int acc = 0;
     uint32_t acc_phase = 0;
     for (int t = blockIdx.x; t < total_tiles; t += gridDim.x) {
       const TileCoord tc = decode_tile(p, t);
       const int m0 = tc.m_tile * TC_BLOCK_M;
       const int n0 = tc.n_tile * BN;
-      mbar_wait(&tfull_bar[acc], acc_phase);
-      tc_fence_after();
 
       bool row_ok = true;
       long long row_off = 0;  // element offset of (row, column n0) in D / residual
@@ -252,98 +260,106 @@ tc_engine_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant_
       const long long tap_stride = static_cast<long long>(p.split_k) * p.m_valid * p.ldd;  // WGRAD: next tap's slab
 
       if (p.epi != EPI_NONE) {
-        // ---- fused attention epilogues (KIND_GEMM, one accumulator row per thread) ----
-        const long long stat_row = static_cast<long long>(tc.z) * p.m_valid + (m0 + r);
-        const float s2 = p.alpha * 1.4426950408889634f;  // scores are handled in the log2 domain: exp(a*s) = 2^(s2*s)
-        if (p.epi == EPI_ROWSTATS) {
-          // online (max, sum 2^(v - max)) over this tile's BN columns -> partial [z][n_tile][row]
-          float mx = -INFINITY, l = 0.0f;
-          for (int cc = 0; cc < BN; cc += 16) {
-            uint32_t v[16];
-            tmem_ld_x16(t_row + static_cast<uint32_t>(cc), v);
-            tmem_ld_wait();
-            float f[16];
-            float cm = -INFINITY;
+        // ---- fused attention epilogues (KIND_GEMM; one accumulator row and <= 128 columns per thread) ----
+        // Global reads this tile needs (softmax partials / delta / the P tile) are issued BEFORE waiting for the
+        // accumulator, so their latency hides behind the tile's MMAs; TMEM is drained 32 columns at a time with the
+        // next tcgen05.ld in flight while the current chunk is processed.
+        const float s2 = p.alpha * 1.4426950408889634f;  // scores live in the log2 domain: exp(a*s) = 2^(s2*s)
+        const bool halfp = p.out_mode == OUT_F16;
+        float mx = -INFINITY, l = 0.0f, lse2 = 0.0f, delta = 0.0f;  // mx: running max of the RAW accumulators
+        uint4 pp[16];  // DSOFTMAX: this thread's 128 P values
+        if (p.epi == EPI_SOFTMAX && row_ok) {
+          // lse2[row] = max + log2(sum 2^(s2*s - max)), combined from the row partials by attn_stats_combine_kernel
+          lse2 = __ldg(p.aux_f32 + static_cast<long long>(tc.z) * p.m_valid + (m0 + r));
+        } else if (p.epi == EPI_DSOFTMAX && row_ok) {
+          delta = __ldg(p.aux_f32 + static_cast<long long>(tc.z) * p.m_valid + (m0 + r));
+          const uint4* psrc = reinterpret_cast<const uint4*>(reinterpret_cast<const uint16_t*>(p.aux16) + row_off + c_begin);
 #pragma unroll
-            for (int i = 0; i < 16; ++i) {
-              f[i] = (n0 + cc + i < p.n_valid) ? __uint_as_float(v[i]) * s2 : -INFINITY;
-              cm = fmaxf(cm, f[i]);
-            }
+          for (int i = 0; i < 16; ++i) pp[i] = __ldg(psrc + i);
+        }
+        mbar_wait(&tfull_bar[acc], acc_phase);
+        tc_fence_after();
+
+        auto process = [&](uint32_t (&v)[32], int cc) {
+          if (p.epi == EPI_ROWSTATS) {
+            // online (max, sum 2^(s2*(v - max))) on raw accumulators: s2 > 0, so the max commutes with the scale
+            float cm = __uint_as_float(v[0]);
+#pragma unroll
+            for (int i = 1; i < 32; ++i) cm = fmaxf(cm, __uint_as_float(v[i]));
             const float mn = fmaxf(mx, cm);
-            float acc_l = 0.0f;
+            const float off = -mn * s2;
+            float a0 = 0.0f, a1 = 0.0f;
 #pragma unroll
-            for (int i = 0; i < 16; ++i) acc_l += exp2f(f[i] - mn);
-            l = l * exp2f(mx - mn) + acc_l;
+            for (int i = 0; i < 32; i += 2) {
+              a0 += fast_exp2(fmaf(__uint_as_float(v[i]), s2, off));
+              a1 += fast_exp2(fmaf(__uint_as_float(v[i + 1]), s2, off));
+            }
+            l = l * fast_exp2((mx - mn) * s2) + (a0 + a1);
             mx = mn;
-          }
-          if (row_ok) {
-            float2* dst = reinterpret_cast<float2*>(p.aux_out) +
-                          (static_cast<long long>(tc.z) * p.num_n_tiles + tc.n_tile) * p.m_valid + (m0 + r);
-            *dst = make_float2(mx, l);
-          }
-        } else if (p.epi == EPI_SOFTMAX) {
-          // combine the row's partials (fixed order), then P = 2^(s2*s - max) / sum
-          float mx = -INFINITY, l = 0.0f;
-          if (row_ok) {
-            const float2* src = reinterpret_cast<const float2*>(p.aux_f32) +
-                                static_cast<long long>(tc.z) * p.num_n_tiles * p.m_valid + (m0 + r);
-            for (int t2 = 0; t2 < p.num_n_tiles; ++t2) mx = fmaxf(mx, __ldg(src + static_cast<long long>(t2) * p.m_valid).x);
-            for (int t2 = 0; t2 < p.num_n_tiles; ++t2) {
-              const float2 pr = __ldg(src + static_cast<long long>(t2) * p.m_valid);
-              l += pr.y * exp2f(pr.x - mx);
-            }
-          }
-          const float inv_l = row_ok ? __fdividef(1.0f, l) : 0.0f;
-          const bool half = p.out_mode == OUT_F16;
-          for (int cc = 0; cc < BN; cc += 16) {
-            uint32_t v[16];
-            tmem_ld_x16(t_row + static_cast<uint32_t>(cc), v);
-            tmem_ld_wait();
-            if (row_ok && n0 + cc < p.n_valid) {
-              float f[16];
+          } else if (row_ok) {
+            uint32_t o[16];
+            {
 #pragma unroll
-              for (int i = 0; i < 16; ++i) f[i] = exp2f(fmaf(__uint_as_float(v[i]), s2, -mx)) * inv_l;
-              uint16_t* dst = reinterpret_cast<uint16_t*>(p.D) + row_off + cc;
-              uint4 o0, o1;
-              o0.x = pack_16x2(f[0], f[1], half);   o0.y = pack_16x2(f[2], f[3], half);
-              o0.z = pack_16x2(f[4], f[5], half);   o0.w = pack_16x2(f[6], f[7], half);
-              o1.x = pack_16x2(f[8], f[9], half);   o1.y = pack_16x2(f[10], f[11], half);
-              o1.z = pack_16x2(f[12], f[13], half); o1.w = pack_16x2(f[14], f[15], half);
-              reinterpret_cast<uint4*>(dst)[0] = o0;
-              reinterpret_cast<uint4*>(dst)[1] = o1;
+              for (int i = 0; i < 16; ++i)
+                o[i] = pack_16x2(fast_exp2(fmaf(__uint_as_float(v[2 * i]), s2, -lse2)),
+                                 fast_exp2(fmaf(__uint_as_float(v[2 * i + 1]), s2, -lse2)), halfp);
             }
+            uint4* dst = reinterpret_cast<uint4*>(reinterpret_cast<uint16_t*>(p.D) + row_off + cc);
+#pragma unroll
+            for (int i = 0; i < 4; ++i) dst[i] = make_uint4(o[4 * i], o[4 * i + 1], o[4 * i + 2], o[4 * i + 3]);
           }
-        } else {  // EPI_DSOFTMAX: dS = P * (dP - delta) * alpha, P read row-wise in D's layout
-          const float delta = row_ok ? __ldg(p.aux_f32 + stat_row) : 0.0f;
-          const bool half = p.out_mode == OUT_F16;
-          for (int cc = 0; cc < BN; cc += 16) {
-            uint32_t v[16];
-            tmem_ld_x16(t_row + static_cast<uint32_t>(cc), v);
+        };
+        // every epilogue warp owns exactly 128 accumulator columns here (BN = 256; the host checks N % 256 == 0)
+        if (p.epi == EPI_DSOFTMAX) {
+          // dS = P * (dP - delta) * alpha: 8 chunks of 16 columns, the next tcgen05.ld in flight during each chunk
+          uint32_t da[16], db[16];
+          tmem_ld_x16(t_row + static_cast<uint32_t>(c_begin), da);
+#pragma unroll
+          for (int j = 0; j < 8; ++j) {
+            uint32_t (&cur)[16] = (j & 1) ? db : da;
+            uint32_t (&nxt)[16] = (j & 1) ? da : db;
             tmem_ld_wait();
-            if (row_ok && n0 + cc < p.n_valid) {
-              const uint4* pp = reinterpret_cast<const uint4*>(reinterpret_cast<const uint16_t*>(p.aux16) + row_off + cc);
-              const uint4 p0 = __ldg(pp), p1 = __ldg(pp + 1);
+            if (j < 7) tmem_ld_x16(t_row + static_cast<uint32_t>(c_begin + 16 * (j + 1)), nxt);
+            if (row_ok) {
+              const uint4 p0 = pp[2 * j], p1 = pp[2 * j + 1];
               const uint32_t pw[8] = {p0.x, p0.y, p0.z, p0.w, p1.x, p1.y, p1.z, p1.w};
-              float f[16];
+              uint32_t o[8];
 #pragma unroll
               for (int i = 0; i < 8; ++i) {
-                const float2 pv = unpack_16x2(pw[i], half);
-                f[2 * i] = pv.x * (__uint_as_float(v[2 * i]) - delta) * p.alpha;
-                f[2 * i + 1] = pv.y * (__uint_as_float(v[2 * i + 1]) - delta) * p.alpha;
+                const float2 pv = unpack_16x2(pw[i], halfp);
+                o[i] = pack_16x2(pv.x * p.alpha * (__uint_as_float(cur[2 * i]) - delta),
+                                 pv.y * p.alpha * (__uint_as_float(cur[2 * i + 1]) - delta), halfp);
               }
-              uint16_t* dst = reinterpret_cast<uint16_t*>(p.D) + row_off + cc;
-              uint4 o0, o1;
-              o0.x = pack_16x2(f[0], f[1], half);   o0.y = pack_16x2(f[2], f[3], half);
-              o0.z = pack_16x2(f[4], f[5], half);   o0.w = pack_16x2(f[6], f[7], half);
-              o1.x = pack_16x2(f[8], f[9], half);   o1.y = pack_16x2(f[10], f[11], half);
-              o1.z = pack_16x2(f[12], f[13], half); o1.w = pack_16x2(f[14], f[15], half);
-              reinterpret_cast<uint4*>(dst)[0] = o0;
-              reinterpret_cast<uint4*>(dst)[1] = o1;
+              uint4* dst = reinterpret_cast<uint4*>(reinterpret_cast<uint16_t*>(p.D) + row_off + c_begin + 16 * j);
+              dst[0] = make_uint4(o[0], o[1], o[2], o[3]);
+              dst[1] = make_uint4(o[4], o[5], o[6], o[7]);
             }
           }
+        } else {
+          uint32_t va[32], vb[32];
+          tmem_ld_x32(t_row + static_cast<uint32_t>(c_begin), va);
+          tmem_ld_wait();
+          tmem_ld_x32(t_row + static_cast<uint32_t>(c_begin + 32), vb);
+          process(va, c_begin);
+          tmem_ld_wait();
+          tmem_ld_x32(t_row + static_cast<uint32_t>(c_begin + 64), va);
+          process(vb, c_begin + 32);
+          tmem_ld_wait();
+          tmem_ld_x32(t_row + static_cast<uint32_t>(c_begin + 96), vb);
+          process(va, c_begin + 64);
+          tmem_ld_wait();
+          process(vb, c_begin + 96);
         }
-      } else
-      for (int cc = 0; cc < acc_cols; cc += 16) {
+        if (p.epi == EPI_ROWSTATS && row_ok) {
+          float2* dst = reinterpret_cast<float2*>(p.aux_out) +
+                        (static_cast<long long>(tc.z) * p.num_n_tiles * nhalf + tc.n_tile * nhalf + half) * p.m_valid +
+                        (m0 + r);
+          *dst = make_float2(mx * s2, l);  // (max, sum) in the scaled log2 domain
+        }
+      } else {
+      mbar_wait(&tfull_bar[acc], acc_phase);
+      tc_fence_after();
+      for (int cc = c_begin; cc < c_end; cc += 16) {
         uint32_t v[16];
         tmem_ld_x16(t_row + static_cast<uint32_t>(cc), v);
         tmem_ld_wait();
@@ -434,6 +450,7 @@ tc_engine_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant_
           }
         }
       }
+      }
       tc_fence_before();
       mbar_arrive(&tempty_bar[acc]);
       if (++acc == num_acc) {
@@ -445,7 +462,7 @@ tc_engine_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant_
 
   tc_fence_before();
   __syncthreads();
-  if (warp == 2) {
+  if (warp == 0) {
     tc_fence_after();
     tmem_dealloc(tmem_base, TC_TMEM_COLS);
   }

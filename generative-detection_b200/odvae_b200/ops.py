@@ -144,7 +144,7 @@ def conv_impl(code, B, H, W, CinP, CoutP, geom):
 
 def attn_fused(code, N, C):
     """The fused tcgen05 attention core needs 16-bit operands and TMA-tileable shapes."""
-    return code != F32 and N % 128 == 0 and C % 64 == 0
+    return code != F32 and N % 256 == 0 and C % 64 == 0
 
 
 def out_hw(geom, H, W):

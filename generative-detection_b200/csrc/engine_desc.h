@@ -20,6 +20,7 @@ struct TcParams {
   int tap_dx[9], tap_dy[9], tap_c[9], tap_ph[9];
   // CONV m-tile geometry (box bw x bh = 128 output pixels)
   int bw_log2, tiles_x, tiles_y;
+  int swap;  // CONV with swapped roles: M = 128 output channels (weights), N = 256 output pixels (2 pixel boxes)
   // WGRAD k-chunk geometry (box kbw x kbh = 64 output pixels)
   int kbw_log2, kch_x, kch_y, split_k, kch_per_split;
   int wg_T, kch_total;  // taps accumulated per tile (1 or 3 = one filter row); pixel chunks over all splits

@@ -24,6 +24,16 @@ struct TileCoord {
   int tap, split; // WGRAD
 };
 
+// pixel box `pb` (128 output pixels) of a CONV problem -> (image, first row, first column)
+__device__ __forceinline__ void decode_pixel_box(const TcParams& p, int pb, int& b, int& y0, int& x0) {
+  const int per_img = p.tiles_x * p.tiles_y;
+  b = pb / per_img;
+  const int q = pb - b * per_img;
+  const int ty = q / p.tiles_x, tx = q - ty * p.tiles_x;
+  x0 = tx << p.bw_log2;
+  y0 = ty * (TC_BLOCK_M >> p.bw_log2);
+}
+
 __device__ __forceinline__ TileCoord decode_tile(const TcParams& p, int t) {
   TileCoord c;
   c.n_tile = t % p.num_n_tiles;
@@ -32,13 +42,8 @@ __device__ __forceinline__ TileCoord decode_tile(const TcParams& p, int t) {
   c.z = r / p.num_m_tiles;
   c.b = c.y0 = c.x0 = c.tap = c.split = 0;
   if (p.kind == KIND_CONV) {
-    int per_img = p.tiles_x * p.tiles_y;
-    c.b = c.m_tile / per_img;
-    int q = c.m_tile - c.b * per_img;
-    int ty = q / p.tiles_x, tx = q - ty * p.tiles_x;
-    int bw = 1 << p.bw_log2;
-    c.x0 = tx * bw;
-    c.y0 = ty * (TC_BLOCK_M >> p.bw_log2);
+    // swapped roles: the N tile is a pair of pixel boxes (2*n_tile, 2*n_tile + 1); (b, y0, x0) = the first one
+    decode_pixel_box(p, p.swap ? 2 * c.n_tile : c.m_tile, c.b, c.y0, c.x0);
   } else if (p.kind == KIND_WGRAD) {
     const int grp = c.z / p.split_k;
     c.split = c.z - grp * p.split_k;
@@ -144,9 +149,20 @@ tc_engine_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant_
           } else if (p.kind == KIND_CONV) {
             const int tap = kit / p.cchunks;
             const int cc = kit - tap * p.cchunks;
-            spatial_load(a_dst, &tmA, fb, p.sp_rank, cc * 64 + p.tap_c[tap], tc.x0 + p.tap_dx[tap], p.tap_ph[tap],
-                         tc.y0 + p.tap_dy[tap], tc.b);
-            tma_load_2d(b_dst, &tmB, fb, kit * TC_BLOCK_K, n0);
+            if (!p.swap) {
+              spatial_load(a_dst, &tmA, fb, p.sp_rank, cc * 64 + p.tap_c[tap], tc.x0 + p.tap_dx[tap], p.tap_ph[tap],
+                           tc.y0 + p.tap_dy[tap], tc.b);
+              tma_load_2d(b_dst, &tmB, fb, kit * TC_BLOCK_K, n0);
+            } else {
+              // A slot <- 128 output channels of the weight matrix; B slot <- two 128-pixel boxes (N = 256 pixels)
+              tma_load_2d(a_dst, &tmB, fb, kit * TC_BLOCK_K, m0);
+              int b1, y1, x1;
+              decode_pixel_box(p, 2 * tc.n_tile + 1, b1, y1, x1);
+              spatial_load(b_dst, &tmA, fb, p.sp_rank, cc * 64 + p.tap_c[tap], tc.x0 + p.tap_dx[tap], p.tap_ph[tap],
+                           tc.y0 + p.tap_dy[tap], tc.b);
+              spatial_load(b_dst + TC_A_BYTES, &tmA, fb, p.sp_rank, cc * 64 + p.tap_c[tap], x1 + p.tap_dx[tap],
+                           p.tap_ph[tap], y1 + p.tap_dy[tap], b1);
+            }
           } else {  // KIND_WGRAD
             const int q = tc.split * p.kch_per_split + kit;
             const int per_img = p.kch_x * p.kch_y;
@@ -259,7 +275,54 @@ tc_engine_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant_
       const long long row_off0 = row_off;
       const long long tap_stride = static_cast<long long>(p.split_k) * p.m_valid * p.ldd;  // WGRAD: next tap's slab
 
-      if (p.epi != EPI_NONE) {
+      if (p.kind == KIND_CONV && p.swap) {
+        // ---- swapped-role conv: lane = output channel, column = output pixel. This warp owns the 128 pixels of
+        // pixel box (2 * n_tile + half); for every pixel the 32 lanes write 32 consecutive channels (one 64-byte
+        // segment), and bias / per-channel work is a per-thread scalar.
+        int pb_b, pb_y, pb_x;
+        decode_pixel_box(p, 2 * tc.n_tile + half, pb_b, pb_y, pb_x);
+        const int n = m0 + r;
+        const bool ch_ok = n < p.n_valid;
+        const float bias = (p.bias != nullptr && ch_ok) ? __ldg(p.bias + n) : 0.0f;
+        const bool halfp = p.out_mode == OUT_F16;
+        uint16_t* D16 = reinterpret_cast<uint16_t*>(p.D);
+        const uint16_t* R16 = reinterpret_cast<const uint16_t*>(p.residual);
+        const long long base0 = static_cast<long long>(pb_b) * p.oB + p.o0 + n;
+        const long long sx = p.oX;
+        mbar_wait(&tfull_bar[acc], acc_phase);
+        tc_fence_after();
+        auto emit = [&](uint32_t (&v)[32], int pi0) {
+          const int yy = pb_y + (pi0 >> p.bw_log2), xx = pb_x + (pi0 & ((1 << p.bw_log2) - 1));
+          const long long base = base0 + static_cast<long long>(yy) * p.oY + static_cast<long long>(xx) * sx;
+          if (ch_ok) {
+            float f[32];
+#pragma unroll
+            for (int i = 0; i < 32; ++i) f[i] = fmaf(__uint_as_float(v[i]), p.alpha, bias);
+            if (R16 != nullptr) {
+              uint16_t rr[32];
+#pragma unroll
+              for (int i = 0; i < 32; ++i) rr[i] = __ldg(R16 + base + i * sx);
+#pragma unroll
+              for (int i = 0; i < 32; ++i) f[i] += unpack_16x2(static_cast<uint32_t>(rr[i]), halfp).x;
+            }
+#pragma unroll
+            for (int i = 0; i < 32; ++i) D16[base + i * sx] = static_cast<uint16_t>(pack_16x2(f[i], 0.0f, halfp) & 0xffffu);
+          }
+        };
+        uint32_t va[32], vb[32];
+        tmem_ld_x32(t_row + static_cast<uint32_t>(c_begin), va);
+        tmem_ld_wait();
+        tmem_ld_x32(t_row + static_cast<uint32_t>(c_begin + 32), vb);
+        emit(va, 0);
+        tmem_ld_wait();
+        tmem_ld_x32(t_row + static_cast<uint32_t>(c_begin + 64), va);
+        emit(vb, 32);
+        tmem_ld_wait();
+        tmem_ld_x32(t_row + static_cast<uint32_t>(c_begin + 96), vb);
+        emit(va, 64);
+        tmem_ld_wait();
+        emit(vb, 96);
+      } else if (p.epi != EPI_NONE) {
         // ---- fused attention epilogues (KIND_GEMM; one accumulator row and <= 128 columns per thread) ----
         // Global reads this tile needs (softmax partials / delta / the P tile) are issued BEFORE waiting for the
         // accumulator, so their latency hides behind the tile's MMAs; TMEM is drained 32 columns at a time with the

@@ -44,6 +44,8 @@ CONV_CASES = [
     (1, 16, 16, 128, 256),
     (2, 16, 16, 64, 64),
     (1, 128, 128, 64, 64),
+    (2, 64, 64, 128, 128),   # N = 128 both ways: fwd and dgrad take the swapped-role tiles (M = channels, N = 256 pixels)
+    (2, 256, 256, 64, 128),  # one full image row (256 pixels) per swapped tile, as in the 256x256 levels
 ]
 
 

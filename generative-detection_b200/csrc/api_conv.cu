@@ -6,6 +6,11 @@ using namespace odvae;
 
 extern "C" {
 
+int odvae_set_conv_halo(int enabled) {
+  set_conv_halo_enabled(enabled);
+  return ODVAE_OK;
+}
+
 int odvae_conv2d_tc_supported(int B, int H, int W, int CinP, int CoutP, int geom) {
   EngineDesc d;
   if (describe_conv_fwd(d, nullptr, nullptr, nullptr, nullptr, nullptr, B, H, W, CinP, CoutP, CoutP, geom, 0) != ODVAE_OK) return 0;

@@ -21,6 +21,11 @@ struct TcParams {
   // CONV m-tile geometry (box bw x bh = 128 output pixels)
   int bw_log2, tiles_x, tiles_y;
   int swap;  // CONV with swapped roles: M = 128 output channels (weights), N = 256 output pixels (2 pixel boxes)
+  // CONV halo mode (swapped 3x3 stride-1 at W = 256): the N tile is ONE image row; each input row (+1 pixel of halo on
+  // both sides) is fetched once per 64-channel chunk into a shared-memory slab and the three horizontally shifted taps
+  // read it through operand descriptors that start 0 / 1 / 2 pixel rows into the slab. `stages` then counts the
+  // 16 KiB weight stages and `halo_slabs` the slab ring.
+  int halo, halo_slabs;
   // WGRAD k-chunk geometry (box kbw x kbh = 64 output pixels)
   int kbw_log2, kch_x, kch_y, split_k, kch_per_split;
   int wg_T, kch_total;  // taps accumulated per tile (1 or 3 = one filter row); pixel chunks over all splits

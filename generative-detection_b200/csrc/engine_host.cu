@@ -60,6 +60,14 @@ static int make_tmap_bf16(CUtensorMap* tm, const OperandView& v, const uint32_t*
   return ODVAE_OK;
 }
 
+// test / profiling switch (odvae_set_conv_halo): 1 = never pick the halo conv path
+static int g_disable_halo = 0;
+int set_conv_halo_enabled(int on) {
+  const int prev = g_disable_halo ? 0 : 1;
+  g_disable_halo = on ? 0 : 1;
+  return prev;
+}
+
 static int pick_bn(long long n) {
   const int cands[] = {256, 128, 64, 32, 16};
   for (int c : cands)
@@ -86,6 +94,11 @@ static int tc_pick_stages(int BN, int num_k_iters) {
   return s;
 }
 
+static size_t tc_halo_smem_bytes(int stages, int slabs) {
+  return static_cast<size_t>(stages) * TC_A_BYTES + static_cast<size_t>(slabs) * TC_SLAB_BYTES +
+         (2 * stages + 6 + 2 * slabs) * 8 + 16 + 1024;
+}
+
 static int launch_tc(EngineDesc& d, cudaStream_t stream) {
   if (!d.tc_ok) return ODVAE_ERR_SHAPE;
   CUtensorMap tmA, tmB;
@@ -95,8 +108,8 @@ static int launch_tc(EngineDesc& d, cudaStream_t stream) {
   if (st != ODVAE_OK) return st;
   TcParams& p = d.p;
   const int b_rows = p.kind == KIND_WGRAD ? p.BN * p.wg_T : p.BN;
-  p.stages = tc_pick_stages(b_rows, p.num_k_iters);
-  const size_t smem = tc_smem_bytes(p.stages, b_rows);
+  p.stages = p.halo ? 5 : tc_pick_stages(b_rows, p.num_k_iters);
+  const size_t smem = p.halo ? tc_halo_smem_bytes(p.stages, p.halo_slabs) : tc_smem_bytes(p.stages, b_rows);
   static std::once_flag once;
   static cudaError_t attr_err = cudaSuccess;
   std::call_once(once, [] {
@@ -337,6 +350,15 @@ static void conv_common(EngineDesc& d, int Bn, int Ho, int Wo, int gatherC, int 
     p.BN = 256;
     p.num_n_tiles = p.num_m_tiles / 2;  // pairs of pixel boxes
     p.num_m_tiles = N / 128;            // tiles of 128 output channels
+  }
+  // Halo mode: W = 256 rows are one N tile; the 9 taps re-read 3 input rows from shared memory instead of 9 shifted
+  // boxes from L2 (the 128-channel layers at 256x256 were L2->SM bound: 14.5 GB per launch at ~10.7 TB/s)
+  p.halo = 0;
+  if (p.swap && !g_disable_halo && p.ntaps == 9 && p.sp_rank == 4 && Wo == 256 && bw == 128 && p.tap_dx[0] == -1 &&
+      p.tap_dy[0] == -1 && p.tap_dx[8] == 1 && p.tap_dy[8] == 1) {
+    p.halo = 1;
+    p.halo_slabs = 4;
+    d.boxA[0] = 64; d.boxA[1] = TC_HALO_BOX; d.boxA[2] = 1; d.boxA[3] = 1;
   }
   p.alpha = 1.0f;
   d.conv_batch = Bn;

@@ -15,6 +15,7 @@ int describe_conv_dgrad(EngineDesc* ds, int* count, const void* dy, const void* 
                         const void* dx_add, void* dx, int B, int H, int W, int CinP, int CoutP, int geom);
 int describe_conv_wgrad(EngineDesc& d, const void* x, const void* dy, float* ws, int B, int H, int W, int CinP,
                         int CoutP, int geom, int impl);
+int set_conv_halo_enabled(int on);  // returns the previous setting
 // pointwise.cu
 int launch_attn_stats_combine(const float* part, float* lse2, int B, int slots, int N, cudaStream_t st);
 // layout.cu

@@ -17,6 +17,10 @@ static constexpr int TC_BLOCK_K = 64;
 static constexpr int TC_A_BYTES = TC_BLOCK_M * TC_BLOCK_K * 2;  // 16 KiB
 static constexpr int TC_THREADS = 320;  // warp 0: TMEM alloc + TMA producer; warp 1: MMA issuer; warps 2-9: epilogue
 static constexpr int TC_TMEM_COLS = 512;
+// halo slab: one input row of 256 pixels + 1 halo pixel on each side, 128 B (64 channels) per pixel, written by two
+// 130-pixel TMA boxes (x = -1..128 and 129..258; out-of-image pixels are zero-filled); padded to a 1 KiB multiple
+static constexpr int TC_HALO_BOX = 130;
+static constexpr int TC_SLAB_BYTES = 33 * 1024;
 
 struct TileCoord {
   int m_tile, n_tile, z;
@@ -81,12 +85,17 @@ tc_engine_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant_
   const int num_acc = 2 * acc_cols <= TC_TMEM_COLS ? 2 : 1;
   uint8_t* sA = smem;
   uint8_t* sB = smem + static_cast<size_t>(stages) * TC_A_BYTES;
-  uint64_t* bars = reinterpret_cast<uint64_t*>(sB + static_cast<size_t>(stages) * b_bytes);
+  // halo mode: sA = weight stages, sB = ring of input-row slabs
+  const int nslabs = p.halo ? p.halo_slabs : 0;
+  uint64_t* bars = reinterpret_cast<uint64_t*>(
+      sB + (p.halo ? static_cast<size_t>(nslabs) * TC_SLAB_BYTES : static_cast<size_t>(stages) * b_bytes));
   uint64_t* full_bar = bars;
   uint64_t* empty_bar = bars + stages;
   uint64_t* tfull_bar = bars + 2 * stages;
   uint64_t* tempty_bar = bars + 2 * stages + 2;
   uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(bars + 2 * stages + 4);
+  uint64_t* sfull_bar = bars + 2 * stages + 6;  // halo slabs: filled by TMA / released by the MMA issuer
+  uint64_t* sempty_bar = sfull_bar + nslabs;
 
   const int warp = threadIdx.x >> 5;
   const int lane = threadIdx.x & 31;
@@ -105,6 +114,10 @@ tc_engine_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant_
       mbar_init(&tfull_bar[i], 1);
       mbar_init(&tempty_bar[i], 256);
     }
+    for (int i = 0; i < nslabs; ++i) {
+      mbar_init(&sfull_bar[i], 1);
+      mbar_init(&sempty_bar[i], 1);
+    }
     fence_barrier_init();
   }
   __syncwarp();
@@ -119,7 +132,40 @@ tc_engine_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant_
 
   if (warp == 0) {
     // ============================ TMA producer ============================
-    if (lane == 0) {
+    if (lane == 0 && p.halo) {
+      // halo conv: per tile (one image row) and 64-channel chunk, 3 input-row slabs, each followed by the weight
+      // tiles of its 3 horizontally shifted taps -- the same order the MMA issuer consumes them in
+      int ws = 0, ss = 0;
+      uint32_t wph = 0, sph = 0;
+      for (int t = blockIdx.x; t < total_tiles; t += gridDim.x) {
+        const TileCoord tc = decode_tile(p, t);
+        const int m0 = tc.m_tile * TC_BLOCK_M;
+        for (int cc = 0; cc < p.cchunks; ++cc) {
+          for (int ry = 0; ry < 3; ++ry) {
+            mbar_wait(&sempty_bar[ss], sph ^ 1u);
+            uint64_t* sb = &sfull_bar[ss];
+            mbar_arrive_expect_tx(sb, 2u * TC_HALO_BOX * 128u);
+            uint8_t* dst = sB + static_cast<size_t>(ss) * TC_SLAB_BYTES;
+            tma_load_4d(dst, &tmA, sb, cc * 64, -1, tc.y0 + ry - 1, tc.b);
+            tma_load_4d(dst + TC_HALO_BOX * 128, &tmA, sb, cc * 64, TC_HALO_BOX - 1, tc.y0 + ry - 1, tc.b);
+            if (++ss == nslabs) {
+              ss = 0;
+              sph ^= 1u;
+            }
+            for (int rx = 0; rx < 3; ++rx) {
+              mbar_wait(&empty_bar[ws], wph ^ 1u);
+              uint64_t* fb = &full_bar[ws];
+              mbar_arrive_expect_tx(fb, TC_A_BYTES);
+              tma_load_2d(sA + static_cast<size_t>(ws) * TC_A_BYTES, &tmB, fb, ((ry * 3 + rx) * p.cchunks + cc) * TC_BLOCK_K, m0);
+              if (++ws == stages) {
+                ws = 0;
+                wph ^= 1u;
+              }
+            }
+          }
+        }
+      }
+    } else if (lane == 0) {
       int stage = 0;
       uint32_t phase = 0;
       for (int t = blockIdx.x; t < total_tiles; t += gridDim.x) {
@@ -201,7 +247,47 @@ tc_engine_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant_
       uint32_t phase = 0;
       int acc = 0;
       uint32_t acc_phase = 0;
-      for (int t = blockIdx.x; t < total_tiles; t += gridDim.x) {
+      int ss = 0;
+      uint32_t sph = 0;
+      for (int t = blockIdx.x; p.halo && t < total_tiles; t += gridDim.x) {
+        mbar_wait(&tempty_bar[acc], acc_phase ^ 1u);
+        tc_fence_after();
+        const uint32_t d_tmem = tmem_base + static_cast<uint32_t>(acc * acc_cols);
+        uint32_t accum = 0;
+        for (int it = 0; it < 3 * p.cchunks; ++it) {  // (channel chunk, input row) slabs
+          mbar_wait(&sfull_bar[ss], sph);
+          tc_fence_after();
+          const uint32_t slab = smem_u32(sB + static_cast<size_t>(ss) * TC_SLAB_BYTES);
+          for (int rx = 0; rx < 3; ++rx) {
+            mbar_wait(&full_bar[stage], phase);
+            tc_fence_after();
+            const uint32_t a_base = smem_u32(sA + static_cast<size_t>(stage) * TC_A_BYTES);
+            const uint32_t b_base = slab + static_cast<uint32_t>(rx) * 128u;  // pixel x + (rx - 1) <-> slab row x + rx
+#pragma unroll
+            for (int k = 0; k < TC_BLOCK_K / 16; ++k) {
+              umma_bf16(d_tmem, make_smem_desc_sw128(a_base + k * 32, 0, 1024), make_smem_desc_sw128(b_base + k * 32, 0, 1024),
+                        idesc, accum);
+              accum = 1u;
+            }
+            umma_commit(&empty_bar[stage]);
+            if (++stage == stages) {
+              stage = 0;
+              phase ^= 1u;
+            }
+          }
+          umma_commit(&sempty_bar[ss]);
+          if (++ss == nslabs) {
+            ss = 0;
+            sph ^= 1u;
+          }
+        }
+        umma_commit(&tfull_bar[acc]);
+        if (++acc == num_acc) {
+          acc = 0;
+          acc_phase ^= 1u;
+        }
+      }
+      for (int t = blockIdx.x; !p.halo && t < total_tiles; t += gridDim.x) {
         mbar_wait(&tempty_bar[acc], acc_phase ^ 1u);
         tc_fence_after();
         const uint32_t d_tmem = tmem_base + static_cast<uint32_t>(acc * acc_cols);

@@ -14,7 +14,9 @@ def act_code(dtype):
         return BF16
     if dtype == torch.float32:
         return F32
-    raise TypeError("activations must be float32 or bfloat16, got %s" % dtype)
+    if dtype == torch.float16:
+        return lib.F16
+    raise TypeError("activations must be float32, bfloat16 or float16, got %s" % dtype)
 
 
 def pad_to(n, m):

@@ -53,6 +53,9 @@ int odvae_device_supported(void);
 int odvae_version(void);
 /* number of kernels this library has launched in this process (all streams, all threads) */
 int64_t odvae_launch_count(void);
+/* test / profiling switch: 0 makes the 3x3 stride-1 convs at W = 256 use the per-tap TMA gather instead of the
+ * shared-memory halo slabs (tests compare the two paths). Returns ODVAE_OK. */
+int odvae_set_conv_halo(int enabled);
 
 /* ---------------------------------------------------------------------------------------------
  * Layout / dtype conversion at the module boundary (AE.py:223, LD/ldm/models/autoencoder.py:344-349)

@@ -46,6 +46,7 @@ CONV_CASES = [
     (1, 128, 128, 64, 64),
     (2, 64, 64, 128, 128),   # N = 128 both ways: fwd and dgrad take the swapped-role tiles (M = channels, N = 256 pixels)
     (2, 256, 256, 64, 128),  # one full image row (256 pixels) per swapped tile, as in the 256x256 levels
+    (3, 256, 256, 128, 128),  # halo-slab path with 2 channel chunks, fwd and dgrad (odd batch: rows cross images)
 ]
 
 
@@ -91,6 +92,39 @@ def test_conv_fwd_dgrad_wgrad(impl, dtype, geom, case):
     torch.cuda.synchronize()
     assert rel_err(dw, wr.grad) < tol(dtype)
     assert rel_err(db, dy.float().sum(dim=(0, 1, 2))) < tol(dtype)
+
+
+@pytest.mark.parametrize("dtype", [torch.bfloat16, torch.float16])
+def test_conv_halo_slabs_match_tap_gather(dtype):
+    """3x3 stride-1 at W = 256: the shared-memory halo-slab path and the per-tap TMA gather accumulate the same
+    products in the same order per output element only up to the K ordering (chunk-major vs tap-major), so they agree
+    to fp32 summation noise; both are checked against torch fp32."""
+    from odvae_b200 import lib
+    B, H, W, C = 2, 256, 256, 128
+    torch.manual_seed(5)
+    x = torch.randn(B, H, W, C, device=DEV).to(dtype)
+    w = torch.randn(C, C, 3, 3, device=DEV) / (C * 9) ** 0.5
+    b = torch.randn(C, device=DEV)
+    res = torch.randn(B, H, W, C, device=DEV).to(dtype)
+    wp = K.pack_conv_weight(w, CONV_3x3_S1, C, C, 0, dtype)
+    wd = K.pack_conv_weight(w, CONV_3x3_S1, C, C, 1, dtype)
+    outs = []
+    try:
+        for on in (1, 0):
+            lib.call("set_conv_halo", on)
+            y = K.conv_fwd(x, wp, b, C, CONV_3x3_S1, IMPL_TC, residual=res)
+            dx = K.conv_dgrad(x, wd, C, CONV_3x3_S1, IMPL_TC, (H, W))
+            torch.cuda.synchronize()
+            outs.append((y.float(), dx.float()))
+    finally:
+        lib.call("set_conv_halo", 1)
+    ref = ref_conv(x, w.to(dtype).float(), b, CONV_3x3_S1) + res.float().permute(0, 3, 1, 2)
+    assert rel_err(outs[0][0].permute(0, 3, 1, 2), ref) < 1e-2
+    assert rel_err(outs[0][0], outs[1][0]) < 4e-3 and rel_err(outs[0][1], outs[1][1]) < 4e-3
+    # image borders: halo columns / rows must be exact zeros, not neighbouring-row pixels
+    edge = torch.cat([outs[0][0][:, :, 0], outs[0][0][:, :, -1], outs[0][0][:, 0], outs[0][0][:, -1]], 1)
+    edge_ref = torch.cat([outs[1][0][:, :, 0], outs[1][0][:, :, -1], outs[1][0][:, 0], outs[1][0][:, -1]], 1)
+    assert rel_err(edge, edge_ref) < 4e-3
 
 
 @pytest.mark.parametrize("impl,dtype", IMPLS2)

@@ -108,8 +108,21 @@ static int launch_tc(EngineDesc& d, cudaStream_t stream) {
   if (st != ODVAE_OK) return st;
   TcParams& p = d.p;
   const int b_rows = p.kind == KIND_WGRAD ? p.BN * p.wg_T : p.BN;
-  p.stages = p.halo ? 5 : tc_pick_stages(b_rows, p.num_k_iters);
-  const size_t smem = p.halo ? tc_halo_smem_bytes(p.stages, p.halo_slabs) : tc_smem_bytes(p.stages, b_rows);
+  size_t smem;
+  if (p.halo && p.kind == KIND_CONV) {
+    p.stages = 5;
+    smem = tc_halo_smem_bytes(p.stages, p.halo_slabs);
+  } else if (p.halo) {  // WGRAD: stage = dy tile + one 9 KiB slab per 64-channel chunk
+    const size_t stage_bytes = TC_A_BYTES + static_cast<size_t>(p.BN / 64) * TC_WSLAB_BYTES;
+    int s = static_cast<int>((224 * 1024 - 2048) / stage_bytes);
+    if (s > 8) s = 8;
+    if (s > p.num_k_iters) s = p.num_k_iters;
+    p.stages = s < 1 ? 1 : s;
+    smem = p.stages * stage_bytes + (2 * p.stages + 4) * 8 + 16 + 1024;
+  } else {
+    p.stages = tc_pick_stages(b_rows, p.num_k_iters);
+    smem = tc_smem_bytes(p.stages, b_rows);
+  }
   static std::once_flag once;
   static cudaError_t attr_err = cudaSuccess;
   std::call_once(once, [] {
@@ -515,6 +528,12 @@ int describe_conv_wgrad(EngineDesc& d, const void* x, const void* dy, float* ws,
     p.num_k_iters = p.kch_per_split;
     spatial_box(d.boxA, 4, kbw, kbh);
     spatial_box(d.boxB, p.sp_rank, kbw, kbh);
+    // Halo mode (3x3 stride 1, K chunk = 64 pixels of one image row): the x tile is fetched once per filter row with one
+    // halo pixel on each side instead of three shifted copies (stage 64 KB -> 34 KB at Cin block 128)
+    if (T == 3 && geom == ODVAE_CONV_3x3_S1 && kbw == 64 && kbh == 1 && !g_disable_halo) {
+      p.halo = 1;
+      d.boxB[0] = 64; d.boxB[1] = TC_WHALO_BOX; d.boxB[2] = 1; d.boxB[3] = 1;
+    }
   } else {
     // SIMT: 64x64 output tiles; split K so the grid fills the machine
     const long long tiles = static_cast<long long>(p.ntaps) * ((CoutP + 63) / 64) * ((CinP + 63) / 64);

@@ -401,6 +401,7 @@ static constexpr int COLSUM_BLOCKS = 592;
 size_t colsum_workspace_bytes(int cols) { return static_cast<size_t>(COLSUM_BLOCKS) * cols * sizeof(float); }
 int launch_colsum(const void* m, long long rows, int cols, int ld, int act_dtype, float* out, int accumulate,
                   float* part, cudaStream_t st) {
+  if (act_dtype != ODVAE_BF16 && act_dtype != ODVAE_F32) return ODVAE_ERR_SHAPE;  // gradients are bf16 or fp32
   int nblk = COLSUM_BLOCKS;
   if (rows < nblk * 8) nblk = static_cast<int>((rows + 7) / 8);
   if (nblk < 1) nblk = 1;

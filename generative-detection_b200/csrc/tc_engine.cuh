@@ -21,6 +21,9 @@ static constexpr int TC_TMEM_COLS = 512;
 // 130-pixel TMA boxes (x = -1..128 and 129..258; out-of-image pixels are zero-filled); padded to a 1 KiB multiple
 static constexpr int TC_HALO_BOX = 130;
 static constexpr int TC_SLAB_BYTES = 33 * 1024;
+// weight-gradient halo slab: 64 output pixels of one image row + 1 halo pixel on each side (one 66-pixel TMA box)
+static constexpr int TC_WHALO_BOX = 66;
+static constexpr int TC_WSLAB_BYTES = 9 * 1024;
 
 struct TileCoord {
   int m_tile, n_tile, z;
@@ -80,15 +83,19 @@ tc_engine_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant_
   const int stages = p.stages;
   const int BN = p.BN;
   const int wgT = p.kind == KIND_WGRAD ? p.wg_T : 1;
-  const uint32_t b_bytes = static_cast<uint32_t>(BN) * 128u * static_cast<uint32_t>(wgT);  // per stage
+  // WGRAD halo mode: per 64-channel chunk ONE slab of 64 + 2 pixels (TC_WSLAB_BYTES) serves the 3 taps of a filter row
+  const bool wg_halo = p.kind == KIND_WGRAD && p.halo;
+  const uint32_t b_bytes = wg_halo ? static_cast<uint32_t>(BN >> 6) * TC_WSLAB_BYTES
+                                   : static_cast<uint32_t>(BN) * 128u * static_cast<uint32_t>(wgT);  // per stage
   const int acc_cols = BN * wgT;                      // TMEM columns of one accumulator
   const int num_acc = 2 * acc_cols <= TC_TMEM_COLS ? 2 : 1;
   uint8_t* sA = smem;
   uint8_t* sB = smem + static_cast<size_t>(stages) * TC_A_BYTES;
   // halo mode: sA = weight stages, sB = ring of input-row slabs
-  const int nslabs = p.halo ? p.halo_slabs : 0;
+  const bool cv_halo = p.kind == KIND_CONV && p.halo;
+  const int nslabs = cv_halo ? p.halo_slabs : 0;
   uint64_t* bars = reinterpret_cast<uint64_t*>(
-      sB + (p.halo ? static_cast<size_t>(nslabs) * TC_SLAB_BYTES : static_cast<size_t>(stages) * b_bytes));
+      sB + (cv_halo ? static_cast<size_t>(nslabs) * TC_SLAB_BYTES : static_cast<size_t>(stages) * b_bytes));
   uint64_t* full_bar = bars;
   uint64_t* empty_bar = bars + stages;
   uint64_t* tfull_bar = bars + 2 * stages;
@@ -132,7 +139,7 @@ tc_engine_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant_
 
   if (warp == 0) {
     // ============================ TMA producer ============================
-    if (lane == 0 && p.halo) {
+    if (lane == 0 && cv_halo) {
       // halo conv: per tile (one image row) and 64-channel chunk, 3 input-row slabs, each followed by the weight
       // tiles of its 3 horizontally shifted taps -- the same order the MMA issuer consumes them in
       int ws = 0, ss = 0;
@@ -176,7 +183,8 @@ tc_engine_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant_
         for (int kit = 0; kit < nk; ++kit) {
           mbar_wait(&empty_bar[stage], phase ^ 1u);
           uint64_t* fb = &full_bar[stage];
-          mbar_arrive_expect_tx(fb, TC_A_BYTES + b_bytes);
+          mbar_arrive_expect_tx(fb, wg_halo ? TC_A_BYTES + static_cast<uint32_t>(BN >> 6) * (TC_WHALO_BOX * 128u)
+                                            : TC_A_BYTES + b_bytes);
           uint8_t* a_dst = sA + static_cast<size_t>(stage) * TC_A_BYTES;
           uint8_t* b_dst = sB + static_cast<size_t>(stage) * b_bytes;
           if (p.kind == KIND_GEMM) {
@@ -219,8 +227,13 @@ tc_engine_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant_
             const int y0 = cy * (TC_BLOCK_K >> p.kbw_log2);
             tma_load_4d(a_dst, &tmA, fb, m0, x0, y0, b);
             tma_load_4d(a_dst + 8192, &tmA, fb, m0 + 64, x0, y0, b);
+            if (wg_halo) {
+              // one slab per 64-channel chunk: pixels x0 - 1 .. x0 + 64 of input row y0 + dy (zero-filled outside)
+              for (int j = 0; j < (BN >> 6); ++j)
+                tma_load_4d(b_dst + j * TC_WSLAB_BYTES, &tmB, fb, n0 + 64 * j, x0 - 1, y0 + p.tap_dy[tc.tap], b);
+            }
             // wg_T tap tiles back to back: [tap][BN/64 chunks of 64 channels x 64 pixels]
-            for (int tt = 0; tt < wgT; ++tt) {
+            for (int tt = 0; !wg_halo && tt < wgT; ++tt) {
               const int tap = tc.tap + tt;
               for (int j = 0; j < (BN >> 6); ++j)
                 spatial_load(b_dst + (tt * (BN >> 6) + j) * 8192, &tmB, fb, p.sp_rank, n0 + 64 * j + p.tap_c[tap],
@@ -243,13 +256,14 @@ tc_engine_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant_
       const int n_rest = acc_cols - n_first;
       const uint32_t idesc = make_idesc_16(TC_BLOCK_M, static_cast<uint32_t>(n_first), p.a_mn, p.b_mn, p.a_fmt, p.b_fmt);
       const uint32_t idesc2 = make_idesc_16(TC_BLOCK_M, static_cast<uint32_t>(n_rest > 0 ? n_rest : 16), p.a_mn, p.b_mn, p.a_fmt, p.b_fmt);
+      const uint32_t idesc_h = make_idesc_16(TC_BLOCK_M, 192u, p.a_mn, p.b_mn, p.a_fmt, p.b_fmt);
       int stage = 0;
       uint32_t phase = 0;
       int acc = 0;
       uint32_t acc_phase = 0;
       int ss = 0;
       uint32_t sph = 0;
-      for (int t = blockIdx.x; p.halo && t < total_tiles; t += gridDim.x) {
+      for (int t = blockIdx.x; cv_halo && t < total_tiles; t += gridDim.x) {
         mbar_wait(&tempty_bar[acc], acc_phase ^ 1u);
         tc_fence_after();
         const uint32_t d_tmem = tmem_base + static_cast<uint32_t>(acc * acc_cols);
@@ -287,7 +301,7 @@ tc_engine_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant_
           acc_phase ^= 1u;
         }
       }
-      for (int t = blockIdx.x; !p.halo && t < total_tiles; t += gridDim.x) {
+      for (int t = blockIdx.x; !cv_halo && t < total_tiles; t += gridDim.x) {
         mbar_wait(&tempty_bar[acc], acc_phase ^ 1u);
         tc_fence_after();
         const uint32_t d_tmem = tmem_base + static_cast<uint32_t>(acc * acc_cols);
@@ -304,6 +318,15 @@ tc_engine_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant_
                                           : make_smem_desc_sw128(a_base + k * 32, 0, 1024);
             const uint64_t bdesc = p.b_mn ? make_smem_desc_sw128(b_base + k * 2048, 8192, 1024)
                                           : make_smem_desc_sw128(b_base + k * 32, 0, 1024);
+            if (wg_halo) {
+              // per 64-channel chunk one N = 192 MMA: the three 64-wide N chunks are the same channels read 0 / 1 / 2
+              // pixel rows into the slab (LBO = 128 B), i.e. the taps dx = -1, 0, +1
+              for (int j = 0; j < (BN >> 6); ++j) {
+                const uint64_t bd = make_smem_desc_sw128(b_base + j * TC_WSLAB_BYTES + k * 2048, 128, 1024);
+                umma_bf16(d_tmem + static_cast<uint32_t>(j * 192), adesc, bd, idesc_h, (kit | k) != 0 ? 1u : 0u);
+              }
+              continue;
+            }
             umma_bf16(d_tmem, adesc, bdesc, idesc, (kit | k) != 0 ? 1u : 0u);
             if (n_rest > 0) {  // WGRAD tap groups only (MN-major B): chunks 4.. of the stage
               const uint64_t bdesc2 = make_smem_desc_sw128(b_base + 4 * 8192 + k * 2048, 8192, 1024);
@@ -513,7 +536,12 @@ tc_engine_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant_
         tmem_ld_x16(t_row + static_cast<uint32_t>(cc), v);
         tmem_ld_wait();
         int c = cc;  // column within this tap's BN-wide block
-        if (wgT > 1) {
+        if (wg_halo) {  // column = [channel chunk j][tap][64 channels]
+          const int j = cc / 192, rem = cc - j * 192;
+          const int tt = rem >> 6;
+          c = j * 64 + (rem & 63);
+          row_off = row_off0 + tt * tap_stride;
+        } else if (wgT > 1) {
           const int tt = cc / BN;
           c = cc - tt * BN;
           row_off = row_off0 + tt * tap_stride;

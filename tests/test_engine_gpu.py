@@ -113,9 +113,11 @@ def test_conv_halo_slabs_match_tap_gather(dtype):
         for on in (1, 0):
             lib.call("set_conv_halo", on)
             y = K.conv_fwd(x, wp, b, C, CONV_3x3_S1, IMPL_TC, residual=res)
-            dx = K.conv_dgrad(x, wd, C, CONV_3x3_S1, IMPL_TC, (H, W))
+            dx = K.conv_dgrad(x, wd, C, CONV_3x3_S1, IMPL_TC, (H, W))  # dgrad always stores bf16 (gradient format)
+            # wgrad: same products in the same K order -> bit-identical (gradients are bf16 in every 16-bit mode)
+            dw, _ = K.conv_wgrad(x.to(torch.bfloat16), res.to(torch.bfloat16), C, C, CONV_3x3_S1, IMPL_TC)
             torch.cuda.synchronize()
-            outs.append((y.float(), dx.float()))
+            outs.append((y.float(), dx.view(torch.bfloat16).float(), dw))
     finally:
         lib.call("set_conv_halo", 1)
     ref = ref_conv(x, w.to(dtype).float(), b, CONV_3x3_S1) + res.float().permute(0, 3, 1, 2)
@@ -125,6 +127,7 @@ def test_conv_halo_slabs_match_tap_gather(dtype):
     edge = torch.cat([outs[0][0][:, :, 0], outs[0][0][:, :, -1], outs[0][0][:, 0], outs[0][0][:, -1]], 1)
     edge_ref = torch.cat([outs[1][0][:, :, 0], outs[1][0][:, :, -1], outs[1][0][:, 0], outs[1][0][:, -1]], 1)
     assert rel_err(edge, edge_ref) < 4e-3
+    assert rel_err(outs[0][2], outs[1][2]) < 1e-5
 
 
 @pytest.mark.parametrize("impl,dtype", IMPLS2)

@@ -83,6 +83,19 @@ __device__ __forceinline__ float silu_grad_f(float u) {
   float s = __fdividef(1.0f, 1.0f + __expf(-u));
   return s * (1.0f + u * (1.0f - s));
 }
+// 16-bit modes: sigmoid(u) = 0.5 + 0.5 tanh(u / 2) with ONE MUFU op (tanh.approx, |rel err| < 2^-10.9, below the
+// fp16/bf16 rounding of the stored result) instead of ex2 + rcp; the fp32 validation mode keeps the exact form.
+__device__ __forceinline__ float fast_sigmoid(float u) {
+  float t;
+  asm("tanh.approx.f32 %0, %1;" : "=f"(t) : "f"(0.5f * u));
+  return fmaf(t, 0.5f, 0.5f);
+}
+template <bool FAST> __device__ __forceinline__ float silu_t(float u) { return FAST ? u * fast_sigmoid(u) : silu_f(u); }
+template <bool FAST> __device__ __forceinline__ float silu_grad_t(float u) {
+  if (!FAST) return silu_grad_f(u);
+  const float s = fast_sigmoid(u);
+  return s * fmaf(u, 1.0f - s, 1.0f);
+}
 
 static inline int ceil_div(int64_t a, int64_t b) { return static_cast<int>((a + b - 1) / b); }
 

@@ -530,9 +530,9 @@ int describe_conv_wgrad(EngineDesc& d, const void* x, const void* dy, float* ws,
     spatial_box(d.boxB, p.sp_rank, kbw, kbh);
     // Halo mode (3x3 stride 1, K chunk = 64 pixels of one image row): the x tile is fetched once per filter row with one
     // halo pixel on each side instead of three shifted copies (stage 64 KB -> 34 KB at Cin block 128)
-    if (T == 3 && geom == ODVAE_CONV_3x3_S1 && kbw == 64 && kbh == 1 && !g_disable_halo) {
+    if (T == 3 && geom == ODVAE_CONV_3x3_S1 && kbw >= 16 && !g_disable_halo) {
       p.halo = 1;
-      d.boxB[0] = 64; d.boxB[1] = TC_WHALO_BOX; d.boxB[2] = 1; d.boxB[3] = 1;
+      d.boxB[0] = 64; d.boxB[1] = static_cast<uint32_t>(kbw + 2); d.boxB[2] = static_cast<uint32_t>(kbh); d.boxB[3] = 1;
     }
   } else {
     // SIMT: 64x64 output tiles; split K so the grid fills the machine

@@ -75,7 +75,7 @@ gn_reduce_kernel(const T* __restrict__ x, const TG* __restrict__ dy, const float
             s1[j] = fmaf(v, v, s1[j]);
           } else {
             float d = to_f32<TG>(dv[u][j]);
-            if (silu) d *= silu_grad_f(fmaf(v, sc[j], sh[j]));
+            if (silu) d *= silu_grad_t<sizeof(T) == 2>(fmaf(v, sc[j], sh[j]));
             s0[j] += d;
             s1[j] = fmaf(d, (v - mu[j]) * rs[j], s1[j]);
           }
@@ -99,7 +99,7 @@ gn_reduce_kernel(const T* __restrict__ x, const TG* __restrict__ dy, const float
         for (int j = 0; j < V; ++j) {
           const float v = to_f32<T>(xv[j]);
           float d = to_f32<TG>(dv[j]);
-          if (silu) d *= silu_grad_f(fmaf(v, sc[j], sh[j]));
+          if (silu) d *= silu_grad_t<sizeof(T) == 2>(fmaf(v, sc[j], sh[j]));
           s0[j] += d;
           s1[j] = fmaf(d, (v - mu[j]) * rs[j], s1[j]);
         }
@@ -196,7 +196,7 @@ gn_apply_kernel(const T* __restrict__ x, const float* __restrict__ stats, const 
 #pragma unroll
       for (int j = 0; j < V; ++j) {
         float v = fmaf(to_f32<T>(xv[u][j]), scale[j], shift[j]);
-        if (silu) v = silu_f(v);
+        if (silu) v = silu_t<sizeof(T) == 2>(v);
         yv[j] = from_f32<TO>(v);
         y2v[j] = from_f32<TO2>(v);
       }
@@ -212,7 +212,7 @@ gn_apply_kernel(const T* __restrict__ x, const float* __restrict__ stats, const 
 #pragma unroll
     for (int j = 0; j < V; ++j) {
       float v = fmaf(to_f32<T>(xv[j]), scale[j], shift[j]);
-      if (silu) v = silu_f(v);
+      if (silu) v = silu_t<sizeof(T) == 2>(v);
       yv[j] = from_f32<TO>(v);
       y2v[j] = from_f32<TO2>(v);
     }
@@ -324,7 +324,7 @@ gn_bwd_apply_kernel(const T* __restrict__ x, const TG* __restrict__ dy, const TG
         for (int j = 0; j < V; ++j) {
           const float xf = to_f32<T>(xv[u][j]);
           float d = to_f32<TG>(dv[u][j]);
-          if (silu) d *= silu_grad_f(fmaf(xf, scale[j], shift[j]));
+          if (silu) d *= silu_grad_t<sizeof(T) == 2>(fmaf(xf, scale[j], shift[j]));
           float o = fmaf(scale[j], d, fmaf(c2[j], xf, c3[j]));
           if (ab) o += to_f32<TG>(av[u][j]);
           ov[j] = from_f32<TG>(o);

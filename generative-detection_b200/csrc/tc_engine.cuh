@@ -21,8 +21,8 @@ static constexpr int TC_TMEM_COLS = 512;
 // 130-pixel TMA boxes (x = -1..128 and 129..258; out-of-image pixels are zero-filled); padded to a 1 KiB multiple
 static constexpr int TC_HALO_BOX = 130;
 static constexpr int TC_SLAB_BYTES = 33 * 1024;
-// weight-gradient halo slab: 64 output pixels of one image row + 1 halo pixel on each side (one 66-pixel TMA box)
-static constexpr int TC_WHALO_BOX = 66;
+// weight-gradient halo slab: the K chunk's 64 output pixels (kbw x kbh, kbw = 64 / 32 / 16) with 1 halo pixel on each
+// side of every row, one TMA box of (kbw + 2) x kbh pixels: 66 / 68 / 72 rows of 128 B
 static constexpr int TC_WSLAB_BYTES = 9 * 1024;
 
 struct TileCoord {
@@ -92,6 +92,7 @@ tc_engine_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant_
   uint8_t* sA = smem;
   uint8_t* sB = smem + static_cast<size_t>(stages) * TC_A_BYTES;
   // halo mode: sA = weight stages, sB = ring of input-row slabs
+  const uint32_t wslab_tx = static_cast<uint32_t>(((1 << p.kbw_log2) + 2) * (TC_BLOCK_K >> p.kbw_log2)) * 128u;
   const bool cv_halo = p.kind == KIND_CONV && p.halo;
   const int nslabs = cv_halo ? p.halo_slabs : 0;
   uint64_t* bars = reinterpret_cast<uint64_t*>(
@@ -183,8 +184,7 @@ tc_engine_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant_
         for (int kit = 0; kit < nk; ++kit) {
           mbar_wait(&empty_bar[stage], phase ^ 1u);
           uint64_t* fb = &full_bar[stage];
-          mbar_arrive_expect_tx(fb, wg_halo ? TC_A_BYTES + static_cast<uint32_t>(BN >> 6) * (TC_WHALO_BOX * 128u)
-                                            : TC_A_BYTES + b_bytes);
+          mbar_arrive_expect_tx(fb, wg_halo ? TC_A_BYTES + static_cast<uint32_t>(BN >> 6) * wslab_tx : TC_A_BYTES + b_bytes);
           uint8_t* a_dst = sA + static_cast<size_t>(stage) * TC_A_BYTES;
           uint8_t* b_dst = sB + static_cast<size_t>(stage) * b_bytes;
           if (p.kind == KIND_GEMM) {
@@ -321,8 +321,11 @@ tc_engine_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant_
             if (wg_halo) {
               // per 64-channel chunk one N = 192 MMA: the three 64-wide N chunks are the same channels read 0 / 1 / 2
               // pixel rows into the slab (LBO = 128 B), i.e. the taps dx = -1, 0, +1
+              // K step k = output pixels 16k .. 16k + 15 of the chunk = slab rows (row r, x offset xo) + tap shift
+              const int r16 = (16 * k) >> p.kbw_log2, xo = (16 * k) & ((1 << p.kbw_log2) - 1);
+              const uint32_t koff = static_cast<uint32_t>(r16 * ((1 << p.kbw_log2) + 2) + xo) * 128u;
               for (int j = 0; j < (BN >> 6); ++j) {
-                const uint64_t bd = make_smem_desc_sw128(b_base + j * TC_WSLAB_BYTES + k * 2048, 128, 1024);
+                const uint64_t bd = make_smem_desc_sw128(b_base + j * TC_WSLAB_BYTES + koff, 128, 1024);
                 umma_bf16(d_tmem + static_cast<uint32_t>(j * 192), adesc, bd, idesc_h, (kit | k) != 0 ? 1u : 0u);
               }
               continue;

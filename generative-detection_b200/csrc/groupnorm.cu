@@ -21,16 +21,20 @@ template <typename T, typename TG, int MODE>
 __global__ void __launch_bounds__(GN_THREADS)
 gn_reduce_kernel(const T* __restrict__ x, const TG* __restrict__ dy, const float* __restrict__ stats,
                  const float* __restrict__ gamma, const float* __restrict__ beta, float* __restrict__ part, int HW,
-                 int C, int G, int silu) {
+                 int C, int G, int silu, int nsplit, int nitems) {
   constexpr int V = VecN<T>::V;
   const int cv = C / V;
   const int rows = GN_THREADS / cv;
   const int col = threadIdx.x % cv, row = threadIdx.x / cv;
-  const int b = blockIdx.y, split = blockIdx.x, nsplit = gridDim.x;
+  const int c0 = col * V;
+  extern __shared__ float red[];
+  // persistent grid (one resident wave): work items (image b, pixel range `split`) are taken grid-stride, so the
+  // kernel has no partial last wave whatever the batch size
+  for (int item = blockIdx.x; item < nitems; item += gridDim.x) {
+  const int b = item / nsplit, split = item - b * nsplit;
   const int per = (HW + nsplit - 1) / nsplit;
   const int p0 = split * per;
   const int p1 = p0 + per < HW ? p0 + per : HW;
-  const int c0 = col * V;
 
   float s0[V], s1[V];
 #pragma unroll
@@ -107,7 +111,6 @@ gn_reduce_kernel(const T* __restrict__ x, const TG* __restrict__ dy, const float
     }
   }
   // block reduction over rows: red[2][rows][C]
-  extern __shared__ float red[];
   float* r0 = red;
   float* r1 = red + rows * C;
   if (row < rows) {
@@ -128,6 +131,8 @@ gn_reduce_kernel(const T* __restrict__ x, const TG* __restrict__ dy, const float
     dst[0] = a;
     dst[1] = bb;
   }
+  __syncthreads();  // red[] is reused by the next item
+  }
 }
 
 // forward finalize: one CTA per image; stats[b][g] = (mean, rstd)
@@ -135,21 +140,25 @@ __global__ void gn_stats_finalize_kernel(const float* __restrict__ part, float* 
                                          int C, int G, float eps) {
   const int b = blockIdx.x;
   const int cpg = C / G;
-  for (int g = threadIdx.x; g < G; g += blockDim.x) {
+  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31, nwarps = blockDim.x >> 5;
+  for (int g = warp; g < G; g += nwarps) {  // one warp per group: lanes over (split, channel) pairs, fixed-order tree
     float s = 0.0f, ss = 0.0f;
-    for (int sp = 0; sp < nsplit; ++sp) {
-      const float* src = part + ((static_cast<long long>(b) * nsplit + sp) * C + g * cpg) * 2;
-      for (int j = 0; j < cpg; ++j) {
-        s += src[2 * j];
-        ss += src[2 * j + 1];
-      }
+    for (int i = lane; i < nsplit * cpg; i += 32) {
+      const int sp = i / cpg, j = i - sp * cpg;
+      const float* src = part + ((static_cast<long long>(b) * nsplit + sp) * C + g * cpg + j) * 2;
+      s += src[0];
+      ss += src[1];
     }
-    const float n = static_cast<float>(cpg) * HW;
-    const float mean = s / n;
-    float var = ss / n - mean * mean;
-    var = var < 0.0f ? 0.0f : var;
-    stats[(static_cast<long long>(b) * G + g) * 2] = mean;
-    stats[(static_cast<long long>(b) * G + g) * 2 + 1] = rsqrtf(var + eps);
+    s = warp_sum(s);
+    ss = warp_sum(ss);
+    if (lane == 0) {
+      const float n = static_cast<float>(cpg) * HW;
+      const float mean = s / n;
+      float var = ss / n - mean * mean;
+      var = var < 0.0f ? 0.0f : var;
+      stats[(static_cast<long long>(b) * G + g) * 2] = mean;
+      stats[(static_cast<long long>(b) * G + g) * 2 + 1] = rsqrtf(var + eps);
+    }
   }
 }
 
@@ -335,14 +344,43 @@ gn_bwd_apply_kernel(const T* __restrict__ x, const TG* __restrict__ dy, const TG
   }
 }
 
-static int gn_nsplit(int B, int HW) {
-  int target = (6 * num_sms() + B - 1) / B;
+// Pixel-range splits per image for the reduce kernels. The reduce grid is ONE resident wave of `slots` CTAs taking
+// (image, split) items grid-stride; B * nsplit is chosen near 4 items per CTA so that items / slots falls just below
+// an integer (no CTA does a whole extra item while the others idle). slots <= 0: conservative 2 CTAs per SM.
+static int gn_nsplit(int B, int HW, int slots) {
+  if (slots <= 0) slots = 2 * num_sms();
   int maxs = HW / 32;
   if (maxs < 1) maxs = 1;
-  if (target > maxs) target = maxs;
-  if (target > 128) target = 128;
-  if (target < 1) target = 1;
-  return target;
+  if (maxs > 128) maxs = 128;
+  int lo = (2 * slots + B - 1) / B, hi = (5 * slots) / B;
+  if (lo < 1) lo = 1;
+  if (hi < lo) hi = lo;
+  if (lo > maxs) lo = maxs;
+  if (hi > maxs) hi = maxs;
+  int best = lo;
+  double best_eff = -1.0;
+  for (int ns = lo; ns <= hi; ++ns) {
+    const double w = static_cast<double>(B) * ns / slots;
+    const double waves = w <= 1.0 ? 1.0 : static_cast<double>(static_cast<long long>(w + 0.999999));
+    const double eff = w <= 1.0 ? w : w / waves;
+    if (eff >= best_eff) {
+      best_eff = eff;
+      best = ns;
+    }
+  }
+  return best;
+}
+// resident CTAs of a reduce-kernel instantiation (cached per kernel pointer / smem size)
+template <typename K>
+static int gn_slots(K kernel, size_t smem) {
+  int per_sm = 0;
+  if (cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, kernel, GN_THREADS, smem) != cudaSuccess || per_sm < 1) per_sm = 1;
+  return per_sm * num_sms();
+}
+static int gn_ws_nsplit(int B, int HW) {  // upper bound of nsplit over both reduce modes (workspace sizing)
+  int maxs = HW / 32;
+  if (maxs < 1) maxs = 1;
+  return maxs > 128 ? 128 : maxs;
 }
 static bool gn_shape_ok(int C, int G, int V) {
   if (C % G != 0 || C % V != 0) return false;
@@ -366,7 +404,7 @@ using namespace odvae;
 extern "C" {
 
 size_t odvae_groupnorm_workspace_bytes(int B, int HW, int C, int G) {
-  const int ns = gn_nsplit(B, HW);
+  const int ns = gn_ws_nsplit(B, HW);
   return (static_cast<size_t>(B) * ns * C * 2 + static_cast<size_t>(B) * C * 2 + static_cast<size_t>(B) * G * 2) * sizeof(float) + 256;
 }
 
@@ -375,21 +413,32 @@ int odvae_groupnorm_stats(const void* x, float* stats, int B, int HW, int C, int
   cudaStream_t st = static_cast<cudaStream_t>(stream);
   const int V = act_dtype == ODVAE_F32 ? 4 : 8;
   if (!gn_shape_ok(C, G, V)) return ODVAE_ERR_SHAPE;
-  const int ns = gn_nsplit(B, HW);
-  if (ws_bytes < static_cast<size_t>(B) * ns * C * 2 * sizeof(float)) return ODVAE_ERR_WORKSPACE;
+  if (ws_bytes < static_cast<size_t>(B) * gn_ws_nsplit(B, HW) * C * 2 * sizeof(float)) return ODVAE_ERR_WORKSPACE;
   float* part = reinterpret_cast<float*>(workspace);
   const int rows = GN_THREADS / (C / V);
   const size_t smem = static_cast<size_t>(2) * rows * C * sizeof(float);
-  dim3 grid(ns, B);
-  if (act_dtype == ODVAE_BF16)
-    gn_reduce_kernel<bf16, bf16, 0><<<grid, GN_THREADS, smem, st>>>(reinterpret_cast<const bf16*>(x), nullptr, nullptr, nullptr, nullptr, part, HW, C, G, 0);
-  else if (act_dtype == ODVAE_F16)
-    gn_reduce_kernel<f16, bf16, 0><<<grid, GN_THREADS, smem, st>>>(reinterpret_cast<const f16*>(x), nullptr, nullptr, nullptr, nullptr, part, HW, C, G, 0);
-  else
-    gn_reduce_kernel<float, float, 0><<<grid, GN_THREADS, smem, st>>>(reinterpret_cast<const float*>(x), nullptr, nullptr, nullptr, nullptr, part, HW, C, G, 0);
+  int ns;
+#define GN_LAUNCH_REDUCE0(T)                                                                                          \
+  {                                                                                                                   \
+    const int slots = gn_slots(gn_reduce_kernel<T, bf16, 0>, smem);                                                   \
+    ns = gn_nsplit(B, HW, slots);                                                                                     \
+    const int items = B * ns;                                                                                         \
+    gn_reduce_kernel<T, bf16, 0><<<items < slots ? items : slots, GN_THREADS, smem, st>>>(                             \
+        reinterpret_cast<const T*>(x), nullptr, nullptr, nullptr, nullptr, part, HW, C, G, 0, ns, items);             \
+  }
+  if (act_dtype == ODVAE_BF16) GN_LAUNCH_REDUCE0(bf16)
+  else if (act_dtype == ODVAE_F16) GN_LAUNCH_REDUCE0(f16)
+  else {
+    const int slots = gn_slots(gn_reduce_kernel<float, float, 0>, smem);
+    ns = gn_nsplit(B, HW, slots);
+    const int items = B * ns;
+    gn_reduce_kernel<float, float, 0><<<items < slots ? items : slots, GN_THREADS, smem, st>>>(
+        reinterpret_cast<const float*>(x), nullptr, nullptr, nullptr, nullptr, part, HW, C, G, 0, ns, items);
+  }
+#undef GN_LAUNCH_REDUCE0
   int s = check_launch("gn_reduce_kernel<0>");
   if (s != ODVAE_OK) return s;
-  gn_stats_finalize_kernel<<<B, 32, 0, st>>>(part, stats, ns, HW, C, G, eps);
+  gn_stats_finalize_kernel<<<B, 256, 0, st>>>(part, stats, ns, HW, C, G, eps);
   return check_launch("gn_stats_finalize_kernel");
 }
 
@@ -429,20 +478,26 @@ int odvae_groupnorm_bwd(const void* x, const float* stats, const float* gamma, c
                     : (act_dtype == ODVAE_F16 && grad_dtype == ODVAE_BF16)  ? 2
                                                                             : -1;
   if (combo < 0) return ODVAE_ERR_SHAPE;
-  const int ns = gn_nsplit(B, HW);
   if (ws_bytes < odvae_groupnorm_workspace_bytes(B, HW, C, G) - 256) return ODVAE_ERR_WORKSPACE;
   float* part = reinterpret_cast<float*>(workspace);
-  float* AB = part + static_cast<size_t>(B) * ns * C * 2;
+  float* AB = part + static_cast<size_t>(B) * gn_ws_nsplit(B, HW) * C * 2;
   float* coef = AB + static_cast<size_t>(B) * C * 2;
   const int rows = GN_THREADS / (C / V);
   const size_t smem = static_cast<size_t>(2) * rows * C * sizeof(float);
-  dim3 grid(ns, B);
-  if (combo == 1)
-    gn_reduce_kernel<bf16, bf16, 1><<<grid, GN_THREADS, smem, st>>>(reinterpret_cast<const bf16*>(x), reinterpret_cast<const bf16*>(dy), stats, gamma, beta, part, HW, C, G, silu);
-  else if (combo == 2)
-    gn_reduce_kernel<f16, bf16, 1><<<grid, GN_THREADS, smem, st>>>(reinterpret_cast<const f16*>(x), reinterpret_cast<const bf16*>(dy), stats, gamma, beta, part, HW, C, G, silu);
-  else
-    gn_reduce_kernel<float, float, 1><<<grid, GN_THREADS, smem, st>>>(reinterpret_cast<const float*>(x), reinterpret_cast<const float*>(dy), stats, gamma, beta, part, HW, C, G, silu);
+  int ns;
+#define GN_LAUNCH_REDUCE1(T, TG)                                                                                      \
+  {                                                                                                                   \
+    const int slots = gn_slots(gn_reduce_kernel<T, TG, 1>, smem);                                                     \
+    ns = gn_nsplit(B, HW, slots);                                                                                     \
+    const int items = B * ns;                                                                                         \
+    gn_reduce_kernel<T, TG, 1><<<items < slots ? items : slots, GN_THREADS, smem, st>>>(                               \
+        reinterpret_cast<const T*>(x), reinterpret_cast<const TG*>(dy), stats, gamma, beta, part, HW, C, G, silu, ns, \
+        items);                                                                                                       \
+  }
+  if (combo == 1) GN_LAUNCH_REDUCE1(bf16, bf16)
+  else if (combo == 2) GN_LAUNCH_REDUCE1(f16, bf16)
+  else GN_LAUNCH_REDUCE1(float, float)
+#undef GN_LAUNCH_REDUCE1
   int s = check_launch("gn_reduce_kernel<1>");
   if (s != ODVAE_OK) return s;
   gn_bwd_finalize_a_kernel<<<B, 256, static_cast<size_t>(2) * C * sizeof(float), st>>>(part, stats, gamma, AB, coef, ns, HW, C, G);

@@ -1,6 +1,7 @@
 // C ABI for convolution and batched GEMM (see include/odvae_b200.h).
 #include "common.cuh"
 #include "engine_host.h"
+#include "skinny_gemm.cuh"
 
 using namespace odvae;
 
@@ -164,6 +165,20 @@ int odvae_attn_dsoftmax(const void* dO, const void* v, const void* P, const floa
 int odvae_gemm_simt(const void* A, const void* B, void* D, int M, int N, int K, int batch, int64_t lda, int64_t ldb,
                     int64_t ldd, int64_t strideA, int64_t strideB, int64_t strideD, int a_mn, int b_mn, int in_dtype,
                     int out_dtype, float alpha, const float* bias, const void* residual, void* stream) {
+  if (in_dtype == ODVAE_F32 && out_dtype == ODVAE_F32 && batch == 1 && !a_mn && residual == nullptr && M <= 64 &&
+      K >= 256 && N >= 1) {
+    // pose-MLP Linears (M = batch): K split over the warps of a CTA, one CTA per narrow column strip
+    cudaStream_t s = static_cast<cudaStream_t>(stream);
+    const float* a = reinterpret_cast<const float*>(A);
+    const float* w = reinterpret_cast<const float*>(B);
+    float* dst = reinterpret_cast<float*>(D);
+    if (!b_mn) {
+      skinny_gemm_nt_kernel<<<(N + 7) / 8, 256, 0, s>>>(a, w, bias, dst, M, N, K, lda, ldb, ldd, alpha);
+      return check_launch("skinny_gemm_nt_kernel");
+    }
+    skinny_gemm_nn_kernel<<<dim3((N + 31) / 32, (M + 31) / 32), 256, 0, s>>>(a, w, bias, dst, M, N, K, lda, ldb, ldd, alpha);
+    return check_launch("skinny_gemm_nn_kernel");
+  }
   EngineDesc d;
   // out_dtype: ODVAE_F32 -> fp32 output; otherwise the activation dtype (= in_dtype)
   int st = describe_gemm(d, A, B, D, M, N, K, batch, lda, ldb, ldd, strideA, strideB, strideD, a_mn, b_mn,

@@ -229,3 +229,22 @@ def test_gemm_rejects_mixed_operand_formats():
     D = torch.empty(128, 128, dtype=torch.float32, device=DEV)
     with pytest.raises(RuntimeError):
         call("gemm_16", A, Bm, D, 128, 128, 64, 1, 64, 64, 128, 0, 0, 0, 0, 0, F16, BF16, F32, 1.0, None, None)
+
+
+@pytest.mark.parametrize("M,N,Kd", [(64, 500, 4096), (64, 27, 500), (5, 4096, 500), (64, 500, 500), (33, 19, 260)])
+@pytest.mark.parametrize("b_mn", [False, True])
+def test_skinny_fp32_linear(M, N, Kd, b_mn):
+    """Pose-MLP Linears (M = batch rows, fp32): the K-split skinny kernels behind odvae_gemm_simt, forward layout
+    (weights [N][K]) and the dx layout (weights [K][N]), against torch fp32 (<= 1e-4, fixed-order sums)."""
+    torch.manual_seed(3)
+    A = torch.randn(M, Kd, device=DEV)
+    W = torch.randn(Kd, N, device=DEV) if b_mn else torch.randn(N, Kd, device=DEV)
+    bias = torch.randn(N, device=DEV)
+    ref = 0.5 * (A @ (W if b_mn else W.t())) + bias
+    out = torch.empty(1, M, N, device=DEV)
+    K.gemm(A, W, M, N, Kd, b_mn=b_mn, alpha=0.5, bias=bias, out=out, impl=IMPL_SIMT)
+    out2 = torch.empty(1, M, N, device=DEV)
+    K.gemm(A, W, M, N, Kd, b_mn=b_mn, alpha=0.5, bias=bias, out=out2, impl=IMPL_SIMT)
+    torch.cuda.synchronize()
+    assert rel_err(out[0], ref) < 1e-4
+    assert torch.equal(out, out2)  # bit-stable run to run

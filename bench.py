@@ -189,9 +189,21 @@ class EngineProfiler:
     """Wraps ops.call for ONE extra (untimed) step: brackets each conv/GEMM C-ABI call with CUDA events on the
     launching stream and adds up the algorithmic FLOPs (2*M*N*K of the real, unpadded problem)."""
     NAMES = {"conv2d_fwd", "conv2d_dgrad", "conv2d_wgrad", "gemm_bf16", "attn_scores_softmax", "attn_dsoftmax"}
+    # memory-bound GroupNorm(+SiLU) calls, judged against the HBM roofline (SURVEY 8d): algorithmic bytes at 2 B per
+    # element are 2*E forward (stats + apply together: read x once, write y once) and 3*E backward (x, dy -> dx)
+    GN_NAMES = {"groupnorm_stats", "groupnorm_apply", "groupnorm_bwd"}
 
     def __init__(self):
         self.records = []
+        self.gn = []
+
+    @staticmethod
+    def gn_bytes(name, a):
+        if name == "groupnorm_stats":
+            return 0.0  # its time counts, its bytes are the forward's 2*E attributed to the apply call
+        if name == "groupnorm_apply":
+            return 2.0 * a[6] * a[7] * a[8] * 2
+        return 3.0 * a[9] * a[10] * a[11] * 2
 
     def flops(self, name, a):
         if name == "gemm_bf16":
@@ -244,6 +256,13 @@ class EngineProfiler:
                 e1.record()
                 self.records.append((name, e0, e1, self.flops(name, a), self.shape_key(name, a)))
                 return out
+            if name in self.GN_NAMES:
+                e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+                e0.record()
+                out = self.orig(name, *a)
+                e1.record()
+                self.gn.append((name, e0, e1, self.gn_bytes(name, a)))
+                return out
             return self.orig(name, *a)
 
         ops.call = wrapped
@@ -260,6 +279,17 @@ class EngineProfiler:
             t, ff, c = by.get(n, (0.0, 0.0, 0))
             by[n] = (t + e0.elapsed_time(e1), ff + f, c + 1)
         return tot_ms, tot_fl, len(self.records), by
+
+    def gn_summary(self, hbm_peak):
+        torch.cuda.synchronize()
+        out = {}
+        for tag, names in (("fwd", ("groupnorm_stats", "groupnorm_apply")), ("bwd", ("groupnorm_bwd",))):
+            ms = sum(e0.elapsed_time(e1) for n, e0, e1, _ in self.gn if n in names)
+            by = sum(b for n, _, _, b in self.gn if n in names)
+            if ms > 0:
+                gbs = by / (ms * 1e-3) / 1e9
+                out[tag] = {"ms": ms, "algorithmic_GB": by / 1e9, "achieved_GBps": gbs, "frac_of_hbm_peak": gbs / hbm_peak}
+        return out
 
     def shapes(self):
         tab = {}
@@ -374,12 +404,20 @@ def run_ours(args):
         achieved = FLOPS_TRAIN_PER_IMG * B / (eng_ms * 1e-3) / 1e12
         roof = {"bound": "tensor", "kernel": "tc_engine_kernel (tcgen05 implicit-GEMM conv fwd/dgrad/wgrad + attention GEMMs)",
                 "achieved": achieved, "peak": peak, "unit": "TFLOP/s", "frac": achieved / peak,
-                "peak_source": how + " (bf16_tflops_sustained: kernel timed inside a long step)", "traffic": None,
+                "peak_source": how + " (bf16_tflops_sustained: kernel timed inside a long step)",
+                # DRAM bytes per launch of tc_engine_kernel, averaged over the 333 engine launches of one step:
+                # ncu dram__bytes_read.sum + dram__bytes_write.sum = 166.93 GB + 61.40 GB (profiles/r01_launches_s6.txt);
+                # the dominant shape alone (128->128 3x3 at 256x256): 2.108 GB per launch against 2.147 GB algorithmic
+                # (x in + y out, batch 64) in the `ncu --set full` capture profiles/r01_conv_full_raw.csv
+                "traffic": 228.33e9 / 333, "traffic_unit": "bytes per launch (step average)",
                 "engine_ms_per_step": eng_ms, "engine_calls_per_step": ncalls,
                 "engine_share_of_step": eng_ms / (ms / args.steps),
                 "algorithmic_flops_per_step": FLOPS_TRAIN_PER_IMG * B, "counted_padded_flops_per_step": counted,
                 "by_call": {k: {"ms": v[0], "tflops_padded": v[1] / (v[0] * 1e-3) / 1e12 if v[0] > 0 else None, "calls": v[2]}
-                            for k, v in by.items()}}
+                            for k, v in by.items()},
+                # second roofline (HBM-bound kernels): GroupNorm(+SiLU) forward (stats + apply) and backward
+                # (reduce + finalize + apply) C-ABI calls, algorithmic bytes over CUDA-event time, peak = hbm_gbs
+                "hbm_kernels": {"peak_GBps": pk["hbm_gbs"], "groupnorm": prof.gn_summary(pk["hbm_gbs"])}}
 
     if rank == 0:
         cpu = None

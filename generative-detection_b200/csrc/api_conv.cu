@@ -71,13 +71,23 @@ int odvae_conv2d_wgrad(const void* x, const void* dy, float* dw_oihw, float* db,
   if (st != ODVAE_OK) return st;
   const size_t part = static_cast<size_t>(d.p.ntaps) * d.p.split_k * CoutP * CinP * sizeof(float);
   if (ws_bytes < part + colsum_workspace_bytes(CoutP)) return ODVAE_ERR_WORKSPACE;
+  float* cpart = reinterpret_cast<float*>(reinterpret_cast<uint8_t*>(workspace) + ((part + 255) / 256) * 256);
+  // tcgen05 path: the bias gradient (column sums of dy) is accumulated by the weight-gradient kernel's idle epilogue
+  // warps from the dy tiles already in shared memory -- no second pass over dy
+  const int cs_rows = (d.p.ntaps / (d.p.wg_T > 0 ? d.p.wg_T : 1)) * d.p.split_k * 2;
+  const bool fused_db = db != nullptr && impl == ODVAE_IMPL_TC && d.tc_ok &&
+                        static_cast<size_t>(cs_rows) * Cout * sizeof(float) <= colsum_workspace_bytes(CoutP);
+  if (fused_db) {
+    d.p.colsum = cpart;
+    d.p.colsum_cols = Cout;
+  }
   st = run_engine(d, impl, act_dtype, s);
   if (st != ODVAE_OK) return st;
   st = launch_wgrad_reduce(ws, dw_oihw, Cout, Cin, d.p.ntaps, CoutP, CinP, d.p.split_k, accumulate, s);
   if (st != ODVAE_OK) return st;
+  if (fused_db) return launch_colsum_final(cpart, cs_rows, Cout, db, accumulate, s);
   if (db != nullptr) {
     const int Ho = geom == ODVAE_CONV_3x3_S2 ? H / 2 : H, Wo = geom == ODVAE_CONV_3x3_S2 ? W / 2 : W;
-    float* cpart = reinterpret_cast<float*>(reinterpret_cast<uint8_t*>(workspace) + ((part + 255) / 256) * 256);
     st = launch_colsum(dy, static_cast<long long>(B) * Ho * Wo, Cout, CoutP, act_dtype, db, accumulate, cpart, s);
   }
   return st;

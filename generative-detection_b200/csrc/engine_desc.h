@@ -40,6 +40,11 @@ struct TcParams {
   const float* bias;
   const void* residual;
   void* D;
+  // WGRAD: bias gradient fused into the weight-gradient GEMM. The epilogue warps (idle during the K loop) sum the dy
+  // tiles from shared memory; tile (tap group g, split s) covers the K chunks kit % ngroups == g of its split and
+  // writes colsum[((g * split_k + s) * 2 + pixel half) * colsum_cols + channel] (fixed order, no atomics).
+  float* colsum;
+  int colsum_cols;
 };
 
 

@@ -397,6 +397,12 @@ int launch_wgrad_reduce(const float* ws, float* dw, int Cout, int Cin, int taps,
   return check_launch("wgrad_reduce_kernel");
 }
 
+// final stage alone: out[c] (+)= sum_r part[r][c] -- the tcgen05 weight-gradient kernel writes the partials itself
+int launch_colsum_final(const float* part, int nrows, int cols, float* out, int accumulate, cudaStream_t st) {
+  colsum_stage2<<<(cols + 31) / 32, dim3(32, 8), 0, st>>>(part, nrows, cols, out, accumulate);
+  return check_launch("colsum_stage2");
+}
+
 static constexpr int COLSUM_BLOCKS = 592;
 size_t colsum_workspace_bytes(int cols) { return static_cast<size_t>(COLSUM_BLOCKS) * cols * sizeof(float); }
 int launch_colsum(const void* m, long long rows, int cols, int ld, int act_dtype, float* out, int accumulate,

@@ -116,7 +116,7 @@ tc_engine_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant_
   if (warp == 1 && lane == 0) {
     for (int i = 0; i < stages; ++i) {
       mbar_init(&full_bar[i], 1);
-      mbar_init(&empty_bar[i], 1);
+      mbar_init(&empty_bar[i], p.colsum != nullptr ? 9 : 1);  // + the 8 epilogue warps that sum the dy tiles
     }
     for (int i = 0; i < 2; ++i) {
       mbar_init(&tfull_bar[i], 1);
@@ -363,10 +363,45 @@ tc_engine_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant_
     const int c_end = split_cols ? c_begin + (acc_cols >> 1) : (half == 0 ? acc_cols : 0);
     int acc = 0;
     uint32_t acc_phase = 0;
+    int cs_stage = 0;
+    uint32_t cs_phase = 0;
     for (int t = blockIdx.x; t < total_tiles; t += gridDim.x) {
       const TileCoord tc = decode_tile(p, t);
       const int m0 = tc.m_tile * TC_BLOCK_M;
       const int n0 = tc.n_tile * BN;
+
+      if (p.kind == KIND_WGRAD && p.colsum != nullptr) {
+        // ---- fused bias gradient: column sums of the dy tiles (A operand, MN-major SW128: pixel row k at k * 128 B,
+        // 16-byte chunk (channel / 8) XOR (k % 8)); thread = (channel, pixel half), fixed summation order ----
+        const int nk = tile_k_iters(p, tc);
+        const int ngroups = p.ntaps / wgT;
+        const int grp = tc.tap / wgT;
+        const int ew = warp - 2;
+        const int ch = (ew & 3) * 32 + lane;
+        const int ph = ew >> 2;
+        const int cc = ch & 63;
+        float csum = 0.0f;
+        for (int kit = 0; kit < nk; ++kit) {
+          mbar_wait(&full_bar[cs_stage], cs_phase);
+          if (tc.n_tile == 0 && (kit % ngroups) == grp) {
+            const uint8_t* a = sA + static_cast<size_t>(cs_stage) * TC_A_BYTES + (ch >> 6) * 8192;
+#pragma unroll 8
+            for (int i = 0; i < 32; ++i) {
+              const int k = ph * 32 + i;
+              const uint16_t raw = *reinterpret_cast<const uint16_t*>(a + k * 128 + ((((cc >> 3) ^ (k & 7)) << 4) | ((cc & 7) << 1)));
+              csum += unpack_16x2(static_cast<uint32_t>(raw), p.a_fmt == FMT_F16).x;
+            }
+          }
+          __syncwarp();
+          if (lane == 0) mbar_arrive(&empty_bar[cs_stage]);
+          if (++cs_stage == stages) {
+            cs_stage = 0;
+            cs_phase ^= 1u;
+          }
+        }
+        if (tc.n_tile == 0 && m0 + ch < p.colsum_cols)
+          p.colsum[(static_cast<long long>(grp * p.split_k + tc.split) * 2 + ph) * p.colsum_cols + m0 + ch] = csum;
+      }
 
       bool row_ok = true;
       long long row_off = 0;  // element offset of (row, column n0) in D / residual

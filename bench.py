@@ -49,6 +49,12 @@ def parse():
                     help="profiling aid: after warm-up run ONE step between cudaProfilerStart/Stop and exit "
                          "(use with `ncu --profile-from-start off`); prints no bench line")
     ap.add_argument("--shapes", default="", help="write the per-shape engine timing table (JSON) to this path")
+    ap.add_argument("--workload", default="train", choices=["train", "encode", "recon"],
+                    help="train = BASELINE.json configs[1] (default, the bench line); encode = configs[2], encode-only "
+                         "inference (Encoder + posterior.mode(), no_grad) at --batch; recon = configs[4]: encode -> mode "
+                         "-> decode -> L1 -> backward through decoder and encoder (no pose heads: the config's pose MLPs "
+                         "are sized for 16x16 latents, i.e. 256x256 crops only, in the reference too), use with --res 512")
+    ap.add_argument("--res", type=int, default=RES, help="crop resolution (configs[4]: 512)")
     return ap.parse_args()
 
 
@@ -303,6 +309,86 @@ class EngineProfiler:
 
 
 # --------------------------------------------------------------------------------------------------
+# encode-only inference (BASELINE.json configs[2]): PoseAutoencoder.encode + posterior.mode(), no_grad
+# --------------------------------------------------------------------------------------------------
+FLOPS_ENCODE_PER_IMG = 175.18e9
+
+
+def run_encode(args, model, dev, B, R, rank, world):
+    import torch.distributed as dist
+    from odvae_b200 import lib, synth
+    host = synth.synthetic_batch(B, R, seed=23 + rank)
+    x_host = host["patch"].float().contiguous()  # [B,3,R,R] in [0,1), as the data loader delivers it
+    x_pin = x_host.pin_memory()
+    x_dev = x_host.to(dev)
+
+    recon = args.workload == "recon"
+
+    def step(x):
+        if recon:
+            for prm in model.parameters():
+                prm.grad = None
+            xr = model._rescale(x)
+            post, _ = model.encode(xr)
+            rec = model.decode(post.mode())
+            loss = (rec - xr).abs().mean()
+            loss.backward()
+            return loss.detach().reshape(1)
+        with torch.no_grad():
+            post, _ = model.encode(model._rescale(x))
+            return post.mode()
+
+    def timed(src, steps, e2e):
+        if world > 1:
+            dist.barrier()
+        torch.cuda.synchronize()
+        e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        e0.record()
+        for _ in range(steps):
+            z = step(src.to(dev, non_blocking=True) if e2e else src)
+            if e2e:
+                z = z.cpu()  # device -> host read of the latents
+        e1.record()
+        torch.cuda.synchronize()
+        ms = e0.elapsed_time(e1)
+        if world > 1:
+            t = torch.tensor([ms], device=dev)
+            dist.all_reduce(t, op=dist.ReduceOp.MAX)
+            ms = float(t)
+        return ms, z
+
+    for _ in range(max(args.warmup, 3)):
+        step(x_dev)
+    l0 = lib.call("launch_count")
+    ms, z = timed(x_dev, args.steps, False)
+    launches = lib.call("launch_count") - l0
+    ms_e2e, z = timed(x_pin, args.steps, True)
+    if rank == 0:
+        n_img = B * world * args.steps
+        pk, how = peaks()
+        line = {"metric": "AutoencoderKL encode+decode fwd+bwd images/sec" if recon else "AutoencoderKL encode-only images/sec", "value": n_img / (ms * 1e-3), "unit": "images/sec",
+                "n_gpus": world, "steps": args.steps, "warmup": max(args.warmup, 3), "ms_per_step": ms / args.steps,
+                "higher_is_better": True, "scaling": "weak", "vs_baseline": None,
+                "dtype": "fp16 fwd (tcgen05 kind::f16, fp32 accumulate)" if args.mode == "mixed" else "bf16",
+                "data": "synthetic",
+                "config": {"workload": ("encode -> mode -> decode -> L1 -> backward (Encoder, Decoder, quant convs; no pose "
+                                        "heads, no optimizer), %dx%d crops (BASELINE.json configs[4])" if recon else
+                                        "encode-only inference: Encoder + DiagonalGaussian mode(), %dx%d crops, no_grad "
+                                        "(BASELINE.json configs[2])") % (R, R), "per_gpu_batch": B, "resolution": R},
+                "e2e": {"value": n_img / (ms_e2e * 1e-3), "unit": "images/sec",
+                        "h2d_bytes_per_step": x_host.numel() * 4, "d2h_bytes_per_step": z.numel() * 4,
+                        "ms_per_step": ms_e2e / args.steps},
+                "gpu_launches": int(launches),
+                # encode: conv/attention flops scale ~ (R/256)^2 for the convs; the recon figure uses SURVEY's 512^2 count
+                "pct_of_tensor_roofline_whole_step": ((3 * 2967e9 if R == 512 else 3 * 483.3e9 * (R / 256.0) ** 2) if recon
+                                                      else FLOPS_ENCODE_PER_IMG * (R / 256.0) ** 2) * B /
+                (ms / args.steps * 1e-3) / 1e12 / pk["bf16_tflops_sustained"]}
+        print(json.dumps(line), flush=True)
+    if world > 1:
+        dist.destroy_process_group()
+
+
+# --------------------------------------------------------------------------------------------------
 # GPU arm
 # --------------------------------------------------------------------------------------------------
 def run_ours(args):
@@ -332,7 +418,10 @@ def run_ours(args):
     model.learning_rate = 1 * world * B * 4.5e-6
     step_fn = TrainStep(model, lr=model.learning_rate, max_grad_norm=1.0)
 
-    host = synth.synthetic_batch(B, RES, seed=23 + rank)  # each rank its own shard of the synthetic stream
+    R = args.res
+    if args.workload in ("encode", "recon"):
+        return run_encode(args, model, dev, B, R, rank, world)
+    host = synth.synthetic_batch(B, R, seed=23 + rank)  # each rank its own shard of the synthetic stream
     pinned = {k: (v.pin_memory() if torch.is_tensor(v) else v) for k, v in host.items()}
     resident = {k: (v.to(dev) if torch.is_tensor(v) else v) for k, v in host.items()}
     h2d = sum(v.numel() * v.element_size() for v in host.values() if torch.is_tensor(v))
@@ -387,6 +476,7 @@ def run_ours(args):
     clocks = sampler.stop() if rank == 0 else None
 
     roof = None
+    flops_img = FLOPS_TRAIN_PER_IMG
     if not args.no_roofline and rank != 0:
         step_fn(clone(resident), 0)  # every rank runs the extra (untimed) step: its gradient all-reduces are collective
         torch.cuda.synchronize()
@@ -401,7 +491,9 @@ def run_ours(args):
                 json.dump(prof.shapes(), f, indent=1)
         pk, how = peaks()
         peak = pk["bf16_tflops_sustained"]
-        achieved = FLOPS_TRAIN_PER_IMG * B / (eng_ms * 1e-3) / 1e12
+        if R != RES:  # other resolutions: count the flops of the launched problems (no SURVEY figure)
+            flops_img = counted / B
+        achieved = flops_img * B / (eng_ms * 1e-3) / 1e12
         roof = {"bound": "tensor", "kernel": "tc_engine_kernel (tcgen05 implicit-GEMM conv fwd/dgrad/wgrad + attention GEMMs)",
                 "achieved": achieved, "peak": peak, "unit": "TFLOP/s", "frac": achieved / peak,
                 "peak_source": how + " (bf16_tflops_sustained: kernel timed inside a long step)",
@@ -412,7 +504,7 @@ def run_ours(args):
                 "traffic": 228.33e9 / 333, "traffic_unit": "bytes per launch (step average)",
                 "engine_ms_per_step": eng_ms, "engine_calls_per_step": ncalls,
                 "engine_share_of_step": eng_ms / (ms / args.steps),
-                "algorithmic_flops_per_step": FLOPS_TRAIN_PER_IMG * B, "counted_padded_flops_per_step": counted,
+                "algorithmic_flops_per_step": flops_img * B, "counted_padded_flops_per_step": counted,
                 "by_call": {k: {"ms": v[0], "tflops_padded": v[1] / (v[0] * 1e-3) / 1e12 if v[0] > 0 else None, "calls": v[2]}
                             for k, v in by.items()},
                 # second roofline (HBM-bound kernels): GroupNorm(+SiLU) forward (stats + apply) and backward
@@ -429,16 +521,16 @@ def run_ours(args):
                 "higher_is_better": True, "scaling": "weak", "vs_baseline": None,
                 "dtype": "fp16 fwd + bf16 attn/grad (tcgen05 kind::f16, fp32 accumulate)" if args.mode == "mixed" else "bf16",
                 "data": "synthetic",
-                "config": {"workload": "autoencoder_kl_16x16x16 pose config, 256x256 crops, train step (fwd + KL/L1/pose "
+                "config": {"workload": "autoencoder_kl_16x16x16 pose config, %dx%d crops, train step (fwd + KL/L1/pose " % (R, R) +
                                        "loss + bwd + allreduce + clip 1.0 + Adam), global_step 80000, perceptual_weight=0, "
-                                       "disc_factor=0 (BASELINE.json configs[1])",
-                           "per_gpu_batch": B, "global_batch": B * world, "resolution": RES,
+                                       "disc_factor=0 (BASELINE.json configs[%d])" % (1 if R == RES else 4),
+                           "per_gpu_batch": B, "global_batch": B * world, "resolution": R,
                            "parallelism": "dp%d" % world,
                            "l2": "per-step working set (activations ~40 GB at batch 64) far exceeds the 126 MB L2"},
                 "e2e": {"value": n_img / (ms_e2e * 1e-3), "unit": "images/sec", "h2d_bytes_per_step": h2d,
                         "d2h_bytes_per_step": 4, "ms_per_step": ms_e2e / args.steps, "last_loss": last_loss},
                 "gpu_launches": int(launches), "clocks": clocks, "roofline": roof, "cpu_baseline": cpu,
-                "pct_of_tensor_roofline_whole_step": FLOPS_TRAIN_PER_IMG * B / (ms / args.steps * 1e-3) / 1e12 /
+                "pct_of_tensor_roofline_whole_step": flops_img * B / (ms / args.steps * 1e-3) / 1e12 /
                 peaks()[0]["bf16_tflops_sustained"]}
         print(json.dumps(line), flush=True)
     if world > 1:

@@ -194,7 +194,8 @@ def run_reference(args):
 class EngineProfiler:
     """Wraps ops.call for ONE extra (untimed) step: brackets each conv/GEMM C-ABI call with CUDA events on the
     launching stream and adds up the algorithmic FLOPs (2*M*N*K of the real, unpadded problem)."""
-    NAMES = {"conv2d_fwd", "conv2d_dgrad", "conv2d_wgrad", "gemm_bf16", "attn_scores_softmax", "attn_dsoftmax"}
+    NAMES = {"conv2d_fwd", "conv2d_fwd_gnstats", "conv2d_dgrad", "conv2d_wgrad", "gemm_bf16", "attn_scores_softmax",
+             "attn_dsoftmax"}
     # memory-bound GroupNorm(+SiLU) calls, judged against the HBM roofline (SURVEY 8d): algorithmic bytes at 2 B per
     # element are 2*E forward (stats + apply together: read x once, write y once) and 3*E backward (x, dy -> dx)
     GN_NAMES = {"groupnorm_stats", "groupnorm_apply", "groupnorm_bwd"}
@@ -222,6 +223,9 @@ class EngineProfiler:
         if name == "conv2d_fwd":
             B, H, W, CinP, CoutP, Cout, geom = a[5], a[6], a[7], a[8], a[9], a[10], a[11]
             cin, cout = self._real(CinP), Cout
+        elif name == "conv2d_fwd_gnstats":  # (x, w, bias, residual, y, stats, B, H, W, CinP, CoutP, geom, ...)
+            B, H, W, CinP, CoutP, geom = a[6], a[7], a[8], a[9], a[10], a[11]
+            cin, cout = CinP, CoutP
         elif name == "conv2d_dgrad":
             B, H, W, CinP, CoutP, geom = a[4], a[5], a[6], a[7], a[8], a[9]
             cin, cout = self._real(CinP), self._real(CoutP)
@@ -242,6 +246,8 @@ class EngineProfiler:
             return "attn dP+dsoftmax B%d N%d C%d" % (a[5], a[6], a[7])
         if name == "conv2d_fwd":
             return "fwd B%d %dx%d %d->%d g%d" % (a[5], a[6], a[7], a[8], a[9], a[11])
+        if name == "conv2d_fwd_gnstats":
+            return "fwd+gnstats B%d %dx%d %d->%d g%d" % (a[6], a[7], a[8], a[9], a[10], a[11])
         if name == "conv2d_dgrad":
             return "dgrad B%d %dx%d %d<-%d g%d" % (a[4], a[5], a[6], a[7], a[8], a[9])
         return "wgrad B%d %dx%d %dx%d g%d" % (a[4], a[5], a[6], a[7], a[8], a[11])

@@ -40,6 +40,37 @@ int odvae_conv2d_fwd(const void* x, const void* w_packed, const float* bias, con
   return run_engine(d, impl, act_dtype, static_cast<cudaStream_t>(stream));
 }
 
+static bool gnstats_served(const EngineDesc& d, int CoutP, int G) {
+  return d.tc_ok && d.p.swap && CoutP % G == 0;
+}
+
+size_t odvae_conv2d_fwd_gnstats_workspace_bytes(int B, int H, int W, int CinP, int CoutP, int geom, int G) {
+  EngineDesc d;
+  if (G <= 0 || describe_conv_fwd(d, nullptr, nullptr, nullptr, nullptr, nullptr, B, H, W, CinP, CoutP, CoutP, geom, 0) != ODVAE_OK)
+    return 0;
+  if (!gnstats_served(d, CoutP, G)) return 0;
+  return static_cast<size_t>(B) * d.p.tiles_x * d.p.tiles_y * CoutP * 2 * sizeof(float);
+}
+
+int odvae_conv2d_fwd_gnstats(const void* x, const void* w_packed, const float* bias, const void* residual, void* y,
+                             float* stats, int B, int H, int W, int CinP, int CoutP, int geom, int G, float eps,
+                             int act_dtype, int out_dtype, void* workspace, size_t ws_bytes, void* stream) {
+  EngineDesc d;
+  int st = describe_conv_fwd(d, x, w_packed, bias, residual, y, B, H, W, CinP, CoutP, CoutP, geom, 0);
+  if (st != ODVAE_OK) return st;
+  if (G <= 0 || !gnstats_served(d, CoutP, G)) return ODVAE_ERR_SHAPE;
+  if (act_dtype == ODVAE_F32 || out_dtype == ODVAE_F32) return ODVAE_ERR_SHAPE;
+  const int boxes = d.p.tiles_x * d.p.tiles_y;
+  if (ws_bytes < static_cast<size_t>(B) * boxes * CoutP * 2 * sizeof(float)) return ODVAE_ERR_WORKSPACE;
+  if (out_dtype == ODVAE_F16) d.p.out_mode = OUT_F16;
+  d.p.gn_part = reinterpret_cast<float*>(workspace);
+  cudaStream_t s = static_cast<cudaStream_t>(stream);
+  st = run_engine(d, ODVAE_IMPL_TC, act_dtype, s);
+  if (st != ODVAE_OK) return st;
+  const int Ho = geom == ODVAE_CONV_3x3_S2 ? H / 2 : H, Wo = geom == ODVAE_CONV_3x3_S2 ? W / 2 : W;
+  return launch_gn_stats_finalize(d.p.gn_part, stats, B, boxes, Ho * Wo, CoutP, G, eps, s);
+}
+
 int odvae_conv2d_dgrad(const void* dy, const void* w_packed_dgrad, const void* dx_add, void* dx, int B, int H, int W,
                        int CinP, int CoutP, int geom, int act_dtype, int impl, void* stream) {
   EngineDesc ds[4];

@@ -45,6 +45,10 @@ struct TcParams {
   // writes colsum[((g * split_k + s) * 2 + pixel half) * colsum_cols + channel] (fixed order, no atomics).
   float* colsum;
   int colsum_cols;
+  // CONV (swapped roles): GroupNorm statistics of the OUTPUT fused into the epilogue. Every epilogue thread owns one
+  // channel and 128 pixels of a pixel box: it writes (sum y, sum y^2) of its fp32 results to
+  // gn_part[((image * boxes_per_image + box) * n_valid + channel) * 2] -- the layout gn_stats_finalize reduces.
+  float* gn_part;
 };
 
 

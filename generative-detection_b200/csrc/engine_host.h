@@ -16,6 +16,9 @@ int describe_conv_dgrad(EngineDesc* ds, int* count, const void* dy, const void* 
 int describe_conv_wgrad(EngineDesc& d, const void* x, const void* dy, float* ws, int B, int H, int W, int CinP,
                         int CoutP, int geom, int impl);
 int set_conv_halo_enabled(int on);  // returns the previous setting
+// groupnorm.cu: stats[b][g] = (mean, rstd) from per-(image, split, channel) partial sums
+int launch_gn_stats_finalize(const float* part, float* stats, int B, int nsplit, int HW, int C, int G, float eps,
+                             cudaStream_t st);
 // pointwise.cu
 int launch_attn_stats_combine(const float* part, float* lse2, int B, int slots, int N, cudaStream_t st);
 // layout.cu

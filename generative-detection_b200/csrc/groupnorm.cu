@@ -4,6 +4,7 @@
 // per-(image,channel) partial sums go through a small fp32 workspace and are combined in a fixed
 // order (deterministic, no atomics).
 #include "common.cuh"
+#include "engine_host.h"
 
 namespace odvae {
 
@@ -395,6 +396,12 @@ static int gn_apply_blocks(int B, int HW, int C, int V) {
   if (blocks > cap) blocks = cap;
   if (blocks < 1) blocks = 1;
   return static_cast<int>(blocks);
+}
+
+int launch_gn_stats_finalize(const float* part, float* stats, int B, int nsplit, int HW, int C, int G, float eps,
+                             cudaStream_t st) {
+  gn_stats_finalize_kernel<<<B, 256, 0, st>>>(part, stats, nsplit, HW, C, G, eps);
+  return check_launch("gn_stats_finalize_kernel");
 }
 
 }  // namespace odvae

@@ -438,6 +438,7 @@ tc_engine_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant_
         const long long sx = p.oX;
         mbar_wait(&tfull_bar[acc], acc_phase);
         tc_fence_after();
+        float gs0 = 0.0f, gs1 = 0.0f, gq0 = 0.0f, gq1 = 0.0f;  // fused GroupNorm statistics (two chains each)
         auto emit = [&](uint32_t (&v)[32], int pi0) {
           const int yy = pb_y + (pi0 >> p.bw_log2), xx = pb_x + (pi0 & ((1 << p.bw_log2) - 1));
           const long long base = base0 + static_cast<long long>(yy) * p.oY + static_cast<long long>(xx) * sx;
@@ -453,7 +454,18 @@ tc_engine_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant_
               for (int i = 0; i < 32; ++i) f[i] += unpack_16x2(static_cast<uint32_t>(rr[i]), halfp).x;
             }
 #pragma unroll
-            for (int i = 0; i < 32; ++i) D16[base + i * sx] = static_cast<uint16_t>(pack_16x2(f[i], 0.0f, halfp) & 0xffffu);
+            for (int i = 0; i < 32; i += 2) {
+              const uint32_t pk = pack_16x2(f[i], f[i + 1], halfp);
+              D16[base + i * sx] = static_cast<uint16_t>(pk & 0xffffu);
+              D16[base + (i + 1) * sx] = static_cast<uint16_t>(pk >> 16);
+              if (p.gn_part != nullptr) {  // statistics of the STORED (rounded) values, as the separate pass sees them
+                const float2 r = unpack_16x2(pk, halfp);
+                gs0 += r.x;
+                gq0 = fmaf(r.x, r.x, gq0);
+                gs1 += r.y;
+                gq1 = fmaf(r.y, r.y, gq1);
+              }
+            }
           }
         };
         uint32_t va[32], vb[32];
@@ -469,6 +481,12 @@ tc_engine_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant_
         emit(va, 64);
         tmem_ld_wait();
         emit(vb, 96);
+        if (p.gn_part != nullptr && ch_ok) {
+          const int boxes = p.tiles_x * p.tiles_y;  // pixel boxes per image
+          const int box = 2 * tc.n_tile + half - pb_b * boxes;
+          float2* dst = reinterpret_cast<float2*>(p.gn_part) + (static_cast<long long>(pb_b) * boxes + box) * p.n_valid + n;
+          *dst = make_float2(gs0 + gs1, gq0 + gq1);
+        }
       } else if (p.epi != EPI_NONE) {
         // ---- fused attention epilogues (KIND_GEMM; one accumulator row and <= 128 columns per thread) ----
         // Global reads this tile needs (softmax partials / delta / the P tile) are issued BEFORE waiting for the

@@ -11,6 +11,8 @@ stays short (~60 nodes for the whole autoencoder).
 
 Reference call sites are cited per Function; LD/ = submodules/latent-diffusion/.
 """
+import os
+
 import torch
 
 from . import lib
@@ -244,9 +246,14 @@ def _ret(g, direct):
 # ------------------------------------------------------------------------------------------------
 # raw (non-autograd) kernel wrappers
 # ------------------------------------------------------------------------------------------------
-def conv_fwd_raw(x, spec, w, b, residual=None, out_nchw=False, op=None, out=None):
+FUSE_GN_STATS = os.environ.get("ODVAE_FUSE_GN_STATS", "1") != "0"  # conv epilogues also emit the GroupNorm statistics of their output where the kernel serves it
+
+
+def conv_fwd_raw(x, spec, w, b, residual=None, out_nchw=False, op=None, out=None, gn_stats=False):
     """op: format code of x and the packed weights; out: format code of the NHWC y / residual.
-    Defaults: the spec's Format (fwd code for both), else what x's torch dtype implies."""
+    Defaults: the spec's Format (fwd code for both), else what x's torch dtype implies.
+    gn_stats: the caller knows y feeds a GroupNorm(32) next; where the tcgen05 swapped-role tiles serve the shape the
+    statistics come out of the conv epilogue and ride on the result as `y._odvae_gn_stats` (see gn_stats_of)."""
     fmt = format_of(x, spec)
     op = fmt.fwd if op is None else op
     out = fmt.fwd if out is None else out
@@ -263,6 +270,15 @@ def conv_fwd_raw(x, spec, w, b, residual=None, out_nchw=False, op=None, out=None
         return y
     impl = conv_impl(op, B, H, W, CinP, spec.coutp, spec.geom)
     y = torch.empty(B, Ho, Wo, spec.coutp, dtype=buf_dtype(out), device=x.device)
+    if gn_stats and FUSE_GN_STATS and impl == IMPL_TC and op != F32 and spec.coutp == spec.cout:
+        nbytes = call("conv2d_fwd_gnstats_workspace_bytes", B, H, W, CinP, spec.coutp, spec.geom, GROUPS)
+        if nbytes:
+            ws = workspace(nbytes, x.device, "gnconv")
+            stats = torch.empty(B, GROUPS, 2, dtype=torch.float32, device=x.device)
+            call("conv2d_fwd_gnstats", x, spec.w_fwd(w, op), spec.bias(b), residual, y, stats, B, H, W, CinP,
+                 spec.coutp, spec.geom, GROUPS, GN_EPS, op, out, ws, ws.numel())
+            y._odvae_gn_stats = stats
+            return y
     call("conv2d_fwd", x, spec.w_fwd(w, op), spec.bias(b), residual, y, B, H, W, CinP, spec.coutp, spec.cout,
          spec.geom, op, out, impl, 0)
     return y
@@ -309,6 +325,14 @@ def gn_stats_raw(x, C, code=None):
     ws = workspace(nbytes, x.device, "gn")
     call("groupnorm_stats", x, stats, B, H * W, C, GROUPS, GN_EPS, code, ws, ws.numel())
     return stats
+
+
+def gn_stats_of(x, C, code=None):
+    """GroupNorm statistics of x: the ones its producing conv attached (conv_fwd_raw gn_stats=True), else one pass."""
+    stats = getattr(x, "_odvae_gn_stats", None)
+    if stats is not None and stats.shape[0] == x.shape[0] and x.shape[-1] == C:
+        return stats
+    return gn_stats_raw(x, C, code)
 
 
 def gn_apply_raw(x, stats, gamma, beta, silu, in_code=None, out_code=None, copy_code=None):
@@ -414,7 +438,7 @@ class Conv(torch.autograd.Function):
         ctx.spec, ctx.out_nchw, ctx.need_dx = spec, out_nchw, need_dx
         ctx.fmt = format_of(x, spec)
         ctx.save_for_backward(x, w, b)
-        return conv_fwd_raw(x, spec, w, b, out_nchw=out_nchw)
+        return conv_fwd_raw(x, spec, w, b, out_nchw=out_nchw, gn_stats=not out_nchw)
 
     @staticmethod
     def backward(ctx, dy):
@@ -438,7 +462,7 @@ class GroupNormAct(torch.autograd.Function):
     @staticmethod
     def forward(ctx, x, gamma, beta, silu, fmt=None):
         fmt = fmt if fmt is not None else format_of(x)
-        stats = gn_stats_raw(x, x.shape[-1], fmt.fwd)
+        stats = gn_stats_of(x, x.shape[-1], fmt.fwd)
         ctx.silu, ctx.fmt = silu, fmt
         ctx.save_for_backward(x, stats, gamma, beta)
         return gn_apply_raw(x, stats, gamma, beta, silu, fmt.fwd, fmt.fwd)
@@ -460,14 +484,14 @@ class ResBlock(torch.autograd.Function):
     @staticmethod
     def forward(ctx, x, g1, b1, w1, c1b, g2, b2, w2, c2b, wn, nb, blk):
         fmt = format_of(x, blk)
-        s1 = gn_stats_raw(x, blk.cin, fmt.fwd)
+        s1 = gn_stats_of(x, blk.cin, fmt.fwd)
         a1, a1g = gn_apply_pair(x, s1, g1, b1, True, fmt)
-        h1 = conv_fwd_raw(a1, blk.spec1, w1, c1b, op=fmt.fwd, out=fmt.fwd)
+        h1 = conv_fwd_raw(a1, blk.spec1, w1, c1b, op=fmt.fwd, out=fmt.fwd, gn_stats=True)
         del a1
-        s2 = gn_stats_raw(h1, blk.cout, fmt.fwd)
+        s2 = gn_stats_of(h1, blk.cout, fmt.fwd)
         a2, a2g = gn_apply_pair(h1, s2, g2, b2, True, fmt)
         sc = x if wn is None else conv_fwd_raw(x, blk.spec_nin, wn, nb, op=fmt.fwd, out=fmt.fwd)
-        out = conv_fwd_raw(a2, blk.spec2, w2, c2b, residual=sc, op=fmt.fwd, out=fmt.fwd)
+        out = conv_fwd_raw(a2, blk.spec2, w2, c2b, residual=sc, op=fmt.fwd, out=fmt.fwd, gn_stats=True)
         ctx.blk, ctx.fmt = blk, fmt
         ctx.has_nin = wn is not None
         ctx.save_for_backward(x, s1, a1g, h1, s2, a2g, g1, b1, w1, c1b, g2, b2, w2, c2b, wn, nb)
@@ -509,7 +533,7 @@ class AttnBlock(torch.autograd.Function):
         fmt = format_of(x, blk)
         ac = fmt.attn            # format code inside the block (bf16 in both 16-bit modes)
         dt = buf_dtype(ac)
-        stats = gn_stats_raw(x, C, fmt.fwd)
+        stats = gn_stats_of(x, C, fmt.fwd)
         hn = gn_apply_raw(x, stats, gamma, beta, False, fmt.fwd, ac)
         wqkv, bqkv = blk.fused_qkv(wq, bq, wk, bk, wv, bv, ac)
         qkv = torch.empty(B, H, W, 3 * C, dtype=dt, device=x.device)
@@ -610,7 +634,7 @@ class UpsampleConv(torch.autograd.Function):
         u = upsample2x_raw(x)
         ctx.spec, ctx.fmt = spec, format_of(x, spec)
         ctx.save_for_backward(x, w, b)
-        return conv_fwd_raw(u, spec, w, b)
+        return conv_fwd_raw(u, spec, w, b, gn_stats=True)
 
     @staticmethod
     def backward(ctx, dy):

@@ -153,6 +153,15 @@ int odvae_rowdot(const void* a, const void* b, float* out, int64_t rows, int C, 
 size_t odvae_groupnorm_workspace_bytes(int B, int HW, int C, int G);
 int odvae_groupnorm_stats(const void* x, float* stats, int B, int HW, int C, int G, float eps, int act_dtype,
                           void* workspace, size_t ws_bytes, void* stream);
+/* Convolution forward (same arguments as odvae_conv2d_fwd, NHWC output only) that ALSO produces the GroupNorm
+ * statistics of its output y -- Normalize of the next ResnetBlock / AttnBlock (model.py:38-39,121-141) -- from the fp32
+ * accumulators in the epilogue, so the separate statistics pass over y disappears. Served by the tcgen05 swapped-role
+ * tiles (Cout = 128 layers); odvae_conv2d_fwd_gnstats_workspace_bytes returns 0 for shapes it does not serve and the
+ * caller then uses odvae_conv2d_fwd + odvae_groupnorm_stats. stats: fp32 [B,G,2] = (mean, rstd). */
+size_t odvae_conv2d_fwd_gnstats_workspace_bytes(int B, int H, int W, int CinP, int CoutP, int geom, int G);
+int odvae_conv2d_fwd_gnstats(const void* x, const void* w_packed, const float* bias, const void* residual, void* y,
+                             float* stats, int B, int H, int W, int CinP, int CoutP, int geom, int G, float eps,
+                             int act_dtype, int out_dtype, void* workspace, size_t ws_bytes, void* stream);
 /* y (and, if y2 != NULL, a second copy y2 in out2_dtype) = [silu](GN(x)). Format triples (in, out, out2):
  * f32->f32; bf16->bf16(+bf16); fp16->fp16(+bf16: the copy a weight-gradient GEMM contracts with bf16 dy);
  * fp16->bf16 (attention blocks of the mixed mode). */

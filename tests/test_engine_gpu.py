@@ -248,3 +248,35 @@ def test_skinny_fp32_linear(M, N, Kd, b_mn):
     torch.cuda.synchronize()
     assert rel_err(out[0], ref) < 1e-4
     assert torch.equal(out, out2)  # bit-stable run to run
+
+
+@pytest.mark.parametrize("dtype", [torch.bfloat16, torch.float16])
+@pytest.mark.parametrize("H", [256, 64])
+def test_conv_fwd_fused_groupnorm_stats(dtype, H):
+    """odvae_conv2d_fwd_gnstats: GroupNorm(32) statistics of the conv output from the epilogue's fp32 accumulators
+    (halo tiles at 256, per-tap gather tiles at 64) against the separate statistics pass over the stored output."""
+    from odvae_b200 import lib
+    B, W, C, G = 3, H, 128, 32
+    torch.manual_seed(7)
+    x = torch.randn(B, H, W, C, device=DEV).to(dtype)
+    w = torch.randn(C, C, 3, 3, device=DEV) / (C * 9) ** 0.5
+    b = torch.randn(C, device=DEV)
+    res = torch.randn(B, H, W, C, device=DEV).to(dtype)
+    wp = K.pack_conv_weight(w, CONV_3x3_S1, C, C, 0, dtype)
+    code = K.act_code(dtype)
+    nbytes = lib.call("conv2d_fwd_gnstats_workspace_bytes", B, H, W, C, C, CONV_3x3_S1, G)
+    assert nbytes > 0
+    ws = torch.empty(nbytes, dtype=torch.uint8, device=DEV)
+    y = torch.empty(B, H, W, C, dtype=dtype, device=DEV)
+    stats = torch.empty(B, G, 2, device=DEV)
+    lib.call("conv2d_fwd_gnstats", x, wp, b, res, y, stats, B, H, W, C, C, CONV_3x3_S1, G, 1e-6, code, code, ws, nbytes)
+    y_plain = K.conv_fwd(x, wp, b, C, CONV_3x3_S1, IMPL_TC, residual=res)
+    torch.cuda.synchronize()
+    assert torch.equal(y, y_plain)  # the statistics ride along, the output is unchanged
+    yf = y.float().reshape(B, H * W, G, C // G)
+    mean = yf.mean(dim=(1, 3))
+    rstd = (yf.var(dim=(1, 3), unbiased=False) + 1e-6).rsqrt()
+    assert rel_err(stats[..., 0], mean) < 2e-3  # fp32 accumulators vs the 16-bit stored values
+    assert rel_err(stats[..., 1], rstd) < 2e-3
+    # shapes the swapped tiles do not serve report 0 and the caller keeps the separate pass
+    assert lib.call("conv2d_fwd_gnstats_workspace_bytes", B, 16, 16, 512, 512, CONV_3x3_S1, G) == 0

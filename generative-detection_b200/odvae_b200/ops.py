@@ -12,6 +12,7 @@ stays short (~60 nodes for the whole autoencoder).
 Reference call sites are cited per Function; LD/ = submodules/latent-diffusion/.
 """
 import os
+import weakref
 
 import torch
 
@@ -160,20 +161,41 @@ def geom_k(geom):
 # ------------------------------------------------------------------------------------------------
 # parameter-side caches: packed weights / padded biases, refreshed when the parameter changes
 # ------------------------------------------------------------------------------------------------
+_CACHES = weakref.WeakSet()
+
+
 class ParamCache:
     """Packed copies of one conv's parameters. Keyed by (param version, global weight epoch)."""
 
     def __init__(self):
         self.store = {}
+        _CACHES.add(self)
+
+    @staticmethod
+    def _stamp(params):
+        return tuple(p._version for p in params) + tuple(p.data_ptr() for p in params) + (_WEIGHT_EPOCH[0],)
 
     def get(self, key, params, build):
-        stamp = tuple(p._version for p in params) + tuple(p.data_ptr() for p in params) + (_WEIGHT_EPOCH[0],)
+        stamp = self._stamp(params)
         hit = self.store.get(key)
         if hit is not None and hit[0] == stamp:
             return hit[1]
         val = build(hit[1] if hit is not None else None)
-        self.store[key] = (stamp, val)
+        self.store[key] = (stamp, val, params, build)
         return val
+
+    def refresh(self):
+        for key, (stamp, val, params, build) in list(self.store.items()):
+            new = self._stamp(params)
+            if new != stamp:
+                self.store[key] = (new, build(val), params, build)
+
+
+def refresh_param_caches():
+    """Re-pack every cached weight copy whose parameter changed, back to back (called right after the optimizer step:
+    ~190 tiny pack kernels queue densely here instead of each one sitting in front of its conv in the next step)."""
+    for c in list(_CACHES):
+        c.refresh()
 
 
 def pack_weight(w, geom, CoutP, CinP, which, code, out=None):

@@ -9,6 +9,7 @@ import torch
 import torch.distributed as dist
 
 from . import modules as M
+from . import ops
 from .ddp import GradArena, bucket_order
 from .optim import FusedAdam
 
@@ -37,4 +38,5 @@ class TrainStep:
             M._ARENA[0] = None
         arena.finish()
         self.opt.step()
+        ops.refresh_param_caches()  # packed 16-bit weight copies for the next step, queued back to back
         return loss.detach()

@@ -43,6 +43,42 @@ def test_groupnorm_fwd_bwd(dtype, shape, silu):
     assert rel(dg, gr.grad) < tol and rel(db, br.grad) < tol
 
 
+@pytest.mark.parametrize("dtype,shape", [(torch.bfloat16, (13, 128, 128, 128)), (torch.bfloat16, (5, 256, 256, 128)),
+                                         (torch.float32, (7, 128, 128, 128)), (torch.bfloat16, (50, 64, 64, 256))])
+@pytest.mark.parametrize("with_add", [False, True])
+@pytest.mark.parametrize("team", ["0", "1"])
+def test_groupnorm_bwd_large(dtype, shape, with_add, team, monkeypatch):
+    """Tensors several times the L2, through both backward paths of csrc/groupnorm.cu: the two-kernel path (default) and
+    the opt-in single cooperative launch (ODVAE_GN_BWD_TEAM=1: teams of CTAs, phase 1 reduce -> barrier -> phase 2 apply
+    out of L2). Same contract: GroupNorm(32, C, 1e-6) + SiLU backward (LD model.py:33-39), checked against torch
+    autograd; bit-stable run to run."""
+    monkeypatch.setenv("ODVAE_GN_BWD_TEAM", team)
+    torch.manual_seed(5)
+    B, H, W, C = shape
+    x = (torch.randn(shape, device=DEV) * 1.5 + 0.3).to(dtype)
+    gamma = 1 + 0.1 * torch.randn(C, device=DEV)
+    beta = 0.1 * torch.randn(C, device=DEV)
+    dy = torch.randn(shape, device=DEV).to(dtype)
+    add = torch.randn(shape, device=DEV).to(dtype) if with_add else None
+    stats = ops.gn_stats_raw(x, C)
+    dx, dg, db = ops.gn_bwd_raw(x, stats, gamma, beta, dy, True, dx_add=add)
+    dx2, dg2, db2 = ops.gn_bwd_raw(x, stats, gamma, beta, dy, True, dx_add=add)
+    torch.cuda.synchronize()
+    assert torch.equal(dx, dx2) and torch.equal(dg, dg2) and torch.equal(db, db2)
+    tol = 1e-2 if dtype == torch.bfloat16 else 2e-4
+    dgr = torch.zeros(C, device=DEV)
+    dbr = torch.zeros(C, device=DEV)
+    for b in range(B):  # per-image autograd keeps the fp32 reference small
+        xr = x[b:b + 1].float().permute(0, 3, 1, 2).requires_grad_(True)
+        gr, br = gamma.clone().requires_grad_(True), beta.clone().requires_grad_(True)
+        F.silu(F.group_norm(xr, 32, gr, br, eps=1e-6)).backward(dy[b:b + 1].float().permute(0, 3, 1, 2))
+        got = dx[b:b + 1].float() - (add[b:b + 1].float() if with_add else 0)
+        assert rel(got, xr.grad.permute(0, 2, 3, 1)) < 2 * tol, b
+        dgr += gr.grad
+        dbr += br.grad
+    assert rel(dg, dgr) < tol and rel(db, dbr) < tol
+
+
 @pytest.mark.parametrize("dtype", [torch.float32, torch.bfloat16])
 @pytest.mark.parametrize("rows,cols,ld", [(4096, 128, 128), (1000, 3, 64), (77, 500, 500), (300000, 64, 64), (513, 512, 512)])
 def test_colsum(dtype, rows, cols, ld):

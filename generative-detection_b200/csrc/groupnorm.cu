@@ -139,26 +139,43 @@ gn_reduce_kernel(const T* __restrict__ x, const TG* __restrict__ dy, const float
   }
 }
 
-// forward finalize: one CTA per image; stats[b][g] = (mean, rstd)
+// forward finalize: grid (image, group block), one warp per group; stats[b][g] = (mean, rstd).
+// The conv-epilogue statistics arrive as 512 partials per image and channel (one per 128-pixel box at 256x256): with one
+// CTA per image this kernel took 28 us per launch (ncu launch list s10); spreading the groups over gridDim.y and reading
+// float2 with 4 independent accumulator pairs per lane makes it latency- instead of serial-add-bound.
 __global__ void gn_stats_finalize_kernel(const float* __restrict__ part, float* __restrict__ stats, int nsplit, int HW,
                                          int C, int G, float eps) {
   const int b = blockIdx.x;
   const int cpg = C / G;
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31, nwarps = blockDim.x >> 5;
-  for (int g = warp; g < G; g += nwarps) {  // one warp per group: lanes over (split, channel) pairs, fixed-order tree
-    float s = 0.0f, ss = 0.0f;
-    for (int i = lane; i < nsplit * cpg; i += 32) {
-      const int sp = i / cpg, j = i - sp * cpg;
-      const float* src = part + ((static_cast<long long>(b) * nsplit + sp) * C + g * cpg + j) * 2;
-      s += src[0];
-      ss += src[1];
+  const float2* part2 = reinterpret_cast<const float2*>(part);
+  for (int g = blockIdx.y * nwarps + warp; g < G; g += gridDim.y * nwarps) {
+    // lanes over (split, channel) pairs in a fixed order; 4 independent chains per lane, combined in a fixed order
+    float s[4] = {0.0f, 0.0f, 0.0f, 0.0f}, ss[4] = {0.0f, 0.0f, 0.0f, 0.0f};
+    const int n = nsplit * cpg;
+    int i = lane;
+    for (; i + 96 < n; i += 128) {
+#pragma unroll
+      for (int u = 0; u < 4; ++u) {
+        const int k = i + 32 * u;
+        const int sp = k / cpg, j = k - sp * cpg;
+        const float2 v = __ldg(part2 + (static_cast<long long>(b) * nsplit + sp) * C + g * cpg + j);
+        s[u] += v.x;
+        ss[u] += v.y;
+      }
     }
-    s = warp_sum(s);
-    ss = warp_sum(ss);
+    for (; i < n; i += 32) {
+      const int sp = i / cpg, j = i - sp * cpg;
+      const float2 v = __ldg(part2 + (static_cast<long long>(b) * nsplit + sp) * C + g * cpg + j);
+      s[0] += v.x;
+      ss[0] += v.y;
+    }
+    float st = warp_sum((s[0] + s[1]) + (s[2] + s[3]));
+    float sst = warp_sum((ss[0] + ss[1]) + (ss[2] + ss[3]));
     if (lane == 0) {
-      const float n = static_cast<float>(cpg) * HW;
-      const float mean = s / n;
-      float var = ss / n - mean * mean;
+      const float nn = static_cast<float>(cpg) * HW;
+      const float mean = st / nn;
+      float var = sst / nn - mean * mean;
       var = var < 0.0f ? 0.0f : var;
       stats[(static_cast<long long>(b) * G + g) * 2] = mean;
       stats[(static_cast<long long>(b) * G + g) * 2 + 1] = rsqrtf(var + eps);
@@ -773,7 +790,7 @@ static int gn_apply_blocks(int B, int HW, int C, int V) {
 
 int launch_gn_stats_finalize(const float* part, float* stats, int B, int nsplit, int HW, int C, int G, float eps,
                              cudaStream_t st) {
-  gn_stats_finalize_kernel<<<B, 256, 0, st>>>(part, stats, nsplit, HW, C, G, eps);
+  gn_stats_finalize_kernel<<<dim3(B, (G + 7) / 8), 256, 0, st>>>(part, stats, nsplit, HW, C, G, eps);
   return check_launch("gn_stats_finalize_kernel");
 }
 
@@ -824,7 +841,7 @@ int odvae_groupnorm_stats(const void* x, float* stats, int B, int HW, int C, int
 #undef GN_LAUNCH_REDUCE0
   int s = check_launch("gn_reduce_kernel<0>");
   if (s != ODVAE_OK) return s;
-  gn_stats_finalize_kernel<<<B, 256, 0, st>>>(part, stats, ns, HW, C, G, eps);
+  gn_stats_finalize_kernel<<<dim3(B, (G + 7) / 8), 256, 0, st>>>(part, stats, ns, HW, C, G, eps);
   return check_launch("gn_stats_finalize_kernel");
 }
 

@@ -122,13 +122,11 @@ __global__ void minmax_stage2(const float* __restrict__ part, int nblk, float* _
 // which=1 (s1 / 1x1): P[ci][tap'][co] = w[co][ci][kh-1-r'][kw-1-s']
 // which=1 (s2): 4 parity-phase matrices [CinP][nt*CoutP], phases (py,px) in order 00,01,10,11,
 //               taps of a phase in (r,s) ascending order: entry = w[co][ci][r][s]
-template <typename T>
-__global__ void pack_conv_weight_kernel(const float* __restrict__ w, T* __restrict__ P, int Cout, int Cin, int k,
-                                        int CoutP, int CinP, int which, int s2) {
+// packed element e of one conv -> its value from the OIHW master (0 in the padding)
+__device__ __forceinline__ float pack_conv_weight_value(const float* __restrict__ w, long long e, int Cout, int Cin,
+                                                        int k, int CoutP, int CinP, int which, int s2) {
   const int taps = k * k;
-  const long long total = static_cast<long long>(CoutP) * CinP * taps;
-  for (long long e = blockIdx.x * static_cast<long long>(blockDim.x) + threadIdx.x; e < total;
-       e += static_cast<long long>(gridDim.x) * blockDim.x) {
+  {
     int co, ci, r, s;
     if (which == 0) {
       ci = static_cast<int>(e % CinP);
@@ -170,7 +168,50 @@ __global__ void pack_conv_weight_kernel(const float* __restrict__ w, T* __restri
     }
     float v = 0.0f;
     if (co < Cout && ci < Cin) v = __ldg(w + ((static_cast<long long>(co) * Cin + ci) * k + r) * k + s);
-    P[e] = from_f32<T>(v);
+    return v;
+  }
+}
+
+template <typename T>
+__global__ void pack_conv_weight_kernel(const float* __restrict__ w, T* __restrict__ P, int Cout, int Cin, int k,
+                                        int CoutP, int CinP, int which, int s2) {
+  const long long total = static_cast<long long>(CoutP) * CinP * k * k;
+  for (long long e = blockIdx.x * static_cast<long long>(blockDim.x) + threadIdx.x; e < total;
+       e += static_cast<long long>(gridDim.x) * blockDim.x)
+    P[e] = from_f32<T>(pack_conv_weight_value(w, e, Cout, Cin, k, CoutP, CinP, which, s2));
+}
+
+// Multi-tensor variant: ONE launch re-packs every conv weight of the model after the optimizer step (188 packed copies
+// in the train step; as separate launches they cost 1.7 ms of 5-10 us kernels, ncu launch list s10).
+// table row (int64 x PACK_MT_COLS): w ptr, P ptr, Cout, Cin, k, CoutP, CinP, which | s2 << 1, dtype code, first block.
+// Block b serves PACK_MT_ELEMS consecutive packed elements of the entry whose block range contains b.
+static constexpr int PACK_MT_COLS = 10;
+static constexpr int PACK_MT_ELEMS = 4096;
+__global__ void __launch_bounds__(256)
+pack_conv_weight_mt_kernel(const long long* __restrict__ table, int n_entries) {
+  int lo = 0, hi = n_entries - 1;
+  const long long blk = blockIdx.x;
+  while (lo < hi) {  // last entry with first_block <= blk
+    const int mid = (lo + hi + 1) >> 1;
+    if (__ldg(table + static_cast<long long>(mid) * PACK_MT_COLS + 9) <= blk) lo = mid; else hi = mid - 1;
+  }
+  const long long* row = table + static_cast<long long>(lo) * PACK_MT_COLS;
+  const float* w = reinterpret_cast<const float*>(__ldg(row + 0));
+  void* P = reinterpret_cast<void*>(__ldg(row + 1));
+  const int Cout = static_cast<int>(__ldg(row + 2)), Cin = static_cast<int>(__ldg(row + 3));
+  const int k = static_cast<int>(__ldg(row + 4)), CoutP = static_cast<int>(__ldg(row + 5));
+  const int CinP = static_cast<int>(__ldg(row + 6)), flags = static_cast<int>(__ldg(row + 7));
+  const int dtype = static_cast<int>(__ldg(row + 8));
+  const long long total = static_cast<long long>(CoutP) * CinP * k * k;
+  const long long e0 = (blk - __ldg(row + 9)) * PACK_MT_ELEMS;
+#pragma unroll 4
+  for (int i = threadIdx.x; i < PACK_MT_ELEMS; i += 256) {
+    const long long e = e0 + i;
+    if (e >= total) break;
+    const float v = pack_conv_weight_value(w, e, Cout, Cin, k, CoutP, CinP, flags & 1, (flags >> 1) & 1);
+    if (dtype == ODVAE_BF16) reinterpret_cast<bf16*>(P)[e] = from_f32<bf16>(v);
+    else if (dtype == ODVAE_F16) reinterpret_cast<f16*>(P)[e] = from_f32<f16>(v);
+    else reinterpret_cast<float*>(P)[e] = v;
   }
 }
 
@@ -499,6 +540,20 @@ int odvae_pack_conv_weight(const float* w_oihw, void* packed, int Cout, int Cin,
   else
     pack_conv_weight_kernel<float><<<grid_for(total, 256), 256, 0, st>>>(w_oihw, reinterpret_cast<float*>(packed), Cout, Cin, k, CoutP, CinP, which, s2);
   return check_launch("pack_conv_weight_kernel");
+}
+
+int64_t odvae_pack_conv_weights_mt_blocks(int CoutP, int CinP, int geom) {
+  const int k = geom == ODVAE_CONV_1x1 ? 1 : 3;
+  const long long total = static_cast<long long>(CoutP) * CinP * k * k;
+  return (total + PACK_MT_ELEMS - 1) / PACK_MT_ELEMS;
+}
+
+int odvae_pack_conv_weights_mt(const int64_t* table_dev, int n_entries, int64_t n_blocks, void* stream) {
+  if (n_entries <= 0 || n_blocks <= 0) return ODVAE_OK;
+  if (n_blocks > 0x7fffffffLL) return ODVAE_ERR_SHAPE;
+  pack_conv_weight_mt_kernel<<<static_cast<unsigned>(n_blocks), 256, 0, static_cast<cudaStream_t>(stream)>>>(
+      reinterpret_cast<const long long*>(table_dev), n_entries);
+  return check_launch("pack_conv_weight_mt_kernel");
 }
 
 int odvae_upsample2x(const void* x, void* y, int B, int H, int W, int C, int act_dtype, void* stream) {

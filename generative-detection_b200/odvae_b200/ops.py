@@ -162,10 +162,13 @@ def geom_k(geom):
 # parameter-side caches: packed weights / padded biases, refreshed when the parameter changes
 # ------------------------------------------------------------------------------------------------
 _CACHES = weakref.WeakSet()
+_MT_PACK = {"key": None, "table": None, "n": 0, "blocks": 0}
 
 
 class ParamCache:
-    """Packed copies of one conv's parameters. Keyed by (param version, global weight epoch)."""
+    """Packed copies of one conv's parameters. Keyed by (param version, global weight epoch).
+    `desc` = (w, geom, CoutP, CinP, which, code) marks an entry that is a plain odvae_pack_conv_weight of one
+    parameter: refresh_param_caches() re-packs all of those in ONE multi-tensor launch."""
 
     def __init__(self):
         self.store = {}
@@ -175,27 +178,48 @@ class ParamCache:
     def _stamp(params):
         return tuple(p._version for p in params) + tuple(p.data_ptr() for p in params) + (_WEIGHT_EPOCH[0],)
 
-    def get(self, key, params, build):
+    def get(self, key, params, build, desc=None):
         stamp = self._stamp(params)
         hit = self.store.get(key)
         if hit is not None and hit[0] == stamp:
             return hit[1]
         val = build(hit[1] if hit is not None else None)
-        self.store[key] = (stamp, val, params, build)
+        self.store[key] = (stamp, val, params, build, desc)
         return val
 
-    def refresh(self):
-        for key, (stamp, val, params, build) in list(self.store.items()):
+    def stale(self):
+        for key, (stamp, val, params, build, desc) in list(self.store.items()):
             new = self._stamp(params)
             if new != stamp:
-                self.store[key] = (new, build(val), params, build)
+                yield key, new, val, params, build, desc
 
 
 def refresh_param_caches():
-    """Re-pack every cached weight copy whose parameter changed, back to back (called right after the optimizer step:
-    ~190 tiny pack kernels queue densely here instead of each one sitting in front of its conv in the next step)."""
+    """Re-pack every cached weight copy whose parameter changed (called right after the optimizer step). Conv-weight
+    packs go through one multi-tensor launch over a device table that is built once (parameter and packed-buffer
+    addresses are stable across steps); anything else (padded biases, fused qkv) re-runs its own builder."""
+    mt = []
     for c in list(_CACHES):
-        c.refresh()
+        for key, new, val, params, build, desc in c.stale():
+            if desc is not None and val is not None:
+                mt.append((c, key, new, val, params, build, desc))
+            else:
+                c.store[key] = (new, build(val), params, build, desc)
+    if not mt:
+        return
+    sig = tuple((d[0].data_ptr(), val.data_ptr(), d[1], d[2], d[3], d[4], d[5]) for _, _, _, val, _, _, d in mt)
+    if _MT_PACK["key"] != sig:
+        rows, first = [], 0
+        for _, _, _, val, _, _, (w, geom, coutp, cinp, which, code) in mt:
+            k = geom_k(geom)
+            flags = which | (2 if (geom == CONV_3x3_S2 and which == 1) else 0)
+            rows.append([w.data_ptr(), val.data_ptr(), w.shape[0], w.shape[1], k, coutp, cinp, flags, code, first])
+            first += call("pack_conv_weights_mt_blocks", coutp, cinp, geom)
+        host = torch.tensor(rows, dtype=torch.int64)
+        _MT_PACK.update(key=sig, table=host.to(mt[0][3].device), n=len(rows), blocks=first)
+    call("pack_conv_weights_mt", _MT_PACK["table"], _MT_PACK["n"], _MT_PACK["blocks"])
+    for c, key, new, val, params, build, desc in mt:
+        c.store[key] = (new, val, params, build, desc)
 
 
 def pack_weight(w, geom, CoutP, CinP, which, code, out=None):
@@ -232,13 +256,17 @@ class ConvSpec:
 
     def w_fwd(self, w, code, coutp=None):
         coutp = coutp or self.coutp
+        code = act_code(code) if isinstance(code, torch.dtype) else code
         return self.cache.get(("f", code, coutp), (w,),
-                              lambda old: pack_weight(w.detach(), self.geom, coutp, self.cinp, 0, code, old))
+                              lambda old: pack_weight(w.detach(), self.geom, coutp, self.cinp, 0, code, old),
+                              desc=(w, self.geom, coutp, self.cinp, 0, code))
 
     def w_dgrad(self, w, code, coutp=None):
         coutp = coutp or self.coutp
+        code = act_code(code) if isinstance(code, torch.dtype) else code
         return self.cache.get(("d", code, coutp), (w,),
-                              lambda old: pack_weight(w.detach(), self.geom, coutp, self.cinp, 1, code, old))
+                              lambda old: pack_weight(w.detach(), self.geom, coutp, self.cinp, 1, code, old),
+                              desc=(w, self.geom, coutp, self.cinp, 1, code))
 
     def bias(self, b, n=None):
         n = n or self.coutp

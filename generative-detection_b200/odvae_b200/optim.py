@@ -57,6 +57,10 @@ class FusedAdam(torch.optim.Optimizer):
         self._plans[key] = plan
         return plan
 
+    def load_state_dict(self, state_dict):
+        super().load_state_dict(state_dict)
+        self._plans = {}  # the chunk tables hold raw pointers into the replaced exp_avg / exp_avg_sq tensors
+
     @torch.no_grad()
     def step(self, closure=None):
         loss = None
@@ -78,7 +82,7 @@ class FusedAdam(torch.optim.Optimizer):
                 plan["host"].numpy()[:, 1] = np.asarray(gptrs, dtype=np.int64)[plan["owner"]] + plan["offs"]
                 plan["table"].copy_(plan["host"], non_blocking=True)
                 plan["gkey"] = gptrs
-            step = self.state[params[0]]["step"] + 1
+            step = int(self.state[params[0]]["step"]) + 1  # a torch.optim.Adam checkpoint stores a tensor here
             for p in params:
                 self.state[p]["step"] = step
             b1, b2 = group["betas"]

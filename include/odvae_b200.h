@@ -81,6 +81,13 @@ int odvae_minmax(const float* src, int64_t n, float* out2, void* workspace, size
  * act_dtype selects bf16 / fp16 (TC path) or f32 (SIMT path) packing. Padded rows/cols are zero. */
 int odvae_pack_conv_weight(const float* w_oihw, void* packed, int Cout, int Cin, int geom, int CoutP, int CinP,
                            int which, int act_dtype, void* stream);
+/* Multi-tensor form of odvae_pack_conv_weight: ONE launch re-packs every entry of a device-resident table (the packed
+ * 16-bit copies of all conv weights after an optimizer step). Row layout, 10 x int64 per entry:
+ *   { w_oihw pointer, packed pointer, Cout, Cin, k (1|3), CoutP, CinP, which | (stride-2 dgrad ? 2 : 0), act_dtype,
+ *     first block }, first block = running sum of odvae_pack_conv_weights_mt_blocks over the previous entries;
+ * n_blocks = the total. Same element mapping as odvae_pack_conv_weight (bit-identical output). */
+int64_t odvae_pack_conv_weights_mt_blocks(int CoutP, int CinP, int geom);
+int odvae_pack_conv_weights_mt(const int64_t* table_dev, int n_entries, int64_t n_blocks, void* stream);
 /* 1 when fwd, dgrad and wgrad of this conv can all run on the tcgen05 engine (TMA tiling constraints:
  * CinP % 64 == 0, CoutP % 64 == 0 for dgrad, power-of-two output width, >= 128 output pixels per image). */
 int odvae_conv2d_tc_supported(int B, int H, int W, int CinP, int CoutP, int geom);

@@ -179,3 +179,35 @@ def test_fused_attention_core_against_torch(B, N, C):
     dP = torch.bmm(dO.float(), v.float().transpose(1, 2))
     dSr = P.float() * (dP - delta.view(B, N, 1)) * scale
     assert float((dS.float() - dSr).abs().max() / dSr.abs().max()) < 1e-2
+
+
+def test_multi_tensor_weight_pack_matches_single_packs():
+    """refresh_param_caches(): one pack_conv_weights_mt launch over the device table must leave every packed copy
+    bit-identical to odvae_pack_conv_weight of the same parameter (all layouts: forward, rotated dgrad, stride-2
+    parity phases, 1x1; bf16 / fp16 / fp32 copies; padded channel counts)."""
+    from odvae_b200.lib import BF16, CONV_1x1, CONV_3x3_S1, CONV_3x3_S2, F16, F32
+    torch.manual_seed(11)
+    specs, ws = [], []
+    for cin, cout, geom in [(3, 128, CONV_3x3_S1), (128, 128, CONV_3x3_S1), (128, 3, CONV_3x3_S1), (128, 128, CONV_3x3_S2),
+                            (256, 256, CONV_1x1), (128, 256, CONV_3x3_S1), (32, 16, CONV_1x1)]:
+        k = 1 if geom == CONV_1x1 else 3
+        w = torch.nn.Parameter(torch.randn(cout, cin, k, k, device=DEV))
+        spec = ops.ConvSpec(cin, cout, geom)
+        specs.append(spec)
+        ws.append(w)
+    packed = []
+    for spec, w in zip(specs, ws):
+        for code in (BF16, F16, F32):
+            packed.append((spec, w, 0, code, spec.w_fwd(w, code)))
+            packed.append((spec, w, 1, code, spec.w_dgrad(w, code)))
+    with torch.no_grad():
+        for w in ws:
+            w.add_(torch.randn_like(w))  # bumps the parameter version: every cached copy is stale now
+    ops.refresh_param_caches()
+    torch.cuda.synchronize()
+    for spec, w, which, code, buf in packed:
+        again = spec.w_fwd(w, code) if which == 0 else spec.w_dgrad(w, code)
+        assert again.data_ptr() == buf.data_ptr()  # cache hit: refreshed in place by the multi-tensor launch
+        ref = ops.pack_weight(w.detach(), spec.geom, spec.coutp, spec.cinp, which, code)
+        torch.cuda.synchronize()
+        assert torch.equal(buf, ref), (spec.cin, spec.cout, spec.geom, which, code)

@@ -32,3 +32,14 @@ if __name__ == "__main__":
             print("%4d %-28s grid %-14s %9.1f us  tensor%% %5.1f  dramR %8.1f MB dramW %8.1f MB  L2 %9.1f MB" % (
                 k, d["name"][:28], d["grid"], dur_us(d), d.get("sm__pipe_tensor_cycles_active.avg.pct_of_peak_sustained_elapsed", -1),
                 byt(d, "dram__bytes_read.sum") / 1e6, byt(d, "dram__bytes_write.sum") / 1e6, byt(d, "lts__t_bytes.sum") / 1e6))
+    if "--dram" in sys.argv:
+        print("\nper-kernel DRAM traffic and achieved bandwidth (ncu: dram__bytes_read.sum + dram__bytes_write.sum over "
+              "gpu__time_duration.sum; cold-cache, serialised)")
+        agg = collections.defaultdict(lambda: [0, 0.0, 0.0, 0.0])
+        for d in rows.values():
+            a = agg[d["name"]]
+            a[0] += 1; a[1] += dur_us(d); a[2] += byt(d, "dram__bytes_read.sum"); a[3] += byt(d, "dram__bytes_write.sum")
+        for n, (c, t, r, w) in sorted(agg.items(), key=lambda x: -x[1][1]):
+            if t < 50: continue
+            print("%-62s n=%4d %8.2f ms  R %7.2f GB W %7.2f GB  -> %6.0f GB/s  (%.1f MB/launch)" % (
+                n[:62], c, t / 1e3, r / 1e9, w / 1e9, (r + w) / (t * 1e-6) / 1e9, (r + w) / c / 1e6))

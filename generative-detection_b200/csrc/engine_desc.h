@@ -49,6 +49,10 @@ struct TcParams {
   // channel and 128 pixels of a pixel box: it writes (sum y, sum y^2) of its fp32 results to
   // gn_part[((image * boxes_per_image + box) * n_valid + channel) * 2] -- the layout gn_stats_finalize reduces.
   float* gn_part;
+  // CONV (swapped roles): byte offset (from the 1024-aligned shared-memory base) of the 8 x 2 KiB per-warp staging
+  // buffers the epilogue transposes 32 pixels x 32 channels through, so that the 16-bit results leave as 16-byte vector
+  // stores (and the residual arrives as 16-byte vector loads); 0 = scalar 2-byte path.
+  int epi_off;
 };
 
 

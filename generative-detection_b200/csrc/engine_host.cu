@@ -6,6 +6,8 @@
 #include <mutex>
 
 #include "engine_host.h"
+
+#include <stdlib.h>
 #include "simt_engine.cuh"
 #include "tc_engine.cuh"
 
@@ -122,6 +124,29 @@ static int launch_tc(EngineDesc& d, cudaStream_t stream) {
   } else {
     p.stages = tc_pick_stages(b_rows, p.num_k_iters);
     smem = tc_smem_bytes(p.stages, b_rows);
+  }
+  // swapped-role conv epilogue: 8 x 2 KiB staging buffers for 16-byte vector stores / residual loads
+  p.epi_off = 0;
+  {
+    static const bool epi_stage_on = [] {
+      const char* v = getenv("ODVAE_EPI_STAGE");
+      return !(v && v[0] == '0');
+    }();
+    const bool aligned = (p.n_valid % 8) == 0 && (p.oX % 8) == 0 && (p.oY % 8) == 0 && (p.oB % 8) == 0 && (p.o0 % 8) == 0;
+    // (only where a residual is added: plain stores measured no faster through the staging buffer)
+    if (epi_stage_on && p.kind == KIND_CONV && p.swap && aligned && p.residual != nullptr &&
+        (p.out_mode == OUT_BF16 || p.out_mode == OUT_F16)) {
+      const size_t limit = 227 * 1024;
+      if (p.halo && smem + 16384 + 128 > limit) {  // give one weight stage to the epilogue
+        p.stages -= 1;
+        smem = tc_halo_smem_bytes(p.stages, p.halo_slabs);
+      }
+      const size_t off = (smem - 1024 + 127) & ~static_cast<size_t>(127);
+      if (off + 16384 + 1024 <= limit && p.stages >= 2) {
+        p.epi_off = static_cast<int>(off);
+        smem = off + 16384 + 1024;
+      }
+    }
   }
   static std::once_flag once;
   static cudaError_t attr_err = cudaSuccess;

@@ -436,13 +436,69 @@ tc_engine_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant_
         const uint16_t* R16 = reinterpret_cast<const uint16_t*>(p.residual);
         const long long base0 = static_cast<long long>(pb_b) * p.oB + p.o0 + n;
         const long long sx = p.oX;
-        mbar_wait(&tfull_bar[acc], acc_phase);
-        tc_fence_after();
         float gs0 = 0.0f, gs1 = 0.0f, gq0 = 0.0f, gq1 = 0.0f;  // fused GroupNorm statistics (two chains each)
+        // staged path: the warp's 32 pixels x 32 channels go through a private 2 KiB buffer ([pixel][32 channels], 64-byte
+        // rows) and leave as 16-byte vectors: lane l, vector k covers pixel (l >> 2) + 8 k, channels 8 (l & 3) .. + 7
+        uint8_t* stg = p.epi_off ? smem + p.epi_off + (warp - 2) * 2048 : nullptr;
+        const int vch = m0 + q * 32 + (lane & 3) * 8;  // first channel of this lane's vectors
+        uint4 rv[4] = {};  // residual vectors of the batch about to be emitted
+        auto load_rv = [&](int pi0) {
+          const int yy = pb_y + (pi0 >> p.bw_log2), xx = pb_x + (pi0 & ((1 << p.bw_log2) - 1));
+          const long long vb = static_cast<long long>(pb_b) * p.oB + p.o0 + vch + static_cast<long long>(yy) * p.oY +
+                               static_cast<long long>(xx + (lane >> 2)) * sx;
+          if (vch < p.n_valid) {
+#pragma unroll
+            for (int k = 0; k < 4; ++k)
+              rv[k] = __ldg(reinterpret_cast<const uint4*>(R16 + vb + static_cast<long long>(8 * k) * sx));
+          }
+        };
         auto emit = [&](uint32_t (&v)[32], int pi0) {
           const int yy = pb_y + (pi0 >> p.bw_log2), xx = pb_x + (pi0 & ((1 << p.bw_log2) - 1));
           const long long base = base0 + static_cast<long long>(yy) * p.oY + static_cast<long long>(xx) * sx;
-          if (ch_ok) {
+          if (stg != nullptr) {
+            const long long vbase = static_cast<long long>(pb_b) * p.oB + p.o0 + vch + static_cast<long long>(yy) * p.oY +
+                                    static_cast<long long>(xx + (lane >> 2)) * sx;
+            float f[32];
+#pragma unroll
+            for (int i = 0; i < 32; ++i) f[i] = fmaf(__uint_as_float(v[i]), p.alpha, bias);
+            if (R16 != nullptr) {
+              // residual: 4 coalesced 16-byte vectors per lane (requested one batch ahead, see load_rv) -> staging
+              // buffer -> this lane's channel column
+#pragma unroll
+              for (int k = 0; k < 4; ++k)
+                *reinterpret_cast<uint4*>(stg + ((lane >> 2) + 8 * k) * 64 + (lane & 3) * 16) = rv[k];
+              __syncwarp();
+              if (pi0 + 32 < 128) load_rv(pi0 + 32);
+#pragma unroll
+              for (int i = 0; i < 32; ++i) {
+                const uint16_t rr = *reinterpret_cast<const uint16_t*>(stg + i * 64 + lane * 2);
+                f[i] += unpack_16x2(static_cast<uint32_t>(rr), halfp).x;
+              }
+              __syncwarp();
+            }
+#pragma unroll
+            for (int i = 0; i < 32; i += 2) {
+              const uint32_t pk = pack_16x2(f[i], f[i + 1], halfp);
+              *reinterpret_cast<uint16_t*>(stg + i * 64 + lane * 2) = static_cast<uint16_t>(pk & 0xffffu);
+              *reinterpret_cast<uint16_t*>(stg + (i + 1) * 64 + lane * 2) = static_cast<uint16_t>(pk >> 16);
+              if (p.gn_part != nullptr && ch_ok) {
+                const float2 r = unpack_16x2(pk, halfp);
+                gs0 += r.x;
+                gq0 = fmaf(r.x, r.x, gq0);
+                gs1 += r.y;
+                gq1 = fmaf(r.y, r.y, gq1);
+              }
+            }
+            __syncwarp();
+            if (vch < p.n_valid) {
+#pragma unroll
+              for (int k = 0; k < 4; ++k) {
+                const uint4 ov = *reinterpret_cast<const uint4*>(stg + ((lane >> 2) + 8 * k) * 64 + (lane & 3) * 16);
+                *reinterpret_cast<uint4*>(D16 + vbase + static_cast<long long>(8 * k) * sx) = ov;
+              }
+            }
+            __syncwarp();
+          } else if (ch_ok) {
             float f[32];
 #pragma unroll
             for (int i = 0; i < 32; ++i) f[i] = fmaf(__uint_as_float(v[i]), p.alpha, bias);
@@ -468,6 +524,9 @@ tc_engine_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant_
             }
           }
         };
+        if (stg != nullptr && R16 != nullptr) load_rv(0);  // in flight while the accumulator completes
+        mbar_wait(&tfull_bar[acc], acc_phase);
+        tc_fence_after();
         uint32_t va[32], vb[32];
         tmem_ld_x32(t_row + static_cast<uint32_t>(c_begin), va);
         tmem_ld_wait();

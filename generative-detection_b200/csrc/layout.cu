@@ -216,28 +216,49 @@ pack_conv_weight_mt_kernel(const long long* __restrict__ table, int n_entries) {
 }
 
 // dw[co][ci][tap] (+)= sum_split ws[(tap*split_k + split)][co][ci]   (ws rows: CoutP x CinP)
+// One thread sums VEC consecutive ci over all splits, 8 independent (vector) loads in flight, added in split order
+// (the order is part of the bit-stability contract). The workspace was written by the preceding weight-gradient kernel
+// and is mostly L2-resident, so the kernel is latency-bound: wide loads and deep unrolling are what shorten it.
+template <int VEC>
 __global__ void wgrad_reduce_kernel(const float* __restrict__ ws, float* __restrict__ dw, int Cout, int Cin,
                                     int taps, int CoutP, int CinP, int split_k, int accumulate) {
-  const long long total = static_cast<long long>(Cout) * Cin * taps;
+  const int cin_v = Cin / VEC;
+  const long long total = static_cast<long long>(Cout) * cin_v * taps;
+  const long long sstride = static_cast<long long>(CoutP) * CinP;
   for (long long e = blockIdx.x * static_cast<long long>(blockDim.x) + threadIdx.x; e < total;
        e += static_cast<long long>(gridDim.x) * blockDim.x) {
     // iterate with ci fastest for coalesced workspace reads
-    const int ci = static_cast<int>(e % Cin);
-    long long q = e / Cin;
+    const int ci = static_cast<int>(e % cin_v) * VEC;
+    long long q = e / cin_v;
     const int tap = static_cast<int>(q % taps);
     const int co = static_cast<int>(q / taps);
-    float acc = 0.0f;
+    float acc[VEC];
+#pragma unroll
+    for (int j = 0; j < VEC; ++j) acc[j] = 0.0f;
     const float* src = ws + (static_cast<long long>(tap) * split_k * CoutP + co) * CinP + ci;
-    const long long sstride = static_cast<long long>(CoutP) * CinP;
+    constexpr int U = 8;
     int s = 0;
-    for (; s + 3 < split_k; s += 4) {  // four independent loads in flight, added in split order
-      const float a0 = __ldg(src + s * sstride), a1 = __ldg(src + (s + 1) * sstride);
-      const float a2 = __ldg(src + (s + 2) * sstride), a3 = __ldg(src + (s + 3) * sstride);
-      acc += a0; acc += a1; acc += a2; acc += a3;
+    for (; s + U - 1 < split_k; s += U) {
+      float v[U][VEC];
+#pragma unroll
+      for (int u = 0; u < U; ++u) {
+        if (VEC == 4) *reinterpret_cast<float4*>(v[u]) = __ldg(reinterpret_cast<const float4*>(src + (s + u) * sstride));
+        else v[u][0] = __ldg(src + (s + u) * sstride);
+      }
+#pragma unroll
+      for (int u = 0; u < U; ++u)
+#pragma unroll
+        for (int j = 0; j < VEC; ++j) acc[j] += v[u][j];
     }
-    for (; s < split_k; ++s) acc += __ldg(src + s * sstride);
-    float* d = dw + (static_cast<long long>(co) * Cin + ci) * taps + tap;
-    *d = accumulate ? (*d + acc) : acc;
+    for (; s < split_k; ++s) {
+#pragma unroll
+      for (int j = 0; j < VEC; ++j) acc[j] += __ldg(src + s * sstride + j);
+    }
+#pragma unroll
+    for (int j = 0; j < VEC; ++j) {
+      float* d = dw + (static_cast<long long>(co) * Cin + ci + j) * taps + tap;
+      *d = accumulate ? (*d + acc[j]) : acc[j];
+    }
   }
 }
 
@@ -434,7 +455,10 @@ static int grid_for(long long work_items, int threads, int per_sm = 8) {
 int launch_wgrad_reduce(const float* ws, float* dw, int Cout, int Cin, int taps, int CoutP, int CinP, int split_k,
                         int accumulate, cudaStream_t st) {
   const long long total = static_cast<long long>(Cout) * Cin * taps;
-  wgrad_reduce_kernel<<<grid_for(total, 256), 256, 0, st>>>(ws, dw, Cout, Cin, taps, CoutP, CinP, split_k, accumulate);
+  if (Cin % 4 == 0 && CinP % 4 == 0 && (reinterpret_cast<uintptr_t>(ws) & 15) == 0)
+    wgrad_reduce_kernel<4><<<grid_for(total / 4, 128), 128, 0, st>>>(ws, dw, Cout, Cin, taps, CoutP, CinP, split_k, accumulate);
+  else
+    wgrad_reduce_kernel<1><<<grid_for(total, 256), 256, 0, st>>>(ws, dw, Cout, Cin, taps, CoutP, CinP, split_k, accumulate);
   return check_launch("wgrad_reduce_kernel");
 }
 

@@ -121,6 +121,75 @@ def test_mixed_mode_matches_reference(name):
     assert l2s[int(0.99 * len(l2s)) - 1] < MIXED_TOL
 
 
+def _full_size_batch(g, B):
+    """BASELINE.json configs[1] size: the golden full-config B=2 samples in slots 0-1 of a batch of B, the rest
+    synthetic. The extra crops are clipped into the value range of the golden pair so that the batch-wide `_rescale`
+    (AE.py:434-436) maps slots 0-1 exactly as in the reference run; noise draws 0-1 are the golden's."""
+    params, batch2, noise2, step = H.case_inputs(g)
+    other = synth.synthetic_batch(B - 2, g["spec"]["resolution"], 777)
+    lo, hi = batch2["patch"].min(), batch2["patch"].max()
+    other["patch"] = other["patch"].clamp(lo, hi)
+    batch = {}
+    for k, v in batch2.items():
+        batch[k] = torch.cat([v, other[k]], 0) if torch.is_tensor(v) else list(v) + list(other[k])
+    extra = synth.draw_noise(B - 2, g["spec"]["dropout_p"], seed=5)
+    noise = tuple(torch.cat([a, b], 0) for a, b in zip(noise2, extra))
+    return params, batch, noise, step
+
+
+def _run_full(params, batch, noise, step, dtype=torch.float16):
+    from odvae_b200.autoencoder import PoseAutoencoder
+    model = PoseAutoencoder(**params, compute_dtype=dtype)
+    synth.fill_state_dict_(model.state_dict(), seed=23)
+    model = model.cuda()
+    model.global_step = step
+    model.inject_noise = noise
+    cap = {}
+    fwd = model.forward
+    model.forward = lambda *a, **k: cap.setdefault("out", fwd(*a, **k))
+    loss = model.training_step(H.clone_batch(batch), 0, 0)
+    loss.backward()
+    torch.cuda.synchronize()
+    return model, loss, cap["out"]
+
+
+def test_full_size_batch64_per_sample_parity_and_permutation():
+    """The train step at BASELINE's full size (full config, 256x256 crops, batch 64, timed mixed mode). Every op on the
+    path is per-sample, so (1) slots 0-1 must reproduce the reference's B=2 golden outputs within the 16-bit
+    tolerance although they now run inside batch-64 tiles, (2) permuting the batch permutes the outputs, bit for bit
+    (tiles are visited in a different order, the arithmetic per sample is the same), and (3) the whole-batch loss and
+    every gradient are finite and bit-stable under that permutation only up to summation order (checked to 1e-5)."""
+    B = 64
+    g = H.load_golden("full_s80000_b2")
+    params, batch, noise, step = _full_size_batch(g, B)
+    model, loss, out = _run_full(params, batch, noise, step)
+    dec_obj, dec_pose, post, bbox_post = out
+    assert dec_obj.shape == (B, 3, 256, 256) and torch.isfinite(loss)
+    assert H.rel_l2(dec_obj[:2], g["out"]["dec_obj"]) < MIXED_TOL
+    assert H.rel_max(dec_pose[:2], g["out"]["dec_pose"]) < MIXED_TOL
+    assert H.rel_max(post.mean[:2], g["out"]["posterior_mean"]) < MIXED_TOL
+    assert H.rel_max(post.logvar[:2], g["out"]["posterior_logvar"]) < MIXED_TOL
+    assert H.rel_max(bbox_post.mean[:2], g["out"]["bbox_mean"]) < MIXED_TOL
+    for k, p in model.named_parameters():
+        if p.grad is not None:
+            assert torch.isfinite(p.grad).all(), k
+
+    perm = torch.arange(B - 1, -1, -1)
+    batch_p = {k: (v[perm] if torch.is_tensor(v) else [v[i] for i in perm.tolist()]) for k, v in batch.items()}
+    noise_p = tuple(t[perm] for t in noise)
+    outs = (dec_obj.detach().clone(), dec_pose.detach().clone(), post.mean.detach().clone())
+    grad_ref = model.encoder.conv_in.weight.grad.detach().clone()
+    loss_ref = float(loss)
+    del model, out, dec_obj, dec_pose, post, bbox_post, loss
+    torch.cuda.empty_cache()
+    model_p, loss_p, out_p = _run_full(params, batch_p, noise_p, step)
+    assert torch.equal(out_p[0][perm], outs[0])
+    assert torch.equal(out_p[1][perm], outs[1])
+    assert torch.equal(out_p[2].mean[perm], outs[2])
+    assert abs(float(loss_p) - loss_ref) <= 1e-5 * abs(loss_ref)
+    assert H.rel_l2(model_p.encoder.conv_in.weight.grad, grad_ref) < 1e-3
+
+
 def test_bit_stable_run_to_run():
     """Fixed-order reductions everywhere: two identical steps give bit-identical loss and gradients."""
     _, m1, l1, _ = run_product("small_s80000_b3", torch.bfloat16)

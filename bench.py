@@ -49,6 +49,8 @@ def parse():
                     help="profiling aid: after warm-up run ONE step between cudaProfilerStart/Stop and exit "
                          "(use with `ncu --profile-from-start off`); prints no bench line")
     ap.add_argument("--shapes", default="", help="write the per-shape engine timing table (JSON) to this path")
+    ap.add_argument("--graph", default="auto", choices=["auto", "on", "off"],
+                    help="encode workload: replay the launch sequence as a CUDA graph (auto = batch <= 32)")
     ap.add_argument("--workload", default="train", choices=["train", "encode", "recon"],
                     help="train = BASELINE.json configs[1] (default, the bench line); encode = configs[2], encode-only "
                          "inference (Encoder + posterior.mode(), no_grad) at --batch; recon = configs[4]: encode -> mode "
@@ -363,11 +365,20 @@ def run_encode(args, model, dev, B, R, rank, world):
             ms = float(t)
         return ms, z
 
+    # small batches are bound by the host's launch rate: replay the static launch sequence as one CUDA graph
+    use_graph = (not recon) and (args.graph == "on" or (args.graph == "auto" and B <= 32))
+    if use_graph:
+        from odvae_b200.graphs import GraphedEncode
+        genc = GraphedEncode(model, B, R)
+        eager_step = step
+        step = lambda x: genc(x)
+        torch.cuda.synchronize()
+        assert torch.equal(step(x_dev), eager_step(x_dev)), "graph replay differs from the eager launch sequence"
     for _ in range(max(args.warmup, 3)):
         step(x_dev)
     l0 = lib.call("launch_count")
     ms, z = timed(x_dev, args.steps, False)
-    launches = lib.call("launch_count") - l0
+    launches = genc.launches_per_replay * args.steps if use_graph else lib.call("launch_count") - l0
     ms_e2e, z = timed(x_pin, args.steps, True)
     if rank == 0:
         n_img = B * world * args.steps
@@ -380,7 +391,8 @@ def run_encode(args, model, dev, B, R, rank, world):
                 "config": {"workload": ("encode -> mode -> decode -> L1 -> backward (Encoder, Decoder, quant convs; no pose "
                                         "heads, no optimizer), %dx%d crops (BASELINE.json configs[4])" if recon else
                                         "encode-only inference: Encoder + DiagonalGaussian mode(), %dx%d crops, no_grad "
-                                        "(BASELINE.json configs[2])") % (R, R), "per_gpu_batch": B, "resolution": R},
+                                        "(BASELINE.json configs[2])") % (R, R), "per_gpu_batch": B, "resolution": R,
+                           "cuda_graph": bool(use_graph)},
                 "e2e": {"value": n_img / (ms_e2e * 1e-3), "unit": "images/sec",
                         "h2d_bytes_per_step": x_host.numel() * 4, "d2h_bytes_per_step": z.numel() * 4,
                         "ms_per_step": ms_e2e / args.steps},

@@ -238,3 +238,32 @@ def test_fused_adam_matches_torch_adam():
         torch.cuda.synchronize()
         for x, y in zip(a, b):
             assert H.rel_max(x, y) < 1e-5
+
+
+def test_graphed_encode_matches_eager_and_tracks_weight_updates():
+    """GraphedEncode (CUDA-graph replay of encode + mode(), BASELINE configs[2]) returns the eager path's latents bit for
+    bit, for new inputs and after an in-place weight update followed by refresh_param_caches()."""
+    from odvae_b200 import ops
+    from odvae_b200.autoencoder import PoseAutoencoder
+    from odvae_b200.graphs import GraphedEncode
+    params = synth.model_config(synth.DDCONFIG_SMALL, H.stats_path(23))
+    model = PoseAutoencoder(**params, compute_dtype=torch.float16)
+    synth.fill_state_dict_(model.state_dict(), seed=23)
+    model = model.cuda()
+    model.global_step = 80000
+    genc = GraphedEncode(model, 3, 64)
+    assert genc.launches_per_replay > 10
+
+    def eager(x):
+        with torch.no_grad():
+            return model.encode(model._rescale(x))[0].mode()
+
+    for seed in (1, 2):
+        x = synth.synthetic_batch(3, 64, seed)["patch"].cuda()
+        assert torch.equal(genc(x).clone(), eager(x))
+    with torch.no_grad():
+        for p in model.encoder.parameters():
+            p.mul_(1.01)
+    ops.refresh_param_caches()
+    z_new = genc(x).clone()
+    assert torch.equal(z_new, eager(x))

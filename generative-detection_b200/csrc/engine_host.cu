@@ -389,10 +389,10 @@ static void conv_common(EngineDesc& d, int Bn, int Ho, int Wo, int gatherC, int 
     p.num_n_tiles = p.num_m_tiles / 2;  // pairs of pixel boxes
     p.num_m_tiles = N / 128;            // tiles of 128 output channels
   }
-  // Halo mode: W = 256 rows are one N tile; the 9 taps re-read 3 input rows from shared memory instead of 9 shifted
+  // Halo mode: 256 consecutive pixels of an image row (W = 256: the whole row, W = 512: half a row) are one N tile; the 9 taps re-read 3 input rows from shared memory instead of 9 shifted
   // boxes from L2 (the 128-channel layers at 256x256 were L2->SM bound: 14.5 GB per launch at ~10.7 TB/s)
   p.halo = 0;
-  if (p.swap && !g_disable_halo && p.ntaps == 9 && p.sp_rank == 4 && Wo == 256 && bw == 128 && p.tap_dx[0] == -1 &&
+  if (p.swap && !g_disable_halo && p.ntaps == 9 && p.sp_rank == 4 && Wo % 256 == 0 && bw == 128 && p.tap_dx[0] == -1 &&
       p.tap_dy[0] == -1 && p.tap_dx[8] == 1 && p.tap_dy[8] == 1) {
     p.halo = 1;
     p.halo_slabs = 4;

@@ -141,7 +141,7 @@ tc_engine_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant_
   if (warp == 0) {
     // ============================ TMA producer ============================
     if (lane == 0 && cv_halo) {
-      // halo conv: per tile (one image row) and 64-channel chunk, 3 input-row slabs, each followed by the weight
+      // halo conv: per tile (256 consecutive pixels of one image row, starting at tc.x0) and 64-channel chunk, 3 input-row slabs, each followed by the weight
       // tiles of its 3 horizontally shifted taps -- the same order the MMA issuer consumes them in
       int ws = 0, ss = 0;
       uint32_t wph = 0, sph = 0;
@@ -154,8 +154,8 @@ tc_engine_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant_
             uint64_t* sb = &sfull_bar[ss];
             mbar_arrive_expect_tx(sb, 2u * TC_HALO_BOX * 128u);
             uint8_t* dst = sB + static_cast<size_t>(ss) * TC_SLAB_BYTES;
-            tma_load_4d(dst, &tmA, sb, cc * 64, -1, tc.y0 + ry - 1, tc.b);
-            tma_load_4d(dst + TC_HALO_BOX * 128, &tmA, sb, cc * 64, TC_HALO_BOX - 1, tc.y0 + ry - 1, tc.b);
+            tma_load_4d(dst, &tmA, sb, cc * 64, tc.x0 - 1, tc.y0 + ry - 1, tc.b);
+            tma_load_4d(dst + TC_HALO_BOX * 128, &tmA, sb, cc * 64, tc.x0 + TC_HALO_BOX - 1, tc.y0 + ry - 1, tc.b);
             if (++ss == nslabs) {
               ss = 0;
               sph ^= 1u;

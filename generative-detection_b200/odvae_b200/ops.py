@@ -781,6 +781,8 @@ class Linear(torch.autograd.Function):
     def forward(ctx, x, w, b):
         M, K = x.shape
         N = w.shape[0]
+        if w.shape[1] != K:  # F.linear's own error (e.g. 512x512 crops into the config's 16x16x16 pose MLP)
+            raise RuntimeError("mat1 and mat2 shapes cannot be multiplied (%dx%d and %dx%d)" % (M, K, w.shape[1], N))
         y = torch.empty(M, N, dtype=torch.float32, device=x.device)
         gemm_raw(x, w.detach(), y, M, N, K, 1, K, K, N, 0, 0, 0, False, False, bias=None if b is None else b.detach())
         ctx.save_for_backward(x, w, b)

@@ -95,12 +95,14 @@ def test_conv_fwd_dgrad_wgrad(impl, dtype, geom, case):
 
 
 @pytest.mark.parametrize("dtype", [torch.bfloat16, torch.float16])
-def test_conv_halo_slabs_match_tap_gather(dtype):
-    """3x3 stride-1 at W = 256: the shared-memory halo-slab path and the per-tap TMA gather accumulate the same
+@pytest.mark.parametrize("B,H,W", [(2, 256, 256), (1, 64, 512), (3, 32, 512)])
+def test_conv_halo_slabs_match_tap_gather(dtype, B, H, W):
+    """3x3 stride-1 at W = 256 (one tile per image row) and W = 512 (two tiles per row, the configs[4] crops; the seam
+    at x = 256 is an interior halo, not zero padding): the shared-memory halo-slab path and the per-tap TMA gather accumulate the same
     products in the same order per output element only up to the K ordering (chunk-major vs tap-major), so they agree
     to fp32 summation noise; both are checked against torch fp32."""
     from odvae_b200 import lib
-    B, H, W, C = 2, 256, 256, 128
+    C = 128
     torch.manual_seed(5)
     x = torch.randn(B, H, W, C, device=DEV).to(dtype)
     w = torch.randn(C, C, 3, 3, device=DEV) / (C * 9) ** 0.5
@@ -127,6 +129,9 @@ def test_conv_halo_slabs_match_tap_gather(dtype):
     edge = torch.cat([outs[0][0][:, :, 0], outs[0][0][:, :, -1], outs[0][0][:, 0], outs[0][0][:, -1]], 1)
     edge_ref = torch.cat([outs[1][0][:, :, 0], outs[1][0][:, :, -1], outs[1][0][:, 0], outs[1][0][:, -1]], 1)
     assert rel_err(edge, edge_ref) < 4e-3
+    if W > 256:  # the columns either side of the tile seam
+        assert rel_err(outs[0][0][:, :, 254:258], outs[1][0][:, :, 254:258]) < 4e-3
+        assert rel_err(outs[0][1][:, :, 254:258], outs[1][1][:, :, 254:258]) < 4e-3
     assert rel_err(outs[0][2], outs[1][2]) < 1e-5
 
 

@@ -267,3 +267,16 @@ def test_graphed_encode_matches_eager_and_tracks_weight_updates():
     ops.refresh_param_caches()
     z_new = genc(x).clone()
     assert torch.equal(z_new, eager(x))
+
+
+def test_wrong_crop_size_raises_like_the_reference():
+    """The config's pose MLPs take 16x16x16 latents (CFG:34-52): other crop sizes fail in the first Linear with torch's own
+    shape error in the reference (pose_decoder.py:60-97 -> F.linear). Here too: a RuntimeError, never a bad launch."""
+    from odvae_b200.autoencoder import PoseAutoencoder
+    params = synth.model_config(synth.DDCONFIG_SMALL, H.stats_path(23))
+    model = PoseAutoencoder(**params, compute_dtype=torch.float16).cuda()
+    model.global_step = 80000
+    batch = synth.synthetic_batch(2, 128, 3)  # latents 32x32 instead of 16x16
+    with pytest.raises(RuntimeError, match="shapes cannot be multiplied"):
+        model.training_step(batch, 0, 0)
+    torch.cuda.synchronize()

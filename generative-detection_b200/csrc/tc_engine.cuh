@@ -554,15 +554,15 @@ tc_engine_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant_
         const float s2 = p.alpha * 1.4426950408889634f;  // scores live in the log2 domain: exp(a*s) = 2^(s2*s)
         const bool halfp = p.out_mode == OUT_F16;
         float mx = -INFINITY, l = 0.0f, lse2 = 0.0f, delta = 0.0f;  // mx: running max of the RAW accumulators
-        uint4 pp[16];  // DSOFTMAX: this thread's 128 P values
+        uint32_t pp[8][8];  // DSOFTMAX: this thread's 128 P values (8 x 32 bytes)
         if (p.epi == EPI_SOFTMAX && row_ok) {
           // lse2[row] = max + log2(sum 2^(s2*s - max)), combined from the row partials by attn_stats_combine_kernel
           lse2 = __ldg(p.aux_f32 + static_cast<long long>(tc.z) * p.m_valid + (m0 + r));
         } else if (p.epi == EPI_DSOFTMAX && row_ok) {
           delta = __ldg(p.aux_f32 + static_cast<long long>(tc.z) * p.m_valid + (m0 + r));
-          const uint4* psrc = reinterpret_cast<const uint4*>(reinterpret_cast<const uint16_t*>(p.aux16) + row_off + c_begin);
+          const uint16_t* psrc = reinterpret_cast<const uint16_t*>(p.aux16) + row_off + c_begin;
 #pragma unroll
-          for (int i = 0; i < 16; ++i) pp[i] = __ldg(psrc + i);
+          for (int i = 0; i < 8; ++i) ld_global_nc_256(psrc + 16 * i, pp[i]);
         }
         mbar_wait(&tfull_bar[acc], acc_phase);
         tc_fence_after();
@@ -591,9 +591,11 @@ tc_engine_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant_
                 o[i] = pack_16x2(fast_exp2(fmaf(__uint_as_float(v[2 * i]), s2, -lse2)),
                                  fast_exp2(fmaf(__uint_as_float(v[2 * i + 1]), s2, -lse2)), halfp);
             }
-            uint4* dst = reinterpret_cast<uint4*>(reinterpret_cast<uint16_t*>(p.D) + row_off + cc);
-#pragma unroll
-            for (int i = 0; i < 4; ++i) dst[i] = make_uint4(o[4 * i], o[4 * i + 1], o[4 * i + 2], o[4 * i + 3]);
+            uint16_t* dst = reinterpret_cast<uint16_t*>(p.D) + row_off + cc;
+            const uint32_t o_lo[8] = {o[0], o[1], o[2], o[3], o[4], o[5], o[6], o[7]};
+            const uint32_t o_hi[8] = {o[8], o[9], o[10], o[11], o[12], o[13], o[14], o[15]};
+            st_global_256(dst, o_lo);
+            st_global_256(dst + 16, o_hi);
           }
         };
         // every epilogue warp owns exactly 128 accumulator columns here (BN = 256; the host checks N % 256 == 0)
@@ -608,8 +610,7 @@ tc_engine_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant_
             tmem_ld_wait();
             if (j < 7) tmem_ld_x16(t_row + static_cast<uint32_t>(c_begin + 16 * (j + 1)), nxt);
             if (row_ok) {
-              const uint4 p0 = pp[2 * j], p1 = pp[2 * j + 1];
-              const uint32_t pw[8] = {p0.x, p0.y, p0.z, p0.w, p1.x, p1.y, p1.z, p1.w};
+              const uint32_t (&pw)[8] = pp[j];
               uint32_t o[8];
 #pragma unroll
               for (int i = 0; i < 8; ++i) {
@@ -617,9 +618,7 @@ tc_engine_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant_
                 o[i] = pack_16x2(pv.x * p.alpha * (__uint_as_float(cur[2 * i]) - delta),
                                  pv.y * p.alpha * (__uint_as_float(cur[2 * i + 1]) - delta), halfp);
               }
-              uint4* dst = reinterpret_cast<uint4*>(reinterpret_cast<uint16_t*>(p.D) + row_off + c_begin + 16 * j);
-              dst[0] = make_uint4(o[0], o[1], o[2], o[3]);
-              dst[1] = make_uint4(o[4], o[5], o[6], o[7]);
+              st_global_256(reinterpret_cast<uint16_t*>(p.D) + row_off + c_begin + 16 * j, o);
             }
           }
         } else {
@@ -684,9 +683,8 @@ tc_engine_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant_
             uint16_t* dst = reinterpret_cast<uint16_t*>(p.D) + row_off + c;
             if (full) {
               if (p.residual != nullptr) {
-                const uint4* rp = reinterpret_cast<const uint4*>(reinterpret_cast<const uint16_t*>(p.residual) + row_off + c);
-                uint4 r0 = __ldg(rp), r1 = __ldg(rp + 1);
-                uint32_t rw[8] = {r0.x, r0.y, r0.z, r0.w, r1.x, r1.y, r1.z, r1.w};
+                uint32_t rw[8];
+                ld_global_nc_256(reinterpret_cast<const uint16_t*>(p.residual) + row_off + c, rw);
 #pragma unroll
                 for (int i = 0; i < 8; ++i) {
                   float2 rv = unpack_16x2(rw[i], half);
@@ -694,13 +692,10 @@ tc_engine_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant_
                   f[2 * i + 1] += rv.y;
                 }
               }
-              uint4 o0, o1;
-              o0.x = pack_16x2(f[0], f[1], half);   o0.y = pack_16x2(f[2], f[3], half);
-              o0.z = pack_16x2(f[4], f[5], half);   o0.w = pack_16x2(f[6], f[7], half);
-              o1.x = pack_16x2(f[8], f[9], half);   o1.y = pack_16x2(f[10], f[11], half);
-              o1.z = pack_16x2(f[12], f[13], half); o1.w = pack_16x2(f[14], f[15], half);
-              reinterpret_cast<uint4*>(dst)[0] = o0;
-              reinterpret_cast<uint4*>(dst)[1] = o1;
+              uint32_t ow[8];
+#pragma unroll
+              for (int i = 0; i < 8; ++i) ow[i] = pack_16x2(f[2 * i], f[2 * i + 1], half);
+              st_global_256(dst, ow);
             } else {
               for (int i = 0; i < 16; ++i)
                 if (ncol + i < p.n_valid) {
@@ -722,8 +717,12 @@ tc_engine_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant_
                 }
               }
 #pragma unroll
-              for (int i = 0; i < 4; ++i)
-                reinterpret_cast<float4*>(dst)[i] = make_float4(f[4 * i], f[4 * i + 1], f[4 * i + 2], f[4 * i + 3]);
+              for (int i = 0; i < 2; ++i) {
+                uint32_t ow[8];
+#pragma unroll
+                for (int j = 0; j < 8; ++j) ow[j] = __float_as_uint(f[8 * i + j]);
+                st_global_256(dst + 8 * i, ow);
+              }
             } else {
               for (int i = 0; i < 16; ++i)
                 if (ncol + i < p.n_valid) {

@@ -19,7 +19,14 @@ b = torch.randn(C, device="cuda")
 wp = K.pack_conv_weight(w, CONV_3x3_S1, C, C, 0, dt)
 wd = K.pack_conv_weight(w, CONV_3x3_S1, C, C, 1, dt)
 fl = 2.0 * B * H * H * C * C * 9
-ev = [torch.cuda.Event(enable_timing=True) for _ in range(5)]
+from odvae_b200 import lib
+G = 32
+gn_bytes = lib.call("conv2d_fwd_gnstats_workspace_bytes", B, H, H, C, C, CONV_3x3_S1, G)
+gn_ws = torch.empty(max(gn_bytes, 1), dtype=torch.uint8, device="cuda")
+y_gn = torch.empty(B, H, H, C, dtype=dt, device="cuda")
+stats = torch.empty(B, G, 2, device="cuda")
+code = K.act_code(dt)
+ev = [torch.cuda.Event(enable_timing=True) for _ in range(6)]
 for it in range(iters):
     ev[0].record()
     y = K.conv_fwd(x, wp, b, C, CONV_3x3_S1, IMPL_TC)
@@ -30,7 +37,11 @@ for it in range(iters):
     ev[3].record()
     dw, db = K.conv_wgrad(x, dy, C, C, CONV_3x3_S1, IMPL_TC)
     ev[4].record()
+    if gn_bytes:
+        lib.call("conv2d_fwd_gnstats", x, wp, b, None, y_gn, stats, B, H, H, C, C, CONV_3x3_S1, G, 1e-6, code, code, gn_ws, gn_bytes)
+    ev[5].record()
     torch.cuda.synchronize()
-    t = [ev[i].elapsed_time(ev[i + 1]) for i in range(4)]
+    t = [ev[i].elapsed_time(ev[i + 1]) for i in range(5)]
+    print("        fwd+gnstats(+finalize) %.3f ms (%.0f TF/s)" % (t[4], fl / t[4] / 1e9))
     print("iter %d: fwd %.3f ms (%.0f TF/s)  fwd+res %.3f ms (%.0f)  dgrad %.3f ms (%.0f)  wgrad(+reduce,colsum) %.3f ms (%.0f)" % (
         it, t[0], fl / t[0] / 1e9, t[1], fl / t[1] / 1e9, t[2], fl / t[2] / 1e9, t[3], fl / t[3] / 1e9), flush=True)

@@ -362,21 +362,30 @@ __global__ void colsum_stage2(const float* __restrict__ part, int nblk, int cols
 // ---------------------------------------------------------------------------------------------
 // nearest 2x upsample and adjoint, NHWC
 // ---------------------------------------------------------------------------------------------
+// one thread per INPUT vector: 1 load, 4 stores (the 2x2 block), 32-bit index math - the per-output-vector form spent
+// its time in 64-bit div/mod chains (2.7 TB/s in the s10 launch list)
 template <typename T>
 __global__ void upsample2x_kernel(const T* __restrict__ x, T* __restrict__ y, int B, int H, int W, int C) {
   constexpr int V = Vec16<T>::N;
   const int cv = C / V;
-  const long long total = static_cast<long long>(B) * (2 * H) * (2 * W) * cv;
-  for (long long i = blockIdx.x * static_cast<long long>(blockDim.x) + threadIdx.x; i < total;
-       i += static_cast<long long>(gridDim.x) * blockDim.x) {
-    const int c = static_cast<int>(i % cv);
-    long long q = i / cv;
-    const int xo = static_cast<int>(q % (2 * W));
-    q /= (2 * W);
-    const int yo = static_cast<int>(q % (2 * H));
-    const int b = static_cast<int>(q / (2 * H));
-    const uint4 v = __ldg(reinterpret_cast<const uint4*>(x + ((static_cast<long long>(b) * H + (yo >> 1)) * W + (xo >> 1)) * C) + c);
-    reinterpret_cast<uint4*>(y)[i] = v;
+  const long long rows = static_cast<long long>(B) * H;  // input rows
+  const int row_vecs = W * cv;                           // vectors per input row
+  const uint4* xv = reinterpret_cast<const uint4*>(x);
+  uint4* yv = reinterpret_cast<uint4*>(y);
+  for (long long r = blockIdx.y; r < rows; r += gridDim.y) {
+    const uint4* src = xv + r * row_vecs;
+    // input row r = (b, yi) -> output rows 2*(b*H + yi) and +1 of the [B*2H][2W][cv] output
+    uint4* d0 = yv + (2 * r) * (2LL * row_vecs);
+    uint4* d1 = d0 + 2LL * row_vecs;
+    for (int i = blockIdx.x * blockDim.x + threadIdx.x; i < row_vecs; i += gridDim.x * blockDim.x) {
+      const int xi = i / cv, c = i - xi * cv;
+      const uint4 v = __ldg(src + i);
+      const int o = (2 * xi) * cv + c;
+      d0[o] = v;
+      d0[o + cv] = v;
+      d1[o] = v;
+      d1[o + cv] = v;
+    }
   }
 }
 template <typename T>
@@ -582,15 +591,21 @@ int odvae_pack_conv_weights_mt(const int64_t* table_dev, int n_entries, int64_t 
 
 int odvae_upsample2x(const void* x, void* y, int B, int H, int W, int C, int act_dtype, void* stream) {
   cudaStream_t st = static_cast<cudaStream_t>(stream);
-  if (act_dtype == ODVAE_BF16 || act_dtype == ODVAE_F16) {  // a copy: any 16-bit format
-    if (C % 8) return ODVAE_ERR_SHAPE;
-    const long long total = static_cast<long long>(B) * 4 * H * W * (C / 8);
-    upsample2x_kernel<bf16><<<grid_for(total, 256), 256, 0, st>>>(reinterpret_cast<const bf16*>(x), reinterpret_cast<bf16*>(y), B, H, W, C);
-  } else {
-    if (C % 4) return ODVAE_ERR_SHAPE;
-    const long long total = static_cast<long long>(B) * 4 * H * W * (C / 4);
-    upsample2x_kernel<float><<<grid_for(total, 256), 256, 0, st>>>(reinterpret_cast<const float*>(x), reinterpret_cast<float*>(y), B, H, W, C);
-  }
+  const int V = (act_dtype == ODVAE_BF16 || act_dtype == ODVAE_F16) ? 8 : 4;
+  if (C % V) return ODVAE_ERR_SHAPE;
+  // grid: x over the vectors of one input row, y over (image, input row) grid-stride; ~8 CTAs per SM in total
+  const int row_vecs = W * (C / V);
+  const int gx = (row_vecs + 255) / 256;
+  long long gy = (8LL * num_sms() + gx - 1) / gx;
+  const long long rows = static_cast<long long>(B) * H;
+  if (gy > rows) gy = rows;
+  if (gy > 65535) gy = 65535;
+  if (gy < 1) gy = 1;
+  const dim3 grid(gx, static_cast<unsigned>(gy));
+  if (V == 8)  // a copy: any 16-bit format
+    upsample2x_kernel<bf16><<<grid, 256, 0, st>>>(reinterpret_cast<const bf16*>(x), reinterpret_cast<bf16*>(y), B, H, W, C);
+  else
+    upsample2x_kernel<float><<<grid, 256, 0, st>>>(reinterpret_cast<const float*>(x), reinterpret_cast<float*>(y), B, H, W, C);
   return check_launch("upsample2x_kernel");
 }
 

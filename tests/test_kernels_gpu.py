@@ -211,3 +211,15 @@ def test_multi_tensor_weight_pack_matches_single_packs():
         ref = ops.pack_weight(w.detach(), spec.geom, spec.coutp, spec.cinp, which, code)
         torch.cuda.synchronize()
         assert torch.equal(buf, ref), (spec.cin, spec.cout, spec.geom, which, code)
+
+
+@pytest.mark.parametrize("dtype", [torch.float32, torch.bfloat16])
+@pytest.mark.parametrize("shape", [(2, 16, 16, 512), (3, 32, 64, 256), (1, 128, 128, 128), (5, 7, 9, 64)])
+def test_upsample2x_matches_nearest_interpolate(dtype, shape):
+    """Upsample.forward's F.interpolate(scale_factor=2.0, mode="nearest") (LD model.py:53-57) on NHWC: exact copy."""
+    torch.manual_seed(9)
+    x = torch.randn(shape, device=DEV).to(dtype)
+    y = ops.upsample2x_raw(x)
+    torch.cuda.synchronize()
+    ref = F.interpolate(x.float().permute(0, 3, 1, 2), scale_factor=2.0, mode="nearest").permute(0, 2, 3, 1)
+    assert torch.equal(y.float(), ref)

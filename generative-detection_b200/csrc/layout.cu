@@ -22,16 +22,22 @@ __global__ void nchw_to_nhwc_kernel(const float* __restrict__ src, T* __restrict
     const int p = static_cast<int>(i - static_cast<long long>(b) * HW);
     const float* s = src + (static_cast<long long>(b) * C) * HW + p;
     T* d = dst + i * Cpad;
-    constexpr int V = Vec16<T>::N;
-    for (int c0 = 0; c0 < Cpad; c0 += V) {
-      T tmp[V];
+    // 32 bytes (one full sector) per store: a thread owns a whole pixel, so 16-byte stores would leave every
+    // instruction with half-filled sectors
+    constexpr int V2 = 2 * Vec16<T>::N;
+    for (int c0 = 0; c0 < Cpad; c0 += V2) {
+      __align__(16) T tmp[V2];
 #pragma unroll
-      for (int j = 0; j < V; ++j) {
+      for (int j = 0; j < V2; ++j) {
         const int c = c0 + j;
         float v = (c < C) ? __ldg(s + static_cast<long long>(c) * HW) * scale + shift : 0.0f;
         tmp[j] = from_f32<T>(v);
       }
-      *reinterpret_cast<uint4*>(d + c0) = *reinterpret_cast<const uint4*>(tmp);
+      if (c0 + V2 <= Cpad) {
+        st_global_256(d + c0, *reinterpret_cast<const uint32_t(*)[8]>(tmp));
+      } else {
+        *reinterpret_cast<uint4*>(d + c0) = *reinterpret_cast<const uint4*>(tmp);
+      }
     }
   }
 }

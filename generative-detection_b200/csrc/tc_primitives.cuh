@@ -63,34 +63,6 @@ __device__ __forceinline__ void mbar_wait(uint64_t* bar, uint32_t parity) {
 }
 
 // ----------------------------------------------------------------------------------------------
-// 256-bit global accesses (sm_100: LDG/STG.E.ENL2.256). A thread that owns one matrix row touches 32 contiguous bytes
-// = one full L2 sector per instruction; as two 16-byte accesses every instruction moved half-filled sectors
-// (ncu, attention softmax pass: 4.43 GB of L1->L2 write traffic for 2.10 GB stored). Falls back to 2 x 128 bit when the
-// address is not 32-byte aligned.
-// ----------------------------------------------------------------------------------------------
-__device__ __forceinline__ void st_global_256(void* ptr, const uint32_t (&o)[8]) {
-  if ((reinterpret_cast<uintptr_t>(ptr) & 31u) == 0) {
-    asm volatile("st.global.v8.b32 [%0], {%1,%2,%3,%4,%5,%6,%7,%8};" ::"l"(ptr), "r"(o[0]), "r"(o[1]), "r"(o[2]),
-                 "r"(o[3]), "r"(o[4]), "r"(o[5]), "r"(o[6]), "r"(o[7])
-                 : "memory");
-  } else {
-    reinterpret_cast<uint4*>(ptr)[0] = make_uint4(o[0], o[1], o[2], o[3]);
-    reinterpret_cast<uint4*>(ptr)[1] = make_uint4(o[4], o[5], o[6], o[7]);
-  }
-}
-__device__ __forceinline__ void ld_global_nc_256(const void* ptr, uint32_t (&r)[8]) {
-  if ((reinterpret_cast<uintptr_t>(ptr) & 31u) == 0) {
-    asm volatile("ld.global.nc.v8.b32 {%0,%1,%2,%3,%4,%5,%6,%7}, [%8];"
-                 : "=r"(r[0]), "=r"(r[1]), "=r"(r[2]), "=r"(r[3]), "=r"(r[4]), "=r"(r[5]), "=r"(r[6]), "=r"(r[7])
-                 : "l"(ptr));
-  } else {
-    const uint4 a = __ldg(reinterpret_cast<const uint4*>(ptr)), b = __ldg(reinterpret_cast<const uint4*>(ptr) + 1);
-    r[0] = a.x; r[1] = a.y; r[2] = a.z; r[3] = a.w;
-    r[4] = b.x; r[5] = b.y; r[6] = b.z; r[7] = b.w;
-  }
-}
-
-// ----------------------------------------------------------------------------------------------
 // TMA tile loads (global -> shared, completion on an mbarrier)
 // ----------------------------------------------------------------------------------------------
 __device__ __forceinline__ void tma_prefetch_desc(const CUtensorMap* m) {

@@ -223,3 +223,25 @@ def test_upsample2x_matches_nearest_interpolate(dtype, shape):
     torch.cuda.synchronize()
     ref = F.interpolate(x.float().permute(0, 3, 1, 2), scale_factor=2.0, mode="nearest").permute(0, 2, 3, 1)
     assert torch.equal(y.float(), ref)
+
+
+@pytest.mark.parametrize("C,Cpad,code", [(3, 64, "bf16"), (3, 64, "f16"), (16, 64, "f16"), (3, 8, "bf16"), (5, 24, "f16"), (3, 4, "f32"),
+                                         (16, 64, "f32")])
+def test_nchw_to_nhwc_pads_and_rescales(C, Cpad, code):
+    """get_input/_rescale boundary (LD autoencoder.py:344-349, AE.py:434-436): NCHW fp32 -> padded NHWC with the affine
+    `x * scale + shift` fused; padding channels are exact zeros."""
+    from odvae_b200.lib import BF16, F16, F32
+    torch.manual_seed(4)
+    B, H, W = 3, 20, 12
+    x = torch.rand(B, C, H, W, device=DEV)
+    dc = {"bf16": BF16, "f16": F16, "f32": F32}[code]
+    y = ops.nchw_to_nhwc_raw(x, Cpad, dc, 2.0, -1.0)
+    torch.cuda.synchronize()
+    tdt = {"bf16": torch.bfloat16, "f16": torch.float16, "f32": torch.float32}[code]
+    yv = y.view(tdt) if y.dtype != tdt else y
+    assert tuple(yv.shape) == (B, H, W, Cpad)
+    ref = (x * 2.0 - 1.0).permute(0, 2, 3, 1).to(tdt)
+    # the kernel may contract x * scale + shift into one FMA: allow one rounding step of the output format
+    assert float((yv[..., :C].float() - ref.float()).abs().max()) <= {"bf16": 2 ** -7, "f16": 2 ** -10, "f32": 2 ** -22}[code]
+    if Cpad > C:
+        assert float(yv[..., C:].float().abs().max()) == 0.0

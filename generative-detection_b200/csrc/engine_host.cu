@@ -383,7 +383,8 @@ static void conv_common(EngineDesc& d, int Bn, int Ho, int Wo, int gatherC, int 
   // of the SM (measured ~750 TF/s), a 128 x 256 tile at 96 B/clk (~1250 TF/s). With M = 128 output channels
   // (weights) and N = 256 pixels the same layer runs the wide tile; the epilogue stores channel-contiguous.
   p.swap = 0;
-  if (d.tc_ok && geo && BN == 128 && N == 128 && out_mode == OUT_BF16 && bw >= 32 && (p.num_m_tiles % 2) == 0) {
+  if (d.tc_ok && geo && BN == 128 && N == 128 && (out_mode == OUT_BF16 || out_mode == OUT_NCHW_F32) && bw >= 32 &&
+      (p.num_m_tiles % 2) == 0) {
     p.swap = 1;
     p.BN = 256;
     p.num_n_tiles = p.num_m_tiles / 2;  // pairs of pixel boxes

@@ -455,7 +455,21 @@ tc_engine_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant_
         auto emit = [&](uint32_t (&v)[32], int pi0) {
           const int yy = pb_y + (pi0 >> p.bw_log2), xx = pb_x + (pi0 & ((1 << p.bw_log2) - 1));
           const long long base = base0 + static_cast<long long>(yy) * p.oY + static_cast<long long>(xx) * sx;
-          if (stg != nullptr) {
+          if (p.out_mode == OUT_NCHW_F32) {
+            // thin output conv (decoder.conv_out, Cout = 3 padded to the 128-row weight tile): lane = channel, the 32
+            // pixels of the batch are consecutive in x -> 128 contiguous bytes of the NCHW fp32 result per valid lane
+            if (ch_ok) {
+              float* dstf = reinterpret_cast<float*>(p.D) +
+                            ((static_cast<long long>(pb_b) * p.n_valid + n) * p.out_h + yy) * p.out_w + xx;
+#pragma unroll
+              for (int k = 0; k < 4; ++k) {
+                uint32_t ow[8];
+#pragma unroll
+                for (int j = 0; j < 8; ++j) ow[j] = __float_as_uint(fmaf(__uint_as_float(v[8 * k + j]), p.alpha, bias));
+                st_global_256(dstf + 8 * k, ow);
+              }
+            }
+          } else if (stg != nullptr) {
             const long long vbase = static_cast<long long>(pb_b) * p.oB + p.o0 + vch + static_cast<long long>(yy) * p.oY +
                                     static_cast<long long>(xx + (lane >> 2)) * sx;
             float f[32];

@@ -314,6 +314,10 @@ def conv_fwd_raw(x, spec, w, b, residual=None, out_nchw=False, op=None, out=None
         coutp = 16 if spec.cout <= 16 else spec.coutp
         impl = conv_impl(op, B, H, W, CinP, 64, spec.geom) if coutp == 16 else \
             conv_impl(op, B, H, W, CinP, coutp, spec.geom)
+        if coutp == 16 and impl == IMPL_TC and spec.geom == CONV_3x3_S1 and Wo % 256 == 0:
+            # N = 16 tiles are MMA-issue and L2->SM bound (1.7 ms for decoder.conv_out at batch 64); padded to one 128-row
+            # weight tile the layer takes the swapped-role halo-slab tiles (0.9 ms), lanes >= Cout are simply not stored
+            coutp = 128
         y = torch.empty(B, spec.cout, Ho, Wo, dtype=torch.float32, device=x.device)
         call("conv2d_fwd", x, spec.w_fwd(w, op, coutp), None if b is None else b.detach(), None, y, B, H, W,
              CinP, coutp, spec.cout, spec.geom, op, out, impl, 1)

@@ -151,6 +151,24 @@ def test_conv_out_nchw_thin(impl, dtype):
     assert rel_err(y, ref_conv(x, wq, b, CONV_3x3_S1)) < tol(dtype)
 
 
+@pytest.mark.parametrize("dtype", [torch.bfloat16, torch.float16])
+@pytest.mark.parametrize("B,H,W", [(3, 8, 256), (1, 4, 512), (2, 64, 64)])
+def test_conv_out_nchw_swapped_tiles(dtype, B, H, W):
+    """decoder.conv_out at full width: weights padded to ONE 128-row tile so the layer takes the swapped-role (halo-slab
+    at W % 256 == 0) tiles; lanes >= Cout are not stored. Must equal the N = 16 tile result and torch."""
+    Cin, Cout = 128, 3
+    torch.manual_seed(2)
+    x = torch.randn(B, H, W, Cin, device=DEV).to(dtype)
+    w = torch.randn(Cout, Cin, 3, 3, device=DEV) / (Cin * 9) ** 0.5
+    b = torch.randn(Cout, device=DEV)
+    y128 = K.conv_fwd(x, K.pack_conv_weight(w, CONV_3x3_S1, 128, Cin, 0, dtype), b, Cout, CONV_3x3_S1, IMPL_TC, out_nchw_f32=True)
+    y16 = K.conv_fwd(x, K.pack_conv_weight(w, CONV_3x3_S1, 16, Cin, 0, dtype), b, Cout, CONV_3x3_S1, IMPL_TC, out_nchw_f32=True)
+    torch.cuda.synchronize()
+    assert y128.shape == (B, Cout, H, W) and y128.dtype == torch.float32
+    assert rel_err(y128, ref_conv(x, w.to(dtype).float(), b, CONV_3x3_S1)) < tol(dtype)
+    assert rel_err(y128, y16) < 1e-5
+
+
 GEMM_CASES = [
     # M, N, K, batch
     (256, 256, 128, 2),

@@ -5,8 +5,9 @@ LD/ldm/modules/losses/contperceptual.py:7-43 (LPIPSWithDiscriminator: `logvar` p
 adaptive weight). optimizer_idx 0 runs as two kernels each way: the fused masked-L1 reduction over the
 images (ops.L1Masked) and the one-CTA "loss heads" kernel for everything per-sample / scalar (LossHeads).
 
-Not implemented yet (arithmetic lives in the un-vendored taming-transformers): LPIPS and the
-PatchGAN discriminator. `perceptual_weight > 0` or `disc_factor > 0` raise at forward time; with
+`perceptual_weight > 0` adds the LPIPS term (odvae_b200/lpips.py: VGG16 towers on the conv engine; taming's class is
+un-vendored, so parity is against oracle/lpips_oracle.py only and the trained vgg.pth must be loaded by the user).
+Not implemented yet: the PatchGAN discriminator - `disc_factor > 0` raises at forward time; with
 `disc_factor == 0` the generator term is exactly 0 in the reference's total (LOSS.py:294-317), only the
 logged `g_loss` differs (reported as 0 here).
 """
@@ -119,6 +120,11 @@ class PoseLoss(nn.Module):
             raise NotImplementedError("the fused loss implements the north-star config: pose_loss_fn='l1', train_on_yaw")
         self.kl_weight, self.pixel_weight = kl_weight, pixelloss_weight
         self.perceptual_weight = perceptual_weight
+        if perceptual_weight > 0:
+            # LD contperceptual.py:17 `self.perceptual_loss = LPIPS().eval()`: frozen VGG16 + lin heads. The trained weights
+            # (taming's vgg.pth) are not downloadable here: load them with load_state_dict / init_from_ckpt.
+            from .lpips import LPIPS
+            self.perceptual_loss = LPIPS().eval()
         self.logvar = nn.Parameter(torch.ones(size=()) * logvar_init)
         self.discriminator = NLayerDiscriminator(input_nc=disc_in_channels, n_layers=disc_num_layers,
                                                  use_actnorm=use_actnorm)
@@ -172,8 +178,6 @@ class PoseLoss(nn.Module):
                 split="train", weights=None):
         if mask_gt is not None or weights is not None or cond is not None:
             raise NotImplementedError("image masks / per-pixel weights / conditioning are unused by the north-star config")
-        if self.perceptual_weight > 0:
-            raise NotImplementedError("LPIPS (taming, needs vgg.pth) is SURVEY 8 f2; set perceptual_weight=0")
         if self.disc_factor > 0:
             raise NotImplementedError("the GAN terms are SURVEY 8 f2; set disc_factor=0")
         dev = rgb_gt.device
@@ -195,6 +199,13 @@ class PoseLoss(nn.Module):
         l1_sums = None
         if use_pixel:
             l1_sums = ops.L1Masked.apply(ops._c(rgb_gt.float()), dec_obj[:, :3].contiguous(), mask2d)
+        if self.perceptual_weight > 0:
+            # LOSS.py:141-145: rec_loss = |x - xhat| + perceptual_weight * p_loss[B,1,1,1], both on the bbox-masked images
+            # (LOSS.py:250-257); per sample that adds perceptual_weight * p_loss[b] to every one of the 3 H W elements
+            m = mask2d.reshape(B, 1, rgb_gt.shape[2], rgb_gt.shape[3])
+            p_loss = self.perceptual_loss(rgb_gt.float() * m, dec_obj[:, :3] * m).reshape(B)
+            p_term = (self.perceptual_weight * npix) * p_loss
+            l1_sums = p_term if l1_sums is None else l1_sums + p_term
         train_rec = global_step > self.encoder_pretrain_steps and self.encoder_pretrain_steps != -1
         w7 = (1.0 if train_rec else 0.0, self.kl_weight_obj if train_rec else 0.0, self.pose_weight,
               self.class_weight, self.bbox_weight, self.fill_factor_weight, self.kl_weight_bbox)

@@ -304,6 +304,27 @@ int odvae_act_bwd(const float* x, const float* dy, float* dx, int64_t n, int act
  * Mixed mode: the bf16 copy of an fp16 forward activation that a weight-gradient GEMM contracts with bf16 dy. */
 int odvae_cast16(const void* src, void* dst, int64_t n, int src_dtype, int dst_dtype, void* stream);
 
+/* ---------------------------------------------------------------------------------------------
+ * LPIPS perceptual distance. Call site: PoseLoss._get_rec_loss (src/modules/losses/contperceptual.py:141-145)
+ * -> taming.modules.losses.lpips.LPIPS (un-vendored; public definition in SURVEY appendix B). The VGG16 3x3 convs run
+ * through odvae_conv2d_fwd / odvae_conv2d_dgrad; these are the kernels around them. dtype: ODVAE_F32 or ODVAE_BF16,
+ * tensors NHWC with C % 8 == 0 (bf16) / C % 4 == 0 (f32).
+ * ------------------------------------------------------------------------------------------- */
+/* nn.ReLU(inplace=True) of torchvision's vgg16.features; bwd: dx = dy where the ReLU OUTPUT y > 0 (dx may alias dy) */
+int odvae_relu(void* x, int64_t n, int dtype, void* stream);
+int odvae_relu_bwd(const void* y, const void* dy, void* dx, int64_t n, int dtype, void* stream);
+/* nn.MaxPool2d(2, 2): x [B,H,W,C] -> y [B,H/2,W/2,C]; bwd routes dy to the first maximum of each window (torch order) */
+int odvae_maxpool2x2(const void* x, void* y, int B, int H, int W, int C, int dtype, void* stream);
+int odvae_maxpool2x2_bwd(const void* x, const void* dy, void* dx, int B, int H, int W, int C, int dtype, void* stream);
+/* One LPIPS level: out[b] (+)= mean_p sum_c w[c] * (f0/(|f0|_c + 1e-10) - f1/(|f1|_c + 1e-10))^2 over features
+ * f0, f1 [B][HW][C] (normalize_tensor + squared difference + NetLinLayer 1x1 conv + spatial_average);
+ * bwd: df1 (+)= dout[b] * d out[b] / d f1 (the reconstruction's features; the input's tower needs no gradient). */
+size_t odvae_lpips_level_workspace_bytes(int B);
+int odvae_lpips_level_fwd(const void* f0, const void* f1, const float* w, float* out, int B, int HW, int C, int dtype,
+                          int accumulate, void* workspace, size_t ws_bytes, void* stream);
+int odvae_lpips_level_bwd(const void* f0, const void* f1, const float* w, const float* dout, void* df1, int B, int HW,
+                          int C, int dtype, int accumulate, void* stream);
+
 /* out[c] (+)= sum_r m[r*ld + c]  (nn.Linear bias gradients); dtype = ODVAE_F32 / ODVAE_BF16 */
 size_t odvae_colsum_workspace_bytes(int cols);
 int odvae_colsum(const void* m, int64_t rows, int cols, int ld, int dtype, float* out, int accumulate,

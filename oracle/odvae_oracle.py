@@ -270,8 +270,12 @@ class Oracle:
         fill_loss = (F.mse_loss(fill_gt, fill_rec.squeeze(), reduction="none") * mask_bg).sum() / nbg if nbg > 0 else zero
 
         rec = torch.abs(inputs_rgb - rec_rgb) if use_pixel else torch.zeros_like(inputs_rgb)  # LOSS:134-145
-        if lp.get("perceptual_weight", 1.0) > 0:
-            raise NotImplementedError("LPIPS needs vgg.pth (SURVEY §8 f2); use perceptual_weight=0")
+        if lp.get("perceptual_weight", 1.0) > 0:  # LOSS:141-145; taming's LPIPS restated in oracle/lpips_oracle.py
+            lpips = getattr(self, "lpips", None)
+            if lpips is None:
+                raise NotImplementedError("perceptual_weight > 0 needs an LPIPS instance: set `.lpips` to an "
+                                          "oracle.lpips_oracle.LPIPSOracle (vgg.pth is not downloadable offline)")
+            rec = rec + lp["perceptual_weight"] * lpips(inputs_rgb.contiguous(), rec_rgb.contiguous())
         nll_el = rec / (torch.exp(logvar) + 1e-8) + logvar  # LOSS:147-158
         nll = (nll_el * mask_bg.view(-1, 1, 1, 1)).sum() / nbg if nbg > 0 else zero
         kl_obj = (post.kl() * mask_bg).sum() / nbg if nbg > 0 else zero  # LOSS:160-164

@@ -49,6 +49,9 @@ def parse():
                     help="profiling aid: after warm-up run ONE step between cudaProfilerStart/Stop and exit "
                          "(use with `ncu --profile-from-start off`); prints no bench line")
     ap.add_argument("--shapes", default="", help="write the per-shape engine timing table (JSON) to this path")
+    ap.add_argument("--perceptual-weight", type=float, default=0.0,
+                    help="train workload: PoseLoss perceptual_weight (the yaml's default is 1.0 = LPIPS on; the bench line "
+                         "keeps 0 as BASELINE.json configs[1] states, this flag measures the step with the LPIPS towers)")
     ap.add_argument("--graph", default="auto", choices=["auto", "on", "off"],
                     help="encode workload: replay the launch sequence as a CUDA graph (auto = batch <= 32)")
     ap.add_argument("--workload", default="train", choices=["train", "encode", "recon"],
@@ -427,9 +430,11 @@ def run_ours(args):
     B = args.batch
 
     params = synth.model_config(synth.DDCONFIG, stats_file())
+    params["lossconfig"]["params"]["perceptual_weight"] = args.perceptual_weight
     torch.manual_seed(23)
     model = PoseAutoencoder(**params, compute_dtype=torch.float16 if args.mode == "mixed" else torch.bfloat16)
-    synth.fill_state_dict_(model.state_dict(), seed=23)  # identical replicas on every rank
+    synth.fill_state_dict_({k: v for k, v in model.state_dict().items() if not k.startswith("loss.perceptual_loss.")},
+                           seed=23)  # identical replicas on every rank (LPIPS keeps its seeded constructor weights)
     model = model.to(dev)
     model.global_step = STEP
     # LR scaling of train.py:383: accumulate_grad_batches * ngpu * batch * base_lr
@@ -540,7 +545,7 @@ def run_ours(args):
                 "dtype": "fp16 fwd + bf16 attn/grad (tcgen05 kind::f16, fp32 accumulate)" if args.mode == "mixed" else "bf16",
                 "data": "synthetic",
                 "config": {"workload": "autoencoder_kl_16x16x16 pose config, %dx%d crops, train step (fwd + KL/L1/pose " % (R, R) +
-                                       "loss + bwd + allreduce + clip 1.0 + Adam), global_step 80000, perceptual_weight=0, "
+                                       "loss + bwd + allreduce + clip 1.0 + Adam), global_step 80000, perceptual_weight=%g, " % args.perceptual_weight +
                                        "disc_factor=0 (BASELINE.json configs[%d])" % (1 if R == RES else 4),
                            "per_gpu_batch": B, "global_batch": B * world, "resolution": R,
                            "parallelism": "dp%d" % world,

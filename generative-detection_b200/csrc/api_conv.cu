@@ -114,9 +114,10 @@ int odvae_conv2d_wgrad(const void* x, const void* dy, float* dw_oihw, float* db,
   }
   st = run_engine(d, impl, act_dtype, s);
   if (st != ODVAE_OK) return st;
-  st = launch_wgrad_reduce(ws, dw_oihw, Cout, Cin, d.p.ntaps, CoutP, CinP, d.p.split_k, accumulate, s);
-  if (st != ODVAE_OK) return st;
-  if (fused_db) return launch_colsum_final(cpart, cs_rows, Cout, db, accumulate, s);
+  // split-K partials -> dw, and (fused_db) the partial column sums of dy -> db, in ONE launch
+  st = launch_wgrad_reduce(ws, dw_oihw, Cout, Cin, d.p.ntaps, CoutP, CinP, d.p.split_k, accumulate, s,
+                           fused_db ? cpart : nullptr, fused_db ? cs_rows : 0, db);
+  if (st != ODVAE_OK || fused_db) return st;
   if (db != nullptr) {
     const int Ho = geom == ODVAE_CONV_3x3_S2 ? H / 2 : H, Wo = geom == ODVAE_CONV_3x3_S2 ? W / 2 : W;
     st = launch_colsum(dy, static_cast<long long>(B) * Ho * Wo, Cout, CoutP, act_dtype, db, accumulate, cpart, s);

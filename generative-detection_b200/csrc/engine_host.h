@@ -23,7 +23,8 @@ int launch_gn_stats_finalize(const float* part, float* stats, int B, int nsplit,
 int launch_attn_stats_combine(const float* part, float* lse2, int B, int slots, int N, cudaStream_t st);
 // layout.cu
 int launch_wgrad_reduce(const float* ws, float* dw, int Cout, int Cin, int taps, int CoutP, int CinP, int split_k,
-                        int accumulate, cudaStream_t st);
+                        int accumulate, cudaStream_t st, const float* cpart = nullptr, int cs_rows = 0,
+                        float* db = nullptr);
 size_t colsum_workspace_bytes(int cols);
 int launch_colsum_final(const float* part, int nrows, int cols, float* out, int accumulate, cudaStream_t st);
 int launch_colsum(const void* m, long long rows, int cols, int ld, int act_dtype, float* out, int accumulate,

@@ -225,9 +225,28 @@ pack_conv_weight_mt_kernel(const long long* __restrict__ table, int n_entries) {
 // One thread sums VEC consecutive ci over all splits, 8 independent (vector) loads in flight, added in split order
 // (the order is part of the bit-stability contract). The workspace was written by the preceding weight-gradient kernel
 // and is mostly L2-resident, so the kernel is latency-bound: wide loads and deep unrolling are what shorten it.
+// The bias gradient rides along: the weight-gradient kernel leaves `cs_rows` partial column sums per output channel
+// (`cpart`, see TcParams::colsum); the first Cout threads of the grid add them up in row order (8 loads in flight).
 template <int VEC>
 __global__ void wgrad_reduce_kernel(const float* __restrict__ ws, float* __restrict__ dw, int Cout, int Cin,
-                                    int taps, int CoutP, int CinP, int split_k, int accumulate) {
+                                    int taps, int CoutP, int CinP, int split_k, int accumulate,
+                                    const float* __restrict__ cpart, int cs_rows, float* __restrict__ db) {
+  if (cpart != nullptr) {
+    const long long c = blockIdx.x * static_cast<long long>(blockDim.x) + threadIdx.x;
+    if (c < Cout) {
+      float t = 0.0f;
+      int r = 0;
+      for (; r + 7 < cs_rows; r += 8) {
+        float v[8];
+#pragma unroll
+        for (int u = 0; u < 8; ++u) v[u] = __ldg(cpart + static_cast<long long>(r + u) * Cout + c);
+#pragma unroll
+        for (int u = 0; u < 8; ++u) t += v[u];
+      }
+      for (; r < cs_rows; ++r) t += __ldg(cpart + static_cast<long long>(r) * Cout + c);
+      db[c] = accumulate ? db[c] + t : t;
+    }
+  }
   const int cin_v = Cin / VEC;
   const long long total = static_cast<long long>(Cout) * cin_v * taps;
   const long long sstride = static_cast<long long>(CoutP) * CinP;
@@ -468,12 +487,17 @@ static int grid_for(long long work_items, int threads, int per_sm = 8) {
 
 // internal entry points used by api.cu ----------------------------------------------------------
 int launch_wgrad_reduce(const float* ws, float* dw, int Cout, int Cin, int taps, int CoutP, int CinP, int split_k,
-                        int accumulate, cudaStream_t st) {
+                        int accumulate, cudaStream_t st, const float* cpart, int cs_rows, float* db) {
   const long long total = static_cast<long long>(Cout) * Cin * taps;
-  if (Cin % 4 == 0 && CinP % 4 == 0 && (reinterpret_cast<uintptr_t>(ws) & 15) == 0)
-    wgrad_reduce_kernel<4><<<grid_for(total / 4, 128), 128, 0, st>>>(ws, dw, Cout, Cin, taps, CoutP, CinP, split_k, accumulate);
-  else
-    wgrad_reduce_kernel<1><<<grid_for(total, 256), 256, 0, st>>>(ws, dw, Cout, Cin, taps, CoutP, CinP, split_k, accumulate);
+  if (Cin % 4 == 0 && CinP % 4 == 0 && (reinterpret_cast<uintptr_t>(ws) & 15) == 0) {
+    int grid = grid_for(total / 4, 128);
+    if (cpart != nullptr && static_cast<long long>(grid) * 128 < Cout) grid = (Cout + 127) / 128;
+    wgrad_reduce_kernel<4><<<grid, 128, 0, st>>>(ws, dw, Cout, Cin, taps, CoutP, CinP, split_k, accumulate, cpart, cs_rows, db);
+  } else {
+    int grid = grid_for(total, 256);
+    if (cpart != nullptr && static_cast<long long>(grid) * 256 < Cout) grid = (Cout + 255) / 256;
+    wgrad_reduce_kernel<1><<<grid, 256, 0, st>>>(ws, dw, Cout, Cin, taps, CoutP, CinP, split_k, accumulate, cpart, cs_rows, db);
+  }
   return check_launch("wgrad_reduce_kernel");
 }
 

@@ -87,3 +87,40 @@ def test_generic_distribution_cross_term_kl():
     want = 0.5 * sum(((a.mean[i, 0] - b.mean[j, 0]) ** 2 + a.var[i, 0]) / (b.var[j, 0] + 1e-5) - 1 - a.logvar[i, 0]
                      + b.logvar[j, 0] for j in range(8))
     assert abs(float(kl[i]) - float(want)) < 1e-4 * abs(float(want))
+
+
+def test_lpips_state_dict_layout_matches_taming_names():
+    """taming.modules.losses.lpips.LPIPS checkpoints (vgg.pth + lin heads) must load unchanged: `net.slice{k}.{features
+    index}.weight|bias` for the 13 VGG16 convs, `lin{k}.model.1.weight` [1,C,1,1], `scaling_layer.shift|scale`
+    (public layout). Product module and CPU oracle agree key for key and shape for shape."""
+    import os
+    import sys
+    sys.path.insert(0, os.path.dirname(os.path.dirname(os.path.abspath(__file__))))
+    from oracle.lpips_oracle import LPIPSOracle
+    from odvae_b200.lpips import LPIPS
+    ref, mod = LPIPSOracle().state_dict(), LPIPS().state_dict()
+    assert list(ref.keys()) == list(mod.keys())
+    for k in ref:
+        assert tuple(ref[k].shape) == tuple(mod[k].shape), k
+    idx = {"slice1": [0, 2], "slice2": [5, 7], "slice3": [10, 12, 14], "slice4": [17, 19, 21], "slice5": [24, 26, 28]}
+    expect = ["scaling_layer.shift", "scaling_layer.scale"]
+    for s, ids in idx.items():
+        for i in ids:
+            expect += ["net.%s.%d.weight" % (s, i), "net.%s.%d.bias" % (s, i)]
+    expect += ["lin%d.model.1.weight" % k for k in range(5)]
+    assert list(mod.keys()) == expect
+    assert tuple(mod["net.slice1.0.weight"].shape) == (64, 3, 3, 3) and tuple(mod["lin4.model.1.weight"].shape) == (1, 512, 1, 1)
+    assert not any(p.requires_grad for p in LPIPS().parameters())  # frozen, as LPIPS.__init__ leaves it
+
+
+def test_pose_loss_perceptual_switch_controls_the_lpips_submodule():
+    """perceptual_weight = 0 (bench config): no LPIPS parameters in the state_dict (the golden key list); > 0: the
+    reference's `loss.perceptual_loss.*` keys appear (LD contperceptual.py:17)."""
+    import helpers as H
+    from odvae_b200 import synth
+    from odvae_b200.autoencoder import PoseAutoencoder
+    params = synth.model_config(synth.DDCONFIG_SMALL, H.stats_path(23))
+    assert not any(k.startswith("loss.perceptual_loss.") for k in PoseAutoencoder(**params).state_dict())
+    params["lossconfig"]["params"]["perceptual_weight"] = 1.0
+    keys = [k for k in PoseAutoencoder(**params).state_dict() if k.startswith("loss.perceptual_loss.")]
+    assert len(keys) == 33 and "loss.perceptual_loss.net.slice5.28.bias" in keys

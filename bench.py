@@ -458,11 +458,14 @@ def run_ours(args):
             dist.barrier()
         torch.cuda.synchronize()
 
+    host_ms = [0.0]
+
     def timed(batch_src, steps, read_loss):
         barrier()
         e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
         e0.record()
         last = None
+        t_host0 = time.perf_counter()
         for i in range(steps):
             if batch_src is pinned:
                 b = {k: (v.to(dev, non_blocking=True) if torch.is_tensor(v) else list(v)) for k, v in pinned.items()}
@@ -472,6 +475,7 @@ def run_ours(args):
             if read_loss:
                 last = float(loss)  # device -> host read of the step's result
         e1.record()
+        host_ms[0] = (time.perf_counter() - t_host0) * 1e3 / steps  # host time to ENQUEUE a step (no sync inside)
         barrier()
         ms = e0.elapsed_time(e1)
         if world > 1:
@@ -494,6 +498,7 @@ def run_ours(args):
     if rank == 0:
         sampler.start()
     ms, _ = timed(resident, args.steps, False)
+    host_enqueue_ms = host_ms[0]
     launches = lib.call("launch_count") - launches0
     ms_e2e, last_loss = timed(pinned, args.steps, True)
     clocks = sampler.stop() if rank == 0 else None
@@ -552,7 +557,8 @@ def run_ours(args):
                            "l2": "per-step working set (activations ~40 GB at batch 64) far exceeds the 126 MB L2"},
                 "e2e": {"value": n_img / (ms_e2e * 1e-3), "unit": "images/sec", "h2d_bytes_per_step": h2d,
                         "d2h_bytes_per_step": 4, "ms_per_step": ms_e2e / args.steps, "last_loss": last_loss},
-                "gpu_launches": int(launches), "clocks": clocks, "roofline": roof, "cpu_baseline": cpu,
+                "gpu_launches": int(launches), "host_enqueue_ms_per_step": host_enqueue_ms,
+                "clocks": clocks, "roofline": roof, "cpu_baseline": cpu,
                 "pct_of_tensor_roofline_whole_step": flops_img * B / (ms / args.steps * 1e-3) / 1e12 /
                 peaks()[0]["bf16_tflops_sustained"]}
         print(json.dumps(line), flush=True)

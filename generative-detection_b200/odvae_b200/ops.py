@@ -17,7 +17,7 @@ import weakref
 import torch
 
 from . import lib
-from .lib import BF16, CONV_1x1, CONV_3x3_S1, CONV_3x3_S2, F16, F32, IMPL_SIMT, IMPL_TC, call
+from .lib import BF16, CONV_1x1, CONV_3x3_S1, CONV_3x3_S2, F16, F32, IMPL_SIMT, IMPL_TC, call, stream_handle
 
 GROUPS = 32      # Normalize(): GroupNorm(num_groups=32, eps=1e-6)  LD model.py:38-39
 GN_EPS = 1e-6
@@ -120,7 +120,7 @@ _WS = {}
 
 def workspace(nbytes, device, tag):
     """Grow-only scratch per (device, stream, tag); never part of a state_dict."""
-    key = (device.index, torch.cuda.current_stream(device).cuda_stream, tag)
+    key = (device.index, stream_handle(device.index), tag)
     buf = _WS.get(key)
     if buf is None or buf.numel() < nbytes:
         buf = torch.empty(max(int(nbytes), 1 << 16), dtype=torch.uint8, device=device)

@@ -5,6 +5,16 @@
 namespace odvae {
 
 enum { KIND_GEMM = 0, KIND_CONV = 1, KIND_WGRAD = 2 };
+// instances of tc_engine_kernel<SPEC>: (kind, operand roles, epilogue) fixed at compile time
+enum {
+  TC_SPEC_CONV = 0,          // KIND_CONV, pixels on M
+  TC_SPEC_CONV_SWAP = 1,     // KIND_CONV, channels on M / pixels on N (halo slabs, GroupNorm statistics, staged residual)
+  TC_SPEC_WGRAD = 2,         // KIND_WGRAD
+  TC_SPEC_GEMM = 3,          // KIND_GEMM, EPI_NONE
+  TC_SPEC_GEMM_SOFTMAX = 4,  // KIND_GEMM, EPI_ROWSTATS / EPI_SOFTMAX
+  TC_SPEC_GEMM_DSOFTMAX = 5, // KIND_GEMM, EPI_DSOFTMAX
+  TC_NUM_SPECS = 6
+};
 enum { OUT_BF16 = 0, OUT_F32 = 1, OUT_NCHW_F32 = 2, OUT_F16 = 3 };
 enum { FMT_F16 = 0, FMT_BF16 = 1 };
 // fused attention epilogues of KIND_GEMM (see tc_engine.cuh): row statistics / softmax / softmax backward

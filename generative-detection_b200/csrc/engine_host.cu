@@ -11,6 +11,15 @@
 #include "simt_engine.cuh"
 #include "tc_engine.cuh"
 
+namespace odvae {  // tc_engine_inst<N>.cu
+#define ODVAE_DECL_TC_LAUNCH(N)                                                                    \
+  cudaError_t tc_engine_launch_##N(int grid, size_t smem, cudaStream_t st, const CUtensorMap& tmA, \
+                                   const CUtensorMap& tmB, const TcParams& p);
+ODVAE_DECL_TC_LAUNCH(0) ODVAE_DECL_TC_LAUNCH(1) ODVAE_DECL_TC_LAUNCH(2)
+ODVAE_DECL_TC_LAUNCH(3) ODVAE_DECL_TC_LAUNCH(4) ODVAE_DECL_TC_LAUNCH(5)
+#undef ODVAE_DECL_TC_LAUNCH
+}  // namespace odvae
+
 namespace odvae {
 
 // ---------------------------------------------------------------------------------------------
@@ -148,20 +157,28 @@ static int launch_tc(EngineDesc& d, cudaStream_t stream) {
       }
     }
   }
-  static std::once_flag once;
-  static cudaError_t attr_err = cudaSuccess;
-  std::call_once(once, [] {
-    attr_err = cudaFuncSetAttribute(tc_engine_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, 227 * 1024);
-  });
-  if (attr_err != cudaSuccess) {
-    set_last_cuda_error(attr_err, "cudaFuncSetAttribute(tc_engine_kernel)");
-    return ODVAE_ERR_CUDA;
-  }
   const long long total = static_cast<long long>(p.num_m_tiles) * p.num_n_tiles * p.num_z;
   if (total <= 0 || p.num_k_iters <= 0) return ODVAE_ERR_SHAPE;
   int grid = num_sms();
   if (total < grid) grid = static_cast<int>(total);
-  tc_engine_kernel<<<grid, TC_THREADS, smem, stream>>>(tmA, tmB, p);
+  // the instance of tc_engine_kernel<SPEC> compiled for this (kind, operand roles, epilogue)
+  int spec;
+  if (p.kind == KIND_CONV) {
+    spec = p.swap ? TC_SPEC_CONV_SWAP : TC_SPEC_CONV;
+  } else if (p.kind == KIND_WGRAD) {
+    spec = TC_SPEC_WGRAD;
+  } else {
+    spec = p.epi == EPI_NONE ? TC_SPEC_GEMM : (p.epi == EPI_DSOFTMAX ? TC_SPEC_GEMM_DSOFTMAX : TC_SPEC_GEMM_SOFTMAX);
+  }
+  if (p.kind != KIND_GEMM && (p.epi != EPI_NONE || (p.swap && p.kind != KIND_CONV))) return ODVAE_ERR_SHAPE;
+  typedef cudaError_t (*LaunchFn)(int, size_t, cudaStream_t, const CUtensorMap&, const CUtensorMap&, const TcParams&);
+  static const LaunchFn launchers[TC_NUM_SPECS] = {tc_engine_launch_0, tc_engine_launch_1, tc_engine_launch_2,
+                                                   tc_engine_launch_3, tc_engine_launch_4, tc_engine_launch_5};
+  const cudaError_t attr_err = launchers[spec](grid, smem, stream, tmA, tmB, p);
+  if (attr_err != cudaSuccess) {
+    set_last_cuda_error(attr_err, "cudaFuncSetAttribute(tc_engine_kernel)");
+    return ODVAE_ERR_CUDA;
+  }
   return check_launch("tc_engine_kernel");
 }
 

@@ -41,17 +41,17 @@ __device__ __forceinline__ void decode_pixel_box(const TcParams& p, int pb, int&
   y0 = ty * (TC_BLOCK_M >> p.bw_log2);
 }
 
-__device__ __forceinline__ TileCoord decode_tile(const TcParams& p, int t) {
+__device__ __forceinline__ TileCoord decode_tile(const TcParams& p, const int kind, const bool swap, int t) {
   TileCoord c;
   c.n_tile = t % p.num_n_tiles;
   int r = t / p.num_n_tiles;
   c.m_tile = r % p.num_m_tiles;
   c.z = r / p.num_m_tiles;
   c.b = c.y0 = c.x0 = c.tap = c.split = 0;
-  if (p.kind == KIND_CONV) {
+  if (kind == KIND_CONV) {
     // swapped roles: the N tile is a pair of pixel boxes (2*n_tile, 2*n_tile + 1); (b, y0, x0) = the first one
-    decode_pixel_box(p, p.swap ? 2 * c.n_tile : c.m_tile, c.b, c.y0, c.x0);
-  } else if (p.kind == KIND_WGRAD) {
+    decode_pixel_box(p, swap ? 2 * c.n_tile : c.m_tile, c.b, c.y0, c.x0);
+  } else if (kind == KIND_WGRAD) {
     const int grp = c.z / p.split_k;
     c.split = c.z - grp * p.split_k;
     c.tap = grp * p.wg_T;  // first tap of this tile's tap group
@@ -60,8 +60,8 @@ __device__ __forceinline__ TileCoord decode_tile(const TcParams& p, int t) {
 }
 
 // k-iterations of one tile: WGRAD splits its pixel chunks unevenly (the last split takes the remainder)
-__device__ __forceinline__ int tile_k_iters(const TcParams& p, const TileCoord& c) {
-  if (p.kind != KIND_WGRAD) return p.num_k_iters;
+__device__ __forceinline__ int tile_k_iters(const TcParams& p, const int kind, const TileCoord& c) {
+  if (kind != KIND_WGRAD) return p.num_k_iters;
   const int rem = p.kch_total - c.split * p.kch_per_split;
   return rem < p.kch_per_split ? rem : p.kch_per_split;
 }
@@ -74,17 +74,25 @@ __device__ __forceinline__ void spatial_load(void* dst, const CUtensorMap* tm, u
     tma_load_4d(dst, tm, bar, c, x, y, b);
 }
 
+// SPEC: TC_SPEC_* (engine_desc.h). One instance per .cu file (tc_engine_inst*.cu) so they compile in parallel.
+template <int SPEC>
 __global__ void __launch_bounds__(TC_THREADS, 1)
 tc_engine_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUtensorMap tmB,
                  const __grid_constant__ TcParams p) {
+  // The operation kind, the operand roles and the epilogue are compile-time constants of each instance: every mode gets
+  // its own register allocation (the monolithic kernel spilled at the 168-register cap of a 320-thread CTA).
+  constexpr int kKind = SPEC <= TC_SPEC_CONV_SWAP ? KIND_CONV : (SPEC == TC_SPEC_WGRAD ? KIND_WGRAD : KIND_GEMM);
+  constexpr bool kSwap = SPEC == TC_SPEC_CONV_SWAP;
+  const int epi = SPEC <= TC_SPEC_GEMM ? static_cast<int>(EPI_NONE)
+                                       : (SPEC == TC_SPEC_GEMM_DSOFTMAX ? static_cast<int>(EPI_DSOFTMAX) : p.epi);
   extern __shared__ __align__(1024) uint8_t smem_raw[];
   // manual 1024-byte alignment (SWIZZLE_128B atoms)
   uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~uintptr_t(1023));
   const int stages = p.stages;
   const int BN = p.BN;
-  const int wgT = p.kind == KIND_WGRAD ? p.wg_T : 1;
+  const int wgT = kKind == KIND_WGRAD ? p.wg_T : 1;
   // WGRAD halo mode: per 64-channel chunk ONE slab of 64 + 2 pixels (TC_WSLAB_BYTES) serves the 3 taps of a filter row
-  const bool wg_halo = p.kind == KIND_WGRAD && p.halo;
+  const bool wg_halo = kKind == KIND_WGRAD && p.halo;
   const uint32_t b_bytes = wg_halo ? static_cast<uint32_t>(BN >> 6) * TC_WSLAB_BYTES
                                    : static_cast<uint32_t>(BN) * 128u * static_cast<uint32_t>(wgT);  // per stage
   const int acc_cols = BN * wgT;                      // TMEM columns of one accumulator
@@ -93,7 +101,7 @@ tc_engine_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant_
   uint8_t* sB = smem + static_cast<size_t>(stages) * TC_A_BYTES;
   // halo mode: sA = weight stages, sB = ring of input-row slabs
   const uint32_t wslab_tx = static_cast<uint32_t>(((1 << p.kbw_log2) + 2) * (TC_BLOCK_K >> p.kbw_log2)) * 128u;
-  const bool cv_halo = p.kind == KIND_CONV && p.halo;
+  const bool cv_halo = kKind == KIND_CONV && p.halo;
   const int nslabs = cv_halo ? p.halo_slabs : 0;
   uint64_t* bars = reinterpret_cast<uint64_t*>(
       sB + (cv_halo ? static_cast<size_t>(nslabs) * TC_SLAB_BYTES : static_cast<size_t>(stages) * b_bytes));
@@ -146,7 +154,7 @@ tc_engine_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant_
       int ws = 0, ss = 0;
       uint32_t wph = 0, sph = 0;
       for (int t = blockIdx.x; t < total_tiles; t += gridDim.x) {
-        const TileCoord tc = decode_tile(p, t);
+        const TileCoord tc = decode_tile(p, kKind, kSwap, t);
         const int m0 = tc.m_tile * TC_BLOCK_M;
         for (int cc = 0; cc < p.cchunks; ++cc) {
           for (int ry = 0; ry < 3; ++ry) {
@@ -177,17 +185,17 @@ tc_engine_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant_
       int stage = 0;
       uint32_t phase = 0;
       for (int t = blockIdx.x; t < total_tiles; t += gridDim.x) {
-        const TileCoord tc = decode_tile(p, t);
+        const TileCoord tc = decode_tile(p, kKind, kSwap, t);
         const int m0 = tc.m_tile * TC_BLOCK_M;
         const int n0 = tc.n_tile * BN;
-        const int nk = tile_k_iters(p, tc);
+        const int nk = tile_k_iters(p, kKind, tc);
         for (int kit = 0; kit < nk; ++kit) {
           mbar_wait(&empty_bar[stage], phase ^ 1u);
           uint64_t* fb = &full_bar[stage];
           mbar_arrive_expect_tx(fb, wg_halo ? TC_A_BYTES + static_cast<uint32_t>(BN >> 6) * wslab_tx : TC_A_BYTES + b_bytes);
           uint8_t* a_dst = sA + static_cast<size_t>(stage) * TC_A_BYTES;
           uint8_t* b_dst = sB + static_cast<size_t>(stage) * b_bytes;
-          if (p.kind == KIND_GEMM) {
+          if (kKind == KIND_GEMM) {
             const int k0 = kit * TC_BLOCK_K;
             if (!p.a_mn) {
               tma_load_3d(a_dst, &tmA, fb, k0, m0, tc.z);
@@ -200,10 +208,10 @@ tc_engine_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant_
             } else {
               for (int j = 0; j < (BN >> 6); ++j) tma_load_3d(b_dst + j * 8192, &tmB, fb, n0 + 64 * j, k0, tc.z);
             }
-          } else if (p.kind == KIND_CONV) {
+          } else if (kKind == KIND_CONV) {
             const int tap = kit / p.cchunks;
             const int cc = kit - tap * p.cchunks;
-            if (!p.swap) {
+            if (!kSwap) {
               spatial_load(a_dst, &tmA, fb, p.sp_rank, cc * 64 + p.tap_c[tap], tc.x0 + p.tap_dx[tap], p.tap_ph[tap],
                            tc.y0 + p.tap_dy[tap], tc.b);
               tma_load_2d(b_dst, &tmB, fb, kit * TC_BLOCK_K, n0);
@@ -305,8 +313,8 @@ tc_engine_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant_
         mbar_wait(&tempty_bar[acc], acc_phase ^ 1u);
         tc_fence_after();
         const uint32_t d_tmem = tmem_base + static_cast<uint32_t>(acc * acc_cols);
-        const TileCoord tcm = decode_tile(p, t);
-        const int nk = tile_k_iters(p, tcm);
+        const TileCoord tcm = decode_tile(p, kKind, kSwap, t);
+        const int nk = tile_k_iters(p, kKind, tcm);
         for (int kit = 0; kit < nk; ++kit) {
           mbar_wait(&full_bar[stage], phase);
           tc_fence_after();
@@ -366,14 +374,14 @@ tc_engine_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant_
     int cs_stage = 0;
     uint32_t cs_phase = 0;
     for (int t = blockIdx.x; t < total_tiles; t += gridDim.x) {
-      const TileCoord tc = decode_tile(p, t);
+      const TileCoord tc = decode_tile(p, kKind, kSwap, t);
       const int m0 = tc.m_tile * TC_BLOCK_M;
       const int n0 = tc.n_tile * BN;
 
-      if (p.kind == KIND_WGRAD && p.colsum != nullptr) {
+      if (kKind == KIND_WGRAD && p.colsum != nullptr) {
         // ---- fused bias gradient: column sums of the dy tiles (A operand, MN-major SW128: pixel row k at k * 128 B,
         // 16-byte chunk (channel / 8) XOR (k % 8)); thread = (channel, pixel half), fixed summation order ----
-        const int nk = tile_k_iters(p, tc);
+        const int nk = tile_k_iters(p, kKind, tc);
         const int ngroups = p.ntaps / wgT;
         const int grp = tc.tap / wgT;
         const int ew = warp - 2;
@@ -406,10 +414,10 @@ tc_engine_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant_
       bool row_ok = true;
       long long row_off = 0;  // element offset of (row, column n0) in D / residual
       int yy = 0, xx = 0;
-      if (p.kind == KIND_GEMM) {
+      if (kKind == KIND_GEMM) {
         row_ok = (m0 + r) < p.m_valid;
         row_off = static_cast<long long>(tc.z) * p.strideD + static_cast<long long>(m0 + r) * p.ldd + n0;
-      } else if (p.kind == KIND_CONV) {
+      } else if (kKind == KIND_CONV) {
         yy = tc.y0 + (r >> p.bw_log2);
         xx = tc.x0 + (r & ((1 << p.bw_log2) - 1));
         row_off = static_cast<long long>(tc.b) * p.oB + static_cast<long long>(yy) * p.oY +
@@ -422,7 +430,7 @@ tc_engine_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant_
       const long long row_off0 = row_off;
       const long long tap_stride = static_cast<long long>(p.split_k) * p.m_valid * p.ldd;  // WGRAD: next tap's slab
 
-      if (p.kind == KIND_CONV && p.swap) {
+      if (kKind == KIND_CONV && kSwap) {
         // ---- swapped-role conv: lane = output channel, column = output pixel. This warp owns the 128 pixels of
         // pixel box (2 * n_tile + half); for every pixel the 32 lanes write 32 consecutive channels (one 64-byte
         // segment), and bias / per-channel work is a per-thread scalar.
@@ -560,7 +568,7 @@ tc_engine_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant_
           float2* dst = reinterpret_cast<float2*>(p.gn_part) + (static_cast<long long>(pb_b) * boxes + box) * p.n_valid + n;
           *dst = make_float2(gs0 + gs1, gq0 + gq1);
         }
-      } else if (p.epi != EPI_NONE) {
+      } else if (epi != EPI_NONE) {
         // ---- fused attention epilogues (KIND_GEMM; one accumulator row and <= 128 columns per thread) ----
         // Global reads this tile needs (softmax partials / delta / the P tile) are issued BEFORE waiting for the
         // accumulator, so their latency hides behind the tile's MMAs; TMEM is drained 32 columns at a time with the
@@ -569,10 +577,10 @@ tc_engine_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant_
         const bool halfp = p.out_mode == OUT_F16;
         float mx = -INFINITY, l = 0.0f, lse2 = 0.0f, delta = 0.0f;  // mx: running max of the RAW accumulators
         uint32_t pp[8][8];  // DSOFTMAX: this thread's 128 P values (8 x 32 bytes)
-        if (p.epi == EPI_SOFTMAX && row_ok) {
+        if (epi == EPI_SOFTMAX && row_ok) {
           // lse2[row] = max + log2(sum 2^(s2*s - max)), combined from the row partials by attn_stats_combine_kernel
           lse2 = __ldg(p.aux_f32 + static_cast<long long>(tc.z) * p.m_valid + (m0 + r));
-        } else if (p.epi == EPI_DSOFTMAX && row_ok) {
+        } else if (epi == EPI_DSOFTMAX && row_ok) {
           delta = __ldg(p.aux_f32 + static_cast<long long>(tc.z) * p.m_valid + (m0 + r));
           const uint16_t* psrc = reinterpret_cast<const uint16_t*>(p.aux16) + row_off + c_begin;
 #pragma unroll
@@ -582,7 +590,7 @@ tc_engine_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant_
         tc_fence_after();
 
         auto process = [&](uint32_t (&v)[32], int cc) {
-          if (p.epi == EPI_ROWSTATS) {
+          if (epi == EPI_ROWSTATS) {
             // online (max, sum 2^(s2*(v - max))) on raw accumulators: s2 > 0, so the max commutes with the scale
             float cm = __uint_as_float(v[0]);
 #pragma unroll
@@ -613,7 +621,7 @@ tc_engine_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant_
           }
         };
         // every epilogue warp owns exactly 128 accumulator columns here (BN = 256; the host checks N % 256 == 0)
-        if (p.epi == EPI_DSOFTMAX) {
+        if (epi == EPI_DSOFTMAX) {
           // dS = P * (dP - delta) * alpha: 8 chunks of 16 columns, the next tcgen05.ld in flight during each chunk
           uint32_t da[16], db[16];
           tmem_ld_x16(t_row + static_cast<uint32_t>(c_begin), da);
@@ -650,7 +658,7 @@ tc_engine_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant_
           tmem_ld_wait();
           process(vb, c_begin + 96);
         }
-        if (p.epi == EPI_ROWSTATS && row_ok) {
+        if (epi == EPI_ROWSTATS && row_ok) {
           float2* dst = reinterpret_cast<float2*>(p.aux_out) +
                         (static_cast<long long>(tc.z) * p.num_n_tiles * nhalf + tc.n_tile * nhalf + half) * p.m_valid +
                         (m0 + r);

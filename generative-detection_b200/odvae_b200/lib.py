@@ -12,7 +12,8 @@ import torch
 _HERE = os.path.dirname(os.path.abspath(__file__))
 REPO_ROOT = os.path.dirname(os.path.dirname(_HERE))
 HEADER = os.path.join(REPO_ROOT, "include", "odvae_b200.h")
-LIB_PATH = os.path.join(_HERE, "libodvae_b200.so")
+# ODVAE_LIB_PATH: A/B runs of two builds of the same C ABI on one box (tools/gpu_ab_lib.sh)
+LIB_PATH = os.environ.get("ODVAE_LIB_PATH") or os.path.join(_HERE, "libodvae_b200.so")
 
 F32, BF16, F16 = 0, 1, 2
 CONV_3x3_S1, CONV_1x1, CONV_3x3_S2 = 0, 1, 2

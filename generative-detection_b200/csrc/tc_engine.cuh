@@ -84,7 +84,8 @@ tc_engine_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant_
   constexpr int kKind = SPEC <= TC_SPEC_CONV_SWAP ? KIND_CONV : (SPEC == TC_SPEC_WGRAD ? KIND_WGRAD : KIND_GEMM);
   constexpr bool kSwap = SPEC == TC_SPEC_CONV_SWAP;
   const int epi = SPEC <= TC_SPEC_GEMM ? static_cast<int>(EPI_NONE)
-                                       : (SPEC == TC_SPEC_GEMM_DSOFTMAX ? static_cast<int>(EPI_DSOFTMAX) : p.epi);
+                  : SPEC == TC_SPEC_GEMM_DSOFTMAX ? static_cast<int>(EPI_DSOFTMAX)
+                  : (p.epi == EPI_ROWSTATS ? static_cast<int>(EPI_ROWSTATS) : static_cast<int>(EPI_SOFTMAX));
   extern __shared__ __align__(1024) uint8_t smem_raw[];
   // manual 1024-byte alignment (SWIZZLE_128B atoms)
   uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~uintptr_t(1023));

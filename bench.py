@@ -526,10 +526,10 @@ def run_ours(args):
                 "achieved": achieved, "peak": peak, "unit": "TFLOP/s", "frac": achieved / peak,
                 "peak_source": how + " (bf16_tflops_sustained: kernel timed inside a long step)",
                 # DRAM bytes per launch of tc_engine_kernel, averaged over the 333 engine launches of one step:
-                # ncu dram__bytes_read.sum + dram__bytes_write.sum = 166.12 GB + 62.60 GB (profiles/r01_launches_s15.txt);
+                # ncu dram__bytes_read.sum + dram__bytes_write.sum = 165.63 GB + 62.19 GB (profiles/r01_launches_s16.txt, six instances);
                 # the dominant shape alone (128->128 3x3 at 256x256): 2.108 GB per launch against 2.147 GB algorithmic
                 # (x in + y out, batch 64) in the `ncu --set full` capture profiles/r01_conv_full_raw.csv
-                "traffic": 228.72e9 / 333, "traffic_unit": "bytes per launch (step average)",
+                "traffic": 227.82e9 / 333, "traffic_unit": "bytes per launch (step average)",
                 "engine_ms_per_step": eng_ms, "engine_calls_per_step": ncalls,
                 "engine_share_of_step": eng_ms / (ms / args.steps),
                 "algorithmic_flops_per_step": flops_img * B, "counted_padded_flops_per_step": counted,

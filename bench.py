@@ -199,7 +199,7 @@ def run_reference(args):
 class EngineProfiler:
     """Wraps ops.call for ONE extra (untimed) step: brackets each conv/GEMM C-ABI call with CUDA events on the
     launching stream and adds up the algorithmic FLOPs (2*M*N*K of the real, unpadded problem)."""
-    NAMES = {"conv2d_fwd", "conv2d_fwd_gnstats", "conv2d_dgrad", "conv2d_wgrad", "gemm_bf16", "attn_scores_softmax",
+    NAMES = {"conv2d_fwd", "conv2d_fwd_gnstats", "conv2d_dgrad", "conv2d_wgrad", "gemm_bf16", "gemm_16", "attn_scores_softmax",
              "attn_dsoftmax"}
     # memory-bound GroupNorm(+SiLU) calls, judged against the HBM roofline (SURVEY 8d): algorithmic bytes at 2 B per
     # element are 2*E forward (stats + apply together: read x once, write y once) and 3*E backward (x, dy -> dx)
@@ -218,7 +218,7 @@ class EngineProfiler:
         return 3.0 * a[9] * a[10] * a[11] * 2
 
     def flops(self, name, a):
-        if name == "gemm_bf16":
+        if name in ("gemm_bf16", "gemm_16"):
             M, N, K, batch = a[3], a[4], a[5], a[6]
             return 2.0 * M * N * K * batch
         if name == "attn_scores_softmax":  # algorithmic: ONE q k^T (the second pass is a recompute, not counted)
@@ -243,7 +243,7 @@ class EngineProfiler:
 
     @staticmethod
     def shape_key(name, a):
-        if name == "gemm_bf16":
+        if name in ("gemm_bf16", "gemm_16"):
             return "gemm M%d N%d K%d b%d a_mn%d b_mn%d" % (a[3], a[4], a[5], a[6], a[13], a[14])
         if name == "attn_scores_softmax":
             return "attn qk^T+softmax (2 passes) B%d N%d C%d" % (a[3], a[4], a[5])

@@ -93,7 +93,7 @@ size_t odvae_conv2d_wgrad_workspace_bytes(int B, int H, int W, int CinP, int Cou
 }
 
 int odvae_conv2d_wgrad(const void* x, const void* dy, float* dw_oihw, float* db, int B, int H, int W, int CinP,
-                       int CoutP, int Cin, int Cout, int geom, int act_dtype, int impl, int accumulate,
+                       int CoutP, int Cin, int Cout, int geom, int act_dtype, int impl, int accumulate, float out_scale,
                        void* workspace, size_t ws_bytes, void* stream) {
   cudaStream_t s = static_cast<cudaStream_t>(stream);
   EngineDesc d;
@@ -116,11 +116,11 @@ int odvae_conv2d_wgrad(const void* x, const void* dy, float* dw_oihw, float* db,
   if (st != ODVAE_OK) return st;
   // split-K partials -> dw, and (fused_db) the partial column sums of dy -> db, in ONE launch
   st = launch_wgrad_reduce(ws, dw_oihw, Cout, Cin, d.p.ntaps, CoutP, CinP, d.p.split_k, accumulate, s,
-                           fused_db ? cpart : nullptr, fused_db ? cs_rows : 0, db);
+                           fused_db ? cpart : nullptr, fused_db ? cs_rows : 0, db, out_scale);
   if (st != ODVAE_OK || fused_db) return st;
   if (db != nullptr) {
     const int Ho = geom == ODVAE_CONV_3x3_S2 ? H / 2 : H, Wo = geom == ODVAE_CONV_3x3_S2 ? W / 2 : W;
-    st = launch_colsum(dy, static_cast<long long>(B) * Ho * Wo, Cout, CoutP, act_dtype, db, accumulate, cpart, s);
+    st = launch_colsum(dy, static_cast<long long>(B) * Ho * Wo, Cout, CoutP, act_dtype, db, accumulate, cpart, s, out_scale);
   }
   return st;
 }

@@ -24,9 +24,9 @@ int launch_attn_stats_combine(const float* part, float* lse2, int B, int slots, 
 // layout.cu
 int launch_wgrad_reduce(const float* ws, float* dw, int Cout, int Cin, int taps, int CoutP, int CinP, int split_k,
                         int accumulate, cudaStream_t st, const float* cpart = nullptr, int cs_rows = 0,
-                        float* db = nullptr);
+                        float* db = nullptr, float scale = 1.0f);
 size_t colsum_workspace_bytes(int cols);
 int launch_colsum_final(const float* part, int nrows, int cols, float* out, int accumulate, cudaStream_t st);
 int launch_colsum(const void* m, long long rows, int cols, int ld, int act_dtype, float* out, int accumulate,
-                  float* part, cudaStream_t st);
+                  float* part, cudaStream_t st, float scale = 1.0f);
 }  // namespace odvae

@@ -289,7 +289,7 @@ __global__ void gn_bwd_finalize_a_kernel(const float* __restrict__ part, const f
 
 // backward finalize B: dgamma[c] = sum_b AB[b][c][1], dbeta[c] = sum_b AB[b][c][0]
 __global__ void gn_bwd_finalize_b_kernel(const float* __restrict__ AB, float* __restrict__ dgamma,
-                                         float* __restrict__ dbeta, int B, int C, int accumulate) {
+                                         float* __restrict__ dbeta, int B, int C, int accumulate, float scale) {
   const int c = blockIdx.x * blockDim.x + threadIdx.x;
   if (c >= C) return;
   float a = 0.0f, bb = 0.0f;
@@ -297,6 +297,8 @@ __global__ void gn_bwd_finalize_b_kernel(const float* __restrict__ AB, float* __
     a += AB[(static_cast<long long>(b) * C + c) * 2];
     bb += AB[(static_cast<long long>(b) * C + c) * 2 + 1];
   }
+  a *= scale;
+  bb *= scale;
   dbeta[c] = accumulate ? dbeta[c] + a : a;
   dgamma[c] = accumulate ? dgamma[c] + bb : bb;
 }
@@ -365,338 +367,6 @@ gn_bwd_apply_kernel(const T* __restrict__ x, const TG* __restrict__ dy, const TG
   }
 }
 
-// ------------------------------------------------------------------------------------------------------------------
-// Backward in ONE cooperative launch with L2 reuse ("team" path).
-// The two-kernel path reads x and dy twice from HBM (reduce, then apply): 5 E s bytes against the algorithmic 3 E s.
-// Here the resident grid is split into `nteams` teams (one CTA of every team per SM). A team walks over items of `ipg`
-// consecutive images sized to a fraction of the L2 (~32 MB of x + dy): phase 1 reduces the item's pixel ranges
-// (copies tagged L2::evict_last), a team barrier, a few duty CTAs combine the partials per (image, group) in a fixed
-// order, a second barrier, then phase 2 re-reads the SAME pixel range newest-first out of L2 (copies/stores tagged
-// evict_first) and writes dx. ncu: 2.23 GB read + 1.04 GB written per launch at 128 ch x 256^2 x 64 images, against
-// 4.30 + 1.04 GB for the two-kernel path.
-// Every CTA's pixel range is one contiguous byte range of the NHWC tensor, so the data moves with 1-D bulk async copies
-// (cp.async.bulk, 8 KB per tensor and chunk) through a 4-stage shared-memory ring with mbarrier completion. The ring
-// runs ahead across the phase boundary: the first chunks of phase 2 are already in flight while the team waits for the
-// coefficients, and the next item's phase 1 starts while phase 2 drains - the barriers hide behind the copies.
-// Barriers are monotonically increasing arrival counters in the workspace (zeroed by a memset before the launch);
-// all sums are fixed-order (deterministic).
-// ------------------------------------------------------------------------------------------------------------------
-static constexpr int GT_CHUNK_BYTES = 8192;  // per tensor and chunk: 512 16-byte vectors = 2 per thread
-static constexpr int GT_MAX_STAGES = 4;  // the host picks the deepest ring that still fits two CTAs per SM
-
-__device__ __forceinline__ uint64_t l2_policy_evict_last() {
-  uint64_t p;
-  asm volatile("createpolicy.fractional.L2::evict_last.b64 %0, 1.0;" : "=l"(p));
-  return p;
-}
-__device__ __forceinline__ uint64_t l2_policy_evict_first() {
-  uint64_t p;
-  asm volatile("createpolicy.fractional.L2::evict_first.b64 %0, 1.0;" : "=l"(p));
-  return p;
-}
-// 1-D bulk async copy global -> shared, completion counted in bytes on an mbarrier
-__device__ __forceinline__ void bulk_load(void* dst_smem, const void* src, uint32_t bytes, uint64_t* bar, uint64_t pol,
-                                          bool hint) {
-  if (hint)
-    asm volatile(
-        "cp.async.bulk.shared::cluster.global.mbarrier::complete_tx::bytes.L2::cache_hint [%0], [%1], %2, [%3], %4;" ::"r"(
-            smem_u32(dst_smem)),
-        "l"(src), "r"(bytes), "r"(smem_u32(bar)), "l"(pol)
-        : "memory");
-  else
-    asm volatile("cp.async.bulk.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1], %2, [%3];" ::"r"(
-                     smem_u32(dst_smem)),
-                 "l"(src), "r"(bytes), "r"(smem_u32(bar))
-                 : "memory");
-}
-__device__ __forceinline__ void st16_hint(void* ptr, const uint4& v, uint64_t pol, bool hint) {
-  if (hint)
-    asm volatile("st.global.L2::cache_hint.v4.u32 [%0], {%1,%2,%3,%4}, %5;" ::"l"(ptr), "r"(v.x), "r"(v.y), "r"(v.z),
-                 "r"(v.w), "l"(pol)
-                 : "memory");
-  else
-    *reinterpret_cast<uint4*>(ptr) = v;
-}
-__device__ __forceinline__ unsigned ld_acquire_u32(const unsigned* p) {
-  unsigned v;
-  asm volatile("ld.acquire.gpu.global.u32 %0, [%1];" : "=r"(v) : "l"(p) : "memory");
-  return v;
-}
-// all threads of the CTA call; returns after the counter reached `target` (bounded: a protocol bug traps, never hangs)
-__device__ __forceinline__ void team_wait(const unsigned* ctr, unsigned target) {
-  if (threadIdx.x == 0) {
-    if (ld_acquire_u32(ctr) < target) {
-      const uint64_t t0 = globaltimer_ns();
-      uint32_t spins = 0;
-      while (ld_acquire_u32(ctr) < target) {
-        if ((++spins & 0xffu) == 0 && globaltimer_ns() - t0 > ODVAE_WAIT_TIMEOUT_NS) __trap();
-      }
-    }
-  }
-  __syncthreads();
-}
-__device__ __forceinline__ void team_arrive(unsigned* ctr) {
-  __syncthreads();
-  if (threadIdx.x == 0) {
-    __threadfence();
-    atomicAdd(ctr, 1u);
-  }
-}
-
-#ifdef ODVAE_GN_TEAM_TIMING
-__device__ unsigned long long gt_dbg[2 * 16 * 8];  // [cta slot][item][stamp]
-#define GT_STAMP(k)                                                                                   \
-  if (threadIdx.x == 0 && team == 0 && (j == 0 || j == 100) && (it / nteams) < 16)                     \
-    gt_dbg[((j == 0 ? 0 : 1) * 16 + it / nteams) * 8 + (k)] = globaltimer_ns();
-#else
-#define GT_STAMP(k)
-#endif
-// ctr layout: [team][2] = (A: CTAs that finished phase 1, B: (image, group) pairs finalized)
-template <typename T, typename TG>
-__global__ void __launch_bounds__(GN_THREADS, 2)
-gn_bwd_team_kernel(const T* __restrict__ x, const TG* __restrict__ dy, const TG* __restrict__ dx_add,
-                   const float* __restrict__ stats, const float* __restrict__ gamma, const float* __restrict__ beta,
-                   float* part, float* AB, float* coef, TG* __restrict__ dx, unsigned* ctr, int B, int HW, int C, int G,
-                   int silu, int ipg, int spi, int nteams, int hint, int GT_STAGES) {
-  static_assert(sizeof(T) == sizeof(TG), "x and dy chunks share one vector index");
-  constexpr int V = VecN<T>::V;
-  const int tsize = gridDim.x / nteams;
-  const int team = blockIdx.x / tsize;
-  if (team >= nteams) return;
-  const int j = blockIdx.x - team * tsize;
-  unsigned* ctrA = ctr + 2 * team;
-  unsigned* ctrB = ctrA + 1;
-  const int cpg = C / G;
-  const int cv = C / V;
-  const int rows = GN_THREADS / cv;
-  const int col = threadIdx.x % cv, row = threadIdx.x / cv;
-  const int c0 = col * V;
-  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
-  extern __shared__ __align__(128) unsigned char gt_smem[];
-  const int GT_STAGE_BYTES = (dx_add ? 3 : 2) * GT_CHUNK_BYTES;                      // x | dy [| dx_add]
-  unsigned char* ring = gt_smem;                                                     // [GT_STAGES][x | dy | add]
-  float* red = reinterpret_cast<float*>(gt_smem + GT_STAGES * GT_STAGE_BYTES);       // [2][rows][C]
-  uint64_t* full = reinterpret_cast<uint64_t*>(red + 2 * rows * C);                  // [GT_STAGES]
-  const unsigned NS = static_cast<unsigned>(GT_STAGES);
-  const bool use_hint = hint != 0;
-  const uint64_t pol_keep = l2_policy_evict_last();
-  const uint64_t pol_drop = l2_policy_evict_first();
-  const int nitems = (B + ipg - 1) / ipg;
-  const int img = j / spi, split = j - img * spi;
-  const int per = (HW + spi - 1) / spi;
-  const int p0 = split * per;
-  const int p1 = p0 + per < HW ? p0 + per : HW;
-  const int len = (img < ipg && p1 > p0) ? p1 - p0 : 0;
-  const int CH = GT_CHUNK_BYTES / (C * static_cast<int>(sizeof(T)));  // pixels per chunk
-  const int nch = (len + CH - 1) / CH;
-  const float inv_n = 1.0f / (static_cast<float>(cpg) * HW);
-
-  if (threadIdx.x == 0) {
-    for (int s = 0; s < GT_STAGES; ++s) mbar_init(full + s, 1);
-    fence_barrier_init();
-  }
-  __syncthreads();
-
-  // producer iterator (thread 0 only): item, phase, chunk, running sequence number
-  int p_it = team, p_phase = 0, p_i = 0;
-  unsigned p_n = 0;
-  auto produce_next = [&]() {
-    // skip items in which this CTA has no pixels (inactive image slot of a partial last item)
-    while (p_it < nitems) {
-      const int nimg_p = B - p_it * ipg < ipg ? B - p_it * ipg : ipg;
-      if (nch > 0 && img < nimg_p) break;
-      p_it += nteams;
-    }
-    if (p_it >= nitems) return;
-    const int c = p_phase == 0 ? p_i : nch - 1 - p_i;
-    const int px0 = p0 + c * CH;
-    const int npx = px0 + CH <= p1 ? CH : p1 - px0;
-    const uint32_t bytes = static_cast<uint32_t>(npx) * C * sizeof(T);
-    const long long off = (static_cast<long long>(p_it * ipg + img) * HW + px0) * C;
-    const int s = p_n % NS;
-    unsigned char* st = ring + s * GT_STAGE_BYTES;
-    const bool add = p_phase == 1 && dx_add != nullptr;
-    mbar_arrive_expect_tx(full + s, bytes * (add ? 3u : 2u));
-    const uint64_t pol = p_phase == 0 ? pol_keep : pol_drop;
-    bulk_load(st, x + off, bytes, full + s, pol, use_hint);
-    bulk_load(st + GT_CHUNK_BYTES, dy + off, bytes, full + s, pol, use_hint);
-    if (add) bulk_load(st + 2 * GT_CHUNK_BYTES, dx_add + off, bytes, full + s, pol_drop, use_hint);
-    ++p_n;
-    if (++p_i == nch) {
-      p_i = 0;
-      if (++p_phase == 2) {
-        p_phase = 0;
-        p_it += nteams;
-      }
-    }
-  };
-  // start the teams half a beat apart: team t begins once team t-1 has finished its first phase 1
-  if (team > 0) team_wait(ctr + 2 * (team - 1), static_cast<unsigned>(tsize));
-  if (threadIdx.x == 0) {
-    for (int s = 0; s < GT_STAGES; ++s) produce_next();
-  }
-
-  unsigned c_n = 0;  // consumer sequence number
-  unsigned targetA = 0, targetB = 0;
-  for (int it = team; it < nitems; it += nteams) {
-    const int b0 = it * ipg;
-    const int nimg = B - b0 < ipg ? B - b0 : ipg;
-    const int b = b0 + img;
-    const int my_nch = img < nimg ? nch : 0;
-    float mu[V], rs[V], sc[V], sh[V];
-    GT_STAMP(0)
-    // ---------------- phase 1: per-(image, split, channel) sums of (dy', dy' xhat) ----------------
-    if (img < nimg) {
-      float s0[V], s1[V];
-#pragma unroll
-      for (int q = 0; q < V; ++q) {
-        s0[q] = s1[q] = 0.0f;
-        const int c = c0 + q;
-        const int g = c / cpg;
-        mu[q] = __ldg(stats + (static_cast<long long>(b) * G + g) * 2);
-        rs[q] = __ldg(stats + (static_cast<long long>(b) * G + g) * 2 + 1);
-        sc[q] = rs[q] * __ldg(gamma + c);
-        sh[q] = __ldg(beta + c) - mu[q] * sc[q];
-      }
-      for (int i = 0; i < my_nch; ++i, ++c_n) {
-        const int s = c_n % NS;
-        mbar_wait(full + s, (c_n / NS) & 1);
-        const int px0 = p0 + i * CH;
-        const int nvec = (px0 + CH <= p1 ? CH : p1 - px0) * cv;
-        const uint4* sx = reinterpret_cast<const uint4*>(ring + s * GT_STAGE_BYTES);
-        const uint4* sd = sx + GT_CHUNK_BYTES / 16;
-#pragma unroll
-        for (int u = 0; u < GT_CHUNK_BYTES / 16 / GN_THREADS; ++u) {
-          const int v = threadIdx.x + u * GN_THREADS;
-          if (v < nvec) {
-            T xv[V];
-            TG dv[V];
-            *reinterpret_cast<uint4*>(xv) = sx[v];
-            *reinterpret_cast<uint4*>(dv) = sd[v];
-#pragma unroll
-            for (int q = 0; q < V; ++q) {
-              const float xf = to_f32<T>(xv[q]);
-              float d = to_f32<TG>(dv[q]);
-              if (silu) d *= silu_grad_t<sizeof(T) == 2>(fmaf(xf, sc[q], sh[q]));
-              s0[q] += d;
-              s1[q] = fmaf(d, (xf - mu[q]) * rs[q], s1[q]);
-            }
-          }
-        }
-        __syncthreads();  // stage s is free again
-        if (threadIdx.x == 0) produce_next();
-      }
-      GT_STAMP(1)
-      float* r0 = red;
-      float* r1 = red + rows * C;
-#pragma unroll
-      for (int q = 0; q < V; ++q) {
-        r0[row * C + c0 + q] = s0[q];
-        r1[row * C + c0 + q] = s1[q];
-      }
-      __syncthreads();
-      for (int c = threadIdx.x; c < C; c += GN_THREADS) {
-        float a = 0.0f, bb = 0.0f;
-        for (int r = 0; r < rows; ++r) {
-          a += r0[r * C + c];
-          bb += r1[r * C + c];
-        }
-        __stcg(reinterpret_cast<float2*>(part + ((static_cast<long long>(b) * spi + split) * C + c) * 2),
-               make_float2(a, bb));
-      }
-    }
-    GT_STAMP(2)
-    team_arrive(ctrA);
-    GT_STAMP(3)
-    targetA += static_cast<unsigned>(tsize);
-    // ---------------- duty: combine the partials of (image, group) pairs, fixed order ----------------
-    const int npairs = nimg * G;
-    if (j < npairs) {
-      team_wait(ctrA, targetA);
-      for (int pr = j; pr < npairs; pr += tsize) {
-        const int bi = b0 + pr / G, g = pr % G;
-        // (channel, value) combos of the group over the warps; lanes stride over the splits
-        for (int cb = warp; cb < cpg * 2; cb += GN_THREADS / 32) {
-          const int ci = cb >> 1, vi = cb & 1;
-          const int c = g * cpg + ci;
-          float sacc = 0.0f;
-          for (int sp = lane; sp < spi; sp += 32)
-            sacc += __ldcg(part + ((static_cast<long long>(bi) * spi + sp) * C + c) * 2 + vi);
-          sacc = warp_sum(sacc);
-          if (lane == 0) {
-            AB[(static_cast<long long>(bi) * C + c) * 2 + vi] = sacc;
-            red[cb] = __ldg(gamma + c) * sacc;
-          }
-        }
-        __syncthreads();
-        if (threadIdx.x == 0) {
-          float s1 = 0.0f, s2 = 0.0f;
-          for (int ci = 0; ci < cpg; ++ci) {
-            s1 += red[2 * ci];
-            s2 += red[2 * ci + 1];
-          }
-          const float mean = __ldg(stats + (static_cast<long long>(bi) * G + g) * 2);
-          const float rstd = __ldg(stats + (static_cast<long long>(bi) * G + g) * 2 + 1);
-          float2 cf;
-          cf.x = -rstd * rstd * s2 * inv_n;
-          cf.y = rstd * (mean * rstd * s2 - s1) * inv_n;
-          __stcg(reinterpret_cast<float2*>(coef + (static_cast<long long>(bi) * G + g) * 2), cf);
-        }
-        team_arrive(ctrB);
-      }
-    }
-    targetB += static_cast<unsigned>(npairs);
-    GT_STAMP(4)
-    team_wait(ctrB, targetB);
-    GT_STAMP(5)
-    // ---------------- phase 2: dx = c1 dy' + c2 x + c3 (+ dx_add), newest pixels first ----------------
-    if (my_nch > 0) {
-      float c2[V], c3[V];
-#pragma unroll
-      for (int q = 0; q < V; ++q) {
-        const int g = (c0 + q) / cpg;
-        const float2 cf = __ldcg(reinterpret_cast<const float2*>(coef + (static_cast<long long>(b) * G + g) * 2));
-        c2[q] = cf.x;
-        c3[q] = cf.y;
-      }
-      for (int i = 0; i < my_nch; ++i, ++c_n) {
-        const int s = c_n % NS;
-        mbar_wait(full + s, (c_n / NS) & 1);
-        const int px0 = p0 + (my_nch - 1 - i) * CH;
-        const int nvec = (px0 + CH <= p1 ? CH : p1 - px0) * cv;
-        const uint4* sx = reinterpret_cast<const uint4*>(ring + s * GT_STAGE_BYTES);
-        const uint4* sd = sx + GT_CHUNK_BYTES / 16;
-        const uint4* sa = sd + GT_CHUNK_BYTES / 16;
-        uint4* dxv = reinterpret_cast<uint4*>(dx + (static_cast<long long>(b) * HW + px0) * C);
-#pragma unroll
-        for (int u = 0; u < GT_CHUNK_BYTES / 16 / GN_THREADS; ++u) {
-          const int v = threadIdx.x + u * GN_THREADS;
-          if (v < nvec) {
-            T xv[V];
-            TG dv[V], av[V], ov[V];
-            *reinterpret_cast<uint4*>(xv) = sx[v];
-            *reinterpret_cast<uint4*>(dv) = sd[v];
-            if (dx_add) *reinterpret_cast<uint4*>(av) = sa[v];
-#pragma unroll
-            for (int q = 0; q < V; ++q) {
-              const float xf = to_f32<T>(xv[q]);
-              float d = to_f32<TG>(dv[q]);
-              if (silu) d *= silu_grad_t<sizeof(T) == 2>(fmaf(xf, sc[q], sh[q]));
-              float o = fmaf(sc[q], d, fmaf(c2[q], xf, c3[q]));
-              if (dx_add) o += to_f32<TG>(av[q]);
-              ov[q] = from_f32<TG>(o);
-            }
-            st16_hint(dxv + v, *reinterpret_cast<const uint4*>(ov), pol_drop, use_hint);
-          }
-        }
-        __syncthreads();
-        if (threadIdx.x == 0) produce_next();
-      }
-    }
-    GT_STAMP(6)
-  }
-}
-
 // Pixel-range splits per image for the reduce kernels. The reduce grid is ONE resident wave of `slots` CTAs taking
 // (image, split) items grid-stride; B * nsplit is chosen near 4 items per CTA so that items / slots falls just below
 // an integer (no CTA does a whole extra item while the others idle). slots <= 0: conservative 2 CTAs per SM.
@@ -735,44 +405,6 @@ static int gn_ws_nsplit(int B, int HW) {  // upper bound of nsplit over the redu
   if (maxs < 1) maxs = 1;
   return maxs > 320 ? 320 : maxs;
 }
-static long long env_ll(const char* name, long long dflt) {
-  const char* v = getenv(name);
-  return v && *v ? atoll(v) : dflt;
-}
-// Team-path plan for the backward: images per item, splits per image, team size. Returns false -> two-kernel path.
-struct GnTeamPlan {
-  int nteams, tsize, ipg, spi, hint;
-};
-template <typename K>
-static bool gn_team_plan(K kernel, size_t smem, int B, int HW, int C, size_t bytes_per_image, GnTeamPlan* plan) {
-  // opt-in (default off): measured on B200 the team path moves 3.27 GB instead of 5.34 GB per launch (128 ch x 256^2 x
-  // 64 images) but runs 1.37 ms against 1.03 ms for the two-kernel path - see profiles/README.md "GroupNorm backward"
-  const long long enable = env_ll("ODVAE_GN_BWD_TEAM", 0);
-  const long long item_mb = env_ll("ODVAE_GN_TEAM_ITEM_MB", 34);
-  const long long min_total_mb = env_ll("ODVAE_GN_TEAM_MIN_MB", 96);
-  const long long hint = env_ll("ODVAE_GN_TEAM_HINTS", 1);
-  if (!enable) return false;
-  const size_t total = bytes_per_image * B;
-  if (total < static_cast<size_t>(min_total_mb) << 20) return false;  // already L2-resident between the two kernels
-  int per_sm = 0;
-  if (cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, kernel, GN_THREADS, smem) != cudaSuccess || per_sm < 2) return false;
-  const long long teams = env_ll("ODVAE_GN_TEAMS", 2);
-  plan->nteams = teams < 1 ? 1 : (teams > 2 ? 2 : static_cast<int>(teams));
-  plan->tsize = 2 * num_sms() / plan->nteams;
-  plan->hint = hint ? 1 : 0;
-  int ipg = static_cast<int>((static_cast<size_t>(item_mb) << 20) / bytes_per_image);
-  if (ipg < 1) ipg = 1;
-  if (ipg > B) ipg = B;
-  int max_spi = gn_ws_nsplit(B, HW);
-  // at least 8 splits per image so a team's CTAs all have work
-  while (ipg > 1 && plan->tsize / ipg < 8) --ipg;
-  int spi = plan->tsize / ipg;
-  if (spi > max_spi) spi = max_spi;
-  if (spi < 1) return false;
-  plan->ipg = ipg;
-  plan->spi = spi;
-  return true;
-}
 static bool gn_shape_ok(int C, int G, int V) {
   if (C % G != 0 || C % V != 0) return false;
   const int cv = C / V;
@@ -800,11 +432,6 @@ using namespace odvae;
 
 extern "C" {
 
-#ifdef ODVAE_GN_TEAM_TIMING
-__attribute__((visibility("default"))) int odvae_debug_gn_team_timing(unsigned long long* out) {
-  return cudaMemcpyFromSymbol(out, gt_dbg, sizeof(gt_dbg)) == cudaSuccess ? 0 : -1;
-}
-#endif
 
 size_t odvae_groupnorm_workspace_bytes(int B, int HW, int C, int G) {
   const int ns = gn_ws_nsplit(B, HW);
@@ -868,17 +495,19 @@ int odvae_groupnorm_apply(const void* x, const float* stats, const float* gamma,
 }
 
 // act_dtype: format of x (the saved forward input); grad_dtype: format of dy / dx_add / dx.
-// Supported pairs: (f32, f32), (bf16, bf16), (fp16, bf16).
+// Supported pairs: (f32, f32), (bf16, bf16), (fp16, bf16), (fp16, fp16). pgrad_scale multiplies dgamma / dbeta (the inverse
+// of the static scale 16-bit activation gradients travel with in the all-fp16 mode; dx keeps the scale).
 int odvae_groupnorm_bwd(const void* x, const float* stats, const float* gamma, const float* beta, const void* dy,
                         const void* dx_add, void* dx, float* dgamma, float* dbeta, int B, int HW, int C, int G,
-                        int silu, int act_dtype, int grad_dtype, int accumulate, void* workspace, size_t ws_bytes,
-                        void* stream) {
+                        int silu, int act_dtype, int grad_dtype, int accumulate, float pgrad_scale, void* workspace,
+                        size_t ws_bytes, void* stream) {
   cudaStream_t st = static_cast<cudaStream_t>(stream);
   const int V = act_dtype == ODVAE_F32 ? 4 : 8;
   if (!gn_shape_ok(C, G, V)) return ODVAE_ERR_SHAPE;
   const int combo = (act_dtype == ODVAE_F32 && grad_dtype == ODVAE_F32)     ? 0
                     : (act_dtype == ODVAE_BF16 && grad_dtype == ODVAE_BF16) ? 1
                     : (act_dtype == ODVAE_F16 && grad_dtype == ODVAE_BF16)  ? 2
+                    : (act_dtype == ODVAE_F16 && grad_dtype == ODVAE_F16)   ? 3
                                                                             : -1;
   if (combo < 0) return ODVAE_ERR_SHAPE;
   if (ws_bytes < odvae_groupnorm_workspace_bytes(B, HW, C, G) - 256) return ODVAE_ERR_WORKSPACE;
@@ -887,54 +516,6 @@ int odvae_groupnorm_bwd(const void* x, const float* stats, const float* gamma, c
   float* coef = AB + static_cast<size_t>(B) * C * 2;
   const int rows = GN_THREADS / (C / V);
   const size_t smem = static_cast<size_t>(2) * rows * C * sizeof(float);
-  {
-    // one cooperative launch with L2 reuse when the tensors are far larger than the L2
-    const size_t esz_x = act_dtype == ODVAE_F32 ? 4 : 2, esz_g = grad_dtype == ODVAE_F32 ? 4 : 2;
-    const size_t bytes_per_image = static_cast<size_t>(HW) * C * (esz_x + esz_g);
-    unsigned* ctr = reinterpret_cast<unsigned*>(coef + static_cast<size_t>(B) * G * 2);
-    GnTeamPlan plan;
-    int launched = 0;
-    int nstages = GT_MAX_STAGES;
-    size_t smem_team = 0;
-#define GN_TRY_TEAM(T, TG)                                                                                            \
-  {                                                                                                                   \
-    auto kfn = gn_bwd_team_kernel<T, TG>;                                                                             \
-    static bool attr_set = false; /* benign race: idempotent */                                                      \
-    if (!attr_set) {                                                                                                  \
-      ODVAE_CUDA_TRY(cudaFuncSetAttribute(kfn, cudaFuncAttributeMaxDynamicSharedMemorySize, 120 * 1024));             \
-      attr_set = true;                                                                                                \
-    }                                                                                                                 \
-    bool ok = false;                                                                                                  \
-    if (ws_bytes >= odvae_groupnorm_workspace_bytes(B, HW, C, G))                                                     \
-      for (nstages = GT_MAX_STAGES; nstages >= 2 && !ok; --nstages) {                                                 \
-        smem_team = static_cast<size_t>(nstages) * (dx_add ? 3 : 2) * GT_CHUNK_BYTES + smem + 64;                                       \
-        ok = smem_team <= 120 * 1024 && gn_team_plan(kfn, smem_team, B, HW, C, bytes_per_image, &plan);               \
-        if (ok) break;                                                                                                \
-      }                                                                                                               \
-    if (ok) {                                                                                                         \
-      ODVAE_CUDA_TRY(cudaMemsetAsync(ctr, 0, 64, st));                                                                \
-      const T* xa = reinterpret_cast<const T*>(x);                                                                    \
-      const TG* dya = reinterpret_cast<const TG*>(dy);                                                                \
-      const TG* adda = reinterpret_cast<const TG*>(dx_add);                                                           \
-      TG* dxa = reinterpret_cast<TG*>(dx);                                                                            \
-      void* args[] = {&xa, &dya, &adda, &stats, &gamma, &beta, &part, &AB, &coef, &dxa, &ctr, &B, &HW, &C, &G, &silu,  \
-                      &plan.ipg, &plan.spi, &plan.nteams, &plan.hint, &nstages};                                                \
-      ODVAE_CUDA_TRY(cudaLaunchCooperativeKernel(reinterpret_cast<void*>(kfn), dim3(plan.nteams * plan.tsize),        \
-                                                 dim3(GN_THREADS), args, smem_team, st));                             \
-      launched = 1;                                                                                                   \
-    }                                                                                                                 \
-  }
-    if (combo == 1) GN_TRY_TEAM(bf16, bf16)
-    else if (combo == 2) GN_TRY_TEAM(f16, bf16)
-    else GN_TRY_TEAM(float, float)
-#undef GN_TRY_TEAM
-    if (launched) {
-      int s = check_launch("gn_bwd_team_kernel");
-      if (s != ODVAE_OK) return s;
-      gn_bwd_finalize_b_kernel<<<(C + 127) / 128, 128, 0, st>>>(AB, dgamma, dbeta, B, C, accumulate);
-      return check_launch("gn_bwd_finalize_b_kernel");
-    }
-  }
   int ns;
 #define GN_LAUNCH_REDUCE1(T, TG)                                                                                      \
   {                                                                                                                   \
@@ -947,6 +528,7 @@ int odvae_groupnorm_bwd(const void* x, const float* stats, const float* gamma, c
   }
   if (combo == 1) GN_LAUNCH_REDUCE1(bf16, bf16)
   else if (combo == 2) GN_LAUNCH_REDUCE1(f16, bf16)
+  else if (combo == 3) GN_LAUNCH_REDUCE1(f16, f16)
   else GN_LAUNCH_REDUCE1(float, float)
 #undef GN_LAUNCH_REDUCE1
   int s = check_launch("gn_reduce_kernel<1>");
@@ -954,16 +536,19 @@ int odvae_groupnorm_bwd(const void* x, const float* stats, const float* gamma, c
   gn_bwd_finalize_a_kernel<<<B, 256, static_cast<size_t>(2) * C * sizeof(float), st>>>(part, stats, gamma, AB, coef, ns, HW, C, G);
   s = check_launch("gn_bwd_finalize_a_kernel");
   if (s != ODVAE_OK) return s;
-  gn_bwd_finalize_b_kernel<<<(C + 127) / 128, 128, 0, st>>>(AB, dgamma, dbeta, B, C, accumulate);
+  gn_bwd_finalize_b_kernel<<<(C + 127) / 128, 128, 0, st>>>(AB, dgamma, dbeta, B, C, accumulate, pgrad_scale);
   s = check_launch("gn_bwd_finalize_b_kernel");
   if (s != ODVAE_OK) return s;
   dim3 grid2(gn_apply_blocks(B, HW, C, V), B);
-  if (combo == 1)
-    gn_bwd_apply_kernel<bf16, bf16><<<grid2, GN_THREADS, 0, st>>>(reinterpret_cast<const bf16*>(x), reinterpret_cast<const bf16*>(dy), reinterpret_cast<const bf16*>(dx_add), stats, gamma, beta, coef, reinterpret_cast<bf16*>(dx), HW, C, G, silu);
-  else if (combo == 2)
-    gn_bwd_apply_kernel<f16, bf16><<<grid2, GN_THREADS, 0, st>>>(reinterpret_cast<const f16*>(x), reinterpret_cast<const bf16*>(dy), reinterpret_cast<const bf16*>(dx_add), stats, gamma, beta, coef, reinterpret_cast<bf16*>(dx), HW, C, G, silu);
-  else
-    gn_bwd_apply_kernel<float, float><<<grid2, GN_THREADS, 0, st>>>(reinterpret_cast<const float*>(x), reinterpret_cast<const float*>(dy), reinterpret_cast<const float*>(dx_add), stats, gamma, beta, coef, reinterpret_cast<float*>(dx), HW, C, G, silu);
+#define GN_LAUNCH_APPLY(T, TG)                                                                                         \
+  gn_bwd_apply_kernel<T, TG><<<grid2, GN_THREADS, 0, st>>>(reinterpret_cast<const T*>(x), reinterpret_cast<const TG*>(dy), \
+                                                           reinterpret_cast<const TG*>(dx_add), stats, gamma, beta, coef,  \
+                                                           reinterpret_cast<TG*>(dx), HW, C, G, silu);
+  if (combo == 1) GN_LAUNCH_APPLY(bf16, bf16)
+  else if (combo == 2) GN_LAUNCH_APPLY(f16, bf16)
+  else if (combo == 3) GN_LAUNCH_APPLY(f16, f16)
+  else GN_LAUNCH_APPLY(float, float)
+#undef GN_LAUNCH_APPLY
   return check_launch("gn_bwd_apply_kernel");
 }
 

@@ -230,7 +230,7 @@ pack_conv_weight_mt_kernel(const long long* __restrict__ table, int n_entries) {
 template <int VEC>
 __global__ void wgrad_reduce_kernel(const float* __restrict__ ws, float* __restrict__ dw, int Cout, int Cin,
                                     int taps, int CoutP, int CinP, int split_k, int accumulate,
-                                    const float* __restrict__ cpart, int cs_rows, float* __restrict__ db) {
+                                    const float* __restrict__ cpart, int cs_rows, float* __restrict__ db, float scale) {
   if (cpart != nullptr) {
     const long long c = blockIdx.x * static_cast<long long>(blockDim.x) + threadIdx.x;
     if (c < Cout) {
@@ -244,6 +244,7 @@ __global__ void wgrad_reduce_kernel(const float* __restrict__ ws, float* __restr
         for (int u = 0; u < 8; ++u) t += v[u];
       }
       for (; r < cs_rows; ++r) t += __ldg(cpart + static_cast<long long>(r) * Cout + c);
+      t *= scale;
       db[c] = accumulate ? db[c] + t : t;
     }
   }
@@ -282,7 +283,7 @@ __global__ void wgrad_reduce_kernel(const float* __restrict__ ws, float* __restr
 #pragma unroll
     for (int j = 0; j < VEC; ++j) {
       float* d = dw + (static_cast<long long>(co) * Cin + ci + j) * taps + tap;
-      *d = accumulate ? (*d + acc[j]) : acc[j];
+      *d = accumulate ? (*d + acc[j] * scale) : acc[j] * scale;
     }
   }
 }
@@ -359,7 +360,7 @@ __global__ void __launch_bounds__(256) colsum_stage1_vec(const T* __restrict__ m
 }
 // blockDim = (32, 8): x over columns, y over 8 row lanes of the partial list; lanes are combined in a fixed order
 __global__ void colsum_stage2(const float* __restrict__ part, int nblk, int cols, float* __restrict__ out,
-                              int accumulate) {
+                              int accumulate, float scale = 1.0f) {
   const int c = blockIdx.x * 32 + threadIdx.x;
   __shared__ float sm[8][33];
   float t = 0.0f;
@@ -380,6 +381,7 @@ __global__ void colsum_stage2(const float* __restrict__ part, int nblk, int cols
     float r = 0.0f;
 #pragma unroll
     for (int j = 0; j < 8; ++j) r += sm[j][threadIdx.x];
+    r *= scale;
     out[c] = accumulate ? out[c] + r : r;
   }
 }
@@ -487,16 +489,16 @@ static int grid_for(long long work_items, int threads, int per_sm = 8) {
 
 // internal entry points used by api.cu ----------------------------------------------------------
 int launch_wgrad_reduce(const float* ws, float* dw, int Cout, int Cin, int taps, int CoutP, int CinP, int split_k,
-                        int accumulate, cudaStream_t st, const float* cpart, int cs_rows, float* db) {
+                        int accumulate, cudaStream_t st, const float* cpart, int cs_rows, float* db, float scale) {
   const long long total = static_cast<long long>(Cout) * Cin * taps;
   if (Cin % 4 == 0 && CinP % 4 == 0 && (reinterpret_cast<uintptr_t>(ws) & 15) == 0) {
     int grid = grid_for(total / 4, 128);
     if (cpart != nullptr && static_cast<long long>(grid) * 128 < Cout) grid = (Cout + 127) / 128;
-    wgrad_reduce_kernel<4><<<grid, 128, 0, st>>>(ws, dw, Cout, Cin, taps, CoutP, CinP, split_k, accumulate, cpart, cs_rows, db);
+    wgrad_reduce_kernel<4><<<grid, 128, 0, st>>>(ws, dw, Cout, Cin, taps, CoutP, CinP, split_k, accumulate, cpart, cs_rows, db, scale);
   } else {
     int grid = grid_for(total, 256);
     if (cpart != nullptr && static_cast<long long>(grid) * 256 < Cout) grid = (Cout + 255) / 256;
-    wgrad_reduce_kernel<1><<<grid, 256, 0, st>>>(ws, dw, Cout, Cin, taps, CoutP, CinP, split_k, accumulate, cpart, cs_rows, db);
+    wgrad_reduce_kernel<1><<<grid, 256, 0, st>>>(ws, dw, Cout, Cin, taps, CoutP, CinP, split_k, accumulate, cpart, cs_rows, db, scale);
   }
   return check_launch("wgrad_reduce_kernel");
 }
@@ -510,30 +512,34 @@ int launch_colsum_final(const float* part, int nrows, int cols, float* out, int 
 static constexpr int COLSUM_BLOCKS = 592;
 size_t colsum_workspace_bytes(int cols) { return static_cast<size_t>(COLSUM_BLOCKS) * cols * sizeof(float); }
 int launch_colsum(const void* m, long long rows, int cols, int ld, int act_dtype, float* out, int accumulate,
-                  float* part, cudaStream_t st) {
-  if (act_dtype != ODVAE_BF16 && act_dtype != ODVAE_F32) return ODVAE_ERR_SHAPE;  // gradients are bf16 or fp32
+                  float* part, cudaStream_t st, float scale) {
+  if (act_dtype != ODVAE_BF16 && act_dtype != ODVAE_F32 && act_dtype != ODVAE_F16) return ODVAE_ERR_SHAPE;
   int nblk = COLSUM_BLOCKS;
   if (rows < nblk * 8) nblk = static_cast<int>((rows + 7) / 8);
   if (nblk < 1) nblk = 1;
-  const int V = act_dtype == ODVAE_BF16 ? 8 : 4;
+  const int V = act_dtype == ODVAE_F32 ? 4 : 8;
   const bool vec = ld % V == 0 && ld / V <= 256 && 256 % (ld / V) == 0 && (reinterpret_cast<uintptr_t>(m) & 15) == 0 &&
                    static_cast<size_t>(256 / (ld / V)) * ld * sizeof(float) <= 48 * 1024;
   if (vec) {
     const size_t smem = static_cast<size_t>(256 / (ld / V)) * ld * sizeof(float);
     if (act_dtype == ODVAE_BF16)
       colsum_stage1_vec<bf16, 8><<<nblk, 256, smem, st>>>(reinterpret_cast<const bf16*>(m), rows, cols, ld, part);
+    else if (act_dtype == ODVAE_F16)
+      colsum_stage1_vec<f16, 8><<<nblk, 256, smem, st>>>(reinterpret_cast<const f16*>(m), rows, cols, ld, part);
     else
       colsum_stage1_vec<float, 4><<<nblk, 256, smem, st>>>(reinterpret_cast<const float*>(m), rows, cols, ld, part);
   } else {
     dim3 blk(32, 8);
     if (act_dtype == ODVAE_BF16)
       colsum_stage1<bf16><<<nblk, blk, 0, st>>>(reinterpret_cast<const bf16*>(m), rows, cols, ld, part);
+    else if (act_dtype == ODVAE_F16)
+      colsum_stage1<f16><<<nblk, blk, 0, st>>>(reinterpret_cast<const f16*>(m), rows, cols, ld, part);
     else
       colsum_stage1<float><<<nblk, blk, 0, st>>>(reinterpret_cast<const float*>(m), rows, cols, ld, part);
   }
   int s = check_launch("colsum_stage1");
   if (s != ODVAE_OK) return s;
-  colsum_stage2<<<(cols + 31) / 32, dim3(32, 8), 0, st>>>(part, nblk, cols, out, accumulate);
+  colsum_stage2<<<(cols + 31) / 32, dim3(32, 8), 0, st>>>(part, nblk, cols, out, accumulate, scale);
   return check_launch("colsum_stage2");
 }
 
@@ -645,6 +651,10 @@ int odvae_upsample2x_bwd(const void* dy, void* dx, int B, int H, int W, int C, i
     if (C % 8) return ODVAE_ERR_SHAPE;
     const long long total = static_cast<long long>(B) * H * W * (C / 8);
     upsample2x_bwd_kernel<bf16><<<grid_for(total, 256), 256, 0, st>>>(reinterpret_cast<const bf16*>(dy), reinterpret_cast<bf16*>(dx), B, H, W, C);
+  } else if (act_dtype == ODVAE_F16) {
+    if (C % 8) return ODVAE_ERR_SHAPE;
+    const long long total = static_cast<long long>(B) * H * W * (C / 8);
+    upsample2x_bwd_kernel<f16><<<grid_for(total, 256), 256, 0, st>>>(reinterpret_cast<const f16*>(dy), reinterpret_cast<f16*>(dx), B, H, W, C);
   } else {
     if (C % 4) return ODVAE_ERR_SHAPE;
     const long long total = static_cast<long long>(B) * H * W * (C / 4);

@@ -74,7 +74,18 @@ template <> __device__ __forceinline__ void load4<bf16>(const bf16* p, int i, fl
   const float2 a = unpack_bf16x2(v.x), b = unpack_bf16x2(v.y);
   f[0] = a.x; f[1] = a.y; f[2] = b.x; f[3] = b.y;
 }
+template <> __device__ __forceinline__ void load4<f16>(const f16* p, int i, float (&f)[4]) {
+  const uint2 v = reinterpret_cast<const uint2*>(p)[i];
+  const float2 a = unpack_f16x2(v.x), b = unpack_f16x2(v.y);
+  f[0] = a.x; f[1] = a.y; f[2] = b.x; f[3] = b.y;
+}
 template <typename T> __device__ __forceinline__ void store4(T* p, int i, const float (&f)[4]);
+template <> __device__ __forceinline__ void store4<f16>(f16* p, int i, const float (&f)[4]) {
+  uint2 o;
+  o.x = pack_f16x2(f[0], f[1]);
+  o.y = pack_f16x2(f[2], f[3]);
+  reinterpret_cast<uint2*>(p)[i] = o;
+}
 template <> __device__ __forceinline__ void store4<float>(float* p, int i, const float (&f)[4]) {
   reinterpret_cast<float4*>(p)[i] = make_float4(f[0], f[1], f[2], f[3]);
 }
@@ -177,7 +188,7 @@ __global__ void __launch_bounds__(256) sample_kl_bwd_kernel(
     const T* __restrict__ dz, const float* __restrict__ dkl, const float* __restrict__ dmean_direct,
     const float* __restrict__ dlogvar_direct, const float* __restrict__ mean, const float* __restrict__ logvar,
     const float* __restrict__ eps, const uint8_t* __restrict__ keep, float keep_scale, T* __restrict__ dmoments,
-    float* __restrict__ denc_pose, int HW, int Cz, int CzPad, int ldm) {
+    float* __restrict__ denc_pose, int HW, int Cz, int CzPad, int ldm, float dz_scale, float out_scale) {
   const int b = blockIdx.x;
   const int n = Cz * HW;
   const float gk = dkl != nullptr ? dkl[b] : 0.0f;
@@ -186,7 +197,7 @@ __global__ void __launch_bounds__(256) sample_kl_bwd_kernel(
     const long long o = static_cast<long long>(b) * n + i;
     const float mu = mean[o], lv = logvar[o];
     float g = 0.0f;
-    if (dz != nullptr) g = to_f32<T>(dz[(static_cast<long long>(b) * HW + p) * CzPad + c]);
+    if (dz != nullptr) g = to_f32<T>(dz[(static_cast<long long>(b) * HW + p) * CzPad + c]) * dz_scale;
     if (denc_pose != nullptr) denc_pose[o] = g;
     if (keep != nullptr) g = keep[o] ? g * keep_scale : 0.0f;
     float dmu = g + gk * mu;
@@ -194,10 +205,10 @@ __global__ void __launch_bounds__(256) sample_kl_bwd_kernel(
     if (dz != nullptr) dlv += g * eps[o] * 0.5f * expf(0.5f * lv);
     if (dmean_direct != nullptr) dmu += dmean_direct[o];
     if (dlogvar_direct != nullptr) dlv += dlogvar_direct[o];
-    if (!(lv > -30.0f && lv < 20.0f)) dlv = 0.0f;  // clamp(-30, 20) passes no gradient outside
+    if (!(lv >= -30.0f && lv <= 20.0f)) dlv = 0.0f;  // torch.clamp(-30, 20) passes the gradient on the CLOSED interval
     const long long mrow = (static_cast<long long>(b) * HW + p) * ldm;
-    dmoments[mrow + c] = from_f32<T>(dmu);
-    dmoments[mrow + Cz + c] = from_f32<T>(dlv);
+    dmoments[mrow + c] = from_f32<T>(dmu * out_scale);
+    dmoments[mrow + Cz + c] = from_f32<T>(dlv * out_scale);
   }
   const int padc = ldm - 2 * Cz;
   for (int i = threadIdx.x; i < padc * HW; i += 256) {
@@ -376,6 +387,9 @@ int odvae_softmax_rows(const float* S, void* P, int64_t rows, int n, float scale
   if (act_dtype == ODVAE_BF16) {
     if (small) softmax_rows_kernel<bf16, 32><<<grid, 256, 0, st>>>(S, reinterpret_cast<bf16*>(P), rows, n, scale);
     else softmax_rows_kernel<bf16, 256><<<grid, 256, 0, st>>>(S, reinterpret_cast<bf16*>(P), rows, n, scale);
+  } else if (act_dtype == ODVAE_F16) {
+    if (small) softmax_rows_kernel<f16, 32><<<grid, 256, 0, st>>>(S, reinterpret_cast<f16*>(P), rows, n, scale);
+    else softmax_rows_kernel<f16, 256><<<grid, 256, 0, st>>>(S, reinterpret_cast<f16*>(P), rows, n, scale);
   } else {
     if (small) softmax_rows_kernel<float, 32><<<grid, 256, 0, st>>>(S, reinterpret_cast<float*>(P), rows, n, scale);
     else softmax_rows_kernel<float, 256><<<grid, 256, 0, st>>>(S, reinterpret_cast<float*>(P), rows, n, scale);
@@ -413,6 +427,11 @@ int odvae_softmax_rows_bwd(const float* dP, const void* P, void* dS, int64_t row
     bf16* d = reinterpret_cast<bf16*>(dS);
     if (small) softmax_rows_bwd_kernel<bf16, 32><<<grid, 256, 0, st>>>(dP, p, d, rows, n, scale);
     else softmax_rows_bwd_kernel<bf16, 256><<<grid, 256, 0, st>>>(dP, p, d, rows, n, scale);
+  } else if (act_dtype == ODVAE_F16) {
+    const f16* p = reinterpret_cast<const f16*>(P);
+    f16* d = reinterpret_cast<f16*>(dS);
+    if (small) softmax_rows_bwd_kernel<f16, 32><<<grid, 256, 0, st>>>(dP, p, d, rows, n, scale);
+    else softmax_rows_bwd_kernel<f16, 256><<<grid, 256, 0, st>>>(dP, p, d, rows, n, scale);
   } else {
     const float* p = reinterpret_cast<const float*>(P);
     float* d = reinterpret_cast<float*>(dS);
@@ -446,7 +465,7 @@ int odvae_sample_kl_fwd(const void* moments, const float* eps, const uint8_t* ke
 int odvae_sample_kl_bwd(const void* dz, const float* dkl, const float* dmean_direct, const float* dlogvar_direct,
                         const float* mean, const float* logvar, const float* eps, const uint8_t* keep, float keep_scale,
                         void* dmoments, float* denc_pose, int B, int HW, int Cz, int CzPad, int ld_moments,
-                        int act_dtype, void* stream) {
+                        int act_dtype, float dz_scale, float out_scale, void* stream) {
   if (B <= 0 || ld_moments < 2 * Cz || CzPad < Cz) return ODVAE_ERR_SHAPE;
   if (dz != nullptr && eps == nullptr) return ODVAE_ERR_SHAPE;
   cudaStream_t st = static_cast<cudaStream_t>(stream);
@@ -454,12 +473,16 @@ int odvae_sample_kl_bwd(const void* dz, const float* dkl, const float* dmean_dir
     sample_kl_bwd_kernel<bf16><<<B, 256, 0, st>>>(reinterpret_cast<const bf16*>(dz), dkl, dmean_direct, dlogvar_direct,
                                                   mean, logvar, eps, keep, keep_scale,
                                                   reinterpret_cast<bf16*>(dmoments), denc_pose, HW, Cz, CzPad,
-                                                  ld_moments);
+                                                  ld_moments, dz_scale, out_scale);
+  else if (act_dtype == ODVAE_F16)
+    sample_kl_bwd_kernel<f16><<<B, 256, 0, st>>>(reinterpret_cast<const f16*>(dz), dkl, dmean_direct, dlogvar_direct,
+                                                 mean, logvar, eps, keep, keep_scale, reinterpret_cast<f16*>(dmoments),
+                                                 denc_pose, HW, Cz, CzPad, ld_moments, dz_scale, out_scale);
   else
     sample_kl_bwd_kernel<float><<<B, 256, 0, st>>>(reinterpret_cast<const float*>(dz), dkl, dmean_direct,
                                                    dlogvar_direct, mean, logvar, eps, keep, keep_scale,
                                                    reinterpret_cast<float*>(dmoments), denc_pose, HW, Cz, CzPad,
-                                                   ld_moments);
+                                                   ld_moments, dz_scale, out_scale);
   return check_launch("sample_kl_bwd_kernel");
 }
 

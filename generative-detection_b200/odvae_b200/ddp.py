@@ -88,7 +88,9 @@ class GradArena:
         """Tensor hook for the activation that enters the module owning `param` (its gradient is produced
         after every parameter gradient of that module and of all later modules)."""
         def hook(grad):
-            self.ready_through(param)
+            from . import ops
+            if ops._PROBE[0] == 0:  # not inside an autograd.grad probe (adaptive GAN weight)
+                self.ready_through(param)
             return None
         return hook
 

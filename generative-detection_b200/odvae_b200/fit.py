@@ -14,9 +14,10 @@ What it reproduces, with the reference line it comes from:
                          and a reference `last.ckpt` loads here the same way.
 
 The optimizer_idx-0 step runs through trainer.TrainStep (gradient arena, bucketed allreduce overlapped with backward,
-fused clip + Adam). The discriminator step (optimizer_idx 1) is taken only when the loss returns a differentiable
-tensor: with `disc_factor = 0` (the only mode until SURVEY 8 f2 lands) the reference's d_loss is identically 0 and its
-Adam update is a no-op on fresh moments, so skipping it is exact; global_step still advances as in Lightning.
+fused clip + Adam). The discriminator step (optimizer_idx 1: hinge loss on detached real / fake crops, its own clip +
+Adam, gradients all-reduced over ranks) is taken while the GAN is active (`disc_factor > 0` and `global_step >=
+disc_start`); before that the reference's d_loss is identically 0 and its Adam update is a no-op on fresh moments, so
+skipping it is exact; global_step still advances as in Lightning.
 """
 import os
 
@@ -41,6 +42,10 @@ class Fit:
         self.ae_step = TrainStep(model, lr=lr, max_grad_norm=max_grad_norm, process_group=process_group)
         self.opt_ae = self.ae_step.opt
         self.opt_disc = model.configure_optimizers()[0][1]
+        if hasattr(self.opt_disc, "max_grad_norm"):  # FusedAdam: clip folded into the multi-tensor kernel
+            self.opt_disc.max_grad_norm = max_grad_norm
+            self.opt_disc.grad_scale = 1.0 / self.world
+        self.pg = process_group
         self.max_grad_norm = max_grad_norm
         self.ckpt_dir, self.ckpt_every = ckpt_dir, ckpt_every_n_batches
         self.log_fn = log_fn
@@ -53,14 +58,30 @@ class Fit:
         aeloss = self.ae_step(batch, batch_idx)
         model.global_step += 1
         discloss = model.training_step(batch, batch_idx, 1)
-        if torch.is_tensor(discloss) and discloss.requires_grad:
-            self.opt_disc.zero_grad(set_to_none=True)
-            discloss.backward()
-            torch.nn.utils.clip_grad_norm_(model.loss.discriminator.parameters(), self.max_grad_norm)
-            self.opt_disc.step()
+        if model._gan_active() and torch.is_tensor(discloss) and discloss.requires_grad:
+            self.disc_step(discloss)
         model.global_step += 1
         self.batches_seen += 1
         return aeloss, discloss.detach()
+
+    def disc_step(self, discloss):
+        """backward + gradient mean over ranks + clip + Adam for the discriminator (PL: second optimizer, CFG:137,140)."""
+        params = [p for p in self.model.loss.discriminator.parameters() if p.requires_grad]
+        self.opt_disc.zero_grad(set_to_none=True)
+        discloss.backward()
+        if self.world > 1:
+            flat = torch.cat([p.grad.reshape(-1) for p in params])
+            dist.all_reduce(flat, op=dist.ReduceOp.SUM, group=self.pg)
+            o = 0
+            for p in params:
+                p.grad.copy_(flat[o:o + p.numel()].view_as(p))
+                o += p.numel()
+        if not hasattr(self.opt_disc, "max_grad_norm"):
+            if self.world > 1:
+                for p in params:
+                    p.grad.div_(self.world)
+            torch.nn.utils.clip_grad_norm_(params, self.max_grad_norm)
+        self.opt_disc.step()
 
     def fit(self, loader, max_steps=None, max_epochs=1):
         """Runs until `max_steps` optimizer steps (Lightning's `max_steps` unit) or `max_epochs` passes over `loader`."""

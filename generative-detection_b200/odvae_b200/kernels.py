@@ -85,7 +85,7 @@ def conv_dgrad(dy, w_packed_dgrad, CinP, geom, impl, in_hw, dx_add=None):
     return dx
 
 
-def conv_wgrad(x, dy, Cin, Cout, geom, impl, want_bias=True, dw=None, db=None, accumulate=False):
+def conv_wgrad(x, dy, Cin, Cout, geom, impl, want_bias=True, dw=None, db=None, accumulate=False, out_scale=1.0):
     B, H, W, CinP = x.shape
     CoutP = dy.shape[-1]
     k = geom_k(geom)
@@ -96,7 +96,7 @@ def conv_wgrad(x, dy, Cin, Cout, geom, impl, want_bias=True, dw=None, db=None, a
     nbytes = call("conv2d_wgrad_workspace_bytes", B, H, W, CinP, CoutP, geom, impl)
     ws = workspace(nbytes, x.device, "wgrad")
     call("conv2d_wgrad", x, dy, dw, db if want_bias else None, B, H, W, CinP, CoutP, Cin, Cout, geom,
-         act_code(x.dtype), impl, 1 if accumulate else 0, ws, ws.numel())
+         act_code(x.dtype), impl, 1 if accumulate else 0, float(out_scale), ws, ws.numel())
     return dw, db
 
 

@@ -7,9 +7,9 @@ images (ops.L1Masked) and the one-CTA "loss heads" kernel for everything per-sam
 
 `perceptual_weight > 0` adds the LPIPS term (odvae_b200/lpips.py: VGG16 towers on the conv engine; taming's class is
 un-vendored, so parity is against oracle/lpips_oracle.py only and the trained vgg.pth must be loaded by the user).
-Not implemented yet: the PatchGAN discriminator - `disc_factor > 0` raises at forward time; with
-`disc_factor == 0` the generator term is exactly 0 in the reference's total (LOSS.py:294-317), only the
-logged `g_loss` differs (reported as 0 here).
+The GAN terms run on odvae_b200/patchgan.py: generator side `g_loss = -mean(D(x_hat * mask) * mask_bg)`
+with the adaptive weight of LD contperceptual.py:32-43 (two `autograd.grad` calls on `decoder.conv_out.weight`), and
+the `optimizer_idx == 1` hinge / vanilla discriminator loss on detached real / fake images (LOSS.py:352-375).
 """
 import ctypes
 import math
@@ -17,8 +17,10 @@ import pickle as pkl
 
 import torch
 import torch.nn as nn
+import torch.nn.functional as F
 
 from . import ops
+from .patchgan import NLayerDiscriminator, weights_init  # noqa: F401  (re-exported: taming's names)
 from .distributions import DiagonalGaussianDistribution
 
 POSE_6D_DIM = 4
@@ -36,33 +38,12 @@ def adopt_weight(weight, global_step, threshold=0, value=0.0):
     return value if global_step < threshold else weight
 
 
-class NLayerDiscriminator(nn.Module):
-    """Parameter container with taming's PatchGAN layout (state_dict keys `main.{0,2,3,5,6,8,9,11}.*`) so that
-    `configure_optimizers` and reference checkpoints keep working; its forward pass is SURVEY 8 f2 (next)."""
+def hinge_d_loss(logits_real, logits_fake):  # taming.modules.losses.vqperceptual
+    return 0.5 * (torch.mean(F.relu(1.0 - logits_real)) + torch.mean(F.relu(1.0 + logits_fake)))
 
-    def __init__(self, input_nc=3, ndf=64, n_layers=3, use_actnorm=False):
-        super().__init__()
-        kw, padw = 4, 1
-        seq = [nn.Conv2d(input_nc, ndf, kw, 2, padw), nn.LeakyReLU(0.2, True)]
-        nf_mult = 1
-        for n in range(1, n_layers):
-            nf_prev, nf_mult = nf_mult, min(2 ** n, 8)
-            seq += [nn.Conv2d(ndf * nf_prev, ndf * nf_mult, kw, 2, padw, bias=False),
-                    nn.BatchNorm2d(ndf * nf_mult), nn.LeakyReLU(0.2, True)]
-        nf_prev, nf_mult = nf_mult, min(2 ** n_layers, 8)
-        seq += [nn.Conv2d(ndf * nf_prev, ndf * nf_mult, kw, 1, padw, bias=False),
-                nn.BatchNorm2d(ndf * nf_mult), nn.LeakyReLU(0.2, True)]
-        seq += [nn.Conv2d(ndf * nf_mult, 1, kw, 1, padw)]
-        self.main = nn.Sequential(*seq)
-        for m in self.modules():  # taming weights_init
-            if isinstance(m, nn.Conv2d):
-                nn.init.normal_(m.weight.data, 0.0, 0.02)
-            elif isinstance(m, nn.BatchNorm2d):
-                nn.init.normal_(m.weight.data, 1.0, 0.02)
-                nn.init.constant_(m.bias.data, 0)
 
-    def forward(self, x):
-        raise NotImplementedError("the PatchGAN discriminator forward is SURVEY 8 f2 (next); run with disc_factor=0")
+def vanilla_d_loss(logits_real, logits_fake):
+    return 0.5 * (torch.mean(F.softplus(-logits_real)) + torch.mean(F.softplus(logits_fake)))
 
 
 class LossHeads(torch.autograd.Function):
@@ -120,15 +101,20 @@ class PoseLoss(nn.Module):
             raise NotImplementedError("the fused loss implements the north-star config: pose_loss_fn='l1', train_on_yaw")
         self.kl_weight, self.pixel_weight = kl_weight, pixelloss_weight
         self.perceptual_weight = perceptual_weight
-        if perceptual_weight > 0:
-            # LD contperceptual.py:17 `self.perceptual_loss = LPIPS().eval()`: frozen VGG16 + lin heads. The trained weights
-            # (taming's vgg.pth) are not downloadable here: load them with load_state_dict / init_from_ckpt.
-            from .lpips import LPIPS
-            self.perceptual_loss = LPIPS().eval()
+        # LD contperceptual.py:17 `self.perceptual_loss = LPIPS().eval()`: frozen VGG16 + lin heads, ALWAYS constructed (the
+        # reference's checkpoints carry its 33 tensors whatever perceptual_weight is). The trained weights (taming's
+        # vgg.pth) are not downloadable here: load them with load_state_dict / init_from_ckpt.
+        from .lpips import LPIPS
+        self.perceptual_loss = LPIPS().eval()
         self.logvar = nn.Parameter(torch.ones(size=()) * logvar_init)
         self.discriminator = NLayerDiscriminator(input_nc=disc_in_channels, n_layers=disc_num_layers,
                                                  use_actnorm=use_actnorm)
         self.discriminator_iter_start = disc_start
+        self.disc_loss = hinge_d_loss if disc_loss == "hinge" else vanilla_d_loss
+        # optimizer_idx == 1 while the GAN is switched off (disc_factor == 0 or global_step < disc_start): the reference
+        # still runs D on real and fake and returns 0 * hinge. True (default) skips those two forward passes and returns
+        # a differentiable zero tied to the discriminator (logged logits are then 0); False reproduces the logs too.
+        self.skip_inactive_gan = True
         self.disc_factor, self.discriminator_weight, self.disc_conditional = disc_factor, disc_weight, disc_conditional
         self.pose_conditioned_generation_steps = pose_conditioned_generation_steps
         self.encoder_pretrain_steps = encoder_pretrain_steps
@@ -178,15 +164,15 @@ class PoseLoss(nn.Module):
                 split="train", weights=None):
         if mask_gt is not None or weights is not None or cond is not None:
             raise NotImplementedError("image masks / per-pixel weights / conditioning are unused by the north-star config")
-        if self.disc_factor > 0:
-            raise NotImplementedError("the GAN terms are SURVEY 8 f2; set disc_factor=0")
+        if self.disc_conditional:
+            raise NotImplementedError("disc_conditional=True is unused by the north-star config")
         dev = rgb_gt.device
         self.use_mask_loss = False  # LOSS.py:230-248 (mask_gt is None)
         use_pixel = not (global_step < (self.encoder_pretrain_steps + self.pose_conditioned_generation_steps))
+        disc_factor = adopt_weight(self.disc_factor, global_step, threshold=self.discriminator_iter_start)
+        mask_bg = (class_gt.to(dev) != BACKGROUND_CLASS_IDX).to(torch.float32)  # LOSS.py:227-228
         if optimizer_idx == 1:
-            zero = torch.zeros((), device=dev)
-            return zero, {"{}/disc_loss".format(split): zero, "{}/logits_real".format(split): zero,
-                          "{}/logits_fake".format(split): zero}
+            return self._discriminator_step(rgb_gt, dec_obj, mask_2d_bbox, mask_bg, disc_factor, split)
 
         B = rgb_gt.shape[0]
         ncls = dec_pose.shape[1] - BBOX_DIM
@@ -212,13 +198,24 @@ class PoseLoss(nn.Module):
         out = LossHeads.apply(dec_pose, bbox_posterior.mean, bbox_posterior.logvar, l1_sums, posterior_obj.kl(),
                               self.logvar, gts, (B, ncls, npix, tuple(float(v) for v in w7)))
         loss = out[O_TOTAL]
+        # ---- generator side of the GAN (LOSS.py:280-304, 313-317)
+        logits_fake = self.discriminator(dec_obj, mask=mask2d, param_grads=False) * mask_bg.view(B, 1, 1, 1)
+        g_loss = -torch.mean(logits_fake)
+        d_weight = torch.zeros((), device=dev)
+        if self.disc_factor > 0.0 and global_step > self.encoder_pretrain_steps:
+            try:
+                d_weight = self.calculate_adaptive_weight(out[O_NLL], g_loss, last_layer=last_layer)
+            except RuntimeError:
+                assert not self.training
+                d_weight = torch.zeros((), device=dev)
+        if train_rec and disc_factor != 0:
+            loss = loss + d_weight * disc_factor * g_loss
         d = out.detach()
-        disc_factor = adopt_weight(self.disc_factor, global_step, threshold=self.discriminator_iter_start)
         zero = torch.zeros((), device=dev)
         k = lambda name: "{}/{}".format(split, name)
-        log = {k("total_loss"): d[O_TOTAL], k("logvar"): self.logvar.detach(), k("kl_loss_obj"): d[O_KL],
+        log = {k("total_loss"): loss.detach(), k("logvar"): self.logvar.detach(), k("kl_loss_obj"): d[O_KL],
                k("nll_loss"): d[O_NLL], k("weighted_nll_loss"): d[O_NLL], k("rec_loss"): d[O_REC],
-               k("d_weight"): zero, k("disc_factor"): torch.tensor(disc_factor), k("g_loss"): zero,
+               k("d_weight"): d_weight.detach(), k("disc_factor"): torch.tensor(disc_factor), k("g_loss"): g_loss.detach(),
                k("pose_loss"): d[O_POSE], k("weighted_pose_loss"): self.pose_weight * d[O_POSE],
                k("mask_loss"): zero, k("weighted_mask_loss"): zero, k("class_loss"): d[O_CLASS],
                k("weighted_class_loss"): self.class_weight * d[O_CLASS], k("bbox_loss"): d[O_BBOX],
@@ -228,6 +225,39 @@ class PoseLoss(nn.Module):
                k("weighted_kl_loss_obj"): self.kl_weight_obj * d[O_KL], k("fill_factor_loss"): d[O_FILL],
                k("weighted_fill_factor_loss"): self.fill_factor_weight * d[O_FILL]}
         return loss, log
+
+    def calculate_adaptive_weight(self, nll_loss, g_loss, last_layer=None):
+        """LD contperceptual.py:32-43: ||d nll / d W_last|| / (||d g / d W_last|| + 1e-4), clamped, detached, times disc_weight.
+        Both gradients come from `torch.autograd.grad(..., retain_graph=True)` through this package's autograd Functions;
+        while they run, parameter gradients are returned as tensors (never written into the DDP gradient arena)."""
+        if last_layer is None:
+            last_layer = self.last_layer[0]
+        with ops.probe_gradients():
+            nll_grads = torch.autograd.grad(nll_loss, last_layer, retain_graph=True)[0]
+            g_grads = torch.autograd.grad(g_loss, last_layer, retain_graph=True)[0]
+        d_weight = torch.norm(nll_grads) / (torch.norm(g_grads) + 1e-4)
+        d_weight = torch.clamp(d_weight, 0.0, 1e4).detach()
+        return d_weight * self.discriminator_weight
+
+    def _discriminator_step(self, rgb_gt, dec_obj, mask_2d_bbox, mask_bg, disc_factor, split):
+        """optimizer_idx == 1 (LOSS.py:352-375): disc_factor * disc_loss(D(x * mask) * mask_bg, D(x_hat * mask) * mask_bg)
+        on detached images."""
+        dev = rgb_gt.device
+        B = rgb_gt.shape[0]
+        k = lambda name: "{}/{}".format(split, name)
+        if disc_factor == 0 and self.skip_inactive_gan:
+            # 0 * hinge: no gradient reaches D; keep the result differentiable for Lightning's automatic optimization
+            zero = sum(p.sum() for p in self.discriminator.parameters() if p.requires_grad) * 0.0
+            z = torch.zeros((), device=dev)
+            return zero, {k("disc_loss"): z, k("logits_real"): z, k("logits_fake"): z}
+        mask2d = ops._c(mask_2d_bbox.to(device=dev, dtype=torch.float32, non_blocking=True))
+        m = mask_bg.view(B, 1, 1, 1)
+        logits_real = self.discriminator(rgb_gt.detach().float(), mask=mask2d) * m
+        logits_fake = self.discriminator(dec_obj.detach()[:, :rgb_gt.shape[1]].float(), mask=mask2d) * m
+        d_loss = disc_factor * self.disc_loss(logits_real, logits_fake)
+        log = {k("disc_loss"): d_loss.clone().detach().mean(), k("logits_real"): logits_real.detach().mean(),
+               k("logits_fake"): logits_fake.detach().mean()}
+        return d_loss, log
 
     def _prior(self, dev):
         if self._prior_table is None or self._prior_table.device != dev:

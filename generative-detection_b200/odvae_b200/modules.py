@@ -65,7 +65,7 @@ class GroupNorm(nn.Module):
     fmt = None  # set by ops.assign_format()
 
     def forward(self, x, silu=False):
-        return ops.GroupNormAct.apply(x, self.weight, self.bias, silu, self.fmt)
+        return ops.GroupNormAct.apply(x, self.weight, self.bias, silu, self.fmt, getattr(self, "gscale", None))
 
 
 class ResnetBlock(nn.Module):
@@ -208,7 +208,7 @@ class Encoder(nn.Module):
     def forward_nhwc(self, x):
         """x: NCHW fp32 image -> NHWC activations [B,h,w,pad64(out_channels)]."""
         _check_cuda(x)
-        h = ops.ToNHWC.apply(x, ops.cpad(self.in_channels), self.compute_dtype)
+        h = ops.ToNHWC.apply(x, ops.cpad(self.in_channels), self.compute_dtype, getattr(self, "gscale", None))
         h = self.conv_in(h, need_dx=x.requires_grad)
         for i_level in range(self.num_resolutions):
             lvl = self.down[i_level]
@@ -223,7 +223,7 @@ class Encoder(nn.Module):
         return _run(self.conv_out, h)
 
     def forward(self, x):
-        return ops.ToNCHW.apply(self.forward_nhwc(x), self.out_channels, self.compute_dtype)
+        return ops.ToNCHW.apply(self.forward_nhwc(x), self.out_channels, self.compute_dtype, getattr(self, "gscale", None))
 
 
 class Decoder(nn.Module):
@@ -276,7 +276,8 @@ class Decoder(nn.Module):
 
     def forward(self, z):
         _check_cuda(z)
-        return self.forward_nhwc(ops.ToNHWC.apply(z, ops.cpad(self.z_channels), self.compute_dtype))
+        return self.forward_nhwc(ops.ToNHWC.apply(z, ops.cpad(self.z_channels), self.compute_dtype,
+                                                  getattr(self, "gscale", None)))
 
 
 class Linear(nn.Module):

@@ -19,6 +19,7 @@ import torch
 from . import lib
 from .lib import BF16, CONV_1x1, CONV_3x3_S1, CONV_3x3_S2, F16, F32, IMPL_SIMT, IMPL_TC, call, stream_handle
 
+DS_SCALE_FP16 = 256.0  # extra factor on the attention score gradient while it is stored in fp16 (see AttnBlock.backward)
 GROUPS = 32      # Normalize(): GroupNorm(num_groups=32, eps=1e-6)  LD model.py:38-39
 GN_EPS = 1e-6
 
@@ -47,14 +48,19 @@ class Format:
 
     compute_dtype float32  -> fwd = attn = grad = f32  (SIMT engine; the <=1e-4 validation mode)
     compute_dtype bfloat16 -> fwd = attn = grad = bf16
-    compute_dtype float16  -> the MIXED mode: fwd = IEEE fp16 (11-bit significand: measured 8x lower forward error
-        than bf16, which does not meet the 1e-2 tolerance through ~60 stacked layers), attn = grad = bf16 (range).
-        tcgen05 needs both MMA operands in one format (a mix traps on B200), so the weight-gradient GEMMs read a bf16
-        copy of the forward operand (written by the GroupNorm apply kernel, or by `cast16` at the few other sites).
+    compute_dtype float16  -> fwd = attn = grad = IEEE fp16: the TIMED mode. 11-bit significands everywhere (bf16 storage
+        measured 1.4-2.6e-2 on reconstructions and 1-3.4e-2 per-tensor on gradients through ~60 stacked layers; fp16 meets
+        the 1e-2 tolerance on both). Range: forward tensors are O(1..1e3) (GroupNorm bounds them; stores saturate at
+        65504 and raise the library's overflow flag); activation GRADIENTS travel multiplied by a static power-of-two
+        scale per domain (GradScale: decoder side / encoder side, chosen from the batch size and the loss weights) that
+        the parameter-gradient kernels divide out again (wgrad / GroupNorm-backward `*_scale` arguments).
+    compute_dtype "mixed"  -> the round-1 mode, kept for A/B runs: fwd = fp16, attn = grad = bf16. tcgen05 needs both MMA
+        operands in one format (a mix traps on B200), so its weight-gradient GEMMs read a bf16 copy of the forward operand
+        (written by the GroupNorm apply kernel, or by `cast16` at the few other sites).
 
-    Torch labelling: autograd casts a gradient to the dtype of the forward tensor it belongs to, so in the mixed mode
-    forward NHWC buffers are labelled torch.bfloat16 while holding fp16 bit patterns (only this library's kernels
-    ever read them; decode with `.view(torch.float16)`), and gradients are genuine bfloat16 tensors.
+    Torch labelling: autograd casts a gradient to the dtype of the forward tensor it belongs to, so every 16-bit NHWC
+    buffer is labelled torch.bfloat16 whatever bit pattern it holds (only this library's kernels ever read them; decode an
+    fp16 one with `.view(torch.float16)`).
     """
 
     def __init__(self, fwd, attn, grad):
@@ -69,12 +75,58 @@ class Format:
 FORMAT_F32 = Format(F32, F32, F32)
 FORMAT_BF16 = Format(BF16, BF16, BF16)
 FORMAT_MIXED = Format(F16, BF16, BF16)
+FORMAT_FP16 = Format(F16, F16, F16)
 
 
 def format_for(compute_dtype):
     if isinstance(compute_dtype, Format):
         return compute_dtype
-    return {torch.float32: FORMAT_F32, torch.bfloat16: FORMAT_BF16, torch.float16: FORMAT_MIXED}[compute_dtype]
+    if compute_dtype == "mixed":
+        return FORMAT_MIXED
+    return {torch.float32: FORMAT_F32, torch.bfloat16: FORMAT_BF16, torch.float16: FORMAT_FP16}[compute_dtype]
+
+
+class GradScale:
+    """Static scale S (a power of two) that the 16-bit activation gradients of one domain (decoder side / encoder side)
+    are multiplied by while they travel through HBM in fp16; one shared object per domain, read at backward time."""
+
+    def __init__(self, value=1.0):
+        self.value = float(value)
+
+    def __repr__(self):
+        return "GradScale(%g)" % self.value
+
+
+_UNIT_SCALE = GradScale(1.0)
+
+
+def gs_of(holder):
+    """Activation-gradient scale of the module / ConvSpec `holder` (1.0 unless assign_grad_scales stamped one)."""
+    gs = getattr(holder, "gscale", None) if holder is not None else None
+    return gs.value if gs is not None else 1.0
+
+
+def assign_grad_scales(root, scale_obj):
+    """Stamp every sub-module and ConvSpec under `root` with the shared GradScale object."""
+    for m in root.modules():
+        m.gscale = scale_obj
+        for name in ("spec", "spec1", "spec2", "spec_nin", "spec_proj"):
+            sp = getattr(m, name, None)
+            if isinstance(sp, ConvSpec):
+                sp.gscale = scale_obj
+
+
+def pow2_near(v):
+    import math
+    return 2.0 ** round(math.log2(max(float(v), 1e-30)))
+
+
+def disc_format(fmt):
+    """Format of the PatchGAN discriminator inside a model of Format `fmt`: same forward format, gradients in bf16 whenever
+    the model's gradient format is 16-bit (its logits gradient is ~1e-5 and unscaled: fp16 would flush it)."""
+    if fmt.grad == F32:
+        return fmt
+    return Format(fmt.fwd, fmt.attn, BF16)
 
 
 def format_of(x, holder=None):
@@ -88,7 +140,15 @@ def format_of(x, holder=None):
 def assign_format(root, compute_dtype):
     """Stamp every sub-module and ConvSpec under `root` with the Format of `compute_dtype`."""
     fmt = format_for(compute_dtype)
+    from .patchgan import NLayerDiscriminator
+    skip = set()
     for m in root.modules():
+        if isinstance(m, NLayerDiscriminator):
+            m.fmt = disc_format(fmt)
+            skip.update(id(c) for c in m.modules())
+    for m in root.modules():
+        if id(m) in skip:
+            continue
         m.fmt = fmt
         spec = getattr(m, "spec", None)
         if isinstance(spec, ConvSpec):
@@ -282,8 +342,23 @@ def grad_dst(p):
     return getattr(p, "_odvae_grad_dst", None)
 
 
+_PROBE = [0]  # > 0 while torch.autograd.grad probes run (PoseLoss.calculate_adaptive_weight)
+
+
+class probe_gradients:
+    """Context: parameter gradients produced inside are returned to autograd as fresh tensors instead of being written
+    into the DDP gradient arena, and the arena's bucket hooks stay quiet (ddp.GradArena.boundary_hook)."""
+
+    def __enter__(self):
+        _PROBE[0] += 1
+
+    def __exit__(self, *exc):
+        _PROBE[0] -= 1
+        return False
+
+
 def _new_grad(p):
-    dst = grad_dst(p)
+    dst = grad_dst(p) if _PROBE[0] == 0 else None
     if dst is not None:
         return dst, True
     return torch.empty(p.shape, dtype=torch.float32, device=p.device), False
@@ -360,8 +435,8 @@ def conv_wgrad_raw(x, dy, spec, w, b):
     db, db_direct = (None, True) if b is None else _new_grad(b)
     nbytes = call("conv2d_wgrad_workspace_bytes", B, H, W, CinP, CoutP, spec.geom, impl)
     ws = workspace(nbytes, x.device, "wgrad")
-    call("conv2d_wgrad", x, dy, dw, db, B, H, W, CinP, CoutP, spec.cin, spec.cout, spec.geom, g, impl, 0, ws,
-         ws.numel())
+    call("conv2d_wgrad", x, dy, dw, db, B, H, W, CinP, CoutP, spec.cin, spec.cout, spec.geom, g, impl, 0,
+         1.0 / gs_of(spec), ws, ws.numel())
     return _ret(dw, dw_direct), _ret(db, db_direct)
 
 
@@ -409,7 +484,7 @@ def gn_apply_pair(x, stats, gamma, beta, silu, fmt):
     return y, y
 
 
-def gn_bwd_raw(x, stats, gamma, beta, dy, silu, dx_add=None, x_code=None, g_code=None):
+def gn_bwd_raw(x, stats, gamma, beta, dy, silu, dx_add=None, x_code=None, g_code=None, pscale=1.0):
     B, H, W, C = x.shape
     x_code = act_code(x.dtype) if x_code is None else x_code
     g_code = act_code(dy.dtype) if g_code is None else g_code
@@ -419,16 +494,18 @@ def gn_bwd_raw(x, stats, gamma, beta, dy, silu, dx_add=None, x_code=None, g_code
     nbytes = call("groupnorm_workspace_bytes", B, H * W, C, GROUPS)
     ws = workspace(nbytes, x.device, "gn")
     call("groupnorm_bwd", x, stats, gamma.detach(), beta.detach(), dy, dx_add, dx, dgamma, dbeta, B, H * W, C,
-         GROUPS, 1 if silu else 0, x_code, g_code, 0, ws, ws.numel())
+         GROUPS, 1 if silu else 0, x_code, g_code, 0, float(pscale), ws, ws.numel())
     return dx, _ret(dgamma, g_direct), _ret(dbeta, b_direct)
 
 
-def gemm_raw(A, Bm, D, M, N, K, batch, lda, ldb, ldd, sA, sB, sD, a_mn, b_mn, alpha=1.0, bias=None, residual=None):
-    """D[b] = alpha * op(A[b]) op(B[b])^T (+bias)(+residual); engine chosen by the operand dtype
-    (bf16 operands -> tcgen05; attention blocks run in bf16 in both 16-bit modes)."""
+def gemm_raw(A, Bm, D, M, N, K, batch, lda, ldb, ldd, sA, sB, sD, a_mn, b_mn, alpha=1.0, bias=None, residual=None,
+             code=None):
+    """D[b] = alpha * op(A[b]) op(B[b])^T (+bias)(+residual); 16-bit operands (format `code`, default bf16) -> tcgen05
+    with D in the same format (fp32 when D is a float tensor); fp32 operands -> the SIMT engine."""
     if A.dtype == torch.bfloat16:
-        call("gemm_bf16", A, Bm, D, M, N, K, batch, lda, ldb, ldd, sA, sB, sD, int(a_mn), int(b_mn),
-             act_code(D.dtype), float(alpha), bias, residual)
+        code = BF16 if code is None else code
+        call("gemm_16", A, Bm, D, M, N, K, batch, lda, ldb, ldd, sA, sB, sD, int(a_mn), int(b_mn), code, code,
+             F32 if D.dtype == torch.float32 else code, float(alpha), bias, residual)
     else:
         call("gemm_simt", A, Bm, D, M, N, K, batch, lda, ldb, ldd, sA, sB, sD, int(a_mn), int(b_mn), F32, F32,
              float(alpha), bias, residual)
@@ -460,27 +537,36 @@ def _c(t):
 # layout conversion at the module boundary (AE.py:223; LD/ldm/models/autoencoder.py:344-349)
 # ------------------------------------------------------------------------------------------------
 class ToNHWC(torch.autograd.Function):
+    """gscale: GradScale of the domain the NHWC side belongs to (its gradient arrives scaled and leaves unscaled)."""
+
     @staticmethod
-    def forward(ctx, x, Cpad, compute_dtype):
+    def forward(ctx, x, Cpad, compute_dtype, gscale=None):
         fmt = format_for(compute_dtype)
-        ctx.C, ctx.fmt = x.shape[1], fmt
+        ctx.C, ctx.fmt, ctx.gscale = x.shape[1], fmt, gscale
         return nchw_to_nhwc_raw(_c(x.float()), Cpad, fmt.fwd)
 
     @staticmethod
     def backward(ctx, dy):
-        return nhwc_to_nchw_raw(_c(dy), ctx.C, ctx.fmt.grad), None, None
+        dx = nhwc_to_nchw_raw(_c(dy), ctx.C, ctx.fmt.grad)
+        gs = ctx.gscale.value if ctx.gscale is not None else 1.0
+        if gs != 1.0:
+            dx.mul_(1.0 / gs)
+        return dx, None, None, None
 
 
 class ToNCHW(torch.autograd.Function):
+    """gscale: GradScale of the NHWC side (the fp32 NCHW gradient is multiplied by it on the way in)."""
+
     @staticmethod
-    def forward(ctx, x, C, compute_dtype=None):
+    def forward(ctx, x, C, compute_dtype=None, gscale=None):
         fmt = format_for(compute_dtype) if compute_dtype is not None else format_of(x)
-        ctx.Cpad, ctx.fmt = x.shape[-1], fmt
+        ctx.Cpad, ctx.fmt, ctx.gscale = x.shape[-1], fmt, gscale
         return nhwc_to_nchw_raw(x, C, fmt.fwd)
 
     @staticmethod
     def backward(ctx, dy):
-        return nchw_to_nhwc_raw(_c(dy.float()), ctx.Cpad, ctx.fmt.grad), None, None
+        gs = ctx.gscale.value if ctx.gscale is not None else 1.0
+        return nchw_to_nhwc_raw(_c(dy.float()), ctx.Cpad, ctx.fmt.grad, scale=gs), None, None, None
 
 
 # ------------------------------------------------------------------------------------------------
@@ -498,8 +584,8 @@ class Conv(torch.autograd.Function):
     def backward(ctx, dy):
         x, w, b = ctx.saved_tensors
         spec, fmt = ctx.spec, ctx.fmt
-        if ctx.out_nchw:  # dec_obj gradient arrives NCHW fp32 (masked-L1 backward): bring it to NHWC
-            dy = nchw_to_nhwc_raw(_c(dy.float()), cpad(spec.cout), fmt.grad)
+        if ctx.out_nchw:  # dec_obj gradient arrives NCHW fp32 (masked-L1 backward): bring it to NHWC, times the domain scale
+            dy = nchw_to_nhwc_raw(_c(dy.float()), cpad(spec.cout), fmt.grad, scale=gs_of(spec))
         else:
             dy = _c(dy)
         dx = None
@@ -514,18 +600,20 @@ class Conv(torch.autograd.Function):
 # ------------------------------------------------------------------------------------------------
 class GroupNormAct(torch.autograd.Function):
     @staticmethod
-    def forward(ctx, x, gamma, beta, silu, fmt=None):
+    def forward(ctx, x, gamma, beta, silu, fmt=None, gscale=None):
         fmt = fmt if fmt is not None else format_of(x)
         stats = gn_stats_of(x, x.shape[-1], fmt.fwd)
-        ctx.silu, ctx.fmt = silu, fmt
+        ctx.silu, ctx.fmt, ctx.gscale = silu, fmt, gscale
         ctx.save_for_backward(x, stats, gamma, beta)
         return gn_apply_raw(x, stats, gamma, beta, silu, fmt.fwd, fmt.fwd)
 
     @staticmethod
     def backward(ctx, dy):
         x, stats, gamma, beta = ctx.saved_tensors
-        dx, dg, db = gn_bwd_raw(x, stats, gamma, beta, _c(dy), ctx.silu, x_code=ctx.fmt.fwd, g_code=ctx.fmt.grad)
-        return dx, dg, db, None, None
+        gs = ctx.gscale.value if ctx.gscale is not None else 1.0
+        dx, dg, db = gn_bwd_raw(x, stats, gamma, beta, _c(dy), ctx.silu, x_code=ctx.fmt.fwd, g_code=ctx.fmt.grad,
+                                pscale=1.0 / gs)
+        return dx, dg, db, None, None, None
 
 
 # ------------------------------------------------------------------------------------------------
@@ -565,12 +653,13 @@ class ResBlock(torch.autograd.Function):
             dsc = dout
         da2 = conv_dgrad_raw(dout, blk.spec2, w2, hw)
         dw2, dc2b = conv_wgrad_raw(a2, dout, blk.spec2, w2, c2b)
-        dh1, dg2, db2 = gn_bwd_raw(h1, s2, g2, b2, da2, True, x_code=fmt.fwd, g_code=fmt.grad)
+        ps = 1.0 / gs_of(blk)
+        dh1, dg2, db2 = gn_bwd_raw(h1, s2, g2, b2, da2, True, x_code=fmt.fwd, g_code=fmt.grad, pscale=ps)
         del da2
         da1 = conv_dgrad_raw(dh1, blk.spec1, w1, hw)
         dw1, dc1b = conv_wgrad_raw(a1, dh1, blk.spec1, w1, c1b)
         del dh1
-        dx, dg1, db1 = gn_bwd_raw(x, s1, g1, b1, da1, True, dx_add=dsc, x_code=fmt.fwd, g_code=fmt.grad)
+        dx, dg1, db1 = gn_bwd_raw(x, s1, g1, b1, da1, True, dx_add=dsc, x_code=fmt.fwd, g_code=fmt.grad, pscale=ps)
         return dx, dg1, db1, dw1, dc1b, dg2, db2, dw2, dc2b, dwn, dnb, None
 
 
@@ -604,11 +693,11 @@ class AttnBlock(torch.autograd.Function):
                  ws.numel())
         else:
             S = torch.empty(B, N, N, dtype=torch.float32, device=x.device)
-            gemm_raw(q, k, S, N, N, C, B, 3 * C, 3 * C, N, N * 3 * C, N * 3 * C, N * N, False, False)
+            gemm_raw(q, k, S, N, N, C, B, 3 * C, 3 * C, N, N * 3 * C, N * 3 * C, N * N, False, False, code=ac)
             call("softmax_rows", S, P, B * N, N, scale, ac)
             del S
         O = torch.empty(B, H, W, C, dtype=dt, device=x.device)
-        gemm_raw(P, v, O, N, C, N, B, N, 3 * C, C, N * N, N * 3 * C, N * C, False, True)
+        gemm_raw(P, v, O, N, C, N, B, N, 3 * C, C, N * N, N * 3 * C, N * C, False, True, code=ac)
         out = conv_fwd_raw(O, blk.spec_proj, wp, bp, residual=x, op=ac, out=fmt.fwd)  # adds into the residual stream
         ctx.blk, ctx.fmt = blk, fmt
         ctx.save_for_backward(x, stats, hn, qkv, P, O, gamma, beta, wq, bq, wk, bk, wv, bv, wp, bp)
@@ -631,35 +720,42 @@ class AttnBlock(torch.autograd.Function):
         dqkv = torch.empty_like(qkv)
         dq, dk, dv = dqkv[..., :C], dqkv[..., C:2 * C], dqkv[..., 2 * C:]
         # dV[j,c] = sum_i P[i,j] dO[i,c]
-        gemm_raw(P, dO, dv, N, C, N, B, N, C, 3 * C, N * N, N * C, N * 3 * C, True, True)
+        gemm_raw(P, dO, dv, N, C, N, B, N, C, 3 * C, N * N, N * C, N * 3 * C, True, True, code=ac)
         # dP[i,j] = sum_c dO[i,c] v[j,c]
         dS = torch.empty(B, N, N, dtype=dt, device=x.device)
+        # fp16: dS = P (dP - delta) / sqrt(C) is ~1/N of the (already scaled) gradient; it is stored times DS_SCALE so that it
+        # stays in fp16's normal range, and the dQ / dK GEMMs divide the factor out again
+        ds_scale = DS_SCALE_FP16 if ac == F16 else 1.0
         if attn_fused(ac, N, C):
             # delta_i = sum_j P_ij dP_ij = sum_c dO_ic O_ic; dS = P * (dO v^T - delta) * scale in the GEMM epilogue
             delta = torch.empty(B * N, dtype=torch.float32, device=x.device)
             call("rowdot", dO, O, delta, B * N, C, C, C, ac)
-            call("attn_dsoftmax", dO, v, P, delta, dS, B, N, C, C, 3 * C, N * C, N * 3 * C, scale, ac)
+            call("attn_dsoftmax", dO, v, P, delta, dS, B, N, C, C, 3 * C, N * C, N * 3 * C, scale * ds_scale, ac)
         else:
             dP = torch.empty(B, N, N, dtype=torch.float32, device=x.device)
-            gemm_raw(dO, v, dP, N, N, C, B, C, 3 * C, N, N * C, N * 3 * C, N * N, False, False)
-            call("softmax_rows_bwd", dP, P, dS, B * N, N, scale, ac)
+            gemm_raw(dO, v, dP, N, N, C, B, C, 3 * C, N, N * C, N * 3 * C, N * N, False, False, code=ac)
+            call("softmax_rows_bwd", dP, P, dS, B * N, N, scale * ds_scale, ac)
             del dP
         # dQ[i,c] = sum_j dS[i,j] k[j,c] ; dK[j,c] = sum_i dS[i,j] q[i,c]
-        gemm_raw(dS, k, dq, N, C, N, B, N, 3 * C, 3 * C, N * N, N * 3 * C, N * 3 * C, False, True)
-        gemm_raw(dS, q, dk, N, C, N, B, N, 3 * C, 3 * C, N * N, N * 3 * C, N * 3 * C, True, True)
+        gemm_raw(dS, k, dq, N, C, N, B, N, 3 * C, 3 * C, N * N, N * 3 * C, N * 3 * C, False, True, alpha=1.0 / ds_scale,
+                 code=ac)
+        gemm_raw(dS, q, dk, N, C, N, B, N, 3 * C, 3 * C, N * N, N * 3 * C, N * 3 * C, True, True, alpha=1.0 / ds_scale,
+                 code=ac)
         del dS
         # fused qkv projection backward: dgrad as a GEMM against the forward packing ([3C][C], N-major view)
         wqkv, _ = blk.fused_qkv(wq, bq, wk, bk, wv, bv, ac)
         dhn = torch.empty_like(hn)
         M = B * N
-        gemm_raw(dqkv, wqkv, dhn, M, C, 3 * C, 1, 3 * C, C, C, 0, 0, 0, False, True)
+        gemm_raw(dqkv, wqkv, dhn, M, C, 3 * C, 1, 3 * C, C, C, 0, 0, 0, False, True, code=ac)
         dwqkv, dbqkv, direct = blk.qkv_grad_buffers(wq, bq)
         impl = conv_impl(ac, B, H, W, C, 3 * C, CONV_1x1)
         nbytes = call("conv2d_wgrad_workspace_bytes", B, H, W, C, 3 * C, CONV_1x1, impl)
         ws = workspace(nbytes, x.device, "wgrad")
-        call("conv2d_wgrad", hn, dqkv, dwqkv, dbqkv, B, H, W, C, 3 * C, C, 3 * C, CONV_1x1, ac, impl, 0, ws,
+        ps = 1.0 / gs_of(blk)
+        call("conv2d_wgrad", hn, dqkv, dwqkv, dbqkv, B, H, W, C, 3 * C, C, 3 * C, CONV_1x1, ac, impl, 0, ps, ws,
              ws.numel())
-        dx, dg, db = gn_bwd_raw(x, stats, gamma, beta, dhn, False, dx_add=dout, x_code=fmt.fwd, g_code=fmt.grad)
+        dx, dg, db = gn_bwd_raw(x, stats, gamma, beta, dhn, False, dx_add=dout, x_code=fmt.fwd, g_code=fmt.grad,
+                                pscale=ps)
         if grad_dst(wq) is not None:  # arena mode: device-to-device copies of the three row blocks
             for i, (w_, b_) in enumerate(((wq, bq), (wk, bk), (wv, bv))):
                 grad_dst(w_).copy_(dwqkv[i * C:(i + 1) * C].view(C, C, 1, 1))
@@ -711,9 +807,11 @@ class UpsampleConv(torch.autograd.Function):
 # ------------------------------------------------------------------------------------------------
 class SampleKL(torch.autograd.Function):
     @staticmethod
-    def forward(ctx, moments, enc_pose, eps, keep, noise, keep_scale, Cz, CzPad, want_z, fmt=None):
+    def forward(ctx, moments, enc_pose, eps, keep, noise, keep_scale, Cz, CzPad, want_z, fmt=None, gs_dec=None, gs_enc=None):
+        """gs_dec / gs_enc: GradScale of the decoder side (the scale dz arrives with) and of the encoder side (the scale
+        dmoments leaves with)."""
         fmt = fmt if fmt is not None else format_of(moments)
-        ctx.fmt = fmt
+        ctx.fmt, ctx.gs = fmt, (gs_dec, gs_enc)
         B, H, W, ld = moments.shape
         HW = H * W
         dev = moments.device
@@ -743,11 +841,13 @@ class SampleKL(torch.autograd.Function):
         dlogvar = None if dlogvar is None else _c(dlogvar.float())
         dmom = torch.empty(B, H, W, ld, dtype=dtype, device=dev)
         dpose = torch.empty(B, Cz * H * W, dtype=torch.float32, device=dev) if (has_pose and dz is not None) else None
+        gs_dec = ctx.gs[0].value if ctx.gs[0] is not None else 1.0
+        gs_enc = ctx.gs[1].value if ctx.gs[1] is not None else 1.0
         call("sample_kl_bwd", dz, dkl, dmean, dlogvar, mean, logvar, eps, keep, keep_scale, dmom, dpose, B, H * W, Cz,
-             CzPad, ld, ctx.fmt.grad)
+             CzPad, ld, ctx.fmt.grad, 1.0 / gs_dec, gs_enc)
         if has_pose and dpose is None:
             dpose = torch.zeros(B, Cz * H * W, dtype=torch.float32, device=dev)
-        return dmom, dpose, None, None, None, None, None, None, None, None
+        return dmom, dpose, None, None, None, None, None, None, None, None, None, None
 
 
 # ------------------------------------------------------------------------------------------------

@@ -76,7 +76,10 @@ def fill_state_dict_(sd, seed=23):
         if t.ndim == 0:
             v = torch.full((), 0.1)
         elif t.ndim == 1:
-            if "norm" in key and key.endswith("weight"):
+            bn = key.startswith("loss.discriminator.") and t.numel() > 1 and not key.endswith(".bias")
+            if key.endswith("running_var"):
+                v = 1.0 + 0.5 * torch.rand(t.shape, generator=g)
+            elif ("norm" in key and key.endswith("weight")) or (bn and key.endswith("weight")):
                 v = 1.0 + 0.1 * torch.randn(t.shape, generator=g)
             else:
                 v = 0.05 * torch.randn(t.shape, generator=g)

@@ -104,10 +104,12 @@ int odvae_conv2d_dgrad(const void* dy, const void* w_packed_dgrad, const void* d
                        int W, int CinP, int CoutP, int geom, int act_dtype, int impl, void* stream);
 /* dw (fp32 OIHW [Cout,Cin,kh,kw]) = sum over batch/pixels of dy (x) x ; db[Cout] = sum dy.
  * Deterministic: split-K partials go to `workspace` and are reduced in a fixed order.
- * accumulate != 0 adds into dw/db instead of overwriting. db may be NULL. */
+ * accumulate != 0 adds into dw/db instead of overwriting. db may be NULL.
+ * out_scale multiplies dw and db: the inverse of the static power-of-two scale that 16-bit activation gradients carry in
+ * the all-fp16 mode (1.0 otherwise). */
 size_t odvae_conv2d_wgrad_workspace_bytes(int B, int H, int W, int CinP, int CoutP, int geom, int impl);
 int odvae_conv2d_wgrad(const void* x, const void* dy, float* dw_oihw, float* db, int B, int H, int W, int CinP,
-                       int CoutP, int Cin, int Cout, int geom, int act_dtype, int impl, int accumulate,
+                       int CoutP, int Cin, int Cout, int geom, int act_dtype, int impl, int accumulate, float out_scale,
                        void* workspace, size_t ws_bytes, void* stream);
 
 /* nearest-neighbour 2x upsample (F.interpolate, model.py:54) and its adjoint (2x2 sum-pool) */
@@ -176,10 +178,11 @@ int odvae_groupnorm_apply(const void* x, const float* stats, const float* gamma,
                           int B, int HW, int C, int G, int silu, int in_dtype, int out_dtype, int out2_dtype,
                           void* stream);
 /* dx = d/dx [silu](GN(x)) . dy (+ dx_add);  dgamma/dbeta fp32 [C] (accumulate != 0 adds).
- * act_dtype = format of x, grad_dtype = format of dy / dx_add / dx: (f32,f32), (bf16,bf16) or (fp16,bf16). */
+ * act_dtype = format of x, grad_dtype = format of dy / dx_add / dx: (f32,f32), (bf16,bf16), (fp16,bf16), (fp16,fp16).
+ * pgrad_scale multiplies dgamma / dbeta (inverse of the static activation-gradient scale of the all-fp16 mode). */
 int odvae_groupnorm_bwd(const void* x, const float* stats, const float* gamma, const float* beta, const void* dy,
                         const void* dx_add, void* dx, float* dgamma, float* dbeta, int B, int HW, int C, int G,
-                        int silu, int act_dtype, int grad_dtype, int accumulate, void* workspace, size_t ws_bytes,
+                        int silu, int act_dtype, int grad_dtype, int accumulate, float pgrad_scale, void* workspace, size_t ws_bytes,
                         void* stream);
 
 /* ---------------------------------------------------------------------------------------------
@@ -211,11 +214,13 @@ int odvae_sample_kl_fwd(const void* moments, const float* eps, const uint8_t* ke
                         const float* enc_pose, float keep_scale, float* mean, float* logvar, void* z,
                         float* kl, int B, int HW, int Cz, int CzPad, int ld_moments, int act_dtype, void* stream);
 /* dmoments = d(z)/d(moments)^T dz + dkl[b] * dKL/dmoments (+ direct grads on mean/logvar outputs).
- * dz: NHWC act_dtype [B,HW,CzPad]; denc_pose fp32 [B,Cz*HW] (NCHW flattened) = dz. */
+ * dz: NHWC act_dtype [B,HW,CzPad]; denc_pose fp32 [B,Cz*HW] (NCHW flattened) = dz * dz_scale.
+ * dz_scale / out_scale: the decoder-side gradient arrives multiplied by a static scale (dz_scale = its inverse) and the
+ * encoder-side gradient leaves multiplied by out_scale (all-fp16 mode; 1.0 otherwise). act_dtype f32 / bf16 / fp16. */
 int odvae_sample_kl_bwd(const void* dz, const float* dkl, const float* dmean_direct, const float* dlogvar_direct,
                         const float* mean, const float* logvar, const float* eps, const uint8_t* keep,
                         float keep_scale, void* dmoments, float* denc_pose, int B, int HW, int Cz, int CzPad,
-                        int ld_moments, int act_dtype, void* stream);
+                        int ld_moments, int act_dtype, float dz_scale, float out_scale, void* stream);
 
 /* ---------------------------------------------------------------------------------------------
  * Masked L1 reconstruction term (PoseLoss._get_rec_loss/_get_nll_loss LOSS.py:134-158, masks :250-257)
@@ -329,6 +334,44 @@ int odvae_lpips_level_bwd(const void* f0, const void* f1, const float* w, const 
 size_t odvae_colsum_workspace_bytes(int cols);
 int odvae_colsum(const void* m, int64_t rows, int cols, int ld, int dtype, float* out, int accumulate,
                  void* workspace, size_t ws_bytes, void* stream);
+
+/* ---------------------------------------------------------------------------------------------
+ * PatchGAN discriminator. Call sites: src/modules/losses/contperceptual.py:280-301 (generator side:
+ * logits_fake = discriminator(reconstructions)) and :352-375 (discriminator side) ->
+ * taming.modules.discriminator.model.NLayerDiscriminator (un-vendored; public definition in SURVEY appendix B:
+ * Conv2d(k=4, s=2|1, p=1) [+ BatchNorm2d, training mode] + LeakyReLU(0.2)). Each conv = im2col + GEMM
+ * (odvae_gemm_16 / odvae_gemm_simt); these are the kernels around the GEMMs. dtypes: ODVAE_F32 / BF16 / F16.
+ * ------------------------------------------------------------------------------------------- */
+/* patches[m][(r*4+s)*C + c] = act(src[b, oy*stride-1+r, ox*stride-1+s, c]) (zero outside the image), m = (b, oy, ox),
+ * Ho = (H-2)/stride + 1.  src_nchw = 0: src NHWC [B,H,W,C] (C % 8 == 0, Kp == 16 C), act(v) = lrelu(v*scale[c]+shift[c])
+ * when scale != NULL (the previous layer's train-mode BatchNorm folded in), lrelu(v) when slope != 1, else identity.
+ * src_nchw = 1: src NCHW fp32 [B,C,H,W] with small C (the image), times mask[B,H,W] when given (`x * mask_2d_bbox`,
+ * contperceptual.py:250-257), Kp >= 16 C (columns beyond are zero). */
+int odvae_patchgan_im2col(const void* src, const float* mask, const float* scale, const float* shift, float slope,
+                          void* dst, int B, int H, int W, int C, int stride, int Kp, int src_nchw, int src_dtype,
+                          int dst_dtype, void* stream);
+/* gather-form inverse: dst[b,iy,ix,c] = lrelu'(u) * sum_{(r,s) reaching (iy,ix)} dP[m][(r*4+s)*C + c], u = ypre*scale+shift
+ * (scale NULL: u = ypre).  dst_nchw = 1: gradient w.r.t. the NCHW fp32 image (times mask), no activation derivative. */
+int odvae_patchgan_col2im(const void* dP, const void* ypre, const float* scale, const float* shift, float slope,
+                          const float* mask, void* dst, int B, int H, int W, int C, int stride, int Kp, int dst_nchw,
+                          int dp_dtype, int y_dtype, int dst_dtype, void* stream);
+/* torch.nn.BatchNorm2d in training mode over y[M][C] (M = B*H*W rows): batch mean / biased variance -> scale = gamma*rstd,
+ * shift = beta - mean*scale (consumed by the next odvae_patchgan_im2col), mean and rstd saved for backward; running_mean,
+ * running_var (unbiased, momentum) and num_batches_tracked updated in place when given. Deterministic two-stage sums. */
+size_t odvae_bn_workspace_bytes(int64_t M, int C);
+int odvae_bn_train_stats(const void* y, int64_t M, int C, int dtype, const float* gamma, const float* beta, float eps,
+                         float momentum, float* running_mean, float* running_var, int64_t* num_batches_tracked,
+                         float* scale, float* shift, float* mean, float* rstd, void* workspace, size_t ws_bytes,
+                         void* stream);
+/* dyp (in: gradient w.r.t. the BatchNorm output, already times lrelu'; out: gradient w.r.t. y), dgamma / dbeta (+)= */
+int odvae_bn_train_bwd(const void* y, void* dyp, int64_t M, int C, int y_dtype, int g_dtype, const float* gamma,
+                       const float* mean, const float* rstd, float* dgamma, float* dbeta, int accumulate,
+                       void* workspace, size_t ws_bytes, void* stream);
+/* fp32 OIHW [Cout][Cin][4][4] -> [CoutP][Kp], k = (r*4+s)*Cin + c, zero padded; and the inverse for weight gradients:
+ * dw (+)= sum over nsplit slabs part[split][CoutP][Kp] (fixed order) */
+int odvae_pack_k4_weight(const float* w, void* out, int Cout, int Cin, int CoutP, int Kp, int dtype, void* stream);
+int odvae_unpack_k4_wgrad(const float* part, int nsplit, float* dw, int Cout, int Cin, int CoutP, int Kp, int accumulate,
+                          void* stream);
 
 #if defined(__GNUC__)
 #pragma GCC visibility pop

@@ -131,6 +131,37 @@ def pose_encoder(sd, z, n=16, m=16, pre="pose_encoder"):  # pose_encoder.py:100-
 
 
 # --------------------------------------------------------------------------------------------
+# PatchGAN discriminator: taming.modules.discriminator.model.NLayerDiscriminator(input_nc=3, ndf=64, n_layers=3)
+# (un-vendored, PARITY UNPINNED; public definition in SURVEY appendix B). BatchNorm2d in training mode: batch statistics,
+# running statistics updated in place in `sd` (momentum 0.1, unbiased variance) like torch.nn.BatchNorm2d.
+# --------------------------------------------------------------------------------------------
+def discriminator(sd, x, pre="loss.discriminator.main", n_layers=3, training=True):
+    idx = 0
+    h = F.leaky_relu(F.conv2d(x, sd["%s.%d.weight" % (pre, idx)], sd["%s.%d.bias" % (pre, idx)], stride=2, padding=1), 0.2)
+    idx = 2
+    for n in range(1, n_layers + 1):
+        stride = 2 if n < n_layers else 1
+        h = F.conv2d(h, sd["%s.%d.weight" % (pre, idx)], None, stride=stride, padding=1)
+        bn = "%s.%d" % (pre, idx + 1)
+        nbt = sd.get(bn + ".num_batches_tracked")
+        if training and nbt is not None:
+            nbt += 1
+        h = F.batch_norm(h, sd[bn + ".running_mean"], sd[bn + ".running_var"], sd[bn + ".weight"], sd[bn + ".bias"],
+                         training=training, momentum=0.1, eps=1e-5)
+        h = F.leaky_relu(h, 0.2)
+        idx += 3
+    return F.conv2d(h, sd["%s.%d.weight" % (pre, idx)], sd["%s.%d.bias" % (pre, idx)], stride=1, padding=1)
+
+
+def hinge_d_loss(logits_real, logits_fake):  # taming vqperceptual (same per-term form as LD vqperceptual.py:11-18)
+    return 0.5 * (torch.mean(F.relu(1.0 - logits_real)) + torch.mean(F.relu(1.0 + logits_fake)))
+
+
+def adopt_weight(weight, global_step, threshold=0, value=0.0):  # LD vqperceptual.py:20-23
+    return value if global_step < threshold else weight
+
+
+# --------------------------------------------------------------------------------------------
 # distributions (DIST:24-62, SDIST:5-41)
 # --------------------------------------------------------------------------------------------
 class Gaussian:
@@ -216,6 +247,10 @@ class Oracle:
         self.labels = labels
         self.pretrain = self.lp["encoder_pretrain_steps"]
         self.priors = prior_table(dataset_stats, labels, model_params.get("train_on_yaw", True))
+        self.has_disc = "loss.discriminator.main.0.weight" in sd
+        # arithmetic type: float32 like the reference; float64 (sd given in double) is the "which side owns the error"
+        # probe of tests/golden/make_golden.py -- the reference itself casts its inputs with .float() and cannot run in fp64
+        self.dt = sd["encoder.conv_in.weight"].dtype
 
     def encode(self, x):  # AE:176-182
         h = encoder(self.sd, self.dd, x)
@@ -227,7 +262,7 @@ class Oracle:
     def forward(self, x, step, noise):
         """noise = (eps_obj, keep{0,1}, z_noise, eps_bbox): the reference's four random draws."""
         eps_obj, keep, z_noise, eps_bbox = noise
-        x = x.contiguous().float()
+        x = x.contiguous().to(self.dt)
         post, pose_feat = self.encode(x)
         z = post.mean + post.std * eps_obj  # DIST:35-37
         p = dropout_prob(step, self.mp, self.pretrain)
@@ -289,14 +324,30 @@ class Oracle:
 
         w_pose, w_class = lp["pose_weight"] * pose_loss, lp["class_weight"] * class_loss
         w_bbox, w_fill = lp["bbox_weight"] * bbox_loss, lp["fill_factor_weight"] * fill_loss
-        if step > self.pretrain:  # LOSS:313-321 (disc_factor = 0 -> GAN term contributes exactly 0)
+        # generator side of the GAN (LOSS:280-304); discriminator parameters are treated as constants here (Lightning's
+        # toggle_optimizer freezes them during the optimizer_idx 0 step)
+        g_loss, d_weight = torch.tensor(0.0), torch.tensor(0.0)
+        disc_cfg = lp.get("disc_factor", 1.0)
+        disc_factor = adopt_weight(disc_cfg, step, threshold=lp.get("disc_start", 0))
+        if self.has_disc:
+            dsd = {k: (v.detach() if "running" in k else v) for k, v in sd.items()
+                   if k.startswith("loss.discriminator.")}
+            logits_fake = discriminator(dsd, (dec_obj * mask_2d_bbox).contiguous()) * mask_bg.view(-1, 1, 1, 1)
+            g_loss = -torch.mean(logits_fake)
+            if disc_cfg > 0.0 and step > self.pretrain:  # LD contperceptual.py:32-43
+                last = sd["decoder.conv_out.weight"]
+                nll_g = torch.autograd.grad(nll, last, retain_graph=True)[0]
+                g_g = torch.autograd.grad(g_loss, last, retain_graph=True)[0]
+                d_weight = torch.clamp(torch.norm(nll_g) / (torch.norm(g_g) + 1e-4), 0.0, 1e4).detach() \
+                    * lp.get("disc_weight", 1.0)
+        if step > self.pretrain:  # LOSS:313-321
             loss = w_pose + 0.0 + nll + w_class + w_bbox + w_fill + lp["kl_weight_obj"] * kl_obj \
-                + lp["kl_weight_bbox"] * kl_bbox
+                + lp["kl_weight_bbox"] * kl_bbox + d_weight * disc_factor * g_loss
         else:
             loss = w_pose + w_class + w_bbox + w_fill + lp["kl_weight_bbox"] * kl_bbox
         d = lambda t: float(torch.as_tensor(t).detach().float().mean())
         log = {"total_loss": d(loss), "logvar": d(logvar), "kl_loss_obj": d(kl_obj), "nll_loss": d(nll),
-               "weighted_nll_loss": d(nll), "rec_loss": d(rec), "d_weight": 0.0, "disc_factor": 0.0,
+               "weighted_nll_loss": d(nll), "rec_loss": d(rec), "d_weight": d(d_weight), "disc_factor": float(disc_factor), "g_loss": d(g_loss),
                "pose_loss": d(pose_loss), "weighted_pose_loss": d(w_pose), "mask_loss": 0.0,
                "weighted_mask_loss": 0.0, "class_loss": d(class_loss), "weighted_class_loss": d(w_class),
                "bbox_loss": d(bbox_loss), "weighted_bbox_loss": d(w_bbox), "t1_loss": d(t1), "t2_loss": d(t2),
@@ -306,15 +357,34 @@ class Oracle:
                "weighted_fill_factor_loss": d(w_fill)}
         return loss, {"%s/%s" % (split, k): v for k, v in log.items()}
 
+    def discriminator_step(self, batch, step, noise, split="train"):
+        """AE:321-330 + LOSS:352-375 (optimizer_idx = 1): disc_factor * hinge(D(x m) mask_bg, D(x_hat m) mask_bg) on detached
+        images. Returns (d_loss, log)."""
+        rgb_gt = rescale(batch["patch"].to(self.dt))
+        with torch.no_grad():
+            dec_obj = self.forward(rgb_gt, step, noise)[0]
+        class_gt = batch["class_id"]
+        mask_bg = torch.zeros_like(class_gt)
+        mask_bg[class_gt != BACKGROUND_CLASS_IDX] = 1
+        m2 = batch["mask_2d_bbox"]
+        dsd = {k: v for k, v in self.sd.items() if k.startswith("loss.discriminator.")}
+        logits_real = discriminator(dsd, (rgb_gt * m2).contiguous().detach()) * mask_bg.view(-1, 1, 1, 1)
+        logits_fake = discriminator(dsd, (dec_obj * m2).contiguous().detach()) * mask_bg.view(-1, 1, 1, 1)
+        disc_factor = adopt_weight(self.lp.get("disc_factor", 1.0), step, threshold=self.lp.get("disc_start", 0))
+        d_loss = disc_factor * hinge_d_loss(logits_real, logits_fake)
+        log = {"disc_loss": float(d_loss.detach()), "logits_real": float(logits_real.detach().mean()),
+               "logits_fake": float(logits_fake.detach().mean())}
+        return d_loss, {"%s/%s" % (split, k): v for k, v in log.items()}
+
     def training_step(self, batch, step, noise):
         """AE:295-319 with optimizer_idx = 0. Returns (loss, log, forward outputs)."""
-        rgb_gt = rescale(batch["patch"].float())  # get_input's permute round trip is an identity on values
+        rgb_gt = rescale(batch["patch"].to(self.dt))  # get_input's permute round trip is an identity on values
         pose_gt = batch["pose_6d"].clone()
         pose_gt[:, 3] = batch["yaw"]  # AE:262-265
-        pose_gt = pose_gt.float()
+        pose_gt = pose_gt.to(self.dt)
         out = self.forward(rgb_gt, step, noise)
         dec_obj, dec_pose, post, bbox_post, _ = out
         loss, log = self.loss(rgb_gt, pose_gt, dec_obj, dec_pose, batch["class_id"], batch["class_name"],
-                              batch["bbox_sizes"], batch["fill_factor"].float(), post, bbox_post, step,
-                              batch["mask_2d_bbox"])
+                              batch["bbox_sizes"].to(self.dt), batch["fill_factor"].to(self.dt), post, bbox_post, step,
+                              batch["mask_2d_bbox"].to(self.dt))
         return loss, log, out

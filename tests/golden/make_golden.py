@@ -7,10 +7,12 @@ Run in the build container only (the reference tree is not on the GPU box):
     python tests/golden/make_golden.py small_s80000_b3
 
 Each case file holds: the case spec (seeds, geometry, global_step), the four noise draws the
-reference consumed, the forward outputs, the loss + 26-entry log dict, and per-parameter gradient
-summaries (l2 norm, sum, 32 sampled elements) for every trainable tensor. Inputs and weights are
+reference consumed, the forward outputs, the loss + 26-entry log dict, and for every trainable tensor the
+reference gradient itself (whole when it has <= 16384 elements, else a fixed RNG-free subset of 16384 elements)
+plus summaries (l2 norm, sum, 32 sampled elements). Inputs and weights are
 NOT stored: they are pure functions of the seeds (odvae_b200/synth.py).
 """
+import math
 import os
 import pickle
 import sys
@@ -37,6 +39,11 @@ CASES = {
     "small_s35000_b2": ("small", 64, 2, 35000, 26, 104, None),
     "small_s130000_b4": ("small", 64, 4, 130000, 27, 105, None),
     "small_s80000_allbg": ("small", 64, 2, 80000, 28, 106, 1),
+    # GAN on (disc_factor = 1.0, the yaml's default; perceptual_weight stays 0: LPIPS weights are not available offline):
+    # adaptive d_weight + generator term in the optimizer_idx 0 step, and the optimizer_idx 1 (discriminator) step
+    "small_s80000_gan_b3": ("small", 64, 3, 80000, 29, 107, None, {"disc_factor": 1.0}),
+    "small_s30000_gan_b2": ("small", 64, 2, 30000, 30, 108, None, {"disc_factor": 1.0}),
+    "full_s80000_gan_b2": ("full", 256, 2, 80000, 31, 109, None, {"disc_factor": 1.0}),
 }
 
 
@@ -45,11 +52,29 @@ def sample_indices(key, numel, n=32):
     return torch.randint(0, numel, (min(n, numel),), generator=g)
 
 
+FULL_GRAD_CAP = 16384  # tensors up to this many elements are stored whole; larger ones as a fixed subset of this size
+
+
+def subset_indices(numel, cap=FULL_GRAD_CAP):
+    """Deterministic, RNG-free element subset of a large tensor: idx_i = (a * i + b) mod numel with a prime multiplier
+    coprime to numel (distinct indices, no alignment with the tensor's tap / channel strides)."""
+    if numel <= cap:
+        return None
+    a = next(q for q in (1000003, 1000033, 1000037, 1000039) if math.gcd(q, numel) == 1)
+    return (torch.arange(cap, dtype=torch.int64) * a + 12345) % numel
+
+
 def grad_summary(key, g):
     flat = g.detach().reshape(-1).double()
     idx = sample_indices(key, flat.numel())
+    sub = subset_indices(flat.numel())
+    ref = g.detach().reshape(-1).float()
     return {"l2": float(flat.norm()), "sum": float(flat.sum()), "abs_sum": float(flat.abs().sum()),
-            "idx": idx, "val": g.detach().reshape(-1)[idx].clone(), "shape": tuple(g.shape)}
+            "absmax": float(flat.abs().max()),
+            "idx": idx, "val": g.detach().reshape(-1)[idx].clone(), "shape": tuple(g.shape),
+            # the reference gradient itself (whole tensor, or the subset_indices() elements of a large one), so the
+            # parity tests can bound ||g - g_ref|| / ||g_ref|| per tensor instead of comparing norms
+            "ref": (ref if sub is None else ref[sub]).clone(), "ref_is_subset": sub is not None}
 
 
 def tensor_summary(t):
@@ -59,13 +84,15 @@ def tensor_summary(t):
 
 
 def run_case(name):
-    cfg_name, R, B, step, bseed, nseed, class_override = CASES[name]
+    cfg_name, R, B, step, bseed, nseed, class_override = CASES[name][:7]
+    loss_override = CASES[name][7] if len(CASES[name]) > 7 else {}
     ddconfig = synth.DDCONFIG if cfg_name == "full" else synth.DDCONFIG_SMALL
     tmp = tempfile.mkdtemp()
     stats_path = os.path.join(tmp, "all.pkl")
     with open(stats_path, "wb") as f:
         pickle.dump(synth.synthetic_dataset_stats(23), f)
     params = synth.model_config(ddconfig, stats_path)
+    params["lossconfig"]["params"].update(loss_override)
     torch.manual_seed(23)
     model = ref_shim.build_reference_model(params, step)
     synth.fill_state_dict_(model.state_dict(), seed=23)
@@ -154,10 +181,30 @@ def run_case(name):
         else:
             grads[k] = grad_summary(k, p.grad)
 
+    disc = None
+    if loss_override.get("disc_factor", 0.0) > 0:
+        # optimizer_idx 1 on the same batch with the same four draws (AE.py:321-330): d_loss, its log, the discriminator's
+        # parameter gradients and the BatchNorm running statistics after the three discriminator forwards of this batch
+        model.zero_grad(set_to_none=True)
+        torch.manual_seed(nseed)
+        b3 = {k: (v.clone() if torch.is_tensor(v) else list(v)) for k, v in batch.items()}
+        hd = model.loss.register_forward_hook(loss_hook)
+        d_loss = model.training_step(b3, 0, 1)
+        hd.remove()
+        d_loss.backward()
+        d_log = cap["loss_out"][1]
+        dgrads = {k: grad_summary(k, p.grad) for k, p in model.named_parameters()
+                  if k.startswith("loss.discriminator") and p.grad is not None}
+        disc = {"loss": float(d_loss.detach()),
+                "log": {k: float(torch.as_tensor(v).detach().float().mean()) for k, v in d_log.items()},
+                "grads": dgrads,
+                "buffers": {k: v.detach().clone() for k, v in model.state_dict().items()
+                            if k.startswith("loss.discriminator") and ("running" in k or "num_batches" in k)}}
+
     out = {
         "spec": {"name": name, "ddconfig": cfg_name, "resolution": R, "batch": B, "global_step": step,
                  "batch_seed": bseed, "noise_seed": nseed, "weight_seed": 23, "stats_seed": 23,
-                 "class_override": class_override, "dropout_p": p_drop,
+                 "class_override": class_override, "dropout_p": p_drop, "loss_override": loss_override,
                  "torch": torch.__version__, "reference_commit": "b09216ca0249d767eab18ebc8afb8bf69ded44e3",
                  "cpu_seconds_fwd_bwd": dt},
         "noise": {"eps_obj": eps_obj, "keep": keep.to(torch.uint8), "noise": noise, "eps_bbox": eps_bbox},
@@ -173,6 +220,7 @@ def run_case(name):
         "grads": grads,
         "params_without_grad": nograd,
         "acts": acts,
+        "disc": disc,
     }
     path = os.path.join(HERE, name + ".pt")
     torch.save(out, path)

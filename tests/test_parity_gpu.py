@@ -22,7 +22,8 @@ FP32_TOL = 1e-4
 # deep latents / reconstructions; the bound asserted here is what bf16 storage can deliver and is stated as such.
 BF16_TOL = 3e-2
 BF16_LOSS_TOL = 1e-2
-FP32_GRAD_TOL = 2e-3
+FP32_FULL_GRAD_TOL = 3e-3  # full config only: the reference's own fp32 L1-sign noise (measured here: 1.2e-3)
+FP32_GRAD_TOL = 1e-4  # per tensor: ||g - g_ref||_2 / ||g_ref||_2 and max|g - g_ref| / max|g_ref| (north_star: fp32 <= 1e-4)
 # bf16 gradients, per tensor |l2 - ref| / ref: measured median ~1e-3, 99% of tensors < 3e-2; the few tensors whose
 # gradient is a small residual of large cancelling sums (pose_encoder.latent_linear, post_quant_conv.bias) reach 5-10e-2
 BF16_GRAD_L2_TOL = 1.5e-1
@@ -70,9 +71,7 @@ def check_outputs(g, model, loss, out, tol, loss_tol=None):
     assert H.rel_scalar(loss, g["loss"]) < loss_tol
     log = model.logged
     for k, ref in g["log"].items():
-        if k.endswith("g_loss"):  # discriminator forward is SURVEY 8 f2 (next); GAN term is exactly 0 in the total
-            continue
-        assert k in log, k
+        assert k in log, k  # incl. g_loss: the discriminator forward runs on every optimizer_idx 0 step (LOSS.py:285)
         assert H.rel_scalar(log[k], ref, floor=1e-6) < loss_tol, (k, float(log[k]), ref)
 
 
@@ -83,9 +82,13 @@ def test_fp32_mode_matches_reference(name):
     grads = {k: p.grad for k, p in model.named_parameters()}
     for k in g["params_without_grad"]:
         assert grads[k] is None or float(grads[k].abs().max()) == 0.0, k
-    errs = H.grad_errors(grads, g["grads"])
+    errs = H.grad_diff_errors(grads, g["grads"])
     worst = max(errs.items(), key=lambda kv: max(kv[1]))
-    assert max(worst[1]) < FP32_GRAD_TOL, worst
+    # full config: bounded by the fp32 REFERENCE's own noise instead of 1e-4 -- a 1e-6 difference in dec_obj flips the sign of
+    # a few of the 2 x 196608 L1 terms with |x - x_hat| ~ 0, which moves every upstream gradient by ~1e-3 (tests/test_oracle_cpu.py:
+    # the float64 oracle sits 3-5e-4 from the fp32 reference there, and 2e-6 on the small cases)
+    tol = FP32_GRAD_TOL if name.startswith("small") else FP32_FULL_GRAD_TOL
+    assert max(worst[1]) < tol, (worst, H.error_table(errs))
 
 
 @pytest.mark.parametrize("name", H.CASES)
@@ -101,24 +104,42 @@ def test_bf16_mode_matches_reference(name):
     assert l2s[int(0.97 * len(l2s))] < 3e-2
 
 
-# mixed mode (compute_dtype=torch.float16: fp16 forward tensors, bf16 attention blocks and gradients, fp32
-# accumulation): meets the north_star's 16-bit tolerance of 1e-2 on latents, reconstructions and losses.
-MIXED_TOL = 1e-2
+# fp16 mode (compute_dtype=torch.float16, the TIMED mode): every 16-bit tensor is IEEE fp16 (activations, weights, attention,
+# and activation gradients with a static power-of-two scale per domain), fp32 accumulation. It meets the north_star's 16-bit
+# tolerance of 1e-2 on latents, reconstructions, losses AND gradients, the latter asserted per parameter tensor on the
+# difference: ||g - g_ref||_2 / ||g_ref||_2 (and max|g - g_ref| / max|g_ref| with 3x slack for the single worst element).
+FP16_TOL = 1e-2
+FP16_GRAD_TOL = 1e-2
 
 
 @pytest.mark.parametrize("name", H.CASES)
-def test_mixed_mode_matches_reference(name):
+def test_fp16_mode_matches_reference(name):
     g, model, loss, out = run_product(name, torch.float16)
-    check_outputs(g, model, loss, out, MIXED_TOL, MIXED_TOL)
-    # gradients, per parameter tensor |l2 - ref| / ref: >= 99% of the 358 tensors within 1e-2 and none beyond 2e-2
-    # (measured: median 1e-3, worst 0.7-1.3e-2 on pose_encoder.latent_linear.weight, whose gradient is a small residual
-    # of large cancelling sums: profiles/r01_mixed_errors.txt); sampled elements are reported there, not bounded
+    check_outputs(g, model, loss, out, FP16_TOL, FP16_TOL)
     grads = {k: p.grad for k, p in model.named_parameters()}
-    errs = H.grad_errors(grads, g["grads"], zero_grad_slack=1e-1)
-    bad = {k: v for k, v in errs.items() if v[0] >= 2 * MIXED_TOL}
-    assert not bad, sorted(bad.items(), key=lambda kv: -kv[1][0])[:5]
-    l2s = sorted(v[0] for v in errs.values())
-    assert l2s[int(0.99 * len(l2s)) - 1] < MIXED_TOL
+    for k in g["params_without_grad"]:
+        assert grads[k] is None or float(grads[k].abs().max()) == 0.0, k
+    errs = H.grad_diff_errors(grads, g["grads"])
+    print(name, H.error_table(errs, 4))
+    worst = max(errs.items(), key=lambda kv: kv[1][0])
+    assert worst[1][0] < FP16_GRAD_TOL, (worst, H.error_table(errs))
+    worst_abs = max(errs.items(), key=lambda kv: kv[1][1])
+    assert worst_abs[1][1] < 3 * FP16_GRAD_TOL, (worst_abs, H.error_table(errs))
+
+
+# the round-1 "mixed" mode (fp16 forward, bf16 attention and gradients), kept for A/B runs: forward outputs within 1e-2,
+# gradients limited by bf16 storage (measured round 2: per-tensor relative L2 of the difference median 1e-2, max 3.4e-2)
+MIXED_TOL = 1e-2
+
+
+@pytest.mark.parametrize("name", ["small_s80000_b3", "full_s80000_b2"])
+def test_mixed_mode_matches_reference(name):
+    g, model, loss, out = run_product(name, "mixed")
+    check_outputs(g, model, loss, out, MIXED_TOL, MIXED_TOL)
+    grads = {k: p.grad for k, p in model.named_parameters()}
+    errs = H.grad_diff_errors(grads, g["grads"])
+    worst = max(errs.items(), key=lambda kv: kv[1][0])
+    assert worst[1][0] < 6e-2, (worst, H.error_table(errs))
 
 
 def _full_size_batch(g, B):
@@ -154,7 +175,7 @@ def _run_full(params, batch, noise, step, dtype=torch.float16):
 
 
 def test_full_size_batch64_per_sample_parity_and_permutation():
-    """The train step at BASELINE's full size (full config, 256x256 crops, batch 64, timed mixed mode). Every op on the
+    """The train step at BASELINE's full size (full config, 256x256 crops, batch 64, timed fp16 mode). Every op on the
     path is per-sample, so (1) slots 0-1 must reproduce the reference's B=2 golden outputs within the 16-bit
     tolerance although they now run inside batch-64 tiles, (2) permuting the batch permutes the outputs, bit for bit
     (tiles are visited in a different order, the arithmetic per sample is the same), and (3) the whole-batch loss and
@@ -165,11 +186,11 @@ def test_full_size_batch64_per_sample_parity_and_permutation():
     model, loss, out = _run_full(params, batch, noise, step)
     dec_obj, dec_pose, post, bbox_post = out
     assert dec_obj.shape == (B, 3, 256, 256) and torch.isfinite(loss)
-    assert H.rel_l2(dec_obj[:2], g["out"]["dec_obj"]) < MIXED_TOL
-    assert H.rel_max(dec_pose[:2], g["out"]["dec_pose"]) < MIXED_TOL
-    assert H.rel_max(post.mean[:2], g["out"]["posterior_mean"]) < MIXED_TOL
-    assert H.rel_max(post.logvar[:2], g["out"]["posterior_logvar"]) < MIXED_TOL
-    assert H.rel_max(bbox_post.mean[:2], g["out"]["bbox_mean"]) < MIXED_TOL
+    assert H.rel_l2(dec_obj[:2], g["out"]["dec_obj"]) < FP16_TOL
+    assert H.rel_max(dec_pose[:2], g["out"]["dec_pose"]) < FP16_TOL
+    assert H.rel_max(post.mean[:2], g["out"]["posterior_mean"]) < FP16_TOL
+    assert H.rel_max(post.logvar[:2], g["out"]["posterior_logvar"]) < FP16_TOL
+    assert H.rel_max(bbox_post.mean[:2], g["out"]["bbox_mean"]) < FP16_TOL
     for k, p in model.named_parameters():
         if p.grad is not None:
             assert torch.isfinite(p.grad).all(), k

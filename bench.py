@@ -6,10 +6,14 @@
 One "step" = the reference's optimizer_idx-0 training step (PoseAutoencoder.training_step -> PoseLoss ->
 backward -> gradient allreduce -> clip 1.0 -> Adam) on one synthetic object-crop batch of the
 autoencoder_kl_16x16x16 pose config at 256x256, per-GPU batch 64 (BASELINE.json configs[1]), global_step 80000
-(decoder, pixel loss and dropout schedule active), perceptual_weight = 0 and disc_factor = 0.
-Prints ONE JSON line (rank 0). `--impl reference` times the CPU restatement of the reference's own PyTorch path
-(oracle/) on the host cores instead (the reference tree itself is Python under /root/reference and does not
-travel to the GPU box).
+(decoder, pixel loss and dropout schedule active), perceptual_weight = 0 and disc_factor = 0 (SURVEY 8d config 2:
+a REDUCED objective -- the yaml's own defaults are perceptual_weight = 1 and disc_factor = 1; that step, with both
+optimizer steps per batch, is measured next to it as `extra.full_objective`, or alone with `--objective full`).
+Prints ONE JSON line (rank 0). At N = 1 the line also carries `extra`: the full-objective step, the encode-only sweep
+(configs[2]), the 512x512 reconstruction step (configs[4]) and `gpu_eager_baseline` (the oracle restatement of the
+reference's PyTorch code run in eager mode on the same B200: cuDNN / cuBLAS with TF32 and with bf16 autocast).
+`--impl reference` times the CPU restatement of the reference's own PyTorch path (oracle/) on the host cores instead
+(the reference tree itself is Python under /root/reference and does not travel to the GPU box).
 """
 import argparse
 import json
@@ -42,9 +46,17 @@ def parse():
     ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
     ap.add_argument("--cpu-baseline", type=int, default=1, help="time the CPU oracle on rank 0 at N=1 (0 = skip)")
     ap.add_argument("--no-roofline", action="store_true")
-    ap.add_argument("--mode", default="mixed", choices=["mixed", "bf16"],
-                    help="16-bit compute mode: mixed = fp16 forward tensors + bf16 attention/gradients (meets the 1e-2 "
-                         "parity tolerance; default), bf16 = everything bf16")
+    ap.add_argument("--mode", default="fp16", choices=["fp16", "mixed", "bf16"],
+                    help="16-bit compute mode: fp16 = every 16-bit tensor IEEE fp16, activation gradients with a static "
+                         "scale (meets the 1e-2 parity tolerance on outputs AND gradients; default); mixed = round 1's fp16 "
+                         "forward + bf16 attention/gradients; bf16 = everything bf16")
+    ap.add_argument("--objective", default="configs1", choices=["configs1", "full"],
+                    help="configs1 = BASELINE.json configs[1] (perceptual_weight 0, disc_factor 0; the bench line); full = the "
+                         "yaml's own objective: LPIPS + PatchGAN generator term with the adaptive weight in the optimizer_idx 0 "
+                         "step AND the optimizer_idx 1 discriminator step, i.e. one whole batch of the reference loop")
+    ap.add_argument("--extras", type=int, default=1,
+                    help="N = 1 only: also measure the full objective, the encode sweep, the 512x512 step and the eager "
+                         "cuDNN/cuBLAS baseline, reported under `extra` (0 = skip)")
     ap.add_argument("--ncu-step", action="store_true",
                     help="profiling aid: after warm-up run ONE step between cudaProfilerStart/Stop and exit "
                          "(use with `ncu --profile-from-start off`); prints no bench line")
@@ -129,65 +141,134 @@ class ClockSampler:
 
 
 # --------------------------------------------------------------------------------------------------
-# CPU arm: the oracle restatement of the reference's PyTorch path on the host cores
+# Reference arms: the oracle restatement of the reference's PyTorch path (oracle/odvae_oracle.py, pinned to goldens made
+# from the unmodified reference) -- on the host cores (`cpu_baseline`, `--impl reference`) and, as the "existing Blackwell
+# kernels on the same box" comparator of SURVEY 8d, in eager mode on the GPU (`extra.gpu_eager_baseline`: ATen / cuDNN /
+# cuBLAS). Same step definition as the product arm: fwd + loss + bwd + clip_grad_norm_(1.0) + Adam(0.5, 0.9).
 # --------------------------------------------------------------------------------------------------
-def cpu_step_fn(batch_size):
+def workload_string(R, perceptual_weight, disc_factor):
+    return ("autoencoder_kl_16x16x16 pose config, %dx%d crops, train step (fwd + KL/L1/pose loss + bwd + allreduce + "
+            "clip 1.0 + Adam), global_step 80000, perceptual_weight=%g, disc_factor=%g (BASELINE.json configs[%d])"
+            % (R, R, perceptual_weight, disc_factor, 1 if R == RES else 4))
+
+
+def oracle_step_fn(batch_size, device="cpu", autocast=None):
     from odvae_b200 import synth
     from odvae_b200.autoencoder import PoseAutoencoder
     from oracle import odvae_oracle
-    torch.set_num_threads(os.cpu_count() or 1)
+    dev = torch.device(device)
+    if dev.type == "cpu":
+        torch.set_num_threads(os.cpu_count() or 1)
     params = synth.model_config(synth.DDCONFIG, stats_file())
     shell = PoseAutoencoder(**params)  # CPU construction only: names/shapes of the reference state_dict
     synth.fill_state_dict_(shell.state_dict(), seed=23)
-    sd = {k: v.detach().clone().requires_grad_(True) for k, v in shell.state_dict().items()
-          if torch.is_floating_point(v) and not k.startswith("loss.discriminator")}
+    sd = {}
+    for k, v in shell.state_dict().items():
+        if k.startswith("loss.perceptual_loss"):
+            continue
+        t = v.detach().clone().to(dev)
+        frozen = (not torch.is_floating_point(t)) or "running_" in k or k.startswith("loss.discriminator")
+        sd[k] = t if frozen else t.requires_grad_(True)
+    del shell
+    train = [v for k, v in sd.items() if v.requires_grad and k != "loss.logvar"]  # AE.py:367-374
+    opt = torch.optim.Adam(train, lr=4.5e-6 * batch_size, betas=(0.5, 0.9))
     orc = odvae_oracle.Oracle(params, sd, synth.synthetic_dataset_stats(23), synth.LABELS)
-    batch = synth.synthetic_batch(batch_size, RES, seed=23)
+    batch = {k: (v.to(dev) if torch.is_tensor(v) else v) for k, v in synth.synthetic_batch(batch_size, RES, seed=23).items()}
     p = odvae_oracle.dropout_prob(STEP, params, params["lossconfig"]["params"]["encoder_pretrain_steps"])
-    noise = synth.draw_noise(batch_size, p, seed=101)
+    noise = tuple(t.to(dev) for t in synth.draw_noise(batch_size, p, seed=101))
 
     def step():
-        for v in sd.values():
-            v.grad = None
-        loss, _, _ = orc.training_step(batch, STEP, noise)
+        opt.zero_grad(set_to_none=True)
+        sd["loss.logvar"].grad = None
+        if autocast is not None:
+            with torch.autocast(dev.type, dtype=autocast):
+                loss, _, _ = orc.training_step(batch, STEP, noise)
+        else:
+            loss, _, _ = orc.training_step(batch, STEP, noise)
         loss.backward()
-        return float(loss.detach())
+        torch.nn.utils.clip_grad_norm_(train, 1.0)
+        opt.step()
+        return loss.detach()
 
     return step
 
 
-def cpu_baseline(batch_size=2, steps=1):
-    step = cpu_step_fn(batch_size)
+def cpu_baseline(batch_size=4, steps=3):
+    step = oracle_step_fn(batch_size)
+    step()  # warm-up (thread pools, mkldnn primitives)
     t0 = time.perf_counter()
     for _ in range(steps):
-        step()
+        float(step())
     dt = time.perf_counter() - t0
     return {"value": batch_size * steps / dt, "unit": "images/sec", "cores": os.cpu_count(), "kind": "port",
-            "sample": "oracle/ (CPU fp32 restatement of the reference PyTorch path, pinned to the reference's goldens): "
-                      "%d step(s) of fwd+loss+bwd at batch %d, 256x256, all host threads, %.1f s" % (steps, batch_size, dt)}
+            "sample": "oracle/ (CPU fp32 restatement of the reference PyTorch path, pinned to the reference's goldens): 1 warm-up + "
+                      "%d timed step(s) of fwd+loss+bwd+clip+Adam at batch %d, 256x256, all host threads, %.1f s"
+                      % (steps, batch_size, dt)}
+
+
+def gpu_eager_baseline(dev, steps=3):
+    """The reference arithmetic (oracle restatement, plain torch ops) in eager mode on this B200: cuDNN 9 convs, cuBLAS
+    bmm, ATen group_norm / softmax. (a) fp32 storage with TF32 tensor-core math (torch's default for convs; the reference
+    sets matmul precision "medium", train.py:521), (b) bf16 autocast. Batch 64 if it fits, else the largest power of two."""
+    out = {"what": "oracle/odvae_oracle.py on cuda (eager ATen/cuDNN/cuBLAS), same step: fwd+loss+bwd+clip+Adam, "
+                   "perceptual_weight=0, disc_factor=0, 256x256, CUDA-event timed"}
+    torch.backends.cudnn.allow_tf32 = True
+    torch.backends.cuda.matmul.allow_tf32 = True
+    for tag, ac in (("tf32", None), ("bf16_autocast", torch.bfloat16)):
+        res = None
+        for B in (64, 32, 16):
+            try:
+                step = oracle_step_fn(B, device=str(dev), autocast=ac)
+                step()
+                step()
+                torch.cuda.synchronize()
+                e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+                e0.record()
+                for _ in range(steps):
+                    step()
+                e1.record()
+                torch.cuda.synchronize()
+                ms = e0.elapsed_time(e1) / steps
+                res = {"images_per_sec": B / (ms * 1e-3), "ms_per_step": ms, "batch": B, "steps": steps,
+                       "peak_mem_GB": torch.cuda.max_memory_allocated() / 1e9}
+                break
+            except torch.cuda.OutOfMemoryError:
+                res = {"error": "out of memory at batch %d" % B}
+            finally:
+                step = None
+                import gc
+                gc.collect()
+                torch.cuda.empty_cache()
+                torch.cuda.reset_peak_memory_stats()
+        out[tag] = res
+    return out
 
 
 def run_reference(args):
     rank = int(os.environ.get("RANK", "0"))
     if rank != 0:
         return
-    B = 1
-    step = cpu_step_fn(B)
+    B = 4  # SURVEY 8d: the reference's own CPU-runnable case (configs[0]) -- a bounded sample of the batch-64 workload
+    step = oracle_step_fn(B)
     for _ in range(args.warmup):
         step()
     t0 = time.perf_counter()
     for _ in range(args.steps):
-        step()
+        float(step())
     dt = time.perf_counter() - t0
     v = B * args.steps / dt
+    world = args.gpus
     line = {"impl": "reference", "metric": "AutoencoderKL train-step images/sec", "value": v, "unit": "images/sec",
             "n_gpus": args.gpus, "steps": args.steps, "warmup": args.warmup, "ms_per_step": 1e3 * dt / args.steps,
             "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "f32", "data": "synthetic",
-            "config": {"workload": "autoencoder_kl_16x16x16 pose config, 256x256 crops, train step "
-                                   "(fwd + KL/L1/pose loss + bwd), global_step 80000, perceptual_weight=0, disc_factor=0",
-                       "per_step_sample": "batch %d on the host cores" % B},
+            "config": {"workload": workload_string(RES, 0.0, 0.0), "per_gpu_batch": args.batch,
+                       "global_batch": args.batch * world, "resolution": RES, "parallelism": "dp%d" % world,
+                       "l2": "per-step working set (activations ~40 GB at batch 64) far exceeds the 126 MB L2"},
+            "per_step_sample": "each timed step = the same train step on a batch of %d crops (a bounded sample of the "
+                               "batch-%d workload) on the host cores" % (B, args.batch),
             "cpu_baseline": {"value": v, "unit": "images/sec", "cores": os.cpu_count(), "kind": "port",
-                             "sample": "%d timed steps of batch %d (oracle/ restatement of the reference)" % (args.steps, B)},
+                             "sample": "%d timed steps of batch %d (oracle/ restatement of the reference, fwd+loss+bwd+clip+Adam)"
+                                       % (args.steps, B)},
             "e2e": {"value": v, "unit": "images/sec", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
             "gpu_launches": 0}
     print(json.dumps(line), flush=True)
@@ -389,7 +470,7 @@ def run_encode(args, model, dev, B, R, rank, world):
         line = {"metric": "AutoencoderKL encode+decode fwd+bwd images/sec" if recon else "AutoencoderKL encode-only images/sec", "value": n_img / (ms * 1e-3), "unit": "images/sec",
                 "n_gpus": world, "steps": args.steps, "warmup": max(args.warmup, 3), "ms_per_step": ms / args.steps,
                 "higher_is_better": True, "scaling": "weak", "vs_baseline": None,
-                "dtype": "fp16 fwd (tcgen05 kind::f16, fp32 accumulate)" if args.mode == "mixed" else "bf16",
+                "dtype": DTYPE_STR[args.mode],
                 "data": "synthetic",
                 "config": {"workload": ("encode -> mode -> decode -> L1 -> backward (Encoder, Decoder, quant convs; no pose "
                                         "heads, no optimizer), %dx%d crops (BASELINE.json configs[4])" if recon else
@@ -412,10 +493,81 @@ def run_encode(args, model, dev, B, R, rank, world):
 # --------------------------------------------------------------------------------------------------
 # GPU arm
 # --------------------------------------------------------------------------------------------------
+MODES = {"fp16": torch.float16, "mixed": "mixed", "bf16": torch.bfloat16}
+DTYPE_STR = {"fp16": "fp16 (tcgen05 kind::f16, fp32 accumulate; fp16 activation gradients with a static power-of-two scale)",
+             "mixed": "fp16 fwd + bf16 attn/grad (tcgen05 kind::f16, fp32 accumulate)", "bf16": "bf16"}
+
+
+def build_model(args, dev, world, perceptual_weight, disc_factor):
+    from odvae_b200 import synth
+    from odvae_b200.autoencoder import PoseAutoencoder
+    params = synth.model_config(synth.DDCONFIG, stats_file())
+    params["lossconfig"]["params"]["perceptual_weight"] = perceptual_weight
+    params["lossconfig"]["params"]["disc_factor"] = disc_factor
+    torch.manual_seed(23)
+    model = PoseAutoencoder(**params, compute_dtype=MODES[args.mode])
+    synth.fill_state_dict_({k: v for k, v in model.state_dict().items() if not k.startswith("loss.perceptual_loss.")},
+                           seed=23)  # identical replicas on every rank (LPIPS keeps its seeded constructor weights)
+    model = model.to(dev)
+    model.global_step = STEP
+    model.learning_rate = 1 * world * args.batch * 4.5e-6  # train.py:383: accumulate_grad_batches * ngpu * batch * base_lr
+    return model
+
+
+def replicas_identical(model, world):
+    """max |param(rank r) - param(rank 0)| over all parameters and ranks after the timed steps (DDP keeps replicas in lockstep:
+    identical initial weights + identical all-reduced gradients + deterministic kernels => exactly 0)."""
+    import torch.distributed as dist
+    flat = torch.cat([p.detach().reshape(-1).float() for p in model.parameters()])
+    ref = flat.clone()
+    dist.broadcast(ref, 0)
+    d = (flat - ref).abs().max().reshape(1)
+    dist.all_reduce(d, op=dist.ReduceOp.MAX)
+    return float(d)
+
+
+def time_full_objective(args, dev, B, R, steps, warmup):
+    """One whole batch of the reference loop with the yaml's own objective (perceptual_weight 1, disc_factor 1): the
+    optimizer_idx 0 step (LPIPS, PatchGAN generator term, adaptive d_weight, Adam) + the optimizer_idx 1 step (two
+    discriminator passes, hinge loss, Adam). `reference_forward_twice` = AE.py:321-327 semantics (the AE forward runs again
+    for the discriminator step); `reuse_forward` = SURVEY 8 f2's cached variant."""
+    from odvae_b200 import lib, synth
+    from odvae_b200.fit import Fit
+    out = {}
+    for tag, reuse in (("reference_forward_twice", False), ("reuse_forward", True)):
+        model = build_model(args, dev, 1, 1.0, 1.0)
+        model.reuse_forward_for_disc = reuse
+        fit = Fit(model, batch_size=B, base_lr=4.5e-6)
+        res = {k: (v.to(dev) if torch.is_tensor(v) else v) for k, v in synth.synthetic_batch(B, R, seed=23).items()}
+        clone = lambda b: {k: (v.clone() if torch.is_tensor(v) else list(v)) for k, v in b.items()}
+        for i in range(warmup):
+            fit.training_batch(clone(res), i)
+        torch.cuda.synchronize()
+        l0 = lib.call("launch_count")
+        e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        e0.record()
+        for i in range(steps):
+            ae, dl = fit.training_batch(clone(res), i)
+        e1.record()
+        torch.cuda.synchronize()
+        ms = e0.elapsed_time(e1) / steps
+        out[tag] = {"images_per_sec": B / (ms * 1e-3), "ms_per_batch": ms, "steps": steps,
+                    "gpu_launches_per_batch": int((lib.call("launch_count") - l0) / steps),
+                    "aeloss": float(ae), "discloss": float(dl),
+                    "d_weight": float(model.logged.get("train/d_weight", 0.0)), "g_loss": float(model.logged.get("train/g_loss", 0.0))}
+        del fit, model
+        import gc
+        gc.collect()
+        torch.cuda.empty_cache()
+    out["what"] = ("one batch = optimizer_idx 0 step + optimizer_idx 1 step, perceptual_weight=1 (LPIPS with seeded stand-in "
+                   "weights: vgg.pth is not downloadable), disc_factor=1, batch %d, %dx%d, global_step 80000+" % (B, R, R))
+    return out
+
+
 def run_ours(args):
     import torch.distributed as dist
     from odvae_b200 import lib, synth
-    from odvae_b200.autoencoder import PoseAutoencoder
+    from odvae_b200.fit import Fit
     from odvae_b200.trainer import TrainStep
 
     world = int(os.environ.get("WORLD_SIZE", "1"))
@@ -428,18 +580,15 @@ def run_ours(args):
         dist.init_process_group("nccl", device_id=dev)
     lib.require_device()
     B = args.batch
-
-    params = synth.model_config(synth.DDCONFIG, stats_file())
-    params["lossconfig"]["params"]["perceptual_weight"] = args.perceptual_weight
-    torch.manual_seed(23)
-    model = PoseAutoencoder(**params, compute_dtype=torch.float16 if args.mode == "mixed" else torch.bfloat16)
-    synth.fill_state_dict_({k: v for k, v in model.state_dict().items() if not k.startswith("loss.perceptual_loss.")},
-                           seed=23)  # identical replicas on every rank (LPIPS keeps its seeded constructor weights)
-    model = model.to(dev)
-    model.global_step = STEP
-    # LR scaling of train.py:383: accumulate_grad_batches * ngpu * batch * base_lr
-    model.learning_rate = 1 * world * B * 4.5e-6
-    step_fn = TrainStep(model, lr=model.learning_rate, max_grad_norm=1.0)
+    full = args.objective == "full"
+    pw = 1.0 if full else args.perceptual_weight
+    df = 1.0 if full else 0.0
+    model = build_model(args, dev, world, pw, df)
+    if full:
+        fit = Fit(model, batch_size=B, base_lr=4.5e-6)
+        step_fn = lambda b, i: fit.training_batch(b, i)[0]
+    else:
+        step_fn = TrainStep(model, lr=model.learning_rate, max_grad_norm=1.0)
 
     R = args.res
     if args.workload in ("encode", "recon"):
@@ -502,6 +651,7 @@ def run_ours(args):
     launches = lib.call("launch_count") - launches0
     ms_e2e, last_loss = timed(pinned, args.steps, True)
     clocks = sampler.stop() if rank == 0 else None
+    identical = replicas_identical(model, world) if world > 1 else None
 
     roof = None
     flops_img = FLOPS_TRAIN_PER_IMG
@@ -519,17 +669,15 @@ def run_ours(args):
                 json.dump(prof.shapes(), f, indent=1)
         pk, how = peaks()
         peak = pk["bf16_tflops_sustained"]
-        if R != RES:  # other resolutions: count the flops of the launched problems (no SURVEY figure)
+        if R != RES or full:  # other workloads: count the flops of the launched problems (no SURVEY figure)
             flops_img = counted / B
         achieved = flops_img * B / (eng_ms * 1e-3) / 1e12
         roof = {"bound": "tensor", "kernel": "tc_engine_kernel (tcgen05 implicit-GEMM conv fwd/dgrad/wgrad + attention GEMMs)",
                 "achieved": achieved, "peak": peak, "unit": "TFLOP/s", "frac": achieved / peak,
                 "peak_source": how + " (bf16_tflops_sustained: kernel timed inside a long step)",
-                # DRAM bytes per launch of tc_engine_kernel, averaged over the 333 engine launches of one step:
-                # ncu dram__bytes_read.sum + dram__bytes_write.sum = 165.63 GB + 62.19 GB (profiles/r01_launches_s16.txt, six instances);
-                # the dominant shape alone (128->128 3x3 at 256x256): 2.108 GB per launch against 2.147 GB algorithmic
-                # (x in + y out, batch 64) in the `ncu --set full` capture profiles/r01_conv_full_raw.csv
-                "traffic": 227.82e9 / 333, "traffic_unit": "bytes per launch (step average)",
+                # DRAM bytes are not measurable from inside this process (no ncu under the timed run): null here; the per-launch
+                # dram__bytes of this same command are in the committed ncu launch list (profiles/r02_launches*.txt)
+                "traffic": None,
                 "engine_ms_per_step": eng_ms, "engine_calls_per_step": ncalls,
                 "engine_share_of_step": eng_ms / (ms / args.steps),
                 "algorithmic_flops_per_step": flops_img * B, "counted_padded_flops_per_step": counted,
@@ -540,30 +688,135 @@ def run_ours(args):
                 "hbm_kernels": {"peak_GBps": pk["hbm_gbs"], "groupnorm": prof.gn_summary(pk["hbm_gbs"])}}
 
     if rank == 0:
-        cpu = None
-        if world == 1 and args.cpu_baseline:
-            cpu = cpu_baseline(batch_size=4, steps=3)
         n_img = B * world * args.steps
         line = {"metric": "AutoencoderKL train-step images/sec", "value": n_img / (ms * 1e-3), "unit": "images/sec",
                 "n_gpus": world, "steps": args.steps, "warmup": max(args.warmup, 3), "ms_per_step": ms / args.steps,
                 "higher_is_better": True, "scaling": "weak", "vs_baseline": None,
-                "dtype": "fp16 fwd + bf16 attn/grad (tcgen05 kind::f16, fp32 accumulate)" if args.mode == "mixed" else "bf16",
-                "data": "synthetic",
-                "config": {"workload": "autoencoder_kl_16x16x16 pose config, %dx%d crops, train step (fwd + KL/L1/pose " % (R, R) +
-                                       "loss + bwd + allreduce + clip 1.0 + Adam), global_step 80000, perceptual_weight=%g, " % args.perceptual_weight +
-                                       "disc_factor=0 (BASELINE.json configs[%d])" % (1 if R == RES else 4),
+                "dtype": DTYPE_STR[args.mode], "data": "synthetic",
+                "config": {"workload": workload_string(R, pw, df) if not full else
+                           "autoencoder_kl_16x16x16 pose config, %dx%d crops, ONE BATCH of the reference loop with the yaml's own "
+                           "objective: optimizer_idx 0 (LPIPS + GAN generator term, adaptive weight) + optimizer_idx 1 "
+                           "(discriminator) steps, global_step 80000+" % (R, R),
                            "per_gpu_batch": B, "global_batch": B * world, "resolution": R,
                            "parallelism": "dp%d" % world,
                            "l2": "per-step working set (activations ~40 GB at batch 64) far exceeds the 126 MB L2"},
                 "e2e": {"value": n_img / (ms_e2e * 1e-3), "unit": "images/sec", "h2d_bytes_per_step": h2d,
                         "d2h_bytes_per_step": 4, "ms_per_step": ms_e2e / args.steps, "last_loss": last_loss},
                 "gpu_launches": int(launches), "host_enqueue_ms_per_step": host_enqueue_ms,
-                "clocks": clocks, "roofline": roof, "cpu_baseline": cpu,
+                "clocks": clocks, "roofline": roof, "cpu_baseline": None,
                 "pct_of_tensor_roofline_whole_step": flops_img * B / (ms / args.steps * 1e-3) / 1e12 /
                 peaks()[0]["bf16_tflops_sustained"]}
+        if identical is not None:
+            line["replicas_identical"] = {"max_abs_param_diff_vs_rank0": identical, "identical": identical == 0.0}
+    # ---- N = 1 extras: the other BASELINE.json configs and comparators, each a short measurement after the main one
+    if world == 1 and rank == 0:
+        import gc
+        del step_fn, model
+        if full:
+            del fit
+        gc.collect()
+        torch.cuda.empty_cache()
+        if args.extras and not full and R == RES:
+            extra = {}
+            try:
+                extra["full_objective"] = time_full_objective(args, dev, B, R, steps=3, warmup=2)
+            except Exception as e:  # an extra must never take the bench line down
+                extra["full_objective"] = {"error": repr(e)[:300]}
+            try:
+                extra["encode_sweep"] = encode_sweep(args, dev)
+            except Exception as e:
+                extra["encode_sweep"] = {"error": repr(e)[:300]}
+            try:
+                extra["recon_512"] = recon_512(args, dev)
+            except Exception as e:
+                extra["recon_512"] = {"error": repr(e)[:300]}
+            gc.collect()
+            torch.cuda.empty_cache()
+            try:
+                extra["gpu_eager_baseline"] = gpu_eager_baseline(dev)
+            except Exception as e:
+                extra["gpu_eager_baseline"] = {"error": repr(e)[:300]}
+            line["extra"] = extra
+        if args.cpu_baseline:
+            line["cpu_baseline"] = cpu_baseline(batch_size=4, steps=3)
+    if rank == 0:
         print(json.dumps(line), flush=True)
     if world > 1:
         dist.destroy_process_group()
+
+
+def _timed_loop(fn, steps):
+    torch.cuda.synchronize()
+    e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    e0.record()
+    for _ in range(steps):
+        out = fn()
+    e1.record()
+    torch.cuda.synchronize()
+    return e0.elapsed_time(e1) / steps, out
+
+
+def encode_sweep(args, dev, batches=(1, 16, 128), steps=10):
+    """BASELINE.json configs[2]: encode-only inference (Encoder + posterior.mode(), no_grad) at 256x256; CUDA-graph replay for
+    batch <= 32 (odvae_b200/graphs.py), eager launches above."""
+    from odvae_b200 import synth
+    pk, _ = peaks()
+    model = build_model(args, dev, 1, 0.0, 0.0)
+    rows = []
+    for B in batches:
+        x = synth.synthetic_batch(B, RES, seed=23)["patch"].float().to(dev)
+        if B <= 32:
+            from odvae_b200.graphs import GraphedEncode
+            genc = GraphedEncode(model, B, RES)
+            fn = lambda: genc(x)
+        else:
+            def fn():
+                with torch.no_grad():
+                    return model.encode(model._rescale(x))[0].mode()
+        for _ in range(3):
+            fn()
+        ms, _ = _timed_loop(fn, steps)
+        rows.append({"batch": B, "images_per_sec": B / (ms * 1e-3), "ms_per_step": ms, "cuda_graph": B <= 32,
+                     "pct_of_tensor_roofline": FLOPS_ENCODE_PER_IMG * B / (ms * 1e-3) / 1e12 / pk["bf16_tflops_sustained"]})
+    del model
+    return rows
+
+
+def recon_512(args, dev, steps=3):
+    """BASELINE.json configs[4]: 512x512 crops, encode -> mode -> decode -> L1 -> backward through decoder and encoder (no pose
+    heads: the config's pose MLPs are sized for 16x16 latents, i.e. 256x256 crops only, in the reference too)."""
+    from odvae_b200 import synth
+    pk, _ = peaks()
+    out = None
+    for B in (32, 16, 8):
+        model = build_model(args, dev, 1, 0.0, 0.0)
+        try:
+            x = synth.synthetic_batch(B, 512, seed=23)["patch"].float().to(dev)
+
+            def fn():
+                for prm in model.parameters():
+                    prm.grad = None
+                xr = model._rescale(x)
+                post, _ = model.encode(xr)
+                rec = model.decode(post.mode())
+                loss = (rec - xr).abs().mean()
+                loss.backward()
+                return loss.detach()
+            fn()
+            fn()
+            ms, _ = _timed_loop(fn, steps)
+            out = {"batch": B, "images_per_sec": B / (ms * 1e-3), "ms_per_step": ms,
+                   "pct_of_tensor_roofline": 3 * 2967e9 * B / (ms * 1e-3) / 1e12 / pk["bf16_tflops_sustained"],
+                   "peak_mem_GB": torch.cuda.max_memory_allocated() / 1e9}
+            break
+        except torch.cuda.OutOfMemoryError:
+            out = {"error": "out of memory at batch %d" % B}
+        finally:
+            del model
+            import gc
+            gc.collect()
+            torch.cuda.empty_cache()
+    return out
 
 
 def main():

@@ -79,6 +79,7 @@ int odvae_conv2d_dgrad(const void* dy, const void* w_packed_dgrad, const void* d
                                CoutP, geom);
   if (st != ODVAE_OK) return st;
   for (int i = 0; i < n; ++i) {
+    if (act_dtype == ODVAE_F16) ds[i].p.out_mode = OUT_F16;  // dx (and dx_add) in the operand format
     st = run_engine(ds[i], impl, act_dtype, static_cast<cudaStream_t>(stream));
     if (st != ODVAE_OK) return st;
   }

@@ -8,6 +8,7 @@
 #include "tc_primitives.cuh"
 
 #include <stdlib.h>
+#include <type_traits>
 
 namespace odvae {
 
@@ -192,7 +193,11 @@ template <typename T, typename TO, typename TO2>
 __global__ void __launch_bounds__(GN_THREADS)
 gn_apply_kernel(const T* __restrict__ x, const float* __restrict__ stats, const float* __restrict__ gamma,
                 const float* __restrict__ beta, TO* __restrict__ y, TO2* __restrict__ y2, int HW, int C, int G,
-                int silu) {
+                int silu, int* __restrict__ overflow) {
+  // fp16 inputs only: a value stored at +-65504 is a SATURATED store of its producer (common.cuh sat_f16) -- every tensor
+  // of the residual stream passes through here, so this is where the forward's range overflow is detected
+  constexpr bool kCheck = std::is_same<T, f16>::value;
+  bool sat = false;
   constexpr int V = VecN<T>::V;
   const int b = blockIdx.y;
   const int cpg = C / G;
@@ -225,7 +230,9 @@ gn_apply_kernel(const T* __restrict__ x, const float* __restrict__ stats, const 
       TO2 y2v[V];
 #pragma unroll
       for (int j = 0; j < V; ++j) {
-        float v = fmaf(to_f32<T>(xv[u][j]), scale[j], shift[j]);
+        const float xf = to_f32<T>(xv[u][j]);
+        if (kCheck) sat |= fabsf(xf) >= 65504.0f;
+        float v = fmaf(xf, scale[j], shift[j]);
         if (silu) v = silu_t<sizeof(T) == 2>(v);
         yv[j] = from_f32<TO>(v);
         y2v[j] = from_f32<TO2>(v);
@@ -241,7 +248,9 @@ gn_apply_kernel(const T* __restrict__ x, const float* __restrict__ stats, const 
     *reinterpret_cast<uint4*>(xv) = __ldg(xb + i);
 #pragma unroll
     for (int j = 0; j < V; ++j) {
-      float v = fmaf(to_f32<T>(xv[j]), scale[j], shift[j]);
+      const float xf = to_f32<T>(xv[j]);
+      if (kCheck) sat |= fabsf(xf) >= 65504.0f;
+      float v = fmaf(xf, scale[j], shift[j]);
       if (silu) v = silu_t<sizeof(T) == 2>(v);
       yv[j] = from_f32<TO>(v);
       y2v[j] = from_f32<TO2>(v);
@@ -249,6 +258,7 @@ gn_apply_kernel(const T* __restrict__ x, const float* __restrict__ stats, const 
     yb[i] = *reinterpret_cast<const uint4*>(yv);
     if (y2b) y2b[i] = *reinterpret_cast<const uint4*>(y2v);
   }
+  if (kCheck && sat && overflow != nullptr) overflow[0] = 1;  // benign race: every writer stores the same value
 }
 
 // backward finalize A: one CTA per image. AB[b][c] = (sum dy', sum dy' xhat); coef[b][g] = (c2, c3)
@@ -308,8 +318,11 @@ template <typename T, typename TG>
 __global__ void __launch_bounds__(GN_THREADS)
 gn_bwd_apply_kernel(const T* __restrict__ x, const TG* __restrict__ dy, const TG* __restrict__ dx_add,
                     const float* __restrict__ stats, const float* __restrict__ gamma, const float* __restrict__ beta,
-                    const float* __restrict__ coef, TG* __restrict__ dx, int HW, int C, int G, int silu) {
+                    const float* __restrict__ coef, TG* __restrict__ dx, int HW, int C, int G, int silu,
+                    int* __restrict__ overflow) {
   constexpr int V = VecN<T>::V;
+  constexpr bool kCheck = std::is_same<TG, f16>::value;  // fp16 gradients: a saturated dy means the gradient scale is too large
+  bool sat = false;
   const int b = blockIdx.y;
   const int cpg = C / G;
   const int cv = C / V;
@@ -356,6 +369,7 @@ gn_bwd_apply_kernel(const T* __restrict__ x, const TG* __restrict__ dy, const TG
         for (int j = 0; j < V; ++j) {
           const float xf = to_f32<T>(xv[u][j]);
           float d = to_f32<TG>(dv[u][j]);
+          if (kCheck) sat |= fabsf(d) >= 65504.0f;
           if (silu) d *= silu_grad_t<sizeof(T) == 2>(fmaf(xf, scale[j], shift[j]));
           float o = fmaf(scale[j], d, fmaf(c2[j], xf, c3[j]));
           if (ab) o += to_f32<TG>(av[u][j]);
@@ -365,6 +379,7 @@ gn_bwd_apply_kernel(const T* __restrict__ x, const TG* __restrict__ dy, const TG
       }
     }
   }
+  if (kCheck && sat && overflow != nullptr) overflow[1] = 1;
 }
 
 // Pixel-range splits per image for the reduce kernels. The reduce grid is ONE resident wave of `slots` CTAs taking
@@ -476,19 +491,19 @@ int odvae_groupnorm_stats(const void* x, float* stats, int B, int HW, int C, int
 // weight-gradient GEMM); fp16 -> bf16 (attention blocks run in bf16 inside the mixed mode)
 int odvae_groupnorm_apply(const void* x, const float* stats, const float* gamma, const float* beta, void* y, void* y2,
                           int B, int HW, int C, int G, int silu, int in_dtype, int out_dtype, int out2_dtype,
-                          void* stream) {
+                          int32_t* overflow_flags, void* stream) {
   cudaStream_t st = static_cast<cudaStream_t>(stream);
   const int V = in_dtype == ODVAE_F32 ? 4 : 8;
   if (!gn_shape_ok(C, G, V)) return ODVAE_ERR_SHAPE;
   dim3 grid(gn_apply_blocks(B, HW, C, V), B);
   if (in_dtype == ODVAE_F32 && out_dtype == ODVAE_F32 && y2 == nullptr)
-    gn_apply_kernel<float, float, float><<<grid, GN_THREADS, 0, st>>>(reinterpret_cast<const float*>(x), stats, gamma, beta, reinterpret_cast<float*>(y), nullptr, HW, C, G, silu);
+    gn_apply_kernel<float, float, float><<<grid, GN_THREADS, 0, st>>>(reinterpret_cast<const float*>(x), stats, gamma, beta, reinterpret_cast<float*>(y), nullptr, HW, C, G, silu, overflow_flags);
   else if (in_dtype == ODVAE_BF16 && out_dtype == ODVAE_BF16 && (y2 == nullptr || out2_dtype == ODVAE_BF16))
-    gn_apply_kernel<bf16, bf16, bf16><<<grid, GN_THREADS, 0, st>>>(reinterpret_cast<const bf16*>(x), stats, gamma, beta, reinterpret_cast<bf16*>(y), reinterpret_cast<bf16*>(y2), HW, C, G, silu);
+    gn_apply_kernel<bf16, bf16, bf16><<<grid, GN_THREADS, 0, st>>>(reinterpret_cast<const bf16*>(x), stats, gamma, beta, reinterpret_cast<bf16*>(y), reinterpret_cast<bf16*>(y2), HW, C, G, silu, overflow_flags);
   else if (in_dtype == ODVAE_F16 && out_dtype == ODVAE_F16 && (y2 == nullptr || out2_dtype == ODVAE_BF16))
-    gn_apply_kernel<f16, f16, bf16><<<grid, GN_THREADS, 0, st>>>(reinterpret_cast<const f16*>(x), stats, gamma, beta, reinterpret_cast<f16*>(y), reinterpret_cast<bf16*>(y2), HW, C, G, silu);
+    gn_apply_kernel<f16, f16, bf16><<<grid, GN_THREADS, 0, st>>>(reinterpret_cast<const f16*>(x), stats, gamma, beta, reinterpret_cast<f16*>(y), reinterpret_cast<bf16*>(y2), HW, C, G, silu, overflow_flags);
   else if (in_dtype == ODVAE_F16 && out_dtype == ODVAE_BF16 && y2 == nullptr)
-    gn_apply_kernel<f16, bf16, bf16><<<grid, GN_THREADS, 0, st>>>(reinterpret_cast<const f16*>(x), stats, gamma, beta, reinterpret_cast<bf16*>(y), nullptr, HW, C, G, silu);
+    gn_apply_kernel<f16, bf16, bf16><<<grid, GN_THREADS, 0, st>>>(reinterpret_cast<const f16*>(x), stats, gamma, beta, reinterpret_cast<bf16*>(y), nullptr, HW, C, G, silu, overflow_flags);
   else
     return ODVAE_ERR_SHAPE;
   return check_launch("gn_apply_kernel");
@@ -499,8 +514,8 @@ int odvae_groupnorm_apply(const void* x, const float* stats, const float* gamma,
 // of the static scale 16-bit activation gradients travel with in the all-fp16 mode; dx keeps the scale).
 int odvae_groupnorm_bwd(const void* x, const float* stats, const float* gamma, const float* beta, const void* dy,
                         const void* dx_add, void* dx, float* dgamma, float* dbeta, int B, int HW, int C, int G,
-                        int silu, int act_dtype, int grad_dtype, int accumulate, float pgrad_scale, void* workspace,
-                        size_t ws_bytes, void* stream) {
+                        int silu, int act_dtype, int grad_dtype, int accumulate, float pgrad_scale,
+                        int32_t* overflow_flags, void* workspace, size_t ws_bytes, void* stream) {
   cudaStream_t st = static_cast<cudaStream_t>(stream);
   const int V = act_dtype == ODVAE_F32 ? 4 : 8;
   if (!gn_shape_ok(C, G, V)) return ODVAE_ERR_SHAPE;
@@ -543,7 +558,7 @@ int odvae_groupnorm_bwd(const void* x, const float* stats, const float* gamma, c
 #define GN_LAUNCH_APPLY(T, TG)                                                                                         \
   gn_bwd_apply_kernel<T, TG><<<grid2, GN_THREADS, 0, st>>>(reinterpret_cast<const T*>(x), reinterpret_cast<const TG*>(dy), \
                                                            reinterpret_cast<const TG*>(dx_add), stats, gamma, beta, coef,  \
-                                                           reinterpret_cast<TG*>(dx), HW, C, G, silu);
+                                                           reinterpret_cast<TG*>(dx), HW, C, G, silu, overflow_flags);
   if (combo == 1) GN_LAUNCH_APPLY(bf16, bf16)
   else if (combo == 2) GN_LAUNCH_APPLY(f16, bf16)
   else if (combo == 3) GN_LAUNCH_APPLY(f16, f16)

@@ -42,6 +42,40 @@ __global__ void nchw_to_nhwc_kernel(const float* __restrict__ src, T* __restrict
   }
 }
 
+// _rescale + NCHW fp32 copy + NHWC conversion in one pass (f4): thread = pixel
+template <typename T>
+__global__ void rescale_nhwc_kernel(const float* __restrict__ src, const float* __restrict__ mm, float* __restrict__ dst_nchw,
+                                    T* __restrict__ dst_nhwc, int B, int C, int HW, int Cpad) {
+  const float mn = mm[0], range = mm[1] - mm[0];
+  const long long total = static_cast<long long>(B) * HW;
+  for (long long i = blockIdx.x * static_cast<long long>(blockDim.x) + threadIdx.x; i < total;
+       i += static_cast<long long>(gridDim.x) * blockDim.x) {
+    const int b = static_cast<int>(i / HW);
+    const int p = static_cast<int>(i - static_cast<long long>(b) * HW);
+    const long long plane0 = (static_cast<long long>(b) * C) * HW + p;
+    T* d = dst_nhwc + i * Cpad;
+    constexpr int V2 = 2 * Vec16<T>::N;
+    for (int c0 = 0; c0 < Cpad; c0 += V2) {
+      __align__(16) T tmp[V2];
+#pragma unroll
+      for (int j = 0; j < V2; ++j) {
+        const int c = c0 + j;
+        float v = 0.0f;
+        if (c < C) {
+          v = 2.0f * (__ldg(src + plane0 + static_cast<long long>(c) * HW) - mn) / range - 1.0f;  // == rescale_kernel
+          dst_nchw[plane0 + static_cast<long long>(c) * HW] = v;
+        }
+        tmp[j] = from_f32<T>(v);
+      }
+      if (c0 + V2 <= Cpad) {
+        st_global_256(d + c0, *reinterpret_cast<const uint32_t(*)[8]>(tmp));
+      } else {
+        *reinterpret_cast<uint4*>(d + c0) = *reinterpret_cast<const uint4*>(tmp);
+      }
+    }
+  }
+}
+
 template <typename T>
 __global__ void nhwc_to_nchw_kernel(const T* __restrict__ src, float* __restrict__ dst, int B, int C, int HW,
                                     int Cpad) {
@@ -565,6 +599,24 @@ int odvae_nchw_to_nhwc(const float* src, void* dst, int B, int C, int H, int W, 
     nchw_to_nhwc_kernel<float><<<grid_for(total, 256), 256, 0, st>>>(src, reinterpret_cast<float*>(dst), B, C, H * W, Cpad, scale, shift);
   }
   return check_launch("nchw_to_nhwc_kernel");
+}
+
+int odvae_rescale_nhwc(const float* src, const float* minmax, float* dst_nchw, void* dst_nhwc, int B, int C, int H, int W,
+                       int Cpad, int act_dtype, void* stream) {
+  if (B <= 0 || C <= 0 || Cpad < C) return ODVAE_ERR_SHAPE;
+  cudaStream_t st = static_cast<cudaStream_t>(stream);
+  const long long total = static_cast<long long>(B) * H * W;
+  if (act_dtype == ODVAE_BF16) {
+    if (Cpad % 8) return ODVAE_ERR_SHAPE;
+    rescale_nhwc_kernel<bf16><<<grid_for(total, 256), 256, 0, st>>>(src, minmax, dst_nchw, reinterpret_cast<bf16*>(dst_nhwc), B, C, H * W, Cpad);
+  } else if (act_dtype == ODVAE_F16) {
+    if (Cpad % 8) return ODVAE_ERR_SHAPE;
+    rescale_nhwc_kernel<f16><<<grid_for(total, 256), 256, 0, st>>>(src, minmax, dst_nchw, reinterpret_cast<f16*>(dst_nhwc), B, C, H * W, Cpad);
+  } else {
+    if (Cpad % 4) return ODVAE_ERR_SHAPE;
+    rescale_nhwc_kernel<float><<<grid_for(total, 256), 256, 0, st>>>(src, minmax, dst_nchw, reinterpret_cast<float*>(dst_nhwc), B, C, H * W, Cpad);
+  }
+  return check_launch("rescale_nhwc_kernel");
 }
 
 int odvae_nhwc_to_nchw(const void* src, float* dst, int B, int C, int H, int W, int Cpad, int act_dtype, void* stream) {

@@ -205,7 +205,9 @@ __global__ void __launch_bounds__(256) sample_kl_bwd_kernel(
     if (dz != nullptr) dlv += g * eps[o] * 0.5f * expf(0.5f * lv);
     if (dmean_direct != nullptr) dmu += dmean_direct[o];
     if (dlogvar_direct != nullptr) dlv += dlogvar_direct[o];
-    if (!(lv >= -30.0f && lv <= 20.0f)) dlv = 0.0f;  // torch.clamp(-30, 20) passes the gradient on the CLOSED interval
+    // `logvar` is the CLAMPED value saved by the forward: an input outside [-30, 20] arrives here as exactly -30 / 20 and must
+    // get no gradient, so the test is strict (an input exactly on a bound -- measure zero -- would pass it in torch.clamp)
+    if (!(lv > -30.0f && lv < 20.0f)) dlv = 0.0f;
     const long long mrow = (static_cast<long long>(b) * HW + p) * ldm;
     dmoments[mrow + c] = from_f32<T>(dmu * out_scale);
     dmoments[mrow + Cz + c] = from_f32<T>(dlv * out_scale);

@@ -237,8 +237,22 @@ class PoseAutoencoder(_Base):
 
     def _rescale(self, x):  # AE.py:434-436, min/max over the whole batch tensor
         if x.is_cuda:
-            return ops.rescale_minmax(x)
+            f = self.fmt
+            return ops.rescale_minmax(x, nhwc=(ops.cpad(x.shape[1]), f.fwd, f.label(f.fwd)) if x.dim() == 4 else None)
         return 2. * (x - x.min()) / (x.max() - x.min()) - 1.
+
+    def check_overflow(self):
+        """fp16 range check (synchronises): raises RuntimeError if, since the last call, a forward activation was stored
+        saturated at +-65504 (pre-GroupNorm residual stream beyond fp16's range: run this model with compute_dtype=
+        torch.bfloat16) or an activation gradient was (lower grad_scale_dec / grad_scale_enc)."""
+        fwd, grad = ops.read_overflow(self.device)
+        if fwd:
+            raise RuntimeError("fp16 overflow: a forward activation exceeded 65504 and was stored saturated; this checkpoint "
+                               "needs compute_dtype=torch.bfloat16 (8 exponent bits) -- results of this step are not valid")
+        if grad:
+            raise RuntimeError("fp16 overflow: an activation gradient exceeded 65504 after scaling (gs_dec=%g, gs_enc=%g); set "
+                               "grad_scale_dec / grad_scale_enc lower -- results of this step are not valid"
+                               % (self.gs_dec.value, self.gs_enc.value))
 
     def _get_dropout_prob(self):  # AE.py:184-206
         step = self.global_step

@@ -111,7 +111,8 @@ class _LPIPSFn(torch.autograd.Function):
                 call("maxpool2x2_bwd", xin, g, gp, Bp, Hp, Wp, Cp, code)
                 g = gp
         dx1 = ops.nhwc_to_nchw_raw(g, 3, code)
-        ctx.t1 = ctx.f0 = None
+        # the saved towers stay alive until autograd frees the node: PoseLoss.calculate_adaptive_weight runs this backward
+        # once with retain_graph=True before the step's own backward
         return dx1, None, None, None
 
 

@@ -34,6 +34,8 @@ def bump_weight_epoch():
 def act_code(dtype):
     if dtype == torch.bfloat16:
         return BF16
+    if dtype == torch.float16:
+        return F16
     if dtype == torch.float32:
         return F32
     raise TypeError("activations must be float32 or bfloat16, got %s" % dtype)
@@ -58,15 +60,24 @@ class Format:
         operands in one format (a mix traps on B200), so its weight-gradient GEMMs read a bf16 copy of the forward operand
         (written by the GroupNorm apply kernel, or by `cast16` at the few other sites).
 
-    Torch labelling: autograd casts a gradient to the dtype of the forward tensor it belongs to, so every 16-bit NHWC
-    buffer is labelled torch.bfloat16 whatever bit pattern it holds (only this library's kernels ever read them; decode an
-    fp16 one with `.view(torch.float16)`).
+    Torch labelling: autograd casts a gradient to the dtype of the forward tensor it belongs to and ADDS the gradients of
+    a tensor that has several consumers with torch's own kernels, so a buffer's torch dtype must say what its gradient
+    holds: float32 / bfloat16 / float16 in the three uniform modes. Only in the "mixed" mode forward NHWC buffers are
+    labelled torch.bfloat16 while holding fp16 bit patterns (their gradients are genuine bf16; only this library's kernels
+    read the forward values; decode with `.view(torch.float16)`). The label is chosen where a tensor enters the NHWC domain
+    (`Format.label`) and propagates from input to output tensors inside the kernels' wrappers.
     """
 
     def __init__(self, fwd, attn, grad):
         self.fwd, self.attn, self.grad = fwd, attn, grad
         self.mixed = fwd != grad
-        self.buf = torch.float32 if fwd == F32 else torch.bfloat16
+        self.buf = self.label(fwd)
+
+    def label(self, code):
+        """torch dtype that labels a buffer of format `code` in this mode (see the class docstring)."""
+        if code == F32:
+            return torch.float32
+        return torch.float16 if (code == F16 and self.fwd == self.grad) else torch.bfloat16
 
     def __repr__(self):
         return "Format(fwd=%d, attn=%d, grad=%d)" % (self.fwd, self.attn, self.grad)
@@ -134,7 +145,7 @@ def format_of(x, holder=None):
     fmt = getattr(holder, "fmt", None) if holder is not None else None
     if fmt is not None:
         return fmt
-    return FORMAT_F32 if x.dtype == torch.float32 else FORMAT_BF16
+    return FORMAT_F32 if x.dtype == torch.float32 else (FORMAT_FP16 if x.dtype == torch.float16 else FORMAT_BF16)
 
 
 def assign_format(root, compute_dtype):
@@ -156,8 +167,14 @@ def assign_format(root, compute_dtype):
     return fmt
 
 
-def buf_dtype(code):
-    return torch.float32 if code == F32 else torch.bfloat16
+def buf_dtype(code, like=None):
+    """torch label of a buffer of format `code`: fp32 -> float32; 16-bit -> the label of the 16-bit tensor `like` it is derived
+    from (so float16-labelled inputs give float16-labelled outputs), else bfloat16."""
+    if code == F32:
+        return torch.float32
+    if like is not None and like in (torch.float16, torch.bfloat16):
+        return like
+    return torch.bfloat16
 
 
 def cast16_raw(x, src, dst):
@@ -186,6 +203,28 @@ def workspace(nbytes, device, tag):
         buf = torch.empty(max(int(nbytes), 1 << 16), dtype=torch.uint8, device=device)
         _WS[key] = buf
     return buf
+
+
+_OVERFLOW = {}
+
+
+def overflow_flags(device):
+    """int32[2] per device, set by the GroupNorm kernels: [0] an fp16 forward activation was stored saturated (+-65504),
+    [1] an fp16 activation gradient was. Sticky until read_overflow() clears them."""
+    t = _OVERFLOW.get(device.index)
+    if t is None:
+        t = torch.zeros(2, dtype=torch.int32, device=device)
+        _OVERFLOW[device.index] = t
+    return t
+
+
+def read_overflow(device):
+    """-> (forward_overflow, gradient_overflow) since the last call; synchronises with the device."""
+    t = overflow_flags(device)
+    f, g = (int(v) for v in t.tolist())
+    if f or g:
+        t.zero_()
+    return bool(f), bool(g)
 
 
 _TC_OK = {}
@@ -398,7 +437,7 @@ def conv_fwd_raw(x, spec, w, b, residual=None, out_nchw=False, op=None, out=None
              CinP, coutp, spec.cout, spec.geom, op, out, impl, 1)
         return y
     impl = conv_impl(op, B, H, W, CinP, spec.coutp, spec.geom)
-    y = torch.empty(B, Ho, Wo, spec.coutp, dtype=buf_dtype(out), device=x.device)
+    y = torch.empty(B, Ho, Wo, spec.coutp, dtype=buf_dtype(out, x.dtype), device=x.device)
     if gn_stats and FUSE_GN_STATS and impl == IMPL_TC and op != F32 and spec.coutp == spec.cout:
         nbytes = call("conv2d_fwd_gnstats_workspace_bytes", B, H, W, CinP, spec.coutp, spec.geom, GROUPS)
         if nbytes:
@@ -469,10 +508,11 @@ def gn_apply_raw(x, stats, gamma, beta, silu, in_code=None, out_code=None, copy_
     B, H, W, C = x.shape
     in_code = act_code(x.dtype) if in_code is None else in_code
     out_code = in_code if out_code is None else out_code
-    y = torch.empty(B, H, W, C, dtype=buf_dtype(out_code), device=x.device)
+    y = torch.empty(B, H, W, C, dtype=buf_dtype(out_code, x.dtype), device=x.device)
     y2 = None if copy_code is None else torch.empty(B, H, W, C, dtype=buf_dtype(copy_code), device=x.device)
     call("groupnorm_apply", x, stats, gamma.detach(), beta.detach(), y, y2, B, H * W, C, GROUPS, 1 if silu else 0,
-         in_code, out_code, copy_code if copy_code is not None else out_code)
+         in_code, out_code, copy_code if copy_code is not None else out_code,
+         overflow_flags(x.device) if in_code == F16 else None)
     return y if copy_code is None else (y, y2)
 
 
@@ -494,7 +534,8 @@ def gn_bwd_raw(x, stats, gamma, beta, dy, silu, dx_add=None, x_code=None, g_code
     nbytes = call("groupnorm_workspace_bytes", B, H * W, C, GROUPS)
     ws = workspace(nbytes, x.device, "gn")
     call("groupnorm_bwd", x, stats, gamma.detach(), beta.detach(), dy, dx_add, dx, dgamma, dbeta, B, H * W, C,
-         GROUPS, 1 if silu else 0, x_code, g_code, 0, float(pscale), ws, ws.numel())
+         GROUPS, 1 if silu else 0, x_code, g_code, 0, float(pscale),
+         overflow_flags(x.device) if g_code == F16 else None, ws, ws.numel())
     return dx, _ret(dgamma, g_direct), _ret(dbeta, b_direct)
 
 
@@ -502,8 +543,8 @@ def gemm_raw(A, Bm, D, M, N, K, batch, lda, ldb, ldd, sA, sB, sD, a_mn, b_mn, al
              code=None):
     """D[b] = alpha * op(A[b]) op(B[b])^T (+bias)(+residual); 16-bit operands (format `code`, default bf16) -> tcgen05
     with D in the same format (fp32 when D is a float tensor); fp32 operands -> the SIMT engine."""
-    if A.dtype == torch.bfloat16:
-        code = BF16 if code is None else code
+    if A.dtype in (torch.bfloat16, torch.float16):
+        code = act_code(A.dtype) if code is None else code
         call("gemm_16", A, Bm, D, M, N, K, batch, lda, ldb, ldd, sA, sB, sD, int(a_mn), int(b_mn), code, code,
              F32 if D.dtype == torch.float32 else code, float(alpha), bias, residual)
     else:
@@ -512,12 +553,12 @@ def gemm_raw(A, Bm, D, M, N, K, batch, lda, ldb, ldd, sA, sB, sD, a_mn, b_mn, al
     return D
 
 
-def nchw_to_nhwc_raw(x, Cpad, code, scale=1.0, shift=0.0):
-    """code: dtype code of the NHWC result (a torch dtype is accepted too)."""
+def nchw_to_nhwc_raw(x, Cpad, code, scale=1.0, shift=0.0, label=None):
+    """code: dtype code of the NHWC result (a torch dtype is accepted too); label: its torch dtype (Format.label)."""
     if isinstance(code, torch.dtype):
         code = act_code(code)
     B, C, H, W = x.shape
-    out = torch.empty(B, H, W, Cpad, dtype=buf_dtype(code), device=x.device)
+    out = torch.empty(B, H, W, Cpad, dtype=buf_dtype(code, label), device=x.device)
     call("nchw_to_nhwc", x, out, B, C, H, W, Cpad, code, float(scale), float(shift))
     return out
 
@@ -543,7 +584,10 @@ class ToNHWC(torch.autograd.Function):
     def forward(ctx, x, Cpad, compute_dtype, gscale=None):
         fmt = format_for(compute_dtype)
         ctx.C, ctx.fmt, ctx.gscale = x.shape[1], fmt, gscale
-        return nchw_to_nhwc_raw(_c(x.float()), Cpad, fmt.fwd)
+        pre = getattr(x, "_odvae_nhwc", None)  # written by rescale_minmax in the same pass as x itself
+        if pre is not None and pre[1] == Cpad and pre[2] == fmt.fwd and pre[0].shape[0] == x.shape[0]:
+            return pre[0]
+        return nchw_to_nhwc_raw(_c(x.float()), Cpad, fmt.fwd, label=fmt.label(fmt.fwd))
 
     @staticmethod
     def backward(ctx, dy):
@@ -560,13 +604,13 @@ class ToNCHW(torch.autograd.Function):
     @staticmethod
     def forward(ctx, x, C, compute_dtype=None, gscale=None):
         fmt = format_for(compute_dtype) if compute_dtype is not None else format_of(x)
-        ctx.Cpad, ctx.fmt, ctx.gscale = x.shape[-1], fmt, gscale
+        ctx.Cpad, ctx.fmt, ctx.gscale, ctx.label = x.shape[-1], fmt, gscale, x.dtype
         return nhwc_to_nchw_raw(x, C, fmt.fwd)
 
     @staticmethod
     def backward(ctx, dy):
         gs = ctx.gscale.value if ctx.gscale is not None else 1.0
-        return nchw_to_nhwc_raw(_c(dy.float()), ctx.Cpad, ctx.fmt.grad, scale=gs), None, None, None
+        return nchw_to_nhwc_raw(_c(dy.float()), ctx.Cpad, ctx.fmt.grad, scale=gs, label=ctx.label), None, None, None
 
 
 # ------------------------------------------------------------------------------------------------
@@ -585,7 +629,7 @@ class Conv(torch.autograd.Function):
         x, w, b = ctx.saved_tensors
         spec, fmt = ctx.spec, ctx.fmt
         if ctx.out_nchw:  # dec_obj gradient arrives NCHW fp32 (masked-L1 backward): bring it to NHWC, times the domain scale
-            dy = nchw_to_nhwc_raw(_c(dy.float()), cpad(spec.cout), fmt.grad, scale=gs_of(spec))
+            dy = nchw_to_nhwc_raw(_c(dy.float()), cpad(spec.cout), fmt.grad, scale=gs_of(spec), label=x.dtype)
         else:
             dy = _c(dy)
         dx = None
@@ -674,8 +718,8 @@ class AttnBlock(torch.autograd.Function):
         B, H, W, C = x.shape
         N = H * W
         fmt = format_of(x, blk)
-        ac = fmt.attn            # format code inside the block (bf16 in both 16-bit modes)
-        dt = buf_dtype(ac)
+        ac = fmt.attn            # format code inside the block
+        dt = buf_dtype(ac, x.dtype)
         stats = gn_stats_of(x, C, fmt.fwd)
         hn = gn_apply_raw(x, stats, gamma, beta, False, fmt.fwd, ac)
         wqkv, bqkv = blk.fused_qkv(wq, bq, wk, bk, wv, bv, ac)
@@ -711,7 +755,7 @@ class AttnBlock(torch.autograd.Function):
         N = H * W
         fmt = ctx.fmt
         ac = fmt.attn
-        dt = buf_dtype(ac)
+        dt = buf_dtype(ac, x.dtype)
         dout = _c(dout)
         scale = float(int(C) ** (-0.5))
         q, k, v = qkv[..., :C], qkv[..., C:2 * C], qkv[..., 2 * C:]
@@ -856,15 +900,27 @@ class SampleKL(torch.autograd.Function):
 class L1Masked(torch.autograd.Function):
     """sums[b] = sum_{c,p} |x*m - xhat*m|.  Gradient flows to xhat only (x is the ground truth)."""
 
+    # Parity-test hook (tests/test_parity_gpu.py): a reconstruction whose sign pattern sign(x*m - ref*m) selects the
+    # subgradient of |.| instead of our own xhat's. |x - xhat| has a kink at 0: two forwards that differ by 1e-3 flip the
+    # sign of ~0.3 % of the pixels, which alone moves every upstream gradient by ~2e-2 whatever the backward's precision.
+    sign_reference = None
+
     @staticmethod
     def forward(ctx, x, xhat, mask2d):
         B, C, H, W = xhat.shape
         HW = H * W
+        if mask2d.numel() != B * HW:
+            raise RuntimeError("mask_2d_bbox must hold one value per pixel ([B,1,H,W] or [B,H,W]), got %s for images %s"
+                               % (tuple(mask2d.shape), tuple(xhat.shape)))
         sums = torch.empty(B, dtype=torch.float32, device=xhat.device)
         sgn = torch.empty(B, C, H, W, dtype=torch.int8, device=xhat.device)
         nbytes = call("l1_masked_workspace_bytes", B, C, HW)
         ws = workspace(nbytes, xhat.device, "l1")
         call("l1_masked_fwd", x, xhat, mask2d, sums, sgn, B, C, HW, ws, ws.numel())
+        ref = L1Masked.sign_reference
+        if ref is not None:
+            scratch = torch.empty_like(sums)
+            call("l1_masked_fwd", x, _c(ref.to(xhat)), mask2d, scratch, sgn, B, C, HW, ws, ws.numel())
         ctx.save_for_backward(sgn)
         return sums
 
@@ -934,12 +990,22 @@ class Act(torch.autograd.Function):
         return dx, None
 
 
-def rescale_minmax(x):
-    """AE.py:434-436 `_rescale`: 2*(x-min)/(max-min)-1 over the whole batch tensor; two kernels, no host sync."""
+def rescale_minmax(x, nhwc=None):
+    """AE.py:434-436 `_rescale`: 2*(x-min)/(max-min)-1 over the whole batch tensor; a two-stage min/max reduction and ONE
+    pass that writes the rescaled NCHW fp32 tensor and, with nhwc = (Cpad, code, label), the NHWC 16-bit operand of
+    encoder.conv_in as well; that copy rides on the result as `out._odvae_nhwc` and ToNHWC picks it up. No host
+    sync."""
     x = _c(x.float())
     mm = torch.empty(2, dtype=torch.float32, device=x.device)
     ws = workspace(1 << 16, x.device, "minmax")
     call("minmax", x, x.numel(), mm, ws, ws.numel())
     out = torch.empty_like(x)
-    call("rescale", x, out, x.numel(), mm)
+    if nhwc is not None and x.dim() == 4:
+        Cpad, code, label = nhwc
+        B, C, H, W = x.shape
+        y = torch.empty(B, H, W, Cpad, dtype=buf_dtype(code, label), device=x.device)
+        call("rescale_nhwc", x, mm, out, y, B, C, H, W, Cpad, code)
+        out._odvae_nhwc = (y, Cpad, code)
+    else:
+        call("rescale", x, out, x.numel(), mm)
     return out

@@ -173,16 +173,19 @@ int odvae_conv2d_fwd_gnstats(const void* x, const void* w_packed, const float* b
                              int act_dtype, int out_dtype, void* workspace, size_t ws_bytes, void* stream);
 /* y (and, if y2 != NULL, a second copy y2 in out2_dtype) = [silu](GN(x)). Format triples (in, out, out2):
  * f32->f32; bf16->bf16(+bf16); fp16->fp16(+bf16: the copy a weight-gradient GEMM contracts with bf16 dy);
- * fp16->bf16 (attention blocks of the mixed mode). */
+ * fp16->bf16 (attention blocks of the mixed mode).
+ * overflow_flags (may be NULL): int32[2] on the device. fp16 inputs: [0] is set to 1 when x holds a value at +-65504, i.e. its
+ * producer's store saturated (forward range overflow); odvae_groupnorm_bwd sets [1] likewise for an fp16 dy (gradient scale too
+ * large). The flags are sticky; the host reads and clears them (PoseAutoencoder.check_overflow). */
 int odvae_groupnorm_apply(const void* x, const float* stats, const float* gamma, const float* beta, void* y, void* y2,
                           int B, int HW, int C, int G, int silu, int in_dtype, int out_dtype, int out2_dtype,
-                          void* stream);
+                          int32_t* overflow_flags, void* stream);
 /* dx = d/dx [silu](GN(x)) . dy (+ dx_add);  dgamma/dbeta fp32 [C] (accumulate != 0 adds).
  * act_dtype = format of x, grad_dtype = format of dy / dx_add / dx: (f32,f32), (bf16,bf16), (fp16,bf16), (fp16,fp16).
  * pgrad_scale multiplies dgamma / dbeta (inverse of the static activation-gradient scale of the all-fp16 mode). */
 int odvae_groupnorm_bwd(const void* x, const float* stats, const float* gamma, const float* beta, const void* dy,
                         const void* dx_add, void* dx, float* dgamma, float* dbeta, int B, int HW, int C, int G,
-                        int silu, int act_dtype, int grad_dtype, int accumulate, float pgrad_scale, void* workspace, size_t ws_bytes,
+                        int silu, int act_dtype, int grad_dtype, int accumulate, float pgrad_scale, int32_t* overflow_flags, void* workspace, size_t ws_bytes,
                         void* stream);
 
 /* ---------------------------------------------------------------------------------------------
@@ -299,6 +302,11 @@ int odvae_add(const void* a, const void* b, void* out, int64_t n, int act_dtype,
 
 /* dst = 2*(src - min)/(max - min) - 1 with minmax = {min, max} on the device (AE.py:434-436 `_rescale`) */
 int odvae_rescale(const float* src, float* dst, int64_t n, const float* minmax, void* stream);
+/* Input path in ONE pass (AE.py:296-304,434-436 + LD autoencoder.py:344-349): src NCHW fp32 [B,C,H,W] ->
+ * dst_nchw = 2*(src-min)/(max-min)-1 (fp32 NCHW: the loss's rgb_gt) AND dst_nhwc = the same values as NHWC act_dtype
+ * [B,H,W,Cpad] (channels >= C zero): encoder.conv_in's operand. Same arithmetic as odvae_rescale (bit-identical values). */
+int odvae_rescale_nhwc(const float* src, const float* minmax, float* dst_nchw, void* dst_nhwc, int B, int C, int H, int W,
+                       int Cpad, int act_dtype, void* stream);
 
 /* Pose MLP activations on fp32 [n] (pose_decoder.py:82-94 Tanh, pose_encoder.py:82-98 SiLU):
  * act = 1 tanh, 2 silu.  bwd: dx = dy * act'(x) with x the pre-activation. */

@@ -290,7 +290,8 @@ class Oracle:
         mask_bg = torch.zeros_like(class_gt)
         mask_bg[class_gt != BACKGROUND_CLASS_IDX] = 1
         nbg = torch.sum(mask_bg)
-        zero = torch.tensor(0.0)
+        dev = rgb_gt.device  # CPU in the tests; bench.py's `gpu_eager_baseline` runs this same restatement on cuda
+        zero = torch.zeros((), device=dev)
         inputs_rgb, rec_rgb = rgb_gt * mask_2d_bbox, dec_obj[:, :3] * mask_2d_bbox
         pose_rec, lhw_rec, fill_rec, logits = dec_pose[:, :4], dec_pose[:, 4:7], dec_pose[:, 7:8], dec_pose[:, 8:]
 
@@ -314,7 +315,7 @@ class Oracle:
         nll_el = rec / (torch.exp(logvar) + 1e-8) + logvar  # LOSS:147-158
         nll = (nll_el * mask_bg.view(-1, 1, 1, 1)).sum() / nbg if nbg > 0 else zero
         kl_obj = (post.kl() * mask_bg).sum() / nbg if nbg > 0 else zero  # LOSS:160-164
-        kl_rows = torch.zeros(len(class_names), 8)  # LOSS:191-205
+        kl_rows = torch.zeros(len(class_names), 8, device=dev, dtype=bbox_post.mean.dtype)  # LOSS:191-205
         for i, label in enumerate(class_names):
             if label == "background":
                 continue
@@ -326,7 +327,7 @@ class Oracle:
         w_bbox, w_fill = lp["bbox_weight"] * bbox_loss, lp["fill_factor_weight"] * fill_loss
         # generator side of the GAN (LOSS:280-304); discriminator parameters are treated as constants here (Lightning's
         # toggle_optimizer freezes them during the optimizer_idx 0 step)
-        g_loss, d_weight = torch.tensor(0.0), torch.tensor(0.0)
+        g_loss, d_weight = torch.zeros((), device=dev), torch.zeros((), device=dev)
         disc_cfg = lp.get("disc_factor", 1.0)
         disc_factor = adopt_weight(disc_cfg, step, threshold=lp.get("disc_start", 0))
         if self.has_disc:

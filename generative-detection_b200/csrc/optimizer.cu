@@ -166,6 +166,76 @@ mt_adam_kernel(const MtRow* __restrict__ rows, float lr, float b1, float b2, flo
   }
 }
 
+// ---------------------------------------------------------------------------------------------
+// Device-resident step counters (one per PARAMETER): the bias corrections 1 - beta^t are computed in the kernel from
+// steps[i], so a CUDA-graph replay of the optimizer advances them without the host, and a parameter whose gradient first
+// appears at step k (the decoder after the encoder-pretrain phase) starts its own count there -- torch.optim.Adam skips
+// parameters whose .grad is None, it does not age them. row = {p, g, m, v, n, step (float*), active (uint8*)}.
+// ---------------------------------------------------------------------------------------------
+struct MtRow7 {
+  unsigned long long p, g, m, v;
+  long long n;
+  unsigned long long step, active;
+};
+
+__global__ void mt_step_incr_kernel(float* __restrict__ steps, const uint8_t* __restrict__ active, int n) {
+  const int i = blockIdx.x * blockDim.x + threadIdx.x;
+  if (i < n && (active == nullptr || active[i])) steps[i] += 1.0f;
+}
+
+__global__ void __launch_bounds__(256)
+mt_adam_dev_kernel(const MtRow7* __restrict__ rows, float lr, float b1, float b2, float eps,
+                   const float* __restrict__ gnorm_sq, float max_norm, float grad_scale) {
+  const MtRow7 r = rows[blockIdx.x];
+  if (r.active != 0ull && *reinterpret_cast<const uint8_t*>(r.active) == 0) return;  // no gradient this step: skipped
+  const float t = *reinterpret_cast<const float*>(r.step);  // already incremented for this step
+  const float bc1 = 1.0f - powf(b1, t), bc2 = 1.0f - powf(b2, t);
+  float* p = reinterpret_cast<float*>(r.p);
+  const float* g = reinterpret_cast<const float*>(r.g);
+  float* m = reinterpret_cast<float*>(r.m);
+  float* v = reinterpret_cast<float*>(r.v);
+  float clip = grad_scale;
+  if (gnorm_sq != nullptr && max_norm > 0.0f) {
+    const float c = max_norm / (sqrtf(gnorm_sq[0]) * grad_scale + 1e-6f);
+    clip = c < 1.0f ? c * grad_scale : grad_scale;
+  }
+  const float step = lr / bc1;
+  const float inv_sqrt_bc2 = rsqrtf(bc2);
+  long long done = 0;
+  if (((r.p | r.g | r.m | r.v) & 15ull) == 0) {
+    const long long nv = r.n >> 2;
+    for (long long i = threadIdx.x; i < nv; i += 256) {
+      float4 pv = reinterpret_cast<float4*>(p)[i];
+      const float4 gv = __ldg(reinterpret_cast<const float4*>(g) + i);
+      float4 mv = reinterpret_cast<float4*>(m)[i];
+      float4 vv = reinterpret_cast<float4*>(v)[i];
+      float* pp = reinterpret_cast<float*>(&pv);
+      const float* gg = reinterpret_cast<const float*>(&gv);
+      float* mm = reinterpret_cast<float*>(&mv);
+      float* vvp = reinterpret_cast<float*>(&vv);
+#pragma unroll
+      for (int j = 0; j < 4; ++j) {
+        const float gr = gg[j] * clip;
+        mm[j] = b1 * mm[j] + (1.0f - b1) * gr;
+        vvp[j] = b2 * vvp[j] + (1.0f - b2) * gr * gr;
+        pp[j] -= step * mm[j] / (sqrtf(vvp[j]) * inv_sqrt_bc2 + eps);
+      }
+      reinterpret_cast<float4*>(p)[i] = pv;
+      reinterpret_cast<float4*>(m)[i] = mv;
+      reinterpret_cast<float4*>(v)[i] = vv;
+    }
+    done = nv << 2;
+  }
+  for (long long i = done + threadIdx.x; i < r.n; i += 256) {
+    const float gr = g[i] * clip;
+    const float mi = b1 * m[i] + (1.0f - b1) * gr;
+    const float vi = b2 * v[i] + (1.0f - b2) * gr * gr;
+    m[i] = mi;
+    v[i] = vi;
+    p[i] -= step * mi / (sqrtf(vi) * inv_sqrt_bc2 + eps);
+  }
+}
+
 }  // namespace odvae
 
 using namespace odvae;
@@ -227,6 +297,21 @@ int odvae_mt_adam_step(const void* table, int nrows, float lr, float beta1, floa
   mt_adam_kernel<<<nrows, 256, 0, st>>>(reinterpret_cast<const MtRow*>(table), lr, beta1, beta2, eps, bias_corr1,
                                         bias_corr2, gnorm_sq, max_norm, grad_scale);
   return check_launch("mt_adam_kernel");
+}
+
+int odvae_mt_step_incr(float* steps, const uint8_t* active, int n, void* stream) {
+  if (n <= 0) return ODVAE_ERR_SHAPE;
+  mt_step_incr_kernel<<<(n + 255) / 256, 256, 0, static_cast<cudaStream_t>(stream)>>>(steps, active, n);
+  return check_launch("mt_step_incr_kernel");
+}
+
+int odvae_mt_adam_step_dev(const void* table7, int nrows, float lr, float beta1, float beta2, float eps,
+                           const float* gnorm_sq, float max_norm, float grad_scale, void* stream) {
+  if (nrows <= 0) return ODVAE_ERR_SHAPE;
+  cudaStream_t st = static_cast<cudaStream_t>(stream);
+  mt_adam_dev_kernel<<<nrows, 256, 0, st>>>(reinterpret_cast<const MtRow7*>(table7), lr, beta1, beta2, eps, gnorm_sq,
+                                            max_norm, grad_scale);
+  return check_launch("mt_adam_dev_kernel");
 }
 
 }  // extern "C"

@@ -148,8 +148,10 @@ template <typename T>
 __global__ void __launch_bounds__(256) sample_kl_fwd_kernel(
     const T* __restrict__ moments, const float* __restrict__ eps, const uint8_t* __restrict__ keep,
     const float* __restrict__ noise, const float* __restrict__ enc_pose, float keep_scale, float* __restrict__ mean_o,
-    float* __restrict__ logvar_o, T* __restrict__ z, float* __restrict__ kl, int HW, int Cz, int CzPad, int ldm) {
+    float* __restrict__ logvar_o, T* __restrict__ z, float* __restrict__ kl, int HW, int Cz, int CzPad, int ldm,
+    const float* __restrict__ keep_scale_dev) {
   __shared__ float sm[8];
+  if (keep_scale_dev != nullptr) keep_scale = keep_scale_dev[0];  // CUDA-graph replay: 1/(1-p) changes every step
   const int b = blockIdx.x;
   const int n = Cz * HW;
   float acc = 0.0f;
@@ -188,7 +190,9 @@ __global__ void __launch_bounds__(256) sample_kl_bwd_kernel(
     const T* __restrict__ dz, const float* __restrict__ dkl, const float* __restrict__ dmean_direct,
     const float* __restrict__ dlogvar_direct, const float* __restrict__ mean, const float* __restrict__ logvar,
     const float* __restrict__ eps, const uint8_t* __restrict__ keep, float keep_scale, T* __restrict__ dmoments,
-    float* __restrict__ denc_pose, int HW, int Cz, int CzPad, int ldm, float dz_scale, float out_scale) {
+    float* __restrict__ denc_pose, int HW, int Cz, int CzPad, int ldm, float dz_scale, float out_scale,
+    const float* __restrict__ keep_scale_dev) {
+  if (keep_scale_dev != nullptr) keep_scale = keep_scale_dev[0];
   const int b = blockIdx.x;
   const int n = Cz * HW;
   const float gk = dkl != nullptr ? dkl[b] : 0.0f;
@@ -445,29 +449,30 @@ int odvae_softmax_rows_bwd(const float* dP, const void* P, void* dS, int64_t row
 
 int odvae_sample_kl_fwd(const void* moments, const float* eps, const uint8_t* keep, const float* noise,
                         const float* enc_pose, float keep_scale, float* mean, float* logvar, void* z, float* kl, int B,
-                        int HW, int Cz, int CzPad, int ld_moments, int act_dtype, void* stream) {
+                        int HW, int Cz, int CzPad, int ld_moments, int act_dtype,
+                        const float* keep_scale_dev, void* stream) {
   if (B <= 0 || ld_moments < 2 * Cz || CzPad < Cz) return ODVAE_ERR_SHAPE;
   if (z != nullptr && eps == nullptr) return ODVAE_ERR_SHAPE;
   cudaStream_t st = static_cast<cudaStream_t>(stream);
   if (act_dtype == ODVAE_BF16)
     sample_kl_fwd_kernel<bf16><<<B, 256, 0, st>>>(reinterpret_cast<const bf16*>(moments), eps, keep, noise, enc_pose,
                                                   keep_scale, mean, logvar, reinterpret_cast<bf16*>(z), kl, HW, Cz,
-                                                  CzPad, ld_moments);
+                                                  CzPad, ld_moments, keep_scale_dev);
   else if (act_dtype == ODVAE_F16)
     sample_kl_fwd_kernel<f16><<<B, 256, 0, st>>>(reinterpret_cast<const f16*>(moments), eps, keep, noise, enc_pose,
                                                  keep_scale, mean, logvar, reinterpret_cast<f16*>(z), kl, HW, Cz,
-                                                 CzPad, ld_moments);
+                                                 CzPad, ld_moments, keep_scale_dev);
   else
     sample_kl_fwd_kernel<float><<<B, 256, 0, st>>>(reinterpret_cast<const float*>(moments), eps, keep, noise, enc_pose,
                                                    keep_scale, mean, logvar, reinterpret_cast<float*>(z), kl, HW, Cz,
-                                                   CzPad, ld_moments);
+                                                   CzPad, ld_moments, keep_scale_dev);
   return check_launch("sample_kl_fwd_kernel");
 }
 
 int odvae_sample_kl_bwd(const void* dz, const float* dkl, const float* dmean_direct, const float* dlogvar_direct,
                         const float* mean, const float* logvar, const float* eps, const uint8_t* keep, float keep_scale,
                         void* dmoments, float* denc_pose, int B, int HW, int Cz, int CzPad, int ld_moments,
-                        int act_dtype, float dz_scale, float out_scale, void* stream) {
+                        int act_dtype, float dz_scale, float out_scale, const float* keep_scale_dev, void* stream) {
   if (B <= 0 || ld_moments < 2 * Cz || CzPad < Cz) return ODVAE_ERR_SHAPE;
   if (dz != nullptr && eps == nullptr) return ODVAE_ERR_SHAPE;
   cudaStream_t st = static_cast<cudaStream_t>(stream);
@@ -475,16 +480,16 @@ int odvae_sample_kl_bwd(const void* dz, const float* dkl, const float* dmean_dir
     sample_kl_bwd_kernel<bf16><<<B, 256, 0, st>>>(reinterpret_cast<const bf16*>(dz), dkl, dmean_direct, dlogvar_direct,
                                                   mean, logvar, eps, keep, keep_scale,
                                                   reinterpret_cast<bf16*>(dmoments), denc_pose, HW, Cz, CzPad,
-                                                  ld_moments, dz_scale, out_scale);
+                                                  ld_moments, dz_scale, out_scale, keep_scale_dev);
   else if (act_dtype == ODVAE_F16)
     sample_kl_bwd_kernel<f16><<<B, 256, 0, st>>>(reinterpret_cast<const f16*>(dz), dkl, dmean_direct, dlogvar_direct,
                                                  mean, logvar, eps, keep, keep_scale, reinterpret_cast<f16*>(dmoments),
-                                                 denc_pose, HW, Cz, CzPad, ld_moments, dz_scale, out_scale);
+                                                 denc_pose, HW, Cz, CzPad, ld_moments, dz_scale, out_scale, keep_scale_dev);
   else
     sample_kl_bwd_kernel<float><<<B, 256, 0, st>>>(reinterpret_cast<const float*>(dz), dkl, dmean_direct,
                                                    dlogvar_direct, mean, logvar, eps, keep, keep_scale,
                                                    reinterpret_cast<float*>(dmoments), denc_pose, HW, Cz, CzPad,
-                                                   ld_moments, dz_scale, out_scale);
+                                                   ld_moments, dz_scale, out_scale, keep_scale_dev);
   return check_launch("sample_kl_bwd_kernel");
 }
 

@@ -166,6 +166,7 @@ class PoseAutoencoder(_Base):
         # True: reuse the reconstruction of the optimizer_idx == 0 call of the same batch_idx instead.
         self.reuse_forward_for_disc = False
         self._fwd_cache = None
+        self._keep_scale_dev = None  # device float [1]: dropout 1/(1-p) read by the kernels (graphs.GraphedTrainStep)
         self.register_load_state_dict_post_hook(lambda *a: ops.bump_weight_epoch())
         self.fmt = ops.assign_format(self, compute_dtype)  # quant convs included (encoder/decoder did their own)
         # all-fp16 mode: static power-of-two scales the 16-bit activation gradients travel with (ops.GradScale); None = chosen
@@ -311,7 +312,8 @@ class PoseAutoencoder(_Base):
         if want_z and eps is None:
             eps = torch.zeros(moments.shape[0], zc, moments.shape[1], moments.shape[2], device=moments.device)
         mean, logvar, z, kl = ops.SampleKL.apply(moments, enc_pose, eps, keep, noise, keep_scale, zc, ops.cpad(zc),
-                                                 want_z, self.fmt, self.gs_dec, self.gs_enc)
+                                                 want_z, self.fmt, self.gs_dec, self.gs_enc,
+                                                 self._keep_scale_dev if keep is not None else None)
         post = FusedPosterior(mean, logvar, kl,
                               lambda: ops.ToNCHW.apply(moments, 2 * zc, self.compute_dtype, self.gs_enc))
         return post, (z if want_z else None)

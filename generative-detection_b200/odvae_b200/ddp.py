@@ -57,6 +57,8 @@ class GradArena:
 
     def begin_step(self):
         self._next = 0
+        for p in self.params:  # set again by every kernel wrapper that writes this parameter's gradient (ops._new_grad)
+            p._odvae_written = False
 
     def _launch(self, b):
         s, e = self.buckets[b]

@@ -130,6 +130,7 @@ class PoseLoss(nn.Module):
         table = torch.stack([torch.cat((d.mean, d.logvar), dim=1) for d in self.bbox_distribution_dict.values()])
         self._prior_table_cpu = table.float().contiguous()  # [L,8,2] (mean, clamped logvar)
         self._prior_table = None
+        self._static_prior_rows = None
 
     def _create_distribution_from_dataset_stats(self, dataset_stats):  # LOSS.py:82-109
         dist_dict = {}
@@ -150,6 +151,11 @@ class PoseLoss(nn.Module):
         return dist_dict
 
     def _prior_rows(self, labels, device):
+        if self._static_prior_rows is not None:  # graphs.GraphedTrainStep stages them outside the captured region
+            return self._static_prior_rows
+        return self._prior_rows_host(labels).to(device, non_blocking=True)
+
+    def _prior_rows_host(self, labels):
         idx = {l: i for i, l in enumerate(self._labels)}
         rows = []
         for l in labels:
@@ -157,7 +163,7 @@ class PoseLoss(nn.Module):
                 rows.append(-1)
             else:
                 rows.append(idx[l])  # KeyError for an unknown label, like the reference's dict lookup
-        return torch.tensor(rows, dtype=torch.int32).to(device, non_blocking=True)
+        return torch.tensor(rows, dtype=torch.int32)
 
     def forward(self, rgb_gt, mask_gt, pose_gt, dec_obj, dec_pose, class_gt, class_gt_label, bbox_gt, fill_factor_gt,
                 posterior_obj, bbox_posterior, optimizer_idx, global_step, mask_2d_bbox, last_layer=None, cond=None,

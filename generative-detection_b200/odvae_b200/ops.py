@@ -399,6 +399,7 @@ class probe_gradients:
 def _new_grad(p):
     dst = grad_dst(p) if _PROBE[0] == 0 else None
     if dst is not None:
+        p._odvae_written = True  # FusedAdam: this parameter has a gradient in this step (ddp.GradArena.begin_step clears)
         return dst, True
     return torch.empty(p.shape, dtype=torch.float32, device=p.device), False
 
@@ -804,6 +805,7 @@ class AttnBlock(torch.autograd.Function):
             for i, (w_, b_) in enumerate(((wq, bq), (wk, bk), (wv, bv))):
                 grad_dst(w_).copy_(dwqkv[i * C:(i + 1) * C].view(C, C, 1, 1))
                 grad_dst(b_).copy_(dbqkv[i * C:(i + 1) * C])
+                w_._odvae_written = b_._odvae_written = True
             gq = gk = gv = gbq = gbk = gbv = None
         else:
             gq, gk, gv = (dwqkv[i * C:(i + 1) * C].view(C, C, 1, 1) for i in range(3))
@@ -851,9 +853,10 @@ class UpsampleConv(torch.autograd.Function):
 # ------------------------------------------------------------------------------------------------
 class SampleKL(torch.autograd.Function):
     @staticmethod
-    def forward(ctx, moments, enc_pose, eps, keep, noise, keep_scale, Cz, CzPad, want_z, fmt=None, gs_dec=None, gs_enc=None):
+    def forward(ctx, moments, enc_pose, eps, keep, noise, keep_scale, Cz, CzPad, want_z, fmt=None, gs_dec=None, gs_enc=None,
+                keep_scale_dev=None):
         """gs_dec / gs_enc: GradScale of the decoder side (the scale dz arrives with) and of the encoder side (the scale
-        dmoments leaves with)."""
+        dmoments leaves with). keep_scale_dev: device float [1] that overrides keep_scale (CUDA-graph replay)."""
         fmt = fmt if fmt is not None else format_of(moments)
         ctx.fmt, ctx.gs = fmt, (gs_dec, gs_enc)
         B, H, W, ld = moments.shape
@@ -864,8 +867,9 @@ class SampleKL(torch.autograd.Function):
         kl = torch.empty(B, dtype=torch.float32, device=dev)
         z = torch.empty(B, H, W, CzPad, dtype=moments.dtype, device=dev) if want_z else None
         call("sample_kl_fwd", moments, eps, keep, noise, enc_pose, float(keep_scale), mean, logvar, z, kl, B, HW, Cz,
-             CzPad, ld, fmt.fwd)
+             CzPad, ld, fmt.fwd, keep_scale_dev)
         ctx.cfg = (Cz, CzPad, ld, float(keep_scale), moments.dtype, enc_pose is not None)
+        ctx.keep_scale_dev = keep_scale_dev
         ctx.save_for_backward(mean, logvar, eps, keep)
         if z is None:
             z = torch.empty(0, device=dev)
@@ -888,10 +892,10 @@ class SampleKL(torch.autograd.Function):
         gs_dec = ctx.gs[0].value if ctx.gs[0] is not None else 1.0
         gs_enc = ctx.gs[1].value if ctx.gs[1] is not None else 1.0
         call("sample_kl_bwd", dz, dkl, dmean, dlogvar, mean, logvar, eps, keep, keep_scale, dmom, dpose, B, H * W, Cz,
-             CzPad, ld, ctx.fmt.grad, 1.0 / gs_dec, gs_enc)
+             CzPad, ld, ctx.fmt.grad, 1.0 / gs_dec, gs_enc, ctx.keep_scale_dev)
         if has_pose and dpose is None:
             dpose = torch.zeros(B, Cz * H * W, dtype=torch.float32, device=dev)
-        return dmom, dpose, None, None, None, None, None, None, None, None, None, None
+        return dmom, dpose, None, None, None, None, None, None, None, None, None, None, None
 
 
 # ------------------------------------------------------------------------------------------------

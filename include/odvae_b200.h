@@ -211,11 +211,13 @@ int odvae_gemm_simt(const void* A, const void* B, void* D, int M, int N, int K, 
  * outputs (all fp32, NCHW [B,Cz,h,w] = the module-boundary layout): mean, logvar (clamped).
  * z: NHWC act_dtype [B,HW,CzPad] = (mean + std*eps)*keep*keep_scale + noise + enc_pose (zero padded).
  * kl[B] = 0.5*sum(mean^2 + var - 1 - logvar).  eps/noise fp32 NCHW, keep uint8 NCHW, enc_pose fp32 [B,Cz*HW]
- * (NCHW flattened; may be NULL).
+ * (NCHW flattened; may be NULL). keep_scale_dev (may be NULL): device float that overrides `keep_scale` -- the dropout
+ * ramp changes 1/(1-p) every step, and a CUDA-graph replay of the train step reads it from memory.
  * ------------------------------------------------------------------------------------------- */
 int odvae_sample_kl_fwd(const void* moments, const float* eps, const uint8_t* keep, const float* noise,
                         const float* enc_pose, float keep_scale, float* mean, float* logvar, void* z,
-                        float* kl, int B, int HW, int Cz, int CzPad, int ld_moments, int act_dtype, void* stream);
+                        float* kl, int B, int HW, int Cz, int CzPad, int ld_moments, int act_dtype,
+                        const float* keep_scale_dev, void* stream);
 /* dmoments = d(z)/d(moments)^T dz + dkl[b] * dKL/dmoments (+ direct grads on mean/logvar outputs).
  * dz: NHWC act_dtype [B,HW,CzPad]; denc_pose fp32 [B,Cz*HW] (NCHW flattened) = dz * dz_scale.
  * dz_scale / out_scale: the decoder-side gradient arrives multiplied by a static scale (dz_scale = its inverse) and the
@@ -223,7 +225,8 @@ int odvae_sample_kl_fwd(const void* moments, const float* eps, const uint8_t* ke
 int odvae_sample_kl_bwd(const void* dz, const float* dkl, const float* dmean_direct, const float* dlogvar_direct,
                         const float* mean, const float* logvar, const float* eps, const uint8_t* keep,
                         float keep_scale, void* dmoments, float* denc_pose, int B, int HW, int Cz, int CzPad,
-                        int ld_moments, int act_dtype, float dz_scale, float out_scale, void* stream);
+                        int ld_moments, int act_dtype, float dz_scale, float out_scale, const float* keep_scale_dev,
+                        void* stream);
 
 /* ---------------------------------------------------------------------------------------------
  * Masked L1 reconstruction term (PoseLoss._get_rec_loss/_get_nll_loss LOSS.py:134-158, masks :250-257)
@@ -260,6 +263,14 @@ int odvae_mt_sumsq(const void* table, int nrows, float* out1, void* workspace, s
 int odvae_mt_adam_step(const void* table, int nrows, float lr, float beta1, float beta2, float eps,
                        float bias_corr1, float bias_corr2, const float* gnorm_sq, float max_norm,
                        float grad_scale, void* stream);
+/* Variant with DEVICE-resident step counters, one per parameter (torch.optim.Adam's state["step"] as a device float): table7
+ * rows = {p, g, m, v, count, step_ptr, active_ptr}; the kernel computes 1 - beta^t from *step_ptr, and skips rows whose
+ * *active_ptr (uint8, may be 0 = always active) is 0 -- a parameter without a gradient this step is neither updated nor aged
+ * (torch skips .grad is None). odvae_mt_step_incr advances steps[i] (+1 where active[i]) and runs first. Lets a CUDA-graph
+ * replay of the whole train step advance the optimizer without the host. */
+int odvae_mt_step_incr(float* steps, const uint8_t* active, int n, void* stream);
+int odvae_mt_adam_step_dev(const void* table7, int nrows, float lr, float beta1, float beta2, float eps,
+                           const float* gnorm_sq, float max_norm, float grad_scale, void* stream);
 
 /* ---------------------------------------------------------------------------------------------
  * Small heads (csrc/heads.cu): pose-MLP glue and the whole PoseLoss reduction tail, one launch each way.

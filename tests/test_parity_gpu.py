@@ -359,7 +359,9 @@ def _scaled_model(dtype, factor):
 
 
 def test_fp16_overflow_is_detected_and_bf16_mode_handles_the_same_weights():
+    from odvae_b200 import ops
     from oracle import odvae_oracle
+    ops.read_overflow(torch.device("cuda", 0))  # the flags are per device and sticky: drop what earlier tests left behind
     # (1) no false positive on the ordinary weights
     model, params, batch, noise, step = _scaled_model(torch.float16, 1.0)
     model.training_step(H.clone_batch(batch), 0, 0).backward()
@@ -389,6 +391,8 @@ def test_fp16_overflow_is_detected_and_bf16_mode_handles_the_same_weights():
 
 
 def test_fp16_gradient_scale_overflow_is_detected():
+    from odvae_b200 import ops
+    ops.read_overflow(torch.device("cuda", 0))
     model, params, batch, noise, step = _scaled_model(torch.float16, 1.0)
     model.grad_scale_dec = 2.0 ** 30  # absurd: |dL/d dec_obj| ~ 0.1 * 2^30 does not fit fp16
     model.training_step(H.clone_batch(batch), 0, 0).backward()

@@ -54,6 +54,10 @@ def parse():
                     help="configs1 = BASELINE.json configs[1] (perceptual_weight 0, disc_factor 0; the bench line); full = the "
                          "yaml's own objective: LPIPS + PatchGAN generator term with the adaptive weight in the optimizer_idx 0 "
                          "step AND the optimizer_idx 1 discriminator step, i.e. one whole batch of the reference loop")
+    ap.add_argument("--step-graph", default="auto", choices=["auto", "on", "off"],
+                    help="train workload: replay the whole step (fwd + loss + bwd + clip + Adam + weight re-pack, ~1000 "
+                         "launches) as ONE CUDA graph (odvae_b200/graphs.py GraphedTrainStep; bit-identical to the eager launch "
+                         "sequence). auto = on for 1 GPU with --objective configs1, off otherwise")
     ap.add_argument("--extras", type=int, default=1,
                     help="N = 1 only: also measure the full objective, the encode sweep, the 512x512 step and the eager "
                          "cuDNN/cuBLAS baseline, reported under `extra` (0 = skip)")
@@ -589,6 +593,12 @@ def run_ours(args):
         step_fn = lambda b, i: fit.training_batch(b, i)[0]
     else:
         step_fn = TrainStep(model, lr=model.learning_rate, max_grad_norm=1.0)
+    eager_fn = step_fn
+    use_graph = (not full) and args.workload == "train" and \
+        (args.step_graph == "on" or (args.step_graph == "auto" and world == 1)) and not args.ncu_step
+    if use_graph:
+        from odvae_b200.graphs import GraphedTrainStep
+        step_fn = GraphedTrainStep(eager_fn)
 
     R = args.res
     if args.workload in ("encode", "recon"):
@@ -648,7 +658,7 @@ def run_ours(args):
         sampler.start()
     ms, _ = timed(resident, args.steps, False)
     host_enqueue_ms = host_ms[0]
-    launches = lib.call("launch_count") - launches0
+    launches = step_fn.launches_per_replay * args.steps if use_graph else lib.call("launch_count") - launches0
     ms_e2e, last_loss = timed(pinned, args.steps, True)
     clocks = sampler.stop() if rank == 0 else None
     identical = replicas_identical(model, world) if world > 1 else None
@@ -656,12 +666,12 @@ def run_ours(args):
     roof = None
     flops_img = FLOPS_TRAIN_PER_IMG
     if not args.no_roofline and rank != 0:
-        step_fn(clone(resident), 0)  # every rank runs the extra (untimed) step: its gradient all-reduces are collective
+        eager_fn(clone(resident), 0)  # every rank runs the extra (untimed) step: its gradient all-reduces are collective
         torch.cuda.synchronize()
     if rank == 0 and not args.no_roofline:
         prof = EngineProfiler()
         prof.install()
-        step_fn(clone(resident), 0)
+        eager_fn(clone(resident), 0)  # the SAME launch sequence eagerly, each conv / GEMM / GroupNorm call between CUDA events
         prof.remove()
         eng_ms, counted, ncalls, by = prof.summary()
         if args.shapes:
@@ -703,6 +713,7 @@ def run_ours(args):
                 "e2e": {"value": n_img / (ms_e2e * 1e-3), "unit": "images/sec", "h2d_bytes_per_step": h2d,
                         "d2h_bytes_per_step": 4, "ms_per_step": ms_e2e / args.steps, "last_loss": last_loss},
                 "gpu_launches": int(launches), "host_enqueue_ms_per_step": host_enqueue_ms,
+                "cuda_graph": bool(use_graph),
                 "clocks": clocks, "roofline": roof, "cpu_baseline": None,
                 "pct_of_tensor_roofline_whole_step": flops_img * B / (ms / args.steps * 1e-3) / 1e12 /
                 peaks()[0]["bf16_tflops_sustained"]}
@@ -711,7 +722,7 @@ def run_ours(args):
     # ---- N = 1 extras: the other BASELINE.json configs and comparators, each a short measurement after the main one
     if world == 1 and rank == 0:
         import gc
-        del step_fn, model
+        del step_fn, eager_fn, model
         if full:
             del fit
         gc.collect()

@@ -126,6 +126,97 @@ int odvae_conv2d_wgrad(const void* x, const void* dy, float* dw_oihw, float* db,
   return st;
 }
 
+// ---- nearest-2x upsample + 3x3 conv as parity-phase 2x2 convs over the low-resolution input (LD model.py:53-57) ----
+int odvae_upconv_tc_supported(int B, int H, int W, int CinP, int CoutP) {
+  EngineDesc ds[4];
+  if (describe_upconv_fwd(ds, nullptr, nullptr, 2, nullptr, nullptr, B, H, W, CinP, CoutP) != ODVAE_OK) return 0;
+  for (int i = 0; i < 4; ++i)
+    if (!ds[i].tc_ok) return 0;
+  EngineDesc d;
+  if (describe_upconv_dgrad(d, nullptr, nullptr, nullptr, B, H, W, CinP, CoutP) != ODVAE_OK || !d.tc_ok) return 0;
+  if (describe_upconv_wgrad(d, 0, nullptr, nullptr, 2, nullptr, B, H, W, CinP, CoutP, ODVAE_IMPL_TC) != ODVAE_OK) return 0;
+  return d.tc_ok ? 1 : 0;
+}
+
+int odvae_upconv_fwd(const void* x, const void* w_phase_packed, const float* bias, void* y, int B, int H, int W, int CinP,
+                     int CoutP, int act_dtype, int impl, void* stream) {
+  EngineDesc ds[4];
+  int st = describe_upconv_fwd(ds, x, w_phase_packed, act_dtype == ODVAE_F32 ? 4 : 2, bias, y, B, H, W, CinP, CoutP);
+  if (st != ODVAE_OK) return st;
+  for (int i = 0; i < 4; ++i) {
+    if (act_dtype == ODVAE_F16) ds[i].p.out_mode = OUT_F16;
+    st = run_engine(ds[i], impl, act_dtype, static_cast<cudaStream_t>(stream));
+    if (st != ODVAE_OK) return st;
+  }
+  return ODVAE_OK;
+}
+
+int odvae_upconv_dgrad(const void* dy, const void* w_dgrad_packed, void* dx, int B, int H, int W, int CinP, int CoutP,
+                       int act_dtype, int impl, void* stream) {
+  EngineDesc d;
+  int st = describe_upconv_dgrad(d, dy, w_dgrad_packed, dx, B, H, W, CinP, CoutP);
+  if (st != ODVAE_OK) return st;
+  if (act_dtype == ODVAE_F16) d.p.out_mode = OUT_F16;
+  return run_engine(d, impl, act_dtype, static_cast<cudaStream_t>(stream));
+}
+
+static size_t upconv_phase_ws(const EngineDesc& d, int CoutP, int CinP) {
+  return ((static_cast<size_t>(d.p.ntaps) * d.p.split_k * CoutP * CinP * sizeof(float) + 255) / 256) * 256;
+}
+
+size_t odvae_upconv_wgrad_workspace_bytes(int B, int H, int W, int CinP, int CoutP, int Cin, int Cout, int impl) {
+  EngineDesc d;
+  if (describe_upconv_wgrad(d, 0, nullptr, nullptr, 2, nullptr, B, H, W, CinP, CoutP, impl) != ODVAE_OK) return 0;
+  // split-K partials of one phase (reused) + colsum partials + the 4 folded phase results [4][Cout][Cin][4] + [4][Cout]
+  return upconv_phase_ws(d, CoutP, CinP) + colsum_workspace_bytes(CoutP) + 256 +
+         (static_cast<size_t>(16) * Cout * Cin + 4 * static_cast<size_t>(Cout)) * sizeof(float) + 256;
+}
+
+int odvae_upconv_wgrad(const void* x, const void* dy, float* dw_oihw, float* db, int B, int H, int W, int CinP, int CoutP,
+                       int Cin, int Cout, int act_dtype, int impl, int accumulate, float out_scale, void* workspace,
+                       size_t ws_bytes, void* stream) {
+  cudaStream_t s = static_cast<cudaStream_t>(stream);
+  if (ws_bytes < odvae_upconv_wgrad_workspace_bytes(B, H, W, CinP, CoutP, Cin, Cout, impl) - 256) return ODVAE_ERR_WORKSPACE;
+  uint8_t* base = reinterpret_cast<uint8_t*>(workspace);
+  float* ws = reinterpret_cast<float*>(base);
+  EngineDesc d0;
+  int st = describe_upconv_wgrad(d0, 0, x, dy, act_dtype == ODVAE_F32 ? 4 : 2, ws, B, H, W, CinP, CoutP, impl);
+  if (st != ODVAE_OK) return st;
+  const size_t part = upconv_phase_ws(d0, CoutP, CinP);
+  float* cpart = reinterpret_cast<float*>(base + part);
+  float* dwp = reinterpret_cast<float*>(base + part + ((colsum_workspace_bytes(CoutP) + 255) / 256) * 256);
+  float* dbp = dwp + static_cast<size_t>(16) * Cout * Cin;
+  for (int ph = 0; ph < 4; ++ph) {
+    EngineDesc d;
+    st = describe_upconv_wgrad(d, ph, x, dy, act_dtype == ODVAE_F32 ? 4 : 2, ws, B, H, W, CinP, CoutP, impl);
+    if (st != ODVAE_OK) return st;
+    const int cs_rows = d.p.ntaps * d.p.split_k * 2;
+    const bool fused_db = db != nullptr && impl == ODVAE_IMPL_TC && d.tc_ok &&
+                          static_cast<size_t>(cs_rows) * Cout * sizeof(float) <= colsum_workspace_bytes(CoutP);
+    if (fused_db) {
+      d.p.colsum = cpart;
+      d.p.colsum_cols = Cout;
+    }
+    st = run_engine(d, impl, act_dtype, s);
+    if (st != ODVAE_OK) return st;
+    float* dbp_ph = dbp + static_cast<size_t>(ph) * Cout;
+    st = launch_wgrad_reduce(ws, dwp + static_cast<size_t>(ph) * 4 * Cout * Cin, Cout, Cin, 4, CoutP, CinP, d.p.split_k, 0, s,
+                             fused_db ? cpart : nullptr, fused_db ? cs_rows : 0, db != nullptr ? dbp_ph : nullptr, 1.0f);
+    if (st != ODVAE_OK) return st;
+    if (db != nullptr && !fused_db) {
+      // column sums of this phase's quarter of dy: a strided gather -> go through the generic colsum on the phase rows
+      // (SIMT / fp32 validation path only): rows of one phase are not contiguous, so sum the whole dy once instead
+      if (ph == 0) {
+        st = launch_colsum(dy, static_cast<long long>(B) * 4 * H * W, Cout, CoutP, act_dtype, dbp_ph, 0, cpart, s, 1.0f);
+        if (st != ODVAE_OK) return st;
+      } else {
+        ODVAE_CUDA_TRY(cudaMemsetAsync(dbp_ph, 0, static_cast<size_t>(Cout) * sizeof(float), s));
+      }
+    }
+  }
+  return launch_upconv_wgrad_fold(dwp, db != nullptr ? dbp : nullptr, dw_oihw, db, Cout, Cin, accumulate, out_scale, s);
+}
+
 int odvae_gemm_bf16(const void* A, const void* B, void* D, int M, int N, int K, int batch, int64_t lda, int64_t ldb,
                     int64_t ldd, int64_t strideA, int64_t strideB, int64_t strideD, int a_mn, int b_mn, int out_dtype,
                     float alpha, const float* bias, const void* residual, void* stream) {

@@ -27,7 +27,7 @@ struct TcParams {
   int num_k_iters;
   // spatial operand (CONV: A, WGRAD: B): coords (c, x, [ph], y, b)
   int sp_rank, cchunks, ntaps;
-  int tap_dx[9], tap_dy[9], tap_c[9], tap_ph[9];
+  int tap_dx[16], tap_dy[16], tap_c[16], tap_ph[16];  // up to 16 taps (the 2x-upsample conv's single-launch dgrad)
   // CONV m-tile geometry (box bw x bh = 128 output pixels)
   int bw_log2, tiles_x, tiles_y;
   int swap;  // CONV with swapped roles: M = 128 output channels (weights), N = 256 output pixels (2 pixel boxes)

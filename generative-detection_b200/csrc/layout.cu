@@ -255,6 +255,78 @@ pack_conv_weight_mt_kernel(const long long* __restrict__ table, int n_entries) {
   }
 }
 
+// ---------------------------------------------------------------------------------------------
+// nearest-2x upsample + 3x3 conv as parity-phase 2x2 convs (engine_host.cu describe_upconv_*): weight pre-sums and the fold of
+// the 16 (phase, tap) weight-gradient matrices back onto the 3x3 filter. r -> a(py, r): py = 0: {0 -> 0; 1, 2 -> 1},
+// py = 1: {0, 1 -> 0; 2 -> 1} (which low-resolution row the upsampled row 2i + py + r - 1 falls on).
+// ---------------------------------------------------------------------------------------------
+__device__ __forceinline__ int up_tap_of(int parity, int r) { return parity == 0 ? (r == 0 ? 0 : 1) : (r == 2 ? 1 : 0); }
+
+__device__ __forceinline__ float upconv_presum(const float* __restrict__ w, int co, int ci, int Cin, int py, int px, int a,
+                                               int b) {
+  float v = 0.0f;
+  for (int r = 0; r < 3; ++r) {
+    if (up_tap_of(py, r) != a) continue;
+    for (int s = 0; s < 3; ++s)
+      if (up_tap_of(px, s) == b) v += __ldg(w + (static_cast<long long>(co) * Cin + ci) * 9 + r * 3 + s);
+  }
+  return v;
+}
+
+// which = 0: fwd [phase][CoutP][tap = a*2+b][CinP];  which = 1: dgrad [CinP][t16 = ((py*2+a)*2+px)*2+b][CoutP]
+template <typename T>
+__global__ void pack_upconv_weight_kernel(const float* __restrict__ w, T* __restrict__ P, int Cout, int Cin, int CoutP,
+                                          int CinP, int which) {
+  const long long total = 16ll * CoutP * CinP;
+  for (long long e = blockIdx.x * static_cast<long long>(blockDim.x) + threadIdx.x; e < total;
+       e += static_cast<long long>(gridDim.x) * blockDim.x) {
+    int co, ci, py, px, a, b;
+    if (which == 0) {
+      ci = static_cast<int>(e % CinP);
+      long long q = e / CinP;
+      const int t = static_cast<int>(q & 3);
+      q >>= 2;
+      co = static_cast<int>(q % CoutP);
+      const int ph = static_cast<int>(q / CoutP);
+      py = ph >> 1; px = ph & 1; a = t >> 1; b = t & 1;
+    } else {
+      co = static_cast<int>(e % CoutP);
+      long long q = e / CoutP;
+      const int t = static_cast<int>(q & 15);
+      ci = static_cast<int>(q >> 4);
+      py = t >> 3; a = (t >> 2) & 1; px = (t >> 1) & 1; b = t & 1;
+    }
+    const float v = (co < Cout && ci < Cin) ? upconv_presum(w, co, ci, Cin, py, px, a, b) : 0.0f;
+    P[e] = from_f32<T>(v);
+  }
+}
+
+// dwp: [4 phases][Cout][Cin][4 taps] (wgrad_reduce layout with taps = 4); dbp: [4][Cout] or null
+__global__ void upconv_wgrad_fold_kernel(const float* __restrict__ dwp, const float* __restrict__ dbp, float* __restrict__ dw,
+                                         float* __restrict__ db, int Cout, int Cin, int accumulate, float scale) {
+  const long long total = static_cast<long long>(Cout) * Cin * 9;
+  const long long slab = static_cast<long long>(Cout) * Cin * 4;
+  for (long long e = blockIdx.x * static_cast<long long>(blockDim.x) + threadIdx.x; e < total;
+       e += static_cast<long long>(gridDim.x) * blockDim.x) {
+    const int rs = static_cast<int>(e % 9);
+    const long long oc = e / 9;
+    const int r = rs / 3, s = rs - r * 3;
+    float acc = 0.0f;
+#pragma unroll
+    for (int ph = 0; ph < 4; ++ph)
+      acc += dwp[ph * slab + oc * 4 + up_tap_of(ph >> 1, r) * 2 + up_tap_of(ph & 1, s)];
+    acc *= scale;
+    dw[e] = accumulate ? dw[e] + acc : acc;
+  }
+  if (db != nullptr && dbp != nullptr) {
+    const long long c = blockIdx.x * static_cast<long long>(blockDim.x) + threadIdx.x;
+    if (c < Cout) {
+      const float t = ((dbp[c] + dbp[Cout + c]) + (dbp[2 * Cout + c] + dbp[3 * Cout + c])) * scale;
+      db[c] = accumulate ? db[c] + t : t;
+    }
+  }
+}
+
 // dw[co][ci][tap] (+)= sum_split ws[(tap*split_k + split)][co][ci]   (ws rows: CoutP x CinP)
 // One thread sums VEC consecutive ci over all splits, 8 independent (vector) loads in flight, added in split order
 // (the order is part of the bit-stability contract). The workspace was written by the preceding weight-gradient kernel
@@ -537,6 +609,15 @@ int launch_wgrad_reduce(const float* ws, float* dw, int Cout, int Cin, int taps,
   return check_launch("wgrad_reduce_kernel");
 }
 
+int launch_upconv_wgrad_fold(const float* dwp, const float* dbp, float* dw, float* db, int Cout, int Cin, int accumulate,
+                             float scale, cudaStream_t st) {
+  long long total = static_cast<long long>(Cout) * Cin * 9;
+  int grid = grid_for(total, 256);
+  if (static_cast<long long>(grid) * 256 < Cout) grid = (Cout + 255) / 256;
+  upconv_wgrad_fold_kernel<<<grid, 256, 0, st>>>(dwp, dbp, dw, db, Cout, Cin, accumulate, scale);
+  return check_launch("upconv_wgrad_fold_kernel");
+}
+
 // final stage alone: out[c] (+)= sum_r part[r][c] -- the tcgen05 weight-gradient kernel writes the partials itself
 int launch_colsum_final(const float* part, int nrows, int cols, float* out, int accumulate, cudaStream_t st) {
   colsum_stage2<<<(cols + 31) / 32, dim3(32, 8), 0, st>>>(part, nrows, cols, out, accumulate);
@@ -661,6 +742,20 @@ int odvae_pack_conv_weight(const float* w_oihw, void* packed, int Cout, int Cin,
   else
     pack_conv_weight_kernel<float><<<grid_for(total, 256), 256, 0, st>>>(w_oihw, reinterpret_cast<float*>(packed), Cout, Cin, k, CoutP, CinP, which, s2);
   return check_launch("pack_conv_weight_kernel");
+}
+
+int odvae_pack_upconv_weight(const float* w_oihw, void* packed, int Cout, int Cin, int CoutP, int CinP, int which,
+                             int act_dtype, void* stream) {
+  if (Cout <= 0 || Cin <= 0 || CoutP < Cout || CinP < Cin || (which != 0 && which != 1)) return ODVAE_ERR_SHAPE;
+  cudaStream_t st = static_cast<cudaStream_t>(stream);
+  const long long total = 16ll * CoutP * CinP;
+  if (act_dtype == ODVAE_BF16)
+    pack_upconv_weight_kernel<bf16><<<grid_for(total, 256), 256, 0, st>>>(w_oihw, reinterpret_cast<bf16*>(packed), Cout, Cin, CoutP, CinP, which);
+  else if (act_dtype == ODVAE_F16)
+    pack_upconv_weight_kernel<f16><<<grid_for(total, 256), 256, 0, st>>>(w_oihw, reinterpret_cast<f16*>(packed), Cout, Cin, CoutP, CinP, which);
+  else
+    pack_upconv_weight_kernel<float><<<grid_for(total, 256), 256, 0, st>>>(w_oihw, reinterpret_cast<float*>(packed), Cout, Cin, CoutP, CinP, which);
+  return check_launch("pack_upconv_weight_kernel");
 }
 
 int64_t odvae_pack_conv_weights_mt_blocks(int CoutP, int CinP, int geom) {

@@ -43,9 +43,12 @@ __device__ __forceinline__ float simt_load_a(const SimtParams& s, long long m, l
     const int tap = static_cast<int>(k / s.chan_per_tap);
     const int c = static_cast<int>(k - static_cast<long long>(tap) * s.chan_per_tap);
     return spatial_fetch<T>(s.A, c + p.tap_c[tap], x + p.tap_dx[tap], p.tap_ph[tap], y + p.tap_dy[tap], b);
-  } else {  // WGRAD: A(m = co, k = output pixel) = dy[pixel][co]
-    const T* a = reinterpret_cast<const T*>(s.A.ptr);
-    return to_f32<T>(a[k * s.lda + m]);
+  } else {  // WGRAD: A(m = co, k = output pixel) = dy[pixel][co], through the operand view (strided for the upsample phases)
+    const int hw = s.out_h * s.out_w;
+    const int b = static_cast<int>(k / hw);
+    const int r = static_cast<int>(k - static_cast<long long>(b) * hw);
+    const int y = r / s.out_w, x = r - y * s.out_w;
+    return spatial_fetch<T>(s.A, static_cast<int>(m), x, 0, y, b);
   }
 }
 

@@ -106,10 +106,12 @@ class GraphedTrainStep:
             else:
                 st["keep"].copy_(torch.empty(st["keep"].shape, dtype=torch.float32, device=st["keep"].device)
                                  .bernoulli_(1.0 - p).to(torch.uint8))
-        st["keep_scale_host"][0] = 1.0 / (1.0 - p) if 0 < p < 1.0 else 1.0
-        st["keep_scale"].copy_(st["keep_scale_host"], non_blocking=True)
-        st["prior_rows_host"].copy_(m.loss._prior_rows_host(batch["class_name"]))
-        st["prior_rows"].copy_(st["prior_rows_host"], non_blocking=True)
+        # fresh pinned sources every step: the copies run asynchronously (the GPU is up to a step behind the host), so a
+        # reused pinned buffer would be overwritten before its copy executes; the caching host allocator recycles them
+        ks = torch.empty(1, pin_memory=True)
+        ks[0] = 1.0 / (1.0 - p) if 0 < p < 1.0 else 1.0
+        st["keep_scale"].copy_(ks, non_blocking=True)
+        st["prior_rows"].copy_(m.loss._prior_rows_host(batch["class_name"]).pin_memory(), non_blocking=True)
         st["labels"] = list(batch["class_name"])
 
     def _static_batch(self, st):
@@ -140,9 +142,7 @@ class GraphedTrainStep:
               "eps": torch.empty(lat, **f32), "noise": torch.empty(lat, **f32) if m.add_noise_to_z_obj else None,
               "eps_bbox": torch.empty(B, 8, **f32),
               "keep": torch.empty(lat, dtype=torch.uint8, device=dev) if p > 0 else None,
-              "keep_scale": torch.ones(1, **f32), "keep_scale_host": torch.ones(1, pin_memory=True),
-              "prior_rows": torch.empty(B, dtype=torch.int32, device=dev),
-              "prior_rows_host": torch.empty(B, dtype=torch.int32, pin_memory=True)}
+              "keep_scale": torch.ones(1, **f32), "prior_rows": torch.empty(B, dtype=torch.int32, device=dev)}
         # eager steps on a side stream first: pack weights, size workspaces, build the optimizer's tables, set kernel
         # attributes. They must leave no trace: parameters, buffers, optimizer state and the RNG streams are snapshotted and
         # restored, so that one call of this object == one optimizer step, like TrainStep.

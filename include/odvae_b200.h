@@ -355,6 +355,27 @@ int odvae_colsum(const void* m, int64_t rows, int cols, int ld, int dtype, float
                  void* workspace, size_t ws_bytes, void* stream);
 
 /* ---------------------------------------------------------------------------------------------
+ * Upsample: F.interpolate(scale 2, nearest) + Conv2d(k=3, s=1, p=1) (LD model.py:53-57) WITHOUT the upsampled tensor: output
+ * pixel (2i+py, 2j+px) only ever reads 2x2 low-resolution pixels, so the layer is four parity-phase 2x2 convolutions with
+ * pre-summed weights over x: NHWC [B,H,W,CinP] -> y: NHWC [B,2H,2W,CoutP] (16/36 of the FLOPs of the literal form).
+ *   odvae_pack_upconv_weight: fp32 OIHW [Cout,Cin,3,3] -> which = 0: [4 phases][CoutP][4 taps][CinP] (forward);
+ *                             which = 1: [CinP][16 (phase, tap)][CoutP] (dgrad: ONE launch over the stride-2 phase view of dy)
+ *   odvae_upconv_wgrad: four 4-tap weight-gradient GEMMs (dy sub-sampled per phase) folded back onto the 3x3 filter;
+ *                       deterministic; out_scale / accumulate as in odvae_conv2d_wgrad.
+ * ------------------------------------------------------------------------------------------- */
+int odvae_upconv_tc_supported(int B, int H, int W, int CinP, int CoutP);
+int odvae_pack_upconv_weight(const float* w_oihw, void* packed, int Cout, int Cin, int CoutP, int CinP, int which,
+                             int act_dtype, void* stream);
+int odvae_upconv_fwd(const void* x, const void* w_phase_packed, const float* bias, void* y, int B, int H, int W, int CinP,
+                     int CoutP, int act_dtype, int impl, void* stream);
+int odvae_upconv_dgrad(const void* dy, const void* w_dgrad_packed, void* dx, int B, int H, int W, int CinP, int CoutP,
+                       int act_dtype, int impl, void* stream);
+size_t odvae_upconv_wgrad_workspace_bytes(int B, int H, int W, int CinP, int CoutP, int Cin, int Cout, int impl);
+int odvae_upconv_wgrad(const void* x, const void* dy, float* dw_oihw, float* db, int B, int H, int W, int CinP, int CoutP,
+                       int Cin, int Cout, int act_dtype, int impl, int accumulate, float out_scale, void* workspace,
+                       size_t ws_bytes, void* stream);
+
+/* ---------------------------------------------------------------------------------------------
  * PatchGAN discriminator. Call sites: src/modules/losses/contperceptual.py:280-301 (generator side:
  * logits_fake = discriminator(reconstructions)) and :352-375 (discriminator side) ->
  * taming.modules.discriminator.model.NLayerDiscriminator (un-vendored; public definition in SURVEY appendix B:

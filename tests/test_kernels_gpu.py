@@ -245,3 +245,45 @@ def test_nchw_to_nhwc_pads_and_rescales(C, Cpad, code):
     assert float((yv[..., :C].float() - ref.float()).abs().max()) <= {"bf16": 2 ** -7, "f16": 2 ** -10, "f32": 2 ** -22}[code]
     if Cpad > C:
         assert float(yv[..., C:].float().abs().max()) == 0.0
+
+
+@pytest.mark.parametrize("dtype,tol", [(torch.float32, 2e-5), (torch.float16, 3e-3), (torch.bfloat16, 2e-2)])
+@pytest.mark.parametrize("B,H,C,Cout", [(2, 16, 64, 64), (3, 32, 128, 128), (2, 64, 256, 128), (2, 128, 128, 128)])
+def test_upsample_conv_phase_decomposition_against_torch(dtype, tol, B, H, C, Cout):
+    """Upsample.forward (LD model.py:53-57): F.interpolate(2x, nearest) + Conv2d(3x3, p=1) -- run as four parity-phase 2x2
+    convolutions over the low-resolution input: forward, input gradient (one 16-tap launch), weight and bias gradients
+    (four 4-tap GEMMs folded back onto the 3x3 filter) against torch fp32 (TF32 off)."""
+    import torch.nn.functional as F
+    from odvae_b200 import modules as M
+    torch.backends.cudnn.allow_tf32 = False
+    torch.backends.cuda.matmul.allow_tf32 = False
+    g = torch.Generator().manual_seed(B * 1000 + H)
+    up = M.Upsample(C).cuda()
+    if Cout != C:
+        up = M.Upsample(C)
+        up.conv = M.Conv2d(C, Cout, 3, up.conv.spec.geom)
+        up = up.cuda()
+    ops.assign_format(up, dtype)
+    fmt = ops.format_for(dtype)
+    xs = torch.randn(B, C, H, H, generator=g).cuda()
+    x = ops.nchw_to_nhwc_raw(xs, C, fmt.fwd, label=fmt.label(fmt.fwd)).requires_grad_(True)
+    y = up(x)
+    assert y.shape == (B, 2 * H, 2 * H, Cout)
+    wy = torch.randn(B, Cout, 2 * H, 2 * H, generator=g).cuda()
+    dy = ops.nchw_to_nhwc_raw(wy, Cout, fmt.grad, label=fmt.label(fmt.grad))
+    y.backward(dy)
+    torch.cuda.synchronize()
+    # reference on the values the kernels actually see (inputs / weights rounded to the 16-bit format)
+    rd = {torch.float32: torch.float32, torch.float16: torch.float16, torch.bfloat16: torch.bfloat16}[dtype]
+    xr = xs.to(rd).float().requires_grad_(True)
+    wr = up.conv.weight.detach().to(rd).float().requires_grad_(True)
+    br = up.conv.bias.detach().clone().requires_grad_(True)
+    yr = F.conv2d(F.interpolate(xr, scale_factor=2.0, mode="nearest"), wr, br, padding=1)
+    yr.backward(wy.to(rd).float())
+    y_n = ops.nhwc_to_nchw_raw(y.detach(), Cout, fmt.fwd)
+    dx_n = ops.nhwc_to_nchw_raw(x.grad, C, fmt.grad)
+    rel = lambda a, b: float((a.float() - b.float()).norm() / b.float().norm())
+    assert rel(y_n, yr) < tol
+    assert rel(dx_n, xr.grad) < tol
+    assert rel(up.conv.weight.grad, wr.grad) < tol
+    assert rel(up.conv.bias.grad, br.grad) < tol

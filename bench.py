@@ -57,7 +57,10 @@ def parse():
     ap.add_argument("--step-graph", default="auto", choices=["auto", "on", "off"],
                     help="train workload: replay the whole step (fwd + loss + bwd + clip + Adam + weight re-pack, ~1000 "
                          "launches) as ONE CUDA graph (odvae_b200/graphs.py GraphedTrainStep; bit-identical to the eager launch "
-                         "sequence). auto = on for 1 GPU with --objective configs1, off otherwise")
+                         "sequence; host enqueue 3 ms instead of ~125 ms per step). auto = off: measured on one box (profiles/"
+                         "README.md r02 A/B) the eager two-stream launch sequence overlaps the weight-gradient GEMMs with the "
+                         "GroupNorm backward better than the replayed graph does (139.4-140.3 vs 142.6 ms); the graph step is "
+                         "reported next to the bench line as extra.cuda_graph_step")
     ap.add_argument("--extras", type=int, default=1,
                     help="N = 1 only: also measure the full objective, the encode sweep, the 512x512 step and the eager "
                          "cuDNN/cuBLAS baseline, reported under `extra` (0 = skip)")
@@ -285,7 +288,7 @@ class EngineProfiler:
     """Wraps ops.call for ONE extra (untimed) step: brackets each conv/GEMM C-ABI call with CUDA events on the
     launching stream and adds up the algorithmic FLOPs (2*M*N*K of the real, unpadded problem)."""
     NAMES = {"conv2d_fwd", "conv2d_fwd_gnstats", "conv2d_dgrad", "conv2d_wgrad", "gemm_bf16", "gemm_16", "attn_scores_softmax",
-             "attn_dsoftmax"}
+             "attn_dsoftmax", "upconv_fwd", "upconv_dgrad", "upconv_wgrad"}
     # memory-bound GroupNorm(+SiLU) calls, judged against the HBM roofline (SURVEY 8d): algorithmic bytes at 2 B per
     # element are 2*E forward (stats + apply together: read x once, write y once) and 3*E backward (x, dy -> dx)
     GN_NAMES = {"groupnorm_stats", "groupnorm_apply", "groupnorm_bwd"}
@@ -310,6 +313,13 @@ class EngineProfiler:
             return 2.0 * a[3] * a[4] * a[4] * a[5]
         if name == "attn_dsoftmax":
             return 2.0 * a[5] * a[6] * a[6] * a[7]
+        if name.startswith("upconv_"):
+            # EXECUTED flops of the parity-phase form: 16 taps over the low-resolution grid (the literal upsample + 3x3 conv the
+            # SURVEY's algorithmic figure counts is 36); args: fwd (x, w, bias, y, B, H, W, CinP, CoutP, ..), dgrad (dy, w, dx,
+            # B, H, W, ..), wgrad (x, dy, dw, db, B, H, W, CinP, CoutP, ..)
+            o = {"upconv_fwd": 4, "upconv_dgrad": 3, "upconv_wgrad": 4}[name]
+            B, H, W, CinP, CoutP = a[o], a[o + 1], a[o + 2], a[o + 3], a[o + 4]
+            return 2.0 * B * H * W * CoutP * CinP * 16
         if name == "conv2d_fwd":
             B, H, W, CinP, CoutP, Cout, geom = a[5], a[6], a[7], a[8], a[9], a[10], a[11]
             cin, cout = self._real(CinP), Cout
@@ -334,6 +344,10 @@ class EngineProfiler:
             return "attn qk^T+softmax (2 passes) B%d N%d C%d" % (a[3], a[4], a[5])
         if name == "attn_dsoftmax":
             return "attn dP+dsoftmax B%d N%d C%d" % (a[5], a[6], a[7])
+        if name.startswith("upconv_"):
+            o = {"upconv_fwd": 4, "upconv_dgrad": 3, "upconv_wgrad": 4}[name]
+            return "%s (2x2 phases) B%d %dx%d->%dx%d %d->%d" % (name, a[o], a[o + 1], a[o + 2], 2 * a[o + 1], 2 * a[o + 2],
+                                                               a[o + 3], a[o + 4])
         if name == "conv2d_fwd":
             return "fwd B%d %dx%d %d->%d g%d" % (a[5], a[6], a[7], a[8], a[9], a[11])
         if name == "conv2d_fwd_gnstats":
@@ -530,6 +544,32 @@ def replicas_identical(model, world):
     return float(d)
 
 
+def time_graph_step(args, dev, B, R, steps):
+    """The configs[1] step replayed as ONE CUDA graph (GraphedTrainStep): same launch sequence, host enqueue ~3 ms."""
+    from odvae_b200 import synth
+    from odvae_b200.graphs import GraphedTrainStep
+    from odvae_b200.trainer import TrainStep
+    model = build_model(args, dev, 1, 0.0, 0.0)
+    fn = GraphedTrainStep(TrainStep(model, lr=model.learning_rate, max_grad_norm=1.0))
+    res = {k: (v.to(dev) if torch.is_tensor(v) else v) for k, v in synth.synthetic_batch(B, R, seed=23).items()}
+    for i in range(3):
+        fn(res, i)
+    torch.cuda.synchronize()
+    e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    t0 = time.perf_counter()
+    e0.record()
+    for i in range(steps):
+        loss = fn(res, i)
+    e1.record()
+    host_ms = (time.perf_counter() - t0) * 1e3 / steps
+    torch.cuda.synchronize()
+    ms = e0.elapsed_time(e1) / steps
+    out = {"images_per_sec": B / (ms * 1e-3), "ms_per_step": ms, "steps": steps, "host_enqueue_ms_per_step": host_ms,
+           "launches_per_replay": fn.launches_per_replay, "last_loss": float(loss)}
+    del fn, model
+    return out
+
+
 def time_full_objective(args, dev, B, R, steps, warmup):
     """One whole batch of the reference loop with the yaml's own objective (perceptual_weight 1, disc_factor 1): the
     optimizer_idx 0 step (LPIPS, PatchGAN generator term, adaptive d_weight, Adam) + the optimizer_idx 1 step (two
@@ -595,7 +635,7 @@ def run_ours(args):
         step_fn = TrainStep(model, lr=model.learning_rate, max_grad_norm=1.0)
     eager_fn = step_fn
     use_graph = (not full) and args.workload == "train" and \
-        (args.step_graph == "on" or (args.step_graph == "auto" and world == 1)) and not args.ncu_step
+        args.step_graph == "on" and not args.ncu_step
     if use_graph:
         from odvae_b200.graphs import GraphedTrainStep
         step_fn = GraphedTrainStep(eager_fn)
@@ -671,7 +711,10 @@ def run_ours(args):
     if rank == 0 and not args.no_roofline:
         prof = EngineProfiler()
         prof.install()
+        from odvae_b200 import ops as _ops
+        overlap, _ops.OVERLAP_WGRAD[0] = _ops.OVERLAP_WGRAD[0], False  # per-call times: every kernel alone on the GPU
         eager_fn(clone(resident), 0)  # the SAME launch sequence eagerly, each conv / GEMM / GroupNorm call between CUDA events
+        _ops.OVERLAP_WGRAD[0] = overlap
         prof.remove()
         eng_ms, counted, ncalls, by = prof.summary()
         if args.shapes:
@@ -729,6 +772,12 @@ def run_ours(args):
         torch.cuda.empty_cache()
         if args.extras and not full and R == RES:
             extra = {}
+            try:
+                extra["cuda_graph_step"] = time_graph_step(args, dev, B, R, steps=args.steps)
+            except Exception as e:
+                extra["cuda_graph_step"] = {"error": repr(e)[:300]}
+            gc.collect()
+            torch.cuda.empty_cache()
             try:
                 extra["full_objective"] = time_full_objective(args, dev, B, R, steps=3, warmup=2)
             except Exception as e:  # an extra must never take the bench line down

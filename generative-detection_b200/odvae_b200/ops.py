@@ -376,6 +376,49 @@ class ConvSpec:
         return self.cache.get(("b", n), (b,), lambda old: pad_vector(b.detach(), n, old))
 
 
+# ------------------------------------------------------------------------------------------------
+# Backward overlap: the weight-gradient GEMMs of a block depend only on tensors that exist before the block's GroupNorm
+# backward starts, and the two kinds of kernel bind on different resources (wgrad: tensor pipe / shared-memory bandwidth, ~1.8
+# TB/s of DRAM; GroupNorm backward: HBM at 4.4-4.5 TB/s). The wgrad of a conv is therefore enqueued on a side stream right
+# after the dgrad that precedes the GroupNorm backward, and co-runs with it (its persistent CTAs leave ~20 KB of shared
+# memory and half the register file per SM: room for the GroupNorm CTAs). The side stream is joined before the block's
+# backward returns, so nothing outside the block sees it (gradient-arena buckets, autograd, CUDA-graph capture).
+# ------------------------------------------------------------------------------------------------
+OVERLAP_WGRAD = [os.environ.get("ODVAE_OVERLAP_WGRAD", "1") != "0"]
+_SIDE = {}
+
+
+class side_stream:
+    """`with side_stream(device):` -- work inside is enqueued on the device's side stream, ordered after everything enqueued so
+    far on the current stream. join_side(device) makes the current stream wait for it. No-ops when overlap is disabled."""
+
+    def __init__(self, device):
+        self.device, self.ctx = device, None
+
+    def __enter__(self):
+        if not OVERLAP_WGRAD[0]:
+            return self
+        side = _SIDE.get(self.device.index)
+        if side is None:
+            side = torch.cuda.Stream(self.device)
+            _SIDE[self.device.index] = side
+        side.wait_stream(torch.cuda.current_stream(self.device))
+        self.ctx = torch.cuda.stream(side)
+        self.ctx.__enter__()
+        return self
+
+    def __exit__(self, *exc):
+        if self.ctx is not None:
+            self.ctx.__exit__(*exc)
+        return False
+
+
+def join_side(device):
+    side = _SIDE.get(device.index)
+    if OVERLAP_WGRAD[0] and side is not None:
+        torch.cuda.current_stream(device).wait_stream(side)
+
+
 def grad_dst(p):
     """Destination view for a parameter gradient when the flat gradient arena is enabled."""
     return getattr(p, "_odvae_grad_dst", None)
@@ -696,15 +739,17 @@ class ResBlock(torch.autograd.Function):
             dwn, dnb = conv_wgrad_raw(grad_operand(x, fmt), dout, blk.spec_nin, wn, nb)
         else:
             dsc = dout
+        dev = x.device
         da2 = conv_dgrad_raw(dout, blk.spec2, w2, hw)
-        dw2, dc2b = conv_wgrad_raw(a2, dout, blk.spec2, w2, c2b)
+        with side_stream(dev):  # co-runs with the GroupNorm backward below
+            dw2, dc2b = conv_wgrad_raw(a2, dout, blk.spec2, w2, c2b)
         ps = 1.0 / gs_of(blk)
         dh1, dg2, db2 = gn_bwd_raw(h1, s2, g2, b2, da2, True, x_code=fmt.fwd, g_code=fmt.grad, pscale=ps)
-        del da2
         da1 = conv_dgrad_raw(dh1, blk.spec1, w1, hw)
-        dw1, dc1b = conv_wgrad_raw(a1, dh1, blk.spec1, w1, c1b)
-        del dh1
+        with side_stream(dev):
+            dw1, dc1b = conv_wgrad_raw(a1, dh1, blk.spec1, w1, c1b)
         dx, dg1, db1 = gn_bwd_raw(x, s1, g1, b1, da1, True, dx_add=dsc, x_code=fmt.fwd, g_code=fmt.grad, pscale=ps)
+        join_side(dev)  # every tensor the side stream read (a1, a2, dout, dh1) is still referenced here
         return dx, dg1, db1, dw1, dc1b, dg2, db2, dw2, dc2b, dwn, dnb, None
 
 
@@ -795,12 +840,14 @@ class AttnBlock(torch.autograd.Function):
         dwqkv, dbqkv, direct = blk.qkv_grad_buffers(wq, bq)
         impl = conv_impl(ac, B, H, W, C, 3 * C, CONV_1x1)
         nbytes = call("conv2d_wgrad_workspace_bytes", B, H, W, C, 3 * C, CONV_1x1, impl)
-        ws = workspace(nbytes, x.device, "wgrad")
         ps = 1.0 / gs_of(blk)
-        call("conv2d_wgrad", hn, dqkv, dwqkv, dbqkv, B, H, W, C, 3 * C, C, 3 * C, CONV_1x1, ac, impl, 0, ps, ws,
-             ws.numel())
+        with side_stream(x.device):  # co-runs with the GroupNorm backward below
+            ws = workspace(nbytes, x.device, "wgrad")
+            call("conv2d_wgrad", hn, dqkv, dwqkv, dbqkv, B, H, W, C, 3 * C, C, 3 * C, CONV_1x1, ac, impl, 0, ps, ws,
+                 ws.numel())
         dx, dg, db = gn_bwd_raw(x, stats, gamma, beta, dhn, False, dx_add=dout, x_code=fmt.fwd, g_code=fmt.grad,
                                 pscale=ps)
+        join_side(x.device)
         if grad_dst(wq) is not None:  # arena mode: device-to-device copies of the three row blocks
             for i, (w_, b_) in enumerate(((wq, bq), (wk, bk), (wv, bv))):
                 grad_dst(w_).copy_(dwqkv[i * C:(i + 1) * C].view(C, C, 1, 1))

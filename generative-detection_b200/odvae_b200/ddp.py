@@ -65,6 +65,10 @@ class GradArena:
         if self.world > 1:
             if self.comm_stream is not None:
                 self.comm_stream.wait_stream(torch.cuda.current_stream())
+                from . import ops
+                side = ops._SIDE.get(self.flat.device.index)
+                if side is not None:  # weight gradients still running on the overlap stream (ops.side_release)
+                    self.comm_stream.wait_stream(side)
                 with torch.cuda.stream(self.comm_stream):
                     dist.all_reduce(self.flat[s:e], op=dist.ReduceOp.SUM, group=self.pg)
             else:

@@ -419,6 +419,38 @@ def join_side(device):
         torch.cuda.current_stream(device).wait_stream(side)
 
 
+# Free-running variant (gradient-arena mode, i.e. trainer.TrainStep): the block does NOT wait for its weight-gradient GEMMs;
+# the side stream is joined once, by a callback autograd runs at the end of the backward pass (and by the gradient arena
+# before it all-reduces a bucket). The wgrad queue then always has work to co-run with whatever HBM-bound kernel the main
+# chain is in. Tensors the side stream reads are handed to it with record_stream (they are freed by autograd as soon as the
+# block's backward returns); the results live in the arena. Outside the arena the gradients are returned to autograd, which
+# may touch them at once, so there the per-block join stays.
+OVERLAP_FREE = [os.environ.get("ODVAE_OVERLAP_FREE", "1") != "0"]
+_JOIN_QUEUED = {}
+
+
+def side_release(device, direct, *tensors):
+    """End of a block's backward: free-running (-> True) when every parameter gradient of the block went straight into the
+    arena, else join now (-> False)."""
+    side = _SIDE.get(device.index)
+    if not OVERLAP_WGRAD[0] or side is None:
+        return False
+    if not (OVERLAP_FREE[0] and direct and _PROBE[0] == 0):
+        join_side(device)
+        return False
+    for t in tensors:
+        if t is not None:
+            t.record_stream(side)
+    if not _JOIN_QUEUED.get(device.index):
+        _JOIN_QUEUED[device.index] = True
+
+        def _final_join():
+            _JOIN_QUEUED[device.index] = False
+            join_side(device)
+        torch.autograd.Variable._execution_engine.queue_callback(_final_join)
+    return True
+
+
 def grad_dst(p):
     """Destination view for a parameter gradient when the flat gradient arena is enabled."""
     return getattr(p, "_odvae_grad_dst", None)
@@ -749,7 +781,9 @@ class ResBlock(torch.autograd.Function):
         with side_stream(dev):
             dw1, dc1b = conv_wgrad_raw(a1, dh1, blk.spec1, w1, c1b)
         dx, dg1, db1 = gn_bwd_raw(x, s1, g1, b1, da1, True, dx_add=dsc, x_code=fmt.fwd, g_code=fmt.grad, pscale=ps)
-        join_side(dev)  # every tensor the side stream read (a1, a2, dout, dh1) is still referenced here
+        # the side stream read a1, a2, dout, dh1: wait for it here, or (arena mode) let it run on and join at the end of backward
+        side_release(dev, dw1 is None and dw2 is None and (c1b is None or dc1b is None) and (c2b is None or dc2b is None),
+                     a1, a2, dout, dh1)
         return dx, dg1, db1, dw1, dc1b, dg2, db2, dw2, dc2b, dwn, dnb, None
 
 
@@ -847,7 +881,7 @@ class AttnBlock(torch.autograd.Function):
                  ws.numel())
         dx, dg, db = gn_bwd_raw(x, stats, gamma, beta, dhn, False, dx_add=dout, x_code=fmt.fwd, g_code=fmt.grad,
                                 pscale=ps)
-        join_side(x.device)
+        join_side(x.device)  # the q|k|v gradient is copied out of dwqkv right below
         if grad_dst(wq) is not None:  # arena mode: device-to-device copies of the three row blocks
             for i, (w_, b_) in enumerate(((wq, bq), (wk, bk), (wv, bv))):
                 grad_dst(w_).copy_(dwqkv[i * C:(i + 1) * C].view(C, C, 1, 1))

@@ -74,5 +74,7 @@ def test_two_rank_step_equals_the_one_rank_step_on_the_concatenated_batch():
     mp.spawn(_worker, args=(1, [full], [nz], one, 0), nprocs=1, join=True)
     a, b = torch.load(two), torch.load(one)
     assert H.rel_l2(a["grads"], b["grads"]) < 1e-5       # mean of the two ranks' gradients == gradient of the 2x batch
-    for k in a["params"]:                                   # ... and the same clip + Adam update on every parameter
-        assert H.rel_max(a["params"][k], b["params"][k]) < 1e-5, k
+    # ... and the same clip + Adam update on every parameter. Adam's first step is lr * g / (|g| + eps): an element whose
+    # gradient is rounding noise can land anywhere in [-lr, lr], so the bound is lr-sized (measured 4e-5), not fp32-sized
+    for k in a["params"]:
+        assert H.rel_max(a["params"][k], b["params"][k]) < 2e-4, k

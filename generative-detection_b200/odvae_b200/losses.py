@@ -115,6 +115,9 @@ class PoseLoss(nn.Module):
         # still runs D on real and fake and returns 0 * hinge. True (default) skips those two forward passes and returns
         # a differentiable zero tied to the discriminator (logged logits are then 0); False reproduces the logs too.
         self.skip_inactive_gan = True
+        # generator step with the GAN on: run LPIPS / masked-L1 / discriminator backward once instead of twice (see
+        # _generator_terms_single_backward); False = the reference's literal two-autograd.grad + backward sequence
+        self.single_backward_gan = True
         self.disc_factor, self.discriminator_weight, self.disc_conditional = disc_factor, disc_weight, disc_conditional
         self.pose_conditioned_generation_steps = pose_conditioned_generation_steps
         self.encoder_pretrain_steps = encoder_pretrain_steps
@@ -201,21 +204,28 @@ class PoseLoss(nn.Module):
         train_rec = global_step > self.encoder_pretrain_steps and self.encoder_pretrain_steps != -1
         w7 = (1.0 if train_rec else 0.0, self.kl_weight_obj if train_rec else 0.0, self.pose_weight,
               self.class_weight, self.bbox_weight, self.fill_factor_weight, self.kl_weight_bbox)
-        out = LossHeads.apply(dec_pose, bbox_posterior.mean, bbox_posterior.logvar, l1_sums, posterior_obj.kl(),
-                              self.logvar, gts, (B, ncls, npix, tuple(float(v) for v in w7)))
-        loss = out[O_TOTAL]
-        # ---- generator side of the GAN (LOSS.py:280-304, 313-317)
-        logits_fake = self.discriminator(dec_obj, mask=mask2d, param_grads=False) * mask_bg.view(B, 1, 1, 1)
-        g_loss = -torch.mean(logits_fake)
-        d_weight = torch.zeros((), device=dev)
-        if self.disc_factor > 0.0 and global_step > self.encoder_pretrain_steps:
-            try:
-                d_weight = self.calculate_adaptive_weight(out[O_NLL], g_loss, last_layer=last_layer)
-            except RuntimeError:
-                assert not self.training
-                d_weight = torch.zeros((), device=dev)
-        if train_rec and disc_factor != 0:
-            loss = loss + d_weight * disc_factor * g_loss
+        heads_cfg = (B, ncls, npix, tuple(float(v) for v in w7))
+        gan_on = self.disc_factor > 0.0 and global_step > self.encoder_pretrain_steps and train_rec and disc_factor != 0
+        if gan_on and self.single_backward_gan and l1_sums is not None and dec_obj.requires_grad and last_layer is not None:
+            loss, out, g_loss, d_weight = self._generator_terms_single_backward(
+                dec_obj, dec_pose, bbox_posterior, l1_sums, posterior_obj, gts, heads_cfg, mask2d, mask_bg, disc_factor,
+                w7[0], last_layer)
+        else:
+            out = LossHeads.apply(dec_pose, bbox_posterior.mean, bbox_posterior.logvar, l1_sums, posterior_obj.kl(),
+                                  self.logvar, gts, heads_cfg)
+            loss = out[O_TOTAL]
+            # ---- generator side of the GAN, literally as LOSS.py:280-304, 313-317
+            logits_fake = self.discriminator(dec_obj, mask=mask2d, param_grads=False) * mask_bg.view(B, 1, 1, 1)
+            g_loss = -torch.mean(logits_fake)
+            d_weight = torch.zeros((), device=dev)
+            if self.disc_factor > 0.0 and global_step > self.encoder_pretrain_steps:
+                try:
+                    d_weight = self.calculate_adaptive_weight(out[O_NLL], g_loss, last_layer=last_layer)
+                except RuntimeError:
+                    assert not self.training
+                    d_weight = torch.zeros((), device=dev)
+            if train_rec and disc_factor != 0:
+                loss = loss + d_weight * disc_factor * g_loss
         d = out.detach()
         zero = torch.zeros((), device=dev)
         k = lambda name: "{}/{}".format(split, name)
@@ -231,6 +241,39 @@ class PoseLoss(nn.Module):
                k("weighted_kl_loss_obj"): self.kl_weight_obj * d[O_KL], k("fill_factor_loss"): d[O_FILL],
                k("weighted_fill_factor_loss"): self.fill_factor_weight * d[O_FILL]}
         return loss, log
+
+    def _generator_terms_single_backward(self, dec_obj, dec_pose, bbox_posterior, l1_sums, posterior_obj, gts, heads_cfg,
+                                         mask2d, mask_bg, disc_factor, w_nll, last_layer):
+        """The generator step with the GAN on, every expensive backward run ONCE. The reference (LOSS.py:280-304 + LD
+        contperceptual.py:32-43) back-propagates nll_loss and g_loss to `last_layer` for the adaptive weight and then the
+        total loss again: LPIPS + masked-L1 backward and the discriminator's input-gradient pass each run twice. Everything
+        between dec_obj and the two scalars is linear in the upstream gradient, so here
+            G1 = d nll / d dec_obj   (loss heads -> masked L1 + LPIPS backward, once)
+            G2 = d g_loss / d dec_obj (discriminator backward, once)
+        give both  ||d nll / d W_last||, ||d g / d W_last||  (two weight-gradient passes of conv_out with G1 / G2 as dy) and the
+        step's own gradient at dec_obj,  w_nll * G1 + d_weight * disc_factor * G2, injected through a surrogate term
+        sum(dec_obj * G) - its detached value. Same numbers as the literal form up to summation order
+        (tests/test_patchgan_gpu.py runs both against the goldens)."""
+        B = dec_obj.shape[0]
+        l1_leaf = l1_sums.detach().requires_grad_(True)
+        out = LossHeads.apply(dec_pose, bbox_posterior.mean, bbox_posterior.logvar, l1_leaf, posterior_obj.kl(), self.logvar,
+                              gts, heads_cfg)
+        dec_leaf = dec_obj.detach().requires_grad_(True)
+        logits_fake = self.discriminator(dec_leaf, mask=mask2d, param_grads=False) * mask_bg.view(B, 1, 1, 1)
+        g_loss = -torch.mean(logits_fake)
+        with ops.probe_gradients():
+            d_l1 = torch.autograd.grad(out[O_NLL], l1_leaf, retain_graph=True)[0]
+            G1 = torch.autograd.grad(l1_sums, dec_obj, grad_outputs=d_l1, retain_graph=True)[0]
+            G2 = torch.autograd.grad(g_loss, dec_leaf)[0]
+            nll_grads = torch.autograd.grad(dec_obj, last_layer, grad_outputs=G1, retain_graph=True)[0]
+            g_grads = torch.autograd.grad(dec_obj, last_layer, grad_outputs=G2, retain_graph=True)[0]
+        d_weight = torch.clamp(torch.norm(nll_grads) / (torch.norm(g_grads) + 1e-4), 0.0, 1e4).detach()
+        d_weight = d_weight * self.discriminator_weight
+        c = d_weight * disc_factor
+        G = (w_nll * G1 + c * G2).detach()
+        surrogate = (dec_obj * G).sum()
+        loss = out[O_TOTAL] + c * g_loss.detach() + (surrogate - surrogate.detach())
+        return loss, out, g_loss.detach(), d_weight
 
     def calculate_adaptive_weight(self, nll_loss, g_loss, last_layer=None):
         """LD contperceptual.py:32-43: ||d nll / d W_last|| / (||d g / d W_last|| + 1e-4), clamped, detached, times disc_weight.

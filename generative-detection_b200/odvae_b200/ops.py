@@ -425,7 +425,7 @@ def join_side(device):
 # chain is in. Tensors the side stream reads are handed to it with record_stream (they are freed by autograd as soon as the
 # block's backward returns); the results live in the arena. Outside the arena the gradients are returned to autograd, which
 # may touch them at once, so there the per-block join stays.
-OVERLAP_FREE = [os.environ.get("ODVAE_OVERLAP_FREE", "1") != "0"]
+OVERLAP_FREE = [os.environ.get("ODVAE_OVERLAP_FREE", "0") != "0"]  # measured: no gain over the per-block join (135.9 ms both)
 _JOIN_QUEUED = {}
 
 
@@ -709,7 +709,8 @@ class Conv(torch.autograd.Function):
         else:
             dy = _c(dy)
         dx = None
-        if ctx.need_dx and ctx.needs_input_grad[0]:
+        # probe mode (torch.autograd.grad of the adaptive GAN weight): only conv_out's weight gradient is wanted
+        if ctx.need_dx and ctx.needs_input_grad[0] and not (_PROBE[0] > 0 and ctx.out_nchw):
             dx = conv_dgrad_raw(dy, spec, w, x.shape[1:3])
         dw, db = conv_wgrad_raw(grad_operand(x, fmt), dy, spec, w, b)
         return dx, dw, db, None, None, None

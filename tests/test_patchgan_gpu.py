@@ -95,7 +95,7 @@ def test_discriminator_is_bit_stable():
 # ---------------------------------------------------------------------------------------------------------------------
 # whole path with the GAN on, against the goldens (reference loss code + restated discriminator)
 # ---------------------------------------------------------------------------------------------------------------------
-def _run_gan(name, dtype):
+def _run_gan(name, dtype, single_backward=True):
     from odvae_b200.autoencoder import PoseAutoencoder
     g = H.load_golden(name)
     params, batch, noise, step = H.case_inputs(g)
@@ -105,6 +105,7 @@ def _run_gan(name, dtype):
     model.global_step = step
     model.inject_noise = noise
     model.loss.skip_inactive_gan = False
+    model.loss.single_backward_gan = single_backward
     loss = model.training_step(H.clone_batch(batch), 0, 0)
     loss.backward()
     log0 = dict(model.logged)
@@ -119,10 +120,14 @@ def _run_gan(name, dtype):
 # fp32: the LeakyReLU / L1 kink noise documented in tests/test_oracle_cpu.py bounds the gradients (the CPU fp32 oracle
 # itself differs from the fp32 reference by 2.9e-3 on small_s80000_gan_b3); 16-bit: the timed mode's stated tolerance
 @pytest.mark.parametrize("name", H.GAN_CASES)
-@pytest.mark.parametrize("mode", ["fp32", "fp16"])
+@pytest.mark.parametrize("mode", ["fp32", "fp16", "fp32-literal"])
 def test_gan_steps_match_reference(name, mode):
+    """mode "...-literal": PoseLoss.single_backward_gan = False, the reference's own two autograd.grad calls + full backward;
+    the default runs every expensive backward once (PoseLoss._generator_terms_single_backward)."""
+    single = not mode.endswith("-literal")
+    mode = mode.split("-")[0]
     dtype = {"fp32": torch.float32, "fp16": torch.float16}[mode]
-    g, model, loss, log0, grads, d_loss, log1 = _run_gan(name, dtype)
+    g, model, loss, log0, grads, d_loss, log1 = _run_gan(name, dtype, single)
     # 16-bit gradient bound: kink noise (L1 sign + LeakyReLU slope flips) times the adaptive weight's amplification; the
     # small config's 6x6-logit discriminator has so few units that single flips show (measured 7e-2; full config 3e-2)
     tol, gtol, dtol = (2e-3, 1e-2, 2e-3) if mode == "fp32" else (1e-2, 5e-2 if name.startswith("full") else 1e-1, 2e-2)

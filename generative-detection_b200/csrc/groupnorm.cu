@@ -18,12 +18,31 @@ template <> struct VecN<bf16> { static constexpr int V = 8; };
 template <> struct VecN<f16> { static constexpr int V = 8; };
 
 static constexpr int GN_THREADS = 256;
+// tuning knobs: minimum resident CTAs per SM (caps registers at 85) and loads in flight. Measured alone on B200, 128 ch x
+// 256^2 x 64, fp16 (tools/gn_bench.py + tools/gpu_gn_variants.sh, round 2): apply 0.576 -> 0.354 ms (6.06 TB/s = 92 % of the HBM
+// copy peak) with 3 CTAs/SM; backward 1.283 -> 1.056 ms with 3 CTAs/SM on both passes and 2 loads in flight per tensor in
+// the reduce pass; 4 CTAs/SM spills and is slower everywhere.
+#ifndef GN_APPLY_MINB
+#define GN_APPLY_MINB 3
+#endif
+#ifndef GN_BWD_MINB
+#define GN_BWD_MINB 3
+#endif
+#ifndef GN_RED_MINB
+#define GN_RED_MINB 3
+#endif
+#ifndef GN_BWD_U
+#define GN_BWD_U 2
+#endif
+#ifndef GN_RED_U
+#define GN_RED_U 2
+#endif
 
 // MODE 0: per-(b,c) sums of (x, x^2)          -> forward statistics
 // MODE 1: per-(b,c) sums of (dy', dy' * xhat)  -> backward reductions, dy' = dy * silu'(u) when silu
 // part layout: [B][nsplit][C][2]
 template <typename T, typename TG, int MODE>
-__global__ void __launch_bounds__(GN_THREADS)
+__global__ void __launch_bounds__(GN_THREADS, GN_RED_MINB)
 gn_reduce_kernel(const T* __restrict__ x, const TG* __restrict__ dy, const float* __restrict__ stats,
                  const float* __restrict__ gamma, const float* __restrict__ beta, float* __restrict__ part, int HW,
                  int C, int G, int silu, int nsplit, int nitems) {
@@ -61,7 +80,7 @@ gn_reduce_kernel(const T* __restrict__ x, const TG* __restrict__ dy, const float
   if (row < rows) {
     const T* xb = x + static_cast<long long>(b) * HW * C + c0;
     const TG* dyb = MODE == 1 ? dy + static_cast<long long>(b) * HW * C + c0 : nullptr;
-    constexpr int U = 4;
+    constexpr int U = MODE == 0 ? 4 : GN_RED_U;  // forward statistics: one tensor, 4 loads in flight
     int p = p0 + row;
     for (; p + (U - 1) * rows < p1; p += U * rows) {
       T xv[U][V];
@@ -190,7 +209,7 @@ __global__ void gn_stats_finalize_kernel(const float* __restrict__ part, float* 
 // TO / TO2: formats of y and of the optional second copy y2 (mixed mode: fp16 for the forward conv, bf16 for wgrad);
 // sizeof(T) == sizeof(TO) == sizeof(TO2) so all three share one vector index.
 template <typename T, typename TO, typename TO2>
-__global__ void __launch_bounds__(GN_THREADS)
+__global__ void __launch_bounds__(GN_THREADS, GN_APPLY_MINB)
 gn_apply_kernel(const T* __restrict__ x, const float* __restrict__ stats, const float* __restrict__ gamma,
                 const float* __restrict__ beta, TO* __restrict__ y, TO2* __restrict__ y2, int HW, int C, int G,
                 int silu, int* __restrict__ overflow) {
@@ -315,7 +334,7 @@ __global__ void gn_bwd_finalize_b_kernel(const float* __restrict__ AB, float* __
 
 // dx = c1 * dy' + c2 * x + c3 (+ dx_add); one channel vector per thread for the whole loop (see gn_apply_kernel)
 template <typename T, typename TG>
-__global__ void __launch_bounds__(GN_THREADS)
+__global__ void __launch_bounds__(GN_THREADS, GN_BWD_MINB)
 gn_bwd_apply_kernel(const T* __restrict__ x, const TG* __restrict__ dy, const TG* __restrict__ dx_add,
                     const float* __restrict__ stats, const float* __restrict__ gamma, const float* __restrict__ beta,
                     const float* __restrict__ coef, TG* __restrict__ dx, int HW, int C, int G, int silu,
@@ -347,7 +366,7 @@ gn_bwd_apply_kernel(const T* __restrict__ x, const TG* __restrict__ dy, const TG
   const uint4* ab = dx_add ? reinterpret_cast<const uint4*>(dx_add + base) : nullptr;
   uint4* dxb = reinterpret_cast<uint4*>(dx + base);
   const long long stride = static_cast<long long>(gridDim.x) * GN_THREADS;
-  constexpr int U = 2;
+  constexpr int U = GN_BWD_U;
   for (; i < nvec; i += U * stride) {
     T xv[U][V];
     TG dv[U][V], av[U][V];

@@ -272,6 +272,12 @@ def test_encode_decode_api():
         assert H.rel_max(post.kl(), 0.5 * (post.mean ** 2 + post.var - 1 - post.logvar).sum(dim=[1, 2, 3])) < 1e-5
         dec = model.decode(post.mode())
         assert dec.shape == (3, 3, 64, 64) and dec.dtype == torch.float32
+        # decode() VALUES (post_quant_conv + Decoder, LD autoencoder.py:330-333) against the CPU oracle on the same latent
+        from oracle import odvae_oracle
+        sd = {k: v.detach().cpu() for k, v in model.state_dict().items() if torch.is_floating_point(v)}
+        orc = odvae_oracle.Oracle(params, sd, synth.synthetic_dataset_stats(23), synth.LABELS)
+        ref = orc.decode(post.mode().cpu())
+        assert H.rel_l2(dec, ref) < FP32_TOL and H.rel_max(dec, ref) < FP32_TOL
 
 
 def test_fused_adam_matches_torch_adam():

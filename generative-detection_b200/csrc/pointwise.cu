@@ -248,10 +248,11 @@ __global__ void __launch_bounds__(256) l1_masked_fwd_kernel(const float* __restr
     acc += fabsf(d0) + fabsf(d1) + fabsf(d2) + fabsf(d3);
     if (sgn != nullptr) {
       char4 s;
-      s.x = static_cast<signed char>(((d0 > 0.0f) - (d0 < 0.0f)) * mv.x);
-      s.y = static_cast<signed char>(((d1 > 0.0f) - (d1 < 0.0f)) * mv.y);
-      s.z = static_cast<signed char>(((d2 > 0.0f) - (d2 < 0.0f)) * mv.z);
-      s.w = static_cast<signed char>(((d3 > 0.0f) - (d3 < 0.0f)) * mv.w);
+      // the pure sign; the backward multiplies by the FLOAT mask, so a soft (bilinear-resized) mask differentiates exactly
+      s.x = static_cast<signed char>((d0 > 0.0f) - (d0 < 0.0f));
+      s.y = static_cast<signed char>((d1 > 0.0f) - (d1 < 0.0f));
+      s.z = static_cast<signed char>((d2 > 0.0f) - (d2 < 0.0f));
+      s.w = static_cast<signed char>((d3 > 0.0f) - (d3 < 0.0f));
       reinterpret_cast<char4*>(sgn + off)[pv] = s;
     }
   }
@@ -265,15 +266,17 @@ __global__ void l1_masked_final_kernel(const float* __restrict__ part, float* __
   for (int i = 0; i < nsplit; ++i) a += part[b * nsplit + i];
   sums[b] = a;
 }
-// dxhat = -sgn * coef[b]
-__global__ void __launch_bounds__(256) l1_masked_bwd_kernel(const int8_t* __restrict__ sgn,
+// dxhat = -sgn * mask * coef[b]   (d |x m - xhat m| / d xhat = -sign(.) m)
+__global__ void __launch_bounds__(256) l1_masked_bwd_kernel(const int8_t* __restrict__ sgn, const float* __restrict__ mask,
                                                             const float* __restrict__ coef, float* __restrict__ dxh,
-                                                            int CHW4, long long total4) {
+                                                            int CHW4, int HW4, long long total4) {
   for (long long i = blockIdx.x * 256ll + threadIdx.x; i < total4; i += gridDim.x * 256ll) {
     const int b = static_cast<int>(i / CHW4);
+    const int p4 = static_cast<int>((i - static_cast<long long>(b) * CHW4) % HW4);
     const float cf = -__ldg(coef + b);
+    const float4 m = __ldg(reinterpret_cast<const float4*>(mask) + static_cast<long long>(b) * HW4 + p4);
     const char4 s = reinterpret_cast<const char4*>(sgn)[i];
-    reinterpret_cast<float4*>(dxh)[i] = make_float4(s.x * cf, s.y * cf, s.z * cf, s.w * cf);
+    reinterpret_cast<float4*>(dxh)[i] = make_float4(s.x * m.x * cf, s.y * m.y * cf, s.z * m.z * cf, s.w * m.w * cf);
   }
 }
 
@@ -516,12 +519,12 @@ int odvae_l1_masked_fwd(const float* x, const float* xhat, const float* mask2d, 
   return check_launch("l1_masked_final_kernel");
 }
 
-int odvae_l1_masked_bwd(const int8_t* sgn, const float* coef, float* dxhat, int B, int C, int HW, void* stream) {
+int odvae_l1_masked_bwd(const int8_t* sgn, const float* mask2d, const float* coef, float* dxhat, int B, int C, int HW, void* stream) {
   if (B <= 0 || (HW & 3)) return ODVAE_ERR_SHAPE;
   cudaStream_t st = static_cast<cudaStream_t>(stream);
   const int chw4 = C * HW / 4;
   const long long total4 = static_cast<long long>(B) * chw4;
-  l1_masked_bwd_kernel<<<grid_1d(total4, 256), 256, 0, st>>>(sgn, coef, dxhat, chw4, total4);
+  l1_masked_bwd_kernel<<<grid_1d(total4, 256), 256, 0, st>>>(sgn, mask2d, coef, dxhat, chw4, HW / 4, total4);
   return check_launch("l1_masked_bwd_kernel");
 }
 

@@ -400,7 +400,11 @@ class side_stream:
             return self
         side = _SIDE.get(self.device.index)
         if side is None:
-            side = torch.cuda.Stream(self.device)
+            # high priority: when a weight-gradient GEMM and a GroupNorm kernel become runnable together, the GEMM's large CTAs
+            # (one per SM, ~200 KB of shared memory) must be placed FIRST -- the GroupNorm CTAs then fit beside them, while the
+            # other order fills every SM with small CTAs and serialises the two kernels (CUDA-graph kernel nodes inherit it)
+            prio = int(os.environ.get("ODVAE_SIDE_PRIORITY", "-1"))
+            side = torch.cuda.Stream(self.device, priority=prio)
             _SIDE[self.device.index] = side
         side.wait_stream(torch.cuda.current_stream(self.device))
         self.ctx = torch.cuda.stream(side)
@@ -1053,15 +1057,15 @@ class L1Masked(torch.autograd.Function):
         if ref is not None:
             scratch = torch.empty_like(sums)
             call("l1_masked_fwd", x, _c(ref.to(xhat)), mask2d, scratch, sgn, B, C, HW, ws, ws.numel())
-        ctx.save_for_backward(sgn)
+        ctx.save_for_backward(sgn, mask2d)
         return sums
 
     @staticmethod
     def backward(ctx, dsums):
-        (sgn,) = ctx.saved_tensors
+        sgn, mask2d = ctx.saved_tensors
         B, C, H, W = sgn.shape
         dxhat = torch.empty(B, C, H, W, dtype=torch.float32, device=sgn.device)
-        call("l1_masked_bwd", sgn, _c(dsums.float()), dxhat, B, C, H * W)
+        call("l1_masked_bwd", sgn, mask2d, _c(dsums.float()), dxhat, B, C, H * W)
         return None, dxhat, None
 
 

@@ -231,13 +231,14 @@ int odvae_sample_kl_bwd(const void* dz, const float* dkl, const float* dmean_dir
 /* ---------------------------------------------------------------------------------------------
  * Masked L1 reconstruction term (PoseLoss._get_rec_loss/_get_nll_loss LOSS.py:134-158, masks :250-257)
  * x, xhat: NCHW fp32 [B,3,H,W]; mask2d: fp32 [B,1,H,W]; sums[b] = sum |x*m - xhat*m| (0 if !use_pixel).
- * sgn (int8 NCHW) = sign(x*m - xhat*m)*m, saved for backward.
+ * sgn (int8 NCHW) = sign(x*m - xhat*m), saved for backward (the backward multiplies by the float mask, so a soft,
+ * e.g. bilinearly resized, mask differentiates exactly; the reference dataset's masks are {0,1}).
  * ------------------------------------------------------------------------------------------- */
 int odvae_l1_masked_fwd(const float* x, const float* xhat, const float* mask2d, float* sums, int8_t* sgn, int B,
                         int C, int HW, void* workspace, size_t ws_bytes, void* stream);
 size_t odvae_l1_masked_workspace_bytes(int B, int C, int HW);
-/* dxhat[b,c,p] = -sgn * coef[b]  (coef folds mask_bg, 1/(exp(logvar)+eps), 1/sum(mask_bg), upstream grad) */
-int odvae_l1_masked_bwd(const int8_t* sgn, const float* coef, float* dxhat, int B, int C, int HW, void* stream);
+/* dxhat[b,c,p] = -sgn * mask2d[b,p] * coef[b]  (coef folds mask_bg, 1/(exp(logvar)+eps), 1/sum(mask_bg), upstream grad) */
+int odvae_l1_masked_bwd(const int8_t* sgn, const float* mask2d, const float* coef, float* dxhat, int B, int C, int HW, void* stream);
 
 /* ---------------------------------------------------------------------------------------------
  * Fused Adam (AE.py:365-377: lr, betas=(0.5,0.9), eps=1e-8) + global-norm clip (CFG:140) on flat

@@ -148,6 +148,16 @@ def test_sample_kl_and_l1_against_torch():
     (ref * w).sum().backward()
     torch.cuda.synchronize()
     assert rel(sums, ref) < 1e-5 and rel(xh.grad, xr.grad) < 1e-6
+    # a SOFT mask (e.g. bilinearly resized): the backward multiplies the saved sign by the float mask
+    soft = torch.rand(B, 1, 32, 32, device=DEV)
+    xh2 = xh.detach().clone().requires_grad_(True)
+    (ops.L1Masked.apply(x, xh2, soft) * w).sum().backward()
+    xr2 = xh.detach().clone().requires_grad_(True)
+    ((x * soft - xr2 * soft).abs().sum(dim=[1, 2, 3]) * w).sum().backward()
+    torch.cuda.synchronize()
+    assert rel(xh2.grad, xr2.grad) < 1e-6
+    with pytest.raises(RuntimeError, match="one value per pixel"):
+        ops.L1Masked.apply(x, xh2, soft[:, :, :16])
 
 
 @pytest.mark.parametrize("B,N,C", [(2, 256, 512), (1, 1024, 256), (2, 4096, 256)])

@@ -63,6 +63,7 @@ struct TcParams {
   // buffers the epilogue transposes 32 pixels x 32 channels through, so that the 16-bit results leave as 16-byte vector
   // stores (and the residual arrives as 16-byte vector loads); 0 = scalar 2-byte path.
   int epi_off;
+  int res_prefetch;  // staged residual epilogue: L2-prefetch the tile's residual lines at tile start (ODVAE_RES_PREFETCH)
 };
 
 

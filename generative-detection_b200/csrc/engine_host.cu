@@ -137,9 +137,12 @@ static int launch_tc(EngineDesc& d, cudaStream_t stream) {
   // swapped-role conv epilogue: 8 x 2 KiB staging buffers for 16-byte vector stores / residual loads
   p.epi_off = 0;
   {
+    // default OFF since round 2: with the tile's residual lines prefetched into L2 at tile start (res_prefetch below) the
+    // direct epilogue (2-byte loads, 64 contiguous bytes per warp and pixel) measured 1.13-1.15 ms for 128->128 3x3 @256^2 x 64
+    // with a residual against 1.25-1.26 ms through the staging buffers (which also cost the halo tiles one weight stage)
     static const bool epi_stage_on = [] {
       const char* v = getenv("ODVAE_EPI_STAGE");
-      return !(v && v[0] == '0');
+      return v && v[0] == '1';
     }();
     const bool aligned = (p.n_valid % 8) == 0 && (p.oX % 8) == 0 && (p.oY % 8) == 0 && (p.oB % 8) == 0 && (p.o0 % 8) == 0;
     // (only where a residual is added: plain stores measured no faster through the staging buffer)
@@ -156,6 +159,11 @@ static int launch_tc(EngineDesc& d, cudaStream_t stream) {
         smem = off + 16384 + 1024;
       }
     }
+    static const bool res_prefetch_on = [] {
+      const char* v = getenv("ODVAE_RES_PREFETCH");
+      return !(v && v[0] == '0');
+    }();
+    p.res_prefetch = (res_prefetch_on && p.kind == KIND_CONV && p.swap && p.residual != nullptr) ? 1 : 0;
   }
   const long long total = static_cast<long long>(p.num_m_tiles) * p.num_n_tiles * p.num_z;
   if (total <= 0 || p.num_k_iters <= 0) return ODVAE_ERR_SHAPE;

@@ -547,7 +547,22 @@ tc_engine_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant_
             }
           }
         };
-        if (stg != nullptr && R16 != nullptr) load_rv(0);  // in flight while the accumulator completes
+        if (R16 != nullptr) {
+          if (stg != nullptr) load_rv(0);  // in flight while the accumulator completes
+          if (p.res_prefetch && ch_ok) {
+            // this warp's residual columns for the whole tile (staged path: the three later 32-pixel batches): pull their lines
+            // into L2 now -- the tile's MMAs take ~6 us -- so that the epilogue's loads see L2 latency, not DRAM latency
+#pragma unroll
+            for (int j = 0; j < 4; ++j) {
+              if (j == 0 && stg != nullptr) continue;
+              const int pi = 32 * j + lane;
+              const int yy = pb_y + (pi >> p.bw_log2), xx = pb_x + (pi & ((1 << p.bw_log2) - 1));
+              const uint16_t* a = R16 + static_cast<long long>(pb_b) * p.oB + p.o0 + (m0 + q * 32) +
+                                  static_cast<long long>(yy) * p.oY + static_cast<long long>(xx) * sx;
+              asm volatile("prefetch.global.L2 [%0];" ::"l"(a));
+            }
+          }
+        }
         mbar_wait(&tfull_bar[acc], acc_phase);
         tc_fence_after();
         uint32_t va[32], vb[32];

@@ -248,9 +248,11 @@ static int attn_nt(int N) {
   return d.p.num_n_tiles;
 }
 
+static constexpr int ATTN_PARTS = tc_epi_warps(TC_SPEC_GEMM_SOFTMAX) / 4;  // column parts of a row-statistics tile
+
 size_t odvae_attn_softmax_workspace_bytes(int B, int N) {
-  // row partials (two column halves per tile) + the combined log-sum-exp per row
-  return static_cast<size_t>(B) * attn_nt(N) * 2 * N * 2 * sizeof(float) + static_cast<size_t>(B) * N * sizeof(float) + 256;
+  // row partials (ATTN_PARTS column parts per tile, one per epilogue warp of a lane quadrant) + the combined log-sum-exp per row
+  return static_cast<size_t>(B) * attn_nt(N) * ATTN_PARTS * N * 2 * sizeof(float) + static_cast<size_t>(B) * N * sizeof(float) + 256;
 }
 
 int odvae_attn_scores_softmax(const void* q, const void* k, void* P, int B, int N, int C, int64_t ldq, int64_t ldk,
@@ -260,7 +262,7 @@ int odvae_attn_scores_softmax(const void* q, const void* k, void* P, int B, int 
   if (ws_bytes < odvae_attn_softmax_workspace_bytes(B, N) - 256) return ODVAE_ERR_WORKSPACE;
   cudaStream_t s = static_cast<cudaStream_t>(stream);
   const int om = dtype == ODVAE_F16 ? OUT_F16 : OUT_BF16;
-  const int slots = attn_nt(N) * 2;
+  const int slots = attn_nt(N) * ATTN_PARTS;
   float* part = reinterpret_cast<float*>(workspace);
   float* lse2 = part + static_cast<size_t>(B) * slots * N * 2;
   for (int pass = 0; pass < 2; ++pass) {

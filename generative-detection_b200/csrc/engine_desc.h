@@ -15,6 +15,12 @@ enum {
   TC_SPEC_GEMM_DSOFTMAX = 5, // KIND_GEMM, EPI_DSOFTMAX
   TC_NUM_SPECS = 6
 };
+// Epilogue warps per CTA (after warp 0 = TMA producer, warp 1 = MMA issuer): two per TMEM lane quadrant, half the accumulator
+// columns each. The softmax-backward instance (its epilogue streams a P tile from HBM and a dS tile back) runs 16: four per
+// quadrant, 64 columns each -- 1.20 -> 1.09 ms per B = 64 block together with the stationary B panel below; the forward
+// softmax instances measured 3 % slower with 16 (their epilogue is issue-bound: 10.7 k warp instructions per tile).
+constexpr int tc_epi_warps(int spec) { return spec == TC_SPEC_GEMM_DSOFTMAX ? 16 : 8; }
+constexpr int tc_threads(int spec) { return 64 + 32 * tc_epi_warps(spec); }
 enum { OUT_BF16 = 0, OUT_F32 = 1, OUT_NCHW_F32 = 2, OUT_F16 = 3 };
 enum { FMT_F16 = 0, FMT_BF16 = 1 };
 // fused attention epilogues of KIND_GEMM (see tc_engine.cuh): row statistics / softmax / softmax backward
@@ -64,6 +70,13 @@ struct TcParams {
   // stores (and the residual arrives as 16-byte vector loads); 0 = scalar 2-byte path.
   int epi_off;
   int res_prefetch;  // staged residual epilogue: L2-prefetch the tile's residual lines at tile start (ODVAE_RES_PREFETCH)
+  // GEMM with a stationary B panel (K <= 256, both operands K-major): a CTA walks RUNS of bstat_mt consecutive m-tiles
+  // that share (n_tile, z); the BN x K panel of B is loaded once per run into shared memory (num_k_iters chunks of
+  // BN x 64) and only the 16 KiB A tiles stream through the stage ring, which cuts the L2 -> SM operand traffic of a
+  // K = 256 score GEMM from 192 KiB to ~68 KiB per 128 x 256 tile (lts throughput 42 % -> 10 %). Used for dO v^T + softmax
+  // backward, whose epilogue needs the L2 bandwidth for the P / dS tiles; the q k^T passes measured 4 % slower with it (the
+  // panel reload at every run boundary stalls the MMAs) and keep the plain schedule. 0 = every tile loads both operands.
+  int bstat_mt, bstat_runs;
 };
 
 

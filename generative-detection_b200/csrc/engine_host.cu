@@ -134,6 +134,38 @@ static int launch_tc(EngineDesc& d, cudaStream_t stream) {
     p.stages = tc_pick_stages(b_rows, p.num_k_iters);
     smem = tc_smem_bytes(p.stages, b_rows);
   }
+  // dO v^T + softmax backward (K = C = 256, 32 x 16 tiles per image): keep the v panel in shared memory for a run of
+  // m-tiles, so that the L2 -> SM path carries the P / dS tiles of the epilogue instead of re-fetched operands (engine_desc.h)
+  p.bstat_mt = p.bstat_runs = 0;
+  {
+    static const bool bstat_on = [] {
+      const char* v = getenv("ODVAE_GEMM_BSTAT");
+      return !(v && v[0] == '0');
+    }();
+    const size_t panel = static_cast<size_t>(p.num_k_iters) * p.BN * 128;
+    if (bstat_on && p.kind == KIND_GEMM && p.epi == EPI_DSOFTMAX && !p.a_mn && !p.b_mn && panel <= 128 * 1024 && p.num_m_tiles >= 8) {
+      const int sms = num_sms();
+      // longest run length (a divisor of the m-tile count) whose last wave of runs still fills >= 90 % of the SMs
+      int best = 0;
+      for (int mt = p.num_m_tiles; mt >= 4; --mt) {
+        if (p.num_m_tiles % mt) continue;
+        const long long runs = static_cast<long long>(p.num_n_tiles) * p.num_z * (p.num_m_tiles / mt);
+        const long long waves = (runs + sms - 1) / sms;
+        if (runs >= sms && static_cast<double>(runs) / static_cast<double>(waves * sms) >= 0.9) {
+          best = mt;
+          break;
+        }
+      }
+      if (best > 0) {
+        p.bstat_mt = best;
+        p.bstat_runs = static_cast<int>(static_cast<long long>(p.num_n_tiles) * p.num_z * (p.num_m_tiles / best));
+        int s = static_cast<int>((224 * 1024 - 2048 - panel) / TC_A_BYTES);
+        if (s > 8) s = 8;
+        p.stages = s;
+        smem = static_cast<size_t>(p.stages) * TC_A_BYTES + panel + (2 * p.stages + 8) * 8 + 16 + 1024;
+      }
+    }
+  }
   // swapped-role conv epilogue: 8 x 2 KiB staging buffers for 16-byte vector stores / residual loads
   p.epi_off = 0;
   {
@@ -169,6 +201,7 @@ static int launch_tc(EngineDesc& d, cudaStream_t stream) {
   if (total <= 0 || p.num_k_iters <= 0) return ODVAE_ERR_SHAPE;
   int grid = num_sms();
   if (total < grid) grid = static_cast<int>(total);
+  if (p.bstat_mt > 0 && p.bstat_runs < grid) grid = p.bstat_runs;
   // the instance of tc_engine_kernel<SPEC> compiled for this (kind, operand roles, epilogue)
   int spec;
   if (p.kind == KIND_CONV) {

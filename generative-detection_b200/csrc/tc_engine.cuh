@@ -16,6 +16,7 @@ static constexpr int TC_BLOCK_M = 128;
 static constexpr int TC_BLOCK_K = 64;
 static constexpr int TC_A_BYTES = TC_BLOCK_M * TC_BLOCK_K * 2;  // 16 KiB
 static constexpr int TC_THREADS = 320;  // warp 0: TMEM alloc + TMA producer; warp 1: MMA issuer; warps 2-9: epilogue
+// (the softmax-backward instance runs 16 epilogue warps: tc_epi_warps / tc_threads in engine_desc.h)
 static constexpr int TC_TMEM_COLS = 512;
 // halo slab: one input row of 256 pixels + 1 halo pixel on each side, 128 B (64 channels) per pixel, written by two
 // 130-pixel TMA boxes (x = -1..128 and 129..258; out-of-image pixels are zero-filled); padded to a 1 KiB multiple
@@ -59,6 +60,25 @@ __device__ __forceinline__ TileCoord decode_tile(const TcParams& p, const int ki
   return c;
 }
 
+// Tile s of this CTA's walk. Default: tiles blockIdx.x, + gridDim.x, ... B-stationary GEMM (bstat_mt > 0): runs blockIdx.x,
+// + gridDim.x, ... of bstat_mt consecutive m-tiles with (n_tile, z) fixed; `mi` = position inside the run. -1 = done.
+__device__ __forceinline__ int sched_tile(const TcParams& p, const int total_tiles, const int s, int& mi) {
+  if (p.bstat_mt <= 0) {
+    mi = 0;
+    const long long t = static_cast<long long>(blockIdx.x) + static_cast<long long>(s) * gridDim.x;
+    return t < total_tiles ? static_cast<int>(t) : -1;
+  }
+  const int rs = s / p.bstat_mt;
+  mi = s - rs * p.bstat_mt;
+  const long long run = static_cast<long long>(blockIdx.x) + static_cast<long long>(rs) * gridDim.x;
+  if (run >= p.bstat_runs) return -1;
+  const int nz = p.num_n_tiles * p.num_z;
+  const int part = static_cast<int>(run / nz);
+  const int rem = static_cast<int>(run - static_cast<long long>(part) * nz);
+  const int z = rem / p.num_n_tiles, n = rem - z * p.num_n_tiles;
+  return (z * p.num_m_tiles + part * p.bstat_mt + mi) * p.num_n_tiles + n;  // decode_tile's order
+}
+
 // k-iterations of one tile: WGRAD splits its pixel chunks unevenly (the last split takes the remainder)
 __device__ __forceinline__ int tile_k_iters(const TcParams& p, const int kind, const TileCoord& c) {
   if (kind != KIND_WGRAD) return p.num_k_iters;
@@ -76,13 +96,14 @@ __device__ __forceinline__ void spatial_load(void* dst, const CUtensorMap* tm, u
 
 // SPEC: TC_SPEC_* (engine_desc.h). One instance per .cu file (tc_engine_inst*.cu) so they compile in parallel.
 template <int SPEC>
-__global__ void __launch_bounds__(TC_THREADS, 1)
+__global__ void __launch_bounds__(tc_threads(SPEC), 1)
 tc_engine_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUtensorMap tmB,
                  const __grid_constant__ TcParams p) {
   // The operation kind, the operand roles and the epilogue are compile-time constants of each instance: every mode gets
   // its own register allocation (the monolithic kernel spilled at the 168-register cap of a 320-thread CTA).
   constexpr int kKind = SPEC <= TC_SPEC_CONV_SWAP ? KIND_CONV : (SPEC == TC_SPEC_WGRAD ? KIND_WGRAD : KIND_GEMM);
   constexpr bool kSwap = SPEC == TC_SPEC_CONV_SWAP;
+  constexpr int kEpiThreads = 32 * tc_epi_warps(SPEC);
   const int epi = SPEC <= TC_SPEC_GEMM ? static_cast<int>(EPI_NONE)
                   : SPEC == TC_SPEC_GEMM_DSOFTMAX ? static_cast<int>(EPI_DSOFTMAX)
                   : (p.epi == EPI_ROWSTATS ? static_cast<int>(EPI_ROWSTATS) : static_cast<int>(EPI_SOFTMAX));
@@ -103,9 +124,13 @@ tc_engine_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant_
   // halo mode: sA = weight stages, sB = ring of input-row slabs
   const uint32_t wslab_tx = static_cast<uint32_t>(((1 << p.kbw_log2) + 2) * (TC_BLOCK_K >> p.kbw_log2)) * 128u;
   const bool cv_halo = kKind == KIND_CONV && p.halo;
-  const int nslabs = cv_halo ? p.halo_slabs : 0;
+  // stationary B panel: sB = num_k_iters chunks of BN x 64, guarded by sfull_bar[0] / sempty_bar[0]
+  const bool bstat = kKind == KIND_GEMM && p.bstat_mt > 0;
+  const uint32_t bchunk = static_cast<uint32_t>(BN) * 128u;
+  const int nslabs = cv_halo ? p.halo_slabs : (bstat ? 1 : 0);
   uint64_t* bars = reinterpret_cast<uint64_t*>(
-      sB + (cv_halo ? static_cast<size_t>(nslabs) * TC_SLAB_BYTES : static_cast<size_t>(stages) * b_bytes));
+      sB + (cv_halo ? static_cast<size_t>(nslabs) * TC_SLAB_BYTES
+                    : (bstat ? static_cast<size_t>(p.num_k_iters) * bchunk : static_cast<size_t>(stages) * b_bytes)));
   uint64_t* full_bar = bars;
   uint64_t* empty_bar = bars + stages;
   uint64_t* tfull_bar = bars + 2 * stages;
@@ -129,7 +154,7 @@ tc_engine_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant_
     }
     for (int i = 0; i < 2; ++i) {
       mbar_init(&tfull_bar[i], 1);
-      mbar_init(&tempty_bar[i], 256);
+      mbar_init(&tempty_bar[i], kEpiThreads);
     }
     for (int i = 0; i < nslabs; ++i) {
       mbar_init(&sfull_bar[i], 1);
@@ -185,15 +210,28 @@ tc_engine_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant_
     } else if (lane == 0) {
       int stage = 0;
       uint32_t phase = 0;
-      for (int t = blockIdx.x; t < total_tiles; t += gridDim.x) {
+      uint32_t bph = 0;
+      for (int s = 0;; ++s) {
+        int mi;
+        const int t = sched_tile(p, total_tiles, s, mi);
+        if (t < 0) break;
         const TileCoord tc = decode_tile(p, kKind, kSwap, t);
         const int m0 = tc.m_tile * TC_BLOCK_M;
         const int n0 = tc.n_tile * BN;
         const int nk = tile_k_iters(p, kKind, tc);
+        if (bstat && mi == 0) {
+          // new run: the panel may be overwritten once every MMA of the previous run has retired
+          mbar_wait(&sempty_bar[0], bph ^ 1u);
+          mbar_arrive_expect_tx(&sfull_bar[0], static_cast<uint32_t>(nk) * bchunk);
+          for (int kit = 0; kit < nk; ++kit)
+            tma_load_3d(sB + static_cast<size_t>(kit) * bchunk, &tmB, &sfull_bar[0], kit * TC_BLOCK_K, n0, tc.z);
+          bph ^= 1u;
+        }
         for (int kit = 0; kit < nk; ++kit) {
           mbar_wait(&empty_bar[stage], phase ^ 1u);
           uint64_t* fb = &full_bar[stage];
-          mbar_arrive_expect_tx(fb, wg_halo ? TC_A_BYTES + static_cast<uint32_t>(BN >> 6) * wslab_tx : TC_A_BYTES + b_bytes);
+          mbar_arrive_expect_tx(fb, wg_halo ? TC_A_BYTES + static_cast<uint32_t>(BN >> 6) * wslab_tx
+                                            : (bstat ? static_cast<uint32_t>(TC_A_BYTES) : TC_A_BYTES + b_bytes));
           uint8_t* a_dst = sA + static_cast<size_t>(stage) * TC_A_BYTES;
           uint8_t* b_dst = sB + static_cast<size_t>(stage) * b_bytes;
           if (kKind == KIND_GEMM) {
@@ -204,7 +242,9 @@ tc_engine_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant_
               tma_load_3d(a_dst, &tmA, fb, m0, k0, tc.z);
               tma_load_3d(a_dst + 8192, &tmA, fb, m0 + 64, k0, tc.z);
             }
-            if (!p.b_mn) {
+            if (bstat) {
+              // B is the run's stationary panel
+            } else if (!p.b_mn) {
               tma_load_3d(b_dst, &tmB, fb, k0, n0, tc.z);
             } else {
               for (int j = 0; j < (BN >> 6); ++j) tma_load_3d(b_dst + j * 8192, &tmB, fb, n0 + 64 * j, k0, tc.z);
@@ -310,17 +350,27 @@ tc_engine_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant_
           acc_phase ^= 1u;
         }
       }
-      for (int t = blockIdx.x; !cv_halo && t < total_tiles; t += gridDim.x) {
+      uint32_t bph = 0;
+      for (int s = 0; !cv_halo; ++s) {
+        int mi;
+        const int t = sched_tile(p, total_tiles, s, mi);
+        if (t < 0) break;
         mbar_wait(&tempty_bar[acc], acc_phase ^ 1u);
         tc_fence_after();
         const uint32_t d_tmem = tmem_base + static_cast<uint32_t>(acc * acc_cols);
         const TileCoord tcm = decode_tile(p, kKind, kSwap, t);
         const int nk = tile_k_iters(p, kKind, tcm);
+        if (bstat && mi == 0) {
+          mbar_wait(&sfull_bar[0], bph);
+          tc_fence_after();
+          bph ^= 1u;
+        }
         for (int kit = 0; kit < nk; ++kit) {
           mbar_wait(&full_bar[stage], phase);
           tc_fence_after();
           const uint32_t a_base = smem_u32(sA + static_cast<size_t>(stage) * TC_A_BYTES);
-          const uint32_t b_base = smem_u32(sB + static_cast<size_t>(stage) * b_bytes);
+          const uint32_t b_base = bstat ? smem_u32(sB + static_cast<size_t>(kit) * bchunk)
+                                        : smem_u32(sB + static_cast<size_t>(stage) * b_bytes);
 #pragma unroll
           for (int k = 0; k < TC_BLOCK_K / 16; ++k) {
             const uint64_t adesc = p.a_mn ? make_smem_desc_sw128(a_base + k * 2048, 8192, 1024)
@@ -352,6 +402,7 @@ tc_engine_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant_
           }
         }
         umma_commit(&tfull_bar[acc]);  // accumulator complete -> epilogue
+        if (bstat && mi == p.bstat_mt - 1) umma_commit(&sempty_bar[0]);  // run complete -> the panel may be replaced
         if (++acc == num_acc) {
           acc = 0;
           acc_phase ^= 1u;
@@ -365,16 +416,21 @@ tc_engine_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant_
     // accumulator's columns in halves, so all four SM sub-partitions carry two epilogue warps each.
     const int q = warp & 3;         // TMEM lane quadrant this warp may access
     const int r = q * 32 + lane;    // row within the tile
+    // (`half` = column part: 0..1 with 8 epilogue warps, 0..3 with the 16 of the attention-score instances)
+    constexpr int kParts = tc_epi_warps(SPEC) / 4;
     const int half = (warp - 2) >> 2;
-    const bool split_cols = (acc_cols % 32) == 0;
-    const int nhalf = split_cols ? 2 : 1;
-    const int c_begin = split_cols ? half * (acc_cols >> 1) : 0;
-    const int c_end = split_cols ? c_begin + (acc_cols >> 1) : (half == 0 ? acc_cols : 0);
+    const bool split_cols = (acc_cols % (16 * kParts)) == 0;
+    const int nhalf = split_cols ? kParts : 1;
+    const int c_begin = split_cols ? half * (acc_cols / kParts) : 0;
+    const int c_end = split_cols ? c_begin + (acc_cols / kParts) : (half == 0 ? acc_cols : 0);
     int acc = 0;
     uint32_t acc_phase = 0;
     int cs_stage = 0;
     uint32_t cs_phase = 0;
-    for (int t = blockIdx.x; t < total_tiles; t += gridDim.x) {
+    for (int s = 0;; ++s) {
+      int mi;
+      const int t = sched_tile(p, total_tiles, s, mi);
+      if (t < 0) break;
       const TileCoord tc = decode_tile(p, kKind, kSwap, t);
       const int m0 = tc.m_tile * TC_BLOCK_M;
       const int n0 = tc.n_tile * BN;
@@ -585,14 +641,16 @@ tc_engine_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant_
           *dst = make_float2(gs0 + gs1, gq0 + gq1);
         }
       } else if (epi != EPI_NONE) {
-        // ---- fused attention epilogues (KIND_GEMM; one accumulator row and <= 128 columns per thread) ----
+        // ---- fused attention epilogues (KIND_GEMM, BN = 256; one accumulator row and kCols columns per thread) ----
         // Global reads this tile needs (softmax partials / delta / the P tile) are issued BEFORE waiting for the
-        // accumulator, so their latency hides behind the tile's MMAs; TMEM is drained 32 columns at a time with the
+        // accumulator, so their latency hides behind the tile's MMAs; TMEM is drained 32 (16) columns at a time with the
         // next tcgen05.ld in flight while the current chunk is processed.
+        constexpr int kCols = 256 / kParts;  // columns per warp (the host checks N % 256 == 0)
+        constexpr int kPV = kCols / 16;      // 32-byte vectors of P per thread
         const float s2 = p.alpha * 1.4426950408889634f;  // scores live in the log2 domain: exp(a*s) = 2^(s2*s)
         const bool halfp = p.out_mode == OUT_F16;
         float mx = -INFINITY, l = 0.0f, lse2 = 0.0f, delta = 0.0f;  // mx: running max of the RAW accumulators
-        uint32_t pp[8][8];  // DSOFTMAX: this thread's 128 P values (8 x 32 bytes)
+        uint32_t pp[kPV][8];  // DSOFTMAX: this thread's kCols P values
         if (epi == EPI_SOFTMAX && row_ok) {
           // lse2[row] = max + log2(sum 2^(s2*s - max)), combined from the row partials by attn_stats_combine_kernel
           lse2 = __ldg(p.aux_f32 + static_cast<long long>(tc.z) * p.m_valid + (m0 + r));
@@ -600,7 +658,17 @@ tc_engine_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant_
           delta = __ldg(p.aux_f32 + static_cast<long long>(tc.z) * p.m_valid + (m0 + r));
           const uint16_t* psrc = reinterpret_cast<const uint16_t*>(p.aux16) + row_off + c_begin;
 #pragma unroll
-          for (int i = 0; i < 8; ++i) ld_global_nc_256(psrc + 16 * i, pp[i]);
+          for (int i = 0; i < kPV; ++i) ld_global_nc_256(psrc + 16 * i, pp[i]);
+          // P streams from HBM (2 GB per block): pull the NEXT tile's segment of this thread's row into L2 now, a whole
+          // tile time ahead of the loads above
+          int mi_n;
+          const int tn = sched_tile(p, total_tiles, s + 1, mi_n);
+          if (tn >= 0) {
+            const TileCoord tcn = decode_tile(p, kKind, kSwap, tn);
+            if (tcn.m_tile * TC_BLOCK_M + r < p.m_valid)
+              prefetch_l2(reinterpret_cast<const uint16_t*>(p.aux16) + static_cast<long long>(tcn.z) * p.strideD +
+                          static_cast<long long>(tcn.m_tile * TC_BLOCK_M + r) * p.ldd + tcn.n_tile * BN + c_begin);
+          }
         }
         mbar_wait(&tfull_bar[acc], acc_phase);
         tc_fence_after();
@@ -608,18 +676,26 @@ tc_engine_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant_
         auto process = [&](uint32_t (&v)[32], int cc) {
           if (epi == EPI_ROWSTATS) {
             // online (max, sum 2^(s2*(v - max))) on raw accumulators: s2 > 0, so the max commutes with the scale
-            float cm = __uint_as_float(v[0]);
+            // (four independent chains each: a 31-deep fmax chain left the MUFU pipe idle for its whole latency)
+            float c0 = __uint_as_float(v[0]), c1 = __uint_as_float(v[1]), c2 = __uint_as_float(v[2]), c3 = __uint_as_float(v[3]);
 #pragma unroll
-            for (int i = 1; i < 32; ++i) cm = fmaxf(cm, __uint_as_float(v[i]));
-            const float mn = fmaxf(mx, cm);
+            for (int i = 4; i < 32; i += 4) {
+              c0 = fmaxf(c0, __uint_as_float(v[i]));
+              c1 = fmaxf(c1, __uint_as_float(v[i + 1]));
+              c2 = fmaxf(c2, __uint_as_float(v[i + 2]));
+              c3 = fmaxf(c3, __uint_as_float(v[i + 3]));
+            }
+            const float mn = fmaxf(mx, fmaxf(fmaxf(c0, c1), fmaxf(c2, c3)));
             const float off = -mn * s2;
-            float a0 = 0.0f, a1 = 0.0f;
+            float a0 = 0.0f, a1 = 0.0f, a2 = 0.0f, a3 = 0.0f;
 #pragma unroll
-            for (int i = 0; i < 32; i += 2) {
+            for (int i = 0; i < 32; i += 4) {
               a0 += fast_exp2(fmaf(__uint_as_float(v[i]), s2, off));
               a1 += fast_exp2(fmaf(__uint_as_float(v[i + 1]), s2, off));
+              a2 += fast_exp2(fmaf(__uint_as_float(v[i + 2]), s2, off));
+              a3 += fast_exp2(fmaf(__uint_as_float(v[i + 3]), s2, off));
             }
-            l = l * fast_exp2((mx - mn) * s2) + (a0 + a1);
+            l = l * fast_exp2((mx - mn) * s2) + ((a0 + a1) + (a2 + a3));
             mx = mn;
           } else if (row_ok) {
             uint32_t o[16];
@@ -636,17 +712,16 @@ tc_engine_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant_
             st_global_256(dst + 16, o_hi);
           }
         };
-        // every epilogue warp owns exactly 128 accumulator columns here (BN = 256; the host checks N % 256 == 0)
         if (epi == EPI_DSOFTMAX) {
-          // dS = P * (dP - delta) * alpha: 8 chunks of 16 columns, the next tcgen05.ld in flight during each chunk
+          // dS = P * (dP - delta) * alpha: chunks of 16 columns, the next tcgen05.ld in flight during each chunk
           uint32_t da[16], db[16];
           tmem_ld_x16(t_row + static_cast<uint32_t>(c_begin), da);
 #pragma unroll
-          for (int j = 0; j < 8; ++j) {
+          for (int j = 0; j < kPV; ++j) {
             uint32_t (&cur)[16] = (j & 1) ? db : da;
             uint32_t (&nxt)[16] = (j & 1) ? da : db;
             tmem_ld_wait();
-            if (j < 7) tmem_ld_x16(t_row + static_cast<uint32_t>(c_begin + 16 * (j + 1)), nxt);
+            if (j < kPV - 1) tmem_ld_x16(t_row + static_cast<uint32_t>(c_begin + 16 * (j + 1)), nxt);
             if (row_ok) {
               const uint32_t (&pw)[8] = pp[j];
               uint32_t o[8];
@@ -662,17 +737,14 @@ tc_engine_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant_
         } else {
           uint32_t va[32], vb[32];
           tmem_ld_x32(t_row + static_cast<uint32_t>(c_begin), va);
-          tmem_ld_wait();
-          tmem_ld_x32(t_row + static_cast<uint32_t>(c_begin + 32), vb);
-          process(va, c_begin);
-          tmem_ld_wait();
-          tmem_ld_x32(t_row + static_cast<uint32_t>(c_begin + 64), va);
-          process(vb, c_begin + 32);
-          tmem_ld_wait();
-          tmem_ld_x32(t_row + static_cast<uint32_t>(c_begin + 96), vb);
-          process(va, c_begin + 64);
-          tmem_ld_wait();
-          process(vb, c_begin + 96);
+#pragma unroll
+          for (int j = 0; j < kCols / 32; ++j) {
+            uint32_t (&cur)[32] = (j & 1) ? vb : va;
+            uint32_t (&nxt)[32] = (j & 1) ? va : vb;
+            tmem_ld_wait();
+            if (j < kCols / 32 - 1) tmem_ld_x32(t_row + static_cast<uint32_t>(c_begin + 32 * (j + 1)), nxt);
+            process(cur, c_begin + 32 * j);
+          }
         }
         if (epi == EPI_ROWSTATS && row_ok) {
           float2* dst = reinterpret_cast<float2*>(p.aux_out) +

@@ -16,7 +16,7 @@
                                       227 * 1024);                                                                  \
     });                                                                                                             \
     if (attr_err != cudaSuccess) return attr_err;                                                                   \
-    tc_engine_kernel<SPEC><<<grid, TC_THREADS, smem, st>>>(tmA, tmB, p);                                            \
+    tc_engine_kernel<SPEC><<<grid, tc_threads(SPEC), smem, st>>>(tmA, tmB, p);                                            \
     return cudaSuccess;                                                                                             \
   }                                                                                                                 \
   }

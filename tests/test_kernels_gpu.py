@@ -160,10 +160,13 @@ def test_sample_kl_and_l1_against_torch():
         ops.L1Masked.apply(x, xh2, soft[:, :, :16])
 
 
-@pytest.mark.parametrize("B,N,C", [(2, 256, 512), (1, 1024, 256), (2, 4096, 256)])
+@pytest.mark.parametrize("B,N,C", [(2, 256, 512), (1, 1024, 256), (2, 4096, 256), (8, 4096, 256), (37, 1024, 128),
+                                   (16, 4096, 256)])
 def test_fused_attention_core_against_torch(B, N, C):
     """odvae_attn_scores_softmax / odvae_rowdot / odvae_attn_dsoftmax vs torch fp32 on the same bf16 inputs
-    (AttnBlock core, LD model.py:187-197). Tolerance 1e-2 relative (bf16 outputs)."""
+    (AttnBlock core, LD model.py:187-197). Tolerance 1e-2 relative (bf16 outputs). In the last three shapes the softmax
+    backward has enough (key tile, image) runs to take the engine's stationary-B-panel schedule (engine_desc.h bstat_mt:
+    runs of 4 / 8 / 8 query tiles per resident v panel); the first three walk tile by tile."""
     torch.manual_seed(11)
     dt = torch.bfloat16
     qkv = torch.randn(B, N, 3 * C, device="cuda").to(dt)

@@ -1,33 +1,46 @@
-"""Runs the fused attention core kernels alone at the bench shape (B=64, N=4096, C=256): timing with CUDA events, and
-a small target for `ncu --set full` (3 engine launches per iteration: row-stats pass, softmax pass, dsoftmax)."""
-import os, sys
-ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
-sys.path[:0] = [os.path.join(ROOT, "generative-detection_b200"), ROOT]
-import torch
-from odvae_b200 import ops
+"""Times the attention score kernels of one AttnBlock at the bench shape (B x 4096 x 4096, C = 256) on the B200:
+    python tools/attn_probe.py [B] [fp16|bf16]
+q k^T + softmax (2 passes), dO v^T + softmax backward, and the plain P v GEMM, CUDA-event timed over 20 calls after 3."""
+import os
+import sys
 
-B, N, C = int(os.environ.get("PB", 64)), 4096, 256
-iters = int(sys.argv[1]) if len(sys.argv) > 1 else 5
-dt = torch.bfloat16
+import torch
+
+sys.path.insert(0, os.path.join(os.path.dirname(os.path.abspath(__file__)), "..", "generative-detection_b200"))
+from odvae_b200 import ops  # noqa: E402
+
+B = int(sys.argv[1]) if len(sys.argv) > 1 else 64
+dt = torch.float16 if (len(sys.argv) < 3 or sys.argv[2] == "fp16") else torch.bfloat16
+N, C = 4096, 256
 torch.manual_seed(0)
-qkv = torch.randn(B, N, 3 * C, device="cuda").to(dt)
+qkv = (torch.randn(B, N, 3 * C, device="cuda") * 0.5).to(dt)
 q, k, v = qkv[..., :C], qkv[..., C:2 * C], qkv[..., 2 * C:]
 P = torch.empty(B, N, N, dtype=dt, device="cuda")
 dS = torch.empty(B, N, N, dtype=dt, device="cuda")
 dO = torch.randn(B, N, C, device="cuda").to(dt)
-O = torch.randn(B, N, C, device="cuda").to(dt)
-delta = torch.empty(B * N, dtype=torch.float32, device="cuda")
+delta = torch.zeros(B * N, dtype=torch.float32, device="cuda")
 ws = torch.empty(ops.call("attn_softmax_workspace_bytes", B, N), dtype=torch.uint8, device="cuda")
+code = ops.act_code(dt)
 scale = C ** -0.5
-ev = [torch.cuda.Event(enable_timing=True) for _ in range(4)]
-for it in range(iters):
-    ev[0].record()
-    ops.call("attn_scores_softmax", q, k, P, B, N, C, 3 * C, 3 * C, N * 3 * C, N * 3 * C, scale, ops.act_code(dt), ws, ws.numel())
-    ev[1].record()
-    ops.call("rowdot", dO, O, delta, B * N, C, C, C, ops.act_code(dt))
-    ev[2].record()
-    ops.call("attn_dsoftmax", dO, v, P, delta, dS, B, N, C, C, 3 * C, N * C, N * 3 * C, scale, ops.act_code(dt))
-    ev[3].record()
+
+
+def timed(fn, n=20):
+    for _ in range(3):
+        fn()
     torch.cuda.synchronize()
-    print("iter %d: scores+softmax %.3f ms  rowdot %.3f ms  dsoftmax %.3f ms" % (
-        it, ev[0].elapsed_time(ev[1]), ev[1].elapsed_time(ev[2]), ev[2].elapsed_time(ev[3])), flush=True)
+    a, b = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    a.record()
+    for _ in range(n):
+        fn()
+    b.record()
+    torch.cuda.synchronize()
+    return a.elapsed_time(b) / n
+
+
+t1 = timed(lambda: ops.call("attn_scores_softmax", q, k, P, B, N, C, 3 * C, 3 * C, N * 3 * C, N * 3 * C, scale, code, ws,
+                            ws.numel()))
+t2 = timed(lambda: ops.call("attn_dsoftmax", dO, v, P, delta, dS, B, N, C, C, 3 * C, N * C, N * 3 * C, scale, code))
+fl = 2.0 * B * N * N * C
+print("B %d %s bstat=%s: qk^T+softmax (2 passes) %.3f ms = %.0f TF/s ; dO v^T+dsoftmax %.3f ms = %.0f TF/s (P+dS traffic %.0f GB/s)"
+      % (B, dt, os.environ.get("ODVAE_GEMM_BSTAT", "1"), t1, 2 * fl / t1 * 1e-9, t2, fl / t2 * 1e-9,
+         2.0 * B * N * N * 2 / t2 * 1e-6))

@@ -53,6 +53,8 @@ __device__ __forceinline__ uint32_t mbar_try_wait(uint64_t* bar, uint32_t parity
 #ifndef ODVAE_WAIT_TIMEOUT_NS
 #define ODVAE_WAIT_TIMEOUT_NS 4000000000ull
 #endif
+// (Measured on one box against this loop, round 2: a 5-instruction poll with the deadline test out of line, and polls that
+// sleep 64 / 200 ns in the producer and epilogue warps -- conv, attention and whole-step times all within +-0.5 %.)
 __device__ __forceinline__ void mbar_wait(uint64_t* bar, uint32_t parity) {
   if (mbar_try_wait(bar, parity)) return;
   const uint64_t t0 = globaltimer_ns();

@@ -1,5 +1,7 @@
 // Layout / dtype conversion, weight packing, nearest-2x upsample and small reductions.
 // All memory-bound: 16-byte vector accesses, grids sized in multiples of the SM count.
+#include <mutex>
+
 #include "common.cuh"
 
 namespace odvae {
@@ -658,6 +660,40 @@ int launch_colsum(const void* m, long long rows, int cols, int ld, int act_dtype
   return check_launch("colsum_stage2");
 }
 
+// ---------------------------------------------------------------------------------------------
+// Column sums without any allocation (odvae_colsum_static): the stage-1 partials live in a file-scope device array instead
+// of a caller-provided workspace, for callers that cannot allocate (CUDA-graph capture, serving loops). Every GPU that loads
+// the library holds the array (COLSUM_BLOCKS x ODVAE_COLSUM_STATIC_MAX_COLS floats = 1.16 MiB) until exit. In host code
+// `g_colsum_static_scratch` is only the symbol's host-side stand-in: the device address comes from cudaGetSymbolAddress,
+// looked up once per device with that device current.
+// ---------------------------------------------------------------------------------------------
+static __device__ __align__(256) float g_colsum_static_scratch[COLSUM_BLOCKS * ODVAE_COLSUM_STATIC_MAX_COLS];
+
+static constexpr int STATIC_MAX_DEVICES = 64;
+static float* g_colsum_static_addr[STATIC_MAX_DEVICES] = {};
+static std::mutex g_colsum_static_mutex;
+
+// device address of the scratch array on the CURRENT device (nullptr + last error set on failure)
+static float* colsum_static_scratch() {
+  int dev = -1;
+  cudaError_t e = cudaGetDevice(&dev);
+  if (e != cudaSuccess || dev < 0 || dev >= STATIC_MAX_DEVICES) {
+    set_last_cuda_error(e != cudaSuccess ? e : cudaErrorInvalidDevice, "odvae_colsum_static: cudaGetDevice");
+    return nullptr;
+  }
+  std::lock_guard<std::mutex> lock(g_colsum_static_mutex);
+  if (g_colsum_static_addr[dev] == nullptr) {
+    float* ptr = nullptr;
+    e = cudaGetSymbolAddress(reinterpret_cast<void**>(&ptr), g_colsum_static_scratch);
+    if (e != cudaSuccess || ptr == nullptr) {
+      set_last_cuda_error(e != cudaSuccess ? e : cudaErrorInvalidSymbol,
+                          "odvae_colsum_static: cudaGetSymbolAddress(g_colsum_static_scratch)");
+      return nullptr;
+    }
+    g_colsum_static_addr[dev] = ptr;
+  }
+  return g_colsum_static_addr[dev];
+}
 }  // namespace odvae
 
 using namespace odvae;
@@ -832,6 +868,21 @@ int odvae_add(const void* a, const void* b, void* out, int64_t n, int act_dtype,
     add_kernel<float><<<grid_for(n / 4, 256), 256, 0, st>>>(reinterpret_cast<const float*>(a), reinterpret_cast<const float*>(b), reinterpret_cast<float*>(out), n / 4);
   }
   return check_launch("add_kernel");
+}
+
+int odvae_colsum_static(const void* m, int64_t rows, int cols, int ld, int dtype, float* out, int accumulate, void* stream) {
+  if (rows <= 0 || cols <= 0 || ld < cols) return ODVAE_ERR_SHAPE;
+  if (cols > ODVAE_COLSUM_STATIC_MAX_COLS) {
+    set_last_cuda_error(cudaErrorInvalidValue,
+                        "odvae_colsum_static: cols exceeds ODVAE_COLSUM_STATIC_MAX_COLS (512), the static scratch array "
+                        "cannot hold the partial sums; use odvae_colsum with a workspace");
+    return ODVAE_ERR_WORKSPACE;
+  }
+  float* part = colsum_static_scratch();  // device address of the file-scope array on the current device
+  if (part == nullptr) return ODVAE_ERR_CUDA;
+  // stage 1 writes every partial stage 2 reads ([nblk][cols], both derived from this call's arguments), so nothing in the
+  // array has to start at zero; what an earlier call left behind is simply overwritten or never read
+  return launch_colsum(m, rows, cols, ld, dtype, out, accumulate, part, static_cast<cudaStream_t>(stream), 1.0f);
 }
 
 }  // extern "C"

@@ -354,6 +354,18 @@ int odvae_lpips_level_bwd(const void* f0, const void* f1, const float* w, const 
 size_t odvae_colsum_workspace_bytes(int cols);
 int odvae_colsum(const void* m, int64_t rows, int cols, int ld, int dtype, float* out, int accumulate,
                  void* workspace, size_t ws_bytes, void* stream);
+/* odvae_colsum without a workspace and without any allocation. No counterpart in the reference: added
+ * for callers that cannot call cudaMalloc (code under CUDA-graph capture, serving loops, harnesses that
+ * forbid it). The stage-1 partial sums live in a file-scope `static __device__` array inside the library (592 x
+ * ODVAE_COLSUM_STATIC_MAX_COLS floats = 1.16 MiB, held by every GPU that loads the library until exit); the call performs
+ * no cudaMalloc / cudaFree and calls no allocating library routine. Same kernels, same summation order, same result bits
+ * as odvae_colsum. cols > ODVAE_COLSUM_STATIC_MAX_COLS returns ODVAE_ERR_WORKSPACE (odvae_last_cuda_error() says why).
+ * All calls on one device SHARE the array: calls that may overlap on the GPU (different streams without an ordering
+ * between them, concurrent graph branches) race on it -- order them, or use odvae_colsum with separate workspaces.
+ * Nothing in the array needs clearing between calls (every partial that is read was written by the same call). */
+#define ODVAE_COLSUM_STATIC_MAX_COLS 512
+int odvae_colsum_static(const void* m, int64_t rows, int cols, int ld, int dtype, float* out, int accumulate,
+                        void* stream);
 
 /* ---------------------------------------------------------------------------------------------
  * Upsample: F.interpolate(scale 2, nearest) + Conv2d(k=3, s=1, p=1) (LD model.py:53-57) WITHOUT the upsampled tensor: output

@@ -1,5 +1,6 @@
 // Host side of the GEMM/conv engines: problem description, TMA tensor maps, tile/BN/split choice,
 // launches of the tcgen05 engine (bf16) and of the SIMT validation engine (f32 or bf16).
+#include <cstdio>
 #include <cuda.h>
 #include <cudaTypedefs.h>
 
@@ -64,8 +65,26 @@ static int make_tmap_bf16(CUtensorMap* tm, const OperandView& v, const uint32_t*
   CUresult r = fn(tm, CU_TENSOR_MAP_DATA_TYPE_BFLOAT16, static_cast<cuuint32_t>(v.rank), const_cast<void*>(v.ptr),
                   gdim, gstr, bx, es, CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_128B,
                   CU_TENSOR_MAP_L2_PROMOTION_L2_256B, CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
+  if (r == CUDA_ERROR_INVALID_CONTEXT) {
+    // a thread that has not touched the CUDA runtime yet (e.g. the first node an autograd worker thread runs): the driver
+    // entry point above needs a current context, which any runtime call binds
+    cudaFree(nullptr);
+    r = fn(tm, CU_TENSOR_MAP_DATA_TYPE_BFLOAT16, static_cast<cuuint32_t>(v.rank), const_cast<void*>(v.ptr), gdim, gstr, bx,
+           es, CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_128B, CU_TENSOR_MAP_L2_PROMOTION_L2_256B,
+           CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
+  }
   if (r != CUDA_SUCCESS) {
-    set_last_cuda_error(cudaErrorInvalidValue, "cuTensorMapEncodeTiled failed");
+    static thread_local char msg[320];
+    int n = snprintf(msg, sizeof(msg), "cuTensorMapEncodeTiled failed (CUresult %d): rank %d ptr %p dims", static_cast<int>(r),
+                     v.rank, v.ptr);
+    for (int i = 0; i < v.rank && n < static_cast<int>(sizeof(msg)); ++i)
+      n += snprintf(msg + n, sizeof(msg) - n, " %lld", static_cast<long long>(v.dims[i]));
+    if (n < static_cast<int>(sizeof(msg))) n += snprintf(msg + n, sizeof(msg) - n, " strides");
+    for (int i = 0; i < v.rank && n < static_cast<int>(sizeof(msg)); ++i)
+      n += snprintf(msg + n, sizeof(msg) - n, " %lld", static_cast<long long>(v.strides[i]));
+    if (n < static_cast<int>(sizeof(msg))) n += snprintf(msg + n, sizeof(msg) - n, " box");
+    for (int i = 0; i < v.rank && n < static_cast<int>(sizeof(msg)); ++i) n += snprintf(msg + n, sizeof(msg) - n, " %u", box[i]);
+    set_last_cuda_error(cudaErrorInvalidValue, msg);
     return ODVAE_ERR_CUDA;
   }
   return ODVAE_OK;

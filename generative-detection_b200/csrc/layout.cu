@@ -78,6 +78,49 @@ __global__ void rescale_nhwc_kernel(const float* __restrict__ src, const float* 
   }
 }
 
+// Thin-channel 3x3 (stride 1, pad 1) im2col: src NCHW fp32 [B,C,H,W] with C <= 4 -> col NHWC [B,H,W,64] 16-bit,
+// col[b,y,x, t*4 + c] = scale * src[b,c, y + s*(t/3 - 1), x + s*(t%3 - 1)] (zero outside the image; columns 36.. and
+// channels >= C zero), s = +1 for a forward / weight-gradient operand, -1 for the data-gradient operand (dy seen from the
+// input pixel). The 3-channel edge convs (encoder.conv_in, decoder.conv_out) then run as ONE K = 64 GEMM step per tile instead
+// of nine 64-channel-padded taps. Eight lanes share a pixel: lane j writes the 16-byte chunk of taps 2j, 2j+1, so a warp
+// stores 512 contiguous bytes.
+template <typename T>
+__global__ void im2col3_thin_kernel(const float* __restrict__ src, T* __restrict__ col, int C, int H, int W, int sgn,
+                                    float scale) {
+  // grid (x chunks, y / 4, b): no index divisions (a flat 64-bit index cost more instructions than the loads and stores), and
+  // four rows per thread so that 24 loads are in flight per thread
+  constexpr int ROWS = 4;
+  const int q = blockIdx.x * blockDim.x + threadIdx.x;
+  const int x = q >> 3, j = q & 7;
+  if (x >= W) return;
+  const int y0 = blockIdx.y * ROWS, b = blockIdx.z;
+  const long long HW = static_cast<long long>(H) * W;
+  const float* img = src + static_cast<long long>(b) * C * HW;
+  float f[ROWS][8];
+#pragma unroll
+  for (int r = 0; r < ROWS; ++r) {
+#pragma unroll
+    for (int h = 0; h < 2; ++h) {
+      const int t = 2 * j + h;
+      const int ty = t / 3, tx = t - 3 * ty;
+      const int yy = y0 + r + sgn * (ty - 1), xx = x + sgn * (tx - 1);
+      const bool ok = t < 9 && yy >= 0 && yy < H && xx >= 0 && xx < W;
+      const float* px = img + static_cast<long long>(yy) * W + xx;
+#pragma unroll
+      for (int c = 0; c < 4; ++c) f[r][4 * h + c] = (ok && c < C) ? __ldg(px + c * HW) : 0.0f;
+    }
+  }
+#pragma unroll
+  for (int r = 0; r < ROWS; ++r) {
+    if (y0 + r >= H) break;
+    __align__(16) T v[8];
+#pragma unroll
+    for (int k = 0; k < 8; ++k) v[k] = from_f32<T>(scale * f[r][k]);
+    *reinterpret_cast<uint4*>(col + ((static_cast<long long>(b) * H + y0 + r) * W + x) * 64 + 8 * j) =
+        *reinterpret_cast<const uint4*>(v);
+  }
+}
+
 template <typename T>
 __global__ void nhwc_to_nchw_kernel(const T* __restrict__ src, float* __restrict__ dst, int B, int C, int HW,
                                     int Cpad) {
@@ -734,6 +777,22 @@ int odvae_rescale_nhwc(const float* src, const float* minmax, float* dst_nchw, v
     rescale_nhwc_kernel<float><<<grid_for(total, 256), 256, 0, st>>>(src, minmax, dst_nchw, reinterpret_cast<float*>(dst_nhwc), B, C, H * W, Cpad);
   }
   return check_launch("rescale_nhwc_kernel");
+}
+
+int odvae_im2col3x3_thin(const float* src, void* col, int B, int C, int H, int W, int flip, float scale, int act_dtype,
+                         void* stream) {
+  if (B <= 0 || C <= 0 || C > 4 || H <= 0 || W <= 0 || H > 4 * 65535 || B > 65535) return ODVAE_ERR_SHAPE;
+  cudaStream_t st = static_cast<cudaStream_t>(stream);
+  const int sgn = flip ? -1 : 1;
+  const dim3 grid(static_cast<unsigned>((static_cast<long long>(W) * 8 + 255) / 256), static_cast<unsigned>((H + 3) / 4),
+                  static_cast<unsigned>(B));
+  if (act_dtype == ODVAE_BF16)
+    im2col3_thin_kernel<bf16><<<grid, 256, 0, st>>>(src, reinterpret_cast<bf16*>(col), C, H, W, sgn, scale);
+  else if (act_dtype == ODVAE_F16)
+    im2col3_thin_kernel<f16><<<grid, 256, 0, st>>>(src, reinterpret_cast<f16*>(col), C, H, W, sgn, scale);
+  else
+    return ODVAE_ERR_SHAPE;
+  return check_launch("im2col3_thin_kernel");
 }
 
 int odvae_nhwc_to_nchw(const void* src, float* dst, int B, int C, int H, int W, int Cpad, int act_dtype, void* stream) {

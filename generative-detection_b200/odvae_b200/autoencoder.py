@@ -239,7 +239,10 @@ class PoseAutoencoder(_Base):
     def _rescale(self, x):  # AE.py:434-436, min/max over the whole batch tensor
         if x.is_cuda:
             f = self.fmt
-            return ops.rescale_minmax(x, nhwc=(ops.cpad(x.shape[1]), f.fwd, f.label(f.fwd)) if x.dim() == 4 else None)
+            # (the NHWC copy for encoder.conv_in is only wanted where that conv takes the generic 64-channel-padded path)
+            thin = ops.THIN_CONV and f.fwd != ops.F32 and x.dim() == 4 and x.shape[1] <= 4 and not x.requires_grad
+            return ops.rescale_minmax(x, nhwc=(ops.cpad(x.shape[1]), f.fwd, f.label(f.fwd)) if x.dim() == 4 and not thin
+                                      else None)
         return 2. * (x - x.min()) / (x.max() - x.min()) - 1.
 
     def check_overflow(self):

@@ -208,8 +208,13 @@ class Encoder(nn.Module):
     def forward_nhwc(self, x):
         """x: NCHW fp32 image -> NHWC activations [B,h,w,pad64(out_channels)]."""
         _check_cuda(x)
-        h = ops.ToNHWC.apply(x, ops.cpad(self.in_channels), self.compute_dtype, getattr(self, "gscale", None))
-        h = self.conv_in(h, need_dx=x.requires_grad)
+        spec = self.conv_in.spec
+        B, C, H, W = x.shape
+        if not x.requires_grad and spec.fmt is not None and ops.thin_conv_ok(spec, spec.fmt.fwd, B, H, W, spec.coutp, C):
+            h = ops.ThinConvIn.apply(x, self.conv_in.weight, self.conv_in.bias, spec)
+        else:
+            h = ops.ToNHWC.apply(x, ops.cpad(self.in_channels), self.compute_dtype, getattr(self, "gscale", None))
+            h = self.conv_in(h, need_dx=x.requires_grad)
         for i_level in range(self.num_resolutions):
             lvl = self.down[i_level]
             for i_block in range(self.num_res_blocks):

@@ -702,12 +702,16 @@ class Conv(torch.autograd.Function):
         ctx.spec, ctx.out_nchw, ctx.need_dx = spec, out_nchw, need_dx
         ctx.fmt = format_of(x, spec)
         ctx.save_for_backward(x, w, b)
+        B, H, W, _ = x.shape
+        ctx.thin = out_nchw and thin_conv_ok(spec, ctx.fmt.grad, B, H, W, spec.cinp, spec.cout)
         return conv_fwd_raw(x, spec, w, b, out_nchw=out_nchw, gn_stats=not out_nchw)
 
     @staticmethod
     def backward(ctx, dy):
         x, w, b = ctx.saved_tensors
         spec, fmt = ctx.spec, ctx.fmt
+        if ctx.thin:
+            return Conv._thin_out_backward(ctx, dy, x, w, b)
         if ctx.out_nchw:  # dec_obj gradient arrives NCHW fp32 (masked-L1 backward): bring it to NHWC, times the domain scale
             dy = nchw_to_nhwc_raw(_c(dy.float()), cpad(spec.cout), fmt.grad, scale=gs_of(spec), label=x.dtype)
         else:
@@ -718,6 +722,118 @@ class Conv(torch.autograd.Function):
             dx = conv_dgrad_raw(dy, spec, w, x.shape[1:3])
         dw, db = conv_wgrad_raw(grad_operand(x, fmt), dy, spec, w, b)
         return dx, dw, db, None, None, None
+
+    @staticmethod
+    def _thin_out_backward(ctx, dy, x, w, b):
+        """decoder.conv_out (Cout <= 4, NCHW fp32 result): the dec_obj gradient [B,C,H,W] fp32 becomes ONE 64-column operand
+        col[q, t*4 + co] = gs * dy[co, q - off_t]; dx = col Wd (1x1 forward), (dWd, dbd) = 1x1 weight gradient of (x, col):
+        dw[co, i, t] = dWd[t*4 + co, i], db[co] = dbd[4*4 + co] (the centre tap's column sum)."""
+        spec, fmt = ctx.spec, ctx.fmt
+        g = fmt.grad
+        C = spec.cout
+        B, H, W, _ = x.shape
+        col = thin_im2col_raw(_c(dy.float()), g, flip=True, scale=gs_of(spec), label=x.dtype)
+        dx = None
+        if ctx.need_dx and ctx.needs_input_grad[0] and _PROBE[0] == 0:
+            wd = spec.cache.get(("thin_out_d", g), (w,), lambda old: _thin_weight(w, g, True, old))
+            dx = torch.empty(B, H, W, spec.cinp, dtype=col.dtype, device=x.device)
+            call("conv2d_fwd", col, wd, None, None, dx, B, H, W, THIN_K, spec.cinp, spec.cin, CONV_1x1, g, g, IMPL_TC, 0)
+        dw, dw_direct = _new_grad(w)
+        db, db_direct = (None, True) if b is None else _new_grad(b)
+        dwp = torch.empty(THIN_K, spec.cin, dtype=torch.float32, device=w.device)
+        dbp = torch.empty(THIN_K, dtype=torch.float32, device=w.device)
+        _wgrad_1x1(grad_operand(x, fmt), col, spec.cin, THIN_K, g, 1.0 / gs_of(spec), dwp, dbp)
+        dw.copy_(dwp.view(16, 4, spec.cin)[:9, :C].permute(1, 2, 0).reshape(dw.shape))
+        if db is not None:
+            db.copy_(dbp.view(16, 4)[4, :C])
+        return dx, _ret(dw, dw_direct), _ret(db, db_direct), None, None, None
+
+
+# ------------------------------------------------------------------------------------------------
+# Thin edge convs: encoder.conv_in (3 -> 128, LD model.py:383-387) and the backward of decoder.conv_out (128 -> 3,
+# LD model.py:529-533). Through the generic path the 3 channels are padded to a 64-channel tile and every one of the 9 taps
+# costs a full K = 64 GEMM step (conv_in weight gradient 1.0 ms, conv_out dgrad + wgrad 2.5 ms at batch 64, 256x256: 21x padded
+# FLOPs, and the weight gradients re-read dy once per filter row). Here the thin side is expanded once by
+# odvae_im2col3x3_thin to 9 taps x 4 channels = 36 of 64 columns and the conv is ONE K = 64 step of the 1x1 path:
+# y = col W1, dW1 = dy^T col, and for conv_out dx = col(dy) Wd, dWd = col(dy)^T x -- all HBM-bound (0.48 / 1.75 ms).
+# ------------------------------------------------------------------------------------------------
+THIN_CONV = os.environ.get("ODVAE_THIN_CONV", "1") != "0"
+THIN_K = 64
+
+
+def thin_conv_ok(spec, code, B, H, W, wide_p, thin_c):
+    return (THIN_CONV and spec.geom == CONV_3x3_S1 and thin_c <= 4 and code != F32 and
+            conv_impl(code, B, H, W, THIN_K, wide_p, CONV_1x1) == IMPL_TC)
+
+
+def thin_im2col_raw(x, code, flip=False, scale=1.0, label=None):
+    """NCHW fp32 [B,C<=4,H,W] -> [B,H,W,64] of format `code`, column t*4 + c = scale * x[c] shifted by tap t (flip: by -t)."""
+    B, C, H, W = x.shape
+    col = torch.empty(B, H, W, THIN_K, dtype=buf_dtype(code, label), device=x.device)
+    call("im2col3x3_thin", x, col, B, C, H, W, 1 if flip else 0, float(scale), code)
+    return col
+
+
+def _thin_weight(w, code, transpose, old=None):
+    """Packed 1x1 weight [wide][64] over the im2col columns. conv_in (transpose False): w [wide, C, 3, 3], column t*4 + c =
+    w[o, c, t]. conv_out data gradient (transpose True): w [C, wide, 3, 3], column t*4 + co = w[co, i, t]. `old`: the previous
+    packed copy, rewritten in place (captured CUDA graphs keep reading that buffer; ParamCache / refresh_param_caches)."""
+    wd = w.detach().float()
+    C = wd.shape[0] if transpose else wd.shape[1]
+    wide = wd.shape[1] if transpose else wd.shape[0]
+    w1 = torch.zeros(wide, 16, 4, dtype=torch.float32, device=w.device)
+    w1[:, :9, :C] = (wd.permute(1, 2, 3, 0) if transpose else wd.permute(0, 2, 3, 1)).reshape(wide, 9, C)
+    return pack_weight(w1.view(wide, THIN_K, 1, 1), CONV_1x1, cpad(wide), THIN_K, 0, code, old)
+
+
+def _wgrad_1x1(x, dy, cin, cout, g, out_scale, dw, db):
+    B, H, W, CinP = x.shape
+    CoutP = dy.shape[-1]
+    impl = conv_impl(g, B, H, W, CinP, CoutP, CONV_1x1)
+    nbytes = call("conv2d_wgrad_workspace_bytes", B, H, W, CinP, CoutP, CONV_1x1, impl)
+    ws = workspace(nbytes, x.device, "wgrad")
+    call("conv2d_wgrad", x, dy, dw, db, B, H, W, CinP, CoutP, cin, cout, CONV_1x1, g, impl, 0, float(out_scale), ws,
+         ws.numel())
+
+
+class ThinConvIn(torch.autograd.Function):
+    """x: NCHW fp32 image (no gradient wanted) -> NHWC [B,H,W,coutp] in the spec's forward format (+ GroupNorm statistics)."""
+
+    @staticmethod
+    def forward(ctx, x, w, b, spec):
+        fmt = spec.fmt
+        op = fmt.fwd
+        B, C, H, W = x.shape
+        col = thin_im2col_raw(_c(x.float()), op, label=fmt.label(op))
+        w1 = spec.cache.get(("thin_in", op), (w,), lambda old: _thin_weight(w, op, False, old))
+        y = torch.empty(B, H, W, spec.coutp, dtype=col.dtype, device=x.device)
+        nbytes = 0
+        if FUSE_GN_STATS and spec.coutp == spec.cout:
+            nbytes = call("conv2d_fwd_gnstats_workspace_bytes", B, H, W, THIN_K, spec.coutp, CONV_1x1, GROUPS)
+        if nbytes:
+            ws = workspace(nbytes, x.device, "gnconv")
+            stats = torch.empty(B, GROUPS, 2, dtype=torch.float32, device=x.device)
+            call("conv2d_fwd_gnstats", col, w1, spec.bias(b), None, y, stats, B, H, W, THIN_K, spec.coutp, CONV_1x1,
+                 GROUPS, GN_EPS, op, op, ws, ws.numel())
+            y._odvae_gn_stats = stats
+        else:
+            call("conv2d_fwd", col, w1, spec.bias(b), None, y, B, H, W, THIN_K, spec.coutp, spec.cout, CONV_1x1, op, op,
+                 IMPL_TC, 0)
+        ctx.spec, ctx.C = spec, C
+        ctx.save_for_backward(grad_operand(col, fmt), w, b)
+        return y
+
+    @staticmethod
+    def backward(ctx, dy):
+        col, w, b = ctx.saved_tensors
+        spec, C = ctx.spec, ctx.C
+        g = spec.fmt.grad
+        dw, dw_direct = _new_grad(w)
+        db, db_direct = (None, True) if b is None else _new_grad(b)
+        dw1 = torch.empty(spec.cout, THIN_K, dtype=torch.float32, device=w.device)
+        _wgrad_1x1(col, _c(dy), THIN_K, spec.cout, g, 1.0 / gs_of(spec), dw1, db)
+        dw.copy_(dw1.view(spec.cout, 16, 4)[:, :9, :C].permute(0, 2, 1).reshape(dw.shape))
+        return None, _ret(dw, dw_direct), _ret(db, db_direct), None
 
 
 # ------------------------------------------------------------------------------------------------

@@ -320,6 +320,15 @@ int odvae_rescale(const float* src, float* dst, int64_t n, const float* minmax, 
 int odvae_rescale_nhwc(const float* src, const float* minmax, float* dst_nchw, void* dst_nhwc, int B, int C, int H, int W,
                        int Cpad, int act_dtype, void* stream);
 
+/* Thin-channel 3x3 / stride 1 / pad 1 im2col for the 3-channel edge convs (encoder.conv_in, LD model.py:383-387; the
+ * backward of decoder.conv_out, LD model.py:529-533): src NCHW fp32 [B,C,H,W], C <= 4 -> col NHWC act_dtype [B,H,W,64] with
+ * col[.., t*4 + c] = scale * src[b, c, y + s*(t/3-1), x + s*(t%3-1)], s = -1 when flip (data-gradient operand: dy as seen
+ * from the input pixel), zero outside the image, in channels >= C and in columns 36..63. The conv then is a 1x1 conv /
+ * GEMM over K = 64: y = col W1 with W1[co][t*4+c] = w[co][c][t]; dx = col(dy, flip) Wd with Wd[ci][t*4+co] = w[co][ci][t];
+ * dW from the 1x1 weight gradient of (col, dy) resp. (x, col(dy, flip)). 16-bit formats only. */
+int odvae_im2col3x3_thin(const float* src, void* col, int B, int C, int H, int W, int flip, float scale, int act_dtype,
+                         void* stream);
+
 /* Pose MLP activations on fp32 [n] (pose_decoder.py:82-94 Tanh, pose_encoder.py:82-98 SiLU):
  * act = 1 tanh, 2 silu.  bwd: dx = dy * act'(x) with x the pre-activation. */
 int odvae_act_fwd(const float* x, float* y, int64_t n, int act, void* stream);

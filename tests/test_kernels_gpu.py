@@ -300,3 +300,78 @@ def test_upsample_conv_phase_decomposition_against_torch(dtype, tol, B, H, C, Co
     assert rel(dx_n, xr.grad) < tol
     assert rel(up.conv.weight.grad, wr.grad) < tol
     assert rel(up.conv.bias.grad, br.grad) < tol
+
+
+@pytest.mark.parametrize("dtype,tol", [(torch.float16, 3e-3), (torch.bfloat16, 2e-2), ("mixed", 2e-2)])
+@pytest.mark.parametrize("B,H,W", [(2, 64, 64), (3, 32, 64), (1, 256, 256)])
+def test_thin_edge_convs_against_torch(dtype, tol, B, H, W, monkeypatch):
+    """encoder.conv_in (3 -> 128) forward / weight + bias gradient and decoder.conv_out (128 -> 3) input / weight / bias
+    gradient through the thin path (odvae_im2col3x3_thin + ONE K = 64 step of the 1x1 tcgen05 path) against torch fp32 on
+    the 16-bit-rounded operands, and against the generic 64-channel-padded path of the same layers."""
+    import torch.nn.functional as F
+    from odvae_b200 import modules as M
+    from odvae_b200.lib import CONV_3x3_S1
+    torch.backends.cudnn.allow_tf32 = False
+    torch.backends.cuda.matmul.allow_tf32 = False
+    g = torch.Generator().manual_seed(7 * B + H)
+    fmt = ops.format_for(dtype)
+    rel = lambda a, b: float((a.detach().float() - b.detach().float()).norm() / b.detach().float().norm())
+    r16 = lambda t, code: (t.half() if code == ops.F16 else t.bfloat16()).float()
+    # (mixed mode: the weight-gradient operand is the bf16 cast of the fp16 forward copy -- two roundings, 1.4e-3)
+    wtol = 3e-3 if dtype == "mixed" else 1e-3
+
+    # ---- conv_in ----
+    conv = M.Conv2d(3, 128, 3, CONV_3x3_S1).cuda()
+    ops.assign_format(conv, dtype)
+    x = (torch.rand(B, 3, H, W, generator=g) * 2 - 1).cuda()
+    wy = torch.randn(B, 128, H, W, generator=g).cuda()
+    dy = ops.nchw_to_nhwc_raw(wy, 128, fmt.grad, label=fmt.label(fmt.grad))
+    assert ops.thin_conv_ok(conv.spec, fmt.fwd, B, H, W, 128, 3)
+    y = ops.ThinConvIn.apply(x, conv.weight, conv.bias, conv.spec)
+    y.backward(dy)
+    torch.cuda.synchronize()
+    xr = r16(x, fmt.fwd)
+    wr = r16(conv.weight.detach(), fmt.fwd).requires_grad_(True)
+    br = conv.bias.detach().clone().requires_grad_(True)
+    yr = F.conv2d(xr, wr, br, padding=1)
+    assert rel(ops.nhwc_to_nchw_raw(y.detach(), 128, fmt.fwd), yr) < tol
+    stats = getattr(y, "_odvae_gn_stats", None)
+    if stats is not None:  # GroupNorm statistics from the epilogue: (mean, rstd) per (image, group)
+        yv = ops.nhwc_to_nchw_raw(y.detach(), 128, fmt.fwd).view(B, 32, -1)
+        assert float((stats[..., 0] - yv.mean(-1)).abs().max()) < 1e-3
+    # weight gradient: contraction of the 16-bit col operand (gradient format) with the 16-bit dy
+    xg = r16(x, fmt.grad)
+    wg = conv.weight.detach().clone().requires_grad_(True)
+    F.conv2d(xg, wg, None, padding=1).backward(r16(wy, fmt.grad))
+    assert rel(conv.weight.grad, wg.grad) < wtol and rel(conv.bias.grad, r16(wy, fmt.grad).sum(dim=(0, 2, 3))) < 1e-3
+    thin_dw = conv.weight.grad.clone()
+    conv.weight.grad = conv.bias.grad = None
+    h = ops.ToNHWC.apply(x, 64, dtype, None)
+    conv(h, need_dx=False).backward(dy)
+    assert rel(thin_dw, conv.weight.grad) < wtol
+
+    # ---- conv_out ----
+    conv = M.Conv2d(128, 3, 3, CONV_3x3_S1).cuda()
+    ops.assign_format(conv, dtype)
+    xs = torch.randn(B, 128, H, W, generator=g).cuda()
+    dyo = torch.randn(B, 3, H, W, generator=g).cuda()
+    res = {}
+    for thin in (True, False):
+        monkeypatch.setattr(ops, "THIN_CONV", thin)
+        xh = ops.nchw_to_nhwc_raw(xs, 128, fmt.fwd, label=fmt.label(fmt.fwd)).requires_grad_(True)
+        conv.weight.grad = conv.bias.grad = None
+        yo = conv(xh, out_nchw=True)
+        yo.backward(dyo)
+        torch.cuda.synchronize()
+        res[thin] = (yo.detach(), ops.nhwc_to_nchw_raw(xh.grad, 128, fmt.grad), conv.weight.grad.clone(), conv.bias.grad.clone())
+    xr = r16(xs, fmt.fwd).requires_grad_(True)
+    wr = r16(conv.weight.detach(), fmt.grad).requires_grad_(True)
+    yr = F.conv2d(xr, wr, conv.bias.detach(), padding=1)
+    yr.backward(r16(dyo, fmt.grad))
+    wg = conv.weight.detach().clone().requires_grad_(True)
+    F.conv2d(r16(xs, fmt.grad), wg, None, padding=1).backward(r16(dyo, fmt.grad))
+    for thin in (True, False):
+        yo, dx, dw, db = res[thin]
+        assert rel(dx, xr.grad) < tol, thin
+        assert rel(dw, wg.grad) < wtol and rel(db, r16(dyo, fmt.grad).sum(dim=(0, 2, 3))) < 1e-3, thin
+    assert torch.equal(res[True][0], res[False][0])  # the forward is the same kernel either way

@@ -171,6 +171,11 @@ tc_engine_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant_
   __syncthreads();
   tc_fence_after();
   const uint32_t tmem_base = *tmem_slot;
+  // Programmatic dependent launch (tc_engine_inst.cuh): everything above overlapped the previous kernel's tail. Let the next
+  // kernel of the stream be scheduled as SMs free up, then wait until the previous grid has completed and its writes are visible
+  // (both are no-ops when the launch did not carry the attribute).
+  asm volatile("griddepcontrol.launch_dependents;" ::: "memory");
+  asm volatile("griddepcontrol.wait;" ::: "memory");
 
   if (warp == 0) {
     // ============================ TMA producer ============================

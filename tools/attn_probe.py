@@ -44,3 +44,14 @@ fl = 2.0 * B * N * N * C
 print("B %d %s bstat=%s: qk^T+softmax (2 passes) %.3f ms = %.0f TF/s ; dO v^T+dsoftmax %.3f ms = %.0f TF/s (P+dS traffic %.0f GB/s)"
       % (B, dt, os.environ.get("ODVAE_GEMM_BSTAT", "1"), t1, 2 * fl / t1 * 1e-9, t2, fl / t2 * 1e-9,
          2.0 * B * N * N * 2 / t2 * 1e-6))
+
+# ---- the plain GEMMs that stream P / dS from HBM: O = P v, dv = P^T dO, dq = dS k, dk = dS^T q ----
+O = torch.empty(B, N, C, dtype=dt, device="cuda")
+dqkv = torch.empty(B, N, 3 * C, dtype=dt, device="cuda")
+t_pv = timed(lambda: ops.gemm_raw(P, v, O, N, C, N, B, N, 3 * C, C, N * N, N * 3 * C, N * C, False, True, code=code))
+t_dv = timed(lambda: ops.gemm_raw(P, dO, dqkv[..., 2 * C:], N, C, N, B, N, C, 3 * C, N * N, N * C, N * 3 * C, True, True, code=code))
+t_dq = timed(lambda: ops.gemm_raw(dS, k, dqkv[..., :C], N, C, N, B, N, 3 * C, 3 * C, N * N, N * 3 * C, N * 3 * C, False, True, code=code))
+t_dk = timed(lambda: ops.gemm_raw(dS, q, dqkv[..., C:2 * C], N, C, N, B, N, 3 * C, 3 * C, N * N, N * 3 * C, N * 3 * C, True, True, code=code))
+gb = B * N * N * 2 * 1e-9
+print("prefetch=%s: P v %.3f ms (%.0f TF/s, %.2f TB/s) | P^T dO %.3f | dS k %.3f | dS^T q %.3f ms"
+      % (os.environ.get("ODVAE_GEMM_PREFETCH", "8"), t_pv, fl / t_pv * 1e-9, gb / t_pv, t_dv, t_dq, t_dk))

@@ -33,7 +33,12 @@ template <> __device__ __forceinline__ float to_f32<f16>(f16 v) { return __half2
 template <typename T> __device__ __forceinline__ T from_f32(float v);
 // fp16 stores saturate (|v| > 65504 -> +-65504) instead of producing inf
 __device__ __forceinline__ float sat_f16(float v) { return fminf(fmaxf(v, -65504.0f), 65504.0f); }
-template <> __device__ __forceinline__ f16 from_f32<f16>(float v) { return __float2half_rn(sat_f16(v)); }
+// (one F2FP.SATFINITE instruction: |v| > 65504 and inf -> +-65504; the min/max pair of sat_f16 cost 2 more per value)
+template <> __device__ __forceinline__ f16 from_f32<f16>(float v) {
+  uint16_t r;
+  asm("cvt.rn.satfinite.f16.f32 %0, %1;" : "=h"(r) : "f"(v));
+  return __ushort_as_half(r);
+}
 template <> __device__ __forceinline__ float from_f32<float>(float v) { return v; }
 template <> __device__ __forceinline__ bf16 from_f32<bf16>(float v) { return __float2bfloat16_rn(v); }
 
@@ -46,8 +51,9 @@ __device__ __forceinline__ float2 unpack_bf16x2(uint32_t v) {
   return __bfloat1622float2(h);
 }
 __device__ __forceinline__ uint32_t pack_f16x2(float lo, float hi) {
-  __half2 h = __floats2half2_rn(sat_f16(lo), sat_f16(hi));
-  return *reinterpret_cast<uint32_t*>(&h);
+  uint32_t r;
+  asm("cvt.rn.satfinite.f16x2.f32 %0, %1, %2;" : "=r"(r) : "f"(hi), "f"(lo));
+  return r;
 }
 __device__ __forceinline__ float2 unpack_f16x2(uint32_t v) {
   __half2 h = *reinterpret_cast<__half2*>(&v);

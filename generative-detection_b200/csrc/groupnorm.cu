@@ -332,16 +332,60 @@ __global__ void gn_bwd_finalize_b_kernel(const float* __restrict__ AB, float* __
   dgamma[c] = accumulate ? dgamma[c] + bb : bb;
 }
 
+// The same sums inside the apply kernels (one launch less per GroupNorm backward: 67 per train step): the first
+// ceil(C / 32) CTAs of the grid (in linear order) each own 32 channels; warp w adds images w, w + 8, ... and warp 0 combines
+// the eight partials in a fixed order before the CTA starts on its share of dx. AB == nullptr: nothing to do.
+__device__ __forceinline__ void gn_bwd_param_grads(const float* __restrict__ AB, float* __restrict__ dgamma,
+                                                   float* __restrict__ dbeta, int B, int C, int accumulate,
+                                                   float scale) {
+  if (AB == nullptr) return;
+  const int nblk = gridDim.x * gridDim.y, blk = blockIdx.y * gridDim.x + blockIdx.x;
+  const int ncb = (C + 31) / 32;
+  if (blk >= ncb) return;  // block-uniform
+  __shared__ float pg[8][32][2];
+  const int lane = threadIdx.x & 31, w = threadIdx.x >> 5;  // GN_THREADS = 256 -> 8 warps
+  for (int cb = blk; cb < ncb; cb += nblk) {
+    const int c = cb * 32 + lane;
+    float a = 0.0f, bb = 0.0f;
+    if (c < C) {
+      for (int b = w; b < B; b += 8) {
+        const float2 v = __ldg(reinterpret_cast<const float2*>(AB) + static_cast<long long>(b) * C + c);
+        a += v.x;
+        bb += v.y;
+      }
+    }
+    pg[w][lane][0] = a;
+    pg[w][lane][1] = bb;
+    __syncthreads();
+    if (w == 0 && c < C) {
+      a = 0.0f;
+      bb = 0.0f;
+#pragma unroll
+      for (int k = 0; k < 8; ++k) {
+        a += pg[k][lane][0];
+        bb += pg[k][lane][1];
+      }
+      a *= scale;
+      bb *= scale;
+      dbeta[c] = accumulate ? dbeta[c] + a : a;
+      dgamma[c] = accumulate ? dgamma[c] + bb : bb;
+    }
+    __syncthreads();
+  }
+}
+
 // dx = c1 * dy' + c2 * x + c3 (+ dx_add); one channel vector per thread for the whole loop (see gn_apply_kernel)
 template <typename T, typename TG>
 __global__ void __launch_bounds__(GN_THREADS, GN_BWD_MINB)
 gn_bwd_apply_kernel(const T* __restrict__ x, const TG* __restrict__ dy, const TG* __restrict__ dx_add,
                     const float* __restrict__ stats, const float* __restrict__ gamma, const float* __restrict__ beta,
                     const float* __restrict__ coef, TG* __restrict__ dx, int HW, int C, int G, int silu,
-                    int* __restrict__ overflow) {
+                    int* __restrict__ overflow, const float* __restrict__ AB, float* __restrict__ dgamma,
+                    float* __restrict__ dbeta, int B, int accumulate, float pscale) {
   constexpr int V = VecN<T>::V;
   constexpr bool kCheck = std::is_same<TG, f16>::value;  // fp16 gradients: a saturated dy means the gradient scale is too large
   bool sat = false;
+  gn_bwd_param_grads(AB, dgamma, dbeta, B, C, accumulate, pscale);
   const int b = blockIdx.y;
   const int cpg = C / G;
   const int cv = C / V;
@@ -399,6 +443,280 @@ gn_bwd_apply_kernel(const T* __restrict__ x, const TG* __restrict__ dy, const TG
     }
   }
   if (kCheck && sat && overflow != nullptr) overflow[1] = 1;
+}
+
+// ------------------------------------------------------------------------------------------------------------------
+// Packed-half2 backward for fp16 activations + fp16 gradients (the timed mode). The fp32 kernels above spend ~14 (reduce)
+// and ~18 (apply) instructions per element -- conversions, a scalar MUFU and scalar FMAs -- and run at 0.67-0.69 of the
+// HBM copy peak: issue-bound, not memory-bound (round-2 launch list). Here every elementwise step works on TWO channels per
+// instruction (HFMA2 / HMNMX2, tanh.approx.f16x2 = one MUFU per pair) and only the sums are fp32:
+//   xc = x - fp16(mean)              exact where it matters (Sterbenz), so no cancellation is left for the constants
+//   xh = xc * rstd + (fp16(mean) - mean) * rstd
+//   uh = xh * gamma/2 + beta/2 = u / 2,  t = tanh(uh),  w = 1 - t^2,  q = t + uh w,  silu'(u) = 0.5 + 0.5 q
+// Reduce: d' / 64 and d' xh / 64 are summed in half2 over 8 pixels (the 1/64 keeps eight near-saturated terms finite),
+// then flushed into fp32 accumulators; the partial sums leave the kernel multiplied by 64 again.
+// Apply: dx = c1 d' + (k2 xh + k3) (+ dx_add), k2 = -rstd S2/n, k3 = -rstd S1/n (the c2 x + c3 of the fp32 kernel
+// rewritten on xh so that no large terms cancel in fp16), clamped to +-65504 like every fp16 store of this library.
+// ------------------------------------------------------------------------------------------------------------------
+#ifndef GN_H2
+#define GN_H2 1
+#endif
+#ifndef GN_FUSE_PGRAD
+#define GN_FUSE_PGRAD 1
+#endif
+#ifndef GN_H2_RED_U
+#define GN_H2_RED_U 4
+#endif
+#ifndef GN_H2_RED_MINB
+#define GN_H2_RED_MINB 2
+#endif
+#ifndef GN_H2_BWD_MINB
+#define GN_H2_BWD_MINB 3
+#endif
+#ifndef GN_H2_BWD_U
+#define GN_H2_BWD_U 2
+#endif
+
+__device__ __forceinline__ __half2 h2_tanh(__half2 v) {
+  uint32_t r, a = *reinterpret_cast<uint32_t*>(&v);
+  asm("tanh.approx.f16x2 %0, %1;" : "=r"(r) : "r"(a));
+  return *reinterpret_cast<__half2*>(&r);
+}
+__device__ __forceinline__ __half2 h2_bits(uint32_t v) { return *reinterpret_cast<__half2*>(&v); }
+__device__ __forceinline__ uint32_t h2_u32(__half2 v) { return *reinterpret_cast<uint32_t*>(&v); }
+
+// per-thread constants of one channel pair
+struct GnH2Const {
+  __half2 muh, rs, k0, hg, hb;
+};
+__device__ __forceinline__ void gn_h2_consts(GnH2Const (&k)[4], const float* __restrict__ stats,
+                                             const float* __restrict__ gamma, const float* __restrict__ beta, int b,
+                                             int c0, int cpg, int G) {
+#pragma unroll
+  for (int j = 0; j < 4; ++j) {
+    float muh[2], rs[2], k0[2], hg[2], hb[2];
+#pragma unroll
+    for (int e = 0; e < 2; ++e) {
+      const int c = c0 + 2 * j + e;
+      const int g = c / cpg;
+      const float mean = __ldg(stats + (static_cast<long long>(b) * G + g) * 2);
+      const float rstd = __ldg(stats + (static_cast<long long>(b) * G + g) * 2 + 1);
+      muh[e] = __half2float(__float2half_rn(sat_f16(mean)));
+      rs[e] = rstd;
+      k0[e] = (muh[e] - mean) * rstd;
+      hg[e] = 0.5f * __ldg(gamma + c);
+      hb[e] = 0.5f * __ldg(beta + c);
+    }
+    k[j].muh = __floats2half2_rn(muh[0], muh[1]);
+    k[j].rs = __floats2half2_rn(rs[0], rs[1]);
+    k[j].k0 = __floats2half2_rn(k0[0], k0[1]);
+    k[j].hg = __floats2half2_rn(hg[0], hg[1]);
+    k[j].hb = __floats2half2_rn(hb[0], hb[1]);
+  }
+}
+// xh and silu'(u) * (0.5 / gs) ... returned as q so that the caller picks the final scale: silu' = 0.5 + 0.5 q
+template <bool SILU>
+__device__ __forceinline__ void gn_h2_core(const GnH2Const& k, __half2 x, __half2& xh, __half2& q) {
+  xh = __hfma2(__hsub2(x, k.muh), k.rs, k.k0);
+  if (SILU) {
+    const __half2 uh = __hfma2(xh, k.hg, k.hb);
+    const __half2 t = h2_tanh(uh);
+    const __half2 w = __hfma2(__hneg2(t), t, __float2half2_rn(1.0f));
+    q = __hfma2(uh, w, t);
+  }
+}
+
+// eight pixels of one channel vector: half2 partial sums, one fp32 flush. GUARD: only the first n (< 8) pixels exist
+// (a missing pixel is loaded as dy = 0 and contributes nothing).
+template <bool SILU, bool GUARD>
+__device__ __forceinline__ void gn_h2_reduce8(const GnH2Const (&k)[4], const uint4* __restrict__ xp,
+                                              const uint4* __restrict__ dp, int step, int n, __half2 inv,
+                                              float (&s0)[8], float (&s1)[8]) {
+  constexpr int U = GN_H2_RED_U, NH = 8 / U;
+  __half2 a0[4], a1[4];
+#pragma unroll
+  for (int j = 0; j < 4; ++j) a0[j] = a1[j] = __float2half2_rn(0.0f);
+#pragma unroll
+  for (int h = 0; h < NH; ++h) {
+    uint4 xv[U], dv[U];
+#pragma unroll
+    for (int u = 0; u < U; ++u) {
+      const int e = h * U + u;
+      if (!GUARD || e < n) {
+        xv[u] = __ldg(xp + e * step);
+        dv[u] = __ldg(dp + e * step);
+      } else {
+        xv[u] = dv[u] = make_uint4(0u, 0u, 0u, 0u);
+      }
+    }
+#pragma unroll
+    for (int u = 0; u < U; ++u) {
+      const uint32_t xw[4] = {xv[u].x, xv[u].y, xv[u].z, xv[u].w};
+      const uint32_t dw[4] = {dv[u].x, dv[u].y, dv[u].z, dv[u].w};
+#pragma unroll
+      for (int j = 0; j < 4; ++j) {
+        __half2 xh, q;
+        gn_h2_core<SILU>(k[j], h2_bits(xw[j]), xh, q);
+        const __half2 ds = SILU ? __hmul2(h2_bits(dw[j]), __hfma2(q, inv, inv)) : __hmul2(h2_bits(dw[j]), inv);
+        a0[j] = __hadd2(a0[j], ds);
+        a1[j] = __hfma2(ds, xh, a1[j]);
+      }
+    }
+  }
+#pragma unroll
+  for (int j = 0; j < 4; ++j) {
+    const float2 f0 = __half22float2(a0[j]), f1 = __half22float2(a1[j]);
+    s0[2 * j] += f0.x;
+    s0[2 * j + 1] += f0.y;
+    s1[2 * j] += f1.x;
+    s1[2 * j + 1] += f1.y;
+  }
+}
+
+// part layout as gn_reduce_kernel MODE 1: [B][nsplit][C][2] = (sum dy', sum dy' xhat)
+template <bool SILU>
+__global__ void __launch_bounds__(GN_THREADS, GN_H2_RED_MINB)
+gn_reduce_h2_kernel(const __half* __restrict__ x, const __half* __restrict__ dy, const float* __restrict__ stats,
+                    const float* __restrict__ gamma, const float* __restrict__ beta, float* __restrict__ part, int HW,
+                    int C, int G, int nsplit, int nitems) {
+  constexpr int V = 8, U = GN_H2_RED_U, NH = 8 / U;  // U loads in flight per tensor, fp32 flush every U * NH = 8 pixels
+  const int cv = C / V;
+  const int rows = GN_THREADS / cv;
+  const int col = threadIdx.x % cv, row = threadIdx.x / cv;
+  const int c0 = col * V;
+  extern __shared__ float red[];
+  const __half2 inv = __float2half2_rn(SILU ? 1.0f / 128.0f : 1.0f / 64.0f);
+  for (int item = blockIdx.x; item < nitems; item += gridDim.x) {
+    const int b = item / nsplit, split = item - b * nsplit;
+    const int per = (HW + nsplit - 1) / nsplit;
+    const int p0 = split * per;
+    const int p1 = p0 + per < HW ? p0 + per : HW;
+    GnH2Const k[4];
+    gn_h2_consts(k, stats, gamma, beta, b, c0, C / G, G);
+    float s0[V], s1[V];
+#pragma unroll
+    for (int j = 0; j < V; ++j) s0[j] = s1[j] = 0.0f;
+    if (row < rows) {
+      const uint4* xb = reinterpret_cast<const uint4*>(x + static_cast<long long>(b) * HW * C + c0);
+      const uint4* dyb = reinterpret_cast<const uint4*>(dy + static_cast<long long>(b) * HW * C + c0);
+      const int cvs = C / V;  // uint4 stride of one pixel
+      const int step = rows * cvs;                        // uint4 distance between this thread's pixels
+      int n = p1 > p0 + row ? (p1 - p0 - row + rows - 1) / rows : 0;  // pixels of this thread
+      const uint4* xp = xb + (p0 + row) * cvs;
+      const uint4* dp = dyb + (p0 + row) * cvs;
+      for (; n >= NH * U; n -= NH * U) {  // whole groups of 8 pixels: no bounds checks
+        gn_h2_reduce8<SILU, false>(k, xp, dp, step, NH * U, inv, s0, s1);
+        xp += NH * U * step;
+        dp += NH * U * step;
+      }
+      if (n > 0) gn_h2_reduce8<SILU, true>(k, xp, dp, step, n, inv, s0, s1);
+    }
+    float* r0 = red;
+    float* r1 = red + rows * C;
+    if (row < rows) {
+#pragma unroll
+      for (int j = 0; j < V; ++j) {
+        r0[row * C + c0 + j] = s0[j];
+        r1[row * C + c0 + j] = s1[j];
+      }
+    }
+    __syncthreads();
+    for (int c = threadIdx.x; c < C; c += GN_THREADS) {
+      float a = 0.0f, bb = 0.0f;
+      for (int r = 0; r < rows; ++r) {
+        a += r0[r * C + c];
+        bb += r1[r * C + c];
+      }
+      float* dst = part + ((static_cast<long long>(b) * nsplit + split) * C + c) * 2;
+      dst[0] = 64.0f * a;
+      dst[1] = 64.0f * bb;
+    }
+    __syncthreads();  // red[] is reused by the next item
+  }
+}
+
+// dx = c1 dy' + k2 xhat + k3 (+ dx_add), one channel vector per thread for the whole loop (see gn_apply_kernel)
+template <bool SILU, bool ADD>
+__global__ void __launch_bounds__(GN_THREADS, GN_H2_BWD_MINB)
+gn_bwd_apply_h2_kernel(const __half* __restrict__ x, const __half* __restrict__ dy, const __half* __restrict__ dx_add,
+                       const float* __restrict__ stats, const float* __restrict__ gamma, const float* __restrict__ beta,
+                       const float* __restrict__ coef, __half* __restrict__ dx, int HW, int C, int G,
+                       int* __restrict__ overflow, const float* __restrict__ AB, float* __restrict__ dgamma,
+                       float* __restrict__ dbeta, int B, int accumulate, float pscale) {
+  constexpr int V = 8, U = GN_H2_BWD_U;
+  gn_bwd_param_grads(AB, dgamma, dbeta, B, C, accumulate, pscale);
+  const int b = blockIdx.y;
+  const int cpg = C / G;
+  const int cv = C / V;
+  int i = blockIdx.x * GN_THREADS + threadIdx.x;  // vector index inside the image: HW * C / 8 < 2^31
+  const int c0 = (i % cv) * V;
+  GnH2Const k[4];
+  gn_h2_consts(k, stats, gamma, beta, b, c0, cpg, G);
+  __half2 c1[4], k2[4], k3[4];
+#pragma unroll
+  for (int j = 0; j < 4; ++j) {
+    float a[2], b2[2], b3[2];
+#pragma unroll
+    for (int e = 0; e < 2; ++e) {
+      const int c = c0 + 2 * j + e;
+      const int g = c / cpg;
+      const float mean = __ldg(stats + (static_cast<long long>(b) * G + g) * 2);
+      const float rstd = __ldg(stats + (static_cast<long long>(b) * G + g) * 2 + 1);
+      const float cc2 = __ldg(coef + (static_cast<long long>(b) * G + g) * 2);      // -rstd^2 S2 / n
+      const float cc3 = __ldg(coef + (static_cast<long long>(b) * G + g) * 2 + 1);  // rstd (mean rstd S2 - S1) / n
+      a[e] = rstd * __ldg(gamma + c);
+      b2[e] = __fdividef(cc2, rstd);     // c2 x + c3 = (c2 / rstd) xhat + (c3 + c2 mean)
+      b3[e] = fmaf(cc2, mean, cc3);
+    }
+    c1[j] = __floats2half2_rn(sat_f16(a[0]), sat_f16(a[1]));
+    k2[j] = __floats2half2_rn(sat_f16(b2[0]), sat_f16(b2[1]));
+    k3[j] = __floats2half2_rn(sat_f16(b3[0]), sat_f16(b3[1]));
+  }
+  const int nvec = HW * cv;
+  const long long base = static_cast<long long>(b) * HW * C;
+  const uint4* xb = reinterpret_cast<const uint4*>(x + base);
+  const uint4* dyb = reinterpret_cast<const uint4*>(dy + base);
+  const uint4* ab = ADD ? reinterpret_cast<const uint4*>(dx_add + base) : nullptr;
+  uint4* dxb = reinterpret_cast<uint4*>(dx + base);
+  const int stride = gridDim.x * GN_THREADS;
+  const __half2 half = __float2half2_rn(0.5f), hmax = __float2half2_rn(65504.0f), hmin = __float2half2_rn(-65504.0f);
+  __half2 amax = __float2half2_rn(0.0f);  // running max |dy|: a saturated dy means the gradient scale is too large
+  for (; i < nvec; i += U * stride) {
+    uint4 xv[U], dv[U], av[U];
+#pragma unroll
+    for (int u = 0; u < U; ++u) {
+      const int kk = i + u * stride;
+      if (kk < nvec) {
+        xv[u] = __ldg(xb + kk);
+        dv[u] = __ldg(dyb + kk);
+        if (ADD) av[u] = __ldg(ab + kk);
+      }
+    }
+#pragma unroll
+    for (int u = 0; u < U; ++u) {
+      const int kk = i + u * stride;
+      if (kk < nvec) {
+        const uint32_t xw[4] = {xv[u].x, xv[u].y, xv[u].z, xv[u].w};
+        const uint32_t dw[4] = {dv[u].x, dv[u].y, dv[u].z, dv[u].w};
+        const uint32_t aw[4] = {ADD ? av[u].x : 0u, ADD ? av[u].y : 0u, ADD ? av[u].z : 0u, ADD ? av[u].w : 0u};
+        uint32_t ow[4];
+#pragma unroll
+        for (int j = 0; j < 4; ++j) {
+          __half2 xh, q;
+          gn_h2_core<SILU>(k[j], h2_bits(xw[j]), xh, q);
+          __half2 d = h2_bits(dw[j]);
+          amax = __hmax2(amax, __habs2(d));
+          if (SILU) d = __hmul2(d, __hfma2(q, half, half));
+          __half2 o = __hfma2(c1[j], d, __hfma2(k2[j], xh, k3[j]));
+          if (ADD) o = __hadd2(o, h2_bits(aw[j]));
+          ow[j] = h2_u32(__hmin2(__hmax2(o, hmin), hmax));
+        }
+        dxb[kk] = make_uint4(ow[0], ow[1], ow[2], ow[3]);
+      }
+    }
+  }
+  if (overflow != nullptr && (__hge(__low2half(amax), __low2half(hmax)) || __hge(__high2half(amax), __low2half(hmax))))
+    overflow[1] = 1;  // benign race: every writer stores the same value
 }
 
 // Pixel-range splits per image for the reduce kernels. The reduce grid is ONE resident wave of `slots` CTAs taking
@@ -560,28 +878,60 @@ int odvae_groupnorm_bwd(const void* x, const float* stats, const float* gamma, c
         reinterpret_cast<const T*>(x), reinterpret_cast<const TG*>(dy), stats, gamma, beta, part, HW, C, G, silu, ns, \
         items);                                                                                                       \
   }
+#define GN_LAUNCH_REDUCE_H2(S)                                                                                        \
+  {                                                                                                                   \
+    const int slots = gn_slots(gn_reduce_h2_kernel<S>, smem);                                                         \
+    ns = gn_nsplit(B, HW, slots);                                                                                     \
+    const int items = B * ns;                                                                                         \
+    gn_reduce_h2_kernel<S><<<items < slots ? items : slots, GN_THREADS, smem, st>>>(                                   \
+        reinterpret_cast<const __half*>(x), reinterpret_cast<const __half*>(dy), stats, gamma, beta, part, HW, C, G,  \
+        ns, items);                                                                                                   \
+  }
   if (combo == 1) GN_LAUNCH_REDUCE1(bf16, bf16)
   else if (combo == 2) GN_LAUNCH_REDUCE1(f16, bf16)
+  else if (combo == 3 && GN_H2) {
+    if (silu) GN_LAUNCH_REDUCE_H2(true)
+    else GN_LAUNCH_REDUCE_H2(false)
+  }
   else if (combo == 3) GN_LAUNCH_REDUCE1(f16, f16)
   else GN_LAUNCH_REDUCE1(float, float)
+#undef GN_LAUNCH_REDUCE_H2
 #undef GN_LAUNCH_REDUCE1
   int s = check_launch("gn_reduce_kernel<1>");
   if (s != ODVAE_OK) return s;
   gn_bwd_finalize_a_kernel<<<B, 256, static_cast<size_t>(2) * C * sizeof(float), st>>>(part, stats, gamma, AB, coef, ns, HW, C, G);
   s = check_launch("gn_bwd_finalize_a_kernel");
   if (s != ODVAE_OK) return s;
+#if GN_FUSE_PGRAD
+  const float* ABp = AB;  // dgamma / dbeta are summed by the first CTAs of the apply kernel
+#else
+  const float* ABp = nullptr;
   gn_bwd_finalize_b_kernel<<<(C + 127) / 128, 128, 0, st>>>(AB, dgamma, dbeta, B, C, accumulate, pgrad_scale);
   s = check_launch("gn_bwd_finalize_b_kernel");
   if (s != ODVAE_OK) return s;
+#endif
   dim3 grid2(gn_apply_blocks(B, HW, C, V), B);
 #define GN_LAUNCH_APPLY(T, TG)                                                                                         \
   gn_bwd_apply_kernel<T, TG><<<grid2, GN_THREADS, 0, st>>>(reinterpret_cast<const T*>(x), reinterpret_cast<const TG*>(dy), \
                                                            reinterpret_cast<const TG*>(dx_add), stats, gamma, beta, coef,  \
-                                                           reinterpret_cast<TG*>(dx), HW, C, G, silu, overflow_flags);
+                                                           reinterpret_cast<TG*>(dx), HW, C, G, silu, overflow_flags,  \
+                                                           ABp, dgamma, dbeta, B, accumulate, pgrad_scale);
+#define GN_LAUNCH_APPLY_H2(S, A)                                                                                       \
+  gn_bwd_apply_h2_kernel<S, A><<<grid2, GN_THREADS, 0, st>>>(                                                          \
+      reinterpret_cast<const __half*>(x), reinterpret_cast<const __half*>(dy), reinterpret_cast<const __half*>(dx_add), \
+      stats, gamma, beta, coef, reinterpret_cast<__half*>(dx), HW, C, G, overflow_flags, ABp, dgamma, dbeta, B,       \
+      accumulate, pgrad_scale);
   if (combo == 1) GN_LAUNCH_APPLY(bf16, bf16)
   else if (combo == 2) GN_LAUNCH_APPLY(f16, bf16)
+  else if (combo == 3 && GN_H2) {
+    if (silu && dx_add) GN_LAUNCH_APPLY_H2(true, true)
+    else if (silu) GN_LAUNCH_APPLY_H2(true, false)
+    else if (dx_add) GN_LAUNCH_APPLY_H2(false, true)
+    else GN_LAUNCH_APPLY_H2(false, false)
+  }
   else if (combo == 3) GN_LAUNCH_APPLY(f16, f16)
   else GN_LAUNCH_APPLY(float, float)
+#undef GN_LAUNCH_APPLY_H2
 #undef GN_LAUNCH_APPLY
   return check_launch("gn_bwd_apply_kernel");
 }

@@ -10,6 +10,11 @@
 #include "tc_primitives.cuh"
 #include "engine_desc.h"
 
+// A/B switch: the compile-time-specialised swapped-role conv epilogue (fp16, pixel stride 128) -- see `emit` below
+#ifndef TC_FAST_EPI
+#define TC_FAST_EPI 1
+#endif
+
 namespace odvae {
 
 static constexpr int TC_BLOCK_M = 128;
@@ -501,11 +506,12 @@ tc_engine_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant_
         const int n = m0 + r;
         const bool ch_ok = n < p.n_valid;
         const float bias = (p.bias != nullptr && ch_ok) ? __ldg(p.bias + n) : 0.0f;
-        const bool halfp = p.out_mode == OUT_F16;
+        const bool halfp_rt = p.out_mode == OUT_F16;
         uint16_t* D16 = reinterpret_cast<uint16_t*>(p.D);
         const uint16_t* R16 = reinterpret_cast<const uint16_t*>(p.residual);
         const long long base0 = static_cast<long long>(pb_b) * p.oB + p.o0 + n;
-        const long long sx = p.oX;
+        const long long sx_rt = p.oX;
+        const long long sx = sx_rt;
         float gs0 = 0.0f, gs1 = 0.0f, gq0 = 0.0f, gq1 = 0.0f;  // fused GroupNorm statistics (two chains each)
         // staged path: the warp's 32 pixels x 32 channels go through a private 2 KiB buffer ([pixel][32 channels], 64-byte
         // rows) and leave as 16-byte vectors: lane l, vector k covers pixel (l >> 2) + 8 k, channels 8 (l & 3) .. + 7
@@ -522,7 +528,14 @@ tc_engine_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant_
               rv[k] = __ldg(reinterpret_cast<const uint4*>(R16 + vb + static_cast<long long>(8 * k) * sx));
           }
         };
-        auto emit = [&](uint32_t (&v)[32], int pi0) {
+        // `fast` (std::true_type): IEEE fp16 output (and residual) with a pixel stride of exactly 128 elements, direct path.
+        // Both become compile-time constants, so the 2-byte accesses of a batch use ONE base register + immediate offsets
+        // and the format select disappears: 3 issue slots per element instead of 7.5 (6 instead of 13.5 with a residual;
+        // SASS of the generic path: predicated bf16 AND fp16 packs with four FMNMX clamps per pair, IADD3 + IADD3.X per access).
+        auto emit = [&](uint32_t (&v)[32], int pi0, auto fast) {
+          constexpr bool kFast = decltype(fast)::value;
+          const bool halfp = kFast ? true : halfp_rt;
+          const long long sx = kFast ? 128ll : sx_rt;
           const int yy = pb_y + (pi0 >> p.bw_log2), xx = pb_x + (pi0 & ((1 << p.bw_log2) - 1));
           const long long base = base0 + static_cast<long long>(yy) * p.oY + static_cast<long long>(xx) * sx;
           if (p.out_mode == OUT_NCHW_F32) {
@@ -624,21 +637,27 @@ tc_engine_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant_
             }
           }
         }
-        mbar_wait(&tfull_bar[acc], acc_phase);
-        tc_fence_after();
-        uint32_t va[32], vb[32];
-        tmem_ld_x32(t_row + static_cast<uint32_t>(c_begin), va);
-        tmem_ld_wait();
-        tmem_ld_x32(t_row + static_cast<uint32_t>(c_begin + 32), vb);
-        emit(va, 0);
-        tmem_ld_wait();
-        tmem_ld_x32(t_row + static_cast<uint32_t>(c_begin + 64), va);
-        emit(vb, 32);
-        tmem_ld_wait();
-        tmem_ld_x32(t_row + static_cast<uint32_t>(c_begin + 96), vb);
-        emit(va, 64);
-        tmem_ld_wait();
-        emit(vb, 96);
+        auto drain = [&](auto fast) {
+          mbar_wait(&tfull_bar[acc], acc_phase);
+          tc_fence_after();
+          uint32_t va[32], vb[32];
+          tmem_ld_x32(t_row + static_cast<uint32_t>(c_begin), va);
+          tmem_ld_wait();
+          tmem_ld_x32(t_row + static_cast<uint32_t>(c_begin + 32), vb);
+          emit(va, 0, fast);
+          tmem_ld_wait();
+          tmem_ld_x32(t_row + static_cast<uint32_t>(c_begin + 64), va);
+          emit(vb, 32, fast);
+          tmem_ld_wait();
+          tmem_ld_x32(t_row + static_cast<uint32_t>(c_begin + 96), vb);
+          emit(va, 64, fast);
+          tmem_ld_wait();
+          emit(vb, 96, fast);
+        };
+        if (TC_FAST_EPI && halfp_rt && sx_rt == 128 && stg == nullptr && p.out_mode != OUT_NCHW_F32)
+          drain(std::true_type{});
+        else
+          drain(std::false_type{});
         if (p.gn_part != nullptr && ch_ok) {
           const int boxes = p.tiles_x * p.tiles_y;  // pixel boxes per image
           const int box = 2 * tc.n_tile + half - pb_b * boxes;

@@ -9,7 +9,7 @@ from odvae_b200.lib import CONV_3x3_S1, IMPL_TC
 
 B, H, C = int(os.environ.get("PB", 64)), int(os.environ.get("PH", 256)), int(os.environ.get("PC", 128))
 iters = int(sys.argv[1]) if len(sys.argv) > 1 else 4
-dt = torch.bfloat16
+dt = torch.float16 if os.environ.get("PDT", "fp16") == "fp16" else torch.bfloat16  # fp16 = the timed mode
 torch.manual_seed(0)
 x = torch.randn(B, H, H, C, device="cuda").to(dt)
 dy = torch.randn(B, H, H, C, device="cuda").to(dt)

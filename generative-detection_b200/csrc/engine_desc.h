@@ -77,6 +77,12 @@ struct TcParams {
   // backward, whose epilogue needs the L2 bandwidth for the P / dS tiles; the q k^T passes measured 4 % slower with it (the
   // panel reload at every run boundary stalls the MMAs) and keep the plain schedule. 0 = every tile loads both operands.
   int bstat_mt, bstat_runs;
+  // GEMM with TWO m-tiles per CTA tile (256 x 256 outputs, K streamed): both 128-row A tiles of a stage are multiplied with
+  // the SAME B tile (two MMAs per K step into the two 256-column accumulators), so B crosses the L2 -> SM fabric once per
+  // 256 rows instead of once per 128. The attention GEMMs P v, P^T dO, dS k, dS^T q (M = K = 4096, N = 256) stream a 2 GB
+  // P / dS matrix from HBM but moved 6.3 GB through L2 -> SM at the fabric's ~11 TB/s ceiling (B = 2/3 of it, re-fetched by
+  // each of the 32 m-tiles of an image): 4.4 TB/s of DRAM. num_m_tiles counts PAIRS when set.
+  int mpair;
 };
 
 

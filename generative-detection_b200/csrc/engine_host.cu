@@ -185,6 +185,25 @@ static int launch_tc(EngineDesc& d, cudaStream_t stream) {
       }
     }
   }
+  // K-streaming GEMMs with N = 256 (the attention P / dS GEMMs): two m-tiles per CTA tile share every B tile (engine_desc.h)
+  p.mpair = 0;
+  {
+    // ODVAE_GEMM_MPAIR: 0 = off, 2 = whenever the shape allows (tests), default = only where the pair tiles still fill
+    // the GPU four times over (read per call: the tests switch it)
+    const char* mv = getenv("ODVAE_GEMM_MPAIR");
+    const int mpair_mode = mv ? atoi(mv) : 1;
+    const long long pairs = static_cast<long long>(p.num_m_tiles / 2) * p.num_n_tiles * p.num_z;
+    if (mpair_mode != 0 && p.kind == KIND_GEMM && p.epi == EPI_NONE && p.bstat_mt == 0 && p.BN == 256 &&
+        (p.num_m_tiles % 2) == 0 && ((p.num_k_iters >= 16 && pairs >= 4ll * num_sms()) || mpair_mode == 2)) {
+      p.mpair = 1;
+      p.num_m_tiles /= 2;
+      const size_t stage_bytes = 2 * static_cast<size_t>(TC_A_BYTES) + static_cast<size_t>(p.BN) * 128;
+      int s = static_cast<int>((224 * 1024 - 2048) / stage_bytes);
+      if (s > p.num_k_iters) s = p.num_k_iters;
+      p.stages = s;
+      smem = static_cast<size_t>(p.stages) * stage_bytes + (2 * p.stages + 4) * 8 + 16 + 1024;
+    }
+  }
   // swapped-role conv epilogue: 8 x 2 KiB staging buffers for 16-byte vector stores / residual loads
   p.epi_off = 0;
   {

@@ -124,8 +124,11 @@ tc_engine_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant_
                                    : static_cast<uint32_t>(BN) * 128u * static_cast<uint32_t>(wgT);  // per stage
   const int acc_cols = BN * wgT;                      // TMEM columns of one accumulator
   const int num_acc = 2 * acc_cols <= TC_TMEM_COLS ? 2 : 1;
+  // m-tile pairs (engine_desc.h `mpair`): a stage holds two 16 KiB A tiles
+  const bool mpair = kKind == KIND_GEMM && p.mpair != 0;
+  const uint32_t a_stage = mpair ? 2u * TC_A_BYTES : static_cast<uint32_t>(TC_A_BYTES);
   uint8_t* sA = smem;
-  uint8_t* sB = smem + static_cast<size_t>(stages) * TC_A_BYTES;
+  uint8_t* sB = smem + static_cast<size_t>(stages) * a_stage;
   // halo mode: sA = weight stages, sB = ring of input-row slabs
   const uint32_t wslab_tx = static_cast<uint32_t>(((1 << p.kbw_log2) + 2) * (TC_BLOCK_K >> p.kbw_log2)) * 128u;
   const bool cv_halo = kKind == KIND_CONV && p.halo;
@@ -226,7 +229,7 @@ tc_engine_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant_
         const int t = sched_tile(p, total_tiles, s, mi);
         if (t < 0) break;
         const TileCoord tc = decode_tile(p, kKind, kSwap, t);
-        const int m0 = tc.m_tile * TC_BLOCK_M;
+        const int m0 = tc.m_tile * (mpair ? 2 * TC_BLOCK_M : TC_BLOCK_M);
         const int n0 = tc.n_tile * BN;
         const int nk = tile_k_iters(p, kKind, tc);
         if (bstat && mi == 0) {
@@ -241,16 +244,20 @@ tc_engine_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant_
           mbar_wait(&empty_bar[stage], phase ^ 1u);
           uint64_t* fb = &full_bar[stage];
           mbar_arrive_expect_tx(fb, wg_halo ? TC_A_BYTES + static_cast<uint32_t>(BN >> 6) * wslab_tx
-                                            : (bstat ? static_cast<uint32_t>(TC_A_BYTES) : TC_A_BYTES + b_bytes));
-          uint8_t* a_dst = sA + static_cast<size_t>(stage) * TC_A_BYTES;
+                                            : (bstat ? a_stage : a_stage + b_bytes));
+          uint8_t* a_dst = sA + static_cast<size_t>(stage) * a_stage;
           uint8_t* b_dst = sB + static_cast<size_t>(stage) * b_bytes;
           if (kKind == KIND_GEMM) {
             const int k0 = kit * TC_BLOCK_K;
-            if (!p.a_mn) {
-              tma_load_3d(a_dst, &tmA, fb, k0, m0, tc.z);
-            } else {
-              tma_load_3d(a_dst, &tmA, fb, m0, k0, tc.z);
-              tma_load_3d(a_dst + 8192, &tmA, fb, m0 + 64, k0, tc.z);
+            for (int h = 0; h < (mpair ? 2 : 1); ++h) {
+              uint8_t* ah = a_dst + h * TC_A_BYTES;
+              const int mh = m0 + h * TC_BLOCK_M;
+              if (!p.a_mn) {
+                tma_load_3d(ah, &tmA, fb, k0, mh, tc.z);
+              } else {
+                tma_load_3d(ah, &tmA, fb, mh, k0, tc.z);
+                tma_load_3d(ah + 8192, &tmA, fb, mh + 64, k0, tc.z);
+              }
             }
             if (bstat) {
               // B is the run's stationary panel
@@ -366,6 +373,7 @@ tc_engine_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant_
         const int t = sched_tile(p, total_tiles, s, mi);
         if (t < 0) break;
         mbar_wait(&tempty_bar[acc], acc_phase ^ 1u);
+        if (mpair) mbar_wait(&tempty_bar[1], acc_phase ^ 1u);  // a pair tile owns both accumulators (acc stays 0)
         tc_fence_after();
         const uint32_t d_tmem = tmem_base + static_cast<uint32_t>(acc * acc_cols);
         const TileCoord tcm = decode_tile(p, kKind, kSwap, t);
@@ -378,7 +386,7 @@ tc_engine_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant_
         for (int kit = 0; kit < nk; ++kit) {
           mbar_wait(&full_bar[stage], phase);
           tc_fence_after();
-          const uint32_t a_base = smem_u32(sA + static_cast<size_t>(stage) * TC_A_BYTES);
+          const uint32_t a_base = smem_u32(sA + static_cast<size_t>(stage) * a_stage);
           const uint32_t b_base = bstat ? smem_u32(sB + static_cast<size_t>(kit) * bchunk)
                                         : smem_u32(sB + static_cast<size_t>(stage) * b_bytes);
 #pragma unroll
@@ -400,6 +408,12 @@ tc_engine_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant_
               continue;
             }
             umma_bf16(d_tmem, adesc, bdesc, idesc, (kit | k) != 0 ? 1u : 0u);
+            if (mpair) {  // rows 128..255 of the pair: second A tile of the stage, same B, second accumulator
+              const uint32_t a1 = a_base + TC_A_BYTES;
+              const uint64_t adesc1 = p.a_mn ? make_smem_desc_sw128(a1 + k * 2048, 8192, 1024)
+                                             : make_smem_desc_sw128(a1 + k * 32, 0, 1024);
+              umma_bf16(d_tmem + static_cast<uint32_t>(acc_cols), adesc1, bdesc, idesc, (kit | k) != 0 ? 1u : 0u);
+            }
             if (n_rest > 0) {  // WGRAD tap groups only (MN-major B): chunks 4.. of the stage
               const uint64_t bdesc2 = make_smem_desc_sw128(b_base + 4 * 8192 + k * 2048, 8192, 1024);
               umma_bf16(d_tmem + 256u, adesc, bdesc2, idesc2, (kit | k) != 0 ? 1u : 0u);
@@ -412,6 +426,11 @@ tc_engine_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant_
           }
         }
         umma_commit(&tfull_bar[acc]);  // accumulator complete -> epilogue
+        if (mpair) {
+          umma_commit(&tfull_bar[1]);
+          acc_phase ^= 1u;
+          continue;
+        }
         if (bstat && mi == p.bstat_mt - 1) umma_commit(&sempty_bar[0]);  // run complete -> the panel may be replaced
         if (++acc == num_acc) {
           acc = 0;
@@ -437,12 +456,15 @@ tc_engine_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant_
     uint32_t acc_phase = 0;
     int cs_stage = 0;
     uint32_t cs_phase = 0;
-    for (int s = 0;; ++s) {
+    for (int s2 = 0;; ++s2) {
+      // m-tile pairs: two passes per scheduled tile, rows 0..127 from accumulator 0, rows 128..255 from accumulator 1
+      const int s = mpair ? (s2 >> 1) : s2;
+      const int mh = mpair ? (s2 & 1) : 0;
       int mi;
       const int t = sched_tile(p, total_tiles, s, mi);
       if (t < 0) break;
       const TileCoord tc = decode_tile(p, kKind, kSwap, t);
-      const int m0 = tc.m_tile * TC_BLOCK_M;
+      const int m0 = (mpair ? 2 * tc.m_tile + mh : tc.m_tile) * TC_BLOCK_M;
       const int n0 = tc.n_tile * BN;
 
       if (kKind == KIND_WGRAD && p.colsum != nullptr) {

@@ -197,6 +197,32 @@ def test_gemm(impl, dtype, a_mn, b_mn, case, out_f32):
     assert rel_err(D, ref) < tol(dtype)
 
 
+@pytest.mark.parametrize("dtype", [torch.float16, torch.bfloat16])
+@pytest.mark.parametrize("a_mn,b_mn", [(False, False), (False, True), (True, False), (True, True)])
+@pytest.mark.parametrize("case", [(512, 256, 1024, 3), (1000, 256, 200, 2), (1024, 256, 4096, 2), (256, 512, 128, 1)])
+def test_gemm_m_tile_pairs(dtype, a_mn, b_mn, case, monkeypatch):
+    """K-streaming GEMM with two m-tiles per CTA tile sharing every B tile (csrc/engine_desc.h `mpair`; the attention
+    P v / P^T dO / dS k / dS^T q shape class): forced on for every shape that allows it, and the same call with the
+    plain schedule must give the same bits (same MMAs per output, same K order)."""
+    M, N, Kd, batch = case
+    torch.manual_seed(4)
+    A = torch.randn(batch, M, Kd, device=DEV).to(dtype)
+    Bm = torch.randn(batch, N, Kd, device=DEV).to(dtype)
+    ref = 0.25 * torch.bmm(A.float(), Bm.float().transpose(1, 2))
+    As = A.transpose(1, 2).contiguous() if a_mn else A
+    Bs = Bm.transpose(1, 2).contiguous() if b_mn else Bm
+    from odvae_b200 import ops
+    out = {}
+    for mode in ("2", "0"):
+        monkeypatch.setenv("ODVAE_GEMM_MPAIR", mode)
+        D = torch.empty(batch, M, N, dtype=dtype, device=DEV)
+        out[mode] = ops.gemm_raw(As, Bs, D, M, N, Kd, batch, M if a_mn else Kd, N if b_mn else Kd, N, M * Kd, N * Kd, M * N,
+                                 a_mn, b_mn, alpha=0.25, code=ops.act_code(dtype))
+    torch.cuda.synchronize()
+    assert rel_err(out["2"], ref) < (2e-3 if dtype == torch.float16 else 1e-2)
+    assert torch.equal(out["2"], out["0"])
+
+
 def test_gemm_tc_strided_views():
     """q/k/v live interleaved in one [B,N,3C] tensor (row stride 3C); S = q k^T, O = P v."""
     Bn, N, C = 2, 256, 128

@@ -719,6 +719,287 @@ gn_bwd_apply_h2_kernel(const __half* __restrict__ x, const __half* __restrict__ 
     overflow[1] = 1;  // benign race: every writer stores the same value
 }
 
+// ------------------------------------------------------------------------------------------------------------------
+// Small feature maps (HW <= 1024: the 32x32 and 16x16 levels, 31 of the 67 GroupNorm sites): ONE launch per direction
+// instead of three (statistics / finalize / apply, each 5-15 us of mostly launch latency for 8-30 us of memory time).
+// CTA = (image, 64-channel slab = 128 bytes of every pixel; 64 channels are whole groups). Phase 1 reads the slab and
+// reduces per channel in registers -> shared memory (fixed order), phase 2 re-reads it (<= 256 KiB per CTA: L1 / L2 hits)
+// and writes the result. fp16 activations and fp16 gradients only (the timed mode), fp32 arithmetic.
+// Backward: dgamma / dbeta need the sums over ALL images; the B CTAs of a channel slab take a ticket from a file-scope
+// device counter after publishing their (sum dy', sum dy' xhat) rows, and the LAST one adds the rows in image order
+// (deterministic: the order does not depend on who is last) and resets the counter. Backward launches of this kernel
+// that overlap on the GPU (two streams) would share the counters: the callers issue GroupNorm backward on one stream.
+// ------------------------------------------------------------------------------------------------------------------
+#ifndef GN_SMALL
+#define GN_SMALL 1
+#endif
+static constexpr int GN_SMALL_MAX_HW = 1024;
+__device__ unsigned int gn_small_ticket[64];  // one per 64-channel slab (C <= 4096); zero at load, zero after every launch
+
+struct GnSmallShared {
+  float r0[32][65], r1[32][65];  // per pixel-phase partial sums of the slab's 64 channels (+1: no bank conflicts)
+  float c0[64], c1[64];          // per channel
+  float ga[32], gb[32];          // per group of the slab: (mean, rstd) forward / (c2, c3) backward
+  int last;
+};
+
+// per-thread slab coordinates: 8 lanes cover the 128 bytes of a pixel, 32 pixel phases
+#define GN_SMALL_COORDS                                                              \
+  const int b = blockIdx.y, slab = blockIdx.x;                                       \
+  const int sub = threadIdx.x & 7, prow = threadIdx.x >> 3;                          \
+  const int c0 = slab * 64 + sub * 8;                                                \
+  const int cpg = C / G, cvs = C / 8;                                                \
+  const int gps = 64 / cpg; /* groups per slab */                                    \
+  const long long base = (static_cast<long long>(b) * HW * C + c0) / 8;
+
+__device__ __forceinline__ void gn_small_block_sums(GnSmallShared& sh, const float (&s0)[8], const float (&s1)[8], int sub,
+                                                    int prow) {
+#pragma unroll
+  for (int j = 0; j < 8; ++j) {
+    sh.r0[prow][sub * 8 + j] = s0[j];
+    sh.r1[prow][sub * 8 + j] = s1[j];
+  }
+  __syncthreads();
+  if (threadIdx.x < 64) {
+    float a = 0.0f, bb = 0.0f;
+#pragma unroll 8
+    for (int r = 0; r < 32; ++r) {
+      a += sh.r0[r][threadIdx.x];
+      bb += sh.r1[r][threadIdx.x];
+    }
+    sh.c0[threadIdx.x] = a;
+    sh.c1[threadIdx.x] = bb;
+  }
+  __syncthreads();
+}
+
+template <bool SILU>
+__global__ void __launch_bounds__(256)
+gn_small_fwd_kernel(const __half* __restrict__ x, const float* __restrict__ gamma, const float* __restrict__ beta,
+                    __half* __restrict__ y, float* __restrict__ stats, int HW, int C, int G, float eps,
+                    int* __restrict__ overflow) {
+  __shared__ GnSmallShared sh;
+  GN_SMALL_COORDS
+  const uint4* xb = reinterpret_cast<const uint4*>(x) + base;
+  uint4* yb = reinterpret_cast<uint4*>(y) + base;
+  float s0[8], s1[8];
+#pragma unroll
+  for (int j = 0; j < 8; ++j) s0[j] = s1[j] = 0.0f;
+  bool sat = false;
+  for (int p = prow; p < HW; p += 128) {
+    uint4 v[4];
+#pragma unroll
+    for (int u = 0; u < 4; ++u) {
+      v[u] = make_uint4(0u, 0u, 0u, 0u);
+      if (p + 32 * u < HW) v[u] = __ldg(xb + static_cast<long long>(p + 32 * u) * cvs);
+    }
+#pragma unroll
+    for (int u = 0; u < 4; ++u) {
+      const __half* hv = reinterpret_cast<const __half*>(&v[u]);
+#pragma unroll
+      for (int j = 0; j < 8; ++j) {
+        const float f = __half2float(hv[j]);
+        sat |= fabsf(f) >= 65504.0f;
+        s0[j] += f;
+        s1[j] = fmaf(f, f, s1[j]);
+      }
+    }
+  }
+  gn_small_block_sums(sh, s0, s1, sub, prow);
+  if (threadIdx.x < gps) {
+    float a = 0.0f, bb = 0.0f;
+    for (int j = 0; j < cpg; ++j) {
+      a += sh.c0[threadIdx.x * cpg + j];
+      bb += sh.c1[threadIdx.x * cpg + j];
+    }
+    const float nn = static_cast<float>(cpg) * HW;
+    const float mean = a / nn;
+    float var = bb / nn - mean * mean;
+    var = var < 0.0f ? 0.0f : var;
+    const float rstd = rsqrtf(var + eps);
+    sh.ga[threadIdx.x] = mean;
+    sh.gb[threadIdx.x] = rstd;
+    const int g = slab * gps + threadIdx.x;
+    stats[(static_cast<long long>(b) * G + g) * 2] = mean;
+    stats[(static_cast<long long>(b) * G + g) * 2 + 1] = rstd;
+  }
+  __syncthreads();
+  float scale[8], shift[8];
+#pragma unroll
+  for (int j = 0; j < 8; ++j) {
+    const int cl = sub * 8 + j;
+    const float mean = sh.ga[cl / cpg], rstd = sh.gb[cl / cpg];
+    scale[j] = rstd * __ldg(gamma + c0 + j);
+    shift[j] = __ldg(beta + c0 + j) - mean * scale[j];
+  }
+  for (int p = prow; p < HW; p += 128) {
+    uint4 v[4];
+#pragma unroll
+    for (int u = 0; u < 4; ++u)
+      if (p + 32 * u < HW) v[u] = __ldg(xb + static_cast<long long>(p + 32 * u) * cvs);
+#pragma unroll
+    for (int u = 0; u < 4; ++u) {
+      if (p + 32 * u < HW) {
+        const __half* hv = reinterpret_cast<const __half*>(&v[u]);
+        __half ov[8];
+#pragma unroll
+        for (int j = 0; j < 8; ++j) {
+          float r = fmaf(__half2float(hv[j]), scale[j], shift[j]);
+          if (SILU) r = silu_t<true>(r);
+          ov[j] = from_f32<f16>(r);
+        }
+        yb[static_cast<long long>(p + 32 * u) * cvs] = *reinterpret_cast<const uint4*>(ov);
+      }
+    }
+  }
+  if (sat && overflow != nullptr) overflow[0] = 1;  // benign race: every writer stores the same value
+}
+
+template <bool SILU, bool ADD>
+__global__ void __launch_bounds__(256)
+gn_small_bwd_kernel(const __half* __restrict__ x, const __half* __restrict__ dy, const __half* __restrict__ dx_add,
+                    const float* __restrict__ stats, const float* __restrict__ gamma, const float* __restrict__ beta,
+                    __half* __restrict__ dx, float* __restrict__ AB, float* __restrict__ dgamma,
+                    float* __restrict__ dbeta, int B, int HW, int C, int G, int accumulate, float pscale,
+                    int* __restrict__ overflow) {
+  __shared__ GnSmallShared sh;
+  GN_SMALL_COORDS
+  const uint4* xb = reinterpret_cast<const uint4*>(x) + base;
+  const uint4* dyb = reinterpret_cast<const uint4*>(dy) + base;
+  const uint4* ab = ADD ? reinterpret_cast<const uint4*>(dx_add) + base : nullptr;
+  uint4* dxb = reinterpret_cast<uint4*>(dx) + base;
+  float mu[8], rs[8], sc[8], shf[8];
+#pragma unroll
+  for (int j = 0; j < 8; ++j) {
+    const int g = (c0 + j) / cpg;
+    mu[j] = __ldg(stats + (static_cast<long long>(b) * G + g) * 2);
+    rs[j] = __ldg(stats + (static_cast<long long>(b) * G + g) * 2 + 1);
+    sc[j] = rs[j] * __ldg(gamma + c0 + j);
+    shf[j] = __ldg(beta + c0 + j) - mu[j] * sc[j];
+  }
+  float s0[8], s1[8];
+#pragma unroll
+  for (int j = 0; j < 8; ++j) s0[j] = s1[j] = 0.0f;
+  bool sat = false;
+  for (int p = prow; p < HW; p += 64) {
+    uint4 xv[2], dv[2];
+#pragma unroll
+    for (int u = 0; u < 2; ++u) {
+      xv[u] = dv[u] = make_uint4(0u, 0u, 0u, 0u);  // a missing pixel has dy = 0
+      if (p + 32 * u < HW) {
+        xv[u] = __ldg(xb + static_cast<long long>(p + 32 * u) * cvs);
+        dv[u] = __ldg(dyb + static_cast<long long>(p + 32 * u) * cvs);
+      }
+    }
+#pragma unroll
+    for (int u = 0; u < 2; ++u) {
+      const __half* hx = reinterpret_cast<const __half*>(&xv[u]);
+      const __half* hd = reinterpret_cast<const __half*>(&dv[u]);
+#pragma unroll
+      for (int j = 0; j < 8; ++j) {
+        const float xf = __half2float(hx[j]);
+        float d = __half2float(hd[j]);
+        sat |= fabsf(d) >= 65504.0f;
+        if (SILU) d *= silu_grad_t<true>(fmaf(xf, sc[j], shf[j]));
+        s0[j] += d;
+        s1[j] = fmaf(d, (xf - mu[j]) * rs[j], s1[j]);
+      }
+    }
+  }
+  gn_small_block_sums(sh, s0, s1, sub, prow);
+  if (threadIdx.x < 64) {  // publish this image's row of the slab for the dgamma / dbeta sums
+    float2* dst = reinterpret_cast<float2*>(AB) + static_cast<long long>(b) * C + slab * 64 + threadIdx.x;
+    *dst = make_float2(sh.c0[threadIdx.x], sh.c1[threadIdx.x]);
+  }
+  if (threadIdx.x < gps) {
+    float a = 0.0f, bb = 0.0f;
+    for (int j = 0; j < cpg; ++j) {
+      const float gm = __ldg(gamma + slab * 64 + threadIdx.x * cpg + j);
+      a += gm * sh.c0[threadIdx.x * cpg + j];
+      bb += gm * sh.c1[threadIdx.x * cpg + j];
+    }
+    const int g = slab * gps + threadIdx.x;
+    const float mean = __ldg(stats + (static_cast<long long>(b) * G + g) * 2);
+    const float rstd = __ldg(stats + (static_cast<long long>(b) * G + g) * 2 + 1);
+    const float inv_n = 1.0f / (static_cast<float>(cpg) * HW);
+    sh.ga[threadIdx.x] = -rstd * rstd * bb * inv_n;                  // c2
+    sh.gb[threadIdx.x] = rstd * (mean * rstd * bb - a) * inv_n;      // c3
+  }
+  __syncthreads();
+  float c2[8], c3[8];
+#pragma unroll
+  for (int j = 0; j < 8; ++j) {
+    c2[j] = sh.ga[(sub * 8 + j) / cpg];
+    c3[j] = sh.gb[(sub * 8 + j) / cpg];
+  }
+  for (int p = prow; p < HW; p += 64) {
+    uint4 xv[2], dv[2], av[2];
+#pragma unroll
+    for (int u = 0; u < 2; ++u) {
+      if (p + 32 * u < HW) {
+        xv[u] = __ldg(xb + static_cast<long long>(p + 32 * u) * cvs);
+        dv[u] = __ldg(dyb + static_cast<long long>(p + 32 * u) * cvs);
+        if (ADD) av[u] = __ldg(ab + static_cast<long long>(p + 32 * u) * cvs);
+      }
+    }
+#pragma unroll
+    for (int u = 0; u < 2; ++u) {
+      if (p + 32 * u < HW) {
+        const __half* hx = reinterpret_cast<const __half*>(&xv[u]);
+        const __half* hd = reinterpret_cast<const __half*>(&dv[u]);
+        const __half* ha = reinterpret_cast<const __half*>(&av[u]);
+        __half ov[8];
+#pragma unroll
+        for (int j = 0; j < 8; ++j) {
+          const float xf = __half2float(hx[j]);
+          float d = __half2float(hd[j]);
+          if (SILU) d *= silu_grad_t<true>(fmaf(xf, sc[j], shf[j]));
+          float o = fmaf(sc[j], d, fmaf(c2[j], xf, c3[j]));
+          if (ADD) o += __half2float(ha[j]);
+          ov[j] = from_f32<f16>(o);
+        }
+        dxb[static_cast<long long>(p + 32 * u) * cvs] = *reinterpret_cast<const uint4*>(ov);
+      }
+    }
+  }
+  if (sat && overflow != nullptr) overflow[1] = 1;
+  // ---- dgamma / dbeta: the last CTA of this slab (over the B images) adds the published rows in image order ----
+  __threadfence();
+  __syncthreads();
+  if (threadIdx.x == 0) {
+    const unsigned int t = atomicAdd(&gn_small_ticket[slab], 1u);
+    sh.last = (t == static_cast<unsigned int>(B) - 1u) ? 1 : 0;
+  }
+  __syncthreads();
+  if (!sh.last) return;
+  __threadfence();
+  {
+    const int ch = threadIdx.x & 63, part = threadIdx.x >> 6;  // 4 image slices per channel
+    float a = 0.0f, bb = 0.0f;
+    for (int i = part; i < B; i += 4) {
+      const float2 v = __ldcg(reinterpret_cast<const float2*>(AB) + static_cast<long long>(i) * C + slab * 64 + ch);
+      a += v.x;
+      bb += v.y;
+    }
+    sh.r0[part][ch] = a;
+    sh.r1[part][ch] = bb;
+  }
+  __syncthreads();
+  if (threadIdx.x < 64) {
+    const float a = ((sh.r0[0][threadIdx.x] + sh.r0[1][threadIdx.x]) + (sh.r0[2][threadIdx.x] + sh.r0[3][threadIdx.x])) * pscale;
+    const float bb = ((sh.r1[0][threadIdx.x] + sh.r1[1][threadIdx.x]) + (sh.r1[2][threadIdx.x] + sh.r1[3][threadIdx.x])) * pscale;
+    const int c = slab * 64 + threadIdx.x;
+    dbeta[c] = accumulate ? dbeta[c] + a : a;
+    dgamma[c] = accumulate ? dgamma[c] + bb : bb;
+  }
+  if (threadIdx.x == 0) gn_small_ticket[slab] = 0u;  // ready for the next launch (stream order)
+}
+#undef GN_SMALL_COORDS
+
+static bool gn_small_ok(int HW, int C, int G) {
+  return GN_SMALL && HW <= GN_SMALL_MAX_HW && C % 64 == 0 && C <= 4096 && C % G == 0 && 64 % (C / G) == 0 && (C / G) >= 2;
+}
+
 // Pixel-range splits per image for the reduce kernels. The reduce grid is ONE resident wave of `slots` CTAs taking
 // (image, split) items grid-stride; B * nsplit is chosen near 4 items per CTA so that items / slots falls just below
 // an integer (no CTA does a whole extra item while the others idle). slots <= 0: conservative 2 CTAs per SM.
@@ -846,6 +1127,19 @@ int odvae_groupnorm_apply(const void* x, const float* stats, const float* gamma,
   return check_launch("gn_apply_kernel");
 }
 
+// statistics + apply in ONE launch for small fp16 feature maps (gn_small_fwd_kernel); ODVAE_ERR_SHAPE when the shape is not
+// served (the caller then uses odvae_groupnorm_stats + odvae_groupnorm_apply).
+int odvae_groupnorm_fwd_small(const void* x, const float* gamma, const float* beta, void* y, float* stats, int B, int HW,
+                              int C, int G, float eps, int silu, int act_dtype, int32_t* overflow_flags, void* stream) {
+  cudaStream_t st = static_cast<cudaStream_t>(stream);
+  if (act_dtype != ODVAE_F16 || !gn_small_ok(HW, C, G)) return ODVAE_ERR_SHAPE;
+  dim3 grid(C / 64, B);
+  if (silu)
+    gn_small_fwd_kernel<true><<<grid, 256, 0, st>>>(reinterpret_cast<const __half*>(x), gamma, beta, reinterpret_cast<__half*>(y), stats, HW, C, G, eps, overflow_flags);
+  else
+    gn_small_fwd_kernel<false><<<grid, 256, 0, st>>>(reinterpret_cast<const __half*>(x), gamma, beta, reinterpret_cast<__half*>(y), stats, HW, C, G, eps, overflow_flags);
+  return check_launch("gn_small_fwd_kernel");
+}
 // act_dtype: format of x (the saved forward input); grad_dtype: format of dy / dx_add / dx.
 // Supported pairs: (f32, f32), (bf16, bf16), (fp16, bf16), (fp16, fp16). pgrad_scale multiplies dgamma / dbeta (the inverse
 // of the static scale 16-bit activation gradients travel with in the all-fp16 mode; dx keeps the scale).
@@ -866,6 +1160,20 @@ int odvae_groupnorm_bwd(const void* x, const float* stats, const float* gamma, c
   float* part = reinterpret_cast<float*>(workspace);
   float* AB = part + static_cast<size_t>(B) * gn_ws_nsplit(B, HW) * C * 2;
   float* coef = AB + static_cast<size_t>(B) * C * 2;
+  if (combo == 3 && gn_small_ok(HW, C, G)) {  // small feature maps: one launch (see gn_small_bwd_kernel)
+    dim3 grid(C / 64, B);
+#define GN_LAUNCH_SMALL_BWD(S, A)                                                                                        \
+    gn_small_bwd_kernel<S, A><<<grid, 256, 0, st>>>(                                                                      \
+        reinterpret_cast<const __half*>(x), reinterpret_cast<const __half*>(dy), reinterpret_cast<const __half*>(dx_add), \
+        stats, gamma, beta, reinterpret_cast<__half*>(dx), AB, dgamma, dbeta, B, HW, C, G, accumulate, pgrad_scale,        \
+        overflow_flags);
+    if (silu && dx_add) GN_LAUNCH_SMALL_BWD(true, true)
+    else if (silu) GN_LAUNCH_SMALL_BWD(true, false)
+    else if (dx_add) GN_LAUNCH_SMALL_BWD(false, true)
+    else GN_LAUNCH_SMALL_BWD(false, false)
+#undef GN_LAUNCH_SMALL_BWD
+    return check_launch("gn_small_bwd_kernel");
+  }
   const int rows = GN_THREADS / (C / V);
   const size_t smem = static_cast<size_t>(2) * rows * C * sizeof(float);
   int ns;

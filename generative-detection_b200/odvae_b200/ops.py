@@ -596,6 +596,29 @@ def gn_apply_raw(x, stats, gamma, beta, silu, in_code=None, out_code=None, copy_
     return y if copy_code is None else (y, y2)
 
 
+def gn_small_ok(HW, C):
+    """Shapes odvae_groupnorm_fwd_small serves (include/odvae_b200.h): small fp16 feature maps, one launch."""
+    cpg = C // GROUPS
+    return HW <= 1024 and C % 64 == 0 and C % GROUPS == 0 and cpg >= 2 and 64 % cpg == 0 and C <= 4096
+
+
+def gn_forward(x, C, gamma, beta, silu, fmt, out_code=None):
+    """-> (stats, y = [silu](GN(x))). Statistics: attached by the producing conv's epilogue if there, else ONE fused launch
+    (statistics + apply) on the small fp16 feature maps, else the statistics pass followed by the apply pass."""
+    out_code = fmt.fwd if out_code is None else out_code
+    B, H, W, Cp = x.shape
+    attached = getattr(x, "_odvae_gn_stats", None)
+    if (attached is None and fmt.fwd == F16 and out_code == F16 and Cp == C and gn_small_ok(H * W, C)
+            and os.environ.get("ODVAE_GN_SMALL", "1") != "0"):
+        stats = torch.empty(B, GROUPS, 2, dtype=torch.float32, device=x.device)
+        y = torch.empty(B, H, W, C, dtype=buf_dtype(F16, x.dtype), device=x.device)
+        call("groupnorm_fwd_small", x, gamma.detach(), beta.detach(), y, stats, B, H * W, C, GROUPS, GN_EPS,
+             1 if silu else 0, F16, overflow_flags(x.device))
+        return stats, y
+    stats = gn_stats_of(x, C, fmt.fwd)
+    return stats, gn_apply_raw(x, stats, gamma, beta, silu, fmt.fwd, out_code)
+
+
 def gn_apply_pair(x, stats, gamma, beta, silu, fmt):
     """(forward operand, weight-gradient operand) of the conv that consumes this GroupNorm output."""
     if fmt.mixed:
@@ -843,10 +866,10 @@ class GroupNormAct(torch.autograd.Function):
     @staticmethod
     def forward(ctx, x, gamma, beta, silu, fmt=None, gscale=None):
         fmt = fmt if fmt is not None else format_of(x)
-        stats = gn_stats_of(x, x.shape[-1], fmt.fwd)
+        stats, y = gn_forward(x, x.shape[-1], gamma, beta, silu, fmt)
         ctx.silu, ctx.fmt, ctx.gscale = silu, fmt, gscale
         ctx.save_for_backward(x, stats, gamma, beta)
-        return gn_apply_raw(x, stats, gamma, beta, silu, fmt.fwd, fmt.fwd)
+        return y
 
     @staticmethod
     def backward(ctx, dy):
@@ -867,12 +890,20 @@ class ResBlock(torch.autograd.Function):
     @staticmethod
     def forward(ctx, x, g1, b1, w1, c1b, g2, b2, w2, c2b, wn, nb, blk):
         fmt = format_of(x, blk)
-        s1 = gn_stats_of(x, blk.cin, fmt.fwd)
-        a1, a1g = gn_apply_pair(x, s1, g1, b1, True, fmt)
+        if fmt.mixed:
+            s1 = gn_stats_of(x, blk.cin, fmt.fwd)
+            a1, a1g = gn_apply_pair(x, s1, g1, b1, True, fmt)
+        else:
+            s1, a1 = gn_forward(x, blk.cin, g1, b1, True, fmt)
+            a1g = a1
         h1 = conv_fwd_raw(a1, blk.spec1, w1, c1b, op=fmt.fwd, out=fmt.fwd, gn_stats=True)
         del a1
-        s2 = gn_stats_of(h1, blk.cout, fmt.fwd)
-        a2, a2g = gn_apply_pair(h1, s2, g2, b2, True, fmt)
+        if fmt.mixed:
+            s2 = gn_stats_of(h1, blk.cout, fmt.fwd)
+            a2, a2g = gn_apply_pair(h1, s2, g2, b2, True, fmt)
+        else:
+            s2, a2 = gn_forward(h1, blk.cout, g2, b2, True, fmt)
+            a2g = a2
         sc = x if wn is None else conv_fwd_raw(x, blk.spec_nin, wn, nb, op=fmt.fwd, out=fmt.fwd)
         out = conv_fwd_raw(a2, blk.spec2, w2, c2b, residual=sc, op=fmt.fwd, out=fmt.fwd, gn_stats=True)
         ctx.blk, ctx.fmt = blk, fmt
@@ -921,8 +952,7 @@ class AttnBlock(torch.autograd.Function):
         fmt = format_of(x, blk)
         ac = fmt.attn            # format code inside the block
         dt = buf_dtype(ac, x.dtype)
-        stats = gn_stats_of(x, C, fmt.fwd)
-        hn = gn_apply_raw(x, stats, gamma, beta, False, fmt.fwd, ac)
+        stats, hn = gn_forward(x, C, gamma, beta, False, fmt, out_code=ac)
         wqkv, bqkv = blk.fused_qkv(wq, bq, wk, bk, wv, bv, ac)
         qkv = torch.empty(B, H, W, 3 * C, dtype=dt, device=x.device)
         impl = conv_impl(ac, B, H, W, C, 3 * C, CONV_1x1)

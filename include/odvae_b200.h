@@ -180,6 +180,13 @@ int odvae_conv2d_fwd_gnstats(const void* x, const void* w_packed, const float* b
 int odvae_groupnorm_apply(const void* x, const float* stats, const float* gamma, const float* beta, void* y, void* y2,
                           int B, int HW, int C, int G, int silu, int in_dtype, int out_dtype, int out2_dtype,
                           int32_t* overflow_flags, void* stream);
+/* GroupNorm(32, eps)+[SiLU] statistics AND apply in one launch for small fp16 feature maps (HW <= 1024, C % 64 == 0: the
+ * 32x32 / 16x16 levels of model.py:38-39,33-35 whose three-launch form is launch-latency bound): y = [silu](GN(x)), stats =
+ * fp32 [B,G,2] (mean, rstd) for the backward. Served: act_dtype fp16, HW <= 1024, C % 64 == 0, channels per group in
+ * {2,4,...,64}; anything else returns ODVAE_ERR_SHAPE (use odvae_groupnorm_stats + odvae_groupnorm_apply).
+ * odvae_groupnorm_bwd picks its one-launch form for the same shapes by itself (fp16 x and fp16 gradients). */
+int odvae_groupnorm_fwd_small(const void* x, const float* gamma, const float* beta, void* y, float* stats, int B, int HW,
+                              int C, int G, float eps, int silu, int act_dtype, int32_t* overflow_flags, void* stream);
 /* dx = d/dx [silu](GN(x)) . dy (+ dx_add);  dgamma/dbeta fp32 [C] (accumulate != 0 adds).
  * act_dtype = format of x, grad_dtype = format of dy / dx_add / dx: (f32,f32), (bf16,bf16), (fp16,bf16), (fp16,fp16).
  * pgrad_scale multiplies dgamma / dbeta (inverse of the static activation-gradient scale of the all-fp16 mode). */

@@ -51,6 +51,47 @@ def test_groupnorm_fwd_bwd(dtype, shape, silu):
     assert torch.equal(dg, dg0) and torch.equal(db, db0)
 
 
+@pytest.mark.parametrize("shape", [(2, 16, 16, 512), (65, 32, 32, 256), (3, 25, 25, 64), (1, 8, 8, 128)])
+@pytest.mark.parametrize("silu", [False, True])
+def test_groupnorm_small_maps_one_launch(shape, silu, monkeypatch):
+    """fp16 feature maps of <= 1024 pixels: odvae_groupnorm_fwd_small (statistics + apply in one launch) and the one-launch
+    backward odvae_groupnorm_bwd picks for them (ticketed dgamma / dbeta sums) against torch autograd, against the
+    three-launch path, bit-stable over repeated calls."""
+    torch.manual_seed(7)
+    B, H, W, C = shape
+    x = (torch.randn(shape, device=DEV) * 1.5 + 0.3).half()
+    gamma = 1 + 0.1 * torch.randn(C, device=DEV)
+    beta = 0.1 * torch.randn(C, device=DEV)
+    dy = torch.randn(shape, device=DEV).half()
+    add = torch.randn(shape, device=DEV).half()
+    assert ops.gn_small_ok(H * W, C)
+    stats = torch.empty(B, ops.GROUPS, 2, device=DEV)
+    y = torch.empty_like(x)
+    ops.call("groupnorm_fwd_small", x, gamma, beta, y, stats, B, H * W, C, ops.GROUPS, ops.GN_EPS, int(silu), ops.F16,
+             ops.overflow_flags(x.device))
+    stats3 = ops.gn_stats_raw(x, C)
+    y3 = ops.gn_apply_raw(x, stats3, gamma, beta, silu)
+    xr = x.float().permute(0, 3, 1, 2).requires_grad_(True)
+    gr, br = gamma.clone().requires_grad_(True), beta.clone().requires_grad_(True)
+    y_ref = F.group_norm(xr, 32, gr, br, eps=1e-6)
+    if silu:
+        y_ref = F.silu(y_ref)
+    y_ref.backward(dy.float().permute(0, 3, 1, 2))
+    tol = GN_TOL[torch.float16]
+    assert rel(stats, stats3) < 1e-5
+    assert rel(y.permute(0, 3, 1, 2), y_ref) < tol and rel(y, y3) < 1e-3
+    outs = [ops.gn_bwd_raw(x, stats, gamma, beta, dy, silu, dx_add=add) for _ in range(3)]
+    dx0, dg0, db0 = ops.gn_bwd_raw(x, stats, gamma, beta, dy, silu)
+    torch.cuda.synchronize()
+    for dx, dg, db in outs[1:]:
+        assert torch.equal(dx, outs[0][0]) and torch.equal(dg, outs[0][1]) and torch.equal(db, outs[0][2])
+    dx, dg, db = outs[0]
+    assert rel(dx.float() - add.float(), xr.grad.permute(0, 2, 3, 1)) < 2 * tol
+    assert rel(dx0, xr.grad.permute(0, 2, 3, 1)) < tol
+    assert rel(dg, gr.grad) < tol and rel(db, br.grad) < tol
+    assert torch.equal(dg, dg0) and torch.equal(db, db0)
+
+
 @pytest.mark.parametrize("mean,std,gscale", [(8.0, 0.5, 1.0), (100.0, 3.0, 300.0), (-2.0, 40.0, 0.05)])
 def test_groupnorm_bwd_fp16_offsets_and_scales(mean, std, gscale):
     """fp16 x / fp16 gradients (the timed mode; packed-half2 kernels of csrc/groupnorm.cu): a mean far from zero must not

@@ -291,7 +291,7 @@ class EngineProfiler:
              "attn_dsoftmax", "upconv_fwd", "upconv_dgrad", "upconv_wgrad"}
     # memory-bound GroupNorm(+SiLU) calls, judged against the HBM roofline: algorithmic bytes at 2 B per
     # element are 2*E forward (stats + apply together: read x once, write y once) and 3*E backward (x, dy -> dx)
-    GN_NAMES = {"groupnorm_stats", "groupnorm_apply", "groupnorm_bwd"}
+    GN_NAMES = {"groupnorm_stats", "groupnorm_apply", "groupnorm_fwd_small", "groupnorm_bwd"}
 
     def __init__(self):
         self.records = []
@@ -303,6 +303,8 @@ class EngineProfiler:
             return 0.0  # its time counts, its bytes are the forward's 2*E attributed to the apply call
         if name == "groupnorm_apply":
             return 2.0 * a[6] * a[7] * a[8] * 2
+        if name == "groupnorm_fwd_small":  # (x, gamma, beta, y, stats, B, HW, C, ...): statistics + apply in one launch
+            return 2.0 * a[5] * a[6] * a[7] * 2
         return 3.0 * a[9] * a[10] * a[11] * 2
 
     def flops(self, name, a):
@@ -399,7 +401,7 @@ class EngineProfiler:
     def gn_summary(self, hbm_peak):
         torch.cuda.synchronize()
         out = {}
-        for tag, names in (("fwd", ("groupnorm_stats", "groupnorm_apply")), ("bwd", ("groupnorm_bwd",))):
+        for tag, names in (("fwd", ("groupnorm_stats", "groupnorm_apply", "groupnorm_fwd_small")), ("bwd", ("groupnorm_bwd",))):
             ms = sum(e0.elapsed_time(e1) for n, e0, e1, _ in self.gn if n in names)
             by = sum(b for n, _, _, b in self.gn if n in names)
             if ms > 0:

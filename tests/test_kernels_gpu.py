@@ -92,6 +92,26 @@ def test_groupnorm_small_maps_one_launch(shape, silu, monkeypatch):
     assert torch.equal(dg, dg0) and torch.equal(db, db0)
 
 
+@pytest.mark.parametrize("shape", [(2, 16, 16, 128), (2, 64, 64, 128)])  # one-launch small-map kernel / packed-half2 kernels
+def test_groupnorm_bwd_flags_saturated_fp16_gradient(shape):
+    """A dy value stored at +-65504 is a saturated store of its producer: both fp16 backward paths raise overflow flag [1]
+    (and only then), and the outputs stay finite (saturating stores)."""
+    torch.manual_seed(9)
+    B, H, W, C = shape
+    dev = torch.device("cuda", 0)
+    x = torch.randn(shape, device=DEV).half()
+    gamma, beta = torch.ones(C, device=DEV), torch.zeros(C, device=DEV)
+    dy = torch.randn(shape, device=DEV).half()
+    stats = ops.gn_stats_raw(x, C)
+    ops.read_overflow(dev)
+    ops.gn_bwd_raw(x, stats, gamma, beta, dy, True)
+    assert ops.read_overflow(dev) == (False, False)
+    dy[1, 3, 5, 7] = 65504.0
+    dx, dg, db = ops.gn_bwd_raw(x, stats, gamma, beta, dy, True)
+    assert ops.read_overflow(dev) == (False, True)
+    assert bool(torch.isfinite(dx.float()).all()) and bool(torch.isfinite(dg).all())
+
+
 @pytest.mark.parametrize("mean,std,gscale", [(8.0, 0.5, 1.0), (100.0, 3.0, 300.0), (-2.0, 40.0, 0.05)])
 def test_groupnorm_bwd_fp16_offsets_and_scales(mean, std, gscale):
     """fp16 x / fp16 gradients (the timed mode; packed-half2 kernels of csrc/groupnorm.cu): a mean far from zero must not

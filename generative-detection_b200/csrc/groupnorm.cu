@@ -773,8 +773,10 @@ __device__ __forceinline__ void gn_small_block_sums(GnSmallShared& sh, const flo
   __syncthreads();
 }
 
-template <bool SILU>
-__global__ void __launch_bounds__(256)
+// KEEP: HW <= 256 -> a thread owns at most 8 pixels of its channel vector, loaded ONCE (all loads in flight together) and kept
+// in registers across the reduction; otherwise phase 2 re-reads the slab (L1 / L2 hits), 4 loads in flight per tensor.
+template <bool SILU, bool KEEP>
+__global__ void __launch_bounds__(256, 2)
 gn_small_fwd_kernel(const __half* __restrict__ x, const float* __restrict__ gamma, const float* __restrict__ beta,
                     __half* __restrict__ y, float* __restrict__ stats, int HW, int C, int G, float eps,
                     int* __restrict__ overflow) {
@@ -782,19 +784,20 @@ gn_small_fwd_kernel(const __half* __restrict__ x, const float* __restrict__ gamm
   GN_SMALL_COORDS
   const uint4* xb = reinterpret_cast<const uint4*>(x) + base;
   uint4* yb = reinterpret_cast<uint4*>(y) + base;
+  constexpr int NP = KEEP ? 8 : 4;  // pixels per thread and round
   float s0[8], s1[8];
 #pragma unroll
   for (int j = 0; j < 8; ++j) s0[j] = s1[j] = 0.0f;
   bool sat = false;
-  for (int p = prow; p < HW; p += 128) {
-    uint4 v[4];
+  uint4 v[NP];
+  for (int p = prow; p < HW; p += 32 * NP) {
 #pragma unroll
-    for (int u = 0; u < 4; ++u) {
+    for (int u = 0; u < NP; ++u) {
       v[u] = make_uint4(0u, 0u, 0u, 0u);
       if (p + 32 * u < HW) v[u] = __ldg(xb + static_cast<long long>(p + 32 * u) * cvs);
     }
 #pragma unroll
-    for (int u = 0; u < 4; ++u) {
+    for (int u = 0; u < NP; ++u) {
       const __half* hv = reinterpret_cast<const __half*>(&v[u]);
 #pragma unroll
       for (int j = 0; j < 8; ++j) {
@@ -804,6 +807,7 @@ gn_small_fwd_kernel(const __half* __restrict__ x, const float* __restrict__ gamm
         s1[j] = fmaf(f, f, s1[j]);
       }
     }
+    if (KEEP) break;  // HW <= 32 * 8: one round, v[] stays live
   }
   gn_small_block_sums(sh, s0, s1, sub, prow);
   if (threadIdx.x < gps) {
@@ -832,13 +836,14 @@ gn_small_fwd_kernel(const __half* __restrict__ x, const float* __restrict__ gamm
     scale[j] = rstd * __ldg(gamma + c0 + j);
     shift[j] = __ldg(beta + c0 + j) - mean * scale[j];
   }
-  for (int p = prow; p < HW; p += 128) {
-    uint4 v[4];
+  for (int p = prow; p < HW; p += 32 * NP) {
+    if (!KEEP) {
 #pragma unroll
-    for (int u = 0; u < 4; ++u)
-      if (p + 32 * u < HW) v[u] = __ldg(xb + static_cast<long long>(p + 32 * u) * cvs);
+      for (int u = 0; u < NP; ++u)
+        if (p + 32 * u < HW) v[u] = __ldg(xb + static_cast<long long>(p + 32 * u) * cvs);
+    }
 #pragma unroll
-    for (int u = 0; u < 4; ++u) {
+    for (int u = 0; u < NP; ++u) {
       if (p + 32 * u < HW) {
         const __half* hv = reinterpret_cast<const __half*>(&v[u]);
         __half ov[8];
@@ -851,12 +856,13 @@ gn_small_fwd_kernel(const __half* __restrict__ x, const float* __restrict__ gamm
         yb[static_cast<long long>(p + 32 * u) * cvs] = *reinterpret_cast<const uint4*>(ov);
       }
     }
+    if (KEEP) break;
   }
   if (sat && overflow != nullptr) overflow[0] = 1;  // benign race: every writer stores the same value
 }
 
-template <bool SILU, bool ADD>
-__global__ void __launch_bounds__(256)
+template <bool SILU, bool ADD, bool KEEP>
+__global__ void __launch_bounds__(256, 2)
 gn_small_bwd_kernel(const __half* __restrict__ x, const __half* __restrict__ dy, const __half* __restrict__ dx_add,
                     const float* __restrict__ stats, const float* __restrict__ gamma, const float* __restrict__ beta,
                     __half* __restrict__ dx, float* __restrict__ AB, float* __restrict__ dgamma,
@@ -868,6 +874,7 @@ gn_small_bwd_kernel(const __half* __restrict__ x, const __half* __restrict__ dy,
   const uint4* dyb = reinterpret_cast<const uint4*>(dy) + base;
   const uint4* ab = ADD ? reinterpret_cast<const uint4*>(dx_add) + base : nullptr;
   uint4* dxb = reinterpret_cast<uint4*>(dx) + base;
+  constexpr int NP = KEEP ? 8 : 4;
   float mu[8], rs[8], sc[8], shf[8];
 #pragma unroll
   for (int j = 0; j < 8; ++j) {
@@ -881,10 +888,10 @@ gn_small_bwd_kernel(const __half* __restrict__ x, const __half* __restrict__ dy,
 #pragma unroll
   for (int j = 0; j < 8; ++j) s0[j] = s1[j] = 0.0f;
   bool sat = false;
-  for (int p = prow; p < HW; p += 64) {
-    uint4 xv[2], dv[2];
+  uint4 xv[NP], dv[NP];
+  for (int p = prow; p < HW; p += 32 * NP) {
 #pragma unroll
-    for (int u = 0; u < 2; ++u) {
+    for (int u = 0; u < NP; ++u) {
       xv[u] = dv[u] = make_uint4(0u, 0u, 0u, 0u);  // a missing pixel has dy = 0
       if (p + 32 * u < HW) {
         xv[u] = __ldg(xb + static_cast<long long>(p + 32 * u) * cvs);
@@ -892,9 +899,9 @@ gn_small_bwd_kernel(const __half* __restrict__ x, const __half* __restrict__ dy,
       }
     }
 #pragma unroll
-    for (int u = 0; u < 2; ++u) {
+    for (int u = 0; u < NP; ++u) {
       const __half* hx = reinterpret_cast<const __half*>(&xv[u]);
-      const __half* hd = reinterpret_cast<const __half*>(&dv[u]);
+      __half* hd = reinterpret_cast<__half*>(&dv[u]);
 #pragma unroll
       for (int j = 0; j < 8; ++j) {
         const float xf = __half2float(hx[j]);
@@ -905,6 +912,7 @@ gn_small_bwd_kernel(const __half* __restrict__ x, const __half* __restrict__ dy,
         s1[j] = fmaf(d, (xf - mu[j]) * rs[j], s1[j]);
       }
     }
+    if (KEEP) break;
   }
   gn_small_block_sums(sh, s0, s1, sub, prow);
   if (threadIdx.x < 64) {  // publish this image's row of the slab for the dgamma / dbeta sums
@@ -932,18 +940,20 @@ gn_small_bwd_kernel(const __half* __restrict__ x, const __half* __restrict__ dy,
     c2[j] = sh.ga[(sub * 8 + j) / cpg];
     c3[j] = sh.gb[(sub * 8 + j) / cpg];
   }
-  for (int p = prow; p < HW; p += 64) {
-    uint4 xv[2], dv[2], av[2];
+  for (int p = prow; p < HW; p += 32 * NP) {
+    uint4 av[NP];
 #pragma unroll
-    for (int u = 0; u < 2; ++u) {
+    for (int u = 0; u < NP; ++u) {
       if (p + 32 * u < HW) {
-        xv[u] = __ldg(xb + static_cast<long long>(p + 32 * u) * cvs);
-        dv[u] = __ldg(dyb + static_cast<long long>(p + 32 * u) * cvs);
+        if (!KEEP) {
+          xv[u] = __ldg(xb + static_cast<long long>(p + 32 * u) * cvs);
+          dv[u] = __ldg(dyb + static_cast<long long>(p + 32 * u) * cvs);
+        }
         if (ADD) av[u] = __ldg(ab + static_cast<long long>(p + 32 * u) * cvs);
       }
     }
 #pragma unroll
-    for (int u = 0; u < 2; ++u) {
+    for (int u = 0; u < NP; ++u) {
       if (p + 32 * u < HW) {
         const __half* hx = reinterpret_cast<const __half*>(&xv[u]);
         const __half* hd = reinterpret_cast<const __half*>(&dv[u]);
@@ -961,6 +971,7 @@ gn_small_bwd_kernel(const __half* __restrict__ x, const __half* __restrict__ dy,
         dxb[static_cast<long long>(p + 32 * u) * cvs] = *reinterpret_cast<const uint4*>(ov);
       }
     }
+    if (KEEP) break;
   }
   if (sat && overflow != nullptr) overflow[1] = 1;
   // ---- dgamma / dbeta: the last CTA of this slab (over the B images) adds the published rows in image order ----
@@ -1134,10 +1145,15 @@ int odvae_groupnorm_fwd_small(const void* x, const float* gamma, const float* be
   cudaStream_t st = static_cast<cudaStream_t>(stream);
   if (act_dtype != ODVAE_F16 || !gn_small_ok(HW, C, G)) return ODVAE_ERR_SHAPE;
   dim3 grid(C / 64, B);
-  if (silu)
-    gn_small_fwd_kernel<true><<<grid, 256, 0, st>>>(reinterpret_cast<const __half*>(x), gamma, beta, reinterpret_cast<__half*>(y), stats, HW, C, G, eps, overflow_flags);
-  else
-    gn_small_fwd_kernel<false><<<grid, 256, 0, st>>>(reinterpret_cast<const __half*>(x), gamma, beta, reinterpret_cast<__half*>(y), stats, HW, C, G, eps, overflow_flags);
+#define GN_LAUNCH_SMALL_FWD(S, K)                                                                                        \
+  gn_small_fwd_kernel<S, K><<<grid, 256, 0, st>>>(reinterpret_cast<const __half*>(x), gamma, beta,                        \
+                                                  reinterpret_cast<__half*>(y), stats, HW, C, G, eps, overflow_flags);
+  const bool keep = HW <= 256;
+  if (silu && keep) GN_LAUNCH_SMALL_FWD(true, true)
+  else if (silu) GN_LAUNCH_SMALL_FWD(true, false)
+  else if (keep) GN_LAUNCH_SMALL_FWD(false, true)
+  else GN_LAUNCH_SMALL_FWD(false, false)
+#undef GN_LAUNCH_SMALL_FWD
   return check_launch("gn_small_fwd_kernel");
 }
 // act_dtype: format of x (the saved forward input); grad_dtype: format of dy / dx_add / dx.
@@ -1163,7 +1179,9 @@ int odvae_groupnorm_bwd(const void* x, const float* stats, const float* gamma, c
   if (combo == 3 && gn_small_ok(HW, C, G)) {  // small feature maps: one launch (see gn_small_bwd_kernel)
     dim3 grid(C / 64, B);
 #define GN_LAUNCH_SMALL_BWD(S, A)                                                                                        \
-    gn_small_bwd_kernel<S, A><<<grid, 256, 0, st>>>(                                                                      \
+    if (HW <= 256) GN_LAUNCH_SMALL_BWD2(S, A, true) else GN_LAUNCH_SMALL_BWD2(S, A, false)
+#define GN_LAUNCH_SMALL_BWD2(S, A, K)                                                                                    \
+    gn_small_bwd_kernel<S, A, K><<<grid, 256, 0, st>>>(                                                                      \
         reinterpret_cast<const __half*>(x), reinterpret_cast<const __half*>(dy), reinterpret_cast<const __half*>(dx_add), \
         stats, gamma, beta, reinterpret_cast<__half*>(dx), AB, dgamma, dbeta, B, HW, C, G, accumulate, pgrad_scale,        \
         overflow_flags);
@@ -1172,6 +1190,7 @@ int odvae_groupnorm_bwd(const void* x, const float* stats, const float* gamma, c
     else if (dx_add) GN_LAUNCH_SMALL_BWD(false, true)
     else GN_LAUNCH_SMALL_BWD(false, false)
 #undef GN_LAUNCH_SMALL_BWD
+#undef GN_LAUNCH_SMALL_BWD2
     return check_launch("gn_small_bwd_kernel");
   }
   const int rows = GN_THREADS / (C / V);

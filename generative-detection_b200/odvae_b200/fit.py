@@ -24,6 +24,7 @@ import os
 import torch
 import torch.distributed as dist
 
+from . import ops
 from .trainer import TrainStep
 
 PL_VERSION = "1.9.0"  # environment.yml:277 of the reference
@@ -82,6 +83,7 @@ class Fit:
                     p.grad.div_(self.world)
             torch.nn.utils.clip_grad_norm_(params, self.max_grad_norm)
         self.opt_disc.step()
+        ops.refresh_param_caches()  # the discriminator's packed weights, in one multi-tensor launch
 
     def fit(self, loader, max_steps=None, max_epochs=1):
         """Runs until `max_steps` optimizer steps (Lightning's `max_steps` unit) or `max_epochs` passes over `loader`."""

@@ -31,6 +31,14 @@ def bump_weight_epoch():
     _WEIGHT_EPOCH[0] += 1
 
 
+def bump_param_epochs(params):
+    """An optimizer updated exactly these parameters in place (the fused Adam kernel does not touch `_version`): only the
+    packed copies of THESE parameters go stale. With a global epoch the discriminator's optimizer step invalidated every
+    packed autoencoder / LPIPS weight as well (216 single-weight re-pack launches per batch of the full objective)."""
+    for p in params:
+        p._odvae_epoch = getattr(p, "_odvae_epoch", 0) + 1
+
+
 def act_code(dtype):
     if dtype == torch.bfloat16:
         return BF16
@@ -261,7 +269,7 @@ def geom_k(geom):
 # parameter-side caches: packed weights / padded biases, refreshed when the parameter changes
 # ------------------------------------------------------------------------------------------------
 _CACHES = weakref.WeakSet()
-_MT_PACK = {"key": None, "table": None, "n": 0, "blocks": 0}
+_MT_PACK = {}  # signature of a set of stale packs -> device table (one per optimizer: autoencoder, discriminator)
 
 
 class ParamCache:
@@ -275,7 +283,8 @@ class ParamCache:
 
     @staticmethod
     def _stamp(params):
-        return tuple(p._version for p in params) + tuple(p.data_ptr() for p in params) + (_WEIGHT_EPOCH[0],)
+        return (tuple(p._version for p in params) + tuple(p.data_ptr() for p in params) +
+                tuple(getattr(p, "_odvae_epoch", 0) for p in params) + (_WEIGHT_EPOCH[0],))
 
     def get(self, key, params, build, desc=None):
         stamp = self._stamp(params)
@@ -307,7 +316,8 @@ def refresh_param_caches():
     if not mt:
         return
     sig = tuple((d[0].data_ptr(), val.data_ptr(), d[1], d[2], d[3], d[4], d[5]) for _, _, _, val, _, _, d in mt)
-    if _MT_PACK["key"] != sig:
+    entry = _MT_PACK.get(sig)
+    if entry is None:
         rows, first = [], 0
         for _, _, _, val, _, _, (w, geom, coutp, cinp, which, code) in mt:
             k = geom_k(geom)
@@ -315,8 +325,9 @@ def refresh_param_caches():
             rows.append([w.data_ptr(), val.data_ptr(), w.shape[0], w.shape[1], k, coutp, cinp, flags, code, first])
             first += call("pack_conv_weights_mt_blocks", coutp, cinp, geom)
         host = torch.tensor(rows, dtype=torch.int64)
-        _MT_PACK.update(key=sig, table=host.to(mt[0][3].device), n=len(rows), blocks=first)
-    call("pack_conv_weights_mt", _MT_PACK["table"], _MT_PACK["n"], _MT_PACK["blocks"])
+        # (never evicted: a table is ~25 KB, and a CUDA-graph capture must find the table its warm-up steps built)
+        entry = _MT_PACK[sig] = dict(table=host.to(mt[0][3].device), n=len(rows), blocks=first)
+    call("pack_conv_weights_mt", entry["table"], entry["n"], entry["blocks"])
     for c, key, new, val, params, build, desc in mt:
         c.store[key] = (new, val, params, build, desc)
 

@@ -118,7 +118,7 @@ class FusedAdam(torch.optim.Optimizer):
                 self.grad_norm_sq = norm
             ops.call("mt_adam_step_dev", plan["table"], plan["rows"], float(group["lr"]), float(b1), float(b2),
                      float(group["eps"]), norm, float(self.max_grad_norm or 0.0), float(self.grad_scale))
-        ops.bump_weight_epoch()
+            ops.bump_param_epochs(params)
         return loss
 
 

@@ -42,6 +42,13 @@ struct TcParams {
   // read it through operand descriptors that start 0 / 1 / 2 pixel rows into the slab. `stages` then counts the
   // 16 KiB weight stages and `halo_slabs` the slab ring.
   int halo, halo_slabs;
+  // halo == 2: the W = 128 form. The N tile is two image rows (y0, y0 + 1); a slab holds input rows (y0 + ky - 1, y0 + ky) of
+  // one 64-channel chunk pixel-interleaved -- slab row 2 (x + 1) + r -- fetched by ONE TMA box (64 ch, 2 rows, 130 px) over a
+  // (c, y, x, b) view of the NHWC tensor, so accumulator column n = 2 x + row reads slab row n + 2 kx: a horizontal tap is a
+  // 256-byte shift of the operand descriptor. The epilogue maps column n back to (x = n / 2, row = n % 2). Operand traffic
+  // per 128 x 256 tile: 288 KB of weights + 200 KB of slabs instead of + 576 KB of nine shifted gathers (these layers were
+  // bound by the ~72 GB/s an SM gets from L2: 860 TF/s). halo2_ok: conv_common's candidate mark, resolved in launch_tc.
+  int halo2_ok;
   // WGRAD k-chunk geometry (box kbw x kbh = 64 output pixels)
   int kbw_log2, kch_x, kch_y, split_k, kch_per_split;
   int wg_T, kch_total;  // taps accumulated per tile (1 or 3 = one filter row); pixel chunks over all splits

@@ -131,12 +131,33 @@ static size_t tc_halo_smem_bytes(int stages, int slabs) {
 
 static int launch_tc(EngineDesc& d, cudaStream_t stream) {
   if (!d.tc_ok) return ODVAE_ERR_SHAPE;
+  TcParams& p = d.p;
+  OperandView viewA = d.A;
+  uint32_t boxA[5] = {d.boxA[0], d.boxA[1], d.boxA[2], d.boxA[3], d.boxA[4]};
+  {
+    // W = 128 halo tiles (conv_common marked the candidate): needs the interleaved epilogue = fp16 output, pixel stride 128
+    static const bool halo2_on = [] {
+      const char* v = getenv("ODVAE_CONV_HALO2");
+      return !(v && v[0] == '0');
+    }();
+    if (halo2_on && TC_FAST_EPI && p.kind == KIND_CONV && p.halo2_ok && p.halo == 0 && p.out_mode == OUT_F16 && p.oX == 128 &&
+        p.a_fmt == FMT_F16) {
+      p.halo = 2;
+      p.halo_slabs = 4;
+      // (c, x, y, b) -> (c, y, x, b): a box of 64 channels x 2 rows x 130 pixels lands in shared memory as [x][row][c]
+      const long long d1 = viewA.dims[1], s1 = viewA.strides[1];
+      viewA.dims[1] = viewA.dims[2];
+      viewA.strides[1] = viewA.strides[2];
+      viewA.dims[2] = d1;
+      viewA.strides[2] = s1;
+      boxA[0] = 64; boxA[1] = 2; boxA[2] = TC_HALO_BOX; boxA[3] = 1;
+    }
+  }
   CUtensorMap tmA, tmB;
-  int st = make_tmap_bf16(&tmA, d.A, d.boxA);
+  int st = make_tmap_bf16(&tmA, viewA, boxA);
   if (st != ODVAE_OK) return st;
   st = make_tmap_bf16(&tmB, d.B, d.boxB);
   if (st != ODVAE_OK) return st;
-  TcParams& p = d.p;
   const int b_rows = p.kind == KIND_WGRAD ? p.BN * p.wg_T : p.BN;
   size_t smem;
   if (p.halo && p.kind == KIND_CONV) {
@@ -216,7 +237,7 @@ static int launch_tc(EngineDesc& d, cudaStream_t stream) {
     }();
     const bool aligned = (p.n_valid % 8) == 0 && (p.oX % 8) == 0 && (p.oY % 8) == 0 && (p.oB % 8) == 0 && (p.o0 % 8) == 0;
     // (only where a residual is added: plain stores measured no faster through the staging buffer)
-    if (epi_stage_on && p.kind == KIND_CONV && p.swap && aligned && p.residual != nullptr &&
+    if (epi_stage_on && p.halo != 2 && p.kind == KIND_CONV && p.swap && aligned && p.residual != nullptr &&
         (p.out_mode == OUT_BF16 || p.out_mode == OUT_F16)) {
       const size_t limit = 227 * 1024;
       if (p.halo && smem + 16384 + 128 > limit) {  // give one weight stage to the epilogue
@@ -495,6 +516,14 @@ static void conv_common(EngineDesc& d, int Bn, int Ho, int Wo, int gatherC, int 
     p.halo_slabs = 4;
     d.boxA[0] = 64; d.boxA[1] = TC_HALO_BOX; d.boxA[2] = 1; d.boxA[3] = 1;
   }
+  // Halo mode for W = 128 (engine_desc.h `halo == 2`): the N tile is TWO image rows; one slab = input rows (y, y + 1) of a
+  // 64-channel chunk, pixel-interleaved ([x][row][c], written by ONE TMA box over a (c, y, x, b) view of the tensor), so the
+  // tile's 256 pixels (x, row) are 256 consecutive slab rows and a horizontal tap is a shift of two rows. Candidate only:
+  // launch_tc turns it on when the output format allows the interleaved epilogue (fp16, pixel stride 128).
+  p.halo2_ok = 0;
+  if (p.swap && !g_disable_halo && p.ntaps == 9 && p.sp_rank == 4 && Wo == 128 && bw == 128 && (Ho % 2) == 0 &&
+      out_mode == OUT_BF16 && p.tap_dx[0] == -1 && p.tap_dy[0] == -1 && p.tap_dx[8] == 1 && p.tap_dy[8] == 1)
+    p.halo2_ok = 1;
   p.alpha = 1.0f;
   d.conv_batch = Bn;
   d.conv_out_h = Ho;

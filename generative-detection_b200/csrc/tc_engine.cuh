@@ -201,8 +201,13 @@ tc_engine_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant_
             uint64_t* sb = &sfull_bar[ss];
             mbar_arrive_expect_tx(sb, 2u * TC_HALO_BOX * 128u);
             uint8_t* dst = sB + static_cast<size_t>(ss) * TC_SLAB_BYTES;
-            tma_load_4d(dst, &tmA, sb, cc * 64, tc.x0 - 1, tc.y0 + ry - 1, tc.b);
-            tma_load_4d(dst + TC_HALO_BOX * 128, &tmA, sb, cc * 64, tc.x0 + TC_HALO_BOX - 1, tc.y0 + ry - 1, tc.b);
+            if (p.halo == 2) {
+              // W = 128: rows (y0 + ry - 1, y0 + ry), pixels -1 .. 128, pixel-interleaved; the view's coordinates are (c, y, x, b)
+              tma_load_4d(dst, &tmA, sb, cc * 64, tc.y0 + ry - 1, -1, tc.b);
+            } else {
+              tma_load_4d(dst, &tmA, sb, cc * 64, tc.x0 - 1, tc.y0 + ry - 1, tc.b);
+              tma_load_4d(dst + TC_HALO_BOX * 128, &tmA, sb, cc * 64, tc.x0 + TC_HALO_BOX - 1, tc.y0 + ry - 1, tc.b);
+            }
             if (++ss == nslabs) {
               ss = 0;
               sph ^= 1u;
@@ -342,7 +347,8 @@ tc_engine_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant_
             mbar_wait(&full_bar[stage], phase);
             tc_fence_after();
             const uint32_t a_base = smem_u32(sA + static_cast<size_t>(stage) * TC_A_BYTES);
-            const uint32_t b_base = slab + static_cast<uint32_t>(rx) * 128u;  // pixel x + (rx - 1) <-> slab row x + rx
+            // pixel x + (rx - 1) <-> slab row x + rx (halo == 2: two interleaved image rows, slab row 2 (x + rx) + r)
+            const uint32_t b_base = slab + static_cast<uint32_t>(rx) * (p.halo == 2 ? 256u : 128u);
 #pragma unroll
             for (int k = 0; k < TC_BLOCK_K / 16; ++k) {
               umma_bf16(d_tmem, make_smem_desc_sw128(a_base + k * 32, 0, 1024), make_smem_desc_sw128(b_base + k * 32, 0, 1024),
@@ -523,8 +529,12 @@ tc_engine_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant_
         // ---- swapped-role conv: lane = output channel, column = output pixel. This warp owns the 128 pixels of
         // pixel box (2 * n_tile + half); for every pixel the 32 lanes write 32 consecutive channels (one 64-byte
         // segment), and bias / per-channel work is a per-thread scalar.
+        // halo == 2 (W = 128, two interleaved rows): accumulator column n = 2 x + row; this warp's 128 columns are pixels
+        // x = 64 half .. 64 half + 63 of rows pb_y and pb_y + 1
+        const bool il_rt = p.halo == 2;
         int pb_b, pb_y, pb_x;
-        decode_pixel_box(p, 2 * tc.n_tile + half, pb_b, pb_y, pb_x);
+        decode_pixel_box(p, il_rt ? 2 * tc.n_tile : 2 * tc.n_tile + half, pb_b, pb_y, pb_x);
+        if (il_rt) pb_x = 64 * half;
         const int n = m0 + r;
         const bool ch_ok = n < p.n_valid;
         const float bias = (p.bias != nullptr && ch_ok) ? __ldg(p.bias + n) : 0.0f;
@@ -554,12 +564,17 @@ tc_engine_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant_
         // Both become compile-time constants, so the 2-byte accesses of a batch use ONE base register + immediate offsets
         // and the format select disappears: 3 issue slots per element instead of 7.5 (6 instead of 13.5 with a residual;
         // SASS of the generic path: predicated bf16 AND fp16 packs with four FMNMX clamps per pair, IADD3 + IADD3.X per access).
-        auto emit = [&](uint32_t (&v)[32], int pi0, auto fast) {
+        auto emit = [&](uint32_t (&v)[32], int pi0, auto fast, auto ilv) {
           constexpr bool kFast = decltype(fast)::value;
+          constexpr bool kIl = decltype(ilv)::value;  // interleaved rows (only together with kFast)
           const bool halfp = kFast ? true : halfp_rt;
           const long long sx = kFast ? 128ll : sx_rt;
-          const int yy = pb_y + (pi0 >> p.bw_log2), xx = pb_x + (pi0 & ((1 << p.bw_log2) - 1));
+          const int yy = kIl ? pb_y : pb_y + (pi0 >> p.bw_log2);
+          const int xx = kIl ? pb_x + (pi0 >> 1) : pb_x + (pi0 & ((1 << p.bw_log2) - 1));
           const long long base = base0 + static_cast<long long>(yy) * p.oY + static_cast<long long>(xx) * sx;
+          const long long base1 = base + p.oY;  // kIl: odd columns are the pixels of the second row
+          // element i of the batch: next pixel in x, or (x + i / 2, row i % 2) when the rows are interleaved
+          auto at = [&](int i) -> long long { return kIl ? ((i & 1) ? base1 : base) + (i >> 1) * sx : base + i * sx; };
           if (p.out_mode == OUT_NCHW_F32) {
             // thin output conv (decoder.conv_out, Cout = 3 padded to the 128-row weight tile): lane = channel, the 32
             // pixels of the batch are consecutive in x -> 128 contiguous bytes of the NCHW fp32 result per valid lane
@@ -624,15 +639,15 @@ tc_engine_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant_
             if (R16 != nullptr) {
               uint16_t rr[32];
 #pragma unroll
-              for (int i = 0; i < 32; ++i) rr[i] = __ldg(R16 + base + i * sx);
+              for (int i = 0; i < 32; ++i) rr[i] = __ldg(R16 + at(i));
 #pragma unroll
               for (int i = 0; i < 32; ++i) f[i] += unpack_16x2(static_cast<uint32_t>(rr[i]), halfp).x;
             }
 #pragma unroll
             for (int i = 0; i < 32; i += 2) {
               const uint32_t pk = pack_16x2(f[i], f[i + 1], halfp);
-              D16[base + i * sx] = static_cast<uint16_t>(pk & 0xffffu);
-              D16[base + (i + 1) * sx] = static_cast<uint16_t>(pk >> 16);
+              D16[at(i)] = static_cast<uint16_t>(pk & 0xffffu);
+              D16[at(i + 1)] = static_cast<uint16_t>(pk >> 16);
               if (p.gn_part != nullptr) {  // statistics of the STORED (rounded) values, as the separate pass sees them
                 const float2 r = unpack_16x2(pk, halfp);
                 gs0 += r.x;
@@ -652,34 +667,37 @@ tc_engine_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant_
             for (int j = 0; j < 4; ++j) {
               if (j == 0 && stg != nullptr) continue;
               const int pi = 32 * j + lane;
-              const int yy = pb_y + (pi >> p.bw_log2), xx = pb_x + (pi & ((1 << p.bw_log2) - 1));
+              const int yy = il_rt ? pb_y + (pi & 1) : pb_y + (pi >> p.bw_log2);
+              const int xx = il_rt ? pb_x + (pi >> 1) : pb_x + (pi & ((1 << p.bw_log2) - 1));
               const uint16_t* a = R16 + static_cast<long long>(pb_b) * p.oB + p.o0 + (m0 + q * 32) +
                                   static_cast<long long>(yy) * p.oY + static_cast<long long>(xx) * sx;
               asm volatile("prefetch.global.L2 [%0];" ::"l"(a));
             }
           }
         }
-        auto drain = [&](auto fast) {
+        auto drain = [&](auto fast, auto ilv) {
           mbar_wait(&tfull_bar[acc], acc_phase);
           tc_fence_after();
           uint32_t va[32], vb[32];
           tmem_ld_x32(t_row + static_cast<uint32_t>(c_begin), va);
           tmem_ld_wait();
           tmem_ld_x32(t_row + static_cast<uint32_t>(c_begin + 32), vb);
-          emit(va, 0, fast);
+          emit(va, 0, fast, ilv);
           tmem_ld_wait();
           tmem_ld_x32(t_row + static_cast<uint32_t>(c_begin + 64), va);
-          emit(vb, 32, fast);
+          emit(vb, 32, fast, ilv);
           tmem_ld_wait();
           tmem_ld_x32(t_row + static_cast<uint32_t>(c_begin + 96), vb);
-          emit(va, 64, fast);
+          emit(va, 64, fast, ilv);
           tmem_ld_wait();
-          emit(vb, 96, fast);
+          emit(vb, 96, fast, ilv);
         };
-        if (TC_FAST_EPI && halfp_rt && sx_rt == 128 && stg == nullptr && p.out_mode != OUT_NCHW_F32)
-          drain(std::true_type{});
+        if (TC_FAST_EPI && il_rt)  // (the host turns halo == 2 on only where the fast path's conditions hold)
+          drain(std::true_type{}, std::true_type{});
+        else if (TC_FAST_EPI && halfp_rt && sx_rt == 128 && stg == nullptr && p.out_mode != OUT_NCHW_F32)
+          drain(std::true_type{}, std::false_type{});
         else
-          drain(std::false_type{});
+          drain(std::false_type{}, std::false_type{});
         if (p.gn_part != nullptr && ch_ok) {
           const int boxes = p.tiles_x * p.tiles_y;  // pixel boxes per image
           const int box = 2 * tc.n_tile + half - pb_b * boxes;

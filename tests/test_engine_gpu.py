@@ -95,10 +95,11 @@ def test_conv_fwd_dgrad_wgrad(impl, dtype, geom, case):
 
 
 @pytest.mark.parametrize("dtype", [torch.bfloat16, torch.float16])
-@pytest.mark.parametrize("B,H,W", [(2, 256, 256), (1, 64, 512), (3, 32, 512)])
+@pytest.mark.parametrize("B,H,W", [(2, 256, 256), (1, 64, 512), (3, 32, 512), (3, 128, 128), (5, 6, 128)])
 def test_conv_halo_slabs_match_tap_gather(dtype, B, H, W):
-    """3x3 stride-1 at W = 256 (one tile per image row) and W = 512 (two tiles per row, the configs[4] crops; the seam
-    at x = 256 is an interior halo, not zero padding): the shared-memory halo-slab path and the per-tap TMA gather accumulate the same
+    """3x3 stride-1 at W = 256 (one tile per image row), W = 512 (two tiles per row, the configs[4] crops; the seam
+    at x = 256 is an interior halo, not zero padding) and W = 128 (fp16 only: one tile = two pixel-interleaved image rows,
+    engine_desc.h halo == 2): the shared-memory halo-slab path and the per-tap TMA gather accumulate the same
     products in the same order per output element only up to the K ordering (chunk-major vs tap-major), so they agree
     to fp32 summation noise; both are checked against torch fp32."""
     from odvae_b200 import lib
@@ -115,15 +116,17 @@ def test_conv_halo_slabs_match_tap_gather(dtype, B, H, W):
         for on in (1, 0):
             lib.call("set_conv_halo", on)
             y = K.conv_fwd(x, wp, b, C, CONV_3x3_S1, IMPL_TC, residual=res)
-            dx = K.conv_dgrad(x, wd, C, CONV_3x3_S1, IMPL_TC, (H, W))  # dgrad always stores bf16 (gradient format)
+            dx = K.conv_dgrad(x, wd, C, CONV_3x3_S1, IMPL_TC, (H, W))  # dx in the operand format
             # wgrad: same products in the same K order -> bit-identical (gradients are bf16 in every 16-bit mode)
             dw, _ = K.conv_wgrad(x.to(torch.bfloat16), res.to(torch.bfloat16), C, C, CONV_3x3_S1, IMPL_TC)
             torch.cuda.synchronize()
-            outs.append((y.float(), dx.view(torch.bfloat16).float(), dw))
+            outs.append((y.float(), dx.float(), dw))
     finally:
         lib.call("set_conv_halo", 1)
     ref = ref_conv(x, w.to(dtype).float(), b, CONV_3x3_S1) + res.float().permute(0, 3, 1, 2)
     assert rel_err(outs[0][0].permute(0, 3, 1, 2), ref) < 1e-2
+    ref_dx = F.conv_transpose2d(x.float().permute(0, 3, 1, 2), w.to(dtype).float(), padding=1)
+    assert rel_err(outs[0][1].permute(0, 3, 1, 2), ref_dx) < 1e-2
     assert rel_err(outs[0][0], outs[1][0]) < 4e-3 and rel_err(outs[0][1], outs[1][1]) < 4e-3
     # image borders: halo columns / rows must be exact zeros, not neighbouring-row pixels
     edge = torch.cat([outs[0][0][:, :, 0], outs[0][0][:, :, -1], outs[0][0][:, 0], outs[0][0][:, -1]], 1)

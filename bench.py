@@ -287,11 +287,11 @@ def run_reference(args):
 class EngineProfiler:
     """Wraps ops.call for ONE extra (untimed) step: brackets each conv/GEMM C-ABI call with CUDA events on the
     launching stream and adds up the algorithmic FLOPs (2*M*N*K of the real, unpadded problem)."""
-    NAMES = {"conv2d_fwd", "conv2d_fwd_gnstats", "conv2d_dgrad", "conv2d_wgrad", "gemm_bf16", "gemm_16", "attn_scores_softmax",
+    NAMES = {"conv2d_fwd", "conv2d_fwd_gnstats", "conv2d_dgrad", "conv2d_dgrad_gnbwd", "conv2d_wgrad", "gemm_bf16", "gemm_16", "attn_scores_softmax",
              "attn_dsoftmax", "upconv_fwd", "upconv_dgrad", "upconv_wgrad"}
     # memory-bound GroupNorm(+SiLU) calls, judged against the HBM roofline (SURVEY 8d): algorithmic bytes at 2 B per
     # element are 2*E forward (stats + apply together: read x once, write y once) and 3*E backward (x, dy -> dx)
-    GN_NAMES = {"groupnorm_stats", "groupnorm_apply", "groupnorm_fwd_small", "groupnorm_bwd"}
+    GN_NAMES = {"groupnorm_stats", "groupnorm_apply", "groupnorm_fwd_small", "groupnorm_bwd", "groupnorm_bwd_from_partials"}
 
     def __init__(self):
         self.records = []
@@ -305,6 +305,8 @@ class EngineProfiler:
             return 2.0 * a[6] * a[7] * a[8] * 2
         if name == "groupnorm_fwd_small":  # (x, gamma, beta, y, stats, B, HW, C, ...): statistics + apply in one launch
             return 2.0 * a[5] * a[6] * a[7] * 2
+        if name == "groupnorm_bwd_from_partials":  # (x, stats, gamma, beta, dy, dx_add, dx, dgamma, dbeta, part, nbox, B, HW, C, ..)
+            return 3.0 * a[11] * a[12] * a[13] * 2  # its reduce pass ran inside the dgrad epilogue (counted with the engine calls)
         return 3.0 * a[9] * a[10] * a[11] * 2
 
     def flops(self, name, a):
@@ -331,6 +333,9 @@ class EngineProfiler:
         elif name == "conv2d_dgrad":
             B, H, W, CinP, CoutP, geom = a[4], a[5], a[6], a[7], a[8], a[9]
             cin, cout = self._real(CinP), self._real(CoutP)
+        elif name == "conv2d_dgrad_gnbwd":  # (dy, w, dx, gn_x, stats, gamma, beta, part, bytes, B, H, W, CinP, CoutP, geom, ..)
+            B, H, W, CinP, CoutP, geom = a[9], a[10], a[11], a[12], a[13], a[14]
+            cin, cout = CinP, CoutP
         else:
             B, H, W, Cin, Cout, geom = a[4], a[5], a[6], a[9], a[10], a[11]
             cin, cout = Cin, Cout
@@ -356,6 +361,8 @@ class EngineProfiler:
             return "fwd+gnstats B%d %dx%d %d->%d g%d" % (a[6], a[7], a[8], a[9], a[10], a[11])
         if name == "conv2d_dgrad":
             return "dgrad B%d %dx%d %d<-%d g%d" % (a[4], a[5], a[6], a[7], a[8], a[9])
+        if name == "conv2d_dgrad_gnbwd":
+            return "dgrad+gnbwd sums B%d %dx%d %d<-%d g%d" % (a[9], a[10], a[11], a[12], a[13], a[14])
         return "wgrad B%d %dx%d %dx%d g%d" % (a[4], a[5], a[6], a[7], a[8], a[11])
 
     @staticmethod
@@ -401,7 +408,7 @@ class EngineProfiler:
     def gn_summary(self, hbm_peak):
         torch.cuda.synchronize()
         out = {}
-        for tag, names in (("fwd", ("groupnorm_stats", "groupnorm_apply", "groupnorm_fwd_small")), ("bwd", ("groupnorm_bwd",))):
+        for tag, names in (("fwd", ("groupnorm_stats", "groupnorm_apply", "groupnorm_fwd_small")), ("bwd", ("groupnorm_bwd", "groupnorm_bwd_from_partials"))):
             ms = sum(e0.elapsed_time(e1) for n, e0, e1, _ in self.gn if n in names)
             by = sum(b for n, _, _, b in self.gn if n in names)
             if ms > 0:

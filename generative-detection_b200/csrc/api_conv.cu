@@ -86,6 +86,42 @@ int odvae_conv2d_dgrad(const void* dy, const void* w_packed_dgrad, const void* d
   return ODVAE_OK;
 }
 
+// dgrad of a 128-channel 3x3 / 1x1 stride-1 conv whose result is the gradient of a GroupNorm+SiLU output: the same launch also
+// writes the two GroupNorm-backward sums per (pixel box, channel) (engine_desc.h gnb_*), so odvae_groupnorm_bwd_from_partials
+// needs no reduce pass over x and dy. Served by the tcgen05 swapped-role tiles with the fp16 epilogue only.
+static bool gnbwd_served(const EngineDesc* ds, int n, int CinP, int G) {
+  return n == 1 && ds[0].tc_ok && ds[0].p.swap && G > 0 && CinP % G == 0 && ds[0].p.oX == 128 && TC_FAST_EPI;
+}
+
+size_t odvae_conv2d_dgrad_gnbwd_workspace_bytes(int B, int H, int W, int CinP, int CoutP, int geom, int G) {
+  EngineDesc ds[4];
+  int n = 0;
+  if (describe_conv_dgrad(ds, &n, nullptr, nullptr, 2, nullptr, nullptr, B, H, W, CinP, CoutP, geom) != ODVAE_OK) return 0;
+  if (!gnbwd_served(ds, n, CinP, G)) return 0;
+  return static_cast<size_t>(B) * ds[0].p.tiles_x * ds[0].p.tiles_y * CinP * 2 * sizeof(float);
+}
+
+int odvae_conv2d_dgrad_gnbwd(const void* dy, const void* w_packed_dgrad, void* dx, const void* gn_x, const float* gn_stats,
+                             const float* gamma, const float* beta, float* part, size_t part_bytes, int B, int H, int W,
+                             int CinP, int CoutP, int geom, int G, int act_dtype, void* stream) {
+  if (act_dtype != ODVAE_F16) return ODVAE_ERR_SHAPE;
+  EngineDesc ds[4];
+  int n = 0;
+  int st = describe_conv_dgrad(ds, &n, dy, w_packed_dgrad, 2, nullptr, dx, B, H, W, CinP, CoutP, geom);
+  if (st != ODVAE_OK) return st;
+  if (!gnbwd_served(ds, n, CinP, G)) return ODVAE_ERR_SHAPE;
+  TcParams& p = ds[0].p;
+  if (part_bytes < static_cast<size_t>(B) * p.tiles_x * p.tiles_y * CinP * 2 * sizeof(float)) return ODVAE_ERR_WORKSPACE;
+  p.out_mode = OUT_F16;
+  p.gnb_x = gn_x;
+  p.gnb_stats = gn_stats;
+  p.gnb_gamma = gamma;
+  p.gnb_beta = beta;
+  p.gnb_part = part;
+  p.gnb_cpg = CinP / G;
+  return run_engine(ds[0], ODVAE_IMPL_TC, act_dtype, static_cast<cudaStream_t>(stream));
+}
+
 size_t odvae_conv2d_wgrad_workspace_bytes(int B, int H, int W, int CinP, int CoutP, int geom, int impl) {
   EngineDesc d;
   if (describe_conv_wgrad(d, nullptr, nullptr, nullptr, B, H, W, CinP, CoutP, geom, impl) != ODVAE_OK) return 0;

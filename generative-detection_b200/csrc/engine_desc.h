@@ -2,6 +2,12 @@
 #pragma once
 #include <stdint.h>
 
+// A/B switch: the compile-time-specialised swapped-role conv epilogue (fp16, pixel stride 128; tc_engine.cuh `emit`), which the
+// W = 128 halo tiles and the fused GroupNorm-backward sums build on
+#ifndef TC_FAST_EPI
+#define TC_FAST_EPI 1
+#endif
+
 namespace odvae {
 
 enum { KIND_GEMM = 0, KIND_CONV = 1, KIND_WGRAD = 2 };
@@ -13,7 +19,9 @@ enum {
   TC_SPEC_GEMM = 3,          // KIND_GEMM, EPI_NONE
   TC_SPEC_GEMM_SOFTMAX = 4,  // KIND_GEMM, EPI_ROWSTATS / EPI_SOFTMAX
   TC_SPEC_GEMM_DSOFTMAX = 5, // KIND_GEMM, EPI_DSOFTMAX
-  TC_NUM_SPECS = 6
+  TC_SPEC_CONV_SWAP_GNB = 6, // TC_SPEC_CONV_SWAP whose fp16 epilogue also produces the GroupNorm-backward sums (gnb_*); no residual,
+                             // no forward statistics, no staged / generic epilogue in this instance (register budget)
+  TC_NUM_SPECS = 7
 };
 // Epilogue warps per CTA (after warp 0 = TMA producer, warp 1 = MMA issuer): two per TMEM lane quadrant, half the accumulator
 // columns each. The softmax-backward instance (its epilogue streams a P tile from HBM and a dS tile back) runs 16: four per
@@ -75,6 +83,17 @@ struct TcParams {
   // CONV (swapped roles): byte offset (from the 1024-aligned shared-memory base) of the 8 x 2 KiB per-warp staging
   // buffers the epilogue transposes 32 pixels x 32 channels through, so that the 16-bit results leave as 16-byte vector
   // stores (and the residual arrives as 16-byte vector loads); 0 = scalar 2-byte path.
+  // CONV (swapped roles, fp16 fast epilogue; the dgrad that produces a GroupNorm+SiLU output gradient): the two sums of the
+  // GroupNorm BACKWARD -- per (pixel box, channel): sum dy', sum dy' xhat with dy' = dy * silu'(gamma xhat + beta), dy = the value
+  // this epilogue STORES, xhat from the GroupNorm input gnb_x (same NHWC layout as D) and gnb_stats [image][group](mean, rstd)
+  // -- in packed half2 over pixel pairs like csrc/groupnorm.cu's gn_reduce_h2_kernel, written to
+  // gnb_part[((image * boxes + box) * n_valid + channel) * 2]. The standalone reduce pass over x and dy disappears.
+  const void* gnb_x;
+  const float* gnb_stats;
+  const float* gnb_gamma;
+  const float* gnb_beta;
+  float* gnb_part;
+  int gnb_cpg;  // channels per group
   int epi_off;
   int res_prefetch;  // staged residual epilogue: L2-prefetch the tile's residual lines at tile start (ODVAE_RES_PREFETCH)
   // GEMM with a stationary B panel (K <= 256, both operands K-major): a CTA walks RUNS of bstat_mt consecutive m-tiles

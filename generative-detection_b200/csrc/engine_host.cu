@@ -17,7 +17,7 @@ namespace odvae {  // tc_engine_inst<N>.cu
   cudaError_t tc_engine_launch_##N(int grid, size_t smem, cudaStream_t st, const CUtensorMap& tmA, \
                                    const CUtensorMap& tmB, const TcParams& p);
 ODVAE_DECL_TC_LAUNCH(0) ODVAE_DECL_TC_LAUNCH(1) ODVAE_DECL_TC_LAUNCH(2)
-ODVAE_DECL_TC_LAUNCH(3) ODVAE_DECL_TC_LAUNCH(4) ODVAE_DECL_TC_LAUNCH(5)
+ODVAE_DECL_TC_LAUNCH(3) ODVAE_DECL_TC_LAUNCH(4) ODVAE_DECL_TC_LAUNCH(5) ODVAE_DECL_TC_LAUNCH(6)
 #undef ODVAE_DECL_TC_LAUNCH
 }  // namespace odvae
 
@@ -264,7 +264,10 @@ static int launch_tc(EngineDesc& d, cudaStream_t stream) {
   // the instance of tc_engine_kernel<SPEC> compiled for this (kind, operand roles, epilogue)
   int spec;
   if (p.kind == KIND_CONV) {
-    spec = p.swap ? TC_SPEC_CONV_SWAP : TC_SPEC_CONV;
+    spec = p.swap ? (p.gnb_part != nullptr ? TC_SPEC_CONV_SWAP_GNB : TC_SPEC_CONV_SWAP) : TC_SPEC_CONV;
+    if (p.gnb_part != nullptr && !(p.swap && TC_FAST_EPI && p.out_mode == OUT_F16 && p.oX == 128 && p.residual == nullptr &&
+                                   p.gn_part == nullptr))
+      return ODVAE_ERR_SHAPE;  // the fused GroupNorm-backward sums exist in the fp16 fast epilogue only
   } else if (p.kind == KIND_WGRAD) {
     spec = TC_SPEC_WGRAD;
   } else {
@@ -273,7 +276,8 @@ static int launch_tc(EngineDesc& d, cudaStream_t stream) {
   if (p.kind != KIND_GEMM && (p.epi != EPI_NONE || (p.swap && p.kind != KIND_CONV))) return ODVAE_ERR_SHAPE;
   typedef cudaError_t (*LaunchFn)(int, size_t, cudaStream_t, const CUtensorMap&, const CUtensorMap&, const TcParams&);
   static const LaunchFn launchers[TC_NUM_SPECS] = {tc_engine_launch_0, tc_engine_launch_1, tc_engine_launch_2,
-                                                   tc_engine_launch_3, tc_engine_launch_4, tc_engine_launch_5};
+                                                   tc_engine_launch_3, tc_engine_launch_4, tc_engine_launch_5,
+                                                   tc_engine_launch_6};
   const cudaError_t attr_err = launchers[spec](grid, smem, stream, tmA, tmB, p);
   if (attr_err != cudaSuccess) {
     set_last_cuda_error(attr_err, "cudaFuncSetAttribute(tc_engine_kernel)");

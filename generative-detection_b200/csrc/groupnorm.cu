@@ -332,6 +332,59 @@ __global__ void gn_bwd_finalize_b_kernel(const float* __restrict__ AB, float* __
   dgamma[c] = accumulate ? dgamma[c] + bb : bb;
 }
 
+// backward finalize from PER-BOX partials (the sums a dgrad epilogue produced, tc_engine.cuh gnb_*: part[(b * nbox + box) * C + c] =
+// (sum dy', sum dy' xhat), 512 boxes per 256 x 256 image): grid (image, group blocks), one warp per group; lane = (channel of the
+// group, box phase); four independent chains per lane, fixed-order xor-shuffle trees. Writes AB[b][c] and coef[b][g] like
+// gn_bwd_finalize_a_kernel.
+__global__ void gn_bwd_finalize_boxes_kernel(const float* __restrict__ part, const float* __restrict__ stats,
+                                             const float* __restrict__ gamma, float* __restrict__ AB,
+                                             float* __restrict__ coef, int nbox, int HW, int C, int G) {
+  const int b = blockIdx.x;
+  const int cpg = C / G;  // power of two <= 32 (host-checked)
+  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31, nwarps = blockDim.x >> 5;
+  const int j = lane % cpg, s0 = lane / cpg, step = 32 / cpg;
+  for (int g = blockIdx.y * nwarps + warp; g < G; g += gridDim.y * nwarps) {
+    const float2* p2 = reinterpret_cast<const float2*>(part) + static_cast<long long>(b) * nbox * C + g * cpg + j;
+    float a[4] = {0.0f, 0.0f, 0.0f, 0.0f}, bb[4] = {0.0f, 0.0f, 0.0f, 0.0f};
+    int sp = s0;
+    for (; sp + 3 * step < nbox; sp += 4 * step) {
+#pragma unroll
+      for (int u = 0; u < 4; ++u) {
+        const float2 v = __ldg(p2 + static_cast<long long>(sp + u * step) * C);
+        a[u] += v.x;
+        bb[u] += v.y;
+      }
+    }
+    for (; sp < nbox; sp += step) {
+      const float2 v = __ldg(p2 + static_cast<long long>(sp) * C);
+      a[0] += v.x;
+      bb[0] += v.y;
+    }
+    float sa = (a[0] + a[1]) + (a[2] + a[3]), sb = (bb[0] + bb[1]) + (bb[2] + bb[3]);
+    for (int o = cpg; o < 32; o <<= 1) {  // box phases of the same channel
+      sa += __shfl_xor_sync(0xffffffffu, sa, o);
+      sb += __shfl_xor_sync(0xffffffffu, sb, o);
+    }
+    if (lane < cpg) {
+      AB[(static_cast<long long>(b) * C + g * cpg + j) * 2] = sa;
+      AB[(static_cast<long long>(b) * C + g * cpg + j) * 2 + 1] = sb;
+    }
+    const float gm = __ldg(gamma + g * cpg + j);
+    float ga = gm * sa, gb = gm * sb;
+    for (int o = 1; o < cpg; o <<= 1) {  // channels of the group
+      ga += __shfl_xor_sync(0xffffffffu, ga, o);
+      gb += __shfl_xor_sync(0xffffffffu, gb, o);
+    }
+    if (lane == 0) {
+      const float mean = stats[(static_cast<long long>(b) * G + g) * 2];
+      const float rstd = stats[(static_cast<long long>(b) * G + g) * 2 + 1];
+      const float inv_n = 1.0f / (static_cast<float>(cpg) * HW);
+      coef[(static_cast<long long>(b) * G + g) * 2] = -rstd * rstd * gb * inv_n;
+      coef[(static_cast<long long>(b) * G + g) * 2 + 1] = rstd * (mean * rstd * gb - ga) * inv_n;
+    }
+  }
+}
+
 // The same sums inside the apply kernels (one launch less per GroupNorm backward: 67 per train step): the first
 // ceil(C / 32) CTAs of the grid (in linear order) each own 32 channels; warp w adds images w, w + 8, ... and warp 0 combines
 // the eight partials in a fixed order before the CTA starts on its share of dx. AB == nullptr: nothing to do.
@@ -1261,6 +1314,37 @@ int odvae_groupnorm_bwd(const void* x, const float* stats, const float* gamma, c
 #undef GN_LAUNCH_APPLY_H2
 #undef GN_LAUNCH_APPLY
   return check_launch("gn_bwd_apply_kernel");
+}
+
+// GroupNorm(+SiLU) backward whose two sums arrive as per-box partials from the dgrad that produced dy (odvae_conv2d_dgrad_gnbwd):
+// finalize (coefficients, per-image channel sums) + ONE pass over x and dy (apply, dgamma / dbeta summed by its first CTAs).
+// fp16 x and fp16 gradients, SiLU on, channels per group a power of two <= 32.
+int odvae_groupnorm_bwd_from_partials(const void* x, const float* stats, const float* gamma, const float* beta,
+                                      const void* dy, const void* dx_add, void* dx, float* dgamma, float* dbeta,
+                                      const float* part, int nbox, int B, int HW, int C, int G, int accumulate,
+                                      float pgrad_scale, int32_t* overflow_flags, void* workspace, size_t ws_bytes,
+                                      void* stream) {
+  cudaStream_t st = static_cast<cudaStream_t>(stream);
+  if (!gn_shape_ok(C, G, 8) || !GN_H2) return ODVAE_ERR_SHAPE;
+  const int cpg = C / G;
+  if (cpg > 32 || (cpg & (cpg - 1)) != 0 || nbox < 1) return ODVAE_ERR_SHAPE;
+  if (ws_bytes < odvae_groupnorm_workspace_bytes(B, HW, C, G) - 256) return ODVAE_ERR_WORKSPACE;
+  float* wsf = reinterpret_cast<float*>(workspace);
+  float* AB = wsf + static_cast<size_t>(B) * gn_ws_nsplit(B, HW) * C * 2;
+  float* coef = AB + static_cast<size_t>(B) * C * 2;
+  gn_bwd_finalize_boxes_kernel<<<dim3(B, (G + 7) / 8), 256, 0, st>>>(part, stats, gamma, AB, coef, nbox, HW, C, G);
+  int s = check_launch("gn_bwd_finalize_boxes_kernel");
+  if (s != ODVAE_OK) return s;
+  dim3 grid2(gn_apply_blocks(B, HW, C, 8), B);
+  if (dx_add)
+    gn_bwd_apply_h2_kernel<true, true><<<grid2, GN_THREADS, 0, st>>>(
+        reinterpret_cast<const __half*>(x), reinterpret_cast<const __half*>(dy), reinterpret_cast<const __half*>(dx_add), stats,
+        gamma, beta, coef, reinterpret_cast<__half*>(dx), HW, C, G, overflow_flags, AB, dgamma, dbeta, B, accumulate, pgrad_scale);
+  else
+    gn_bwd_apply_h2_kernel<true, false><<<grid2, GN_THREADS, 0, st>>>(
+        reinterpret_cast<const __half*>(x), reinterpret_cast<const __half*>(dy), nullptr, stats, gamma, beta, coef,
+        reinterpret_cast<__half*>(dx), HW, C, G, overflow_flags, AB, dgamma, dbeta, B, accumulate, pgrad_scale);
+  return check_launch("gn_bwd_apply_h2_kernel");
 }
 
 }  // extern "C"

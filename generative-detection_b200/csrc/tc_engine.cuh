@@ -106,10 +106,11 @@ tc_engine_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant_
                  const __grid_constant__ TcParams p) {
   // The operation kind, the operand roles and the epilogue are compile-time constants of each instance: every mode gets
   // its own register allocation (the monolithic kernel spilled at the 168-register cap of a 320-thread CTA).
-  constexpr int kKind = SPEC <= TC_SPEC_CONV_SWAP ? KIND_CONV : (SPEC == TC_SPEC_WGRAD ? KIND_WGRAD : KIND_GEMM);
-  constexpr bool kSwap = SPEC == TC_SPEC_CONV_SWAP;
+  constexpr bool kGnb = SPEC == TC_SPEC_CONV_SWAP_GNB;
+  constexpr int kKind = (SPEC <= TC_SPEC_CONV_SWAP || kGnb) ? KIND_CONV : (SPEC == TC_SPEC_WGRAD ? KIND_WGRAD : KIND_GEMM);
+  constexpr bool kSwap = SPEC == TC_SPEC_CONV_SWAP || kGnb;
   constexpr int kEpiThreads = 32 * tc_epi_warps(SPEC);
-  const int epi = SPEC <= TC_SPEC_GEMM ? static_cast<int>(EPI_NONE)
+  const int epi = (SPEC <= TC_SPEC_GEMM || kGnb) ? static_cast<int>(EPI_NONE)
                   : SPEC == TC_SPEC_GEMM_DSOFTMAX ? static_cast<int>(EPI_DSOFTMAX)
                   : (p.epi == EPI_ROWSTATS ? static_cast<int>(EPI_ROWSTATS) : static_cast<int>(EPI_SOFTMAX));
   extern __shared__ __align__(1024) uint8_t smem_raw[];
@@ -540,14 +541,30 @@ tc_engine_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant_
         const float bias = (p.bias != nullptr && ch_ok) ? __ldg(p.bias + n) : 0.0f;
         const bool halfp_rt = p.out_mode == OUT_F16;
         uint16_t* D16 = reinterpret_cast<uint16_t*>(p.D);
-        const uint16_t* R16 = reinterpret_cast<const uint16_t*>(p.residual);
+        const uint16_t* R16 = kGnb ? nullptr : reinterpret_cast<const uint16_t*>(p.residual);
         const long long base0 = static_cast<long long>(pb_b) * p.oB + p.o0 + n;
         const long long sx_rt = p.oX;
         const long long sx = sx_rt;
         float gs0 = 0.0f, gs1 = 0.0f, gq0 = 0.0f, gq1 = 0.0f;  // fused GroupNorm statistics (two chains each)
+        // fused GroupNorm-backward sums (engine_desc.h gnb_*): this thread's channel constants for the tile's image
+        const bool gnb = kGnb && ch_ok;
+        const uint16_t* X16 = reinterpret_cast<const uint16_t*>(p.gnb_x);
+        __half2 b_muh, b_rs, b_k0, b_hg, b_hb;
+        float bs0 = 0.0f, bs1 = 0.0f;
+        if (gnb) {
+          const int G = p.n_valid / p.gnb_cpg;
+          const float* st2 = p.gnb_stats + (static_cast<long long>(pb_b) * G + n / p.gnb_cpg) * 2;
+          const float mean = __ldg(st2), rstd = __ldg(st2 + 1);
+          const float muh = __half2float(__float2half_rn(mean));
+          b_muh = __float2half2_rn(muh);
+          b_rs = __float2half2_rn(rstd);
+          b_k0 = __float2half2_rn((muh - mean) * rstd);
+          b_hg = __float2half2_rn(0.5f * __ldg(p.gnb_gamma + n));
+          b_hb = __float2half2_rn(0.5f * __ldg(p.gnb_beta + n));
+        }
         // staged path: the warp's 32 pixels x 32 channels go through a private 2 KiB buffer ([pixel][32 channels], 64-byte
         // rows) and leave as 16-byte vectors: lane l, vector k covers pixel (l >> 2) + 8 k, channels 8 (l & 3) .. + 7
-        uint8_t* stg = p.epi_off ? smem + p.epi_off + (warp - 2) * 2048 : nullptr;
+        uint8_t* stg = (!kGnb && p.epi_off) ? smem + p.epi_off + (warp - 2) * 2048 : nullptr;
         const int vch = m0 + q * 32 + (lane & 3) * 8;  // first channel of this lane's vectors
         uint4 rv[4] = {};  // residual vectors of the batch about to be emitted
         auto load_rv = [&](int pi0) {
@@ -636,24 +653,48 @@ tc_engine_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant_
             float f[32];
 #pragma unroll
             for (int i = 0; i < 32; ++i) f[i] = fmaf(__uint_as_float(v[i]), p.alpha, bias);
+            uint16_t rr[32];  // residual values, or (gnb) the GroupNorm input at the same positions
             if (R16 != nullptr) {
-              uint16_t rr[32];
 #pragma unroll
               for (int i = 0; i < 32; ++i) rr[i] = __ldg(R16 + at(i));
 #pragma unroll
               for (int i = 0; i < 32; ++i) f[i] += unpack_16x2(static_cast<uint32_t>(rr[i]), halfp).x;
+            } else if (kFast && gnb) {
+#pragma unroll
+              for (int i = 0; i < 32; ++i) rr[i] = __ldg(X16 + at(i));
             }
+            __half2 ba0 = __float2half2_rn(0.0f), ba1 = __float2half2_rn(0.0f);
 #pragma unroll
             for (int i = 0; i < 32; i += 2) {
               const uint32_t pk = pack_16x2(f[i], f[i + 1], halfp);
               D16[at(i)] = static_cast<uint16_t>(pk & 0xffffu);
               D16[at(i + 1)] = static_cast<uint16_t>(pk >> 16);
-              if (p.gn_part != nullptr) {  // statistics of the STORED (rounded) values, as the separate pass sees them
+              if (!kGnb && p.gn_part != nullptr) {  // statistics of the STORED (rounded) values, as the separate pass sees them
                 const float2 r = unpack_16x2(pk, halfp);
                 gs0 += r.x;
                 gq0 = fmaf(r.x, r.x, gq0);
                 gs1 += r.y;
                 gq1 = fmaf(r.y, r.y, gq1);
+              }
+              if (kFast && gnb) {
+                // GroupNorm backward sums on the pair (two pixels of this thread's channel), dy = the stored pair
+                const uint32_t xw = static_cast<uint32_t>(rr[i]) | (static_cast<uint32_t>(rr[i + 1]) << 16);
+                const __half2 xh = __hfma2(__hsub2(*reinterpret_cast<const __half2*>(&xw), b_muh), b_rs, b_k0);
+                const __half2 uh = __hfma2(xh, b_hg, b_hb);
+                uint32_t tw, uw = *reinterpret_cast<const uint32_t*>(&uh);
+                asm("tanh.approx.f16x2 %0, %1;" : "=r"(tw) : "r"(uw));
+                const __half2 t = *reinterpret_cast<const __half2*>(&tw);
+                const __half2 wq = __hfma2(uh, __hfma2(__hneg2(t), t, __float2half2_rn(1.0f)), t);
+                const __half2 inv = __float2half2_rn(1.0f / 128.0f);
+                const __half2 ds = __hmul2(*reinterpret_cast<const __half2*>(&pk), __hfma2(wq, inv, inv));  // dy' / 64
+                ba0 = __hadd2(ba0, ds);
+                ba1 = __hfma2(ds, xh, ba1);
+                if ((i & 6) == 6) {  // every 4 pairs: flush the half2 partial sums into fp32
+                  const float2 f0 = __half22float2(ba0), f1 = __half22float2(ba1);
+                  bs0 += f0.x + f0.y;
+                  bs1 += f1.x + f1.y;
+                  ba0 = ba1 = __float2half2_rn(0.0f);
+                }
               }
             }
           }
@@ -694,15 +735,21 @@ tc_engine_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant_
         };
         if (TC_FAST_EPI && il_rt)  // (the host turns halo == 2 on only where the fast path's conditions hold)
           drain(std::true_type{}, std::true_type{});
-        else if (TC_FAST_EPI && halfp_rt && sx_rt == 128 && stg == nullptr && p.out_mode != OUT_NCHW_F32)
-          drain(std::true_type{}, std::false_type{});
+        else if (kGnb || (TC_FAST_EPI && halfp_rt && sx_rt == 128 && stg == nullptr && p.out_mode != OUT_NCHW_F32))
+          drain(std::true_type{}, std::false_type{});  // (the host picks the GNB instance only under these conditions)
         else
           drain(std::false_type{}, std::false_type{});
-        if (p.gn_part != nullptr && ch_ok) {
+        if (!kGnb && p.gn_part != nullptr && ch_ok) {
           const int boxes = p.tiles_x * p.tiles_y;  // pixel boxes per image
           const int box = 2 * tc.n_tile + half - pb_b * boxes;
           float2* dst = reinterpret_cast<float2*>(p.gn_part) + (static_cast<long long>(pb_b) * boxes + box) * p.n_valid + n;
           *dst = make_float2(gs0 + gs1, gq0 + gq1);
+        }
+        if (gnb) {
+          const int boxes = p.tiles_x * p.tiles_y;
+          const int box = 2 * tc.n_tile + half - pb_b * boxes;
+          float2* dst = reinterpret_cast<float2*>(p.gnb_part) + (static_cast<long long>(pb_b) * boxes + box) * p.n_valid + n;
+          *dst = make_float2(64.0f * bs0, 64.0f * bs1);
         }
       } else if (epi != EPI_NONE) {
         // ---- fused attention epilogues (KIND_GEMM, BN = 256; one accumulator row and kCols columns per thread) ----

@@ -554,6 +554,34 @@ def conv_dgrad_raw(dy, spec, w, in_hw, dx_add=None):
     return dx
 
 
+def conv_dgrad_gnbwd_raw(dy, spec, w, in_hw, gn_x, gn_stats, gamma, beta):
+    """dgrad whose epilogue also produces the GroupNorm+SiLU backward sums for the GroupNorm that made this conv's input
+    (include/odvae_b200.h odvae_conv2d_dgrad_gnbwd). -> (dx, (part, nbox)) or None when the shape / mode is not served
+    (uniform fp16 mode, tcgen05 swapped-role tiles of the 128-channel stride-1 convs)."""
+    fmt = format_of(dy, spec)
+    if fmt.grad != F16 or fmt.fwd != F16 or not _GN_BWD_FUSE[0] or gn_x.dtype != torch.float16:
+        return None
+    B, Ho, Wo, CoutP = dy.shape
+    H, W = in_hw
+    if conv_impl(F16, B, H, W, spec.cinp, CoutP, spec.geom) != IMPL_TC or gn_x.shape[-1] != spec.cinp:
+        return None
+    key = (B, H, W, spec.cinp, CoutP, spec.geom)
+    nbytes = _GNBWD_BYTES.get(key)
+    if nbytes is None:
+        nbytes = _GNBWD_BYTES[key] = call("conv2d_dgrad_gnbwd_workspace_bytes", B, H, W, spec.cinp, CoutP, spec.geom, GROUPS)
+    if nbytes == 0:
+        return None
+    dx = torch.empty(B, H, W, spec.cinp, dtype=dy.dtype, device=dy.device)
+    part = torch.empty(nbytes // 4, dtype=torch.float32, device=dy.device)
+    call("conv2d_dgrad_gnbwd", dy, spec.w_dgrad(w, F16, CoutP), dx, gn_x, gn_stats, gamma.detach(), beta.detach(), part, nbytes,
+         B, H, W, spec.cinp, CoutP, spec.geom, GROUPS, F16)
+    return dx, (part, nbytes // (8 * B * spec.cinp))
+
+
+_GN_BWD_FUSE = [os.environ.get("ODVAE_GN_BWD_FUSE", "1") != "0"]
+_GNBWD_BYTES = {}
+
+
 def conv_wgrad_raw(x, dy, spec, w, b):
     """x must already be in the GRADIENT format (mixed mode: the bf16 copy of the fp16 forward operand).
     -> (dw, db) as autograd return values (None where written straight into the gradient arena)."""
@@ -638,7 +666,9 @@ def gn_apply_pair(x, stats, gamma, beta, silu, fmt):
     return y, y
 
 
-def gn_bwd_raw(x, stats, gamma, beta, dy, silu, dx_add=None, x_code=None, g_code=None, pscale=1.0):
+def gn_bwd_raw(x, stats, gamma, beta, dy, silu, dx_add=None, x_code=None, g_code=None, pscale=1.0, partials=None):
+    """partials = (part, nbox): the two backward sums per pixel box from the dgrad that produced dy (conv_dgrad_gnbwd_raw):
+    no reduce pass over x and dy."""
     B, H, W, C = x.shape
     x_code = act_code(x.dtype) if x_code is None else x_code
     g_code = act_code(dy.dtype) if g_code is None else g_code
@@ -647,6 +677,11 @@ def gn_bwd_raw(x, stats, gamma, beta, dy, silu, dx_add=None, x_code=None, g_code
     dbeta, b_direct = _new_grad(beta)
     nbytes = call("groupnorm_workspace_bytes", B, H * W, C, GROUPS)
     ws = workspace(nbytes, x.device, "gn")
+    if partials is not None:
+        assert silu and x_code == F16 and g_code == F16
+        call("groupnorm_bwd_from_partials", x, stats, gamma.detach(), beta.detach(), dy, dx_add, dx, dgamma, dbeta, partials[0],
+             partials[1], B, H * W, C, GROUPS, 0, float(pscale), overflow_flags(x.device), ws, ws.numel())
+        return dx, _ret(dgamma, g_direct), _ret(dbeta, b_direct)
     call("groupnorm_bwd", x, stats, gamma.detach(), beta.detach(), dy, dx_add, dx, dgamma, dbeta, B, H * W, C,
          GROUPS, 1 if silu else 0, x_code, g_code, 0, float(pscale),
          overflow_flags(x.device) if g_code == F16 else None, ws, ws.numel())
@@ -935,15 +970,19 @@ class ResBlock(torch.autograd.Function):
         else:
             dsc = dout
         dev = x.device
-        da2 = conv_dgrad_raw(dout, blk.spec2, w2, hw)
+        # (128-channel layers, fp16 mode: the dgrad epilogue also produces the GroupNorm backward's two sums -> no reduce pass)
+        fused = conv_dgrad_gnbwd_raw(dout, blk.spec2, w2, hw, h1, s2, g2, b2)
+        da2, part2 = fused if fused is not None else (conv_dgrad_raw(dout, blk.spec2, w2, hw), None)
         with side_stream(dev):  # co-runs with the GroupNorm backward below
             dw2, dc2b = conv_wgrad_raw(a2, dout, blk.spec2, w2, c2b)
         ps = 1.0 / gs_of(blk)
-        dh1, dg2, db2 = gn_bwd_raw(h1, s2, g2, b2, da2, True, x_code=fmt.fwd, g_code=fmt.grad, pscale=ps)
-        da1 = conv_dgrad_raw(dh1, blk.spec1, w1, hw)
+        dh1, dg2, db2 = gn_bwd_raw(h1, s2, g2, b2, da2, True, x_code=fmt.fwd, g_code=fmt.grad, pscale=ps, partials=part2)
+        fused = conv_dgrad_gnbwd_raw(dh1, blk.spec1, w1, hw, x, s1, g1, b1)
+        da1, part1 = fused if fused is not None else (conv_dgrad_raw(dh1, blk.spec1, w1, hw), None)
         with side_stream(dev):
             dw1, dc1b = conv_wgrad_raw(a1, dh1, blk.spec1, w1, c1b)
-        dx, dg1, db1 = gn_bwd_raw(x, s1, g1, b1, da1, True, dx_add=dsc, x_code=fmt.fwd, g_code=fmt.grad, pscale=ps)
+        dx, dg1, db1 = gn_bwd_raw(x, s1, g1, b1, da1, True, dx_add=dsc, x_code=fmt.fwd, g_code=fmt.grad, pscale=ps,
+                                  partials=part1)
         # the side stream read a1, a2, dout, dh1: wait for it here, or (arena mode) let it run on and join at the end of backward
         side_release(dev, dw1 is None and dw2 is None and (c1b is None or dc1b is None) and (c2b is None or dc2b is None),
                      a1, a2, dout, dh1)

@@ -194,6 +194,22 @@ int odvae_groupnorm_bwd(const void* x, const float* stats, const float* gamma, c
                         const void* dx_add, void* dx, float* dgamma, float* dbeta, int B, int HW, int C, int G,
                         int silu, int act_dtype, int grad_dtype, int accumulate, float pgrad_scale, int32_t* overflow_flags, void* workspace, size_t ws_bytes,
                         void* stream);
+/* GroupNorm+SiLU backward with the reduce pass fused into the producing dgrad (model.py:121-141 backward: conv -> GroupNorm ->
+ * SiLU chains of the 128-channel ResnetBlocks): odvae_conv2d_dgrad_gnbwd is odvae_conv2d_dgrad (stride-1 geometries, fp16) that
+ * ALSO writes, per 128-pixel box and channel, (sum dy', sum dy' xhat) for the GroupNorm whose OUTPUT gradient it produces --
+ * gn_x = that GroupNorm's input (same NHWC layout as dx), gn_stats / gamma / beta as in odvae_groupnorm_bwd, part = fp32
+ * [B * boxes * CinP * 2] with boxes = H * W / 128. ..._workspace_bytes returns part's size, or 0 when the shape is not served
+ * (tcgen05 swapped-role tiles with a pixel stride of 128 elements only). odvae_groupnorm_bwd_from_partials then finishes the
+ * backward (finalize + one pass over x and dy); same outputs as odvae_groupnorm_bwd to fp16 rounding of the elementwise chain. */
+size_t odvae_conv2d_dgrad_gnbwd_workspace_bytes(int B, int H, int W, int CinP, int CoutP, int geom, int G);
+int odvae_conv2d_dgrad_gnbwd(const void* dy, const void* w_packed_dgrad, void* dx, const void* gn_x, const float* gn_stats,
+                             const float* gamma, const float* beta, float* part, size_t part_bytes, int B, int H, int W,
+                             int CinP, int CoutP, int geom, int G, int act_dtype, void* stream);
+int odvae_groupnorm_bwd_from_partials(const void* x, const float* stats, const float* gamma, const float* beta,
+                                      const void* dy, const void* dx_add, void* dx, float* dgamma, float* dbeta,
+                                      const float* part, int nbox, int B, int HW, int C, int G, int accumulate,
+                                      float pgrad_scale, int32_t* overflow_flags, void* workspace, size_t ws_bytes,
+                                      void* stream);
 
 /* ---------------------------------------------------------------------------------------------
  * Attention core of AttnBlock (model.py:183-198): single head, scale = C^-0.5.

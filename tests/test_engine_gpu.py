@@ -138,6 +138,43 @@ def test_conv_halo_slabs_match_tap_gather(dtype, B, H, W):
     assert rel_err(outs[0][2], outs[1][2]) < 1e-5
 
 
+@pytest.mark.parametrize("B,H,W", [(2, 256, 256), (3, 128, 128), (1, 64, 512)])
+def test_dgrad_with_fused_groupnorm_backward_sums(B, H, W):
+    """odvae_conv2d_dgrad_gnbwd: the dgrad of a 128-channel 3x3 conv whose fp16 epilogue also produces the GroupNorm+SiLU
+    backward sums per pixel box; odvae_groupnorm_bwd_from_partials then skips the reduce pass. dx of the conv is bit-identical
+    to odvae_conv2d_dgrad; the GroupNorm backward agrees with the two-pass kernels and with torch autograd."""
+    from odvae_b200 import lib, ops
+    C, G = 128, 32
+    torch.manual_seed(11)
+    dy = torch.randn(B, H, W, C, device=DEV).half()
+    gx = (torch.randn(B, H, W, C, device=DEV) * 1.5 + 0.3).half()  # the GroupNorm input
+    add = torch.randn(B, H, W, C, device=DEV).half()
+    gamma = 1 + 0.1 * torch.randn(C, device=DEV)
+    beta = 0.1 * torch.randn(C, device=DEV)
+    w = torch.randn(C, C, 3, 3, device=DEV) / (C * 9) ** 0.5
+    wd = K.pack_conv_weight(w, CONV_3x3_S1, C, C, 1, torch.float16)
+    stats = ops.gn_stats_raw(gx, C)
+    nbytes = lib.call("conv2d_dgrad_gnbwd_workspace_bytes", B, H, W, C, C, CONV_3x3_S1, G)
+    assert nbytes == B * (H * W // 128) * C * 8
+    part = torch.empty(nbytes // 4, device=DEV)
+    dx = torch.empty(B, H, W, C, dtype=torch.float16, device=DEV)
+    lib.call("conv2d_dgrad_gnbwd", dy, wd, dx, gx, stats, gamma, beta, part, nbytes, B, H, W, C, C, CONV_3x3_S1, G, F16)
+    dx_plain = K.conv_dgrad(dy, wd, C, CONV_3x3_S1, IMPL_TC, (H, W))
+    torch.cuda.synchronize()
+    assert torch.equal(dx, dx_plain)
+    nbox = H * W // 128
+    for dx_add in (None, add):
+        a = ops.gn_bwd_raw(gx, stats, gamma, beta, dx, True, dx_add=dx_add, partials=(part, nbox))
+        b = ops.gn_bwd_raw(gx, stats, gamma, beta, dx, True, dx_add=dx_add)
+        torch.cuda.synchronize()
+        for u, v in zip(a, b):
+            assert rel_err(u, v) < 2e-3
+    xr = gx[:1].float().permute(0, 3, 1, 2).requires_grad_(True)
+    gr, br = gamma.clone().requires_grad_(True), beta.clone().requires_grad_(True)
+    F.silu(F.group_norm(xr, 32, gr, br, eps=1e-6)).backward(dx[:1].float().permute(0, 3, 1, 2))
+    assert rel_err(a[0][:1].float() - add[:1].float(), xr.grad.permute(0, 2, 3, 1)) < 8e-3
+
+
 @pytest.mark.parametrize("impl,dtype", IMPLS2)
 def test_conv_out_nchw_thin(impl, dtype):
     """decoder.conv_out: 128 -> 3 channels written as NCHW fp32 (weights padded to 16 rows)."""

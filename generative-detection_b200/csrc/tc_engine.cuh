@@ -699,9 +699,10 @@ tc_engine_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant_
             }
           }
         };
-        if (R16 != nullptr) {
+        const uint16_t* P16 = kGnb ? X16 : R16;  // what the epilogue will read per element: residual, or the GroupNorm input
+        if (P16 != nullptr) {
           if (stg != nullptr) load_rv(0);  // in flight while the accumulator completes
-          if (p.res_prefetch && ch_ok) {
+          if ((kGnb || p.res_prefetch) && ch_ok) {
             // this warp's residual columns for the whole tile (staged path: the three later 32-pixel batches): pull their lines
             // into L2 now -- the tile's MMAs take ~6 us -- so that the epilogue's loads see L2 latency, not DRAM latency
 #pragma unroll
@@ -710,7 +711,7 @@ tc_engine_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant_
               const int pi = 32 * j + lane;
               const int yy = il_rt ? pb_y + (pi & 1) : pb_y + (pi >> p.bw_log2);
               const int xx = il_rt ? pb_x + (pi >> 1) : pb_x + (pi & ((1 << p.bw_log2) - 1));
-              const uint16_t* a = R16 + static_cast<long long>(pb_b) * p.oB + p.o0 + (m0 + q * 32) +
+              const uint16_t* a = P16 + static_cast<long long>(pb_b) * p.oB + p.o0 + (m0 + q * 32) +
                                   static_cast<long long>(yy) * p.oY + static_cast<long long>(xx) * sx;
               asm volatile("prefetch.global.L2 [%0];" ::"l"(a));
             }
